@@ -1,0 +1,384 @@
+// Flat-slab kernels: everything that the reference does as per-tensor Python loops over a
+// state_dict is one launch over the flat parameter slab here.
+//
+//   nidt_masked_sgd_step     clip_grad_norm_(10) + SGD(momentum, wd) + `w *= mask`
+//                            (ref: sailentgrads/my_model_trainer.py:209,224-231)
+//   nidt_weighted_aggregate  w_g = sum_i (n_i/sum n) w_i [* mask]   (ref: sailentgrads_api.py:212-227)
+//   nidt_saliency_accumulate scores += |g*w|                          (ref: snip.py:60-71)
+//   nidt_global_topk_mask    sum -> /sum -> k-th largest -> mask      (ref: snip.py:80-116)
+//   nidt_count_nonzero / nidt_hamming / nidt_sq_dist                  (ref: model_trainer.py:49-53, slim_util.py:10-19)
+#include "common.cuh"
+#include <cooperative_groups.h>
+#include <stdarg.h>
+#include <string.h>
+
+namespace cg = cooperative_groups;
+
+static thread_local char g_err[1024] = "";
+void nidt_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+NIDT_API const char* nidt_last_error() { return g_err; }
+NIDT_API int nidt_abi_version() { return 1; }
+
+namespace nidt {
+
+constexpr int kFlatThreads = 256;
+constexpr int kNormBlocks = 2 * kNumSMs;  // fixed => the partial-sum tree is launch-invariant
+
+// ---------------------------------------------------------------------------- grad norm
+__global__ void __launch_bounds__(kFlatThreads) sq_norm_partials_kernel(const float* __restrict__ g, int64_t n, float* __restrict__ partials) {
+    __shared__ float red[kFlatThreads / 32];
+    const int64_t n4 = n >> 2;
+    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
+    for (int64_t i = (int64_t)blockIdx.x * kFlatThreads + threadIdx.x; i < n4; i += (int64_t)gridDim.x * kFlatThreads) {
+        float4 v = ld4(g + 4 * i);
+        acc0 = fmaf(v.x, v.x, acc0); acc1 = fmaf(v.y, v.y, acc1);
+        acc2 = fmaf(v.z, v.z, acc2); acc3 = fmaf(v.w, v.w, acc3);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+        for (int64_t i = n4 << 2; i < n; ++i) acc0 = fmaf(g[i], g[i], acc0);
+    float t = block_sum<kFlatThreads>((acc0 + acc1) + (acc2 + acc3), red);
+    if (threadIdx.x == 0) partials[blockIdx.x] = t;
+}
+
+// --------------------------------------------------------------------------- masked SGD
+__global__ void __launch_bounds__(kFlatThreads) masked_sgd_kernel(
+    float* __restrict__ w, const float* __restrict__ g, float* __restrict__ mom, const float* __restrict__ mask,
+    int64_t n, float lr, float mu, float wd, float clip, int first_step,
+    const float* __restrict__ partials, int n_partials, float* __restrict__ norm_out) {
+    __shared__ float red[kFlatThreads / 32];
+    float coef = 1.f;
+    if (partials != nullptr) {
+        float p = 0.f;
+        for (int i = threadIdx.x; i < n_partials; i += kFlatThreads) p += partials[i];
+        const float total = sqrtf(block_sum<kFlatThreads>(p, red));
+        if (clip > 0.f) coef = fminf(clip / (total + 1e-6f), 1.f);
+        if (blockIdx.x == 0 && threadIdx.x == 0 && norm_out) *norm_out = total;
+    }
+    const int64_t n4 = n >> 2;
+    for (int64_t i = (int64_t)blockIdx.x * kFlatThreads + threadIdx.x; i < n4; i += (int64_t)gridDim.x * kFlatThreads) {
+        float4 wv = ld4(w + 4 * i);
+        float4 gv = ld4(g + 4 * i);
+        float4 d;
+        d.x = fmaf(wd, wv.x, gv.x * coef); d.y = fmaf(wd, wv.y, gv.y * coef);
+        d.z = fmaf(wd, wv.z, gv.z * coef); d.w = fmaf(wd, wv.w, gv.w * coef);
+        if (mom != nullptr) {
+            if (!first_step) {
+                float4 mv = ld4(mom + 4 * i);
+                d.x = fmaf(mu, mv.x, d.x); d.y = fmaf(mu, mv.y, d.y);
+                d.z = fmaf(mu, mv.z, d.z); d.w = fmaf(mu, mv.w, d.w);
+            }
+            st4(mom + 4 * i, d);
+        }
+        wv.x = fmaf(-lr, d.x, wv.x); wv.y = fmaf(-lr, d.y, wv.y);
+        wv.z = fmaf(-lr, d.z, wv.z); wv.w = fmaf(-lr, d.w, wv.w);
+        if (mask != nullptr) {
+            float4 mk = ld4(mask + 4 * i);
+            wv.x *= mk.x; wv.y *= mk.y; wv.z *= mk.z; wv.w *= mk.w;
+        }
+        st4(w + 4 * i, wv);
+    }
+}
+
+// -------------------------------------------------------------------------- aggregation
+constexpr int kMaxAggSrc = 64;
+struct AggArgs {
+    const float* src[kMaxAggSrc];
+    float wt[kMaxAggSrc];
+    int k;
+};
+
+// out = sum_i wt[i]*src[i] in list order, multiply and add kept separate (no FMA contraction)
+// so that the result is bit-identical to the reference's Python loop; optional `accumulate`
+// continues a sum that was split over several launches (> kMaxAggSrc clients).
+__global__ void __launch_bounds__(kFlatThreads) weighted_aggregate_kernel(
+    float* __restrict__ out, const AggArgs a, const float* __restrict__ mask, int64_t n_mask, int64_t n, int accumulate, int last) {
+    const int64_t n4 = n >> 2;
+    for (int64_t i = (int64_t)blockIdx.x * kFlatThreads + threadIdx.x; i < n4; i += (int64_t)gridDim.x * kFlatThreads) {
+        float4 acc;
+        int s = 0;
+        if (accumulate) {
+            acc = ld4(out + 4 * i);
+        } else {
+            float4 v = ld4(a.src[0] + 4 * i);
+            const float wt = a.wt[0];
+            acc.x = __fmul_rn(v.x, wt); acc.y = __fmul_rn(v.y, wt); acc.z = __fmul_rn(v.z, wt); acc.w = __fmul_rn(v.w, wt);
+            s = 1;
+        }
+#pragma unroll 4
+        for (; s < a.k; ++s) {
+            float4 v = ld4(a.src[s] + 4 * i);
+            const float wt = a.wt[s];
+            acc.x = __fadd_rn(acc.x, __fmul_rn(v.x, wt)); acc.y = __fadd_rn(acc.y, __fmul_rn(v.y, wt));
+            acc.z = __fadd_rn(acc.z, __fmul_rn(v.z, wt)); acc.w = __fadd_rn(acc.w, __fmul_rn(v.w, wt));
+        }
+        if (last && mask != nullptr && 4 * i < n_mask) {
+            float4 mk = ld4(mask + 4 * i);
+            acc.x *= mk.x; acc.y *= mk.y; acc.z *= mk.z; acc.w *= mk.w;
+        }
+        st4(out + 4 * i, acc);
+    }
+}
+
+// ------------------------------------------------------------------------------ saliency
+__global__ void __launch_bounds__(kFlatThreads) saliency_accumulate_kernel(
+    float* __restrict__ scores, const float* __restrict__ g, const float* __restrict__ w, int64_t n, float scale) {
+    const int64_t n4 = n >> 2;
+    for (int64_t i = (int64_t)blockIdx.x * kFlatThreads + threadIdx.x; i < n4; i += (int64_t)gridDim.x * kFlatThreads) {
+        float4 s = ld4(scores + 4 * i), gv = ld4(g + 4 * i), wv = ld4(w + 4 * i);
+        s.x = fmaf(scale, fabsf(gv.x * wv.x), s.x); s.y = fmaf(scale, fabsf(gv.y * wv.y), s.y);
+        s.z = fmaf(scale, fabsf(gv.z * wv.z), s.z); s.w = fmaf(scale, fabsf(gv.w * wv.w), s.w);
+        st4(scores + 4 * i, s);
+    }
+}
+
+// ------------------------------------------------------------------ global top-k -> mask
+// One cooperative launch: (1) sum of the prunable scores (fixed-order block partials), (2) four
+// 8-bit radix-select passes over the fp32 bit pattern of q = s/sum (q >= 0, so the unsigned bit
+// pattern is order preserving) to find the k-th largest q exactly, (3) mask = (q >= thr) on
+// prunable entries, 1 on other real parameters, 0 on slab padding.
+// `flags[i]`: 0 = padding, 1 = real but never pruned (bias / BN affine), 2 = prunable weight.
+constexpr int kTopkThreads = 512;
+struct TopkScratch {           // lives in caller-provided global scratch (zeroed by the kernel)
+    unsigned int hist[4][256];
+    float block_sums[2 * kNumSMs];
+    float threshold;           // out: k-th largest q
+    float norm;                // out: sum of prunable scores
+    unsigned int kept;         // out: number of prunable entries kept
+};
+
+__global__ void __launch_bounds__(kTopkThreads) global_topk_mask_kernel(
+    const float* __restrict__ scores, const unsigned char* __restrict__ flags, float* __restrict__ mask,
+    int64_t n, unsigned long long k, TopkScratch* __restrict__ sc) {
+    cg::grid_group grid = cg::this_grid();
+    __shared__ unsigned int sh_hist[256];
+    __shared__ float red[kTopkThreads / 32];
+    __shared__ unsigned int sh_prefix;
+    __shared__ unsigned long long sh_k;
+    const int64_t tid = (int64_t)blockIdx.x * kTopkThreads + threadIdx.x;
+    const int64_t nth = (int64_t)gridDim.x * kTopkThreads;
+
+    // phase 0: clear scratch, block-partial sums
+    if (blockIdx.x == 0) {
+        for (int i = threadIdx.x; i < 4 * 256; i += kTopkThreads) (&sc->hist[0][0])[i] = 0u;
+        if (threadIdx.x == 0) sc->kept = 0u;
+    }
+    float acc = 0.f;
+    for (int64_t i = tid; i < n; i += nth) acc += (flags[i] == 2) ? scores[i] : 0.f;
+    float bs = block_sum<kTopkThreads>(acc, red);
+    if (threadIdx.x == 0) sc->block_sums[blockIdx.x] = bs;
+    grid.sync();
+
+    float p = 0.f;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += kTopkThreads) p += sc->block_sums[i];
+    const float norm = block_sum<kTopkThreads>(p, red);
+
+    unsigned int prefix = 0u;
+    unsigned long long krem = k;
+    for (int pass = 0; pass < 4; ++pass) {
+        const int shift = 24 - 8 * pass;
+        const unsigned int hi_mask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
+        for (int i = threadIdx.x; i < 256; i += kTopkThreads) sh_hist[i] = 0u;
+        __syncthreads();
+        for (int64_t i = tid; i < n; i += nth) {
+            if (flags[i] == 2) {
+                const unsigned int key = __float_as_uint(__fdiv_rn(scores[i], norm));
+                if ((key & hi_mask) == prefix) atomicAdd(&sh_hist[(key >> shift) & 0xffu], 1u);
+            }
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < 256; i += kTopkThreads)
+            if (sh_hist[i]) atomicAdd(&sc->hist[pass][i], sh_hist[i]);
+        grid.sync();
+        if (threadIdx.x == 0) {
+            unsigned long long cum = 0ull;
+            int d = 255;
+            for (; d > 0; --d) {
+                const unsigned long long c = sc->hist[pass][d];
+                if (cum + c >= krem) break;
+                cum += c;
+            }
+            sh_prefix = prefix | ((unsigned int)d << shift);
+            sh_k = krem - cum;
+        }
+        __syncthreads();
+        prefix = sh_prefix;
+        krem = sh_k;
+    }
+    const float thr = k == 0ull ? __int_as_float(0x7f800000) : __uint_as_float(prefix);
+
+    unsigned int kept = 0u;
+    for (int64_t i = tid; i < n; i += nth) {
+        const unsigned char f = flags[i];
+        float m = 0.f;
+        if (f == 1) m = 1.f;
+        else if (f == 2) {
+            m = (__fdiv_rn(scores[i], norm) >= thr) ? 1.f : 0.f;
+            kept += (unsigned int)m;
+        }
+        mask[i] = m;
+    }
+    kept = (unsigned int)warp_sum_u64(kept);
+    if ((threadIdx.x & 31) == 0 && kept) atomicAdd(&sc->kept, kept);
+    if (tid == 0) { sc->threshold = thr; sc->norm = norm; }
+}
+
+// ----------------------------------------------------------------------------- statistics
+// mode 0: count(a != 0); mode 1: count((a != 0) xor (b != 0)); result added to *out (u64)
+__global__ void __launch_bounds__(kFlatThreads) count_kernel(const float* __restrict__ a, const float* __restrict__ b, int64_t n, int mode,
+                                                             unsigned long long* __restrict__ out) {
+    unsigned long long c = 0ull;
+    for (int64_t i = (int64_t)blockIdx.x * kFlatThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kFlatThreads) {
+        const bool x = a[i] != 0.f;
+        c += mode == 0 ? (unsigned long long)x : (unsigned long long)(x != (b[i] != 0.f));
+    }
+    c = warp_sum_u64(c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
+}
+
+__global__ void __launch_bounds__(kFlatThreads) sq_dist_partials_kernel(const float* __restrict__ a, const float* __restrict__ b, int64_t n,
+                                                                        float* __restrict__ partials) {
+    __shared__ float red[kFlatThreads / 32];
+    float acc = 0.f;
+    for (int64_t i = (int64_t)blockIdx.x * kFlatThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kFlatThreads) {
+        const float d = a[i] - b[i];
+        acc = fmaf(d, d, acc);
+    }
+    float t = block_sum<kFlatThreads>(acc, red);
+    if (threadIdx.x == 0) partials[blockIdx.x] = t;
+}
+
+__global__ void __launch_bounds__(kFlatThreads) sum_partials_kernel(const float* __restrict__ partials, int n, float* __restrict__ out, int take_sqrt) {
+    __shared__ float red[kFlatThreads / 32];
+    float p = 0.f;
+    for (int i = threadIdx.x; i < n; i += kFlatThreads) p += partials[i];
+    float t = block_sum<kFlatThreads>(p, red);
+    if (threadIdx.x == 0) *out = take_sqrt ? sqrtf(t) : t;
+}
+
+// Ditto proximal pull:  w -= lr*lamda*(w - w_ref)
+__global__ void __launch_bounds__(kFlatThreads) prox_pull_kernel(float* __restrict__ w, const float* __restrict__ ref, int64_t n, float coef) {
+    for (int64_t i = (int64_t)blockIdx.x * kFlatThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kFlatThreads)
+        w[i] = fmaf(-coef, w[i] - ref[i], w[i]);
+}
+
+static inline int flat_grid(int64_t n_items) {
+    int64_t b = ceil_div64(n_items, kFlatThreads);
+    const int64_t cap = (int64_t)kNumSMs * 8;
+    return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+}  // namespace nidt
+
+using namespace nidt;
+
+NIDT_API int nidt_norm_scratch_floats() { return kNormBlocks + 4; }
+NIDT_API int nidt_topk_scratch_bytes() { return (int)sizeof(TopkScratch); }
+NIDT_API int nidt_max_agg_sources() { return kMaxAggSrc; }
+
+// scratch: >= nidt_norm_scratch_floats() floats.  norm_out may be null.
+NIDT_API int nidt_masked_sgd_step(float* w, const float* g, float* mom, const float* mask, int64_t n,
+                                    float lr, float momentum, float wd, float clip_norm, int first_step,
+                                    float* scratch, float* norm_out, void* stream) {
+    NIDT_REQUIRE(n % 4 == 0, "nidt_masked_sgd_step: n=%lld must be a multiple of 4 (slab alignment)", (long long)n);
+    NIDT_REQUIRE(scratch != nullptr, "nidt_masked_sgd_step: scratch is null");
+    cudaStream_t s = (cudaStream_t)stream;
+    sq_norm_partials_kernel<<<kNormBlocks, kFlatThreads, 0, s>>>(g, n, scratch);
+    NIDT_LAUNCH_CHECK();
+    masked_sgd_kernel<<<flat_grid(n / 4), kFlatThreads, 0, s>>>(w, g, momentum != 0.f ? mom : nullptr, mask, n, lr, momentum, wd,
+                                                                  clip_norm, first_step, scratch, kNormBlocks, norm_out);
+    NIDT_LAUNCH_CHECK();
+    return 0;
+}
+
+NIDT_API int nidt_grad_norm(const float* g, int64_t n, float* scratch, float* norm_out, void* stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    sq_norm_partials_kernel<<<kNormBlocks, kFlatThreads, 0, s>>>(g, n, scratch);
+    NIDT_LAUNCH_CHECK();
+    sum_partials_kernel<<<1, kFlatThreads, 0, s>>>(scratch, kNormBlocks, norm_out, 1);
+    NIDT_LAUNCH_CHECK();
+    return 0;
+}
+
+NIDT_API int nidt_weighted_aggregate(float* out, const float* const* srcs, const float* weights, int k,
+                                       const float* mask, int64_t n_mask, int64_t n, void* stream) {
+    NIDT_REQUIRE(k >= 1, "nidt_weighted_aggregate: need at least one source");
+    NIDT_REQUIRE(n % 4 == 0 && n_mask % 4 == 0, "nidt_weighted_aggregate: n and n_mask must be multiples of 4");
+    cudaStream_t s = (cudaStream_t)stream;
+    for (int base = 0; base < k; base += kMaxAggSrc) {
+        AggArgs a;
+        a.k = k - base < kMaxAggSrc ? k - base : kMaxAggSrc;
+        for (int i = 0; i < a.k; ++i) { a.src[i] = srcs[base + i]; a.wt[i] = weights[base + i]; }
+        const int last = base + a.k >= k;
+        weighted_aggregate_kernel<<<flat_grid(n / 4), kFlatThreads, 0, s>>>(out, a, mask, n_mask, n, base > 0, last);
+        NIDT_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
+NIDT_API int nidt_saliency_accumulate(float* scores, const float* g, const float* w, int64_t n, float scale, void* stream) {
+    NIDT_REQUIRE(n % 4 == 0, "nidt_saliency_accumulate: n must be a multiple of 4");
+    saliency_accumulate_kernel<<<flat_grid(n / 4), kFlatThreads, 0, (cudaStream_t)stream>>>(scores, g, w, n, scale);
+    NIDT_LAUNCH_CHECK();
+    return 0;
+}
+
+// scratch: >= nidt_topk_scratch_bytes() bytes of device memory (contents ignored on entry).
+// On return (stream-ordered) scratch holds {.., threshold, norm, kept} -- see TopkScratch.
+NIDT_API int nidt_global_topk_mask(const float* scores, const unsigned char* flags, float* mask, int64_t n,
+                                     unsigned long long k, void* scratch, void* stream) {
+    NIDT_REQUIRE(scratch != nullptr, "nidt_global_topk_mask: scratch is null");
+    int dev = 0, sms = 0, per_sm = 0;
+    NIDT_CUDA_CHECK(cudaGetDevice(&dev));
+    NIDT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    NIDT_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, global_topk_mask_kernel, kTopkThreads, 0));
+    NIDT_REQUIRE(per_sm >= 1, "nidt_global_topk_mask: kernel does not fit on an SM");
+    int grid = sms * (per_sm > 2 ? 2 : per_sm);
+    if (grid > 2 * kNumSMs) grid = 2 * kNumSMs;
+    TopkScratch* sc = (TopkScratch*)scratch;
+    void* args[] = {(void*)&scores, (void*)&flags, (void*)&mask, (void*)&n, (void*)&k, (void*)&sc};
+    NIDT_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)global_topk_mask_kernel, dim3(grid), dim3(kTopkThreads), args, 0, (cudaStream_t)stream));
+    return 0;
+}
+
+NIDT_API int nidt_topk_read_result(const void* scratch, float* threshold, float* norm, unsigned int* kept, void* stream) {
+    TopkScratch h;
+    NIDT_CUDA_CHECK(cudaMemcpyAsync(&h, scratch, sizeof(h), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    NIDT_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
+    if (threshold) *threshold = h.threshold;
+    if (norm) *norm = h.norm;
+    if (kept) *kept = h.kept;
+    return 0;
+}
+
+// *out (device u64) must be zeroed by the caller (or hold a running total to add to).
+NIDT_API int nidt_count_nonzero(const float* a, int64_t n, unsigned long long* out, void* stream) {
+    count_kernel<<<flat_grid(n), kFlatThreads, 0, (cudaStream_t)stream>>>(a, nullptr, n, 0, out);
+    NIDT_LAUNCH_CHECK();
+    return 0;
+}
+
+NIDT_API int nidt_hamming(const float* a, const float* b, int64_t n, unsigned long long* out, void* stream) {
+    count_kernel<<<flat_grid(n), kFlatThreads, 0, (cudaStream_t)stream>>>(a, b, n, 1, out);
+    NIDT_LAUNCH_CHECK();
+    return 0;
+}
+
+NIDT_API int nidt_sq_dist(const float* a, const float* b, int64_t n, float* scratch, float* out, void* stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    sq_dist_partials_kernel<<<kNormBlocks, kFlatThreads, 0, s>>>(a, b, n, scratch);
+    NIDT_LAUNCH_CHECK();
+    sum_partials_kernel<<<1, kFlatThreads, 0, s>>>(scratch, kNormBlocks, out, 0);
+    NIDT_LAUNCH_CHECK();
+    return 0;
+}
+
+NIDT_API int nidt_prox_pull(float* w, const float* ref, int64_t n, float coef, void* stream) {
+    prox_pull_kernel<<<flat_grid(n), kFlatThreads, 0, (cudaStream_t)stream>>>(w, ref, n, coef);
+    NIDT_LAUNCH_CHECK();
+    return 0;
+}

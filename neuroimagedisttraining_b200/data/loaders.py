@@ -1,0 +1,189 @@
+"""Light-weight batch iterators and the FedML 8-tuple builders.
+
+``load_partition_data_abcd`` returns the same structure as the reference
+(``ABCD/data_loader.py:157-212``): ``[train_num, test_num, train_global, test_global,
+local_num_dict, train_local_dict, test_local_dict, class_num]`` whose local loaders yield
+``(sample_index, label, site)`` batches -- the volumes themselves are fetched from a
+:class:`~.volumes.VolumeStore` by index when the batch is staged for the device.
+"""
+from __future__ import annotations
+
+from typing import Dict, Iterator, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from .partition import partition_labels, rescale_partition, site_partition
+from .volumes import VolumeStore
+
+
+class IndexLoader:
+    """Iterates ``(idx, y, site)`` mini-batches over a fixed index set.  ``shuffle`` draws a new
+    permutation per epoch from a private, seeded generator (so runs are reproducible and
+    independent of global RNG state).  ``len()`` = number of batches; ``.dataset`` mimics the
+    attribute the reference reads for sample counts."""
+
+    def __init__(self, indices, labels, sites, batch_size: int, shuffle: bool, seed: int = 0, drop_last: bool = False):
+        self.indices = torch.as_tensor(np.asarray(indices), dtype=torch.int64)
+        self.labels = torch.as_tensor(np.asarray(labels), dtype=torch.float32)
+        self.sites = torch.as_tensor(np.asarray(sites), dtype=torch.float32)
+        self.batch_size = int(batch_size)
+        self.shuffle = shuffle
+        self.drop_last = drop_last
+        self._gen = torch.Generator()
+        self._gen.manual_seed(int(seed))
+        self.dataset = self.indices  # len(loader.dataset) == sample count
+
+    def __len__(self) -> int:
+        n = self.indices.numel()
+        return n // self.batch_size if self.drop_last else (n + self.batch_size - 1) // self.batch_size
+
+    @property
+    def num_samples(self) -> int:
+        return self.indices.numel()
+
+    def __iter__(self) -> Iterator[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]]:
+        n = self.indices.numel()
+        order = torch.randperm(n, generator=self._gen) if self.shuffle else torch.arange(n)
+        for b in range(len(self)):
+            sel = order[b * self.batch_size:(b + 1) * self.batch_size]
+            yield self.indices[sel], self.labels[sel], self.sites[sel]
+
+    def state(self):
+        return self._gen.get_state()
+
+    def set_state(self, s):
+        self._gen.set_state(s)
+
+
+class TensorBatchLoader:
+    """``(x, y)`` mini-batches over in-memory tensors (image datasets)."""
+
+    def __init__(self, x: torch.Tensor, y: torch.Tensor, batch_size: int, shuffle: bool, seed: int = 0):
+        self.x, self.y = x, y
+        self.batch_size = int(batch_size)
+        self.shuffle = shuffle
+        self._gen = torch.Generator()
+        self._gen.manual_seed(int(seed))
+        self.dataset = y
+
+    def __len__(self):
+        return (self.y.numel() + self.batch_size - 1) // self.batch_size
+
+    @property
+    def num_samples(self):
+        return self.y.numel()
+
+    def __iter__(self):
+        n = self.y.shape[0]
+        order = torch.randperm(n, generator=self._gen) if self.shuffle else torch.arange(n)
+        for b in range(len(self)):
+            sel = order[b * self.batch_size:(b + 1) * self.batch_size]
+            yield self.x[sel], self.y[sel]
+
+
+def _abcd_tuple(store: VolumeStore, train: Sequence[np.ndarray], test: Sequence[np.ndarray], batch_size: int, seed: int):
+    local_num, train_local, test_local = {}, {}, {}
+    for cid, (tr, te) in enumerate(zip(train, test)):
+        train_local[cid] = IndexLoader(tr, store.labels[tr], store.sites[tr], batch_size, shuffle=True, seed=seed * 100003 + cid)
+        test_local[cid] = IndexLoader(te, store.labels[te], store.sites[te], batch_size, shuffle=False)
+        local_num[cid] = len(tr)
+    # class_num 2 mirrors the reference's return value (``data_loader.py:211-212``); the model has 1 logit
+    return [None, None, None, None, local_num, train_local, test_local, 2]
+
+
+def load_partition_data_abcd(store: VolumeStore, partition_method: str = "site", partition_alpha: float = 0.3,
+                             client_number: Optional[int] = None, batch_size: int = 16, logger=None, seed: int = 0):
+    """One client per site.  The reference hard-codes 21 clients (``data_loader.py:176``); here the
+    count is data-driven and ``client_number`` (if given) keeps the first N sites, which is what the
+    reference's default ``client_num_in_total=4`` effectively does."""
+    train, test, ids = site_partition(store.sites)
+    if client_number is not None:
+        if client_number > len(train):
+            raise ValueError(f"{client_number} clients requested but the data has {len(train)} sites; "
+                             "use load_partition_data_abcd_rescale")
+        train, test = train[:client_number], test[:client_number]
+    if logger is not None:
+        logger.info("*********partition data based on site***************")
+        for cid, (tr, te) in enumerate(zip(train, test)):
+            logger.info("client_idx = %d, local_train_sample_number = %d, local_test_sample_number = %d" % (cid, len(tr), len(te)))
+    return _abcd_tuple(store, train, test, batch_size, seed)
+
+
+def load_partition_data_abcd_rescale(store: VolumeStore, partition_method: str = "site", partition_alpha: float = 0.3,
+                                     client_number: int = 84, batch_size: int = 16, logger=None, seed: int = 0):
+    train, test, _ = site_partition(store.sites)
+    tr, te = rescale_partition(train, test, client_number)
+    if logger is not None:
+        for cid in range(client_number):
+            logger.info("client_idx = %d, local_train_sample_number = %d, local_test_sample_number = %d" % (cid, len(tr[cid]), len(te[cid])))
+    return _abcd_tuple(store, tr, te, batch_size, seed)
+
+
+# ------------------------------------------------------------------------- image datasets
+def synthetic_image_dataset(n_train: int, n_test: int, n_cls: int, shape=(3, 32, 32), seed: int = 0):
+    """Class-conditional Gaussian blobs standing in for CIFAR/Tiny-ImageNet when the files are absent."""
+    g = torch.Generator().manual_seed(seed)
+    protos = torch.randn((n_cls,) + tuple(shape), generator=g) * 0.5
+    def make(n):
+        y = torch.randint(0, n_cls, (n,), generator=g)
+        x = protos[y] + torch.randn((n,) + tuple(shape), generator=g) * 0.7
+        return x, y
+    return make(n_train), make(n_test)
+
+
+def _load_torchvision(dataset: str, data_dir: str):
+    import torchvision  # local import: optional dependency
+    import torchvision.transforms as T
+    stats = {"cifar10": ((0.4914, 0.4822, 0.4465), (0.2470, 0.2435, 0.2616)),
+             "cifar100": ((0.5071, 0.4865, 0.4409), (0.2673, 0.2564, 0.2762))}[dataset]
+    cls = {"cifar10": torchvision.datasets.CIFAR10, "cifar100": torchvision.datasets.CIFAR100}[dataset]
+    tr = cls(data_dir, train=True, download=False)
+    te = cls(data_dir, train=False, download=False)
+    def conv(ds):
+        x = torch.from_numpy(ds.data).permute(0, 3, 1, 2).float() / 255.0
+        m = torch.tensor(stats[0]).view(1, 3, 1, 1)
+        s = torch.tensor(stats[1]).view(1, 3, 1, 1)
+        return (x - m) / s, torch.tensor(ds.targets, dtype=torch.int64)
+    return conv(tr), conv(te)
+
+
+def load_partition_data_images(dataset: str, data_dir: Optional[str], partition_method: str, partition_alpha: float,
+                               client_number: int, batch_size: int, logger=None, seed: int = 0,
+                               val_split: float = 0.0, synthetic_size: Tuple[int, int] = (2000, 500)):
+    """CIFAR-10/100/Tiny-ImageNet 8-tuple (``cifar10/data_loader.py:208-249``; the ``_val`` variant
+    with a 10 % validation split, ``cifar10/data_val_loader.py:260-326``, via ``val_split``).
+    Test data of a client follows the client's own label distribution, as in the reference."""
+    n_cls = {"cifar10": 10, "cifar100": 100, "tiny": 200}[dataset]
+    shape = (3, 64, 64) if dataset == "tiny" else (3, 32, 32)
+    try:
+        if data_dir is None or dataset == "tiny":
+            raise FileNotFoundError
+        (xtr, ytr), (xte, yte) = _load_torchvision(dataset, data_dir)
+    except Exception:
+        (xtr, ytr), (xte, yte) = synthetic_image_dataset(synthetic_size[0], synthetic_size[1], n_cls, shape, seed)
+    ytr_np, yte_np = ytr.numpy(), yte.numpy()
+    idx_map = partition_labels(ytr_np, partition_method, client_number, partition_alpha, seed)
+    stats = {c: {int(k): int(v) for k, v in zip(*np.unique(ytr_np[i], return_counts=True))} for c, i in idx_map.items()}
+    rng = np.random.RandomState(seed + 1)
+    local_num, train_local, test_local, val_local = {}, {}, {}, {}
+    te_pools = {c: np.where(yte_np == c)[0] for c in range(n_cls)}
+    for cid in range(client_number):
+        idx = idx_map[cid]
+        if val_split > 0:
+            nv = int(len(idx) * val_split)
+            vidx, idx = idx[:nv], idx[nv:]
+            val_local[cid] = TensorBatchLoader(xtr[vidx], ytr[vidx], batch_size, False)
+        total = max(1, sum(stats[cid].values()))
+        n_te = max(1, int(len(yte_np) / client_number))
+        te_idx = np.concatenate([rng.choice(te_pools[c], max(1, int(n_te * cnt / total)), replace=True)
+                                 for c, cnt in stats[cid].items()]) if stats[cid] else np.arange(0)
+        train_local[cid] = TensorBatchLoader(xtr[idx], ytr[idx], batch_size, True, seed=seed * 100003 + cid)
+        test_local[cid] = TensorBatchLoader(xte[te_idx], yte[te_idx], batch_size, False)
+        local_num[cid] = len(idx)
+    train_global = TensorBatchLoader(xtr, ytr, batch_size, True, seed)
+    test_global = TensorBatchLoader(xte, yte, batch_size, False)
+    out = [len(ytr), len(yte), train_global, test_global, local_num, train_local, test_local, stats]
+    if val_split > 0:
+        out.append(val_local)
+    return out

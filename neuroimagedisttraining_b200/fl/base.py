@@ -1,0 +1,205 @@
+"""Shared machinery of the FL orchestrators: client set-up, deterministic sampling, device-side
+aggregation, evaluation of all clients, statistics, phase timing and checkpoint/resume.
+
+Reference orchestrators: ``fedml_api/standalone/{fedavg/fedavg_api.py:12-196,
+sailentgrads/sailentgrads_api.py:18-346}``.  Departures: the global model, every
+client's personal model and the mask are device-resident slabs; clients are placed on ranks
+(one process per GPU) and train there; aggregation is a flat kernel (+ fused cross-rank collective).
+"""
+from __future__ import annotations
+
+import time
+from collections import defaultdict
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from .. import ops
+from ..parallel.aggregation import Aggregator
+from ..parallel.context import DistContext
+from ..runtime.slab import ParamSlab
+from ..utils.checkpoint import load_checkpoint, save_checkpoint
+from ..utils.timing import PhaseTimer
+from .client import Client
+from .trainer import SlabTrainer
+
+
+class FedAPIBase:
+    NAME = "fed"
+
+    def __init__(self, dataset, device, args, model_trainer: SlabTrainer, logger, dist: Optional[DistContext] = None,
+                 agg_mode: str = "auto"):
+        self.logger = logger
+        self.device = torch.device(device)
+        self.args = args
+        self.dist = dist if dist is not None else DistContext(device=self.device)
+        [train_data_num, test_data_num, train_data_global, test_data_global,
+         train_data_local_num_dict, train_data_local_dict, test_data_local_dict, class_counts] = dataset[:8]
+        self.train_global = train_data_global
+        self.test_global = test_data_global
+        self.val_global = None
+        self.val_data_local_dict = dataset[8] if len(dataset) > 8 else None
+        self.train_data_num_in_total = train_data_num
+        self.test_data_num_in_total = test_data_num
+        self.train_data_local_num_dict = train_data_local_num_dict
+        self.train_data_local_dict = train_data_local_dict
+        self.test_data_local_dict = test_data_local_dict
+        self.class_counts = class_counts
+        self.model_trainer = model_trainer
+        self.layout = model_trainer.layout
+        self.client_list: List[Client] = []
+        self._setup_clients(train_data_local_num_dict, train_data_local_dict, test_data_local_dict, model_trainer)
+        self.init_stat_info()
+        self.w_global: ParamSlab = model_trainer.engine.new_slab()
+        self.aggregator = Aggregator(self.dist, self.layout, self.device, agg_mode)
+        self.timer = PhaseTimer(self.device)
+        self.start_round = 0
+        self.mask: Optional[ParamSlab] = None
+        self.w_init: Optional[ParamSlab] = None   # personalised model of a client that never trained
+
+    # ------------------------------------------------------------------------- set-up
+    def _setup_clients(self, train_data_local_num_dict, train_data_local_dict, test_data_local_dict, model_trainer):
+        self.logger.info("############setup_clients (START)#############")
+        for client_idx in range(self.args.client_num_in_total):
+            c = Client(client_idx, train_data_local_dict[client_idx], test_data_local_dict[client_idx],
+                       train_data_local_num_dict[client_idx], self.args, self.device, model_trainer, self.logger)
+            self.client_list.append(c)
+        self.logger.info("############setup_clients (END)#############")
+
+    def init_stat_info(self):
+        self.stat_info = {
+            "label_num": self.class_counts, "sum_comm_params": 0, "sum_training_flops": 0, "avg_inference_flops": 0,
+            "old_mask_test_acc": [], "new_mask_test_acc": [], "final_masks": [], "mask_dis_matrix": [],
+            "global_test_acc": [], "person_test_acc": [], "global_test_loss": [], "person_test_loss": [],
+            "round_time_s": [],
+        }
+        self._comm_params_dev = None
+
+    # ----------------------------------------------------------------------- sampling
+    def _client_sampling(self, round_idx, client_num_in_total, client_num_per_round):
+        """All clients when ``per_round == total``; otherwise ``np.random.seed(round_idx)`` +
+        ``choice`` without replacement, so every framework picks the same clients each round
+        (``sailentgrads_api.py:152-160``)."""
+        if client_num_in_total == client_num_per_round:
+            client_indexes = [i for i in range(client_num_in_total)]
+        else:
+            num_clients = min(client_num_per_round, client_num_in_total)
+            np.random.seed(round_idx)
+            client_indexes = np.random.choice(range(client_num_in_total), num_clients, replace=False)
+        self.logger.info("client_indexes = %s" % str(client_indexes))
+        return client_indexes
+
+    def local_clients(self, indexes: Sequence[int]) -> List[int]:
+        return [int(c) for c in indexes if self.dist.owns(int(c))]
+
+    # -------------------------------------------------------------------- aggregation
+    def _aggregate(self, w_locals: Sequence[Tuple[int, ParamSlab]], training_num: Optional[int] = None,
+                   mask: Optional[ParamSlab] = None, out: Optional[ParamSlab] = None) -> ParamSlab:
+        """``w_global = sum_i (n_i / sum n) * w_i`` over all 39 state entries incl. BN buffers
+        (``sailentgrads_api.py:212-227``).  ``w_locals`` are this rank's sampled clients in client
+        order; ``training_num`` is the global sample total (defaults to the local one)."""
+        if training_num is None:
+            training_num = sum(n for n, _ in w_locals)
+        out = out if out is not None else self.w_global
+        pairs = [(n / training_num, s) for n, s in w_locals]
+        with self.timer.phase("aggregate"):
+            self.aggregator.aggregate(out, pairs, mask)
+        return out
+
+    # --------------------------------------------------------------------- evaluation
+    def _evaluate_clients(self, slabs: Dict[int, ParamSlab], client_ids: Sequence[int]) -> Tuple[np.ndarray, np.ndarray]:
+        """Per-client (accuracy, loss/sample) for the locally owned ``client_ids``; zeros elsewhere."""
+        n = self.args.client_num_in_total
+        acc = np.zeros(n)
+        loss = np.zeros(n)
+        for cid in client_ids:
+            m = self.client_list[cid].local_test(slabs[cid], True)
+            tot = max(m["test_total"], 1.0)
+            acc[cid] = m["test_correct"] / tot
+            loss[cid] = m["test_loss"] / tot
+        return acc, loss
+
+    def _reduce_metric(self, *arrays: np.ndarray) -> List[np.ndarray]:
+        if not self.dist.is_distributed:
+            return list(arrays)
+        t = torch.tensor(np.stack(arrays), dtype=torch.float64, device=self.device)
+        self.dist.all_reduce_sum(t)
+        return [a for a in t.cpu().numpy()]
+
+    def _test_on_all_clients(self, w_global: ParamSlab, w_per_mdls: Optional[Dict[int, ParamSlab]], round_idx):
+        """Global model and personalised models on every client's test split; metrics are
+        client-uniform means (``sailentgrads_api.py:231-285``).  ``--ci 1`` evaluates only the first
+        client (and, unlike the reference, averages over what was evaluated)."""
+        self.logger.info("################global_test_on_all_clients : {}".format(round_idx))
+        n_total = self.args.client_num_in_total
+        ids = [0] if getattr(self.args, "ci", 0) == 1 else list(range(n_total))
+        mine = self.local_clients(ids)
+        with self.timer.phase("eval"):
+            g_acc, g_loss = self._evaluate_clients({c: w_global for c in mine}, mine)
+            if w_per_mdls is not None:
+                p_acc, p_loss = self._evaluate_clients({c: (w_per_mdls.get(c) or self.w_init or w_global) for c in mine}, mine)
+            else:
+                p_acc, p_loss = g_acc.copy(), g_loss.copy()
+            g_acc, g_loss, p_acc, p_loss = self._reduce_metric(g_acc, g_loss, p_acc, p_loss)
+        denom = len(ids)
+        stats = {'global_test_acc': g_acc.sum() / denom, 'global_test_loss': g_loss.sum() / denom}
+        self.stat_info["global_test_acc"].append(stats['global_test_acc'])
+        self.stat_info["global_test_loss"].append(stats['global_test_loss'])
+        self.logger.info(stats)
+        pstats = {'person_test_acc': p_acc.sum() / denom, 'person_test_loss': p_loss.sum() / denom}
+        self.stat_info["person_test_acc"].append(pstats['person_test_acc'])
+        self.stat_info["person_test_loss"].append(pstats['person_test_loss'])
+        self.logger.info(pstats)
+        return stats, pstats
+
+    # ------------------------------------------------------------------------- stats
+    def _add_comm_params(self, n) -> None:
+        if torch.is_tensor(n):
+            self._comm_params_dev = n.clone() if self._comm_params_dev is None else self._comm_params_dev + n
+        else:
+            self.stat_info["sum_comm_params"] += n
+
+    def finalize_stats(self) -> dict:
+        if self._comm_params_dev is not None:
+            t = self._comm_params_dev.to(torch.float64)
+            self.dist.all_reduce_sum(t)
+            self.stat_info["sum_comm_params"] += int(t.item())
+            self._comm_params_dev = None
+        self.stat_info["phase_time_s"] = self.timer.summary()
+        return self.stat_info
+
+    def get_model_sps_for_weight(self, slab: ParamSlab) -> float:
+        """Sparsity (%) over *all* state entries of a model (``sailentgrads_api.py:68-83``)."""
+        nz = int(ops.count_nonzero(slab.flat).item())
+        total = self.layout.numel_real()
+        return 100.0 * (total - nz) / total
+
+    # ------------------------------------------------------------------- checkpointing
+    def personal_slabs(self) -> Dict[int, ParamSlab]:
+        return {c.client_idx: c.slab for c in self.client_list if c.slab is not None}
+
+    def save(self, path: str, round_idx: int) -> None:
+        if self.dist.is_main:
+            save_checkpoint(path, round_idx, self.w_global, self.mask, self.args, self.stat_info,
+                            personal=self.personal_slabs() if getattr(self.args, "save_personal", False) else None)
+
+    def resume(self, path: str) -> int:
+        ck = load_checkpoint(path, map_location=self.device)
+        self.w_global.load_state_dict(ck["state_dict"])
+        if ck.get("mask") is not None:
+            self.mask = self.model_trainer.mask_slab(ck["mask"])
+        for k, v in ck.get("stat_info", {}).items():
+            self.stat_info[k] = v
+        for cid, sd in (ck.get("personal") or {}).items():
+            c = self.client_list[int(cid)]
+            c.ensure_slab(self.w_global).load_state_dict(sd)
+        self.start_round = int(ck["round"]) + 1
+        self.logger.info("resumed from %s at round %d" % (path, self.start_round))
+        return self.start_round
+
+    def _maybe_checkpoint(self, round_idx: int) -> None:
+        every = int(getattr(self.args, "checkpoint_every", 0) or 0)
+        path = getattr(self.args, "checkpoint_path", None)
+        if path and every > 0 and (round_idx + 1) % every == 0:
+            self.save(path, round_idx)

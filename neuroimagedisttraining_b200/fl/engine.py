@@ -1,0 +1,130 @@
+"""Compute engines: what runs one local step / eval batch on a model bound to a ParamSlab.
+
+``TorchEngine``  module autograd over slab-bound parameters.  This is the CPU path and the
+                 scaffolding path for architectures without a native plan (2-D image models);
+                 the optimizer / mask / saliency / aggregation still run as flat slab ops.
+``B200Engine``   (``ops/engine_b200.py``) the sm_100a path for plan-based 3-D models: hand-written
+                 conv / BN / ReLU / MaxPool / head kernels launched directly on the slab.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .. import ops
+from ..runtime.slab import ParamSlab, SlabLayout
+
+
+@dataclass
+class StepHParams:
+    lr: float
+    momentum: float = 0.0
+    wd: float = 0.0
+    clip_norm: float = 10.0
+
+
+class EvalCounters:
+    """Device-side accumulators (correct, loss_sum, total): no per-batch ``.item()`` syncs
+    (the reference does three per batch, ``my_model_trainer.py:270-273``)."""
+
+    def __init__(self, device):
+        self.buf = torch.zeros(3, dtype=torch.float64, device=device)
+
+    def reset(self):
+        self.buf.zero_()
+
+    def result(self):
+        c, l, t = self.buf.tolist()
+        return {"test_correct": c, "test_loss": l, "test_total": t, "test_acc": (c / t if t else 0.0)}
+
+
+class TorchEngine:
+    def __init__(self, model: nn.Module, device, loss_kind: str = "bce", volumetric: bool = True, input_scale: float = 1.0 / 255.0):
+        self.device = torch.device(device)
+        self.model = model.to(self.device)
+        self.layout = SlabLayout.from_module(self.model)
+        self.loss_kind = loss_kind
+        self.volumetric = volumetric
+        self.input_scale = input_scale
+        self.grad = ParamSlab(self.layout, device=self.device, params_only=True)
+        self.slab: Optional[ParamSlab] = None
+        self.loss_acc = torch.zeros((), dtype=torch.float32, device=self.device)
+        self.loss_steps = 0
+        self.native = False
+
+    # -- parameter binding ---------------------------------------------------------------
+    def new_slab(self) -> ParamSlab:
+        """A fresh slab initialised from the module's current values (unbound)."""
+        return ParamSlab.from_module(self.model, device=self.device, bind=False)
+
+    def attach(self, slab: ParamSlab) -> None:
+        if self.slab is not None and self.slab is not slab:
+            self.slab.sync_int_buffers_from(self.model)
+        self.slab = slab
+        slab.bind_module(self.model, grad=self.grad)
+        slab.sync_int_buffers_to(self.model)
+
+    def detach_sync(self) -> None:
+        if self.slab is not None:
+            self.slab.sync_int_buffers_from(self.model)
+
+    # -- helpers ---------------------------------------------------------------------------
+    def _prep(self, x: torch.Tensor) -> torch.Tensor:
+        x = x.to(self.device, non_blocking=True)
+        if self.volumetric:
+            if x.dtype == torch.uint8:
+                x = x.to(torch.float32) * self.input_scale
+            if x.dim() == 4:
+                x = x.unsqueeze(1)
+        return x
+
+    def _loss(self, logits, y):
+        if isinstance(logits, (list, tuple)):
+            logits = logits[0]
+        if self.loss_kind == "bce":   # BCEWithLogitsLoss()(logits[B,1], y[:,None]) == mean over B
+            return F.binary_cross_entropy_with_logits(logits.flatten(), y.to(self.device).float().flatten())
+        return F.cross_entropy(logits, y.to(self.device).long())
+
+    # -- one local step ----------------------------------------------------------------------
+    def compute_grads(self, x, y, train_mode: bool = True) -> torch.Tensor:
+        """Forward + backward; gradients land in ``self.grad.flat`` (zeroed first)."""
+        self.model.train(train_mode)
+        self.grad.flat.zero_()
+        for name, p in self.model.named_parameters():   # autograd may have replaced .grad; re-pin cheaply
+            if p.grad is None or p.grad.data_ptr() != self.grad.view(name).data_ptr():
+                p.grad = self.grad.view(name)
+        loss = self._loss(self.model(self._prep(x)), y)
+        loss.backward()
+        return loss.detach()
+
+    def train_step(self, x, y, hp: StepHParams, mask: Optional[torch.Tensor], mom: Optional[torch.Tensor], first_step: bool) -> None:
+        loss = self.compute_grads(x, y, train_mode=True)
+        self.loss_acc += loss
+        self.loss_steps += 1
+        ops.masked_sgd_step(self.slab.params_flat, self.grad.flat, mom, mask, hp.lr, hp.momentum, hp.wd, hp.clip_norm, first_step)
+
+    def pop_mean_loss(self) -> float:
+        v = float(self.loss_acc.item()) / max(1, self.loss_steps)
+        self.loss_acc.zero_()
+        self.loss_steps = 0
+        return v
+
+    # -- evaluation -----------------------------------------------------------------------------
+    @torch.no_grad()
+    def eval_batch(self, x, y, counters: EvalCounters, double_sigmoid: bool = True) -> None:
+        self.model.eval()
+        logits = self.model(self._prep(x))
+        if isinstance(logits, (list, tuple)):
+            logits = logits[0]
+        y = y.to(self.device)
+        if self.loss_kind == "bce":
+            correct, loss = ops.reference.bce_eval_counters(logits, y, double_sigmoid)
+            # the reference accumulates mean-loss * batch (``my_model_trainer.py:271``) == summed loss
+        else:
+            loss = F.cross_entropy(logits, y.long(), reduction="sum")
+            correct = (logits.argmax(1) == y.long()).float().sum()
+        counters.buf += torch.stack([correct.double(), loss.double(), torch.tensor(float(y.shape[0]), dtype=torch.float64, device=self.device)])

@@ -1,0 +1,54 @@
+"""FedAvg (reference: ``fedml_api/standalone/fedavg/fedavg_api.py:12-196``)."""
+from __future__ import annotations
+
+import time
+
+import numpy as np
+
+from .base import FedAPIBase
+
+
+class FedAvgAPI(FedAPIBase):
+    NAME = "fedavg"
+
+    def run_round(self, round_idx: int, mask=None, evaluate: bool = True):
+        """sample -> local training of the owned sampled clients -> weighted aggregation -> eval."""
+        args = self.args
+        self.logger.info("################Communication round : {}".format(round_idx))
+        client_indexes = np.sort(self._client_sampling(round_idx, args.client_num_in_total, args.client_num_per_round))
+        self.logger.info("client_indexes = " + str(client_indexes))
+        training_num = sum(self.client_list[int(c)].get_sample_number() for c in client_indexes)
+        w_locals = []
+        with self.timer.phase("train"):
+            for cur_clnt in self.local_clients(client_indexes):
+                self.logger.info('@@@@@@@@@@@@@@@@ Training Client CM({}): {}'.format(round_idx, cur_clnt))
+                client = self.client_list[cur_clnt]
+                slab, training_flops, num_comm_params = client.train(self.w_global, round_idx, mask)
+                w_locals.append((client.get_sample_number(), slab))
+                self.stat_info["sum_training_flops"] += training_flops
+                self._add_comm_params(num_comm_params)
+        self._aggregate(w_locals, training_num, mask=None)
+        if evaluate and round_idx % max(1, int(getattr(args, "frequency_of_the_test", 1))) == 0:
+            self._test_on_all_clients(self.w_global, self.personal_slabs(), round_idx)
+        self._maybe_checkpoint(round_idx)
+
+    def train(self):
+        args = self.args
+        if self.w_init is None:
+            self.w_init = self.w_global.clone()
+        for round_idx in range(self.start_round, args.comm_round):
+            t0 = time.time()
+            self.run_round(round_idx)
+            self.stat_info["round_time_s"].append(time.time() - t0)
+        if getattr(args, "final_finetune", True):
+            self.finetune_round()
+        return self.finalize_stats()
+
+    def finetune_round(self):
+        """Final round: *every* client trains once from the global model with ``round=-1``
+        (lr * decay^-1) and the personalised accuracy is re-evaluated (``fedavg_api.py:79-88``)."""
+        self.logger.info("################ final fine-tune round")
+        with self.timer.phase("train"):
+            for cid in self.local_clients(range(self.args.client_num_in_total)):
+                self.client_list[cid].train(self.w_global, -1, None)
+        self._test_on_all_clients(self.w_global, self.personal_slabs(), -1)

@@ -1,0 +1,259 @@
+"""ModelTrainer ABC and the slab-backed trainer used by every algorithm.
+
+API surface follows ``fedml_core/trainer/model_trainer.py:8-58`` and
+``fedml_api/standalone/sailentgrads/my_model_trainer.py:22-280`` (``get_model_params``,
+``set_model_params``, ``train``, ``test``, ``get_trainable_params``, ``get_model_sps``,
+``calculate_sparsities``, ``init_masks``, ``screen_gradients``, ``count_communication_params``),
+but the state lives in device-resident :class:`ParamSlab` s instead of CPU state_dict copies.
+"""
+from __future__ import annotations
+
+from abc import ABC, abstractmethod
+from collections import OrderedDict
+from typing import Dict, Optional, Union
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from .. import ops
+from ..runtime.slab import ParamSlab, make_mask_slab
+from ..runtime.staging import BatchStager
+from .engine import EvalCounters, StepHParams, TorchEngine
+
+
+class ModelTrainer(ABC):
+    """Abstract trainer (same contract as the reference's ABC)."""
+
+    def __init__(self, model, args=None):
+        self.model = model
+        self.id = 0
+        self.args = args
+
+    def set_id(self, trainer_id):
+        self.id = trainer_id
+
+    @abstractmethod
+    def get_model_params(self):
+        ...
+
+    @abstractmethod
+    def set_model_params(self, model_parameters):
+        ...
+
+    @abstractmethod
+    def train(self, train_data, device, args=None):
+        ...
+
+    @abstractmethod
+    def test(self, test_data, device, args=None):
+        ...
+
+    def test_on_the_server(self, train_data_local_dict, test_data_local_dict, device, args=None) -> bool:
+        return False
+
+    def count_training_flops_per_sample(self):
+        from ..utils.flops import count_training_flops
+        return count_training_flops(self.model, getattr(self.args, "dataset", "ABCD"))
+
+    def count_full_flops_per_sample(self):
+        from ..utils.flops import count_training_flops
+        return count_training_flops(self.model, getattr(self.args, "dataset", "ABCD"), full=True)
+
+    def count_inference_flops(self, w):
+        from ..utils.flops import count_inference_flops
+        self.set_model_params(w)
+        return count_inference_flops(self.model, getattr(self.args, "dataset", "ABCD"))
+
+    def count_communication_params(self, update_to_server):
+        """Number of non-zero entries (``model_trainer.py:49-53``); accepts a state_dict or a slab."""
+        if isinstance(update_to_server, ParamSlab):
+            return ops.count_nonzero(update_to_server.flat)
+        total = 0
+        for name in update_to_server:
+            total = total + torch.count_nonzero(update_to_server[name])
+        return total
+
+
+MaskLike = Union[None, ParamSlab, Dict[str, torch.Tensor]]
+
+
+class SlabTrainer(ModelTrainer):
+    """Local SGD on a slab.  One instance is shared by all simulated clients of a rank (as in the
+    reference, ``sailentgrads_api.py:36-45``); per-client state is the slab it is attached to."""
+
+    def __init__(self, model: nn.Module, args=None, logger=None, device=None, store=None, engine=None,
+                 loss_kind: str = "bce", clip_norm: float = 10.0):
+        super().__init__(model, args)
+        self.logger = logger
+        self.device = torch.device(device) if device is not None else next(model.parameters()).device
+        self.store = store
+        self.engine = engine if engine is not None else TorchEngine(
+            model, self.device, loss_kind=loss_kind, volumetric=store is not None,
+            input_scale=getattr(store, "scale", 1.0))
+        self.layout = self.engine.layout
+        self.clip_norm = clip_norm
+        self.work = self.engine.new_slab()         # the slab API-compat calls operate on
+        self.engine.attach(self.work)
+        self.mom = ParamSlab(self.layout, device=self.device, params_only=True)
+        self.masks: Optional[ParamSlab] = None
+        self._stagers: Dict[int, BatchStager] = {}
+        self.double_sigmoid_eval = True
+        self.step_counter = 0
+
+    # ------------------------------------------------------------------ slab plumbing
+    @property
+    def slab(self) -> ParamSlab:
+        return self.engine.slab
+
+    def attach(self, slab: ParamSlab) -> None:
+        self.engine.attach(slab)
+
+    def _stager(self, batch_size: int) -> BatchStager:
+        st = self._stagers.get(batch_size)
+        if st is None:
+            st = BatchStager(self.store, self.device, batch_size)
+            self._stagers[batch_size] = st
+        return st
+
+    def _batches(self, data):
+        """Uniform ``(x, y)`` stream: index loaders go through the volume store, tensor loaders pass through."""
+        if self.store is not None and hasattr(data, "indices"):
+            yield from self._stager(data.batch_size).iterate(data)
+        else:
+            for batch in data:
+                yield batch[0], batch[1]
+
+    def mask_slab(self, masks: MaskLike) -> Optional[ParamSlab]:
+        if masks is None or isinstance(masks, ParamSlab):
+            return masks
+        m = make_mask_slab(self.layout, self.device)
+        for name, t in masks.items():
+            if name in self.layout:
+                m.view(name).copy_(t.to(self.device, torch.float32))
+        return m
+
+    # ------------------------------------------------------------- reference-style API
+    def set_masks(self, masks: MaskLike):
+        self.masks = self.mask_slab(masks)
+
+    def get_model_params(self):
+        self.engine.detach_sync()
+        return self.slab.state_dict()
+
+    def set_model_params(self, model_parameters):
+        if isinstance(model_parameters, ParamSlab):
+            self.slab.copy_(model_parameters)
+        else:
+            self.slab.load_state_dict(model_parameters)
+        self.slab.sync_int_buffers_to(self.model)
+
+    def get_trainable_params(self):
+        return OrderedDict((n, self.slab.view(n)) for n in self.layout.param_names)
+
+    def get_model_sps(self, slab: Optional[ParamSlab] = None) -> float:
+        """Percentage of zero entries among the trainable parameters (``my_model_trainer.py:144-158``)."""
+        s = slab if slab is not None else self.slab
+        nz = int(ops.count_nonzero(s.params_flat).item())
+        total = self.layout.numel_real(params_only=True)
+        return 100.0 * (total - nz) / total
+
+    # ----------------------------------------------------------------- sparsity helpers
+    def calculate_sparsities(self, params=None, tabu=(), distribution: str = "ERK", sparse: float = 0.5) -> Dict[str, float]:
+        """Per-tensor sparsity: ``uniform`` (1-dense_ratio everywhere) or Erdos-Renyi-Kernel with the
+        densify-and-retry loop (``DisPFL/my_model_trainer.py:43-117``)."""
+        shapes = {n: tuple(self.layout[n].shape) for n in (params if params is not None else self.layout.param_names)}
+        if distribution == "uniform":
+            return {n: (0.0 if n in tabu else 1.0 - float(self.args.dense_ratio)) for n in shapes}
+        power = float(getattr(self.args, "erk_power_scale", 1.0))
+        density = sparse
+        dense_layers = set(n for n in shapes if n in tabu)
+        while True:
+            divisor, rhs, raw = 0.0, 0.0, {}
+            for n, shp in shapes.items():
+                n_param = float(np.prod(shp))
+                if n in dense_layers:
+                    rhs -= n_param * (1 - density)
+                else:
+                    rhs += n_param * density
+                    raw[n] = (float(np.sum(shp)) / n_param) ** power
+                    divisor += raw[n] * n_param
+            eps = rhs / divisor
+            mx = max(raw.values())
+            if mx * eps > 1:
+                dense_layers |= {n for n, v in raw.items() if v == mx}
+            else:
+                break
+        return {n: (0.0 if n in dense_layers else 1.0 - eps * raw[n]) for n in shapes}
+
+    def init_masks(self, params=None, sparsities: Dict[str, float] = None, generator: Optional[torch.Generator] = None) -> ParamSlab:
+        """Random per-tensor masks at the given sparsities (``DisPFL/my_model_trainer.py:31-41``)."""
+        m = ParamSlab(self.layout, device=self.device, params_only=True)
+        for n in (params if params is not None else self.layout.param_names):
+            e = self.layout[n]
+            dense = int((1 - sparsities[n]) * e.numel)
+            if dense > 0:
+                perm = torch.randperm(e.numel, generator=generator)[:dense].to(self.device)
+                m.view(n).view(-1)[perm] = 1
+        return m
+
+    # -------------------------------------------------------------------------- train
+    def train(self, train_data, device=None, args=None, round_idx: int = 0, masks: MaskLike = None,
+              prox_ref: Optional[ParamSlab] = None, lamda: float = 0.0, epochs: Optional[int] = None,
+              apply_mask: Optional[bool] = None, grad_mask: bool = False):
+        """``epochs`` of local SGD on the attached slab.  A fresh optimizer per call (momentum
+        buffers reset), ``lr * lr_decay**round``, grad-clip 10, weight decay on every parameter and
+        ``w *= mask`` after every step when ``snip_mask`` (``my_model_trainer.py:201-235``)."""
+        args = args if args is not None else self.args
+        mslab = self.mask_slab(masks) if masks is not None else self.masks
+        use_mask = bool(getattr(args, "snip_mask", True)) if apply_mask is None else apply_mask
+        mask_flat = mslab.flat if (mslab is not None and use_mask) else None
+        if getattr(args, "client_optimizer", "sgd") != "sgd":
+            raise ValueError("only client_optimizer='sgd' defines an optimizer (as in the reference)")
+        hp = StepHParams(lr=args.lr * (args.lr_decay ** round_idx), momentum=float(getattr(args, "momentum", 0.0)),
+                         wd=float(getattr(args, "wd", 0.0)), clip_norm=self.clip_norm)
+        mom = self.mom.flat if hp.momentum != 0 else None
+        first = True
+        losses = []
+        for epoch in range(int(epochs if epochs is not None else args.epochs)):
+            for x, y in self._batches(train_data):
+                if grad_mask and mask_flat is not None:
+                    self.engine.grad_mask = mask_flat
+                self.engine.train_step(x, y, hp, mask_flat, mom, first)
+                if prox_ref is not None and lamda != 0:
+                    ops.prox_pull(self.slab.params_flat, prox_ref.params_flat, hp.lr, lamda)
+                first = False
+                self.step_counter += 1
+            mean_loss = self.engine.pop_mean_loss()
+            losses.append(mean_loss)
+            if self.logger is not None:
+                self.logger.info('Client Index = {}\tEpoch: {}\tLoss: {:.6f}'.format(self.id, epoch, mean_loss))
+        return losses
+
+    # --------------------------------------------------------------------------- test
+    def test(self, test_data, device=None, args=None):
+        c = EvalCounters(self.device)
+        for x, y in self._batches(test_data):
+            self.engine.eval_batch(x, y, c, double_sigmoid=self.double_sigmoid_eval)
+        return c.result()
+
+    # --------------------------------------------------------------- gradient screening
+    def screen_gradients(self, train_data, device=None) -> ParamSlab:
+        """Dense gradient of one batch in eval mode (``DisPFL/my_model_trainer.py:166-189``)."""
+        for x, y in self._batches(train_data):
+            self.engine.compute_grads(x, y, train_mode=False)
+            break
+        g = ParamSlab(self.layout, device=self.device, params_only=True)
+        g.flat.copy_(self.engine.grad.flat)
+        return g
+
+    def saliency_batch(self, x, y, scores: ParamSlab, scale: float = 1.0) -> None:
+        """One SNIP evaluation: ``scores += scale*|g*w|`` with BN in batch-stat mode and dropout on,
+        as the reference's deep-copied model is (``snip.py:38-66``); weights are not modified."""
+        P = self.layout.param_numel
+        self.engine.detach_sync()
+        saved = self.slab.flat[P:].clone()           # BN running stats must not move (the reference scores a deep copy)
+        self.engine.compute_grads(x, y, train_mode=True)
+        self.slab.flat[P:].copy_(saved)
+        self.slab.sync_int_buffers_to(self.model)
+        ops.saliency_accumulate(scores.flat, self.engine.grad.flat, self.slab.params_flat, scale)

@@ -1,0 +1,103 @@
+"""End-to-end parity against the unmodified reference on CPU: same
+synthetic data, same initial weights, dropout p=0, unshuffled loaders -> the SalientGrads mask must
+be identical and the aggregated global model must match to fp32 round-off."""
+import numpy as np
+import pytest
+import torch
+
+from baseline import ref_harness
+from neuroimagedisttraining_b200.data import SyntheticABCD, site_partition
+from neuroimagedisttraining_b200.data.loaders import IndexLoader
+from neuroimagedisttraining_b200.fl import FedAvgAPI, SalientGradsAPI, SlabTrainer
+from neuroimagedisttraining_b200.models import AlexNet3D_Dropout
+
+from helpers import make_args, quiet_logger
+
+pytestmark = pytest.mark.skipif(ref_harness.reference_available() is not None, reason="reference not installed")
+
+
+def _setup(n_clients=2, per_site=5, batch=2):
+    store = SyntheticABCD(n_clients * per_site, n_sites=n_clients, seed=3, pool=2, site_sizes=[per_site] * n_clients)
+    train, test, _ = site_partition(store.sites)
+    return store, train, test
+
+
+def _ours(algo, store, train, test, args, init_state):
+    torch.manual_seed(0)
+    model = AlexNet3D_Dropout(num_classes=1, p_drop=0.0)
+    model.load_state_dict(init_state)
+    tr = SlabTrainer(model, args, quiet_logger(), device="cpu", store=store)
+    local_num = {c: len(t) for c, t in enumerate(train)}
+    trl = {c: IndexLoader(t, store.labels[t], store.sites[t], args.batch_size, shuffle=False) for c, t in enumerate(train)}
+    tel = {c: IndexLoader(t, store.labels[t], store.sites[t], args.batch_size, shuffle=False) for c, t in enumerate(test)}
+    ds = [None, None, None, None, local_num, trl, tel, 2]
+    api = (SalientGradsAPI if algo == "salientgrads" else FedAvgAPI)(ds, "cpu", args, tr, quiet_logger())
+    return api
+
+
+@pytest.mark.slow
+def test_salientgrads_matches_reference_cpu():
+    torch.set_num_threads(max(1, torch.get_num_threads()))
+    store, train, test = _setup()
+    args = make_args(client_num_in_total=2, batch_size=2, epochs=1, comm_round=1, dense_ratio=0.5)
+    torch.manual_seed(123)
+    init = AlexNet3D_Dropout(num_classes=1).state_dict()
+
+    ref_api, ref_model, _ = ref_harness.build_reference_api("salientgrads", store, train, test, args, "cpu", shuffle=False,
+                                                           model_state=init, p_drop=0.0)
+    ref_mask = ref_api.generate_global_mask_snip()
+    ours = _ours("salientgrads", store, train, test, args, init)
+    mask = ours.generate_global_mask_snip()
+    total = diff = 0
+    for name, m in ref_mask.items():
+        d = int((mask.view(name) != m).sum())
+        diff += d
+        total += m.numel()
+    # identical up to ties / last-bit differences of the normalising sum (documented tolerance)
+    assert diff <= max(2, total // 100000), f"mask differs at {diff}/{total} positions"
+    assert abs(float(mask.flat.sum()) - sum(float(m.sum()) for m in ref_mask.values())) <= 2
+
+    # one full round with the shared mask, then compare the aggregated global model
+    ref_api.generate_global_mask_snip = lambda: ref_mask
+    ref_model.load_state_dict(init)
+    captured = {}
+    orig_agg = ref_api._aggregate
+    def agg(w_locals):
+        out = orig_agg(w_locals)
+        captured["w"] = out
+        return out
+    ref_api._aggregate = agg
+    ref_api.train()
+    ours.mask = mask
+    ours.train()
+    sd = ours.w_global.state_dict(cast_int=False)
+    for k, v in captured["w"].items():
+        torch.testing.assert_close(sd[k].float(), v.float(), rtol=2e-4, atol=2e-5, msg=lambda m: f"{k}: {m}")
+    # metric keys and values
+    assert abs(ours.stat_info["global_test_acc"][0] - ref_api.stat_info["global_test_acc"][0]) < 1e-6
+    assert abs(ours.stat_info["person_test_acc"][0] - ref_api.stat_info["person_test_acc"][0]) < 1e-6
+
+
+@pytest.mark.slow
+def test_fedavg_matches_reference_cpu():
+    store, train, test = _setup()
+    args = make_args(client_num_in_total=2, batch_size=2, epochs=1, comm_round=1, lr=0.001)
+    torch.manual_seed(7)
+    init = AlexNet3D_Dropout(num_classes=1).state_dict()
+    ref_api, ref_model, _ = ref_harness.build_reference_api("fedavg", store, train, test, args, "cpu", shuffle=False,
+                                                           model_state=init, p_drop=0.0)
+    captured = {}
+    orig_agg = ref_api._aggregate
+    def agg(w_locals):
+        out = orig_agg(w_locals)
+        captured.setdefault("w", {k: v.clone() for k, v in out.items()})
+        return out
+    ref_api._aggregate = agg
+    # the reference's main_fedavg hard-requires CUDA; on CPU its trainer's model.to(device) is a no-op
+    ref_api.train()
+    ours = _ours("fedavg", store, train, test, args, init)
+    args.final_finetune = False
+    ours.run_round(0)
+    sd = ours.w_global.state_dict(cast_int=False)
+    for k, v in captured["w"].items():
+        torch.testing.assert_close(sd[k].float(), v.float(), rtol=2e-4, atol=2e-5, msg=lambda m: f"{k}: {m}")
