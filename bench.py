@@ -1,0 +1,359 @@
+#!/usr/bin/env python
+"""Headline benchmark: SalientGrads FL rounds, 3-D AlexNet at ABCD shape (1x121x145x121),
+21 site clients, batch 16, 2 local epochs, dense_ratio 0.5 (BASELINE.json config 3).
+
+    python bench.py --gpus N --steps K --warmup W            # this framework
+    python bench.py --impl reference --gpus N --steps K ...  # the unmodified reference (baseline/_ref)
+
+One *step* = one communication round: local training of all 21 sampled clients (84 SGD steps of 16
+volumes), the sample-weighted masked aggregation, and the evaluation of the global + personalised
+model on every client's test split.  ``value`` = trained samples / s over the whole job (device-timed
+with inputs resident on the device); ``e2e`` = the same through the public API with every batch copied
+host->device from pinned memory and the metrics read back.  Data are synthetic 8-bit volumes, weights
+random-init.  Rank 0 prints ONE JSON line.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import logging
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+import types
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np
+import torch
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=3)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--clients", type=int, default=21)
+    p.add_argument("--per-site", type=int, default=40, help="subjects per site (80/20 train/test split)")
+    p.add_argument("--batch", type=int, default=16)
+    p.add_argument("--epochs", type=int, default=2)
+    p.add_argument("--dense-ratio", type=float, default=0.5)
+    p.add_argument("--engine", default="auto", choices=["auto", "b200", "torch"])
+    p.add_argument("--agg", default="auto", choices=["auto", "fused", "nccl"])
+    p.add_argument("--shape", default="121,145,121")
+    p.add_argument("--skip-e2e", action="store_true")
+    return p.parse_args()
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                                          "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thr = threading.Thread(target=self._read, daemon=True)
+            self.thr.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        load = [s for s in sm if s > 0.5 * max(sm)] if sm else []
+        return {"sm_mhz": statistics.median(load) if load else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_fl_args(a, world):
+    return types.SimpleNamespace(
+        model="3DCNN", dataset="ABCD", batch_size=a.batch, client_optimizer="sgd", lr=0.01, lr_decay=0.998, wd=5e-4,
+        epochs=a.epochs, client_num_in_total=a.clients, client_num_per_round=a.clients, frac=1.0, momentum=0.0,
+        comm_round=a.steps + a.warmup, frequency_of_the_test=1, gpu=0, ci=0, dense_ratio=a.dense_ratio, anneal_factor=0.5,
+        seed=1024, cs="v0", itersnip_iteration=1, stratified_sampling=False, active=1.0, snip_mask=True, erk_power_scale=1.0,
+        final_finetune=False)
+
+
+def build_store(a, shape, pin):
+    from neuroimagedisttraining_b200.data import SyntheticABCD
+    return SyntheticABCD(a.clients * a.per_site, shape=shape, n_sites=a.clients, seed=0, pool=4, pin=pin,
+                         site_sizes=[a.per_site] * a.clients)
+
+
+def timed_rounds(fn, k, ctx, device):
+    """barrier + sync | K rounds between CUDA events | sync + barrier; returns max-over-ranks seconds."""
+    ctx.barrier()
+    torch.cuda.synchronize(device)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(k):
+        fn(i)
+    e1.record()
+    torch.cuda.synchronize(device)
+    ctx.barrier()
+    t = torch.tensor([e0.elapsed_time(e1) / 1e3], dtype=torch.float64, device=device)
+    ctx.all_reduce_max(t)
+    return float(t.item())
+
+
+def run_ours(a):
+    from neuroimagedisttraining_b200.data import load_partition_data_abcd
+    from neuroimagedisttraining_b200.fl import SalientGradsAPI, SlabTrainer
+    from neuroimagedisttraining_b200.models import AlexNet3D_Dropout
+    from neuroimagedisttraining_b200.ops import native
+    from neuroimagedisttraining_b200.parallel import init_distributed, shutdown
+
+    ctx = init_distributed()
+    device = ctx.device
+    assert device.type == "cuda", "bench.py needs a GPU"
+    shape = tuple(int(s) for s in a.shape.split(","))
+    fl_args = make_fl_args(a, ctx.world_size)
+    logger = logging.getLogger("bench"); logger.setLevel(logging.ERROR)
+    torch.manual_seed(fl_args.seed)
+    store = build_store(a, shape, pin=True)
+    dataset = load_partition_data_abcd(store, client_number=a.clients, batch_size=a.batch)
+    model = AlexNet3D_Dropout(num_classes=1, in_shape=shape)
+    engine = None
+    engine_name = "torch(scaffold)+flat-kernels"
+    if a.engine in ("auto", "b200"):
+        try:
+            from neuroimagedisttraining_b200.ops.engine_b200 import B200Engine
+            engine = B200Engine(model, device, max_batch=a.batch, input_scale=store.scale)
+            engine_name = "b200"
+        except ImportError:
+            if a.engine == "b200":
+                raise
+    trainer = SlabTrainer(model, fl_args, logger, device=device, store=store, engine=engine)
+    api = SalientGradsAPI(dataset, device, fl_args, trainer, logger, dist=ctx, agg_mode=a.agg)
+    api.w_init = api.w_global.clone()
+
+    torch.cuda.synchronize(device)
+    t0 = time.perf_counter()
+    api.mask = api.generate_global_mask_snip()
+    torch.cuda.synchronize(device)
+    mask_s = time.perf_counter() - t0
+
+    samples_per_round = a.epochs * sum(api.client_list[c].get_sample_number() for c in range(a.clients))
+    rnd = [0]
+
+    def one_round(_i):
+        api.run_round(rnd[0], mask=api.mask)
+        rnd[0] += 1
+
+    for _ in range(a.warmup):
+        one_round(0)
+    # ---- e2e: public API, pinned host -> device copies every batch, metrics read back every round
+    e2e = None
+    stager = trainer._stager(a.batch)
+    if not a.skip_e2e:
+        h0 = stager.h2d_bytes
+        n0 = native.LAUNCH_COUNT
+        t_e2e = timed_rounds(one_round, a.steps, ctx, device)
+        h2d = (stager.h2d_bytes - h0) / a.steps
+        steps_local = sum(len(api.client_list[c].local_training_data) for c in api.local_clients(range(a.clients))) * a.epochs
+        # D2H per round: one fp32 mean loss per client-epoch + 3 fp64 counters per evaluated (client, model)
+        d2h = 4 * a.epochs * len(api.local_clients(range(a.clients))) + 2 * 24 * len(api.local_clients(range(a.clients)))
+        e2e = {"value": samples_per_round * a.steps / t_e2e, "unit": "samples/s", "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * t_e2e / a.steps}
+    # ---- device-timed: inputs resident on the device (no H2D inside the timed region)
+    trainer._stagers[a.batch] = make_device_stager(store, device, a.batch)
+    one_round(0)
+    clk = ClockSampler(ctx.local_rank)
+    if ctx.is_main:
+        clk.start()
+    n0 = native.LAUNCH_COUNT
+    t_dev = timed_rounds(one_round, a.steps, ctx, device)
+    launches = native.LAUNCH_COUNT - n0
+    clocks = clk.stop() if ctx.is_main else None
+    stat = api.finalize_stats()
+    if ctx.is_main:
+        out = {
+            "metric": "samples_per_s_salientgrads_alexnet3d_abcd_round", "value": samples_per_round * a.steps / t_dev,
+            "unit": "samples/s", "n_gpus": ctx.world_size, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": 1e3 * t_dev / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "bf16" if engine_name == "b200" else "fp32(tf32 conv)", "data": "synthetic 8-bit ABCD-shape volumes, random-init weights",
+            "impl": "ours", "engine": engine_name,
+            "config": {"model": "AlexNet3D_Dropout(1 logit)", "algorithm": "SalientGrads dense_ratio=%g" % a.dense_ratio,
+                       "clients": a.clients, "clients_per_round": a.clients, "local_epochs": a.epochs, "batch": a.batch,
+                       "global_batch": a.batch, "seq_len": "x".join(map(str, shape)), "train_samples_per_round": samples_per_round,
+                       "sgd_steps_per_round": samples_per_round // a.batch, "eval_samples_per_round": 2 * a.clients * (a.per_site // 5),
+                       "parallelism": "client-parallel x%d (one process per GPU)" % ctx.world_size,
+                       "step_definition": "one FL communication round (train + aggregate + eval of all clients)",
+                       "l2_policy": "inputs larger than L2 (506 MB conv1 activations per SGD step)",
+                       "aggregation": api.aggregator.mode},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "mask_generation_s": mask_s,
+            "global_test_acc": float(stat["global_test_acc"][-1]) if stat["global_test_acc"] else None,
+            "phase_time_s": {k: round(v["total_s"], 4) for k, v in stat["phase_time_s"].items()},
+        }
+        print(json.dumps(out))
+    shutdown()
+
+
+def make_device_stager(store, device, batch):
+    """Stager variant with the whole synthetic dataset resident on the device."""
+    from neuroimagedisttraining_b200.runtime.staging import BatchStager
+
+    class DeviceStager(BatchStager):
+        def __init__(self):
+            self.store, self.device, self.batch_size, self.cuda = store, torch.device(device), batch, True
+            self.h2d_bytes = 0
+            self.vol = store._cache.to(device)
+            self.lab = torch.from_numpy(store.labels).to(device)
+
+        def iterate(self, loader):
+            for b in loader:
+                idx = torch.sort(b[0])[0].to(self.device, non_blocking=True)
+                yield self.vol.index_select(0, idx), self.lab.index_select(0, idx)
+
+    return DeviceStager()
+
+
+# ------------------------------------------------------------------------------- reference arm
+def run_reference(a):
+    sys.path.insert(0, ROOT)
+    from baseline import ref_harness
+    why = ref_harness.reference_available()
+    if why:
+        print(json.dumps({"impl": "reference", "unavailable": why}))
+        return
+    import copy
+    import torch.distributed as dist
+    from neuroimagedisttraining_b200.data import site_partition
+    from neuroimagedisttraining_b200.parallel import init_distributed, shutdown
+
+    ctx = init_distributed()
+    device = ctx.device
+    shape = tuple(int(s) for s in a.shape.split(","))
+    fl_args = make_fl_args(a, ctx.world_size)
+    import random
+    random.seed(fl_args.seed); np.random.seed(fl_args.seed); torch.manual_seed(fl_args.seed); torch.cuda.manual_seed_all(fl_args.seed)
+    torch.backends.cudnn.deterministic = True   # main_sailentgrads.py:268
+    store = build_store(a, shape, pin=False)
+    train, test, _ = site_partition(store.sites)
+    api, model, source = ref_harness.build_reference_api("salientgrads", store, train, test, fl_args, device)
+    samples_per_round = a.epochs * sum(len(t) for t in train)
+    marks = []
+
+    def mark():
+        torch.cuda.synchronize(device)
+        marks.append(time.perf_counter())
+
+    if ctx.world_size == 1:
+        # stock code path, verbatim: api.train(); round boundaries are observed by wrapping the
+        # per-round evaluation call (timing hooks only -- nothing on the compute path is replaced)
+        orig_test, orig_mask = api._test_on_all_clients, api.generate_global_mask_snip
+        def test_hook(*x, **k):
+            r = orig_test(*x, **k); mark(); return r
+        def mask_hook(*x, **k):
+            r = orig_mask(*x, **k); mark(); return r
+        api._test_on_all_clients, api.generate_global_mask_snip = test_hook, mask_hook
+        clk = ClockSampler(ctx.local_rank); clk.start()
+        h0 = None
+        t_start = time.perf_counter()
+        api.train()
+        clocks = clk.stop()
+        # marks: [after mask, after round 0, ..., after round W+K-1, after final test]
+        bounds = marks[: 1 + a.warmup + a.steps]
+        t = bounds[-1] - bounds[a.warmup]
+        mask_s = marks[0] - t_start
+        h2d = source.h2d_bytes / (a.warmup + a.steps + 1)
+    else:
+        # the reference is single-GPU only: unchanged per-client code on each rank + the thinnest NCCL wrapper
+        mine = [c for c in range(a.clients) if ctx.owns(c)]
+        t_start = time.perf_counter()
+        scores = None
+        from fedml_api.standalone.sailentgrads.snip import get_mask_from_grads
+        for c in mine:
+            s = api.client_list[c].generate_sailency_scores_from_each_client(itersnip_iteration=1, stratified_sampling=False)
+            scores = s if scores is None else {k: scores[k] + v for k, v in s.items()}
+        keys = list(dict(api.client_list[0].generate_sailency_scores_from_each_client(1, False)).keys()) if scores is None else list(scores.keys())
+        flat = torch.cat([scores[k].flatten() for k in keys]) if scores is not None else None
+        if flat is None:
+            flat = torch.zeros(sum(p.numel() for n, p in model.named_parameters() if p.dim() > 1), device=device)
+        dist.all_reduce(flat); flat /= a.clients
+        off = 0; avg = {}
+        ref_shapes = {n: m.weight.shape for n, m in model.named_modules() if isinstance(m, (torch.nn.Conv3d, torch.nn.Linear))}
+        for k in keys:
+            n = ref_shapes[k].numel(); avg[k] = flat[off:off + n].view(ref_shapes[k]); off += n
+        _, _, mask = get_mask_from_grads(api.model_trainer, avg, fl_args.dense_ratio, api.model_trainer.get_trainable_params())
+        torch.cuda.synchronize(device); mask_s = time.perf_counter() - t_start
+        w_global = api.model_trainer.get_model_params()
+        w_per = {c: copy.deepcopy(w_global) for c in mine}
+        total_n = sum(len(t) for t in train)
+        def one_round(r):
+            nonlocal w_global
+            part = None
+            for c in mine:
+                w, _, _ = api.client_list[c].train(copy.deepcopy(w_global), r, mask)
+                w_per[c] = copy.deepcopy(w)
+                wt = api.client_list[c].get_sample_number() / total_n
+                part = {k: v * wt for k, v in w.items()} if part is None else {k: part[k] + w[k] * wt for k in part}
+            keys_ = list(w_global.keys())
+            flat = torch.cat([(part[k] if part is not None else torch.zeros_like(w_global[k])).flatten().float() for k in keys_]).to(device)
+            dist.all_reduce(flat)
+            flat = flat.cpu(); off = 0
+            for k in keys_:
+                n = w_global[k].numel(); w_global[k] = flat[off:off + n].view(w_global[k].shape); off += n
+            for c in mine:
+                api.client_list[c].local_test(w_global, True)
+                api.client_list[c].local_test(w_per[c], True)
+        for r in range(a.warmup):
+            one_round(r)
+        clk = ClockSampler(ctx.local_rank)
+        if ctx.is_main:
+            clk.start()
+        t = timed_rounds(lambda i: one_round(a.warmup + i), a.steps, ctx, device)
+        clocks = clk.stop() if ctx.is_main else None
+        h2d = source.h2d_bytes / (a.warmup + a.steps + 1)
+    if ctx.is_main:
+        print(json.dumps({
+            "impl": "reference", "metric": "samples_per_s_salientgrads_alexnet3d_abcd_round", "value": samples_per_round * a.steps / t,
+            "unit": "samples/s", "n_gpus": ctx.world_size, "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * t / a.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "fp32 (TF32 conv, cudnn.deterministic=True)",
+            "data": "synthetic 8-bit ABCD-shape volumes served as fp32, random-init weights",
+            "config": {"model": "AlexNet3D_Dropout(1 logit)", "algorithm": "SalientGrads dense_ratio=%g" % a.dense_ratio,
+                       "clients": a.clients, "local_epochs": a.epochs, "batch": a.batch, "global_batch": a.batch,
+                       "seq_len": "x".join(map(str, shape)), "train_samples_per_round": samples_per_round,
+                       "parallelism": "reference loop verbatim" if ctx.world_size == 1 else "reference Client.train per rank + NCCL all_reduce wrapper x%d" % ctx.world_size},
+            "clocks": clocks, "e2e": {"value": samples_per_round * a.steps / t, "unit": "samples/s", "h2d_bytes_per_step": h2d,
+                                      "d2h_bytes_per_step": None, "note": "the reference has no device-resident mode: its only path is end to end"},
+            "gpu_launches": 0, "mask_generation_s": mask_s}))
+    shutdown()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

@@ -1,0 +1,145 @@
+"""Flat-slab ops: CPU restatements vs. hand formulas (always) and sm_100a kernels vs. the fp32
+PyTorch restatements (``-m gpu``)."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from neuroimagedisttraining_b200 import ops
+from neuroimagedisttraining_b200.models import AlexNet3D_Dropout, Tiny3DCNN
+from neuroimagedisttraining_b200.ops import reference as R
+from neuroimagedisttraining_b200.runtime.slab import ParamSlab, SlabLayout
+
+
+def _rand(n, seed=0, device="cpu"):
+    g = torch.Generator().manual_seed(seed)
+    return torch.randn(n, generator=g).to(device)
+
+
+def test_sgd_reference_matches_torch_optimizer():
+    torch.manual_seed(0)
+    lin = torch.nn.Linear(8, 4)
+    w0 = torch.cat([p.detach().flatten() for p in lin.parameters()]).clone()
+    opt = torch.optim.SGD(lin.parameters(), lr=0.1, momentum=0.9, weight_decay=5e-4)
+    w = w0.clone()
+    mom = torch.zeros_like(w)
+    for step in range(3):
+        x = torch.randn(5, 8)
+        lin.zero_grad()
+        (lin(x) ** 2).sum().backward()
+        g = torch.cat([p.grad.flatten() for p in lin.parameters()]).clone()
+        torch.nn.utils.clip_grad_norm_(lin.parameters(), 10)
+        opt.step()
+        R.masked_sgd_step(w, g, mom, None, 0.1, 0.9, 5e-4, 10.0, first_step=(step == 0))
+        torch.testing.assert_close(w, torch.cat([p.detach().flatten() for p in lin.parameters()]), rtol=1e-5, atol=1e-6)
+
+
+def test_aggregate_reference_order_is_bit_exact():
+    xs = [_rand(1000, s) for s in range(5)]
+    ns = [3, 7, 11, 2, 9]
+    ws = [n / sum(ns) for n in ns]
+    out = torch.empty(1000)
+    R.weighted_aggregate(out, xs, ws)
+    ref = xs[0] * ws[0]
+    for x, w in zip(xs[1:], ws[1:]):
+        ref += x * w
+    assert torch.equal(out, ref)
+
+
+def test_topk_reference_semantics():
+    m = Tiny3DCNN(1)
+    layout = SlabLayout.from_module(m)
+    scores = torch.rand(layout.param_numel)
+    mask = torch.empty(layout.param_numel)
+    _, info = ops.global_topk_mask(scores, layout, 0.3, mask)
+    kept = sum(float(mask[layout[n].offset:layout[n].offset + layout[n].numel].sum()) for n in layout.prunable_names)
+    assert kept == info["k"] == int(layout.prunable_numel() * 0.3)
+    for n in layout.param_names:
+        if not layout[n].prunable:
+            assert bool((mask[layout[n].offset:layout[n].offset + layout[n].numel] == 1).all())
+
+
+# ------------------------------------------------------------------------------------ GPU
+@pytest.mark.gpu
+@pytest.mark.parametrize("momentum,use_mask,first", [(0.0, True, True), (0.9, True, False), (0.9, False, True), (0.0, False, False)])
+def test_masked_sgd_kernel(momentum, use_mask, first):
+    n = 2570244
+    dev = "cuda"
+    w, g, mom = _rand(n, 1, dev), _rand(n, 2, dev) * 0.01, _rand(n, 3, dev)
+    mask = (torch.rand(n, device=dev) > 0.5).float() if use_mask else None
+    w_ref, mom_ref = w.clone().cpu(), mom.clone().cpu()
+    tn = R.masked_sgd_step(w_ref, g.cpu(), mom_ref, mask.cpu() if use_mask else None, 0.01, momentum, 5e-4, 10.0, first)
+    norm = torch.zeros((), device=dev)
+    ops.masked_sgd_step(w, g, mom, mask, 0.01, momentum, 5e-4, 10.0, first, norm_out=norm)
+    torch.testing.assert_close(w.cpu(), w_ref, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(norm.cpu(), tn, rtol=1e-4, atol=1e-5)
+    if momentum:
+        torch.testing.assert_close(mom.cpu(), mom_ref, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.gpu
+def test_masked_sgd_kernel_clips():
+    n = 4096
+    w, g = _rand(n, 1, "cuda"), _rand(n, 2, "cuda") * 5.0
+    w_ref = w.clone().cpu()
+    R.masked_sgd_step(w_ref, g.cpu(), None, None, 0.1, 0.0, 0.0, 10.0, True)
+    ops.masked_sgd_step(w, g, None, None, 0.1, 0.0, 0.0, 10.0, True)
+    torch.testing.assert_close(w.cpu(), w_ref, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("k", [1, 3, 21, 70])
+def test_weighted_aggregate_kernel_bit_exact(k):
+    n, nm = 2571672, 2570244
+    xs = [_rand(n, s, "cuda") for s in range(k)]
+    ns = [5 + 3 * i for i in range(k)]
+    ws = [x / sum(ns) for x in ns]
+    mask = (torch.rand(nm, device="cuda") > 0.5).float()
+    out = torch.empty(n, device="cuda")
+    ops.weighted_aggregate(out, xs, ws, mask)
+    ref = torch.empty(n)
+    R.weighted_aggregate(ref, [x.cpu() for x in xs], ws, mask.cpu())
+    assert torch.equal(out.cpu(), ref), float((out.cpu() - ref).abs().max())
+
+
+@pytest.mark.gpu
+def test_saliency_accumulate_kernel():
+    n = 2570244
+    s, g, w = torch.rand(n, device="cuda"), _rand(n, 1, "cuda"), _rand(n, 2, "cuda")
+    ref = R.saliency_accumulate(s.clone().cpu(), g.cpu(), w.cpu(), 0.25)
+    ops.saliency_accumulate(s, g, w, 0.25)
+    torch.testing.assert_close(s.cpu(), ref, rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("keep", [0.5, 0.1, 0.9])
+def test_global_topk_mask_kernel(keep):
+    layout = SlabLayout.from_module(AlexNet3D_Dropout(1))
+    torch.manual_seed(0)
+    scores = (torch.rand(layout.param_numel) ** 4) * 1e-3
+    scores[::7] = scores[3]          # plenty of exact ties
+    ref_mask = torch.empty(layout.param_numel)
+    _, info_ref = ops.global_topk_mask(scores.clone(), layout, keep, ref_mask)
+    mask = torch.empty(layout.param_numel, device="cuda")
+    _, info = ops.global_topk_mask(scores.cuda(), layout, keep, mask)
+    diff = int((mask.cpu() != ref_mask).sum())
+    # the only tolerated disagreement is at the threshold value itself (normalising-sum round-off)
+    assert diff <= 8, (diff, info, info_ref)
+    assert abs(info["threshold"] - info_ref["threshold"]) <= 1e-6 * abs(info_ref["threshold"]) + 1e-12
+    assert info["kept"] >= info["k"]
+
+
+@pytest.mark.gpu
+def test_count_hamming_sqdist_kernels():
+    n = 1000003
+    a = (torch.rand(n, device="cuda") > 0.3).float() * _rand(n, 1, "cuda")
+    b = (torch.rand(n, device="cuda") > 0.6).float()
+    assert int(ops.count_nonzero(a)) == int(torch.count_nonzero(a))
+    assert int(ops.hamming_distance(a, b)) == int(R.hamming_distance(a.cpu(), b.cpu()))
+    torch.testing.assert_close(ops.squared_distance(a, b).cpu(), R.squared_distance(a.cpu(), b.cpu()), rtol=1e-4, atol=1e-3)
+    w, ref = _rand(4096, 5, "cuda"), _rand(4096, 6, "cuda")
+    w2 = w.clone().cpu()
+    R.prox_sgd_pull(w2, ref.cpu(), 0.1, 0.5)
+    ops.prox_pull(w, ref, 0.1, 0.5)
+    torch.testing.assert_close(w.cpu(), w2, rtol=1e-6, atol=1e-7)
