@@ -1,0 +1,368 @@
+// Fused BatchNorm3d (training or eval statistics) + ReLU + MaxPool3d on channels-last (NDHWC) bf16
+// activations, forward and backward.  Replaces K3+K4+K5 of SURVEY §2.5 (cuDNN BN, ATen ReLU,
+// ATen MaxPool3d fwd/bwd = 6 library kernels and 4 full-size intermediates per block in the
+// reference, fedml_api/model/cv/salient_models.py:147-168) with:
+//
+//   conv epilogue        -> per-tile (sum, sum^2) partials               (conv kernels)
+//   nidt_bn_finalize     -> mean / invstd / scale / shift, running stats  (tiny)
+//   nidt_bn_relu_pool_fwd-> a = maxpool(relu(y*scale+shift))              (1 read of y, 1/27 write)
+//   nidt_bn_relu_pool_bwd_reduce -> sum(dyhat), sum(dyhat*xhat) partials  (argmax recomputed from y)
+//   nidt_bn_bwd_finalize -> c1, c2, dgamma, dbeta
+//   nidt_bn_relu_pool_bwd_apply  -> dy = scale*(dyhat - c1 - xhat*c2)     (input of dgrad / wgrad)
+//
+// No argmax indices, no normalised activations and no ReLU masks are ever stored.
+#include "common.cuh"
+
+namespace nidt {
+
+struct BlockGeom {
+    int N, D, H, W, C;       // conv output (pre-pool) extents
+    int pk, ps;              // pool kernel / stride (0 = no pooling)
+    int Dp, Hp, Wp;          // pooled extents (== D,H,W when pk == 0)
+};
+
+__device__ __forceinline__ void unpack8(const uint4& v, float* f) {
+    const __nv_bfloat162* p = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float2 t = __bfloat1622float2(p[i]);
+        f[2 * i] = t.x;
+        f[2 * i + 1] = t.y;
+    }
+}
+__device__ __forceinline__ uint4 pack8(const float* f) {
+    uint4 v;
+    __nv_bfloat162* p = reinterpret_cast<__nv_bfloat162*>(&v);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) p[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+    return v;
+}
+
+// ------------------------------------------------------------------------------- finalize
+// partials: [T][2][C] (sum, sumsq) per conv tile.  One block per 32 channels, 8 tile-slices.
+__global__ void __launch_bounds__(256) bn_finalize_kernel(
+    const float* __restrict__ partials, int T, int C, double count, const float* __restrict__ gamma, const float* __restrict__ beta,
+    float* __restrict__ running_mean, float* __restrict__ running_var, float* __restrict__ num_batches, float momentum, float eps,
+    float* __restrict__ scale, float* __restrict__ shift, float* __restrict__ mean_out, float* __restrict__ invstd_out) {
+    __shared__ double s1[8][32], s2[8][32];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + tx;
+    double a = 0.0, b = 0.0;
+    if (c < C)
+        for (int t = ty; t < T; t += 8) {
+            a += (double)partials[((size_t)t * 2 + 0) * C + c];
+            b += (double)partials[((size_t)t * 2 + 1) * C + c];
+        }
+    s1[ty][tx] = a;
+    s2[ty][tx] = b;
+    __syncthreads();
+    if (ty == 0 && c < C) {
+        for (int i = 1; i < 8; ++i) { a += s1[i][tx]; b += s2[i][tx]; }
+        const double mean = a / count;
+        double var = b / count - mean * mean;
+        if (var < 0.0) var = 0.0;
+        const float invstd = (float)(1.0 / sqrt(var + (double)eps));
+        const float g = gamma[c];
+        scale[c] = g * invstd;
+        shift[c] = beta[c] - (float)mean * g * invstd;
+        mean_out[c] = (float)mean;
+        invstd_out[c] = invstd;
+        if (running_mean != nullptr) {
+            const double unbiased = count > 1.0 ? var * count / (count - 1.0) : var;
+            running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)mean;
+            running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && num_batches != nullptr) *num_batches += 1.f;
+}
+
+// eval mode: scale/shift from the running statistics
+__global__ void bn_eval_prepare_kernel(int C, const float* __restrict__ gamma, const float* __restrict__ beta,
+                                       const float* __restrict__ running_mean, const float* __restrict__ running_var, float eps,
+                                       float* __restrict__ scale, float* __restrict__ shift) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < C) {
+        const float s = gamma[c] * rsqrtf(running_var[c] + eps);
+        scale[c] = s;
+        shift[c] = beta[c] - running_mean[c] * s;
+    }
+}
+
+// -------------------------------------------------------------------------------- forward
+// one thread = one output position x 8 channels
+__global__ void __launch_bounds__(256) bn_relu_pool_fwd_kernel(
+    const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ a, BlockGeom g,
+    const float* __restrict__ scale, const float* __restrict__ shift, int relu) {
+    const int CG = g.C >> 3;
+    const int64_t total = (int64_t)g.N * g.Dp * g.Hp * g.Wp * CG;
+    for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+        const int cg = (int)(idx % CG);
+        int64_t p = idx / CG;
+        const int wp = (int)(p % g.Wp); p /= g.Wp;
+        const int hp = (int)(p % g.Hp); p /= g.Hp;
+        const int dp = (int)(p % g.Dp);
+        const int n = (int)(p / g.Dp);
+        float sc[8], sh[8], best[8];
+        *reinterpret_cast<float4*>(sc) = ld4(scale + cg * 8);
+        *reinterpret_cast<float4*>(sc + 4) = ld4(scale + cg * 8 + 4);
+        *reinterpret_cast<float4*>(sh) = ld4(shift + cg * 8);
+        *reinterpret_cast<float4*>(sh + 4) = ld4(shift + cg * 8 + 4);
+        if (g.pk == 0) {
+            const uint4 v = *reinterpret_cast<const uint4*>(y + ((((int64_t)n * g.D + dp) * g.H + hp) * g.W + wp) * g.C + cg * 8);
+            unpack8(v, best);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                best[i] = fmaf(best[i], sc[i], sh[i]);
+                if (relu) best[i] = fmaxf(best[i], 0.f);
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) best[i] = -INFINITY;
+            for (int kd = 0; kd < g.pk; ++kd)
+                for (int kh = 0; kh < g.pk; ++kh) {
+                    const __nv_bfloat16* row = y + ((((int64_t)n * g.D + dp * g.ps + kd) * g.H + hp * g.ps + kh) * g.W + wp * g.ps) * g.C + cg * 8;
+                    for (int kw = 0; kw < g.pk; ++kw) {
+                        float f[8];
+                        unpack8(*reinterpret_cast<const uint4*>(row + (int64_t)kw * g.C), f);
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) best[i] = fmaxf(best[i], fmaf(f[i], sc[i], sh[i]));
+                    }
+                }
+            if (relu) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) best[i] = fmaxf(best[i], 0.f);
+            }
+        }
+        *reinterpret_cast<uint4*>(a + idx * 8) = pack8(best);
+    }
+}
+
+// ------------------------------------------------------------------------------- backward
+// Shared by reduce (write_dy = 0) and apply (write_dy = 1).  One thread = one pooling window
+// (or one position when pk == 0) x 8 channels.  Windows are enumerated over ceil(D/ps) etc. so
+// that the remainder positions no pooled output covers are visited too (their dyhat is 0).
+template <bool kApply>
+__global__ void __launch_bounds__(256) bn_relu_pool_bwd_kernel(
+    const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ da, __nv_bfloat16* __restrict__ dy, BlockGeom g,
+    const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean, const float* __restrict__ invstd,
+    const float* __restrict__ c12 /* [2][C]: c1, c2 */, float* __restrict__ partials /* [grid][2][C] */, int relu) {
+    extern __shared__ float sh_red[];   // reduce only: [2][PB][C]
+    const int CG = g.C >> 3;
+    const int PB = blockDim.x / CG;     // positions per block pass (blockDim.x == PB*CG)
+    const int cg = threadIdx.x % CG;
+    const int pl = threadIdx.x / CG;
+    const int step = g.pk ? g.ps : 1;
+    const int Dw = g.pk ? (g.D + step - 1) / step : g.D;
+    const int Hw = g.pk ? (g.H + step - 1) / step : g.H;
+    const int Ww = g.pk ? (g.W + step - 1) / step : g.W;
+    const int64_t nwin = (int64_t)g.N * Dw * Hw * Ww;
+    float sc[8], shf[8], mu[8], is[8], k1[8], k2[8], acc1[8], acc2[8];
+    *reinterpret_cast<float4*>(sc) = ld4(scale + cg * 8);   *reinterpret_cast<float4*>(sc + 4) = ld4(scale + cg * 8 + 4);
+    *reinterpret_cast<float4*>(shf) = ld4(shift + cg * 8);  *reinterpret_cast<float4*>(shf + 4) = ld4(shift + cg * 8 + 4);
+    *reinterpret_cast<float4*>(mu) = ld4(mean + cg * 8);    *reinterpret_cast<float4*>(mu + 4) = ld4(mean + cg * 8 + 4);
+    *reinterpret_cast<float4*>(is) = ld4(invstd + cg * 8);  *reinterpret_cast<float4*>(is + 4) = ld4(invstd + cg * 8 + 4);
+    if (kApply) {
+        *reinterpret_cast<float4*>(k1) = ld4(c12 + cg * 8);        *reinterpret_cast<float4*>(k1 + 4) = ld4(c12 + cg * 8 + 4);
+        *reinterpret_cast<float4*>(k2) = ld4(c12 + g.C + cg * 8);  *reinterpret_cast<float4*>(k2 + 4) = ld4(c12 + g.C + cg * 8 + 4);
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc1[i] = acc2[i] = 0.f;
+
+    for (int64_t win = (int64_t)blockIdx.x * PB + pl; win < nwin; win += (int64_t)gridDim.x * PB) {
+        if (pl >= PB) break;
+        int64_t p = win;
+        const int ww = (int)(p % Ww); p /= Ww;
+        const int hw = (int)(p % Hw); p /= Hw;
+        const int dw = (int)(p % Dw);
+        const int n = (int)(p / Dw);
+        if (g.pk == 0) {
+            const int64_t off = ((((int64_t)n * g.D + dw) * g.H + hw) * g.W + ww) * g.C + cg * 8;
+            float f[8], d[8];
+            unpack8(*reinterpret_cast<const uint4*>(y + off), f);
+            unpack8(*reinterpret_cast<const uint4*>(da + off), d);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float xh = (f[i] - mu[i]) * is[i];
+                const float dyh = (!relu || fmaf(f[i], sc[i], shf[i]) > 0.f) ? d[i] : 0.f;
+                if (kApply) d[i] = sc[i] * (dyh - k1[i] - xh * k2[i]);
+                else { acc1[i] += dyh; acc2[i] = fmaf(dyh, xh, acc2[i]); }
+            }
+            if (kApply) *reinterpret_cast<uint4*>(dy + off) = pack8(d);
+            continue;
+        }
+        const bool has_out = dw < g.Dp && hw < g.Hp && ww < g.Wp;
+        float best[8], dav[8];
+        int arg[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { best[i] = -INFINITY; arg[i] = -1; dav[i] = 0.f; }
+        if (has_out) {
+            unpack8(*reinterpret_cast<const uint4*>(da + ((((int64_t)n * g.Dp + dw) * g.Hp + hw) * g.Wp + ww) * g.C + cg * 8), dav);
+            for (int kd = 0; kd < g.pk; ++kd)
+                for (int kh = 0; kh < g.pk; ++kh) {
+                    const __nv_bfloat16* row = y + ((((int64_t)n * g.D + dw * step + kd) * g.H + hw * step + kh) * g.W + ww * step) * g.C + cg * 8;
+                    for (int kw = 0; kw < g.pk; ++kw) {
+                        float f[8];
+                        unpack8(*reinterpret_cast<const uint4*>(row + (int64_t)kw * g.C), f);
+                        const int t = (kd * g.pk + kh) * g.pk + kw;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const float v = fmaf(f[i], sc[i], shf[i]);   // pooling runs on the post-BN value
+                            if (v > best[i]) { best[i] = v; arg[i] = t; }
+                        }
+                    }
+                }
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                if (relu && !(best[i] > 0.f)) arg[i] = -1;             // ReLU gate on the winner
+        }
+        if (!kApply) {
+            if (has_out) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    if (arg[i] >= 0) {
+                        // xhat of the winner, reconstructed from its post-BN value: v = gamma*xhat + beta
+                        // is avoided (gamma may be 0); re-read the winner's y instead.
+                        const int t = arg[i];
+                        const int kd = t / (g.pk * g.pk), kh = (t / g.pk) % g.pk, kw = t % g.pk;
+                        const float yv = __bfloat162float(
+                            y[((((int64_t)n * g.D + dw * step + kd) * g.H + hw * step + kh) * g.W + ww * step + kw) * g.C + cg * 8 + i]);
+                        const float xh = (yv - mu[i]) * is[i];
+                        acc1[i] += dav[i];
+                        acc2[i] = fmaf(dav[i], xh, acc2[i]);
+                    }
+            }
+        } else {
+            for (int kd = 0; kd < g.pk; ++kd) {
+                const int d_ = dw * step + kd;
+                if (d_ >= g.D) break;
+                for (int kh = 0; kh < g.pk; ++kh) {
+                    const int h_ = hw * step + kh;
+                    if (h_ >= g.H) break;
+                    for (int kw = 0; kw < g.pk; ++kw) {
+                        const int w_ = ww * step + kw;
+                        if (w_ >= g.W) break;
+                        const int64_t off = ((((int64_t)n * g.D + d_) * g.H + h_) * g.W + w_) * g.C + cg * 8;
+                        float f[8], o[8];
+                        unpack8(*reinterpret_cast<const uint4*>(y + off), f);
+                        const int t = (kd * g.pk + kh) * g.pk + kw;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const float xh = (f[i] - mu[i]) * is[i];
+                            const float dyh = (arg[i] == t) ? dav[i] : 0.f;
+                            o[i] = sc[i] * (dyh - k1[i] - xh * k2[i]);
+                        }
+                        *reinterpret_cast<uint4*>(dy + off) = pack8(o);
+                    }
+                }
+            }
+        }
+    }
+    if (!kApply) {
+        // deterministic block reduction over the PB positions that share a channel group
+        float* r1 = sh_red;
+        float* r2 = sh_red + PB * g.C;
+        if (pl < PB) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                r1[pl * g.C + cg * 8 + i] = acc1[i];
+                r2[pl * g.C + cg * 8 + i] = acc2[i];
+            }
+        }
+        __syncthreads();
+        for (int c = threadIdx.x; c < g.C; c += blockDim.x) {
+            float a = 0.f, b = 0.f;
+            for (int q = 0; q < PB; ++q) { a += r1[q * g.C + c]; b += r2[q * g.C + c]; }
+            partials[((size_t)blockIdx.x * 2 + 0) * g.C + c] = a;
+            partials[((size_t)blockIdx.x * 2 + 1) * g.C + c] = b;
+        }
+    }
+}
+
+// partials [T][2][C] -> c12 [2][C] (c1 = sum(dyhat)/M, c2 = sum(dyhat*xhat)/M), dgamma, dbeta
+__global__ void __launch_bounds__(256) bn_bwd_finalize_kernel(const float* __restrict__ partials, int T, int C, double count,
+                                                              float* __restrict__ c12, float* __restrict__ dgamma, float* __restrict__ dbeta) {
+    __shared__ double s1[8][32], s2[8][32];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + tx;
+    double a = 0.0, b = 0.0;
+    if (c < C)
+        for (int t = ty; t < T; t += 8) {
+            a += (double)partials[((size_t)t * 2 + 0) * C + c];
+            b += (double)partials[((size_t)t * 2 + 1) * C + c];
+        }
+    s1[ty][tx] = a;
+    s2[ty][tx] = b;
+    __syncthreads();
+    if (ty == 0 && c < C) {
+        for (int i = 1; i < 8; ++i) { a += s1[i][tx]; b += s2[i][tx]; }
+        c12[c] = (float)(a / count);
+        c12[C + c] = (float)(b / count);
+        if (dgamma) dgamma[c] = (float)b;
+        if (dbeta) dbeta[c] = (float)a;
+    }
+}
+
+}  // namespace nidt
+using namespace nidt;
+
+static inline BlockGeom make_geom(int N, int D, int H, int W, int C, int pk, int ps) {
+    BlockGeom g{N, D, H, W, C, pk, ps, D, H, W};
+    if (pk) { g.Dp = (D - pk) / ps + 1; g.Hp = (H - pk) / ps + 1; g.Wp = (W - pk) / ps + 1; }
+    return g;
+}
+
+NIDT_API int nidt_bn_bwd_grid() { return 4 * kNumSMs; }
+
+NIDT_API int nidt_bn_finalize(const float* partials, int T, int C, double count, const float* gamma, const float* beta,
+                              float* running_mean, float* running_var, float* num_batches, float momentum, float eps,
+                              float* scale, float* shift, float* mean, float* invstd, void* stream) {
+    bn_finalize_kernel<<<(C + 31) / 32, 256, 0, (cudaStream_t)stream>>>(partials, T, C, count, gamma, beta, running_mean, running_var,
+                                                                        num_batches, momentum, eps, scale, shift, mean, invstd);
+    NIDT_LAUNCH_CHECK();
+    return 0;
+}
+
+NIDT_API int nidt_bn_eval_prepare(int C, const float* gamma, const float* beta, const float* running_mean, const float* running_var,
+                                  float eps, float* scale, float* shift, void* stream) {
+    bn_eval_prepare_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(C, gamma, beta, running_mean, running_var, eps, scale, shift);
+    NIDT_LAUNCH_CHECK();
+    return 0;
+}
+
+NIDT_API int nidt_bn_relu_pool_fwd(const void* y, void* a, int N, int D, int H, int W, int C, int pk, int ps,
+                                   const float* scale, const float* shift, int relu, void* stream) {
+    NIDT_REQUIRE(C % 8 == 0, "nidt_bn_relu_pool_fwd: C=%d must be a multiple of 8", C);
+    BlockGeom g = make_geom(N, D, H, W, C, pk, ps);
+    const int64_t total = (int64_t)N * g.Dp * g.Hp * g.Wp * (C / 8);
+    int64_t blocks = (total + 255) / 256;
+    if (blocks > (int64_t)kNumSMs * 16) blocks = kNumSMs * 16;
+    if (blocks < 1) blocks = 1;
+    bn_relu_pool_fwd_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)y, (__nv_bfloat16*)a, g, scale, shift, relu);
+    NIDT_LAUNCH_CHECK();
+    return 0;
+}
+
+// partials: >= nidt_bn_bwd_grid()*2*C floats.  Sequence: reduce -> finalize -> apply.
+NIDT_API int nidt_bn_relu_pool_bwd(const void* y, const void* da, void* dy, int N, int D, int H, int W, int C, int pk, int ps,
+                                   const float* scale, const float* shift, const float* mean, const float* invstd,
+                                   float* partials, float* c12, float* dgamma, float* dbeta, int relu, void* stream) {
+    NIDT_REQUIRE(C % 8 == 0 && C <= 2048, "nidt_bn_relu_pool_bwd: unsupported C=%d", C);
+    BlockGeom g = make_geom(N, D, H, W, C, pk, ps);
+    const int CG = C / 8;
+    const int PB = 256 / CG > 0 ? 256 / CG : 1;
+    const int threads = PB * CG;
+    NIDT_REQUIRE(threads <= 1024, "nidt_bn_relu_pool_bwd: C too large");
+    const int grid = nidt_bn_bwd_grid();
+    const size_t smem = (size_t)2 * PB * C * sizeof(float);
+    cudaStream_t s = (cudaStream_t)stream;
+    const double count = (double)N * D * H * W;
+    bn_relu_pool_bwd_kernel<false><<<grid, threads, smem, s>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)da, nullptr, g, scale, shift,
+                                                               mean, invstd, nullptr, partials, relu);
+    NIDT_LAUNCH_CHECK();
+    bn_bwd_finalize_kernel<<<(C + 31) / 32, 256, 0, s>>>(partials, grid, C, count, c12, dgamma, dbeta);
+    NIDT_LAUNCH_CHECK();
+    bn_relu_pool_bwd_kernel<true><<<grid, threads, 0, s>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)da, (__nv_bfloat16*)dy, g, scale, shift,
+                                                           mean, invstd, c12, nullptr, relu);
+    NIDT_LAUNCH_CHECK();
+    return 0;
+}

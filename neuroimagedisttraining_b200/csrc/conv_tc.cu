@@ -1,0 +1,508 @@
+// 3-D convolution as implicit GEMM on the 5th-gen tensor cores (tcgen05.mma, fp32 accumulators in
+// TMEM) fed by TMA, for channels-last bf16 activations with Cin % 64 == 0.
+//
+//   fprop :  Y[m, co]  = sum_{tap, ci} X[m (+) tap, ci] * Wf[co][tap][ci]          (ref K1: nn.Conv3d fwd)
+//   dgrad :  the same kernel on dY with tap-flipped, transposed weights and pad' = k-1-pad (ref K2)
+//   wgrad :  dW[tap][co][ci] = sum_m dY[m, co] * X[m (+) tap, ci]   (MN-major operands, split-K) (ref K2)
+//
+// The GEMM M dimension is a *box* of output positions {bw x bh x bd x bn}: one TMA tiled load of the
+// 5-D activation tensor per filter tap brings the shifted input box into shared memory, zero-filling
+// everything outside the volume -- padding, ragged edge tiles and halos cost no instructions.
+// Persistent CTAs (one per SM), warp-specialised: warp 0 = TMA producer, warp 1 = MMA issuer,
+// warps 2-5 = epilogue (TMEM -> registers -> bf16 -> swizzled smem -> TMA store, plus the
+// per-channel (sum, sum^2) partials BatchNorm needs, so the conv output is never re-read for them).
+// Reference call sites: fedml_api/model/cv/salient_models.py:152-166 (cuDNN fp32 there).
+#include "tc_common.cuh"
+#include <mutex>
+#include <string.h>
+
+namespace nidt {
+
+// --------------------------------------------------------------------------- tensor maps
+PFN_encodeTiled get_encode_tiled() {
+    static PFN_encodeTiled fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = (PFN_encodeTiled)p;
+    });
+    return fn;
+}
+
+int make_tmap_act5d(CUtensorMap* out, const void* base, int N, int D, int H, int W, int C, int bw, int bh, int bd, int bn, int stride) {
+    PFN_encodeTiled enc = get_encode_tiled();
+    if (!enc) { nidt_set_error("cuTensorMapEncodeTiled is unavailable"); return 1; }
+    cuuint64_t gdim[5] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)D, (cuuint64_t)N};
+    cuuint64_t gstr[4] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2, (cuuint64_t)D * H * W * C * 2};
+    // with an element stride s the box spans (b-1)*s+1 input elements and yields b of them
+    cuuint32_t box[5] = {64u, (cuuint32_t)((bw - 1) * stride + 1), (cuuint32_t)((bh - 1) * stride + 1), (cuuint32_t)((bd - 1) * stride + 1),
+                         (cuuint32_t)bn};
+    cuuint32_t estr[5] = {1u, (cuuint32_t)stride, (cuuint32_t)stride, (cuuint32_t)stride, 1u};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        nidt_set_error("cuTensorMapEncodeTiled(5d) failed: %d (N=%d D=%d H=%d W=%d C=%d box=%d,%d,%d,%d stride=%d)", (int)r, N, D, H, W, C, bw, bh, bd, bn, stride);
+        return 1;
+    }
+    return 0;
+}
+
+int make_tmap_mat2d(CUtensorMap* out, const void* base, int64_t rows, int64_t cols, int box_rows) {
+    PFN_encodeTiled enc = get_encode_tiled();
+    if (!enc) { nidt_set_error("cuTensorMapEncodeTiled is unavailable"); return 1; }
+    cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t gstr[1] = {(cuuint64_t)cols * 2};
+    cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1u, 1u};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { nidt_set_error("cuTensorMapEncodeTiled(2d) failed: %d rows=%lld cols=%lld", (int)r, (long long)rows, (long long)cols); return 1; }
+    return 0;
+}
+
+struct ConvGeom {
+    int N, Do, Ho, Wo, Cout;    // output tensor (GEMM M = N*Do*Ho*Wo, GEMM N = Cout)
+    int k, stride, pad;         // filter extent, stride, padding (dgrad passes pad' = k-1-pad)
+    int cin_blocks;             // Cin / 64
+    int bw, bh, bd, bn;         // M-tile box
+    int tw, th, td, tn;         // tiles per dimension
+    int n_tiles;                // ceil(Cout / BLOCK_N)
+    int box_rows;               // bw*bh*bd*bn (<= 128)
+};
+
+constexpr int kConvThreads = 192;
+constexpr int kATileBytes = 128 * 128;   // 128 rows x 64 bf16
+
+template <int BLOCK_N>
+struct FpropCfg {
+    static constexpr int kStages = BLOCK_N == 128 ? 5 : 6;
+    static constexpr int kBTileBytes = BLOCK_N * 128;
+    static constexpr int kStageBytes = kATileBytes + kBTileBytes;
+    static constexpr int kStagingBytes = (BLOCK_N / 64) * kATileBytes;
+    static constexpr int kTmemCols = 2 * BLOCK_N;   // double-buffered accumulator (power of two: 128 / 256)
+    static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers, flags*/ + 128;
+};
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(kConvThreads, 1) conv3d_fprop_tc_kernel(
+    const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_y,
+    const ConvGeom g, const float* __restrict__ bias, float* __restrict__ stats_partials, int total_tiles) {
+    using Cfg = FpropCfg<BLOCK_N>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* stage_base = smem;
+    uint8_t* staging = smem + Cfg::kStages * Cfg::kStageBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(staging + Cfg::kStagingBytes);
+    uint64_t* full = bars;                       // [kStages]
+    uint64_t* empty = bars + Cfg::kStages;       // [kStages]
+    uint64_t* tmem_full = empty + Cfg::kStages;  // [2]
+    uint64_t* tmem_empty = tmem_full + 2;        // [2]
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    uint8_t* row_valid = reinterpret_cast<uint8_t*>(tmem_ptr + 2);   // [128]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int taps = g.k * g.k * g.k;
+    const int num_kb = taps * g.cin_blocks;
+
+    if (warp == 0 && lane == 0) {
+        tc::tma_prefetch_desc(&tm_x);
+        tc::tma_prefetch_desc(&tm_w);
+        tc::tma_prefetch_desc(&tm_y);
+        for (int i = 0; i < Cfg::kStages; ++i) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { tc::mbar_init(&tmem_full[i], 1); tc::mbar_init(&tmem_empty[i], 128); }
+        tc::mbar_fence_init();
+    }
+    if (warp == 1) tc::tmem_alloc<Cfg::kTmemCols>(tmem_ptr);
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    auto decode = [&](int tile, int& n_tile, int& w0, int& h0, int& d0, int& n0) {
+        n_tile = tile % g.n_tiles;
+        int m = tile / g.n_tiles;
+        w0 = (m % g.tw) * g.bw; m /= g.tw;
+        h0 = (m % g.th) * g.bh; m /= g.th;
+        d0 = (m % g.td) * g.bd; m /= g.td;
+        n0 = m * g.bn;
+    };
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===== TMA producer =====
+            uint32_t it = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                int n_tile, w0, h0, d0, n0;
+                decode(tile, n_tile, w0, h0, d0, n0);
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const int s = it % Cfg::kStages;
+                    const uint32_t ph = (it / Cfg::kStages) & 1;
+                    tc::mbar_wait(&empty[s], ph ^ 1);
+                    const int tap = kb / g.cin_blocks, cb = kb - tap * g.cin_blocks;
+                    const int kd = tap / (g.k * g.k), kh = (tap / g.k) % g.k, kw = tap % g.k;
+                    uint8_t* a_dst = stage_base + s * Cfg::kStageBytes;
+                    uint8_t* b_dst = a_dst + kATileBytes;
+                    tc::mbar_expect_tx(&full[s], (uint32_t)(g.box_rows * 128 + Cfg::kBTileBytes));
+                    tc::tma_load_5d(&tm_x, &full[s], a_dst, cb * 64, w0 * g.stride - g.pad + kw, h0 * g.stride - g.pad + kh,
+                                    d0 * g.stride - g.pad + kd, n0);
+                    tc::tma_load_2d(&tm_w, &full[s], b_dst, kb * 64, n_tile * BLOCK_N);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ===== MMA issuer =====
+            constexpr uint32_t idesc = tc::make_idesc_bf16(128, BLOCK_N, 0, 0);
+            uint32_t it = 0, local = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+                const int buf = local & 1;
+                const uint32_t aph = (local >> 1) & 1;
+                tc::mbar_wait(&tmem_empty[buf], aph ^ 1);
+                tc::tc_fence_after();
+                const uint32_t d_tmem = tmem_base + buf * BLOCK_N;
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const int s = it % Cfg::kStages;
+                    const uint32_t ph = (it / Cfg::kStages) & 1;
+                    tc::mbar_wait(&full[s], ph);
+                    tc::tc_fence_after();
+                    const uint32_t a_addr = tc::smem_u32(stage_base + s * Cfg::kStageBytes);
+                    const uint32_t b_addr = a_addr + kATileBytes;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint64_t da = tc::make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
+                        const uint64_t db = tc::make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
+                        tc::umma_bf16(d_tmem, da, db, idesc, (kb | k) != 0);
+                    }
+                    tc::umma_commit(&empty[s]);
+                }
+                tc::umma_commit(&tmem_full[buf]);
+            }
+        }
+    } else {
+        // ===== epilogue: warps 2..5; TMEM lane quarter = warp % 4 =====
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        const int et = threadIdx.x - 64;     // 0..127
+        uint32_t local = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+            int n_tile, w0, h0, d0, n0;
+            decode(tile, n_tile, w0, h0, d0, n0);
+            const int buf = local & 1;
+            const uint32_t aph = (local >> 1) & 1;
+            // the previous tile's TMA store must have finished reading the staging buffer
+            if (et == 0) tc::tma_store_wait_read();
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            {
+                int r = row;
+                const int iw = r % g.bw; r /= g.bw;
+                const int ih = r % g.bh; r /= g.bh;
+                const int id = r % g.bd; r /= g.bd;
+                row_valid[row] = (row < g.box_rows && w0 + iw < g.Wo && h0 + ih < g.Ho && d0 + id < g.Do && n0 + r < g.N) ? 1 : 0;
+            }
+            tc::mbar_wait(&tmem_full[buf], aph);
+            tc::tc_fence_after();
+            const int co0 = n_tile * BLOCK_N;
+#pragma unroll 1
+            for (int c = 0; c < BLOCK_N; c += 16) {
+                float v[16];
+                tc::tmem_ld16(tmem_base + buf * BLOCK_N + c + ((uint32_t)(q * 32) << 16), v);
+                if (bias != nullptr) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] += (co0 + c + i < g.Cout) ? __ldg(bias + co0 + c + i) : 0.f;
+                }
+                uint4 o[2];
+                __nv_bfloat162* ob = reinterpret_cast<__nv_bfloat162*>(o);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) ob[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+                uint8_t* blk = staging + (c >> 6) * kATileBytes + row * 128;
+                const int ch0 = (c & 63) >> 3;
+                *reinterpret_cast<uint4*>(blk + (((ch0) ^ (row & 7)) << 4)) = o[0];
+                *reinterpret_cast<uint4*>(blk + (((ch0 + 1) ^ (row & 7)) << 4)) = o[1];
+            }
+            tc::tc_fence_before();
+            tc::mbar_arrive(&tmem_empty[buf]);
+            tc::fence_proxy_async_smem();
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (et == 0) {
+#pragma unroll
+                for (int j = 0; j < BLOCK_N / 64; ++j)
+                    if (co0 + j * 64 < g.Cout) tc::tma_store_5d(&tm_y, staging + j * kATileBytes, co0 + j * 64, w0, h0, d0, n0);
+                tc::tma_store_commit();
+            }
+            if (stats_partials != nullptr) {
+                // per-channel (sum, sum^2) over the valid rows of this tile, from the bf16 values just staged
+                for (int ch = et; ch < BLOCK_N; ch += 128) {
+                    if (co0 + ch >= g.Cout) continue;
+                    const uint8_t* blk = staging + (ch >> 6) * kATileBytes;
+                    const int chunk = (ch & 63) >> 3, within = (ch & 7) * 2;
+                    float s1 = 0.f, s2 = 0.f;
+                    for (int r = 0; r < g.box_rows; ++r) {
+                        if (!row_valid[r]) continue;
+                        const float x = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(blk + r * 128 + ((chunk ^ (r & 7)) << 4) + within));
+                        s1 += x;
+                        s2 = fmaf(x, x, s2);
+                    }
+                    const int m_tile = tile / g.n_tiles;
+                    stats_partials[((size_t)m_tile * 2 + 0) * g.Cout + co0 + ch] = s1;
+                    stats_partials[((size_t)m_tile * 2 + 1) * g.Cout + co0 + ch] = s2;
+                }
+            }
+        }
+        if (et == 0) tc::tma_store_wait_read();
+    }
+    tc::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc::tc_fence_after();
+        tc::tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+    }
+}
+
+// ------------------------------------------------------------------------------- wgrad
+// Work item = (tap, co tile of 128, ci block of 64, K split).  D[co][ci] (128x64 fp32 in TMEM)
+// accumulates dY^T * X_shift over the positions of the split; both operands are MN-major
+// (positions are the GEMM K dimension, channels are contiguous in memory).
+struct WgradGeom {
+    int N, Do, Ho, Wo, Cout, Cin;
+    int k, stride, pad;
+    int bw, bh, bd, bn, tw, th, td, tn;
+    int box_rows, m_tiles, splits, co_tiles, ci_blocks;
+};
+constexpr int kWgStages = 4;
+constexpr int kWgStageBytes = 3 * kATileBytes;    // A: 2 x [128 pos][64 co], B: [128 pos][64 ci]
+constexpr int kWgSmemBytes = kWgStages * kWgStageBytes + 1024 + 256;
+
+__global__ void __launch_bounds__(kConvThreads, 1) conv3d_wgrad_tc_kernel(
+    const __grid_constant__ CUtensorMap tm_dy, const __grid_constant__ CUtensorMap tm_x, const WgradGeom g, float* __restrict__ partials) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kWgStages * kWgStageBytes);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + kWgStages;
+    uint64_t* tmem_full = empty + kWgStages;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full + 1);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int taps = g.k * g.k * g.k;
+
+    // work item decode: ci block fastest, then co tile, then tap, then split
+    int wi = blockIdx.x;
+    const int cib = wi % g.ci_blocks; wi /= g.ci_blocks;
+    const int cot = wi % g.co_tiles; wi /= g.co_tiles;
+    const int tap = wi % taps;
+    const int split = wi / taps;
+    const int per = (g.m_tiles + g.splits - 1) / g.splits;
+    const int mt_begin = split * per;
+    const int mt_end = min(g.m_tiles, mt_begin + per);
+    const int kd = tap / (g.k * g.k), kh = (tap / g.k) % g.k, kw = tap % g.k;
+
+    // rows >= box_rows of every stage are never written by TMA: keep them zero (they are GEMM-K here)
+    for (int i = threadIdx.x; i < kWgStages * kWgStageBytes / 16; i += kConvThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+    tc::fence_proxy_async_smem();
+    if (warp == 0 && lane == 0) {
+        tc::tma_prefetch_desc(&tm_dy);
+        tc::tma_prefetch_desc(&tm_x);
+        for (int i = 0; i < kWgStages; ++i) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 1); }
+        tc::mbar_init(tmem_full, 1);
+        tc::mbar_fence_init();
+    }
+    if (warp == 1) tc::tmem_alloc<64>(tmem_ptr);
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int mt = mt_begin; mt < mt_end; ++mt, ++it) {
+                int m = mt;
+                const int w0 = (m % g.tw) * g.bw; m /= g.tw;
+                const int h0 = (m % g.th) * g.bh; m /= g.th;
+                const int d0 = (m % g.td) * g.bd; m /= g.td;
+                const int n0 = m * g.bn;
+                const int s = it % kWgStages;
+                const uint32_t ph = (it / kWgStages) & 1;
+                tc::mbar_wait(&empty[s], ph ^ 1);
+                uint8_t* a_dst = smem + s * kWgStageBytes;
+                tc::mbar_expect_tx(&full[s], (uint32_t)(3 * g.box_rows * 128));
+                tc::tma_load_5d(&tm_dy, &full[s], a_dst, cot * 128, w0, h0, d0, n0);
+                tc::tma_load_5d(&tm_dy, &full[s], a_dst + kATileBytes, cot * 128 + 64, w0, h0, d0, n0);
+                tc::tma_load_5d(&tm_x, &full[s], a_dst + 2 * kATileBytes, cib * 64, w0 * g.stride - g.pad + kw, h0 * g.stride - g.pad + kh,
+                                d0 * g.stride - g.pad + kd, n0);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = tc::make_idesc_bf16(128, 64, 1, 1);
+            uint32_t it = 0;
+            for (int mt = mt_begin; mt < mt_end; ++mt, ++it) {
+                const int s = it % kWgStages;
+                const uint32_t ph = (it / kWgStages) & 1;
+                tc::mbar_wait(&full[s], ph);
+                tc::tc_fence_after();
+                const uint32_t a_addr = tc::smem_u32(smem + s * kWgStageBytes);
+                const uint32_t b_addr = a_addr + 2 * kATileBytes;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {   // 16 positions per MMA: two 8-row swizzle groups (SBO = 1024 B)
+                    const uint64_t da = tc::make_smem_desc_sw128(a_addr + k * 2048, kATileBytes, 1024);
+                    const uint64_t db = tc::make_smem_desc_sw128(b_addr + k * 2048, kATileBytes, 1024);
+                    tc::umma_bf16(tmem_base, da, db, idesc, (it | (uint32_t)k) != 0);
+                }
+                tc::umma_commit(&empty[s]);
+            }
+            tc::umma_commit(tmem_full);
+        }
+    } else {
+        const int q = warp & 3;
+        const int co = cot * 128 + q * 32 + lane;
+        if (mt_end > mt_begin) {
+            tc::mbar_wait(tmem_full, 0);
+            tc::tc_fence_after();
+        }
+        float* dst = partials + (((size_t)split * taps + tap) * g.Cout + co) * g.Cin + cib * 64;
+#pragma unroll 1
+        for (int c = 0; c < 64; c += 16) {
+            float v[16];
+            if (mt_end > mt_begin) tc::tmem_ld16(tmem_base + c + ((uint32_t)(q * 32) << 16), v);
+            else {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) v[i] = 0.f;
+            }
+            if (co < g.Cout) {
+#pragma unroll
+                for (int i = 0; i < 16; i += 4) st4(dst + c + i, make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]));
+            }
+        }
+    }
+    tc::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc::tc_fence_after();
+        tc::tmem_dealloc<64>(tmem_base);
+    }
+}
+
+// dW (PyTorch layout [co][ci][taps], fp32, in the gradient slab) = sum_splits partials[split][tap][co][ci];
+// optional saliency epilogue: scores[co][ci][tap] += scale * |dW * W|   (ref K11: snip.py:60-71)
+__global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ partials, int splits, int taps, int Cout, int Cin,
+                                                           float* __restrict__ grad) {
+    const int64_t total = (int64_t)Cout * Cin * taps;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int t = (int)(i % taps);
+        const int64_t r = i / taps;
+        const int ci = (int)(r % Cin);
+        const int co = (int)(r / Cin);
+        float acc = 0.f;
+        for (int s = 0; s < splits; ++s) acc += partials[(((size_t)s * taps + t) * Cout + co) * Cin + ci];
+        grad[i] = acc;
+    }
+}
+
+// fp32 master weights [co][ci][taps] -> bf16 GEMM operands:
+//   wf[co][tap][ci]            (fprop B operand, K-major)
+//   wd[ci][taps-1-tap][co]     (dgrad B operand: transposed and tap-flipped)
+__global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restrict__ w, int Cout, int Cin, int taps,
+                                                           __nv_bfloat16* __restrict__ wf, __nv_bfloat16* __restrict__ wd) {
+    const int64_t total = (int64_t)Cout * Cin * taps;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        // iterate in wf order so the writes of the larger-stride operand stay coalesced
+        const int ci = (int)(i % Cin);
+        const int64_t r = i / Cin;
+        const int t = (int)(r % taps);
+        const int co = (int)(r / taps);
+        const __nv_bfloat16 v = __float2bfloat16(w[((size_t)co * Cin + ci) * taps + t]);
+        wf[i] = v;
+        if (wd != nullptr) wd[((size_t)ci * taps + (taps - 1 - t)) * Cout + co] = v;
+    }
+}
+
+}  // namespace nidt
+using namespace nidt;
+
+static int pick_tiles(int n, int b) { return (n + b - 1) / b; }
+
+// x: bf16 [N][Di][Hi][Wi][Cin]; w: bf16 [Cout][k^3][Cin]; y: bf16 [N][Do][Ho][Wo][Cout]
+// stats_partials: nullptr or fp32 [m_tiles][2][Cout]; box (bw,bh,bd,bn) with bw*bh*bd*bn <= 128.
+NIDT_API int nidt_conv3d_fprop_tc(const void* x, const void* w, const float* bias, void* y, float* stats_partials, int N, int Di, int Hi, int Wi,
+                                  int Cin, int Do, int Ho, int Wo, int Cout, int k, int stride, int pad, int bw, int bh, int bd, int bn,
+                                  int block_n, void* stream) {
+    NIDT_REQUIRE(Cin % 64 == 0 && Cout % 8 == 0, "conv3d_fprop_tc: Cin=%d must be a multiple of 64, Cout=%d of 8", Cin, Cout);
+    NIDT_REQUIRE(bw * bh * bd * bn <= 128 && bw >= 1 && bh >= 1 && bd >= 1 && bn >= 1, "conv3d_fprop_tc: box %dx%dx%dx%d exceeds 128 rows", bw, bh, bd, bn);
+    NIDT_REQUIRE(block_n == 64 || block_n == 128, "conv3d_fprop_tc: block_n must be 64 or 128");
+    ConvGeom g;
+    g.N = N; g.Do = Do; g.Ho = Ho; g.Wo = Wo; g.Cout = Cout; g.k = k; g.stride = stride; g.pad = pad; g.cin_blocks = Cin / 64;
+    g.bw = bw; g.bh = bh; g.bd = bd; g.bn = bn;
+    g.tw = pick_tiles(Wo, bw); g.th = pick_tiles(Ho, bh); g.td = pick_tiles(Do, bd); g.tn = pick_tiles(N, bn);
+    g.n_tiles = pick_tiles(Cout, block_n);
+    g.box_rows = bw * bh * bd * bn;
+    const int m_tiles = g.tw * g.th * g.td * g.tn;
+    const int total = m_tiles * g.n_tiles;
+    CUtensorMap tx, tw_, ty;
+    if (make_tmap_act5d(&tx, x, N, Di, Hi, Wi, Cin, bw, bh, bd, bn, stride)) return 1;
+    if (make_tmap_mat2d(&tw_, w, Cout, (int64_t)k * k * k * Cin, block_n)) return 1;
+    if (make_tmap_act5d(&ty, y, N, Do, Ho, Wo, Cout, bw, bh, bd, bn, 1)) return 1;
+    int dev = 0, sms = 0;
+    NIDT_CUDA_CHECK(cudaGetDevice(&dev));
+    NIDT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const int grid = total < sms ? total : sms;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (block_n == 128) {
+        NIDT_CUDA_CHECK(cudaFuncSetAttribute(conv3d_fprop_tc_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, FpropCfg<128>::kSmemBytes));
+        conv3d_fprop_tc_kernel<128><<<grid, kConvThreads, FpropCfg<128>::kSmemBytes, s>>>(tx, tw_, ty, g, bias, stats_partials, total);
+    } else {
+        NIDT_CUDA_CHECK(cudaFuncSetAttribute(conv3d_fprop_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, FpropCfg<64>::kSmemBytes));
+        conv3d_fprop_tc_kernel<64><<<grid, kConvThreads, FpropCfg<64>::kSmemBytes, s>>>(tx, tw_, ty, g, bias, stats_partials, total);
+    }
+    NIDT_LAUNCH_CHECK();
+    return 0;
+}
+
+NIDT_API int nidt_conv3d_m_tiles(int N, int Do, int Ho, int Wo, int bw, int bh, int bd, int bn) {
+    return pick_tiles(Wo, bw) * pick_tiles(Ho, bh) * pick_tiles(Do, bd) * pick_tiles(N, bn);
+}
+
+NIDT_API int64_t nidt_conv3d_wgrad_scratch_floats(int Cout, int Cin, int k, int splits) { return (int64_t)splits * k * k * k * Cout * Cin; }
+
+// dy: bf16 [N][Do][Ho][Wo][Cout]; x: bf16 [N][Di][Hi][Wi][Cin]; grad: fp32 [Cout][Cin][k^3] (PyTorch layout);
+// scratch: >= nidt_conv3d_wgrad_scratch_floats() floats of split-K partials.
+NIDT_API int nidt_conv3d_wgrad_tc(const void* dy, const void* x, float* grad, float* scratch, int N, int Di, int Hi, int Wi, int Cin, int Do, int Ho,
+                                  int Wo, int Cout, int k, int stride, int pad, int bw, int bh, int bd, int bn, int splits, void* stream) {
+    NIDT_REQUIRE(Cin % 64 == 0 && Cout % 8 == 0, "conv3d_wgrad_tc: Cin=%d must be a multiple of 64, Cout=%d of 8", Cin, Cout);
+    NIDT_REQUIRE(bw * bh * bd * bn <= 128, "conv3d_wgrad_tc: box exceeds 128 rows");
+    NIDT_REQUIRE(splits >= 1 && scratch != nullptr, "conv3d_wgrad_tc: need splits >= 1 and a scratch buffer");
+    WgradGeom g;
+    g.N = N; g.Do = Do; g.Ho = Ho; g.Wo = Wo; g.Cout = Cout; g.Cin = Cin; g.k = k; g.stride = stride; g.pad = pad;
+    g.bw = bw; g.bh = bh; g.bd = bd; g.bn = bn;
+    g.tw = pick_tiles(Wo, bw); g.th = pick_tiles(Ho, bh); g.td = pick_tiles(Do, bd); g.tn = pick_tiles(N, bn);
+    g.box_rows = bw * bh * bd * bn;
+    g.m_tiles = g.tw * g.th * g.td * g.tn;
+    g.splits = splits;
+    g.co_tiles = pick_tiles(Cout, 128);
+    g.ci_blocks = Cin / 64;
+    const int taps = k * k * k;
+    CUtensorMap tdy, tx;
+    if (make_tmap_act5d(&tdy, dy, N, Do, Ho, Wo, Cout, bw, bh, bd, bn, 1)) return 1;
+    if (make_tmap_act5d(&tx, x, N, Di, Hi, Wi, Cin, bw, bh, bd, bn, stride)) return 1;
+    cudaStream_t s = (cudaStream_t)stream;
+    NIDT_CUDA_CHECK(cudaFuncSetAttribute(conv3d_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmemBytes));
+    const int grid = splits * taps * g.co_tiles * g.ci_blocks;
+    conv3d_wgrad_tc_kernel<<<grid, kConvThreads, kWgSmemBytes, s>>>(tdy, tx, g, scratch);
+    NIDT_LAUNCH_CHECK();
+    const int64_t total = (int64_t)Cout * Cin * taps;
+    int64_t blocks = (total + 255) / 256;
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    wgrad_reduce_kernel<<<(int)blocks, 256, 0, s>>>(scratch, splits, taps, Cout, Cin, grad);
+    NIDT_LAUNCH_CHECK();
+    return 0;
+}
+
+NIDT_API int nidt_pack_conv_weights(const float* w, int Cout, int Cin, int taps, void* wf, void* wd, void* stream) {
+    const int64_t total = (int64_t)Cout * Cin * taps;
+    int64_t blocks = (total + 255) / 256;
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    pack_weights_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(w, Cout, Cin, taps, (__nv_bfloat16*)wf, (__nv_bfloat16*)wd);
+    NIDT_LAUNCH_CHECK();
+    return 0;
+}

@@ -1,0 +1,322 @@
+"""sm_100a compute engine for plan-based 3-D CNNs (AlexNet3D family).
+
+Walks ``model.plan`` / ``model.head_spec`` and launches the hand-written kernels directly on the
+parameter slab -- no autograd, no cuDNN/cuBLAS, no intermediate fp32 tensors:
+
+  conv_in (Cin=1, tcgen05, im2col built in smem from the 8-bit volume) | conv3d_fprop_tc (tcgen05+TMA)
+  -> bn_finalize -> bn_relu_pool_fwd  ...  head_fwd_bwd  ...  bn_relu_pool_bwd -> conv3d_wgrad_tc
+  -> conv3d_fprop_tc as dgrad ... -> masked_sgd_step
+
+Activations are channels-last (NDHWC) bf16; master weights, BN statistics, gradients and the
+optimizer state are fp32 in the slab.  Interface-compatible with :class:`fl.engine.TorchEngine`.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+from ..models.volumetric import ConvBlockSpec, HeadSpec, trace_shapes
+from ..runtime.slab import ParamSlab, SlabLayout
+from . import flat as flat_ops
+from . import native
+
+_declared = False
+
+
+def _declare(lib) -> None:
+    global _declared
+    if _declared:
+        return
+    i32, i64, f32, f64, vp, u64 = C.c_int, C.c_int64, C.c_float, C.c_double, C.c_void_p, C.c_uint64
+    sigs = {
+        "nidt_bn_bwd_grid": [],
+        "nidt_bn_finalize": [vp, i32, i32, f64, vp, vp, vp, vp, vp, f32, f32, vp, vp, vp, vp, vp],
+        "nidt_bn_eval_prepare": [i32, vp, vp, vp, vp, f32, vp, vp, vp],
+        "nidt_bn_relu_pool_fwd": [vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp, i32, vp],
+        "nidt_bn_relu_pool_bwd": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, vp],
+        "nidt_head_fwd_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, u64, i32, i32, vp],
+        "nidt_conv3d_fprop_tc": [vp, vp, vp, vp, vp] + [i32] * 17 + [vp],
+        "nidt_conv3d_m_tiles": [i32] * 8,
+        "nidt_conv3d_wgrad_tc": [vp, vp, vp, vp] + [i32] * 17 + [vp],
+        "nidt_pack_conv_weights": [vp, i32, i32, i32, vp, vp, vp],
+        "nidt_conv_in_grid": [],
+        "nidt_conv_in_fprop": [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, f32, vp],
+        "nidt_conv_in_wgrad": [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, f32, vp],
+    }
+    for name, argtypes in sigs.items():
+        fn = getattr(lib, name)
+        fn.argtypes = argtypes
+        fn.restype = C.c_int
+    lib.nidt_conv3d_wgrad_scratch_floats.argtypes = [i32, i32, i32, i32]
+    lib.nidt_conv3d_wgrad_scratch_floats.restype = i64
+    _declared = True
+
+
+def choose_box(W: int, H: int, D: int, N: int, max_rows: int = 128) -> Tuple[int, int, int, int]:
+    """Box of output positions (bw,bh,bd,bn), bw*bh*bd*bn <= 128, maximising tensor-core row use:
+    valid positions / (tiles * 128).  Ties prefer wider (more contiguous) boxes."""
+    best, best_key = (1, 1, 1, 1), (-1.0, 0)
+    total = W * H * D * N
+    for bw in range(1, min(W, max_rows) + 1):
+        tw = -(-W // bw)
+        for bh in range(1, min(H, max_rows // bw) + 1):
+            th = -(-H // bh)
+            for bd in range(1, min(D, max_rows // (bw * bh)) + 1):
+                td = -(-D // bd)
+                bn = min(N, max_rows // (bw * bh * bd))
+                if bn < 1:
+                    continue
+                tn = -(-N // bn)
+                util = total / (tw * th * td * tn * 128.0)
+                key = (round(util, 4), bw * 1000 + bh)
+                if key > best_key:
+                    best, best_key = (bw, bh, bd, bn), key
+    return best
+
+
+class _Block:
+    pass
+
+
+class B200Engine:
+    native = True
+
+    def __init__(self, model: nn.Module, device, max_batch: int = 16, input_scale: float = 1.0 / 255.0, seed: int = 1234,
+                 wgrad_ctas: int = 296):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("B200Engine needs a CUDA device")
+        if not hasattr(model, "plan") or not hasattr(model, "head_spec"):
+            raise ImportError("model has no native plan")
+        self.lib = native.load()
+        _declare(self.lib)
+        self.model = model
+        self.plan: List[ConvBlockSpec] = list(model.plan)
+        self.head: HeadSpec = model.head_spec
+        self.in_shape = tuple(model.in_shape)
+        self.layout = SlabLayout.from_module(model)
+        self.input_scale = float(input_scale)
+        self.max_batch = int(max_batch)
+        self.seed = seed
+        self.step = 0
+        p0 = self.plan[0]
+        if not (p0.cin == 1 and p0.cout == 64 and p0.k in (3, 5)):
+            raise ImportError("first block must be a 1->64 channel conv with k in (3,5)")
+        for b in self.plan[1:]:
+            if b.cin % 64 or b.stride != 1 or b.cout % 8:
+                raise ImportError(f"block {b.conv}: native path needs Cin%64==0, stride 1")
+        if self.head.out_features != 1:
+            raise ImportError("native head supports one logit")
+        self.grad = ParamSlab(self.layout, device=self.device, params_only=True)
+        self.slab: Optional[ParamSlab] = None
+        self.loss_acc = torch.zeros((), dtype=torch.float32, device=self.device)
+        self.loss_steps = 0
+        self._packed_dirty = True
+        self._alloc(wgrad_ctas)
+
+    # ----------------------------------------------------------------------------- buffers
+    def _alloc(self, wgrad_ctas: int) -> None:
+        dev, B = self.device, self.max_batch
+        bf = torch.bfloat16
+        shapes = trace_shapes(self.plan, self.in_shape)
+        self.blocks: List[_Block] = []
+        lib = self.lib
+        in_dhw = self.in_shape
+        bn_grid = lib.nidt_bn_bwd_grid()
+        for i, (spec, (cdhw, adhw)) in enumerate(zip(self.plan, shapes)):
+            b = _Block()
+            b.spec, b.in_dhw, b.c_dhw, b.a_dhw = spec, in_dhw, cdhw, adhw
+            D, H, W = cdhw
+            b.y = torch.empty((B, D, H, W, spec.cout), dtype=bf, device=dev)
+            b.dy = torch.empty_like(b.y)
+            b.a = torch.empty((B,) + adhw + (spec.cout,), dtype=bf, device=dev) if spec.pool_k else torch.empty_like(b.y)
+            b.da = torch.empty_like(b.a)
+            C_ = spec.cout
+            b.scale, b.shift, b.mean, b.invstd = (torch.zeros(C_, dtype=torch.float32, device=dev) for _ in range(4))
+            b.c12 = torch.zeros(2 * C_, dtype=torch.float32, device=dev)
+            b.bwd_partials = torch.zeros(bn_grid * 2 * C_, dtype=torch.float32, device=dev)
+            taps = spec.k ** 3
+            if i == 0:
+                b.stats = torch.zeros(lib.nidt_conv_in_grid() * 2 * C_, dtype=torch.float32, device=dev)
+                b.stats_tiles = lib.nidt_conv_in_grid()
+                b.wg_scratch = torch.zeros(lib.nidt_conv_in_grid() * 128 * 64, dtype=torch.float32, device=dev)
+            else:
+                b.box = choose_box(W, H, D, B)
+                b.m_tiles = lib.nidt_conv3d_m_tiles(B, D, H, W, *b.box)
+                b.block_n = 128 if (spec.cout % 128 == 0 and b.m_tiles * (spec.cout // 128) >= 148) else 64
+                b.stats = torch.zeros(b.m_tiles * 2 * C_, dtype=torch.float32, device=dev)
+                b.stats_tiles = b.m_tiles
+                b.wf = torch.empty((spec.cout, taps, spec.cin), dtype=bf, device=dev)
+                b.wd = torch.empty((spec.cin, taps, spec.cout), dtype=bf, device=dev)
+                iD, iH, iW = in_dhw
+                b.dbox = choose_box(iW, iH, iD, B)
+                b.dgrad_block_n = 128 if (spec.cin % 128 == 0 and lib.nidt_conv3d_m_tiles(B, iD, iH, iW, *b.dbox) * (spec.cin // 128) >= 148) else 64
+                work = taps * (-(-spec.cout // 128)) * (spec.cin // 64)
+                b.splits = max(1, min(b.m_tiles, wgrad_ctas // work))
+                b.wg_scratch = torch.zeros(lib.nidt_conv3d_wgrad_scratch_floats(spec.cout, spec.cin, spec.k, b.splits),
+                                           dtype=torch.float32, device=dev)
+            self.blocks.append(b)
+            in_dhw = adhw
+        d, h, w = shapes[-1][1]
+        self.head_S = d * h * w
+        self.head_C = self.plan[-1].cout
+        assert self.head_S * self.head_C == self.head.in_features
+        self.eval_logits = torch.zeros(B, dtype=torch.float32, device=dev)
+
+    # ------------------------------------------------------------------------- slab plumbing
+    def new_slab(self) -> ParamSlab:
+        return ParamSlab.from_module(self.model, device=self.device, bind=False)
+
+    def attach(self, slab: ParamSlab) -> None:
+        if slab is not self.slab:
+            self._packed_dirty = True
+        self.slab = slab
+
+    def detach_sync(self) -> None:
+        return None
+
+    def _p(self, slab: ParamSlab, name: str) -> int:
+        return slab.flat.data_ptr() + 4 * self.layout[name].offset
+
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _chk(self, rc: int, what: str) -> None:
+        native.check(rc, what)
+
+    # ------------------------------------------------------------------------------ kernels
+    def _pack_weights(self) -> None:
+        lib, st = self.lib, self._stream()
+        for b in self.blocks[1:]:
+            s = b.spec
+            self._chk(lib.nidt_pack_conv_weights(self._p(self.slab, s.conv + ".weight"), s.cout, s.cin, s.k ** 3,
+                                                 b.wf.data_ptr(), b.wd.data_ptr(), st), "pack_conv_weights")
+            native.count_launches(1)
+        self._packed_dirty = False
+
+    def _forward(self, x: torch.Tensor, train: bool) -> int:
+        """Runs the conv stack; returns the batch size.  ``x``: uint8 [B, D, H, W] on the device."""
+        assert x.dtype == torch.uint8 and x.is_cuda and x.dim() == 4, "B200Engine consumes 8-bit volumes [B,D,H,W]"
+        x = x.contiguous()
+        B = x.shape[0]
+        assert B <= self.max_batch and tuple(x.shape[1:]) == self.in_shape
+        lib, st, slab = self.lib, self._stream(), self.slab
+        if self._packed_dirty:
+            self._pack_weights()
+        self._x = x
+        prev = None
+        for i, b in enumerate(self.blocks):
+            s = b.spec
+            D, H, W = b.c_dhw
+            stats = b.stats.data_ptr() if train else None
+            bias = self._p(slab, s.conv + ".bias") if s.bias else None
+            if i == 0:
+                iD, iH, iW = b.in_dhw
+                self._chk(lib.nidt_conv_in_fprop(x.data_ptr(), self._p(slab, s.conv + ".weight"), bias, b.y.data_ptr(), stats,
+                                                 B, iD, iH, iW, s.k, s.stride, s.pad, self.input_scale, st), "conv_in_fprop")
+            else:
+                iD, iH, iW = b.in_dhw
+                bw, bh, bd, bn = b.box if B == self.max_batch else choose_box(W, H, D, B)
+                b.cur_box = (bw, bh, bd, bn)
+                self._chk(lib.nidt_conv3d_fprop_tc(prev.data_ptr(), b.wf.data_ptr(), bias, b.y.data_ptr(), stats, B, iD, iH, iW, s.cin,
+                                                   D, H, W, s.cout, s.k, s.stride, s.pad, bw, bh, bd, bn, b.block_n, st), "conv3d_fprop_tc")
+            native.count_launches(1)
+            g, be = self._p(slab, s.bn + ".weight"), self._p(slab, s.bn + ".bias")
+            rm, rv = self._p(slab, s.bn + ".running_mean"), self._p(slab, s.bn + ".running_var")
+            if train:
+                tiles = b.stats_tiles if (i == 0 or B == self.max_batch) else lib.nidt_conv3d_m_tiles(B, D, H, W, *b.cur_box)
+                self._chk(lib.nidt_bn_finalize(b.stats.data_ptr(), tiles, s.cout, float(B * D * H * W), g, be, rm, rv,
+                                               self._p(slab, s.bn + ".num_batches_tracked"), 0.1, 1e-5, b.scale.data_ptr(), b.shift.data_ptr(),
+                                               b.mean.data_ptr(), b.invstd.data_ptr(), st), "bn_finalize")
+            else:
+                self._chk(lib.nidt_bn_eval_prepare(s.cout, g, be, rm, rv, 1e-5, b.scale.data_ptr(), b.shift.data_ptr(), st), "bn_eval_prepare")
+            self._chk(lib.nidt_bn_relu_pool_fwd(b.y.data_ptr(), b.a.data_ptr(), B, D, H, W, s.cout, s.pool_k, s.pool_s,
+                                                b.scale.data_ptr(), b.shift.data_ptr(), int(s.relu), st), "bn_relu_pool_fwd")
+            native.count_launches(2)
+            prev = b.a
+        return B
+
+    def _head(self, B: int, y: torch.Tensor, train: bool, counters=None, double_sigmoid=True, want_grads=True) -> None:
+        lib, st, slab, h = self.lib, self._stream(), self.slab, self.head
+        last = self.blocks[-1]
+        gp = (lambda n: self._p(self.grad, n)) if (train and want_grads) else (lambda n: None)
+        self._chk(lib.nidt_head_fwd_bwd(
+            last.a.data_ptr(), y.data_ptr(), self._p(slab, h.fc1 + ".weight"), self._p(slab, h.fc1 + ".bias"),
+            self._p(slab, h.fc2 + ".weight"), self._p(slab, h.fc2 + ".bias"),
+            gp(h.fc1 + ".weight"), gp(h.fc1 + ".bias"), gp(h.fc2 + ".weight"), gp(h.fc2 + ".bias"),
+            last.da.data_ptr() if train else None, self.loss_acc.data_ptr() if train else None,
+            counters.buf.data_ptr() if counters is not None else None, self.eval_logits.data_ptr(),
+            B, self.head_S, self.head_C, h.hidden, float(h.p_drop), self.seed + 7919 * self.step, int(train), int(double_sigmoid), st),
+            "head_fwd_bwd")
+        native.count_launches(1)
+
+    def _backward(self, B: int) -> None:
+        lib, st, slab = self.lib, self._stream(), self.slab
+        for i in range(len(self.blocks) - 1, -1, -1):
+            b = self.blocks[i]
+            s = b.spec
+            D, H, W = b.c_dhw
+            self._chk(lib.nidt_bn_relu_pool_bwd(b.y.data_ptr(), b.da.data_ptr(), b.dy.data_ptr(), B, D, H, W, s.cout, s.pool_k, s.pool_s,
+                                                b.scale.data_ptr(), b.shift.data_ptr(), b.mean.data_ptr(), b.invstd.data_ptr(),
+                                                b.bwd_partials.data_ptr(), b.c12.data_ptr(), self._p(self.grad, s.bn + ".weight"),
+                                                self._p(self.grad, s.bn + ".bias"), int(s.relu), st), "bn_relu_pool_bwd")
+            native.count_launches(3)
+            iD, iH, iW = b.in_dhw
+            if i == 0:
+                self._chk(lib.nidt_conv_in_wgrad(self._x.data_ptr(), b.dy.data_ptr(), self._p(self.grad, s.conv + ".weight"),
+                                                 b.wg_scratch.data_ptr(), B, iD, iH, iW, s.k, s.stride, s.pad, self.input_scale, st), "conv_in_wgrad")
+                native.count_launches(2)
+            else:
+                prev = self.blocks[i - 1]
+                bw, bh, bd, bn = b.cur_box
+                splits = b.splits if B == self.max_batch else max(1, min(b.splits, lib.nidt_conv3d_m_tiles(B, D, H, W, bw, bh, bd, bn)))
+                self._chk(lib.nidt_conv3d_wgrad_tc(b.dy.data_ptr(), prev.a.data_ptr(), self._p(self.grad, s.conv + ".weight"),
+                                                   b.wg_scratch.data_ptr(), B, iD, iH, iW, s.cin, D, H, W, s.cout, s.k, s.stride, s.pad,
+                                                   bw, bh, bd, bn, splits, st), "conv3d_wgrad_tc")
+                # dgrad = fprop of dY with transposed, tap-flipped weights and pad' = k-1-pad
+                dbox = b.dbox if B == self.max_batch else choose_box(iW, iH, iD, B)
+                self._chk(lib.nidt_conv3d_fprop_tc(b.dy.data_ptr(), b.wd.data_ptr(), None, prev.da.data_ptr(), None, B, D, H, W, s.cout,
+                                                   iD, iH, iW, s.cin, s.k, 1, s.k - 1 - s.pad, *dbox, b.dgrad_block_n, st), "conv3d_dgrad_tc")
+                native.count_launches(3)
+            # conv bias gradient is identically zero in exact arithmetic (BatchNorm subtracts the batch mean
+            # right after the conv); the grad slab keeps it at 0, weight decay still applies in the update.
+
+    # ---------------------------------------------------------------------------- public API
+    def compute_grads(self, x, y, train_mode: bool = True) -> torch.Tensor:
+        """Forward + backward; gradients land in ``self.grad.flat``.  ``train_mode=False`` (DisPFL
+        gradient screening) uses running statistics and no dropout in the forward pass."""
+        if not train_mode:
+            raise NotImplementedError("eval-mode gradient screening runs on the TorchEngine")
+        y = y.to(self.device, torch.float32).contiguous()
+        B = self._forward(x, train=True)
+        self._head(B, y, train=True)
+        self._backward(B)
+        self.step += 1
+        return self.loss_acc
+
+    def train_step(self, x, y, hp, mask: Optional[torch.Tensor], mom: Optional[torch.Tensor], first_step: bool) -> None:
+        self.compute_grads(x, y, True)
+        self.loss_steps += 1
+        flat_ops.masked_sgd_step(self.slab.params_flat, self.grad.flat, mom, mask, hp.lr, hp.momentum, hp.wd, hp.clip_norm, first_step)
+        self._packed_dirty = True
+
+    def pop_mean_loss(self) -> float:
+        v = float(self.loss_acc.item()) / max(1, self.loss_steps)
+        self.loss_acc.zero_()
+        self.loss_steps = 0
+        return v
+
+    def eval_batch(self, x, y, counters, double_sigmoid: bool = True) -> None:
+        y = y.to(self.device, torch.float32).contiguous()
+        B = self._forward(x, train=False)
+        self._head(B, y, train=False, counters=counters, double_sigmoid=double_sigmoid)
+
+    def logits(self, x) -> torch.Tensor:
+        """Eval-mode logits of one batch (testing aid)."""
+        B = self._forward(x, train=False)
+        yz = torch.zeros(B, dtype=torch.float32, device=self.device)
+        self._head(B, yz, train=False)
+        return self.eval_logits[:B].clone()

@@ -1,0 +1,259 @@
+"""sm_100a volumetric kernels vs. plain PyTorch fp32 references of the same ops (``-m gpu``).
+Inputs are rounded to bf16 first, so the comparison isolates the kernel from the input quantisation;
+tolerances are bf16-output bands (rtol ~ 2^-8)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda"
+
+
+def _cl(x):      # NCDHW -> NDHWC
+    return x.permute(0, 2, 3, 4, 1).contiguous()
+
+
+def _cf(x):      # NDHWC -> NCDHW
+    return x.permute(0, 4, 1, 2, 3).contiguous()
+
+
+def _close(a, b, rtol=2e-2, atol=2e-2, what=""):
+    a, b = a.float(), b.float()
+    scale = b.abs().max().item() + 1e-12
+    err = (a - b).abs().max().item()
+    assert err <= atol * scale + rtol * 0, f"{what}: max err {err:.4g} vs scale {scale:.4g}"
+
+
+@pytest.mark.parametrize("C,pool", [(64, 3), (128, 3), (192, 0), (128, 0)])
+def test_bn_relu_pool_fwd_bwd(C, pool):
+    from neuroimagedisttraining_b200.ops import volumetric as V
+    torch.manual_seed(0)
+    N, D, H, W = 3, 8, 11, 7
+    y = (torch.randn(N, C, D, H, W, device=DEV) * 1.5 + 0.3).bfloat16()
+    gamma = torch.rand(C, device=DEV) + 0.5
+    beta = torch.randn(C, device=DEV) * 0.2
+    yf = y.float().requires_grad_(True)
+    g2, b2 = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    rm, rv = torch.zeros(C, device=DEV), torch.ones(C, device=DEV)
+    ref = F.relu(F.batch_norm(yf, rm.clone(), rv.clone(), g2, b2, training=True, momentum=0.1, eps=1e-5))
+    if pool:
+        ref = F.max_pool3d(ref, pool, pool)
+    # our stats: partials from the bf16 tensor (one "tile")
+    ycl = _cl(y)
+    flat = ycl.float().reshape(-1, C)
+    partials = torch.stack([flat.sum(0), (flat * flat).sum(0)]).unsqueeze(0).contiguous()
+    nb = torch.zeros(1, device=DEV)
+    scale, shift, mean, invstd = V.bn_finalize(partials, flat.shape[0], gamma, beta, rm, rv, nb)
+    a = V.bn_relu_pool_fwd(ycl, scale, shift, pool, pool, True)
+    _close(_cf(a), ref, what="fwd")
+    ref_rm, ref_rv = torch.zeros(C, device=DEV), torch.ones(C, device=DEV)
+    F.batch_norm(y.float(), ref_rm, ref_rv, gamma, beta, training=True, momentum=0.1, eps=1e-5)
+    torch.testing.assert_close(rm, ref_rm, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(rv, ref_rv, rtol=1e-4, atol=1e-5)
+    assert nb.item() == 1.0
+    # backward
+    da = torch.randn_like(ref).bfloat16()
+    ref.backward(da.float())
+    dy, dg, db = V.bn_relu_pool_bwd(ycl, _cl(da), scale, shift, mean, invstd, pool, pool, True)
+    _close(_cf(dy), yf.grad, what="dy")
+    _close(dg, g2.grad, atol=1e-2, what="dgamma")
+    _close(db, b2.grad, atol=1e-2, what="dbeta")
+
+
+def test_head_fwd_bwd_matches_torch():
+    from neuroimagedisttraining_b200.ops import native
+    from neuroimagedisttraining_b200.ops.engine_b200 import _declare
+    lib = native.load(); _declare(lib)
+    torch.manual_seed(1)
+    B, S, C, Hd = 16, 2, 128, 64
+    Fdim = S * C
+    feat = torch.randn(B, S, C, device=DEV).bfloat16()          # NDHWC with D*H*W = S
+    yl = (torch.rand(B, device=DEV) > 0.5).float()
+    W1 = (torch.randn(Hd, Fdim, device=DEV) * 0.05).requires_grad_(True)
+    b1 = torch.zeros(Hd, device=DEV).requires_grad_(True)
+    W2 = (torch.randn(1, Hd, device=DEV) * 0.1).requires_grad_(True)
+    b2 = torch.zeros(1, device=DEV).requires_grad_(True)
+    fl = feat.float().permute(0, 2, 1).reshape(B, Fdim).requires_grad_(True)   # reference order c*S+s
+    z = F.linear(F.relu(F.linear(fl, W1, b1)), W2, b2)
+    loss = F.binary_cross_entropy_with_logits(z.flatten(), yl)
+    loss.backward()
+    gW1, gb1, gW2, gb2 = torch.zeros_like(W1), torch.zeros_like(b1), torch.zeros_like(W2), torch.zeros_like(b2)
+    dfeat = torch.zeros_like(feat)
+    lacc = torch.zeros((), device=DEV)
+    logits = torch.zeros(B, device=DEV)
+    st = torch.cuda.current_stream().cuda_stream
+    native.check(lib.nidt_head_fwd_bwd(feat.data_ptr(), yl.data_ptr(), W1.data_ptr(), b1.data_ptr(), W2.data_ptr(), b2.data_ptr(),
+                                       gW1.data_ptr(), gb1.data_ptr(), gW2.data_ptr(), gb2.data_ptr(), dfeat.data_ptr(), lacc.data_ptr(),
+                                       None, logits.data_ptr(), B, S, C, Hd, 0.0, 5, 1, 1, st))
+    torch.testing.assert_close(logits, z.flatten().detach(), rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(lacc, loss.detach(), rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(gW1, W1.grad, rtol=1e-3, atol=1e-5)
+    torch.testing.assert_close(gb1, b1.grad, rtol=1e-3, atol=1e-6)
+    torch.testing.assert_close(gW2, W2.grad, rtol=1e-3, atol=1e-5)
+    torch.testing.assert_close(gb2, b2.grad, rtol=1e-3, atol=1e-6)
+    ref_df = fl.grad.reshape(B, C, S).permute(0, 2, 1)
+    _close(dfeat, ref_df, atol=1e-2, what="dfeat")
+    # eval counters incl. the reference's double-sigmoid loss
+    cnt = torch.zeros(3, dtype=torch.float64, device=DEV)
+    native.check(lib.nidt_head_fwd_bwd(feat.data_ptr(), yl.data_ptr(), W1.data_ptr(), b1.data_ptr(), W2.data_ptr(), b2.data_ptr(),
+                                       None, None, None, None, None, None, cnt.data_ptr(), logits.data_ptr(), B, S, C, Hd, 0.5, 5, 0, 1, st))
+    p = torch.sigmoid(z.flatten().detach())
+    assert cnt[2].item() == B
+    assert cnt[0].item() == ((p >= 0.5).float() == yl).float().sum().item()
+    assert abs(cnt[1].item() - F.binary_cross_entropy_with_logits(p, yl, reduction="sum").item()) < 1e-3
+
+
+def test_head_dropout_is_consistent_and_seeded():
+    from neuroimagedisttraining_b200.ops import native
+    from neuroimagedisttraining_b200.ops.engine_b200 import _declare
+    lib = native.load(); _declare(lib)
+    torch.manual_seed(2)
+    B, S, C, Hd = 8, 2, 128, 64
+    feat = torch.randn(B, S, C, device=DEV).bfloat16()
+    yl = (torch.rand(B, device=DEV) > 0.5).float()
+    W1, b1 = torch.randn(Hd, S * C, device=DEV) * 0.05, torch.zeros(Hd, device=DEV)
+    W2, b2 = torch.randn(1, Hd, device=DEV) * 0.1, torch.zeros(1, device=DEV)
+    st = torch.cuda.current_stream().cuda_stream
+    outs = []
+    for seed in (11, 11, 12):
+        logits = torch.zeros(B, device=DEV)
+        g = [torch.zeros_like(t) for t in (W1, b1, W2, b2)]
+        df = torch.zeros_like(feat)
+        native.check(lib.nidt_head_fwd_bwd(feat.data_ptr(), yl.data_ptr(), W1.data_ptr(), b1.data_ptr(), W2.data_ptr(), b2.data_ptr(),
+                                           g[0].data_ptr(), g[1].data_ptr(), g[2].data_ptr(), g[3].data_ptr(), df.data_ptr(), None, None,
+                                           logits.data_ptr(), B, S, C, Hd, 0.5, seed, 1, 1, st))
+        outs.append((logits.clone(), df.clone()))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    assert not torch.equal(outs[0][0], outs[2][0])
+    dropped = (outs[0][1].float() == 0).float().mean().item()
+    assert 0.35 < dropped < 0.65      # p = 0.5 on the feature gradient
+
+
+CONV_CASES = [
+    # N, Cin, D,H,W, Cout, k, pad, block_n
+    (2, 64, 19, 23, 19, 128, 3, 0, 128),     # conv2 of AlexNet3D
+    (2, 64, 19, 23, 19, 128, 3, 0, 64),
+    (4, 128, 5, 7, 5, 192, 3, 1, 64),        # conv3
+    (3, 192, 5, 7, 5, 192, 3, 1, 64),        # conv4
+    (16, 192, 5, 7, 5, 128, 3, 1, 128),      # conv5, full batch
+]
+
+
+@pytest.mark.parametrize("N,Cin,D,H,W,Cout,k,pad,block_n", CONV_CASES)
+def test_conv3d_fprop_dgrad_wgrad_tc(N, Cin, D, H, W, Cout, k, pad, block_n):
+    from neuroimagedisttraining_b200.ops import volumetric as V
+    torch.manual_seed(3)
+    x = torch.randn(N, Cin, D, H, W, device=DEV).bfloat16()
+    w = (torch.randn(Cout, Cin, k, k, k, device=DEV) / (Cin * k ** 3) ** 0.5).bfloat16().float()
+    bias = torch.randn(Cout, device=DEV) * 0.1
+    xf = x.float().requires_grad_(True)
+    wr = w.clone().requires_grad_(True)
+    ref = F.conv3d(xf, wr, bias, stride=1, padding=pad)
+    wf, wd = V.pack_conv_weights(w)
+    y, part = V.conv3d_fprop(_cl(x), wf, bias, k, 1, pad, block_n=block_n, stats=True)
+    torch.cuda.synchronize()
+    _close(_cf(y), ref, atol=1e-2, what="fprop")
+    yb = y.float().reshape(-1, Cout)
+    torch.testing.assert_close(part[:, 0].sum(0), yb.sum(0), rtol=1e-3, atol=1e-2)
+    torch.testing.assert_close(part[:, 1].sum(0), (yb * yb).sum(0), rtol=1e-3, atol=1e-2)
+    dy = torch.randn_like(ref).bfloat16()
+    ref.backward(dy.float())
+    dx = V.conv3d_dgrad(_cl(dy), wd, k, pad, (D, H, W), block_n=64)
+    _close(_cf(dx), xf.grad, atol=1e-2, what="dgrad")
+    for splits in (1, 3):
+        dw = V.conv3d_wgrad(_cl(dy), _cl(x), k, 1, pad, splits=splits)
+        _close(dw, wr.grad, atol=1e-2, what=f"wgrad splits={splits}")
+
+
+@pytest.mark.parametrize("N,D,H,W,k,stride,pad", [(2, 121, 145, 121, 5, 2, 0), (1, 29, 33, 31, 5, 2, 0), (2, 20, 22, 21, 3, 2, 3)])
+def test_conv_in_fprop_wgrad(N, D, H, W, k, stride, pad):
+    from neuroimagedisttraining_b200.ops import volumetric as V
+    torch.manual_seed(4)
+    x = torch.randint(0, 256, (N, D, H, W), dtype=torch.uint8, device=DEV)
+    scale = 1.0 / 255.0
+    w = (torch.randn(64, 1, k, k, k, device=DEV) / (k ** 3) ** 0.5)
+    bias = torch.randn(64, device=DEV) * 0.1
+    xb = (x.float() * scale).bfloat16().float().unsqueeze(1).requires_grad_(False)
+    wr = w.bfloat16().float().requires_grad_(True)
+    ref = F.conv3d(xb, wr, bias, stride=stride, padding=pad)
+    y, part = V.conv_in_fprop(x, w, bias, k, stride, pad, scale, stats=True)
+    torch.cuda.synchronize()
+    _close(_cf(y), ref, atol=1e-2, what="conv_in fprop")
+    yb = y.float().reshape(-1, 64)
+    torch.testing.assert_close(part[:, 0].sum(0), yb.sum(0), rtol=2e-3, atol=5e-2)
+    torch.testing.assert_close(part[:, 1].sum(0), (yb * yb).sum(0), rtol=2e-3, atol=5e-2)
+    dy = (torch.randn_like(ref) * 0.1).bfloat16()
+    ref.backward(dy.float())
+    dw = V.conv_in_wgrad(x, _cl(dy), k, stride, pad, scale)
+    _close(dw, wr.grad, atol=1e-2, what="conv_in wgrad")
+
+
+def _engine_pair(B, p_drop=0.0):
+    from neuroimagedisttraining_b200.fl.engine import TorchEngine
+    from neuroimagedisttraining_b200.models import AlexNet3D_Dropout
+    from neuroimagedisttraining_b200.ops.engine_b200 import B200Engine
+    torch.manual_seed(5)
+    model = AlexNet3D_Dropout(1, p_drop=p_drop)
+    import copy
+    tmodel = copy.deepcopy(model)
+    eng = B200Engine(model, DEV, max_batch=B)
+    ref = TorchEngine(tmodel, DEV, volumetric=True, input_scale=1 / 255.0)
+    return eng, ref
+
+
+def test_engine_gradients_match_torch_engine():
+    B = 4
+    eng, ref = _engine_pair(B)
+    slab = eng.new_slab()
+    slab2 = slab.clone()
+    eng.attach(slab)
+    ref.attach(slab2)
+    g = torch.Generator(device="cpu").manual_seed(0)
+    x = torch.randint(0, 256, (B, 121, 145, 121), dtype=torch.uint8, generator=g).to(DEV)
+    y = torch.tensor([0.0, 1.0, 1.0, 0.0], device=DEV)
+    loss = eng.compute_grads(x, y, True)
+    rloss = ref.compute_grads(x, y, True)
+    torch.cuda.synchronize()
+    assert abs(loss.item() - rloss.item()) < 2e-2, (loss.item(), rloss.item())
+    lay = eng.layout
+    for name in lay.param_names:
+        if name.endswith(".bias") and name.startswith("features") and lay[name].shape[0] in (64, 128, 192) and "features." in name:
+            idx = int(name.split(".")[1])
+            if isinstance(eng.model.features[idx], torch.nn.Conv3d):
+                continue   # conv bias gradient: exactly 0 here, ~1e-7 noise in autograd
+        a, b = eng.grad.view(name).float(), ref.grad.view(name).float()
+        denom = b.abs().max().item() + 1e-8
+        rel = (a - b).abs().max().item() / denom
+        cos = F.cosine_similarity(a.flatten(), b.flatten(), dim=0).item()
+        assert cos > 0.98 and rel < 0.15, f"{name}: rel {rel:.3g} cos {cos:.4f}"
+    # BN running statistics moved identically
+    P = lay.param_numel
+    torch.testing.assert_close(slab.flat[P:], slab2.flat[P:].clone().copy_(slab2.flat[P:]), rtol=2e-2, atol=2e-3)
+
+
+def test_engine_trains_and_evaluates():
+    from neuroimagedisttraining_b200.fl.engine import EvalCounters, StepHParams
+    B = 4
+    eng, ref = _engine_pair(B, p_drop=0.5)
+    slab = eng.new_slab()
+    eng.attach(slab)
+    g = torch.Generator(device="cpu").manual_seed(1)
+    x = torch.randint(0, 256, (B, 121, 145, 121), dtype=torch.uint8, generator=g).to(DEV)
+    y = torch.tensor([0.0, 1.0, 1.0, 0.0], device=DEV)
+    hp = StepHParams(lr=0.01, momentum=0.0, wd=5e-4, clip_norm=10.0)
+    losses = []
+    for step in range(6):
+        eng.train_step(x, y, hp, None, None, step == 0)
+        losses.append(eng.pop_mean_loss())
+    assert all(l == l for l in losses) and losses[-1] < losses[0] + 0.05, losses
+    c = EvalCounters(DEV)
+    eng.eval_batch(x, y, c)
+    r = c.result()
+    assert r["test_total"] == B and 0 <= r["test_correct"] <= B
+    # eval logits agree with the PyTorch module on the trained weights
+    ref.attach(slab.clone())
+    ref.model.eval()
+    with torch.no_grad():
+        z = ref.model(ref._prep(x)).flatten()
+    torch.testing.assert_close(eng.logits(x), z, rtol=5e-2, atol=5e-2)
