@@ -115,6 +115,8 @@ class B200Engine:
         self.loss_acc = torch.zeros((), dtype=torch.float32, device=self.device)
         self.loss_steps = 0
         self._packed_dirty = True
+        self.profile = None
+        self._tag = ""
         self._alloc(wgrad_ctas)
 
     # ----------------------------------------------------------------------------- buffers
@@ -186,6 +188,23 @@ class B200Engine:
 
     def _chk(self, rc: int, what: str) -> None:
         native.check(rc, what)
+        if self.profile is not None:      # per-launch CUDA-event timing (scripts/profile_step.py)
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self.profile.append((what + self._tag, ev))
+
+    def start_profile(self) -> None:
+        self.profile = []
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        self.profile.append(("<start>", ev))
+
+    def stop_profile(self):
+        """-> list of (kernel tag, ms) in launch order (time between consecutive completion events)."""
+        torch.cuda.synchronize(self.device)
+        out = [(n, self.profile[i - 1][1].elapsed_time(e)) for i, (n, e) in enumerate(self.profile) if i > 0]
+        self.profile = None
+        return out
 
     # ------------------------------------------------------------------------------ kernels
     def _pack_weights(self) -> None:
@@ -210,6 +229,7 @@ class B200Engine:
         prev = None
         for i, b in enumerate(self.blocks):
             s = b.spec
+            self._tag = f"[{i}]"
             D, H, W = b.c_dhw
             stats = b.stats.data_ptr() if train else None
             bias = self._p(slab, s.conv + ".bias") if s.bias else None
@@ -241,6 +261,7 @@ class B200Engine:
 
     def _head(self, B: int, y: torch.Tensor, train: bool, counters=None, double_sigmoid=True, want_grads=True) -> None:
         lib, st, slab, h = self.lib, self._stream(), self.slab, self.head
+        self._tag = ""
         last = self.blocks[-1]
         gp = (lambda n: self._p(self.grad, n)) if (train and want_grads) else (lambda n: None)
         self._chk(lib.nidt_head_fwd_bwd(
@@ -258,6 +279,7 @@ class B200Engine:
         for i in range(len(self.blocks) - 1, -1, -1):
             b = self.blocks[i]
             s = b.spec
+            self._tag = f"[{i}]"
             D, H, W = b.c_dhw
             self._chk(lib.nidt_bn_relu_pool_bwd(b.y.data_ptr(), b.da.data_ptr(), b.dy.data_ptr(), B, D, H, W, s.cout, s.pool_k, s.pool_s,
                                                 b.scale.data_ptr(), b.shift.data_ptr(), b.mean.data_ptr(), b.invstd.data_ptr(),
