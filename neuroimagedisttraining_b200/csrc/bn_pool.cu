@@ -278,6 +278,216 @@ __global__ void __launch_bounds__(256) bn_relu_pool_bwd_kernel(
     }
 }
 
+// ---------------------------------------------------------------- 3x3x3 / stride-3 fast paths
+// Forward: also emits ymax = the raw conv output at the window's arg-max (first maximum in d,h,w scan
+// order, PyTorch's rule).  With it the backward needs no arg-max search and no second pass over y:
+//   reduce: elementwise over the *pooled* tensor (1/27 of the data),
+//   apply : one streaming pass; the winner is the first element whose post-BN value equals the
+//           post-BN value of ymax.
+template <int V> struct VecT;
+template <> struct VecT<8> { using T = uint4; };
+template <> struct VecT<4> { using T = uint2; };
+template <int V>
+__device__ __forceinline__ void unpackv(const typename VecT<V>::T& v, float* f) {
+    const __nv_bfloat162* p = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+    for (int i = 0; i < V / 2; ++i) {
+        float2 t = __bfloat1622float2(p[i]);
+        f[2 * i] = t.x;
+        f[2 * i + 1] = t.y;
+    }
+}
+template <int V>
+__device__ __forceinline__ typename VecT<V>::T packv(const float* f) {
+    typename VecT<V>::T v;
+    __nv_bfloat162* p = reinterpret_cast<__nv_bfloat162*>(&v);
+#pragma unroll
+    for (int i = 0; i < V / 2; ++i) p[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+    return v;
+}
+template <int V>
+__device__ __forceinline__ void ldv(const float* p, float* f) {
+#pragma unroll
+    for (int i = 0; i < V; i += 4) *reinterpret_cast<float4*>(f + i) = ld4(p + i);
+}
+
+// one thread = one pooled output x V channels (V = 4: twice the threads, half the registers -> more loads in flight)
+template <int V>
+__global__ void __launch_bounds__(256) bn_relu_pool3_fwd_kernel(
+    const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ a, __nv_bfloat16* __restrict__ ymax, BlockGeom g,
+    const float* __restrict__ scale, const float* __restrict__ shift, int relu) {
+    using VT = typename VecT<V>::T;
+    const int CG = g.C / V;
+    const int64_t total = (int64_t)g.N * g.Dp * g.Hp * g.Wp * CG;
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const int cg = (int)(idx % CG);
+    int64_t p = idx / CG;
+    const int wp = (int)(p % g.Wp); p /= g.Wp;
+    const int hp = (int)(p % g.Hp); p /= g.Hp;
+    const int dp = (int)(p % g.Dp);
+    const int n = (int)(p / g.Dp);
+    float sc[V], sh[V], best[V], yb[V];
+    ldv<V>(scale + cg * V, sc);
+    ldv<V>(shift + cg * V, sh);
+#pragma unroll
+    for (int i = 0; i < V; ++i) { best[i] = -INFINITY; yb[i] = 0.f; }
+    const __nv_bfloat16* base = y + ((((int64_t)n * g.D + dp * 3) * g.H + hp * 3) * g.W + wp * 3) * g.C + cg * V;
+    const int64_t sH = (int64_t)g.W * g.C, sD = (int64_t)g.H * g.W * g.C;
+#pragma unroll
+    for (int kd = 0; kd < 3; ++kd) {
+        VT v[9];
+#pragma unroll
+        for (int t = 0; t < 9; ++t) v[t] = *reinterpret_cast<const VT*>(base + kd * sD + (t / 3) * sH + (t % 3) * g.C);
+#pragma unroll
+        for (int t = 0; t < 9; ++t) {
+            float f[V];
+            unpackv<V>(v[t], f);
+#pragma unroll
+            for (int i = 0; i < V; ++i) {
+                const float pv = fmaf(f[i], sc[i], sh[i]);
+                if (pv > best[i]) { best[i] = pv; yb[i] = f[i]; }
+            }
+        }
+    }
+    if (relu) {
+#pragma unroll
+        for (int i = 0; i < V; ++i) best[i] = fmaxf(best[i], 0.f);
+    }
+    *reinterpret_cast<VT*>(a + idx * V) = packv<V>(best);
+    *reinterpret_cast<VT*>(ymax + idx * V) = packv<V>(yb);
+}
+
+// reduce over the pooled tensor: partials[block][2][C]
+__global__ void __launch_bounds__(256) bn_pool3_bwd_reduce_kernel(
+    const __nv_bfloat16* __restrict__ ymax, const __nv_bfloat16* __restrict__ da, int64_t npos, int C,
+    const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean, const float* __restrict__ invstd,
+    float* __restrict__ partials, int relu) {
+    extern __shared__ float sh_red[];
+    const int CG = C >> 3;
+    const int PB = blockDim.x / CG;
+    const int cg = threadIdx.x % CG, pl = threadIdx.x / CG;
+    float sc[8], shf[8], mu[8], is[8], acc1[8], acc2[8];
+    *reinterpret_cast<float4*>(sc) = ld4(scale + cg * 8);   *reinterpret_cast<float4*>(sc + 4) = ld4(scale + cg * 8 + 4);
+    *reinterpret_cast<float4*>(shf) = ld4(shift + cg * 8);  *reinterpret_cast<float4*>(shf + 4) = ld4(shift + cg * 8 + 4);
+    *reinterpret_cast<float4*>(mu) = ld4(mean + cg * 8);    *reinterpret_cast<float4*>(mu + 4) = ld4(mean + cg * 8 + 4);
+    *reinterpret_cast<float4*>(is) = ld4(invstd + cg * 8);  *reinterpret_cast<float4*>(is + 4) = ld4(invstd + cg * 8 + 4);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc1[i] = acc2[i] = 0.f;
+    for (int64_t pos = (int64_t)blockIdx.x * PB + pl; pos < npos; pos += (int64_t)gridDim.x * PB) {
+        float ym[8], d[8];
+        unpack8(*reinterpret_cast<const uint4*>(ymax + pos * C + cg * 8), ym);
+        unpack8(*reinterpret_cast<const uint4*>(da + pos * C + cg * 8), d);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const bool on = !relu || fmaf(ym[i], sc[i], shf[i]) > 0.f;
+            const float dv = on ? d[i] : 0.f;
+            acc1[i] += dv;
+            acc2[i] = fmaf(dv, (ym[i] - mu[i]) * is[i], acc2[i]);
+        }
+    }
+    float* r1 = sh_red;
+    float* r2 = sh_red + PB * C;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { r1[pl * C + cg * 8 + i] = acc1[i]; r2[pl * C + cg * 8 + i] = acc2[i]; }
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float a = 0.f, b = 0.f;
+        for (int q = 0; q < PB; ++q) { a += r1[q * C + c]; b += r2[q * C + c]; }
+        partials[((size_t)blockIdx.x * 2 + 0) * C + c] = a;
+        partials[((size_t)blockIdx.x * 2 + 1) * C + c] = b;
+    }
+}
+
+// apply: one thread = one 3x3x3 window (incl. the remainder windows at the far edges) x V channels.
+//   dy = scale*dyhat + A*y + B   with  A = -scale*invstd*c2,  B = scale*(mean*invstd*c2 - c1)
+template <int V>
+__global__ void __launch_bounds__(256) bn_relu_pool3_bwd_apply_kernel(
+    const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ ymax, const __nv_bfloat16* __restrict__ da,
+    __nv_bfloat16* __restrict__ dy, BlockGeom g, const float* __restrict__ scale, const float* __restrict__ shift,
+    const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ c12, int relu) {
+    using VT = typename VecT<V>::T;
+    const int CG = g.C / V;
+    const int Dw = (g.D + 2) / 3, Hw = (g.H + 2) / 3, Ww = (g.W + 2) / 3;
+    const int64_t total = (int64_t)g.N * Dw * Hw * Ww * CG;
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const int cg = (int)(idx % CG);
+    int64_t p = idx / CG;
+    const int ww = (int)(p % Ww); p /= Ww;
+    const int hw = (int)(p % Hw); p /= Hw;
+    const int dw = (int)(p % Dw);
+    const int n = (int)(p / Dw);
+    float sc[V], shf[V], cA[V], cB[V], vb[V], dav[V];
+    {
+        float mu[V], is[V], k1[V], k2[V];
+        ldv<V>(scale + cg * V, sc);
+        ldv<V>(shift + cg * V, shf);
+        ldv<V>(mean + cg * V, mu);
+        ldv<V>(invstd + cg * V, is);
+        ldv<V>(c12 + cg * V, k1);
+        ldv<V>(c12 + g.C + cg * V, k2);
+#pragma unroll
+        for (int i = 0; i < V; ++i) {
+            cA[i] = -sc[i] * is[i] * k2[i];
+            cB[i] = sc[i] * (mu[i] * is[i] * k2[i] - k1[i]);
+        }
+    }
+    const bool has_out = dw < g.Dp && hw < g.Hp && ww < g.Wp;
+#pragma unroll
+    for (int i = 0; i < V; ++i) { vb[i] = INFINITY; dav[i] = 0.f; }
+    if (has_out) {
+        const int64_t po = ((((int64_t)n * g.Dp + dw) * g.Hp + hw) * g.Wp + ww) * g.C + cg * V;
+        float ym[V];
+        unpackv<V>(*reinterpret_cast<const VT*>(ymax + po), ym);
+        unpackv<V>(*reinterpret_cast<const VT*>(da + po), dav);
+#pragma unroll
+        for (int i = 0; i < V; ++i) {
+            vb[i] = fmaf(ym[i], sc[i], shf[i]);
+            if (relu && !(vb[i] > 0.f)) { dav[i] = 0.f; vb[i] = INFINITY; }   // gated: nobody wins
+            dav[i] *= sc[i];
+        }
+    }
+    const int64_t sH = (int64_t)g.W * g.C, sD = (int64_t)g.H * g.W * g.C;
+    const int64_t b0 = ((((int64_t)n * g.D + dw * 3) * g.H + hw * 3) * g.W + ww * 3) * g.C + cg * V;
+    const bool interior = dw * 3 + 2 < g.D && hw * 3 + 2 < g.H && ww * 3 + 2 < g.W;
+    if (interior) {
+#pragma unroll
+        for (int kd = 0; kd < 3; ++kd) {
+            VT v[9];
+#pragma unroll
+            for (int t = 0; t < 9; ++t) v[t] = *reinterpret_cast<const VT*>(y + b0 + kd * sD + (t / 3) * sH + (t % 3) * g.C);
+#pragma unroll
+            for (int t = 0; t < 9; ++t) {
+                float f[V], o[V];
+                unpackv<V>(v[t], f);
+#pragma unroll
+                for (int i = 0; i < V; ++i) {
+                    const bool win = fmaf(f[i], sc[i], shf[i]) == vb[i];
+                    o[i] = fmaf(cA[i], f[i], cB[i]) + (win ? dav[i] : 0.f);
+                    if (win) vb[i] = INFINITY;       // first match only
+                }
+                *reinterpret_cast<VT*>(dy + b0 + kd * sD + (t / 3) * sH + (t % 3) * g.C) = packv<V>(o);
+            }
+        }
+    } else {
+        for (int kd = 0; kd < 3 && dw * 3 + kd < g.D; ++kd)
+            for (int kh = 0; kh < 3 && hw * 3 + kh < g.H; ++kh)
+                for (int kw = 0; kw < 3 && ww * 3 + kw < g.W; ++kw) {
+                    const int64_t off = b0 + kd * sD + kh * sH + kw * g.C;
+                    float f[V], o[V];
+                    unpackv<V>(*reinterpret_cast<const VT*>(y + off), f);
+#pragma unroll
+                    for (int i = 0; i < V; ++i) {
+                        const bool win = fmaf(f[i], sc[i], shf[i]) == vb[i];
+                        o[i] = fmaf(cA[i], f[i], cB[i]) + (win ? dav[i] : 0.f);
+                        if (win) vb[i] = INFINITY;
+                    }
+                    *reinterpret_cast<VT*>(dy + off) = packv<V>(o);
+                }
+    }
+}
+
 // partials [T][2][C] -> c12 [2][C] (c1 = sum(dyhat)/M, c2 = sum(dyhat*xhat)/M), dgamma, dbeta
 __global__ void __launch_bounds__(256) bn_bwd_finalize_kernel(const float* __restrict__ partials, int T, int C, double count,
                                                               float* __restrict__ c12, float* __restrict__ dgamma, float* __restrict__ dbeta) {
@@ -329,11 +539,19 @@ NIDT_API int nidt_bn_eval_prepare(int C, const float* gamma, const float* beta, 
     return 0;
 }
 
-NIDT_API int nidt_bn_relu_pool_fwd(const void* y, void* a, int N, int D, int H, int W, int C, int pk, int ps,
+// ymax (bf16, pooled shape) is optional: when given with pool 3/3 the fast path runs and the backward can use it
+NIDT_API int nidt_bn_relu_pool_fwd(const void* y, void* a, void* ymax, int N, int D, int H, int W, int C, int pk, int ps,
                                    const float* scale, const float* shift, int relu, void* stream) {
     NIDT_REQUIRE(C % 8 == 0, "nidt_bn_relu_pool_fwd: C=%d must be a multiple of 8", C);
     BlockGeom g = make_geom(N, D, H, W, C, pk, ps);
     const int64_t total = (int64_t)N * g.Dp * g.Hp * g.Wp * (C / 8);
+    if (pk == 3 && ps == 3 && ymax != nullptr) {
+        const int64_t total4 = total * 2;   // 4 channels per thread
+        bn_relu_pool3_fwd_kernel<4><<<(unsigned)((total4 + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)y, (__nv_bfloat16*)a,
+                                                                                                    (__nv_bfloat16*)ymax, g, scale, shift, relu);
+        NIDT_LAUNCH_CHECK();
+        return 0;
+    }
     int64_t blocks = (total + 255) / 256;
     if (blocks > (int64_t)kNumSMs * 16) blocks = kNumSMs * 16;
     if (blocks < 1) blocks = 1;
@@ -343,7 +561,7 @@ NIDT_API int nidt_bn_relu_pool_fwd(const void* y, void* a, int N, int D, int H, 
 }
 
 // partials: >= nidt_bn_bwd_grid()*2*C floats.  Sequence: reduce -> finalize -> apply.
-NIDT_API int nidt_bn_relu_pool_bwd(const void* y, const void* da, void* dy, int N, int D, int H, int W, int C, int pk, int ps,
+NIDT_API int nidt_bn_relu_pool_bwd(const void* y, const void* ymax, const void* da, void* dy, int N, int D, int H, int W, int C, int pk, int ps,
                                    const float* scale, const float* shift, const float* mean, const float* invstd,
                                    float* partials, float* c12, float* dgamma, float* dbeta, int relu, void* stream) {
     NIDT_REQUIRE(C % 8 == 0 && C <= 2048, "nidt_bn_relu_pool_bwd: unsupported C=%d", C);
@@ -356,6 +574,22 @@ NIDT_API int nidt_bn_relu_pool_bwd(const void* y, const void* da, void* dy, int 
     const size_t smem = (size_t)2 * PB * C * sizeof(float);
     cudaStream_t s = (cudaStream_t)stream;
     const double count = (double)N * D * H * W;
+    if (pk == 3 && ps == 3 && ymax != nullptr) {
+        const int64_t npos = (int64_t)N * g.Dp * g.Hp * g.Wp;
+        int rgrid = (int)((npos + PB - 1) / PB);
+        if (rgrid > grid) rgrid = grid;
+        bn_pool3_bwd_reduce_kernel<<<rgrid, threads, smem, s>>>((const __nv_bfloat16*)ymax, (const __nv_bfloat16*)da, npos, C, scale, shift, mean,
+                                                               invstd, partials, relu);
+        NIDT_LAUNCH_CHECK();
+        bn_bwd_finalize_kernel<<<(C + 31) / 32, 256, 0, s>>>(partials, rgrid, C, count, c12, dgamma, dbeta);
+        NIDT_LAUNCH_CHECK();
+        const int64_t total = (int64_t)N * ((D + 2) / 3) * ((H + 2) / 3) * ((W + 2) / 3) * (C / 4);
+        bn_relu_pool3_bwd_apply_kernel<4><<<(unsigned)((total + 255) / 256), 256, 0, s>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)ymax,
+                                                                                       (const __nv_bfloat16*)da, (__nv_bfloat16*)dy, g, scale, shift,
+                                                                                       mean, invstd, c12, relu);
+        NIDT_LAUNCH_CHECK();
+        return 0;
+    }
     bn_relu_pool_bwd_kernel<false><<<grid, threads, smem, s>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)da, nullptr, g, scale, shift,
                                                                mean, invstd, nullptr, partials, relu);
     NIDT_LAUNCH_CHECK();

@@ -90,8 +90,8 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv3d_fprop_tc_kernel(
     const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_y,
     const ConvGeom g, const float* __restrict__ bias, float* __restrict__ stats_partials, int total_tiles) {
     using Cfg = FpropCfg<BLOCK_N>;
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    extern __shared__ __align__(1024) uint8_t smem[];   // SWIZZLE_128B tiles need 1024-byte alignment
+    if ((tc::smem_u32(smem) & 1023u) != 0u) __trap();
     uint8_t* stage_base = smem;
     uint8_t* staging = smem + Cfg::kStages * Cfg::kStageBytes;
     uint64_t* bars = reinterpret_cast<uint64_t*>(staging + Cfg::kStagingBytes);
@@ -276,8 +276,8 @@ constexpr int kWgSmemBytes = kWgStages * kWgStageBytes + 1024 + 256;
 
 __global__ void __launch_bounds__(kConvThreads, 1) conv3d_wgrad_tc_kernel(
     const __grid_constant__ CUtensorMap tm_dy, const __grid_constant__ CUtensorMap tm_x, const WgradGeom g, float* __restrict__ partials) {
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    extern __shared__ __align__(1024) uint8_t smem[];   // SWIZZLE_128B tiles need 1024-byte alignment
+    if ((tc::smem_u32(smem) & 1023u) != 0u) __trap();
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kWgStages * kWgStageBytes);
     uint64_t* full = bars;
     uint64_t* empty = bars + kWgStages;

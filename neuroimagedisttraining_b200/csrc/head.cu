@@ -39,8 +39,9 @@ struct HeadArgs {
     int double_sigmoid;          // eval loss = BCEWithLogits(sigmoid(z)) as the reference does
 };
 
-// one CTA, 256 threads; dynamic smem: f[B][F] (post-dropout, fp32) | h[B][Hd] | dh[B][Hd] | z[B] | dz[B]
-__global__ void __launch_bounds__(256) head_kernel(HeadArgs a) {
+// one CTA, 1024 threads; dynamic smem: f[B][F] (post-dropout, fp32) | h[B][Hd] | dh[B][Hd] | z[B] | dz[B] | W1[Hd][F+1]
+// (W1 is staged once with coalesced loads; every later pass reads it from shared memory)
+__global__ void __launch_bounds__(1024) head_kernel(HeadArgs a) {
     extern __shared__ float sm[];
     const int F = a.S * a.C;
     float* f = sm;
@@ -48,7 +49,10 @@ __global__ void __launch_bounds__(256) head_kernel(HeadArgs a) {
     float* dh = h + (size_t)a.B * a.Hd;
     float* z = dh + (size_t)a.B * a.Hd;
     float* dz = z + a.B;
+    float* sW1 = dz + a.B;
+    const int FP = F + 1;
     const int tid = threadIdx.x, nt = blockDim.x;
+    for (int i = tid; i < a.Hd * F; i += nt) sW1[(i / F) * FP + (i % F)] = a.W1[i];
     const float keep_scale = (a.train && a.p_drop > 0.f) ? 1.f / (1.f - a.p_drop) : 1.f;
 
     // features: memory (n, s, c) -> logical index c*S + s ; dropout 1
@@ -64,7 +68,7 @@ __global__ void __launch_bounds__(256) head_kernel(HeadArgs a) {
     // fc1 + relu + dropout 2:  h[n][j]
     for (int i = tid; i < a.B * a.Hd; i += nt) {
         const int n = i / a.Hd, j = i % a.Hd;
-        const float* w = a.W1 + (size_t)j * F;
+        const float* w = sW1 + (size_t)j * FP;
         const float* x = f + (size_t)n * F;
         float acc = a.b1[j];
         for (int k = 0; k < F; ++k) acc = fmaf(w[k], x[k], acc);
@@ -151,7 +155,7 @@ __global__ void __launch_bounds__(256) head_kernel(HeadArgs a) {
             const int s = r / a.C, c = r % a.C;
             const int lf = c * a.S + s;
             float g = 0.f;
-            for (int j = 0; j < a.Hd; ++j) g = fmaf(dh[n * a.Hd + j], a.W1[(size_t)j * F + lf], g);
+            for (int j = 0; j < a.Hd; ++j) g = fmaf(dh[n * a.Hd + j], sW1[j * FP + lf], g);
             if (a.p_drop > 0.f) g = (uniform01(a.seed, 1u, (uint32_t)(n * F + lf)) >= a.p_drop) ? g * keep_scale : 0.f;
             a.dfeat[i] = __float2bfloat16(g);
         }
@@ -166,11 +170,11 @@ NIDT_API int nidt_head_fwd_bwd(const void* feat, const float* y, const float* W1
                                int double_sigmoid, void* stream) {
     HeadArgs a{(const __nv_bfloat16*)feat, y, W1, b1, W2, b2, gW1, gb1, gW2, gb2, (__nv_bfloat16*)dfeat, loss_acc, eval_counters,
                logits_out, B, S, C, Hd, p_drop, seed, train, double_sigmoid};
-    const size_t smem = ((size_t)B * S * C + 2 * (size_t)B * Hd + 2 * (size_t)B) * sizeof(float);
-    NIDT_REQUIRE(smem <= 200 * 1024, "nidt_head_fwd_bwd: B*F=%d too large for one CTA", B * S * C);
+    const size_t smem = ((size_t)B * S * C + 2 * (size_t)B * Hd + 2 * (size_t)B + (size_t)Hd * (S * C + 1)) * sizeof(float);
+    NIDT_REQUIRE(smem <= 220 * 1024, "nidt_head_fwd_bwd: B*F=%d with hidden %d does not fit one CTA", B * S * C, Hd);
     NIDT_REQUIRE(B <= 256, "nidt_head_fwd_bwd: batch %d > 256", B);
     NIDT_CUDA_CHECK(cudaFuncSetAttribute(head_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    head_kernel<<<1, 256, smem, (cudaStream_t)stream>>>(a);
+    head_kernel<<<1, 1024, smem, (cudaStream_t)stream>>>(a);
     NIDT_LAUNCH_CHECK();
     return 0;
 }

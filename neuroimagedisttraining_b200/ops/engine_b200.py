@@ -35,8 +35,8 @@ def _declare(lib) -> None:
         "nidt_bn_bwd_grid": [],
         "nidt_bn_finalize": [vp, i32, i32, f64, vp, vp, vp, vp, vp, f32, f32, vp, vp, vp, vp, vp],
         "nidt_bn_eval_prepare": [i32, vp, vp, vp, vp, f32, vp, vp, vp],
-        "nidt_bn_relu_pool_fwd": [vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp, i32, vp],
-        "nidt_bn_relu_pool_bwd": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, vp],
+        "nidt_bn_relu_pool_fwd": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp, i32, vp],
+        "nidt_bn_relu_pool_bwd": [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, vp],
         "nidt_head_fwd_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, u64, i32, i32, vp],
         "nidt_conv3d_fprop_tc": [vp, vp, vp, vp, vp] + [i32] * 17 + [vp],
         "nidt_conv3d_m_tiles": [i32] * 8,
@@ -44,7 +44,7 @@ def _declare(lib) -> None:
         "nidt_pack_conv_weights": [vp, i32, i32, i32, vp, vp, vp],
         "nidt_conv_in_grid": [],
         "nidt_conv_in_fprop": [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, f32, vp],
-        "nidt_conv_in_wgrad": [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, f32, vp],
+        "nidt_conv_in_wgrad": [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, f32, vp],
     }
     for name, argtypes in sigs.items():
         fn = getattr(lib, name)
@@ -136,6 +136,7 @@ class B200Engine:
             b.dy = torch.empty_like(b.y)
             b.a = torch.empty((B,) + adhw + (spec.cout,), dtype=bf, device=dev) if spec.pool_k else torch.empty_like(b.y)
             b.da = torch.empty_like(b.a)
+            b.ymax = torch.empty_like(b.a) if (spec.pool_k == 3 and spec.pool_s == 3) else None
             C_ = spec.cout
             b.scale, b.shift, b.mean, b.invstd = (torch.zeros(C_, dtype=torch.float32, device=dev) for _ in range(4))
             b.c12 = torch.zeros(2 * C_, dtype=torch.float32, device=dev)
@@ -253,7 +254,7 @@ class B200Engine:
                                                b.mean.data_ptr(), b.invstd.data_ptr(), st), "bn_finalize")
             else:
                 self._chk(lib.nidt_bn_eval_prepare(s.cout, g, be, rm, rv, 1e-5, b.scale.data_ptr(), b.shift.data_ptr(), st), "bn_eval_prepare")
-            self._chk(lib.nidt_bn_relu_pool_fwd(b.y.data_ptr(), b.a.data_ptr(), B, D, H, W, s.cout, s.pool_k, s.pool_s,
+            self._chk(lib.nidt_bn_relu_pool_fwd(b.y.data_ptr(), b.a.data_ptr(), b.ymax.data_ptr() if (train and b.ymax is not None) else None, B, D, H, W, s.cout, s.pool_k, s.pool_s,
                                                 b.scale.data_ptr(), b.shift.data_ptr(), int(s.relu), st), "bn_relu_pool_fwd")
             native.count_launches(2)
             prev = b.a
@@ -281,7 +282,7 @@ class B200Engine:
             s = b.spec
             self._tag = f"[{i}]"
             D, H, W = b.c_dhw
-            self._chk(lib.nidt_bn_relu_pool_bwd(b.y.data_ptr(), b.da.data_ptr(), b.dy.data_ptr(), B, D, H, W, s.cout, s.pool_k, s.pool_s,
+            self._chk(lib.nidt_bn_relu_pool_bwd(b.y.data_ptr(), b.ymax.data_ptr() if b.ymax is not None else None, b.da.data_ptr(), b.dy.data_ptr(), B, D, H, W, s.cout, s.pool_k, s.pool_s,
                                                 b.scale.data_ptr(), b.shift.data_ptr(), b.mean.data_ptr(), b.invstd.data_ptr(),
                                                 b.bwd_partials.data_ptr(), b.c12.data_ptr(), self._p(self.grad, s.bn + ".weight"),
                                                 self._p(self.grad, s.bn + ".bias"), int(s.relu), st), "bn_relu_pool_bwd")
@@ -289,7 +290,7 @@ class B200Engine:
             iD, iH, iW = b.in_dhw
             if i == 0:
                 self._chk(lib.nidt_conv_in_wgrad(self._x.data_ptr(), b.dy.data_ptr(), self._p(self.grad, s.conv + ".weight"),
-                                                 b.wg_scratch.data_ptr(), B, iD, iH, iW, s.k, s.stride, s.pad, self.input_scale, st), "conv_in_wgrad")
+                                                 self._p(self.grad, s.conv + ".bias") if s.bias else None, b.wg_scratch.data_ptr(), B, iD, iH, iW, s.k, s.stride, s.pad, self.input_scale, st), "conv_in_wgrad")
                 native.count_launches(2)
             else:
                 prev = self.blocks[i - 1]
@@ -303,8 +304,9 @@ class B200Engine:
                 self._chk(lib.nidt_conv3d_fprop_tc(b.dy.data_ptr(), b.wd.data_ptr(), None, prev.da.data_ptr(), None, B, D, H, W, s.cout,
                                                    iD, iH, iW, s.cin, s.k, 1, s.k - 1 - s.pad, *dbox, b.dgrad_block_n, st), "conv3d_dgrad_tc")
                 native.count_launches(3)
-            # conv bias gradient is identically zero in exact arithmetic (BatchNorm subtracts the batch mean
-            # right after the conv); the grad slab keeps it at 0, weight decay still applies in the update.
+            # Conv bias gradients: block 0 gets sum(dY) for free from the bias column of its wgrad GEMM.  For the
+            # other blocks it is identically zero in exact arithmetic (BatchNorm subtracts the batch mean right
+            # after the conv): the grad slab keeps 0 there, weight decay still applies in the update.
 
     # ---------------------------------------------------------------------------- public API
     def compute_grads(self, x, y, train_mode: bool = True) -> torch.Tensor:

@@ -88,14 +88,16 @@ def conv_in_fprop(x_u8: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tens
     return (y, part) if stats else y
 
 
-def conv_in_wgrad(x_u8: torch.Tensor, dy: torch.Tensor, k: int, stride: int, pad: int, scale: float) -> torch.Tensor:
+def conv_in_wgrad(x_u8: torch.Tensor, dy: torch.Tensor, k: int, stride: int, pad: int, scale: float, with_bias: bool = False):
+    """-> dW fp32 [64,1,k,k,k] (and dbias [64] = sum of dy, from the bias column of the same GEMM)."""
     lib = _lib()
     N, D, H, W = x_u8.shape
     grad = torch.empty((64, 1, k, k, k), dtype=torch.float32, device=dy.device)
+    gb = torch.empty(64, dtype=torch.float32, device=dy.device) if with_bias else None
     scratch = torch.zeros(lib.nidt_conv_in_grid() * 128 * 64, dtype=torch.float32, device=dy.device)
-    native.check(lib.nidt_conv_in_wgrad(x_u8.data_ptr(), dy.data_ptr(), grad.data_ptr(), scratch.data_ptr(), N, D, H, W, k, stride, pad, scale,
-                                        _st(dy)), "conv_in_wgrad")
-    return grad
+    native.check(lib.nidt_conv_in_wgrad(x_u8.data_ptr(), dy.data_ptr(), grad.data_ptr(), gb.data_ptr() if with_bias else None,
+                                        scratch.data_ptr(), N, D, H, W, k, stride, pad, scale, _st(dy)), "conv_in_wgrad")
+    return (grad, gb) if with_bias else grad
 
 
 def bn_finalize(partials: torch.Tensor, count: float, gamma, beta, running_mean=None, running_var=None, num_batches=None,
@@ -111,7 +113,7 @@ def bn_finalize(partials: torch.Tensor, count: float, gamma, beta, running_mean=
     return scale, shift, mean, invstd
 
 
-def bn_relu_pool_fwd(y: torch.Tensor, scale, shift, pool_k: int = 0, pool_s: int = 0, relu: bool = True) -> torch.Tensor:
+def bn_relu_pool_fwd(y: torch.Tensor, scale, shift, pool_k: int = 0, pool_s: int = 0, relu: bool = True, want_ymax: bool = False):
     lib = _lib()
     N, D, H, W, Cc = y.shape
     if pool_k:
@@ -119,12 +121,13 @@ def bn_relu_pool_fwd(y: torch.Tensor, scale, shift, pool_k: int = 0, pool_s: int
     else:
         od = (D, H, W)
     a = torch.empty((N,) + od + (Cc,), dtype=torch.bfloat16, device=y.device)
-    native.check(lib.nidt_bn_relu_pool_fwd(y.data_ptr(), a.data_ptr(), N, D, H, W, Cc, pool_k, pool_s, scale.data_ptr(), shift.data_ptr(),
-                                           int(relu), _st(y)), "bn_relu_pool_fwd")
-    return a
+    ymax = torch.empty_like(a) if want_ymax else None
+    native.check(lib.nidt_bn_relu_pool_fwd(y.data_ptr(), a.data_ptr(), ymax.data_ptr() if want_ymax else None, N, D, H, W, Cc, pool_k, pool_s,
+                                           scale.data_ptr(), shift.data_ptr(), int(relu), _st(y)), "bn_relu_pool_fwd")
+    return (a, ymax) if want_ymax else a
 
 
-def bn_relu_pool_bwd(y, da, scale, shift, mean, invstd, pool_k: int = 0, pool_s: int = 0, relu: bool = True):
+def bn_relu_pool_bwd(y, da, scale, shift, mean, invstd, pool_k: int = 0, pool_s: int = 0, relu: bool = True, ymax=None):
     """-> (dy bf16 like y, dgamma, dbeta)"""
     lib = _lib()
     N, D, H, W, Cc = y.shape
@@ -133,7 +136,7 @@ def bn_relu_pool_bwd(y, da, scale, shift, mean, invstd, pool_k: int = 0, pool_s:
     partials = torch.zeros(lib.nidt_bn_bwd_grid() * 2 * Cc, dtype=torch.float32, device=dev)
     c12 = torch.empty(2 * Cc, dtype=torch.float32, device=dev)
     dg, db = torch.empty(Cc, dtype=torch.float32, device=dev), torch.empty(Cc, dtype=torch.float32, device=dev)
-    native.check(lib.nidt_bn_relu_pool_bwd(y.data_ptr(), da.data_ptr(), dy.data_ptr(), N, D, H, W, Cc, pool_k, pool_s, scale.data_ptr(),
+    native.check(lib.nidt_bn_relu_pool_bwd(y.data_ptr(), ymax.data_ptr() if ymax is not None else None, da.data_ptr(), dy.data_ptr(), N, D, H, W, Cc, pool_k, pool_s, scale.data_ptr(),
                                            shift.data_ptr(), mean.data_ptr(), invstd.data_ptr(), partials.data_ptr(), c12.data_ptr(),
                                            dg.data_ptr(), db.data_ptr(), int(relu), _st(y)), "bn_relu_pool_bwd")
     return dy, dg, db

@@ -25,8 +25,8 @@ def _close(a, b, rtol=2e-2, atol=2e-2, what=""):
     assert err <= atol * scale + rtol * 0, f"{what}: max err {err:.4g} vs scale {scale:.4g}"
 
 
-@pytest.mark.parametrize("C,pool", [(64, 3), (128, 3), (192, 0), (128, 0)])
-def test_bn_relu_pool_fwd_bwd(C, pool):
+@pytest.mark.parametrize("C,pool,fast", [(64, 3, False), (64, 3, True), (128, 3, True), (192, 0, False), (128, 0, False)])
+def test_bn_relu_pool_fwd_bwd(C, pool, fast):
     from neuroimagedisttraining_b200.ops import volumetric as V
     torch.manual_seed(0)
     N, D, H, W = 3, 8, 11, 7
@@ -45,7 +45,11 @@ def test_bn_relu_pool_fwd_bwd(C, pool):
     partials = torch.stack([flat.sum(0), (flat * flat).sum(0)]).unsqueeze(0).contiguous()
     nb = torch.zeros(1, device=DEV)
     scale, shift, mean, invstd = V.bn_finalize(partials, flat.shape[0], gamma, beta, rm, rv, nb)
-    a = V.bn_relu_pool_fwd(ycl, scale, shift, pool, pool, True)
+    ymax = None
+    if fast:      # 3x3x3 fast path: forward also emits the raw arg-max values the backward consumes
+        a, ymax = V.bn_relu_pool_fwd(ycl, scale, shift, pool, pool, True, want_ymax=True)
+    else:
+        a = V.bn_relu_pool_fwd(ycl, scale, shift, pool, pool, True)
     _close(_cf(a), ref, what="fwd")
     ref_rm, ref_rv = torch.zeros(C, device=DEV), torch.ones(C, device=DEV)
     F.batch_norm(y.float(), ref_rm, ref_rv, gamma, beta, training=True, momentum=0.1, eps=1e-5)
@@ -55,7 +59,7 @@ def test_bn_relu_pool_fwd_bwd(C, pool):
     # backward
     da = torch.randn_like(ref).bfloat16()
     ref.backward(da.float())
-    dy, dg, db = V.bn_relu_pool_bwd(ycl, _cl(da), scale, shift, mean, invstd, pool, pool, True)
+    dy, dg, db = V.bn_relu_pool_bwd(ycl, _cl(da), scale, shift, mean, invstd, pool, pool, True, ymax=ymax)
     _close(_cf(dy), yf.grad, what="dy")
     _close(dg, g2.grad, atol=1e-2, what="dgamma")
     _close(db, b2.grad, atol=1e-2, what="dbeta")
@@ -176,7 +180,8 @@ def test_conv_in_fprop_wgrad(N, D, H, W, k, stride, pad):
     bias = torch.randn(64, device=DEV) * 0.1
     xb = (x.float() * scale).bfloat16().float().unsqueeze(1).requires_grad_(False)
     wr = w.bfloat16().float().requires_grad_(True)
-    ref = F.conv3d(xb, wr, bias, stride=stride, padding=pad)
+    br = bias.bfloat16().float().requires_grad_(True)      # the bias rides the GEMM as a bf16 K column
+    ref = F.conv3d(xb, wr, br, stride=stride, padding=pad)
     y, part = V.conv_in_fprop(x, w, bias, k, stride, pad, scale, stats=True)
     torch.cuda.synchronize()
     _close(_cf(y), ref, atol=1e-2, what="conv_in fprop")
@@ -185,8 +190,9 @@ def test_conv_in_fprop_wgrad(N, D, H, W, k, stride, pad):
     torch.testing.assert_close(part[:, 1].sum(0), (yb * yb).sum(0), rtol=2e-3, atol=5e-2)
     dy = (torch.randn_like(ref) * 0.1).bfloat16()
     ref.backward(dy.float())
-    dw = V.conv_in_wgrad(x, _cl(dy), k, stride, pad, scale)
+    dw, dbias = V.conv_in_wgrad(x, _cl(dy), k, stride, pad, scale, with_bias=True)
     _close(dw, wr.grad, atol=1e-2, what="conv_in wgrad")
+    _close(dbias, br.grad, atol=1e-2, what="conv_in bias grad")
 
 
 def _engine_pair(B, p_drop=0.0):
