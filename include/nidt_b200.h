@@ -1,0 +1,108 @@
+/* C ABI of libnidt_b200.so -- the sm_100a kernels of neuroimagedisttraining_b200.
+ *
+ * Conventions
+ *   - every function returns 0 on success; otherwise nidt_last_error() (per host thread) says why;
+ *   - all pointers are device pointers unless stated; `stream` is a cudaStream_t passed as void*;
+ *   - nothing here allocates device memory: callers pass every buffer, including scratch
+ *     (the size queries next to each function say how much);
+ *   - "slab" = one flat fp32 buffer holding all parameters (then all buffers) of a model, every
+ *     entry 16-byte aligned, padding kept at zero (neuroimagedisttraining_b200/runtime/slab.py);
+ *   - activations are channels-last (NDHWC) bf16.
+ * Citations name the reference code each entry point replaces (paths relative to the reference repo).
+ */
+#ifndef NIDT_B200_H_
+#define NIDT_B200_H_
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* nidt_last_error(void);
+int nidt_abi_version(void);
+
+/* ------------------------------------------------------------------ flat-slab ops (flat_ops.cu) */
+int nidt_norm_scratch_floats(void);
+int nidt_topk_scratch_bytes(void);
+int nidt_max_agg_sources(void);
+
+/* clip_grad_norm_(clip) + SGD(momentum, wd) + `w *= mask` in two launches over the whole slab.
+ * ref: fedml_api/standalone/sailentgrads/my_model_trainer.py:209,224-231.  scratch: nidt_norm_scratch_floats() floats. */
+int nidt_masked_sgd_step(float* w, const float* g, float* mom, const float* mask, int64_t n, float lr, float momentum,
+                         float wd, float clip_norm, int first_step, float* scratch, float* norm_out, void* stream);
+int nidt_grad_norm(const float* g, int64_t n, float* scratch, float* norm_out, void* stream);
+
+/* out = sum_i weights[i]*srcs[i] in list order (separate mul/add: bit-identical to the reference loop), optional
+ * mask over the first n_mask elements.  srcs/weights are HOST arrays.  ref: sailentgrads_api.py:212-227, fedavg_api.py:102-117. */
+int nidt_weighted_aggregate(float* out, const float* const* srcs, const float* weights, int k, const float* mask,
+                            int64_t n_mask, int64_t n, void* stream);
+
+/* scores += scale*|g*w|  (SNIP |dL/dm| at m = 1).  ref: sailentgrads/snip.py:9-16,60-71. */
+int nidt_saliency_accumulate(float* scores, const float* g, const float* w, int64_t n, float scale, void* stream);
+
+/* One cooperative kernel: sum of prunable scores, 4 radix-select passes for the k-th largest normalised score, mask
+ * emission (ties kept).  flags[i]: 0 padding, 1 never pruned, 2 prunable.  scratch: nidt_topk_scratch_bytes().
+ * ref: sailentgrads/snip.py:80-116. */
+int nidt_global_topk_mask(const float* scores, const unsigned char* flags, float* mask, int64_t n, unsigned long long k,
+                          void* scratch, void* stream);
+int nidt_topk_read_result(const void* scratch, float* threshold, float* norm, unsigned int* kept, void* stream);
+
+/* nnz / Hamming distance / squared distance without host syncs.  `out` counters are added to.
+ * ref: fedml_core/trainer/model_trainer.py:49-53, fedml_api/standalone/DisPFL/slim_util.py:10-19. */
+int nidt_count_nonzero(const float* a, int64_t n, unsigned long long* out, void* stream);
+int nidt_hamming(const float* a, const float* b, int64_t n, unsigned long long* out, void* stream);
+int nidt_sq_dist(const float* a, const float* b, int64_t n, float* scratch, float* out, void* stream);
+/* Ditto proximal pull w -= coef*(w - ref).  ref: fedml_api/standalone/ditto/my_model_trainer.py:63-64. */
+int nidt_prox_pull(float* w, const float* ref, int64_t n, float coef, void* stream);
+
+/* ------------------------------------------------- BatchNorm3d + ReLU + MaxPool3d, fused (bn_pool.cu) */
+/* ref: fedml_api/model/cv/salient_models.py:147-168 (cuDNN BN, ATen ReLU/MaxPool3d there). */
+int nidt_bn_bwd_grid(void);
+int nidt_bn_finalize(const float* partials /*[T][2][C]*/, int T, int C, double count, const float* gamma, const float* beta,
+                     float* running_mean, float* running_var, float* num_batches, float momentum, float eps, float* scale,
+                     float* shift, float* mean, float* invstd, void* stream);
+int nidt_bn_eval_prepare(int C, const float* gamma, const float* beta, const float* running_mean, const float* running_var,
+                         float eps, float* scale, float* shift, void* stream);
+/* a = maxpool(relu(y*scale+shift)); ymax (optional, pool 3/3) = raw y at each window's arg-max, consumed by the backward. */
+int nidt_bn_relu_pool_fwd(const void* y, void* a, void* ymax, int N, int D, int H, int W, int C, int pk, int ps,
+                          const float* scale, const float* shift, int relu, void* stream);
+/* dy, dgamma, dbeta from da.  partials: nidt_bn_bwd_grid()*2*C floats, c12: 2*C floats. */
+int nidt_bn_relu_pool_bwd(const void* y, const void* ymax, const void* da, void* dy, int N, int D, int H, int W, int C, int pk,
+                          int ps, const float* scale, const float* shift, const float* mean, const float* invstd,
+                          float* partials, float* c12, float* dgamma, float* dbeta, int relu, void* stream);
+
+/* ------------------------------------------------------------------ classifier head (head.cu) */
+/* Dropout-Linear-ReLU-Dropout-Linear(1)-BCEWithLogits forward + loss + full backward, or eval counters
+ * (incl. the reference's double-sigmoid loss).  ref: salient_models.py:171-176, my_model_trainer.py:207-222,239-274. */
+int nidt_head_fwd_bwd(const void* feat, const float* y, const float* W1, const float* b1, const float* W2, const float* b2,
+                      float* gW1, float* gb1, float* gW2, float* gb2, void* dfeat, float* loss_acc, double* eval_counters,
+                      float* logits_out, int B, int S, int C, int Hd, float p_drop, uint64_t seed, int train,
+                      int double_sigmoid, void* stream);
+
+/* ------------------------------------------------- tcgen05/TMA implicit-GEMM 3-D convolution (conv_tc.cu) */
+/* ref: nn.Conv3d forward/backward at salient_models.py:152-166 (cuDNN fp32).  Cin % 64 == 0; box = tile of output
+ * positions (bw*bh*bd*bn <= 128).  dgrad = the same entry point on dY with the `wd` weights and pad' = k-1-pad. */
+int nidt_conv3d_m_tiles(int N, int Do, int Ho, int Wo, int bw, int bh, int bd, int bn);
+int nidt_conv3d_fprop_tc(const void* x, const void* w, const float* bias, void* y, float* stats_partials, int N, int Di, int Hi,
+                         int Wi, int Cin, int Do, int Ho, int Wo, int Cout, int k, int stride, int pad, int bw, int bh, int bd,
+                         int bn, int block_n, void* stream);
+int64_t nidt_conv3d_wgrad_scratch_floats(int Cout, int Cin, int k, int splits);
+/* grad: fp32 [Cout][Cin][k^3] (PyTorch layout); scratch: split-K partials, nidt_conv3d_wgrad_scratch_floats() floats. */
+int nidt_conv3d_wgrad_tc(const void* dy, const void* x, float* grad, float* scratch, int N, int Di, int Hi, int Wi, int Cin,
+                         int Do, int Ho, int Wo, int Cout, int k, int stride, int pad, int bw, int bh, int bd, int bn,
+                         int splits, void* stream);
+/* fp32 [Cout][Cin][taps] -> bf16 wf [Cout][taps][Cin] and wd [Cin][taps (flipped)][Cout]. */
+int nidt_pack_conv_weights(const float* w, int Cout, int Cin, int taps, void* wf, void* wd, void* stream);
+
+/* ------------------------------------------------------- first layer, Cin = 1 -> 64 (conv_in.cu) */
+/* ref: nn.Conv3d(1,64,5,stride 2) at salient_models.py:147.  x is the 8-bit volume; normalisation x*scale is fused. */
+int nidt_conv_in_grid(void);
+int nidt_conv_in_fprop(const void* x, const float* w, const float* bias, void* y, float* stats_partials, int N, int Di, int Hi,
+                       int Wi, int k, int stride, int pad, float scale, void* stream);
+int nidt_conv_in_wgrad(const void* x, const void* dy, float* grad, float* grad_bias, float* scratch, int N, int Di, int Hi, int Wi,
+                       int k, int stride, int pad, float scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NIDT_B200_H_ */
