@@ -465,10 +465,8 @@ NIDT_API int nidt_conv3d_m_tiles(int N, int Do, int Ho, int Wo, int bw, int bh, 
 
 NIDT_API int64_t nidt_conv3d_wgrad_scratch_floats(int Cout, int Cin, int k, int splits) { return (int64_t)splits * k * k * k * Cout * Cin; }
 
-// dy: bf16 [N][Do][Ho][Wo][Cout]; x: bf16 [N][Di][Hi][Wi][Cin]; grad: fp32 [Cout][Cin][k^3] (PyTorch layout);
-// scratch: >= nidt_conv3d_wgrad_scratch_floats() floats of split-K partials.
-NIDT_API int nidt_conv3d_wgrad_tc(const void* dy, const void* x, float* grad, float* scratch, int N, int Di, int Hi, int Wi, int Cin, int Do, int Ho,
-                                  int Wo, int Cout, int k, int stride, int pad, int bw, int bh, int bd, int bn, int splits, void* stream) {
+static int wgrad_impl(const void* dy, const void* x, float* grad, float* scratch, int N, int Di, int Hi, int Wi, int Cin, int Do, int Ho,
+                      int Wo, int Cout, int k, int stride, int pad, int bw, int bh, int bd, int bn, int splits, void* stream) {
     NIDT_REQUIRE(Cin % 64 == 0 && Cout % 8 == 0, "conv3d_wgrad_tc: Cin=%d must be a multiple of 64, Cout=%d of 8", Cin, Cout);
     NIDT_REQUIRE(bw * bh * bd * bn <= 128, "conv3d_wgrad_tc: box exceeds 128 rows");
     NIDT_REQUIRE(splits >= 1 && scratch != nullptr, "conv3d_wgrad_tc: need splits >= 1 and a scratch buffer");
@@ -496,6 +494,13 @@ NIDT_API int nidt_conv3d_wgrad_tc(const void* dy, const void* x, float* grad, fl
     wgrad_reduce_kernel<<<(int)blocks, 256, 0, s>>>(scratch, splits, taps, Cout, Cin, grad);
     NIDT_LAUNCH_CHECK();
     return 0;
+}
+
+// dy: bf16 [N][Do][Ho][Wo][Cout]; x: bf16 [N][Di][Hi][Wi][Cin]; grad: fp32 [Cout][Cin][k^3] (PyTorch layout);
+// scratch: >= nidt_conv3d_wgrad_scratch_floats() floats of split-K partials.
+NIDT_API int nidt_conv3d_wgrad_tc(const void* dy, const void* x, float* grad, float* scratch, int N, int Di, int Hi, int Wi, int Cin, int Do, int Ho,
+                                  int Wo, int Cout, int k, int stride, int pad, int bw, int bh, int bd, int bn, int splits, void* stream) {
+    return wgrad_impl(dy, x, grad, scratch, N, Di, Hi, Wi, Cin, Do, Ho, Wo, Cout, k, stride, pad, bw, bh, bd, bn, splits, stream);
 }
 
 NIDT_API int nidt_pack_conv_weights(const float* w, int Cout, int Cin, int taps, void* wf, void* wd, void* stream) {
