@@ -91,6 +91,17 @@ int64_t nidt_conv3d_wgrad_scratch_floats(int Cout, int Cin, int k, int splits);
 int nidt_conv3d_wgrad_tc(const void* dy, const void* x, float* grad, float* scratch, int N, int Di, int Hi, int Wi, int Cin,
                          int Do, int Ho, int Wo, int Cout, int k, int stride, int pad, int bw, int bh, int bd, int bn,
                          int splits, void* stream);
+/* Same result as nidt_conv3d_wgrad_tc without a caller-provided scratch buffer: the split-K partials go to a 16 MiB
+ * array built into the library (held by every GPU that loads it, until exit).  For callers that cannot allocate device
+ * memory where the call happens (custom-call bodies inside another framework's executor, code inside a stream capture,
+ * fixed-memory deployments).  Refuses problems needing more than nidt_conv3d_wgrad_static_capacity_floats() floats
+ * (splits*k^3*Cout*Cin).  The first call on a device looks the array's address up: make it at start-up, before any
+ * stream capture.  Calls share the array: do not let two of them overlap on the GPU.
+ * This entry point has no counterpart in the reference. */
+int64_t nidt_conv3d_wgrad_static_capacity_floats(void);
+int nidt_conv3d_wgrad_tc_static(const void* dy, const void* x, float* grad, int N, int Di, int Hi, int Wi, int Cin, int Do, int Ho,
+                                int Wo, int Cout, int k, int stride, int pad, int bw, int bh, int bd, int bn, int splits,
+                                void* stream);
 /* fp32 [Cout][Cin][taps] -> bf16 wf [Cout][taps][Cin] and wd [Cin][taps (flipped)][Cout]. */
 int nidt_pack_conv_weights(const float* w, int Cout, int Cin, int taps, void* wf, void* wd, void* stream);
 

@@ -511,3 +511,62 @@ NIDT_API int nidt_pack_conv_weights(const float* w, int Cout, int Cin, int taps,
     NIDT_LAUNCH_CHECK();
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// nidt_conv3d_wgrad_tc_static: the same weight-gradient kernels, but the split-K partials live in a
+// scratch array that is part of the library image instead of a buffer the caller allocates.
+//
+// It is meant for callers that hold device pointers but have no way to obtain more device memory at
+// the point of the call: a custom-call body inside another framework's executor (which owns the
+// allocator and hands the callee only its operands), code running between cudaStreamBeginCapture and
+// cudaStreamEndCapture (allocation is not a capturable operation), and deployments whose memory is
+// carved up once at start-up and where a late cudaMalloc is forbidden or may fail.  Such a caller passes
+// only the inputs (dy, x) and the output (grad).
+//
+// Cost and limits: kWgradStaticFloats floats (16 MiB) of global memory are reserved on every GPU that
+// loads libnidt_b200.so, from load until the process exits, whether or not this entry point is used.
+// A problem needs splits*k^3*Cout*Cin floats; anything larger is refused (return code 2, message via
+// nidt_last_error()) -- use nidt_conv3d_wgrad_tc with your own buffer for those.
+//
+// Set-up: the first call on each device resolves the device address of the array with
+// cudaGetSymbolAddress (the symbol's name is only a host-side handle, not something a kernel can be
+// given) and caches it.  Make that first call during initialisation, with the target device current,
+// before starting any stream capture.  No cudaMalloc / cudaFree / allocating library routine is called.
+//
+// Sharing: all calls on a device use the same array and it keeps whatever the previous call left there.
+// Every partial that a call reads back is first written by that call's own GEMM kernel (empty splits
+// write zeros), so nothing needs clearing between calls -- but two calls whose kernels may overlap on the
+// GPU (different streams, or graph branches without a dependency) would overwrite each other's partials:
+// serialise them.
+constexpr size_t kWgradStaticFloats = (size_t)4 << 20;
+static __device__ __align__(256) float g_wgrad_static_scratch[kWgradStaticFloats];
+
+constexpr int kMaxStaticDevices = 64;
+static float* g_wgrad_static_ptr[kMaxStaticDevices];   // device address of the array, per device ordinal
+static std::mutex g_wgrad_static_mu;
+
+NIDT_API int64_t nidt_conv3d_wgrad_static_capacity_floats() { return (int64_t)kWgradStaticFloats; }
+
+NIDT_API int nidt_conv3d_wgrad_tc_static(const void* dy, const void* x, float* grad, int N, int Di, int Hi, int Wi, int Cin, int Do, int Ho,
+                                         int Wo, int Cout, int k, int stride, int pad, int bw, int bh, int bd, int bn, int splits, void* stream) {
+    NIDT_REQUIRE(splits >= 1 && k >= 1 && Cout >= 1 && Cin >= 1, "conv3d_wgrad_tc_static: bad shape (splits=%d k=%d Cout=%d Cin=%d)", splits, k, Cout, Cin);
+    const int64_t need = (int64_t)splits * k * k * k * Cout * Cin;
+    NIDT_REQUIRE(need <= (int64_t)kWgradStaticFloats,
+                 "conv3d_wgrad_tc_static: needs %lld scratch floats (splits=%d x k^3=%d x Cout=%d x Cin=%d) but the built-in scratch holds %lld; "
+                 "lower `splits` or call nidt_conv3d_wgrad_tc with a caller-provided buffer",
+                 (long long)need, splits, k * k * k, Cout, Cin, (long long)kWgradStaticFloats);
+    int dev = -1;
+    NIDT_CUDA_CHECK(cudaGetDevice(&dev));
+    NIDT_REQUIRE(dev >= 0 && dev < kMaxStaticDevices, "conv3d_wgrad_tc_static: device ordinal %d out of range", dev);
+    float* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_wgrad_static_mu);
+        if (g_wgrad_static_ptr[dev] == nullptr) {
+            void* p = nullptr;
+            NIDT_CUDA_CHECK(cudaGetSymbolAddress(&p, g_wgrad_static_scratch));
+            g_wgrad_static_ptr[dev] = static_cast<float*>(p);
+        }
+        scratch = g_wgrad_static_ptr[dev];
+    }
+    return wgrad_impl(dy, x, grad, scratch, N, Di, Hi, Wi, Cin, Do, Ho, Wo, Cout, k, stride, pad, bw, bh, bd, bn, splits, stream);
+}
