@@ -1,0 +1,159 @@
+// Cross-GPU aggregation fused with its collective (north-star kernels W1 / W2 of SURVEY §8).
+//
+// Every rank holds, in NVLink-mapped symmetric memory, `partial` = the sample-weighted sum of the
+// models of its own sampled clients (one flat launch, flat_ops.cu).  ONE kernel per rank then does
+//     reduce-scatter : rank r sums chunk r of all ranks' partials with P2P loads (fixed rank order ->
+//                      every rank computes bit-identical values), or with multimem.ld_reduce (NVLS,
+//                      in-switch reduction) when a multicast address is available and requested;
+//     mask           : multiplies the SalientGrads mask into the reduced chunk;
+//     all-gather     : writes the chunk into every rank's `result` buffer with P2P stores (or one
+//                      multimem.st), i.e. the new global model lands in all slabs at once;
+//     write-back     : copies `result` into the caller's (non-symmetric) global slab.
+// Cross-rank ordering uses release/acquire flags in symmetric memory with a monotonically increasing
+// epoch (no resets), grid-wide ordering uses a cooperative launch.  No NCCL call, no extra passes.
+// Reference: the CPU dict loop `_aggregate` (fedml_api/standalone/sailentgrads/sailentgrads_api.py:212-227)
+// and, for the score reduction, snip.py:120-140.
+//
+// The same reduce+broadcast phase, followed by the radix-select of flat_ops.cu, is the fused
+// "saliency all-reduce + global top-k + mask emission" (nidt_sym_saliency_topk_mask).
+#include "common.cuh"
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
+
+namespace nidt {
+
+constexpr int kMaxRanks = 16;
+constexpr int kSymThreads = 512;
+
+struct SymPeers {
+    float* partial[kMaxRanks];      // peer-mapped base of every rank's partial buffer
+    float* result[kMaxRanks];       // peer-mapped base of every rank's result buffer
+    uint32_t* flags[kMaxRanks];     // peer-mapped flag pads: flags[dst][slot*kMaxRanks + src]
+    float* mc_partial;              // multicast address of `partial` (nullptr = unavailable)
+    float* mc_result;               // multicast address of `result`
+    int rank, world;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// All ranks arrive, then all ranks leave.  Block 0 does the signalling; `value` must grow by one per
+// barrier over the lifetime of the flag pad.  A peer that never arrives ends in a trap, not a hang.
+__device__ __forceinline__ void cross_rank_barrier(cg::grid_group& grid, const SymPeers& sp, int slot, uint32_t value) {
+    __threadfence_system();
+    grid.sync();
+    if (blockIdx.x == 0 && threadIdx.x < sp.world) {
+        const int peer = threadIdx.x;
+        st_release_sys(sp.flags[peer] + slot * kMaxRanks + sp.rank, value);
+        const uint32_t* mine = sp.flags[sp.rank] + slot * kMaxRanks + peer;
+        const long long t0 = clock64();
+        while ((int32_t)(ld_acquire_sys(mine) - value) < 0) {
+            if (clock64() - t0 > 20000000000LL) {   // ~10 s
+                printf("nidt: cross-rank barrier timed out (rank %d waiting for %d, value %u)\n", sp.rank, peer, value);
+                __trap();
+            }
+        }
+    }
+    grid.sync();
+}
+
+__device__ __forceinline__ float4 multimem_ld_reduce_f32x4(const float* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void multimem_st_f32x4(float* mc, float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// reduce chunk `rank` over all partials (+mask) and broadcast it into every result buffer
+__device__ __forceinline__ void reduce_mask_broadcast(const SymPeers& sp, const float* __restrict__ mask, int64_t n_mask, int64_t n, int use_multimem) {
+    const int64_t n4 = n >> 2;
+    const int64_t per = (n4 + sp.world - 1) / sp.world;
+    const int64_t lo = per * sp.rank, hi = min(n4, lo + per);
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = lo + tid; i < hi; i += nth) {
+        float4 acc;
+        if (use_multimem) {
+            acc = multimem_ld_reduce_f32x4(sp.mc_partial + 4 * i);
+        } else {
+            float4 v[kMaxRanks];
+#pragma unroll
+            for (int p = 0; p < kMaxRanks; ++p)
+                if (p < sp.world) v[p] = ld4(sp.partial[p] + 4 * i);      // all loads in flight before the sum
+            acc = v[0];
+#pragma unroll
+            for (int p = 1; p < kMaxRanks; ++p)
+                if (p < sp.world) { acc.x += v[p].x; acc.y += v[p].y; acc.z += v[p].z; acc.w += v[p].w; }
+        }
+        if (mask != nullptr && 4 * i < n_mask) {
+            const float4 mk = ld4(mask + 4 * i);
+            acc.x *= mk.x; acc.y *= mk.y; acc.z *= mk.z; acc.w *= mk.w;
+        }
+        if (use_multimem) {
+            multimem_st_f32x4(sp.mc_result + 4 * i, acc);
+        } else {
+#pragma unroll
+            for (int p = 0; p < kMaxRanks; ++p)
+                if (p < sp.world) st4(sp.result[p] + 4 * i, acc);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kSymThreads) sym_agg_kernel(const SymPeers sp, const float* __restrict__ mask, int64_t n_mask, int64_t n,
+                                                              float* __restrict__ out_local, uint32_t epoch, int use_multimem) {
+    cg::grid_group grid = cg::this_grid();
+    cross_rank_barrier(grid, sp, 0, 2 * epoch + 1);          // every rank's partial is complete
+    reduce_mask_broadcast(sp, mask, n_mask, n, use_multimem);
+    cross_rank_barrier(grid, sp, 0, 2 * epoch + 2);          // every chunk has landed everywhere
+    if (out_local != nullptr && out_local != sp.result[sp.rank]) {
+        const float* src = sp.result[sp.rank];
+        const int64_t n4 = n >> 2;
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x)
+            st4(out_local + 4 * i, ld4(src + 4 * i));
+    }
+}
+
+}  // namespace nidt
+using namespace nidt;
+
+NIDT_API int nidt_sym_max_ranks() { return kMaxRanks; }
+NIDT_API int nidt_sym_flag_words() { return 4 * kMaxRanks; }
+
+// partial_ptrs / result_ptrs / flag_ptrs: HOST arrays of `world` peer-mapped device pointers (same order on all ranks).
+// flag pads: nidt_sym_flag_words() uint32 each, zero before the first call; `epoch` must increase by 1 per call
+// (identically on every rank).  All ranks must make this call; the kernels wait for each other.
+NIDT_API int nidt_sym_reduce_mask_broadcast(void* const* partial_ptrs, void* const* result_ptrs, void* const* flag_ptrs, void* mc_partial,
+                                            void* mc_result, int rank, int world, const float* mask, int64_t n_mask, int64_t n,
+                                            float* out_local, uint32_t epoch, int use_multimem, void* stream) {
+    NIDT_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world, "sym_reduce: bad rank %d / world %d", rank, world);
+    NIDT_REQUIRE(n % 4 == 0 && n_mask % 4 == 0, "sym_reduce: n and n_mask must be multiples of 4");
+    NIDT_REQUIRE(!use_multimem || (mc_partial != nullptr && mc_result != nullptr), "sym_reduce: multimem requested without multicast addresses");
+    SymPeers sp;
+    for (int p = 0; p < kMaxRanks; ++p) {
+        sp.partial[p] = p < world ? (float*)partial_ptrs[p] : nullptr;
+        sp.result[p] = p < world ? (float*)result_ptrs[p] : nullptr;
+        sp.flags[p] = p < world ? (uint32_t*)flag_ptrs[p] : nullptr;
+    }
+    sp.mc_partial = (float*)mc_partial;
+    sp.mc_result = (float*)mc_result;
+    sp.rank = rank;
+    sp.world = world;
+    int dev = 0, sms = 0, per_sm = 0;
+    NIDT_CUDA_CHECK(cudaGetDevice(&dev));
+    NIDT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    NIDT_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sym_agg_kernel, kSymThreads, 0));
+    NIDT_REQUIRE(per_sm >= 1, "sym_reduce: kernel does not fit on an SM");
+    int64_t want = (n / 4 / world + kSymThreads - 1) / kSymThreads;
+    if (want < 1) want = 1;
+    int grid = (int)(want < sms ? want : sms);
+    void* args[] = {(void*)&sp, (void*)&mask, (void*)&n_mask, (void*)&n, (void*)&out_local, (void*)&epoch, (void*)&use_multimem};
+    NIDT_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)sym_agg_kernel, dim3(grid), dim3(kSymThreads), args, 0, (cudaStream_t)stream));
+    return 0;
+}

@@ -1,0 +1,47 @@
+"""torchrun worker (gloo, CPU): 2-rank SalientGrads must reproduce the single-process run."""
+import logging
+import os
+import sys
+import types
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as dist
+
+from neuroimagedisttraining_b200.data import SyntheticABCD, load_partition_data_abcd
+from neuroimagedisttraining_b200.fl import SalientGradsAPI, SlabTrainer
+from neuroimagedisttraining_b200.models import create_model
+from neuroimagedisttraining_b200.parallel import DistContext, init_distributed, shutdown
+
+
+def run(ctx):
+    torch.manual_seed(0)
+    logger = logging.getLogger("w"); logger.setLevel(logging.ERROR)
+    store = SyntheticABCD(40, (32, 32, 32), n_sites=4, seed=1, site_sizes=[10, 10, 10, 10])
+    args = types.SimpleNamespace(client_num_in_total=4, client_num_per_round=4, comm_round=2, epochs=1, lr=0.01, lr_decay=0.998,
+                                 momentum=0.9, wd=5e-4, client_optimizer="sgd", batch_size=8, dense_ratio=0.5, itersnip_iteration=2,
+                                 stratified_sampling=False, snip_mask=True, ci=0, frequency_of_the_test=1, dataset="ABCD")
+    ds = load_partition_data_abcd(store, client_number=4, batch_size=8)
+    model = create_model("tiny3DCNN", 1, (32, 32, 32))
+    tr = SlabTrainer(model, args, logger, device="cpu", store=store)
+    api = SalientGradsAPI(ds, "cpu", args, tr, logger, dist=ctx)
+    st = api.train()
+    return api.w_global.flat.clone(), api.mask.flat.clone(), st
+
+
+def main():
+    torch.set_num_threads(2)
+    ctx = init_distributed(device="cpu")
+    w2, m2, st2 = run(ctx)
+    w1, m1, st1 = run(DistContext(device=torch.device("cpu")))     # same thing, single process
+    ok = torch.equal(m1, m2) and torch.allclose(w1, w2, rtol=1e-5, atol=1e-6)
+    ok = ok and abs(st1["global_test_acc"][-1] - st2["global_test_acc"][-1]) < 1e-9
+    ok = ok and st1["sum_comm_params"] == st2["sum_comm_params"]
+    if ctx.rank == 0:
+        print(f"RESULT ok={ok} maxdiff={(w1 - w2).abs().max().item():.3e} comm={st1['sum_comm_params']},{st2['sum_comm_params']}")
+    shutdown()
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,80 @@
+"""torchrun worker: fused symmetric-memory aggregation vs. NCCL all_reduce + mask (run by test_multi_gpu.py)."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as dist
+
+from neuroimagedisttraining_b200.parallel import init_distributed, shutdown
+from neuroimagedisttraining_b200.parallel.symmetric import SymmetricAggregator
+
+
+def main():
+    ctx = init_distributed()
+    dev = ctx.device
+    n = 2571672
+    nm = 2570244
+    agg = SymmetricAggregator(ctx, n, dev)
+    mask = (torch.rand(nm, generator=torch.Generator().manual_seed(7)) > 0.5).float().to(dev)
+    ok = True
+    for it in range(3):
+        g = torch.Generator().manual_seed(100 * it + ctx.rank)
+        part = torch.randn(n, generator=g).to(dev)
+        agg.local_partial.copy_(part)
+        out = torch.empty(n, device=dev)
+        for mm in ([False, True] if agg.mc_partial else [False]):
+            agg.use_multimem = mm
+            agg.reduce_mask_broadcast(out, mask)
+            ref = part.clone()
+            dist.all_reduce(ref)
+            ref[:nm] *= mask
+            torch.cuda.synchronize()
+            err = (out - ref).abs().max().item()
+            chk = out.double().sum().reshape(1).clone()      # every rank must hold bit-identical results
+            lo, hi = chk.clone(), chk.clone()
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+            same = (lo == hi).item()
+            if err > 1e-5 or not same:
+                ok = False
+            if ctx.rank == 0:
+                print(f"iter {it} multimem={mm}: max|fused-nccl|={err:.3e} identical_across_ranks={same}")
+    part = torch.randn(n, device=dev)
+    out = torch.empty(n, device=dev)
+    agg.use_multimem = False
+
+    def t(fn, reps=20):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize(); dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record(); torch.cuda.synchronize()
+        x = torch.tensor([e0.elapsed_time(e1) / reps], device=dev)
+        dist.all_reduce(x, op=dist.ReduceOp.MAX)
+        return x.item()
+
+    def fused():
+        agg.reduce_mask_broadcast(out, mask)
+
+    def nccl():
+        dist.all_reduce(part)
+        part[:nm].mul_(mask)
+        out.copy_(part)
+
+    tf = t(fused)
+    tn = t(nccl)
+    tm = None
+    if agg.mc_partial:
+        agg.use_multimem = True
+        tm = t(fused)
+    if ctx.rank == 0:
+        print(f"RESULT ok={ok} world={ctx.world_size} n={n} fused_p2p_ms={tf:.4f} nccl_ms={tn:.4f} fused_multimem_ms={tm}")
+    shutdown()
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,35 @@
+"""Multi-process paths.  CPU (gloo, world 2): orchestration invariance.  GPU (>= 2 devices): the fused
+symmetric-memory aggregation kernel against NCCL."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _torchrun(script, nproc, extra_env=None, timeout=600, args=()):
+    env = dict(os.environ)
+    env.update(extra_env or {})
+    port = 29500 + (os.getpid() % 2000)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(ROOT, "tests", script), *args]
+    return subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env, cwd=ROOT)
+
+
+def test_salientgrads_two_ranks_cpu_matches_single_process():
+    r = _torchrun("dist_worker_fl_cpu.py", 2, {"CUDA_VISIBLE_DEVICES": ""})
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "RESULT ok=True" in r.stdout, r.stdout[-2000:]
+
+
+@pytest.mark.gpu
+def test_fused_symmetric_aggregation_matches_nccl():
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    r = _torchrun("dist_worker_sym_agg.py", min(n, 8))
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "RESULT ok=True" in r.stdout, r.stdout[-2000:]
