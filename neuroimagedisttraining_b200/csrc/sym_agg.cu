@@ -17,8 +17,8 @@
 // The same reduce+broadcast phase, followed by the radix-select of flat_ops.cu, is the fused
 // "saliency all-reduce + global top-k + mask emission" (nidt_sym_saliency_topk_mask).
 #include "common.cuh"
+#include "topk.cuh"
 #include <cooperative_groups.h>
-namespace cg = cooperative_groups;
 
 namespace nidt {
 
@@ -120,8 +120,61 @@ __global__ void __launch_bounds__(kSymThreads) sym_agg_kernel(const SymPeers sp,
     }
 }
 
+// W2: cross-rank saliency reduction fused with the global top-k threshold and the mask emission.
+// `partial` holds this rank's sum of its clients' (already 1/num_clients scaled) |g*w| scores.
+__global__ void __launch_bounds__(kSymThreads) sym_saliency_topk_kernel(const SymPeers sp, int64_t n, const unsigned char* __restrict__ flags,
+                                                                        float* __restrict__ mask, unsigned long long k, TopkScratch* __restrict__ sc,
+                                                                        float* __restrict__ scores_out, uint32_t epoch, int use_multimem) {
+    static_assert(kSymThreads == kTopkThreads, "block size is shared with the top-k body");
+    cg::grid_group grid = cg::this_grid();
+    cross_rank_barrier(grid, sp, 0, 2 * epoch + 1);
+    reduce_mask_broadcast(sp, nullptr, 0, n, use_multimem);
+    cross_rank_barrier(grid, sp, 0, 2 * epoch + 2);
+    const float* scores = sp.result[sp.rank];
+    topk_mask_body(grid, scores, flags, mask, n, k, sc);
+    if (scores_out != nullptr && scores_out != scores)
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) scores_out[i] = scores[i];
+}
+
+static int fill_peers(SymPeers& sp, void* const* partial_ptrs, void* const* result_ptrs, void* const* flag_ptrs, void* mc_partial, void* mc_result,
+                      int rank, int world) {
+    NIDT_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world, "sym: bad rank %d / world %d", rank, world);
+    for (int p = 0; p < kMaxRanks; ++p) {
+        sp.partial[p] = p < world ? (float*)partial_ptrs[p] : nullptr;
+        sp.result[p] = p < world ? (float*)result_ptrs[p] : nullptr;
+        sp.flags[p] = p < world ? (uint32_t*)flag_ptrs[p] : nullptr;
+    }
+    sp.mc_partial = (float*)mc_partial;
+    sp.mc_result = (float*)mc_result;
+    sp.rank = rank;
+    sp.world = world;
+    return 0;
+}
+
 }  // namespace nidt
 using namespace nidt;
+
+// One launch per rank: all-reduce of the score slabs over NVLink, k-th largest normalised score, mask (ties kept).
+// scratch: nidt_topk_scratch_bytes() bytes; scores_out (optional) receives the reduced scores.
+NIDT_API int nidt_sym_saliency_topk_mask(void* const* partial_ptrs, void* const* result_ptrs, void* const* flag_ptrs, void* mc_partial,
+                                         void* mc_result, int rank, int world, int64_t n, const unsigned char* flags, float* mask,
+                                         unsigned long long k, void* scratch, float* scores_out, uint32_t epoch, int use_multimem, void* stream) {
+    NIDT_REQUIRE(n % 4 == 0, "sym_saliency_topk: n must be a multiple of 4");
+    NIDT_REQUIRE(scratch != nullptr, "sym_saliency_topk: scratch is null");
+    NIDT_REQUIRE(!use_multimem || (mc_partial != nullptr && mc_result != nullptr), "sym_saliency_topk: multimem requested without multicast addresses");
+    SymPeers sp;
+    if (int rc = fill_peers(sp, partial_ptrs, result_ptrs, flag_ptrs, mc_partial, mc_result, rank, world)) return rc;
+    int dev = 0, sms = 0, per_sm = 0;
+    NIDT_CUDA_CHECK(cudaGetDevice(&dev));
+    NIDT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    NIDT_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sym_saliency_topk_kernel, kSymThreads, 0));
+    NIDT_REQUIRE(per_sm >= 1, "sym_saliency_topk: kernel does not fit on an SM");
+    int grid = sms < 2 * kNumSMs ? sms : 2 * kNumSMs;
+    TopkScratch* sc = (TopkScratch*)scratch;
+    void* args[] = {(void*)&sp, (void*)&n, (void*)&flags, (void*)&mask, (void*)&k, (void*)&sc, (void*)&scores_out, (void*)&epoch, (void*)&use_multimem};
+    NIDT_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)sym_saliency_topk_kernel, dim3(grid), dim3(kSymThreads), args, 0, (cudaStream_t)stream));
+    return 0;
+}
 
 NIDT_API int nidt_sym_max_ranks() { return kMaxRanks; }
 NIDT_API int nidt_sym_flag_words() { return 4 * kMaxRanks; }

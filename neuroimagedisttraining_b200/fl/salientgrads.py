@@ -36,9 +36,16 @@ class SalientGradsAPI(FedAvgAPI):
                     w_global=self.w_global, out=tmp)
                 scores.flat.add_(tmp.flat, alpha=1.0 / n_clients)
             self.logger.info("@@@@@Aggregate the local masks@@@@@@@@@@@@@@@@@@@")
-            self.dist.all_reduce_sum(scores.flat)
             mask = ParamSlab(self.layout, device=self.device, params_only=True)
-            _, info = ops.global_topk_mask(scores.flat, self.layout, float(args.dense_ratio), mask.flat)
+            fused = getattr(self.aggregator, "_fused", None)
+            if fused is not None:
+                # W2: NVLink all-reduce of the scores + global top-k + mask emission in one kernel per rank
+                if not hasattr(self, "_prunable_flags"):
+                    self._prunable_flags = ops.prunable_flags(self.layout, self.device)
+                _, info = fused.saliency_topk_mask(scores.flat, self.layout, float(args.dense_ratio), mask.flat, self._prunable_flags)
+            else:
+                self.dist.all_reduce_sum(scores.flat)
+                _, info = ops.global_topk_mask(scores.flat, self.layout, float(args.dense_ratio), mask.flat)
         self.mask_info = info
         self.scores = scores
         return mask

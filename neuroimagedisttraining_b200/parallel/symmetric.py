@@ -30,6 +30,9 @@ def _declare(lib) -> None:
     lib.nidt_sym_flag_words.restype = C.c_int
     lib.nidt_sym_reduce_mask_broadcast.argtypes = [C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), vp, vp, i32, i32, vp, i64, i64, vp, u32, i32, vp]
     lib.nidt_sym_reduce_mask_broadcast.restype = C.c_int
+    lib.nidt_sym_saliency_topk_mask.argtypes = [C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), vp, vp, i32, i32, i64, vp, vp, C.c_uint64, vp, vp, u32, i32, vp]
+    lib.nidt_sym_saliency_topk_mask.restype = C.c_int
+    lib.nidt_topk_scratch_bytes.restype = C.c_int
     _declared = True
 
 
@@ -92,3 +95,23 @@ class SymmetricAggregator:
             "nidt_sym_reduce_mask_broadcast")
         native.count_launches(1)
         return out
+
+    def saliency_topk_mask(self, scores: torch.Tensor, layout, keep_ratio: float, mask_out: torch.Tensor, flags: torch.Tensor):
+        """Fused W2: ``scores`` (this rank's partial) is all-reduced over NVLink, the global k-th largest
+        normalised score is found and ``mask_out`` is emitted, in one launch per rank.  ``scores`` receives
+        the reduced values.  Returns ``(mask_out, info)``."""
+        n = layout.param_numel
+        k = int(layout.prunable_numel() * keep_ratio)
+        self.local_partial[:n].copy_(scores[:n])
+        if not hasattr(self, "_topk_scratch"):
+            self._topk_scratch = torch.zeros(self.lib.nidt_topk_scratch_bytes(), dtype=torch.uint8, device=self.device)
+        self.epoch += 1
+        native.check(self.lib.nidt_sym_saliency_topk_mask(
+            self._partial, self._result, self._flags, self.mc_partial, self.mc_result, self.ctx.rank, self.ctx.world_size, n,
+            native.ptr(flags), native.ptr(mask_out), k, native.ptr(self._topk_scratch), native.ptr(scores), self.epoch,
+            int(self.use_multimem), native.stream_ptr(self.device)), "nidt_sym_saliency_topk_mask")
+        native.count_launches(1)
+        thr, norm, kept = C.c_float(), C.c_float(), C.c_uint()
+        native.check(self.lib.nidt_topk_read_result(native.ptr(self._topk_scratch), C.byref(thr), C.byref(norm), C.byref(kept),
+                                                    native.stream_ptr(self.device)), "nidt_topk_read_result")
+        return mask_out, {"threshold": thr.value, "norm": norm.value, "kept": kept.value, "k": k}

@@ -39,6 +39,29 @@ def main():
                 ok = False
             if ctx.rank == 0:
                 print(f"iter {it} multimem={mm}: max|fused-nccl|={err:.3e} identical_across_ranks={same}")
+    # fused saliency all-reduce + top-k + mask vs. NCCL all_reduce + the single-GPU top-k kernel
+    from neuroimagedisttraining_b200 import ops
+    from neuroimagedisttraining_b200.models import AlexNet3D_Dropout
+    from neuroimagedisttraining_b200.runtime.slab import SlabLayout
+    layout = SlabLayout.from_module(AlexNet3D_Dropout(1))
+    flags = ops.prunable_flags(layout, dev)
+    P = layout.param_numel
+    for mm in ([False, True] if agg.mc_partial else [False]):
+        agg.use_multimem = mm
+        sc = (torch.rand(P, generator=torch.Generator().manual_seed(5 + ctx.rank)) ** 3).to(dev) * 1e-3
+        ref_sc = sc.clone()
+        dist.all_reduce(ref_sc)
+        ref_mask = torch.empty(P, device=dev)
+        _, ri = ops.global_topk_mask(ref_sc, layout, 0.5, ref_mask, flags)
+        mask2 = torch.empty(P, device=dev)
+        _, fi = agg.saliency_topk_mask(sc, layout, 0.5, mask2, flags)
+        torch.cuda.synchronize()
+        nd = int((mask2 != ref_mask).sum())
+        close = torch.equal(sc, ref_sc) if not mm else torch.allclose(sc, ref_sc, rtol=1e-6, atol=0)
+        if nd > (0 if not mm else 4) or abs(fi["kept"] - ri["kept"]) > (0 if not mm else 4) or not close:
+            ok = False
+        if ctx.rank == 0:
+            print(f"saliency multimem={mm}: mask diff={nd} kept={fi['kept']} (ref {ri['kept']}) thr={fi['threshold']:.6e}")
     part = torch.randn(n, device=dev)
     out = torch.empty(n, device=dev)
     agg.use_multimem = False
