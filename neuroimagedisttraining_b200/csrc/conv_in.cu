@@ -33,52 +33,79 @@ constexpr int kT16 = 16384;           // one [128 rows][64 bf16] swizzled sub-ti
 
 __device__ __forceinline__ void named_bar(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 
-// ---- stage the u8 input patch of one tile as normalised bf16: patch[KS][PH][PW]
-// pad == 0: the PH input rows of a plane are one contiguous byte run -> (1) aligned 16-byte copies into a raw
-// u8 buffer, (2) a conversion pass in which consecutive lanes handle consecutive 4-element groups (conflict-free
-// 8-byte shared stores).  Patch rows past the volume are zero.  pad != 0: element-wise gather with bounds checks.
-template <int KS, int PHT, int PWT, int ST>
-__device__ __forceinline__ void stage_patch(const uint8_t* __restrict__ x, uint8_t* __restrict__ raw, __nv_bfloat16* __restrict__ patch,
-                                            const InConvGeom& g, int n, int d, int h0, int gt, int bar_id) {
-    const int PH = PHT ? PHT : g.PH, PW = PWT ? PWT : g.PW;
-    const int stride = ST ? ST : g.stride;      // ST != 0 also promises pad == 0
-    const int z0 = d * stride - g.pad, y0 = h0 * stride - g.pad;
-    if (ST != 0 || g.pad == 0) {
-        const int rows = min(PH, g.Hi - y0);
-        const int bytes = rows * g.Wi;
-        const int nv = g.raw_pitch >> 4;
-        for (int v = gt; v < KS * nv; v += 128) {
-            const int plane = v / nv, vi = v - plane * nv;
-            const uint8_t* src = x + (((size_t)n * g.Di + z0 + plane) * g.Hi + y0) * g.Wi;
-            const int mis = (int)(reinterpret_cast<uintptr_t>(src) & 15);
-            if (vi * 16 - mis < bytes)
-                *reinterpret_cast<uint4*>(raw + plane * g.raw_pitch + vi * 16) = __ldg(reinterpret_cast<const uint4*>(src - mis) + vi);
-        }
-        named_bar(bar_id, 128);
-        const int QW = PW >> 2;
-        for (int item = gt; item < KS * PH * QW; item += 128) {
-            const int R = item / QW, q = item - R * QW;
-            const int plane = R / PH, hr = R - plane * PH;
-            const uint8_t* src = x + (((size_t)n * g.Di + z0 + plane) * g.Hi + y0) * g.Wi;
-            const int mis = (int)(reinterpret_cast<uintptr_t>(src) & 15);
-            const int o = hr * g.Wi + 4 * q;                 // offset of the group's first byte within the run
-            const int a = plane * g.raw_pitch + mis + o;     // its address in the raw buffer
-            const uint32_t* rw = reinterpret_cast<const uint32_t*>(raw + (a & ~3));
-            const uint32_t four = __funnelshift_r(rw[0], rw[1], (a & 3) * 8);
-            float f[4];
+// ---- staging of the u8 input patch of one tile as normalised bf16: patch[KS][PH][PW]
+// pad == 0 (ST != 0 promises it): the PH input rows of a plane are one contiguous byte run.  It is fetched with
+// aligned 16-byte loads into REGISTERS one tile ahead (raw_prefetch), parked in a raw u8 smem buffer (raw_store)
+// and converted by a pass in which consecutive lanes handle consecutive 4-element groups (conflict-free 8-byte
+// shared stores).  Patch rows past the volume are zero.  pad != 0: element-wise gather with bounds checks.
+constexpr int kRawVecs = 3;   // 16-byte vectors per builder thread and tile (KS * raw_pitch / 16 <= 128 * kRawVecs)
+
+__device__ __forceinline__ const uint8_t* plane_src(const uint8_t* __restrict__ x, const InConvGeom& g, int n, int z, int y0) {
+    return x + (((size_t)n * g.Di + z) * g.Hi + y0) * g.Wi;
+}
+
+template <int KS, int ST>
+__device__ __forceinline__ void raw_prefetch(const uint8_t* __restrict__ x, const InConvGeom& g, int n, int d, int h0, int gt, uint4 (&q)[kRawVecs]) {
+    const int stride = ST ? ST : g.stride;
+    const int z0 = d * stride, y0 = h0 * stride;
+    const int bytes = min(g.PH, g.Hi - y0) * g.Wi;
+    const int nv = g.raw_pitch >> 4;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const bool ok = hr < rows && 4 * q + i < g.Wi;
-                f[i] = ok ? (float)((four >> (8 * i)) & 0xffu) * g.scale : 0.f;
-            }
-            __nv_bfloat162 p0 = __floats2bfloat162_rn(f[0], f[1]), p1 = __floats2bfloat162_rn(f[2], f[3]);
-            uint2 o2;
-            o2.x = *reinterpret_cast<uint32_t*>(&p0);
-            o2.y = *reinterpret_cast<uint32_t*>(&p1);
-            *reinterpret_cast<uint2*>(patch + R * PW + 4 * q) = o2;
+    for (int j = 0; j < kRawVecs; ++j) {
+        const int v = gt + j * 128;
+        q[j] = make_uint4(0, 0, 0, 0);
+        if (v < KS * nv) {
+            const int plane = v / nv, vi = v - plane * nv;
+            const uint8_t* src = plane_src(x, g, n, z0 + plane, y0);
+            const int mis = (int)(reinterpret_cast<uintptr_t>(src) & 15);
+            if (vi * 16 - mis < bytes) q[j] = __ldg(reinterpret_cast<const uint4*>(src - mis) + vi);
         }
-        return;
     }
+}
+
+template <int KS>
+__device__ __forceinline__ void raw_store(uint8_t* __restrict__ raw, const InConvGeom& g, int gt, const uint4 (&q)[kRawVecs]) {
+    const int nv = g.raw_pitch >> 4;
+#pragma unroll
+    for (int j = 0; j < kRawVecs; ++j) {
+        const int v = gt + j * 128;
+        if (v < KS * nv) reinterpret_cast<uint4*>(raw)[v] = q[j];     // raw[plane][vi] with pitch nv vectors == linear index v
+    }
+}
+
+template <int KS, int PHT, int PWT, int ST>
+__device__ __forceinline__ void convert_patch(const uint8_t* __restrict__ x, const uint8_t* __restrict__ raw, __nv_bfloat16* __restrict__ patch,
+                                              const InConvGeom& g, int n, int d, int h0, int gt) {
+    const int PH = PHT ? PHT : g.PH, PW = PWT ? PWT : g.PW;
+    const int stride = ST ? ST : g.stride;
+    const int z0 = d * stride, y0 = h0 * stride;
+    const int rows = min(PH, g.Hi - y0);
+    const int QW = PW >> 2;
+    for (int item = gt; item < KS * PH * QW; item += 128) {
+        const int R = item / QW, q = item - R * QW;
+        const int plane = R / PH, hr = R - plane * PH;
+        const int mis = (int)(reinterpret_cast<uintptr_t>(plane_src(x, g, n, z0 + plane, y0)) & 15);
+        const int a = plane * g.raw_pitch + mis + hr * g.Wi + 4 * q;     // address of the group's first byte in the raw buffer
+        const uint32_t* rw = reinterpret_cast<const uint32_t*>(raw + (a & ~3));
+        const uint32_t four = __funnelshift_r(rw[0], rw[1], (a & 3) * 8);
+        float f[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const bool ok = hr < rows && 4 * q + i < g.Wi;
+            f[i] = ok ? (float)((four >> (8 * i)) & 0xffu) * g.scale : 0.f;
+        }
+        __nv_bfloat162 p0 = __floats2bfloat162_rn(f[0], f[1]), p1 = __floats2bfloat162_rn(f[2], f[3]);
+        uint2 o2;
+        o2.x = *reinterpret_cast<uint32_t*>(&p0);
+        o2.y = *reinterpret_cast<uint32_t*>(&p1);
+        *reinterpret_cast<uint2*>(patch + R * PW + 4 * q) = o2;
+    }
+}
+
+template <int KS, int PHT, int PWT, int ST>
+__device__ __forceinline__ void gather_patch(const uint8_t* __restrict__ x, __nv_bfloat16* __restrict__ patch, const InConvGeom& g, int n, int d, int h0, int gt) {
+    const int PH = PHT ? PHT : g.PH, PW = PWT ? PWT : g.PW;
+    const int z0 = d * g.stride - g.pad, y0 = h0 * g.stride - g.pad;
     const int total = KS * PH * PW;
     for (int idx = gt; idx < total; idx += 128) {
         const int w = idx % PW;
@@ -160,7 +187,9 @@ __device__ __forceinline__ void decode_tile(const InConvGeom& g, int tile, int& 
 
 __device__ __forceinline__ int patch_elems(const InConvGeom& g, int ks) { return (ks * g.PH * g.PW + 7) & ~7; }
 
-// builder warps (0-7): two groups of 128 threads alternate tiles; group `grp` owns A tile / patch / raw buffer `grp`
+// builder warps (0-7): two groups of 128 threads alternate tiles; group `grp` owns A tile / patch / raw buffer `grp`.
+// Software pipeline per group: the global loads of the group's NEXT tile are in flight while the current tile is
+// converted and built, and the A tile is only waited for (MMA of two tiles ago finished) right before it is rewritten.
 template <int KS, int PHT, int PWT, int ST>
 __device__ __forceinline__ void builder_loop(const uint8_t* __restrict__ x, const InConvGeom& g, uint8_t* a_tiles, uint8_t* raws, __nv_bfloat16* patches,
                                              uint64_t* a_full, uint64_t* a_empty) {
@@ -168,18 +197,36 @@ __device__ __forceinline__ void builder_loop(const uint8_t* __restrict__ x, cons
     __nv_bfloat16* patch = patches + grp * patch_elems(g, KS);
     uint8_t* raw = raws + grp * KS * g.raw_pitch;
     uint8_t* a_tile = a_tiles + grp * 2 * kT16;
-    for (int i = grp;; i += 2) {
-        const int tile = blockIdx.x + i * gridDim.x;
-        if (tile >= g.total_tiles) break;
-        const uint32_t u = i >> 1;
-        int n, d, h0, valid;
+    const bool fast = (ST != 0) || (g.pad == 0 && KS * (g.raw_pitch >> 4) <= 128 * kRawVecs);
+    uint4 q[kRawVecs];
+    int n, d, h0, valid;
+    int tile = blockIdx.x + grp * gridDim.x;
+    if (fast && tile < g.total_tiles) {
         decode_tile(g, tile, n, d, h0, valid);
-        tc::mbar_wait(&a_empty[grp], (u & 1) ^ 1);
-        stage_patch<KS, PHT, PWT, ST>(x, raw, patch, g, n, d, h0, gt, 1 + grp);
+        raw_prefetch<KS, ST>(x, g, n, d, h0, gt, q);
+    }
+    for (int i = grp; tile < g.total_tiles; i += 2) {
+        const uint32_t u = i >> 1;
+        decode_tile(g, tile, n, d, h0, valid);
+        const int next = tile + 2 * gridDim.x;
+        if (fast) {
+            raw_store<KS>(raw, g, gt, q);
+            named_bar(1 + grp, 128);
+            if (next < g.total_tiles) {
+                int n2, d2, h2, v2;
+                decode_tile(g, next, n2, d2, h2, v2);
+                raw_prefetch<KS, ST>(x, g, n2, d2, h2, gt, q);
+            }
+            convert_patch<KS, PHT, PWT, ST>(x, raw, patch, g, n, d, h0, gt);
+        } else {
+            gather_patch<KS, PHT, PWT, ST>(x, patch, g, n, d, h0, gt);
+        }
         named_bar(1 + grp, 128);
+        tc::mbar_wait(&a_empty[grp], (u & 1) ^ 1);
         build_row<KS, PHT, PWT, ST>(patch, g, valid, a_tile, gt);
         tc::fence_proxy_async_smem();
         tc::mbar_arrive(&a_full[grp]);
+        tile = next;
     }
 }
 

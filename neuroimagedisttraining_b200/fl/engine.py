@@ -101,10 +101,13 @@ class TorchEngine:
         loss.backward()
         return loss.detach()
 
-    def train_step(self, x, y, hp: StepHParams, mask: Optional[torch.Tensor], mom: Optional[torch.Tensor], first_step: bool) -> None:
+    def train_step(self, x, y, hp: StepHParams, mask: Optional[torch.Tensor], mom: Optional[torch.Tensor], first_step: bool,
+                   grad_mask: Optional[torch.Tensor] = None) -> None:
         loss = self.compute_grads(x, y, train_mode=True)
         self.loss_acc += loss
         self.loss_steps += 1
+        if grad_mask is not None:      # Sub-FedAvg masks the gradient before clipping (subavg/my_model_trainer.py:66-68)
+            self.grad.flat.mul_(grad_mask)
         ops.masked_sgd_step(self.slab.params_flat, self.grad.flat, mom, mask, hp.lr, hp.momentum, hp.wd, hp.clip_norm, first_step)
 
     def pop_mean_loss(self) -> float:

@@ -217,9 +217,10 @@ class SlabTrainer(ModelTrainer):
         losses = []
         for epoch in range(int(epochs if epochs is not None else args.epochs)):
             for x, y in self._batches(train_data):
-                if grad_mask and mask_flat is not None:
-                    self.engine.grad_mask = mask_flat
-                self.engine.train_step(x, y, hp, mask_flat, mom, first)
+                if grad_mask:
+                    self.engine.train_step(x, y, hp, None, mom, first, grad_mask=mslab.flat if mslab is not None else None)
+                else:
+                    self.engine.train_step(x, y, hp, mask_flat, mom, first)
                 if prox_ref is not None and lamda != 0:
                     ops.prox_pull(self.slab.params_flat, prox_ref.params_flat, hp.lr, lamda)
                 first = False

@@ -55,6 +55,10 @@ def _declare(lib) -> None:
     _declared = True
 
 
+import functools
+
+
+@functools.lru_cache(maxsize=None)
 def choose_box(W: int, H: int, D: int, N: int, max_rows: int = 128) -> Tuple[int, int, int, int]:
     """Box of output positions (bw,bh,bd,bn), bw*bh*bd*bn <= 128, maximising tensor-core row use:
     valid positions / (tiles * 128).  Ties prefer wider (more contiguous) boxes."""
@@ -321,9 +325,12 @@ class B200Engine:
         self.step += 1
         return self.loss_acc
 
-    def train_step(self, x, y, hp, mask: Optional[torch.Tensor], mom: Optional[torch.Tensor], first_step: bool) -> None:
+    def train_step(self, x, y, hp, mask: Optional[torch.Tensor], mom: Optional[torch.Tensor], first_step: bool,
+                   grad_mask: Optional[torch.Tensor] = None) -> None:
         self.compute_grads(x, y, True)
         self.loss_steps += 1
+        if grad_mask is not None:
+            self.grad.flat.mul_(grad_mask)
         flat_ops.masked_sgd_step(self.slab.params_flat, self.grad.flat, mom, mask, hp.lr, hp.momentum, hp.wd, hp.clip_norm, first_step)
         self._packed_dirty = True
 
