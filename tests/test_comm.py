@@ -1,0 +1,64 @@
+"""Message-passing runtime: in-process and gRPC transports, and FedAvg over messages == the slab aggregation."""
+import threading
+import time
+
+import pytest
+import torch
+
+from neuroimagedisttraining_b200 import ops
+from neuroimagedisttraining_b200.comm import (FedAvgClientManager, FedAvgServerManager, GrpcCommManager, InProcessCommManager, Message,
+                                              MqttCommManager)
+
+
+def test_message_roundtrip():
+    m = Message("t", 1, 2)
+    m.add_params("w", {"a": torch.arange(6).float().view(2, 3)})
+    m2 = Message.from_bytes(m.to_bytes())
+    assert m2.get_type() == "t" and m2.get_sender_id() == 1 and m2.get_receiver_id() == 2
+    assert torch.equal(m2.get("w")["a"], m.get("w")["a"])
+    assert '"a": [[0.0, 1.0, 2.0]' in m.to_json()
+
+
+def _run_fedavg(make_comm, n_clients=3, rounds=2):
+    torch.manual_seed(0)
+    state = {"w": torch.randn(50), "b": torch.randn(5)}
+    ns = [3, 5, 9][:n_clients]
+
+    def train_fn(i):
+        def fn(sd):
+            return ns[i], {k: v + (i + 1) * 0.1 for k, v in sd.items()}
+        return fn
+    size = n_clients + 1
+    server = FedAvgServerManager(state, rounds, comm=make_comm(0, size), rank=0, size=size)
+    clients = [FedAvgClientManager(train_fn(i), comm=make_comm(i + 1, size), rank=i + 1, size=size) for i in range(n_clients)]
+    threads = [threading.Thread(target=m.run, daemon=True) for m in [server] + clients]
+    for t in threads:
+        t.start()
+    time.sleep(0.2)
+    server.start()
+    assert server.done.wait(30)
+    for t in threads:
+        t.join(10)
+    # expected: every round adds sum_i n_i/N * (i+1)*0.1
+    delta = sum(n * (i + 1) * 0.1 for i, n in enumerate(ns)) / sum(ns)
+    for k in state:
+        torch.testing.assert_close(server.state[k], state[k] + rounds * delta, rtol=1e-5, atol=1e-6)
+        torch.testing.assert_close(clients[0].final_state[k], server.state[k])
+
+
+def test_fedavg_over_inprocess_messages():
+    _run_fedavg(lambda r, s: InProcessCommManager(r, s, network="t1"))
+
+
+def test_fedavg_over_grpc_loopback():
+    pytest.importorskip("grpc")
+    _run_fedavg(lambda r, s: GrpcCommManager("127.0.0.1", 52310, r, s), n_clients=2, rounds=1)
+
+
+def test_mqtt_backend_reports_missing_dependency():
+    try:
+        import paho.mqtt.client  # noqa: F401
+        pytest.skip("paho-mqtt is installed")
+    except ImportError:
+        with pytest.raises(ImportError, match="paho-mqtt"):
+            MqttCommManager("127.0.0.1", 1883, 0, 1)
