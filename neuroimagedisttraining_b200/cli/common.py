@@ -1,0 +1,165 @@
+"""Shared pieces of the experiment entry points (reference: ``fedml_experiments/standalone/<algo>/main_<algo>.py``):
+argument groups with the reference's flag names and defaults, the ``identity`` string that names
+logs / results, seeding, data + model + trainer construction, and the B200 extras
+(``--engine``, ``--agg``, ``--resume``, ``--checkpoint_every``, ``--synthetic_subjects`` ...)."""
+from __future__ import annotations
+
+import argparse
+import os
+import random
+from typing import Optional
+
+import numpy as np
+import torch
+
+from ..data import (SyntheticABCD, HDF5VolumeStore, load_partition_data_abcd, load_partition_data_abcd_rescale,
+                    load_partition_data_images)
+from ..fl import SlabTrainer
+from ..models import create_model
+from ..parallel import init_distributed
+from ..utils.logger import logger_config, JsonlMetrics
+
+
+def str2bool(v) -> bool:
+    """The reference declares ``--snip_mask type=bool`` (any non-empty string is True, ``main_sailentgrads.py:125``);
+    this accepts the usual spellings instead."""
+    if isinstance(v, bool):
+        return v
+    return str(v).lower() in ("1", "true", "t", "yes", "y")
+
+
+def add_common_args(p: argparse.ArgumentParser, *, model="3DCNN", dataset="ABCD", lr=0.01, epochs=2, frac=1.0, clients=4,
+                    comm_round=200, seed=1024, batch_size=16) -> argparse.ArgumentParser:
+    p.add_argument("--model", type=str, default=model, metavar="N", help="network architecture: 3DCNN, 3DResNet, tiny3DCNN, resnet18, vgg11, cnn_cifar10, ...")
+    p.add_argument("--dataset", type=str, default=dataset, metavar="N", help="ABCD | cifar10 | cifar100 | tiny")
+    p.add_argument("--data_dir", type=str, default=None, help="HDF5 file (ABCD) or dataset directory; omitted -> synthetic data")
+    p.add_argument("--partition_method", type=str, default="dir", metavar="N", help="site (ABCD) | dir | n_cls | my_part | homo | hetero")
+    p.add_argument("--partition_alpha", type=float, default=0.3, metavar="PA")
+    p.add_argument("--batch_size", type=int, default=batch_size, metavar="N")
+    p.add_argument("--client_optimizer", type=str, default="sgd")
+    p.add_argument("--lr", type=float, default=lr, metavar="LR")
+    p.add_argument("--lr_decay", type=float, default=0.998, metavar="LR_decay")
+    p.add_argument("--wd", type=float, default=5e-4)
+    p.add_argument("--epochs", type=int, default=epochs, metavar="EP")
+    p.add_argument("--client_num_in_total", type=int, default=clients, metavar="NN")
+    p.add_argument("--frac", type=float, default=frac, metavar="NN")
+    p.add_argument("--momentum", type=float, default=0, metavar="NN")
+    p.add_argument("--comm_round", type=int, default=comm_round)
+    p.add_argument("--frequency_of_the_test", type=int, default=1)
+    p.add_argument("--gpu", type=int, default=0)
+    p.add_argument("--ci", type=int, default=0)
+    p.add_argument("--seed", type=int, default=seed)
+    p.add_argument("--tag", type=str, default="test")
+    p.add_argument("--logfile", type=str, default="logfile")
+    # ---- additions of this framework
+    g = p.add_argument_group("b200")
+    g.add_argument("--engine", default="auto", choices=["auto", "b200", "torch"], help="compute engine (auto: sm_100a kernels when the model has a plan)")
+    g.add_argument("--agg", default="auto", choices=["auto", "fused", "nccl"], help="cross-rank aggregation: fused symmetric-memory kernel or NCCL baseline")
+    g.add_argument("--device", default=None, help="cpu | cuda (default: cuda if available)")
+    g.add_argument("--resume", default=None, help="checkpoint to resume from")
+    g.add_argument("--checkpoint_path", default=None)
+    g.add_argument("--checkpoint_every", type=int, default=0, help="save every k rounds (0 = never)")
+    g.add_argument("--log_dir", default="LOG")
+    g.add_argument("--results_dir", default="results")
+    g.add_argument("--synthetic_subjects", type=int, default=0, help="ABCD without --data_dir: number of synthetic subjects (default 20 per client)")
+    g.add_argument("--in_shape", default="121,145,121", help="volume shape D,H,W")
+    g.add_argument("--rescale", action="store_true", help="ABCD: cut the site-ordered data into client_num_in_total equal shards")
+    g.add_argument("--correct_eval_loss", action="store_true", help="evaluate BCEWithLogits(logit) instead of the reference's BCEWithLogits(sigmoid(logit))")
+    return p
+
+
+def add_sparse_args(p: argparse.ArgumentParser, cs="v0") -> argparse.ArgumentParser:
+    p.add_argument("--dense_ratio", type=float, default=0.5, help="fraction of weights KEPT (90%% sparsity = 0.1)")
+    p.add_argument("--anneal_factor", type=float, default=0.5)
+    p.add_argument("--cs", type=str, default=cs)
+    p.add_argument("--active", type=float, default=1.0)
+    p.add_argument("--public_portion", type=float, default=0)
+    p.add_argument("--erk_power_scale", type=float, default=1)
+    p.add_argument("--dis_gradient_check", action="store_true")
+    p.add_argument("--strict_avg", action="store_true")
+    p.add_argument("--static", action="store_true")
+    p.add_argument("--uniform", action="store_true")
+    p.add_argument("--save_masks", action="store_true")
+    p.add_argument("--different_initial", action="store_true")
+    p.add_argument("--record_mask_diff", action="store_true")
+    p.add_argument("--diff_spa", action="store_true")
+    p.add_argument("--global_test", action="store_true")
+    return p
+
+
+def seed_everything(seed: int) -> None:
+    """np seed fixes the partition, torch seed the initial weights (``main_sailentgrads.py:264-268``)."""
+    random.seed(seed)
+    np.random.seed(seed)
+    torch.manual_seed(seed)
+    if torch.cuda.is_available():
+        torch.cuda.manual_seed_all(seed)
+
+
+def build_identity(args, prefix: str, extra: Optional[list] = None) -> str:
+    part = args.partition_method if args.partition_method == "homo" else args.partition_method + str(args.partition_alpha)
+    ident = f"{prefix}-{args.dataset}-{part}-mdl{args.model}"
+    for e in (extra or []):
+        ident += e
+    ident += f"-cm{args.comm_round}-total_clnt{args.client_num_in_total}-neighbor{args.client_num_per_round}"
+    if hasattr(args, "dense_ratio"):
+        ident += f"-dr{args.dense_ratio}"
+    if hasattr(args, "active"):
+        ident += f"-active{args.active}"
+    ident += f"-seed{args.seed}-lr{args.lr}-batchsize{args.batch_size}"
+    return ident
+
+
+def setup(args, prefix: str, extra_identity: Optional[list] = None, loss_kind: Optional[str] = None, val_split: float = 0.0):
+    """-> (ctx, device, logger, dataset 8-tuple, trainer).  Everything an entry point needs before building its API."""
+    args.client_num_per_round = int(args.client_num_in_total * args.frac)
+    args.identity = build_identity(args, prefix, extra_identity)
+    ctx = init_distributed(device=args.device)
+    device = ctx.device
+    log_path = os.path.join(args.log_dir, args.dataset, args.identity + (f".rank{ctx.rank}" if ctx.rank else "") + ".log")
+    logger = logger_config(log_path=log_path, logging_name=args.identity, console=ctx.is_main)
+    logger.info(args)
+    logger.info(device)
+    seed_everything(args.seed)
+    in_shape = tuple(int(s) for s in args.in_shape.split(","))
+    store = None
+    if args.dataset == "ABCD":
+        if args.data_dir:
+            store = HDF5VolumeStore(args.data_dir)
+        else:
+            n = args.synthetic_subjects or 20 * args.client_num_in_total
+            n_sites = args.client_num_in_total if not args.rescale else min(21, args.client_num_in_total)
+            store = SyntheticABCD(n, shape=in_shape, n_sites=n_sites, seed=args.seed, pin=device.type == "cuda")
+        loader = load_partition_data_abcd_rescale if args.rescale else load_partition_data_abcd
+        dataset = loader(store, args.partition_method, args.partition_alpha, args.client_num_in_total, args.batch_size, logger, seed=args.seed)
+        class_num, loss_kind = 1, loss_kind or "bce"
+    else:
+        dataset = load_partition_data_images(args.dataset, args.data_dir, args.partition_method if args.partition_method != "site" else "dir",
+                                             args.partition_alpha, args.client_num_in_total, args.batch_size, logger, seed=args.seed, val_split=val_split)
+        class_num, loss_kind = {"cifar10": 10, "cifar100": 100, "tiny": 200}[args.dataset], loss_kind or "ce"
+    model = create_model(args.model, class_num, in_shape, args.dataset)
+    logger.info(model)
+    engine = None
+    if device.type == "cuda" and args.engine in ("auto", "b200") and store is not None:
+        try:
+            from ..ops.engine_b200 import B200Engine
+            engine = B200Engine(model, device, max_batch=args.batch_size, input_scale=store.scale, seed=args.seed)
+        except ImportError as e:
+            if args.engine == "b200":
+                raise
+            logger.info(f"native engine unavailable for {args.model}: {e}; using the PyTorch engine for forward/backward")
+    trainer = SlabTrainer(model, args, logger, device=device, store=store, engine=engine, loss_kind=loss_kind)
+    trainer.double_sigmoid_eval = not args.correct_eval_loss
+    return ctx, device, logger, dataset, trainer
+
+
+def finish(api, args, logger, ctx) -> dict:
+    stat = api.finalize_stats() if "phase_time_s" not in api.stat_info else api.stat_info
+    if ctx.is_main:
+        JsonlMetrics(os.path.join(args.log_dir, args.dataset, args.identity + ".jsonl")).write(
+            identity=args.identity, global_test_acc=[float(x) for x in stat.get("global_test_acc", [])],
+            person_test_acc=[float(x) for x in stat.get("person_test_acc", [])], sum_comm_params=int(stat.get("sum_comm_params", 0)),
+            sum_training_flops=float(stat.get("sum_training_flops", 0)), phase_time_s=stat.get("phase_time_s"))
+        logger.info({"sum_comm_params": stat.get("sum_comm_params"), "sum_training_flops": stat.get("sum_training_flops"),
+                     "phase_time_s": stat.get("phase_time_s")})
+    return stat

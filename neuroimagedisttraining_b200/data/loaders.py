@@ -157,9 +157,13 @@ def load_partition_data_images(dataset: str, data_dir: Optional[str], partition_
     n_cls = {"cifar10": 10, "cifar100": 100, "tiny": 200}[dataset]
     shape = (3, 64, 64) if dataset == "tiny" else (3, 32, 32)
     try:
-        if data_dir is None or dataset == "tiny":
+        if data_dir is None:
             raise FileNotFoundError
-        (xtr, ytr), (xte, yte) = _load_torchvision(dataset, data_dir)
+        if dataset == "tiny":
+            from .tiny_imagenet import TinyImageNet
+            (xtr, ytr), (xte, yte) = TinyImageNet(data_dir, True).tensors(), TinyImageNet(data_dir, False).tensors()
+        else:
+            (xtr, ytr), (xte, yte) = _load_torchvision(dataset, data_dir)
     except Exception:
         (xtr, ytr), (xte, yte) = synthetic_image_dataset(synthetic_size[0], synthetic_size[1], n_cls, shape, seed)
     ytr_np, yte_np = ytr.numpy(), yte.numpy()
