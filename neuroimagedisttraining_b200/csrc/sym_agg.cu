@@ -45,9 +45,11 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
 
 // All ranks arrive, then all ranks leave.  Block 0 does the signalling; `value` must grow by one per
 // barrier over the lifetime of the flag pad.  A peer that never arrives ends in a trap, not a hang.
-__device__ __forceinline__ void cross_rank_barrier(cg::grid_group& grid, const SymPeers& sp, int slot, uint32_t value) {
-    __threadfence_system();
-    grid.sync();
+__device__ __forceinline__ void cross_rank_barrier(cg::grid_group& grid, const SymPeers& sp, int slot, uint32_t value, bool order_prior_writes = true) {
+    if (order_prior_writes) {      // entry barrier of a kernel: the data it publishes was written by earlier launches on this stream
+        __threadfence_system();
+        grid.sync();
+    }
     if (blockIdx.x == 0 && threadIdx.x < sp.world) {
         const int peer = threadIdx.x;
         st_release_sys(sp.flags[peer] + slot * kMaxRanks + sp.rank, value);
@@ -72,45 +74,80 @@ __device__ __forceinline__ void multimem_st_f32x4(float* mc, float4 v) {
     asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
-// reduce chunk `rank` over all partials (+mask) and broadcast it into every result buffer
-__device__ __forceinline__ void reduce_mask_broadcast(const SymPeers& sp, const float* __restrict__ mask, int64_t n_mask, int64_t n, int use_multimem) {
+// reduce chunk `rank` over all partials (+mask) and broadcast it into every result buffer.
+// kWorld (2/4/8/16 >= world) bounds the registers; two 16-byte vectors per thread and iteration are in flight per peer.
+template <int kWorld>
+__device__ __forceinline__ void reduce_mask_broadcast_p2p(const SymPeers& sp, const float* __restrict__ mask, int64_t n_mask, int64_t n) {
     const int64_t n4 = n >> 2;
     const int64_t per = (n4 + sp.world - 1) / sp.world;
     const int64_t lo = per * sp.rank, hi = min(n4, lo + per);
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = lo + tid; i < hi; i += nth) {
-        float4 acc;
-        if (use_multimem) {
-            acc = multimem_ld_reduce_f32x4(sp.mc_partial + 4 * i);
-        } else {
-            float4 v[kMaxRanks];
+    constexpr int kVec = kWorld <= 4 ? 2 : 1;       // keep <= 64 registers so two CTAs fit per SM
+    for (int64_t i0 = lo + tid; i0 < hi; i0 += kVec * nth) {
+        const int64_t i1 = i0 + nth;
+        const bool two = kVec == 2 && i1 < hi;
+        float4 a[kWorld], b[kWorld];
 #pragma unroll
-            for (int p = 0; p < kMaxRanks; ++p)
-                if (p < sp.world) v[p] = ld4(sp.partial[p] + 4 * i);      // all loads in flight before the sum
-            acc = v[0];
+        for (int p = 0; p < kWorld; ++p)
+            if (p < sp.world) {
+                a[p] = ld4(sp.partial[p] + 4 * i0);
+                if (two) b[p] = ld4(sp.partial[p] + 4 * i1);
+            }
+        float4 s0 = a[0], s1 = two ? b[0] : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-            for (int p = 1; p < kMaxRanks; ++p)
-                if (p < sp.world) { acc.x += v[p].x; acc.y += v[p].y; acc.z += v[p].z; acc.w += v[p].w; }
+        for (int p = 1; p < kWorld; ++p)
+            if (p < sp.world) {
+                s0.x += a[p].x; s0.y += a[p].y; s0.z += a[p].z; s0.w += a[p].w;
+                if (two) { s1.x += b[p].x; s1.y += b[p].y; s1.z += b[p].z; s1.w += b[p].w; }
+            }
+        if (mask != nullptr) {
+            if (4 * i0 < n_mask) { const float4 mk = ld4(mask + 4 * i0); s0.x *= mk.x; s0.y *= mk.y; s0.z *= mk.z; s0.w *= mk.w; }
+            if (two && 4 * i1 < n_mask) { const float4 mk = ld4(mask + 4 * i1); s1.x *= mk.x; s1.y *= mk.y; s1.z *= mk.z; s1.w *= mk.w; }
         }
-        if (mask != nullptr && 4 * i < n_mask) {
-            const float4 mk = ld4(mask + 4 * i);
-            acc.x *= mk.x; acc.y *= mk.y; acc.z *= mk.z; acc.w *= mk.w;
-        }
-        if (use_multimem) {
-            multimem_st_f32x4(sp.mc_result + 4 * i, acc);
-        } else {
 #pragma unroll
-            for (int p = 0; p < kMaxRanks; ++p)
-                if (p < sp.world) st4(sp.result[p] + 4 * i, acc);
+        for (int p = 0; p < kWorld; ++p)
+            if (p < sp.world) {
+                st4(sp.result[p] + 4 * i0, s0);
+                if (two) st4(sp.result[p] + 4 * i1, s1);
+            }
+    }
+}
+
+__device__ __forceinline__ void reduce_mask_broadcast_multimem(const SymPeers& sp, const float* __restrict__ mask, int64_t n_mask, int64_t n) {
+    const int64_t n4 = n >> 2;
+    const int64_t per = (n4 + sp.world - 1) / sp.world;
+    const int64_t lo = per * sp.rank, hi = min(n4, lo + per);
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
+    constexpr int U = 4;
+    for (int64_t i = lo + tid; i < hi; i += U * nth) {
+        float4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (i + u * nth < hi) v[u] = multimem_ld_reduce_f32x4(sp.mc_partial + 4 * (i + u * nth));
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t j = i + u * nth;
+            if (j < hi) {
+                if (mask != nullptr && 4 * j < n_mask) { const float4 mk = ld4(mask + 4 * j); v[u].x *= mk.x; v[u].y *= mk.y; v[u].z *= mk.z; v[u].w *= mk.w; }
+                multimem_st_f32x4(sp.mc_result + 4 * j, v[u]);
+            }
         }
     }
 }
 
-__global__ void __launch_bounds__(kSymThreads) sym_agg_kernel(const SymPeers sp, const float* __restrict__ mask, int64_t n_mask, int64_t n,
-                                                              float* __restrict__ out_local, uint32_t epoch, int use_multimem) {
+// kWorld == 0 selects the NVLS multimem path
+template <int kWorld>
+__device__ __forceinline__ void reduce_mask_broadcast(const SymPeers& sp, const float* __restrict__ mask, int64_t n_mask, int64_t n) {
+    if constexpr (kWorld == 0) reduce_mask_broadcast_multimem(sp, mask, n_mask, n);
+    else reduce_mask_broadcast_p2p<kWorld>(sp, mask, n_mask, n);
+}
+
+template <int kWorld>
+__global__ void __launch_bounds__(kSymThreads, kWorld <= 8 ? 2 : 1) sym_agg_kernel(const SymPeers sp, const float* __restrict__ mask, int64_t n_mask, int64_t n,
+                                                                                   float* __restrict__ out_local, uint32_t epoch) {
     cg::grid_group grid = cg::this_grid();
-    cross_rank_barrier(grid, sp, 0, 2 * epoch + 1);          // every rank's partial is complete
-    reduce_mask_broadcast(sp, mask, n_mask, n, use_multimem);
+    cross_rank_barrier(grid, sp, 0, 2 * epoch + 1, false);   // every rank's partial is complete
+    reduce_mask_broadcast<kWorld>(sp, mask, n_mask, n);
     cross_rank_barrier(grid, sp, 0, 2 * epoch + 2);          // every chunk has landed everywhere
     if (out_local != nullptr && out_local != sp.result[sp.rank]) {
         const float* src = sp.result[sp.rank];
@@ -122,13 +159,14 @@ __global__ void __launch_bounds__(kSymThreads) sym_agg_kernel(const SymPeers sp,
 
 // W2: cross-rank saliency reduction fused with the global top-k threshold and the mask emission.
 // `partial` holds this rank's sum of its clients' (already 1/num_clients scaled) |g*w| scores.
+template <int kWorld>
 __global__ void __launch_bounds__(kSymThreads) sym_saliency_topk_kernel(const SymPeers sp, int64_t n, const unsigned char* __restrict__ flags,
                                                                         float* __restrict__ mask, unsigned long long k, TopkScratch* __restrict__ sc,
-                                                                        float* __restrict__ scores_out, uint32_t epoch, int use_multimem) {
+                                                                        float* __restrict__ scores_out, uint32_t epoch) {
     static_assert(kSymThreads == kTopkThreads, "block size is shared with the top-k body");
     cg::grid_group grid = cg::this_grid();
-    cross_rank_barrier(grid, sp, 0, 2 * epoch + 1);
-    reduce_mask_broadcast(sp, nullptr, 0, n, use_multimem);
+    cross_rank_barrier(grid, sp, 0, 2 * epoch + 1, false);
+    reduce_mask_broadcast<kWorld>(sp, nullptr, 0, n);
     cross_rank_barrier(grid, sp, 0, 2 * epoch + 2);
     const float* scores = sp.result[sp.rank];
     topk_mask_body(grid, scores, flags, mask, n, k, sc);
@@ -151,6 +189,21 @@ static int fill_peers(SymPeers& sp, void* const* partial_ptrs, void* const* resu
     return 0;
 }
 
+static const void* pick_agg_kernel(int world, int use_multimem) {
+    if (use_multimem) return (const void*)sym_agg_kernel<0>;
+    if (world <= 2) return (const void*)sym_agg_kernel<2>;
+    if (world <= 4) return (const void*)sym_agg_kernel<4>;
+    if (world <= 8) return (const void*)sym_agg_kernel<8>;
+    return (const void*)sym_agg_kernel<16>;
+}
+static const void* pick_topk_kernel(int world, int use_multimem) {
+    if (use_multimem) return (const void*)sym_saliency_topk_kernel<0>;
+    if (world <= 2) return (const void*)sym_saliency_topk_kernel<2>;
+    if (world <= 4) return (const void*)sym_saliency_topk_kernel<4>;
+    if (world <= 8) return (const void*)sym_saliency_topk_kernel<8>;
+    return (const void*)sym_saliency_topk_kernel<16>;
+}
+
 }  // namespace nidt
 using namespace nidt;
 
@@ -167,12 +220,13 @@ NIDT_API int nidt_sym_saliency_topk_mask(void* const* partial_ptrs, void* const*
     int dev = 0, sms = 0, per_sm = 0;
     NIDT_CUDA_CHECK(cudaGetDevice(&dev));
     NIDT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    NIDT_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sym_saliency_topk_kernel, kSymThreads, 0));
+    const void* kern = pick_topk_kernel(world, use_multimem);
+    NIDT_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kSymThreads, 0));
     NIDT_REQUIRE(per_sm >= 1, "sym_saliency_topk: kernel does not fit on an SM");
     int grid = sms < 2 * kNumSMs ? sms : 2 * kNumSMs;
     TopkScratch* sc = (TopkScratch*)scratch;
-    void* args[] = {(void*)&sp, (void*)&n, (void*)&flags, (void*)&mask, (void*)&k, (void*)&sc, (void*)&scores_out, (void*)&epoch, (void*)&use_multimem};
-    NIDT_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)sym_saliency_topk_kernel, dim3(grid), dim3(kSymThreads), args, 0, (cudaStream_t)stream));
+    void* args[] = {(void*)&sp, (void*)&n, (void*)&flags, (void*)&mask, (void*)&k, (void*)&sc, (void*)&scores_out, (void*)&epoch};
+    NIDT_CUDA_CHECK(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(kSymThreads), args, 0, (cudaStream_t)stream));
     return 0;
 }
 
@@ -201,12 +255,14 @@ NIDT_API int nidt_sym_reduce_mask_broadcast(void* const* partial_ptrs, void* con
     int dev = 0, sms = 0, per_sm = 0;
     NIDT_CUDA_CHECK(cudaGetDevice(&dev));
     NIDT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    NIDT_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sym_agg_kernel, kSymThreads, 0));
+    const void* kern = pick_agg_kernel(world, use_multimem);
+    NIDT_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kSymThreads, 0));
     NIDT_REQUIRE(per_sm >= 1, "sym_reduce: kernel does not fit on an SM");
-    int64_t want = (n / 4 / world + kSymThreads - 1) / kSymThreads;
+    int64_t want = (n / 4 / world + 2 * kSymThreads - 1) / (2 * kSymThreads);
     if (want < 1) want = 1;
-    int grid = (int)(want < sms ? want : sms);
-    void* args[] = {(void*)&sp, (void*)&mask, (void*)&n_mask, (void*)&n, (void*)&out_local, (void*)&epoch, (void*)&use_multimem};
-    NIDT_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)sym_agg_kernel, dim3(grid), dim3(kSymThreads), args, 0, (cudaStream_t)stream));
+    const int cap = sms * (per_sm > 2 ? 2 : per_sm);
+    int grid = (int)(want < cap ? want : cap);
+    void* args[] = {(void*)&sp, (void*)&mask, (void*)&n_mask, (void*)&n, (void*)&out_local, (void*)&epoch};
+    NIDT_CUDA_CHECK(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(kSymThreads), args, 0, (cudaStream_t)stream));
     return 0;
 }
