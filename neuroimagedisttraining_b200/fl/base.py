@@ -113,8 +113,8 @@ class FedAPIBase:
         n = self.args.client_num_in_total
         acc = np.zeros(n)
         loss = np.zeros(n)
-        for cid in client_ids:
-            m = self.client_list[cid].local_test(slabs[cid], True)
+        results = self.model_trainer.test_many([(slabs[cid], self.client_list[cid].local_test_data) for cid in client_ids])
+        for cid, m in zip(client_ids, results):
             tot = max(m["test_total"], 1.0)
             acc[cid] = m["test_correct"] / tot
             loss[cid] = m["test_loss"] / tot

@@ -124,6 +124,53 @@ class SlabTrainer(ModelTrainer):
             for batch in data:
                 yield batch[0], batch[1]
 
+    def _batches_epochs(self, data, epochs: int):
+        """``(epoch, x, y)`` over ``epochs`` passes of ``data`` as ONE staged stream."""
+        if self.store is not None and hasattr(data, "indices"):
+            tags = []
+
+            def index_stream():
+                for e in range(epochs):
+                    for b in data:
+                        tags.append(e)
+                        yield b
+            for i, (x, y) in enumerate(self._stager(data.batch_size).iterate(index_stream())):
+                yield tags[i], x, y
+        else:
+            for e in range(epochs):
+                for batch in data:
+                    yield e, batch[0], batch[1]
+
+    def test_many(self, jobs):
+        """Evaluate ``[(slab, loader), ...]`` back to back as one staged stream (the copy of the next client's test
+        batch overlaps the current forward pass).  Returns one metrics dict per job."""
+        jobs = list(jobs)
+        if not jobs:
+            return []
+        if not (self.store is not None and all(hasattr(l, "indices") for _, l in jobs)):
+            out = []
+            for slab, loader in jobs:
+                self.attach(slab)
+                out.append(self.test(loader))
+            return out
+        bs = max(l.batch_size for _, l in jobs)
+        tags = []
+
+        def index_stream():
+            for j, (_, loader) in enumerate(jobs):
+                for b in loader:
+                    tags.append(j)
+                    yield b
+        counters = [EvalCounters(self.device) for _ in jobs]
+        cur = -1
+        for i, (x, y) in enumerate(self._stager(bs).iterate(index_stream())):
+            j = tags[i]
+            if j != cur:
+                self.attach(jobs[j][0])
+                cur = j
+            self.engine.eval_batch(x, y, counters[j], double_sigmoid=self.double_sigmoid_eval)
+        return [c.result() for c in counters]
+
     def mask_slab(self, masks: MaskLike) -> Optional[ParamSlab]:
         if masks is None or isinstance(masks, ParamSlab):
             return masks
@@ -215,20 +262,30 @@ class SlabTrainer(ModelTrainer):
         mom = self.mom.flat if hp.momentum != 0 else None
         first = True
         losses = []
-        for epoch in range(int(epochs if epochs is not None else args.epochs)):
-            for x, y in self._batches(train_data):
-                if grad_mask:
-                    self.engine.train_step(x, y, hp, None, mom, first, grad_mask=mslab.flat if mslab is not None else None)
-                else:
-                    self.engine.train_step(x, y, hp, mask_flat, mom, first)
-                if prox_ref is not None and lamda != 0:
-                    ops.prox_pull(self.slab.params_flat, prox_ref.params_flat, hp.lr, lamda)
-                first = False
-                self.step_counter += 1
+        n_epochs = int(epochs if epochs is not None else args.epochs)
+
+        def end_epoch(epoch):
             mean_loss = self.engine.pop_mean_loss()
             losses.append(mean_loss)
             if self.logger is not None:
                 self.logger.info('Client Index = {}\tEpoch: {}\tLoss: {:.6f}'.format(self.id, epoch, mean_loss))
+
+        # all epochs are one batch stream, so the host->device prefetch runs across epoch boundaries
+        cur = 0
+        for epoch, x, y in self._batches_epochs(train_data, n_epochs):
+            if epoch != cur:
+                end_epoch(cur)
+                cur = epoch
+            if grad_mask:
+                self.engine.train_step(x, y, hp, None, mom, first, grad_mask=mslab.flat if mslab is not None else None)
+            else:
+                self.engine.train_step(x, y, hp, mask_flat, mom, first)
+            if prox_ref is not None and lamda != 0:
+                ops.prox_pull(self.slab.params_flat, prox_ref.params_flat, hp.lr, lamda)
+            first = False
+            self.step_counter += 1
+        if n_epochs > 0:
+            end_epoch(cur)
         return losses
 
     # --------------------------------------------------------------------------- test
