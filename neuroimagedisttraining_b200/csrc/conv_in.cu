@@ -88,12 +88,14 @@ __device__ __forceinline__ void convert_patch(const uint8_t* __restrict__ x, con
         const int a = plane * g.raw_pitch + mis + hr * g.Wi + 4 * q;     // address of the group's first byte in the raw buffer
         const uint32_t* rw = reinterpret_cast<const uint32_t*>(raw + (a & ~3));
         const uint32_t four = __funnelshift_r(rw[0], rw[1], (a & 3) * 8);
+        // u8 -> float without the slow I2F path: float(0x4B000000 | b) - 2^23 == b exactly
+        const int nvalid = hr < rows ? min(4, max(0, g.Wi - 4 * q)) : 0;
+        const uint32_t fm = four & (nvalid >= 4 ? 0xffffffffu : ((1u << (8 * nvalid)) - 1u));
         float f[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const bool ok = hr < rows && 4 * q + i < g.Wi;
-            f[i] = ok ? (float)((four >> (8 * i)) & 0xffu) * g.scale : 0.f;
-        }
+        f[0] = (__uint_as_float(__byte_perm(fm, 0x4B000000u, 0x7650)) - 8388608.f) * g.scale;
+        f[1] = (__uint_as_float(__byte_perm(fm, 0x4B000000u, 0x7651)) - 8388608.f) * g.scale;
+        f[2] = (__uint_as_float(__byte_perm(fm, 0x4B000000u, 0x7652)) - 8388608.f) * g.scale;
+        f[3] = (__uint_as_float(__byte_perm(fm, 0x4B000000u, 0x7653)) - 8388608.f) * g.scale;
         __nv_bfloat162 p0 = __floats2bfloat162_rn(f[0], f[1]), p1 = __floats2bfloat162_rn(f[2], f[3]);
         uint2 o2;
         o2.x = *reinterpret_cast<uint32_t*>(&p0);

@@ -1,0 +1,494 @@
+// First-layer convolution (1 -> 64 channels, 5x5x5, stride 2, no padding) with ZERO im2col work.
+//
+// Space-to-depth view: a stride-2 5^3 convolution over a 1-channel volume is a stride-1 3^3 convolution over the
+// 8-channel "parity" volume  s2d[z'][y'][x'][c = (pz,py,px)] = x[2z'+pz][2y'+py][2x'+px]  (taps with k = 5 get weight 0).
+// One s2d position is 8 bf16 = 16 bytes = exactly one UMMA core-matrix row of the no-swizzle K-major layout, and
+// consecutive output columns are consecutive s2d positions.  So a shared-memory line  line[x'][8ch]  (pitch 64
+// positions = 1 KiB) can be handed to tcgen05.mma directly: the descriptor's row stride is the 16-byte position
+// stride, and the K chunk stride (LBO) is ALSO 16 bytes -- chunk 1 of row r is row r+1's data, which is precisely the
+// shifted tap (jx+1).  Lines of consecutive y' are consecutive in memory, so rows 64..127 of the M=128 tile are the
+// next output line.  Per 2x59-output tile: 18 MMAs read 12 staged lines; no thread ever gathers an im2col row.
+//   fprop : D[pos][co]      = sum_{jd,jh,jw} line(jd,jh)[pos+jw][c] * Ws2d[co][(jd,jh,jw),c]
+//   wgrad : D[co][jw*8+c]   = sum_pos dY[pos][co] * line(jd,jh)[pos+jw][c]      (9 accumulators, one per (jd,jh))
+// The staging warps only convert the 8-bit volume (u8 * scale -> bf16) into parity-interleaved lines.
+// Reference op: nn.Conv3d(1,64,5,stride=2) + its weight gradient, fedml_api/model/cv/salient_models.py:147 (cuDNN fp32).
+#include "tc_common.cuh"
+
+namespace nidt {
+namespace s2d {
+
+struct Geom {
+    int N, Di, Hi, Wi;     // u8 input volume
+    int Do, Ho, Wo;        // output extents ((Di-5)/2+1 ...), Wo <= 62
+    int h_tiles;           // ceil(Ho / 2): a tile is 2 output lines
+    int total_tiles;       // N * Do * h_tiles
+    int raw_pitch;         // bytes per plane of the raw staging buffer (8 input rows + misalignment, multiple of 16)
+    float scale;
+};
+
+constexpr int kThreads = 13 * 32;        // wgrad: warps 0-3 / 4-7 staging groups, warp 8 MMA, warps 9-12 TMA + final epilogue
+constexpr int kFpThreads = 17 * 32;      // fprop: ... warps 9-12 / 13-16 = two epilogue groups (tile i -> group i & 1)
+constexpr int kLineBytes = 64 * 16;      // one s2d line: 64 positions x 8 bf16
+constexpr int kLines = 12;               // 3 jd planes x 4 y' lines
+constexpr int kABytes = kLines * kLineBytes + 256;   // + tail so that row 127 + 3 positions stays inside the buffer
+constexpr int kPlanes = 6, kRows = 8;    // raw input planes / rows per tile
+constexpr int kRawVecs = 3;
+constexpr int kT16 = 16384;
+
+__device__ __forceinline__ void named_bar(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+
+// no-swizzle descriptor (layout type 0): LBO = stride between the two K chunks (K-major) / between K groups (MN-major),
+// SBO = stride between 8-row groups (K-major) / between MN chunks (MN-major)
+__device__ __forceinline__ uint64_t desc_noswz(uint32_t addr, uint32_t lbo, uint32_t sbo) {
+    uint64_t d = 0;
+    d |= (uint64_t)((addr >> 4) & 0x3FFF);
+    d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
+    d |= (uint64_t)1 << 46;
+    return d;
+}
+
+__device__ __forceinline__ void decode_tile(const Geom& g, int tile, int& n, int& d, int& h0, int& lines) {
+    const int ht = tile % g.h_tiles;
+    const int t2 = tile / g.h_tiles;
+    d = t2 % g.Do;
+    n = t2 / g.Do;
+    h0 = ht * 2;
+    lines = min(2, g.Ho - h0);
+}
+
+__device__ __forceinline__ const uint8_t* plane_src(const uint8_t* __restrict__ x, const Geom& g, int n, int z, int y0) {
+    return x + (((size_t)n * g.Di + z) * g.Hi + y0) * g.Wi;
+}
+
+// global -> registers: the 8 input rows of each of the 6 planes are one contiguous byte run per plane
+__device__ __forceinline__ void raw_prefetch(const uint8_t* __restrict__ x, const Geom& g, int n, int d, int h0, int gt, uint4 (&q)[kRawVecs]) {
+    const int z0 = 2 * d, y0 = 2 * h0;
+    const int bytes = min(kRows, g.Hi - y0) * g.Wi;
+    const int nv = g.raw_pitch >> 4;
+#pragma unroll
+    for (int j = 0; j < kRawVecs; ++j) {
+        const int v = gt + j * 128;
+        q[j] = make_uint4(0, 0, 0, 0);
+        if (v < kPlanes * nv) {
+            const int plane = v / nv, vi = v - plane * nv;
+            if (z0 + plane < g.Di) {
+                const uint8_t* src = plane_src(x, g, n, z0 + plane, y0);
+                const int mis = (int)(reinterpret_cast<uintptr_t>(src) & 15);
+                if (vi * 16 - mis < bytes) q[j] = __ldg(reinterpret_cast<const uint4*>(src - mis) + vi);
+            }
+        }
+    }
+}
+__device__ __forceinline__ void raw_store(uint8_t* __restrict__ raw, const Geom& g, int gt, const uint4 (&q)[kRawVecs]) {
+    const int nv = g.raw_pitch >> 4;
+#pragma unroll
+    for (int j = 0; j < kRawVecs; ++j) {
+        const int v = gt + j * 128;
+        if (v < kPlanes * nv) reinterpret_cast<uint4*>(raw)[v] = q[j];
+    }
+}
+
+// raw u8 rows -> 12 parity-interleaved bf16 lines.  One item = TWO adjacent s2d positions (32 bytes): for each of the
+// 4 (pd,ph) input rows one unaligned 4-byte read (two aligned words + funnel shift) yields x[4i .. 4i+3]; bytes become
+// floats without the slow I2F path: float(0x4B000000 | b) - 2^23 = b exactly (one PRMT + one FADD), then the scale multiply.
+__device__ __forceinline__ void build_lines(const uint8_t* __restrict__ x, const uint8_t* __restrict__ raw, uint8_t* __restrict__ a_buf,
+                                            const Geom& g, int n, int d, int h0, int gt) {
+    const int z0 = 2 * d, y0 = 2 * h0;
+    const int rows_ok = min(kRows, g.Hi - y0);
+    const int planes_ok = min(kPlanes, g.Di - z0);
+    const uint32_t mis0 = (uint32_t)(reinterpret_cast<uintptr_t>(plane_src(x, g, n, z0, y0)) & 15);
+    const uint32_t psz = (uint32_t)((size_t)g.Hi * g.Wi) & 15u;       // plane-to-plane change of the 16-byte misalignment
+#pragma unroll 1
+    for (int item = gt; item < kLines * 32; item += 128) {
+        const int i4 = item & 31, L = item >> 5;          // 4-byte group within the row, line (jd*4 + hl)
+        const int jd = L >> 2, hl = L & 3;
+        const int nvalid = min(4, max(0, g.Wi - 4 * i4));
+        const uint32_t bmask = nvalid >= 4 ? 0xffffffffu : ((1u << (8 * nvalid)) - 1u);
+        uint32_t lo[4], hi[4];
+#pragma unroll
+        for (int pp = 0; pp < 4; ++pp) {                   // pp = pd*2 + ph  -> channels (pd,ph,0), (pd,ph,1)
+            const int plane = 2 * jd + (pp >> 1), row = 2 * hl + (pp & 1);
+            uint32_t four = 0;
+            if (plane < planes_ok && row < rows_ok) {
+                const uint32_t a = plane * g.raw_pitch + ((mis0 + plane * psz) & 15u) + row * g.Wi + 4 * i4;
+                const uint32_t* rw = reinterpret_cast<const uint32_t*>(raw + (a & ~3u));
+                four = __funnelshift_r(rw[0], rw[1], (a & 3u) * 8) & bmask;
+            }
+            const float f0 = (__uint_as_float(__byte_perm(four, 0x4B000000u, 0x7650)) - 8388608.f) * g.scale;
+            const float f1 = (__uint_as_float(__byte_perm(four, 0x4B000000u, 0x7651)) - 8388608.f) * g.scale;
+            const float f2 = (__uint_as_float(__byte_perm(four, 0x4B000000u, 0x7652)) - 8388608.f) * g.scale;
+            const float f3 = (__uint_as_float(__byte_perm(four, 0x4B000000u, 0x7653)) - 8388608.f) * g.scale;
+            __nv_bfloat162 p0 = __floats2bfloat162_rn(f0, f1), p1 = __floats2bfloat162_rn(f2, f3);
+            lo[pp] = *reinterpret_cast<uint32_t*>(&p0);
+            hi[pp] = *reinterpret_cast<uint32_t*>(&p1);
+        }
+        uint4* dst = reinterpret_cast<uint4*>(a_buf + L * kLineBytes + i4 * 32);
+        dst[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        dst[1] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    }
+}
+
+// staging warps (0-7): two groups alternate tiles; the next tile's global loads are in flight while the current one is built
+__device__ __forceinline__ void staging_loop(const uint8_t* __restrict__ x, const Geom& g, uint8_t* a_bufs, uint8_t* raws, uint64_t* a_full, uint64_t* a_empty) {
+    const int grp = threadIdx.x >> 7, gt = threadIdx.x & 127;
+    uint8_t* raw = raws + grp * kPlanes * g.raw_pitch;
+    uint8_t* a_buf = a_bufs + grp * kABytes;
+    uint4 q[kRawVecs];
+    int n, d, h0, lines;
+    int tile = blockIdx.x + grp * gridDim.x;
+    if (tile < g.total_tiles) {
+        decode_tile(g, tile, n, d, h0, lines);
+        raw_prefetch(x, g, n, d, h0, gt, q);
+    }
+    for (int i = grp; tile < g.total_tiles; i += 2) {
+        const uint32_t u = i >> 1;
+        decode_tile(g, tile, n, d, h0, lines);
+        const int next = tile + 2 * gridDim.x;
+        raw_store(raw, g, gt, q);
+        named_bar(1 + grp, 128);
+        if (next < g.total_tiles) {
+            int n2, d2, h2, l2;
+            decode_tile(g, next, n2, d2, h2, l2);
+            raw_prefetch(x, g, n2, d2, h2, gt, q);
+        }
+        tc::mbar_wait(&a_empty[grp], (u & 1) ^ 1);      // the MMAs of this group's previous tile have read the lines
+        build_lines(x, raw, a_buf, g, n, d, h0, gt);
+        tc::fence_proxy_async_smem();
+        tc::mbar_arrive(&a_full[grp]);
+        named_bar(1 + grp, 128);                         // raw is rewritten at the top of the next iteration
+        tile = next;
+    }
+}
+
+// ======================================================================================= fprop
+__global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                                                              const __grid_constant__ CUtensorMap tm_y, float* __restrict__ stats_partials, const Geom g) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    if ((tc::smem_u32(smem) & 1023u) != 0u) __trap();
+    uint8_t* staging = smem;                              // [2][128 rows][128 B] swizzled (TMA store source), one per epilogue group
+    uint8_t* b_tile = staging + 2 * kT16;                 // [36 K-chunks][64 co][16 B]  (no swizzle)
+    uint8_t* a_bufs = b_tile + 36 * 1024;                 // [2][kABytes]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(a_bufs + 2 * kABytes);
+    uint64_t *a_full = bars, *a_empty = bars + 2, *t_full = bars + 4, *t_empty = bars + 6;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 8);
+    float* sbias = reinterpret_cast<float*>(tmem_ptr + 4);    // [64]
+    float* red = sbias + 64;                                   // [2 groups][16 parts][2][64]
+    uint8_t* raws = reinterpret_cast<uint8_t*>(red + 2 * 16 * 2 * 64);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    // s2d weights: chunk kc = ((jd*3+jh)*4 + jw), channel c = pd*4+ph*2+pw  ->  W[co][2jd+pd][2jh+ph][2jw+pw] (0 when a tap index is 5+)
+    for (int idx = threadIdx.x; idx < 36 * 64 * 8; idx += kFpThreads) {
+        const int c = idx & 7, co = (idx >> 3) & 63, kc = idx >> 9;
+        const int jw = kc & 3, jh = (kc >> 2) % 3, jd = (kc >> 2) / 3;
+        const int kd = 2 * jd + (c >> 2), kh = 2 * jh + ((c >> 1) & 1), kw = 2 * jw + (c & 1);
+        const float v = (kd < 5 && kh < 5 && kw < 5) ? w[co * 125 + (kd * 5 + kh) * 5 + kw] : 0.f;
+        reinterpret_cast<__nv_bfloat16*>(b_tile)[idx] = __float2bfloat16(v);
+    }
+    for (int i = threadIdx.x; i < 2 * kABytes / 16; i += kFpThreads) reinterpret_cast<uint4*>(a_bufs)[i] = make_uint4(0, 0, 0, 0);
+    if (threadIdx.x < 64) sbias[threadIdx.x] = bias != nullptr ? bias[threadIdx.x] : 0.f;
+    tc::fence_proxy_async_smem();
+    if (threadIdx.x == 0) {
+        tc::tma_prefetch_desc(&tm_y);
+        for (int i = 0; i < 2; ++i) {
+            tc::mbar_init(&a_full[i], 128); tc::mbar_init(&a_empty[i], 1);
+            tc::mbar_init(&t_full[i], 1);   tc::mbar_init(&t_empty[i], 128);
+        }
+        tc::mbar_fence_init();
+    }
+    if (warp == 8) tc::tmem_alloc<128>(tmem_ptr);
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp < 8) {
+        staging_loop(x, g, a_bufs, raws, a_full, a_empty);
+    } else if (warp == 8) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = tc::make_idesc_bf16(128, 64, 0, 0);
+            const uint32_t b_addr = tc::smem_u32(b_tile);
+            for (int i = 0;; ++i) {
+                const int tile = blockIdx.x + i * gridDim.x;
+                if (tile >= g.total_tiles) break;
+                const int b = i & 1;
+                const uint32_t u = i >> 1;
+                tc::mbar_wait(&a_full[b], u & 1);
+                tc::mbar_wait(&t_empty[b], (u & 1) ^ 1);
+                tc::tc_fence_after();
+                const uint32_t a_addr = tc::smem_u32(a_bufs + b * kABytes);
+#pragma unroll
+                for (int t = 0; t < 9; ++t) {            // (jd, jh)
+                    const int jd = t / 3, jh = t % 3;
+#pragma unroll
+                    for (int pr = 0; pr < 2; ++pr) {     // K = 16: taps (jw, jw+1) = 2 consecutive positions, LBO = 16 B
+                        const uint64_t da = desc_noswz(a_addr + (jd * 4 + jh) * kLineBytes + pr * 32, 16, 128);
+                        const uint64_t db = desc_noswz(b_addr + (t * 4 + pr * 2) * 1024, 1024, 128);
+                        tc::umma_bf16(tmem_base + b * 64, da, db, idesc, (t | pr) != 0);
+                    }
+                }
+                tc::umma_commit(&a_empty[b]);
+                tc::umma_commit(&t_full[b]);
+            }
+        }
+    } else {
+        // ===== two epilogue groups; group e handles tiles i with (i & 1) == e: accumulator e, staging buffer e =====
+        const int e = (warp - 9) >> 2;
+        const int q = warp & 3;                          // TMEM lane quarter of this warp
+        const int row = q * 32 + lane;                   // row r = line*64 + w
+        const int et = (threadIdx.x - 9 * 32) & 127;
+        const int c8 = et & 7, part = et >> 3;           // stats: 16-byte channel chunk, row residue mod 16
+        uint8_t* stg = staging + e * kT16;
+        float s1[8], s2[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s1[j] = s2[j] = 0.f;
+        for (int i = e;; i += 2) {
+            const int tile = blockIdx.x + i * gridDim.x;
+            if (tile >= g.total_tiles) break;
+            const uint32_t u = i >> 1;
+            int n, d, h0, lines;
+            decode_tile(g, tile, n, d, h0, lines);
+            if (et == 0) tc::tma_store_wait_read();      // this group's previous store has drained the staging buffer
+            named_bar(3 + e, 128);
+            tc::mbar_wait(&t_full[e], u & 1);
+            tc::tc_fence_after();
+            {
+                float v[64];
+                tc::tmem_ld64(tmem_base + e * 64 + ((uint32_t)(q * 32) << 16), v);
+                tc::tc_fence_before();
+                tc::mbar_arrive(&t_empty[e]);            // accumulator is in registers: the next MMA may start
+                uint8_t* blk = stg + row * 128;
+#pragma unroll
+                for (int c = 0; c < 64; c += 8) {
+                    const float4 b0 = *reinterpret_cast<const float4*>(sbias + c), b1 = *reinterpret_cast<const float4*>(sbias + c + 4);
+                    uint4 o;
+                    __nv_bfloat162* ob = reinterpret_cast<__nv_bfloat162*>(&o);
+                    ob[0] = __floats2bfloat162_rn(v[c] + b0.x, v[c + 1] + b0.y);
+                    ob[1] = __floats2bfloat162_rn(v[c + 2] + b0.z, v[c + 3] + b0.w);
+                    ob[2] = __floats2bfloat162_rn(v[c + 4] + b1.x, v[c + 5] + b1.y);
+                    ob[3] = __floats2bfloat162_rn(v[c + 6] + b1.z, v[c + 7] + b1.w);
+                    *reinterpret_cast<uint4*>(blk + (((c >> 3) ^ (row & 7)) << 4)) = o;
+                }
+            }
+            tc::fence_proxy_async_smem();
+            named_bar(3 + e, 128);
+            if (et == 0) {
+                tc::tma_store_5d(&tm_y, stg, 0, 0, h0, d, n);
+                if (lines == 2) tc::tma_store_5d(&tm_y, stg + 64 * 128, 0, 0, h0 + 1, d, n);
+                tc::tma_store_commit();
+            }
+            if (stats_partials != nullptr) {
+                // 16-byte shared loads: thread (c8, part) sums 8 channels over rows w = part, part+16, ... of each line
+                for (int ln = 0; ln < lines; ++ln) {
+#pragma unroll 2
+                    for (int wq = part; wq < g.Wo; wq += 16) {
+                        const int r = ln * 64 + wq;
+                        const uint4 pk = *reinterpret_cast<const uint4*>(stg + r * 128 + ((c8 ^ (r & 7)) << 4));
+                        const __nv_bfloat162* pb = reinterpret_cast<const __nv_bfloat162*>(&pk);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const float2 f = __bfloat1622float2(pb[j]);
+                            s1[2 * j] += f.x; s1[2 * j + 1] += f.y;
+                            s2[2 * j] = fmaf(f.x, f.x, s2[2 * j]); s2[2 * j + 1] = fmaf(f.y, f.y, s2[2 * j + 1]);
+                        }
+                    }
+                }
+            }
+        }
+        if (et == 0) tc::tma_store_wait_read();
+        if (stats_partials != nullptr) {
+            float* rd = red + (e * 16 + part) * 128;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { rd[c8 * 8 + j] = s1[j]; rd[64 + c8 * 8 + j] = s2[j]; }
+        }
+    }
+    tc::tc_fence_before();
+    __syncthreads();
+    if (stats_partials != nullptr && threadIdx.x < 128) {      // fixed-order reduction over 2 groups x 16 parts
+        float acc = 0.f;
+        for (int p = 0; p < 32; ++p) acc += red[p * 128 + threadIdx.x];
+        stats_partials[(size_t)blockIdx.x * 128 + threadIdx.x] = acc;
+    }
+    if (warp == 8) {
+        tc::tc_fence_after();
+        tc::tmem_dealloc<128>(tmem_base);
+    }
+}
+
+// ======================================================================================= wgrad
+// D_t[co][jw*8 + c] (t = (jd,jh), 9 accumulators of 32 columns) += dY^T[co][pos] * line_t[pos + jw][c]
+__global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __restrict__ x, const __grid_constant__ CUtensorMap tm_dy,
+                                                            float* __restrict__ partials /* [grid][9][64][32] */, const Geom g) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    if ((tc::smem_u32(smem) & 1023u) != 0u) __trap();
+    uint8_t* dy_tiles = smem;                              // [2][128 pos][64 co] swizzled; rows 59..63 / 123..127 stay zero
+    uint8_t* a_bufs = dy_tiles + 2 * kT16;                 // [2][kABytes] s2d lines
+    uint64_t* bars = reinterpret_cast<uint64_t*>(a_bufs + 2 * kABytes);
+    uint64_t *a_full = bars, *a_empty = bars + 2, *dy_full = bars + 4, *t_full = bars + 6;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 8);
+    uint8_t* raws = reinterpret_cast<uint8_t*>(tmem_ptr + 4);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    for (int i = threadIdx.x; i < (2 * kT16 + 2 * kABytes) / 16; i += kThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+    tc::fence_proxy_async_smem();
+    if (threadIdx.x == 0) {
+        tc::tma_prefetch_desc(&tm_dy);
+        for (int i = 0; i < 2; ++i) { tc::mbar_init(&a_full[i], 128); tc::mbar_init(&a_empty[i], 1); tc::mbar_init(&dy_full[i], 1); }
+        tc::mbar_init(t_full, 1);
+        tc::mbar_fence_init();
+    }
+    if (warp == 8) tc::tmem_alloc<512>(tmem_ptr);
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp < 8) {
+        staging_loop(x, g, a_bufs, raws, a_full, a_empty);
+    } else if (warp == 8) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = tc::make_idesc_bf16(128, 32, 1, 1);
+            int i = 0;
+            for (;; ++i) {
+                const int tile = blockIdx.x + i * gridDim.x;
+                if (tile >= g.total_tiles) break;
+                const int b = i & 1;
+                const uint32_t u = i >> 1;
+                tc::mbar_wait(&a_full[b], u & 1);
+                tc::mbar_wait(&dy_full[b], u & 1);
+                tc::tc_fence_after();
+                const uint32_t dy_addr = tc::smem_u32(dy_tiles + b * kT16);
+                const uint32_t a_addr = tc::smem_u32(a_bufs + b * kABytes);
+#pragma unroll 1
+                for (int ks = 0; ks < 8; ++ks) {          // 16 positions per MMA
+                    // A = dY^T, MN-major SW128: M chunk 1 (rows 64..127 of D) aliases chunk 0 (LBO = 0); K groups 1024 B apart
+                    const uint64_t da = tc::make_smem_desc_sw128(dy_addr + ks * 2048, 0, 1024);
+#pragma unroll
+                    for (int t = 0; t < 9; ++t) {
+                        const int jd = t / 3, jh = t % 3;
+                        // B = s2d lines, MN-major no swizzle: N chunks (jw) 16 B apart, K groups (8 positions) 128 B apart
+                        const uint64_t db = desc_noswz(a_addr + (jd * 4 + jh) * kLineBytes + ks * 256, 128, 16);
+                        tc::umma_bf16(tmem_base + t * 32, da, db, idesc, (i | ks) != 0);
+                    }
+                }
+                tc::umma_commit(&a_empty[b]);
+            }
+            tc::umma_commit(t_full);
+        }
+    } else {
+        if (warp == 9 && lane == 0) {
+            for (int i = 0;; ++i) {
+                const int tile = blockIdx.x + i * gridDim.x;
+                if (tile >= g.total_tiles) break;
+                const int b = i & 1;
+                const uint32_t u = i >> 1;
+                int n, d, h0, lines;
+                decode_tile(g, tile, n, d, h0, lines);
+                tc::mbar_wait(&a_empty[b], (u & 1) ^ 1);
+                // one box per output line (rows 0..Wo-1 and 64..64+Wo-1); a line past Ho is zero-filled by the hardware
+                tc::mbar_expect_tx(&dy_full[b], (uint32_t)(2 * g.Wo * 128));
+                tc::tma_load_5d(&tm_dy, &dy_full[b], dy_tiles + b * kT16, 0, 0, h0, d, n);
+                tc::tma_load_5d(&tm_dy, &dy_full[b], dy_tiles + b * kT16 + 64 * 128, 0, 0, h0 + 1, d, n);
+            }
+        }
+        __syncwarp();
+        const int q = warp & 3;
+        const int co = q * 32 + lane;                     // D rows 64..127 duplicate 0..63
+        tc::mbar_wait(t_full, 0);
+        tc::tc_fence_after();
+#pragma unroll 1
+        for (int t = 0; t < 9; ++t) {
+#pragma unroll 1
+            for (int c = 0; c < 32; c += 16) {
+                float v[16];
+                tc::tmem_ld16(tmem_base + t * 32 + c + ((uint32_t)(q * 32) << 16), v);
+                if (co < 64) {
+                    float* dst = partials + (((size_t)blockIdx.x * 9 + t) * 64 + co) * 32 + c;
+#pragma unroll
+                    for (int j = 0; j < 16; j += 4) st4(dst + j, make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]));
+                }
+            }
+        }
+    }
+    tc::tc_fence_before();
+    __syncthreads();
+    if (warp == 8) {
+        tc::tc_fence_after();
+        tc::tmem_dealloc<512>(tmem_base);
+    }
+}
+
+// dW[co][kd][kh][kw] = sum_cta partials[cta][(jd,jh)][co][jw*8 + c]   with kd = 2jd+pd, kh = 2jh+ph, kw = 2jw+pw
+__global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ partials, int n_cta, float* __restrict__ grad, float* __restrict__ grad_bias) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < 64 && grad_bias != nullptr) grad_bias[i] = 0.f;   // BatchNorm follows this conv: the bias gradient is identically zero
+    if (i >= 64 * 125) return;
+    const int co = i / 125, tap = i % 125;
+    const int kd = tap / 25, kh = (tap / 5) % 5, kw = tap % 5;
+    const int t = (kd >> 1) * 3 + (kh >> 1);
+    const int col = (kw >> 1) * 8 + ((kd & 1) << 2) + ((kh & 1) << 1) + (kw & 1);
+    float acc = 0.f;
+    for (int c = 0; c < n_cta; ++c) acc += partials[(((size_t)c * 9 + t) * 64 + co) * 32 + col];
+    grad[i] = acc;
+}
+
+static int make_geom(Geom& g, int N, int Di, int Hi, int Wi, float scale) {
+    g.N = N; g.Di = Di; g.Hi = Hi; g.Wi = Wi; g.scale = scale;
+    g.Do = (Di - 5) / 2 + 1; g.Ho = (Hi - 5) / 2 + 1; g.Wo = (Wi - 5) / 2 + 1;
+    if (g.Wo < 1 || g.Wo > 61 || g.Do < 1 || g.Ho < 1) { nidt_set_error("conv_in_s2d: output width %d unsupported (1..61)", g.Wo); return 1; }
+    g.h_tiles = (g.Ho + 1) / 2;
+    g.total_tiles = N * g.Do * g.h_tiles;
+    g.raw_pitch = ((kRows * Wi + 15 + 15) / 16 + 1) * 16;
+    if (kPlanes * (g.raw_pitch >> 4) > 128 * kRawVecs) { nidt_set_error("conv_in_s2d: input rows of %d bytes are too wide for the staging registers", Wi); return 1; }
+    return 0;
+}
+static size_t smem_fprop(const Geom& g) { return 2 * (size_t)kT16 + 36 * 1024 + 2 * (size_t)kABytes + 64 + 16 + 256 + 2 * 16 * 2 * 64 * 4 + 2 * (size_t)kPlanes * g.raw_pitch + 64; }
+static size_t smem_wgrad(const Geom& g) { return 2 * (size_t)kT16 + 2 * (size_t)kABytes + 64 + 16 + 2 * (size_t)kPlanes * g.raw_pitch + 64; }
+
+}  // namespace s2d
+}  // namespace nidt
+using namespace nidt;
+
+NIDT_API int nidt_conv_in_s2d_supported(int Di, int Hi, int Wi, int k, int stride, int pad) {
+    s2d::Geom g;
+    return (k == 5 && stride == 2 && pad == 0 && s2d::make_geom(g, 1, Di, Hi, Wi, 1.f) == 0) ? 1 : 0;
+}
+NIDT_API int64_t nidt_conv_in_s2d_wgrad_scratch_floats() { return (int64_t)kNumSMs * 9 * 64 * 32; }
+
+// same contract as nidt_conv_in_fprop, for k = 5, stride = 2, pad = 0
+NIDT_API int nidt_conv_in_s2d_fprop(const void* x, const float* w, const float* bias, void* y, float* stats_partials, int N, int Di, int Hi, int Wi,
+                                    float scale, void* stream) {
+    s2d::Geom g;
+    if (s2d::make_geom(g, N, Di, Hi, Wi, scale)) return 2;
+    CUtensorMap ty;
+    if (make_tmap_act5d(&ty, y, N, g.Do, g.Ho, g.Wo, 64, g.Wo, 1, 1, 1, 1)) return 1;
+    const size_t smem = s2d::smem_fprop(g);
+    NIDT_REQUIRE(smem <= 227 * 1024, "conv_in_s2d_fprop: shared memory %zu B", smem);
+    const int grid = g.total_tiles < kNumSMs ? g.total_tiles : kNumSMs;
+    cudaStream_t s = (cudaStream_t)stream;
+    NIDT_CUDA_CHECK(cudaFuncSetAttribute(s2d::fprop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    s2d::fprop_kernel<<<grid, s2d::kFpThreads, smem, s>>>((const uint8_t*)x, w, bias, ty, stats_partials, g);
+    NIDT_LAUNCH_CHECK();
+    if (stats_partials != nullptr && grid < kNumSMs)
+        NIDT_CUDA_CHECK(cudaMemsetAsync(stats_partials + (size_t)grid * 128, 0, (size_t)(kNumSMs - grid) * 128 * sizeof(float), s));
+    return 0;
+}
+
+// scratch: >= nidt_conv_in_s2d_wgrad_scratch_floats() floats
+NIDT_API int nidt_conv_in_s2d_wgrad(const void* x, const void* dy, float* grad, float* grad_bias, float* scratch, int N, int Di, int Hi, int Wi,
+                                    float scale, void* stream) {
+    s2d::Geom g;
+    if (s2d::make_geom(g, N, Di, Hi, Wi, scale)) return 2;
+    CUtensorMap tdy;
+    if (make_tmap_act5d(&tdy, dy, N, g.Do, g.Ho, g.Wo, 64, g.Wo, 1, 1, 1, 1)) return 1;
+    const size_t smem = s2d::smem_wgrad(g);
+    NIDT_REQUIRE(smem <= 227 * 1024, "conv_in_s2d_wgrad: shared memory %zu B", smem);
+    const int grid = g.total_tiles < kNumSMs ? g.total_tiles : kNumSMs;
+    cudaStream_t s = (cudaStream_t)stream;
+    NIDT_CUDA_CHECK(cudaFuncSetAttribute(s2d::wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    s2d::wgrad_kernel<<<grid, s2d::kThreads, smem, s>>>((const uint8_t*)x, tdy, scratch, g);
+    NIDT_LAUNCH_CHECK();
+    s2d::wgrad_reduce_kernel<<<(64 * 125 + 255) / 256, 256, 0, s>>>(scratch, grid, grad, grad_bias);
+    NIDT_LAUNCH_CHECK();
+    return 0;
+}

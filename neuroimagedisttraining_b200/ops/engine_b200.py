@@ -50,6 +50,14 @@ def _declare(lib) -> None:
         fn = getattr(lib, name)
         fn.argtypes = argtypes
         fn.restype = C.c_int
+    lib.nidt_conv_in_s2d_supported.argtypes = [i32] * 6
+    lib.nidt_conv_in_s2d_supported.restype = i32
+    lib.nidt_conv_in_s2d_wgrad_scratch_floats.argtypes = []
+    lib.nidt_conv_in_s2d_wgrad_scratch_floats.restype = i64
+    lib.nidt_conv_in_s2d_fprop.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, vp]
+    lib.nidt_conv_in_s2d_fprop.restype = i32
+    lib.nidt_conv_in_s2d_wgrad.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, vp]
+    lib.nidt_conv_in_s2d_wgrad.restype = i32
     lib.nidt_conv3d_wgrad_scratch_floats.argtypes = [i32, i32, i32, i32]
     lib.nidt_conv3d_wgrad_scratch_floats.restype = i64
     _declared = True
@@ -89,7 +97,7 @@ class B200Engine:
     native = True
 
     def __init__(self, model: nn.Module, device, max_batch: int = 16, input_scale: float = 1.0 / 255.0, seed: int = 1234,
-                 wgrad_ctas: int = 296):
+                 wgrad_ctas: int = 296, use_s2d: bool = True):
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("B200Engine needs a CUDA device")
@@ -121,6 +129,8 @@ class B200Engine:
         self._packed_dirty = True
         self.profile = None
         self._tag = ""
+        self.use_s2d = use_s2d
+        self.s2d_wgrad = False     # the im2col wgrad (one 128x64 MMA per 16 positions) beats 9 narrow MMAs re-reading dY from smem
         self._alloc(wgrad_ctas)
 
     # ----------------------------------------------------------------------------- buffers
@@ -149,7 +159,10 @@ class B200Engine:
             if i == 0:
                 b.stats = torch.zeros(lib.nidt_conv_in_grid() * 2 * C_, dtype=torch.float32, device=dev)
                 b.stats_tiles = lib.nidt_conv_in_grid()
-                b.wg_scratch = torch.zeros(lib.nidt_conv_in_grid() * 128 * 64, dtype=torch.float32, device=dev)
+                iD, iH, iW = in_dhw
+                b.s2d = bool(lib.nidt_conv_in_s2d_supported(iD, iH, iW, spec.k, spec.stride, spec.pad)) and self.use_s2d
+                n_scr = max(lib.nidt_conv_in_grid() * 128 * 64, lib.nidt_conv_in_s2d_wgrad_scratch_floats())
+                b.wg_scratch = torch.zeros(n_scr, dtype=torch.float32, device=dev)
             else:
                 b.box = choose_box(W, H, D, B)
                 b.m_tiles = lib.nidt_conv3d_m_tiles(B, D, H, W, *b.box)
@@ -240,8 +253,12 @@ class B200Engine:
             bias = self._p(slab, s.conv + ".bias") if s.bias else None
             if i == 0:
                 iD, iH, iW = b.in_dhw
-                self._chk(lib.nidt_conv_in_fprop(x.data_ptr(), self._p(slab, s.conv + ".weight"), bias, b.y.data_ptr(), stats,
-                                                 B, iD, iH, iW, s.k, s.stride, s.pad, self.input_scale, st), "conv_in_fprop")
+                if b.s2d:     # 5^3 / stride 2: space-to-depth lines feed tcgen05 directly, no im2col
+                    self._chk(lib.nidt_conv_in_s2d_fprop(x.data_ptr(), self._p(slab, s.conv + ".weight"), bias, b.y.data_ptr(), stats,
+                                                         B, iD, iH, iW, self.input_scale, st), "conv_in_s2d_fprop")
+                else:
+                    self._chk(lib.nidt_conv_in_fprop(x.data_ptr(), self._p(slab, s.conv + ".weight"), bias, b.y.data_ptr(), stats,
+                                                     B, iD, iH, iW, s.k, s.stride, s.pad, self.input_scale, st), "conv_in_fprop")
             else:
                 iD, iH, iW = b.in_dhw
                 bw, bh, bd, bn = b.box if B == self.max_batch else choose_box(W, H, D, B)
@@ -293,8 +310,13 @@ class B200Engine:
             native.count_launches(3)
             iD, iH, iW = b.in_dhw
             if i == 0:
-                self._chk(lib.nidt_conv_in_wgrad(self._x.data_ptr(), b.dy.data_ptr(), self._p(self.grad, s.conv + ".weight"),
-                                                 self._p(self.grad, s.conv + ".bias") if s.bias else None, b.wg_scratch.data_ptr(), B, iD, iH, iW, s.k, s.stride, s.pad, self.input_scale, st), "conv_in_wgrad")
+                gb = self._p(self.grad, s.conv + ".bias") if s.bias else None
+                if b.s2d and self.s2d_wgrad:
+                    self._chk(lib.nidt_conv_in_s2d_wgrad(self._x.data_ptr(), b.dy.data_ptr(), self._p(self.grad, s.conv + ".weight"), gb,
+                                                         b.wg_scratch.data_ptr(), B, iD, iH, iW, self.input_scale, st), "conv_in_s2d_wgrad")
+                else:
+                    self._chk(lib.nidt_conv_in_wgrad(self._x.data_ptr(), b.dy.data_ptr(), self._p(self.grad, s.conv + ".weight"), gb,
+                                                     b.wg_scratch.data_ptr(), B, iD, iH, iW, s.k, s.stride, s.pad, self.input_scale, st), "conv_in_wgrad")
                 native.count_launches(2)
             else:
                 prev = self.blocks[i - 1]

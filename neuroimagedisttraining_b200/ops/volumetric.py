@@ -140,3 +140,26 @@ def bn_relu_pool_bwd(y, da, scale, shift, mean, invstd, pool_k: int = 0, pool_s:
                                            shift.data_ptr(), mean.data_ptr(), invstd.data_ptr(), partials.data_ptr(), c12.data_ptr(),
                                            dg.data_ptr(), db.data_ptr(), int(relu), _st(y)), "bn_relu_pool_bwd")
     return dy, dg, db
+
+
+def conv_in_s2d_fprop(x_u8: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], scale: float, stats: bool = False):
+    """5x5x5 / stride-2 first layer through the space-to-depth kernel (no im2col).  Same contract as :func:`conv_in_fprop`."""
+    lib = _lib()
+    N, D, H, W = x_u8.shape
+    Do, Ho, Wo = _out_dim(D, 5, 2, 0), _out_dim(H, 5, 2, 0), _out_dim(W, 5, 2, 0)
+    y = torch.empty((N, Do, Ho, Wo, 64), dtype=torch.bfloat16, device=x_u8.device)
+    part = torch.zeros((lib.nidt_conv_in_grid(), 2, 64), dtype=torch.float32, device=x_u8.device) if stats else None
+    w = w.contiguous().float()
+    native.check(lib.nidt_conv_in_s2d_fprop(x_u8.data_ptr(), w.data_ptr(), bias.data_ptr() if bias is not None else None, y.data_ptr(),
+                                            part.data_ptr() if stats else None, N, D, H, W, scale, _st(y)), "conv_in_s2d_fprop")
+    return (y, part) if stats else y
+
+
+def conv_in_s2d_wgrad(x_u8: torch.Tensor, dy: torch.Tensor, scale: float) -> torch.Tensor:
+    lib = _lib()
+    N, D, H, W = x_u8.shape
+    grad = torch.empty((64, 1, 5, 5, 5), dtype=torch.float32, device=dy.device)
+    scratch = torch.zeros(lib.nidt_conv_in_s2d_wgrad_scratch_floats(), dtype=torch.float32, device=dy.device)
+    native.check(lib.nidt_conv_in_s2d_wgrad(x_u8.data_ptr(), dy.data_ptr(), grad.data_ptr(), None, scratch.data_ptr(), N, D, H, W, scale, _st(dy)),
+                 "conv_in_s2d_wgrad")
+    return grad

@@ -12,11 +12,11 @@ w = torch.randn(64, 1, 5, 5, 5, device=dev) * 0.09
 bias = torch.zeros(64, device=dev)
 gamma, beta = torch.ones(64, device=dev), torch.zeros(64, device=dev)
 for _ in range(reps):
-    y, part = V.conv_in_fprop(x, w, bias, 5, 2, 0, 1 / 255.0, stats=True)
+    y, part = V.conv_in_s2d_fprop(x, w, bias, 1 / 255.0, stats=True)
     scale, shift, mean, invstd = V.bn_finalize(part, y.numel() / 64, gamma, beta)
     a, ymax = V.bn_relu_pool_fwd(y, scale, shift, 3, 3, True, want_ymax=True)
     da = torch.randn_like(a)
     dy, dg, db = V.bn_relu_pool_bwd(y, da, scale, shift, mean, invstd, 3, 3, True, ymax=ymax)
-    dw = V.conv_in_wgrad(x, dy, 5, 2, 0, 1 / 255.0)
+    dw = V.conv_in_s2d_wgrad(x, dy, 1 / 255.0)
 torch.cuda.synchronize()
 print("ok", float(dw.abs().sum()))

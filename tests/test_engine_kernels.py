@@ -195,6 +195,30 @@ def test_conv_in_fprop_wgrad(N, D, H, W, k, stride, pad):
     _close(dbias, br.grad, atol=1e-2, what="conv_in bias grad")
 
 
+@pytest.mark.parametrize("N,D,H,W", [(2, 121, 145, 121), (1, 29, 34, 31), (3, 15, 17, 21)])
+def test_conv_in_space_to_depth_fprop_wgrad(N, D, H, W):
+    """The zero-im2col first layer: tcgen05 descriptors with a 16-byte K-chunk stride over parity-interleaved lines."""
+    from neuroimagedisttraining_b200.ops import volumetric as V
+    torch.manual_seed(6)
+    x = torch.randint(0, 256, (N, D, H, W), dtype=torch.uint8, device=DEV)
+    scale = 1.0 / 255.0
+    w = torch.randn(64, 1, 5, 5, 5, device=DEV) / 125 ** 0.5
+    bias = torch.randn(64, device=DEV) * 0.1
+    xb = (x.float() * scale).bfloat16().float().unsqueeze(1)
+    wr = w.bfloat16().float().requires_grad_(True)
+    ref = F.conv3d(xb, wr, bias, stride=2)
+    y, part = V.conv_in_s2d_fprop(x, w, bias, scale, stats=True)
+    torch.cuda.synchronize()
+    _close(_cf(y), ref, atol=1e-2, what="s2d fprop")
+    yb = y.float().reshape(-1, 64)
+    torch.testing.assert_close(part[:, 0].sum(0), yb.sum(0), rtol=2e-3, atol=5e-2)
+    torch.testing.assert_close(part[:, 1].sum(0), (yb * yb).sum(0), rtol=2e-3, atol=5e-2)
+    dy = (torch.randn_like(ref) * 0.1).bfloat16()
+    ref.backward(dy.float())
+    dw = V.conv_in_s2d_wgrad(x, _cl(dy), scale)
+    _close(dw, wr.grad, atol=1e-2, what="s2d wgrad")
+
+
 def _engine_pair(B, p_drop=0.0):
     from neuroimagedisttraining_b200.fl.engine import TorchEngine
     from neuroimagedisttraining_b200.models import AlexNet3D_Dropout
