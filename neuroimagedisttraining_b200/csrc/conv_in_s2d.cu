@@ -23,17 +23,20 @@ struct Geom {
     int h_tiles;           // ceil(Ho / 2): a tile is 2 output lines
     int total_tiles;       // N * Do * h_tiles
     int raw_pitch;         // bytes per plane of the raw staging buffer (8 input rows + misalignment, multiple of 16)
+    long long in_bytes;    // size of the input tensor (bulk copies never read past its 16-byte-rounded end)
     float scale;
 };
 
-constexpr int kThreads = 13 * 32;        // wgrad: warps 0-3 / 4-7 staging groups, warp 8 MMA, warps 9-12 TMA + final epilogue
-constexpr int kFpThreads = 17 * 32;      // fprop: ... warps 9-12 / 13-16 = two epilogue groups (tile i -> group i & 1)
+constexpr int kThreads = 13 * 32;        // wgrad: warps 0-3 / 4-7 staging groups, warp 8 MMA, warps 9-12 producers (dY TMA, raw bulk copies) + final epilogue
+constexpr int kFpThreads = 18 * 32;      // fprop: ... warps 9-12 / 13-16 = two epilogue groups (tile i -> group i & 1), warp 17 = raw producer
 constexpr int kLineBytes = 64 * 16;      // one s2d line: 64 positions x 8 bf16
 constexpr int kLines = 12;               // 3 jd planes x 4 y' lines
-constexpr int kABytes = kLines * kLineBytes + 256;   // + tail so that row 127 + 3 positions stays inside the buffer
+constexpr int kABytes = 16 * kLineBytes + 2048 + 256;   // 12 lines are written; wgrad addresses 16 line-chunks x 128 positions (+ taps): the rest stays zero
 constexpr int kPlanes = 6, kRows = 8;    // raw input planes / rows per tile
-constexpr int kRawVecs = 3;
 constexpr int kT16 = 16384;
+constexpr int kRawRing = 4;               // raw u8 tiles in flight (bulk copies issued by one producer thread)
+constexpr int kARing = 4;                 // line buffers: each staging group runs one of its own tiles ahead of the MMAs
+constexpr int kDyRing = 4;                // dY tiles in flight ahead of the wgrad MMAs
 
 __device__ __forceinline__ void named_bar(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 
@@ -61,31 +64,36 @@ __device__ __forceinline__ const uint8_t* plane_src(const uint8_t* __restrict__ 
     return x + (((size_t)n * g.Di + z) * g.Hi + y0) * g.Wi;
 }
 
-// global -> registers: the 8 input rows of each of the 6 planes are one contiguous byte run per plane
-__device__ __forceinline__ void raw_prefetch(const uint8_t* __restrict__ x, const Geom& g, int n, int d, int h0, int gt, uint4 (&q)[kRawVecs]) {
-    const int z0 = 2 * d, y0 = 2 * h0;
-    const int bytes = min(kRows, g.Hi - y0) * g.Wi;
-    const int nv = g.raw_pitch >> 4;
+// producer thread: the 8 input rows of each of the 6 planes are one contiguous byte run per plane -> one bulk copy per plane
+// (aligned superset of the run) into raw slot `tile_seq % kRawRing`
+__device__ __forceinline__ void raw_producer_loop(const uint8_t* __restrict__ x, const Geom& g, uint8_t* raws, uint64_t* raw_full, uint64_t* raw_empty) {
+    const uintptr_t x_end = (reinterpret_cast<uintptr_t>(x) + (uintptr_t)g.in_bytes + 15) & ~(uintptr_t)15;
+    for (int i = 0;; ++i) {
+        const int tile = blockIdx.x + i * gridDim.x;
+        if (tile >= g.total_tiles) break;
+        const int slot = i % kRawRing;
+        int n, d, h0, lines;
+        decode_tile(g, tile, n, d, h0, lines);
+        tc::mbar_wait(&raw_empty[slot], ((i / kRawRing) & 1) ^ 1);
+        const int z0 = 2 * d, y0 = 2 * h0;
+        const int planes = min(kPlanes, g.Di - z0);
+        uint32_t total = 0, sz[kPlanes];
+        const uint8_t* src[kPlanes];
 #pragma unroll
-    for (int j = 0; j < kRawVecs; ++j) {
-        const int v = gt + j * 128;
-        q[j] = make_uint4(0, 0, 0, 0);
-        if (v < kPlanes * nv) {
-            const int plane = v / nv, vi = v - plane * nv;
-            if (z0 + plane < g.Di) {
-                const uint8_t* src = plane_src(x, g, n, z0 + plane, y0);
-                const int mis = (int)(reinterpret_cast<uintptr_t>(src) & 15);
-                if (vi * 16 - mis < bytes) q[j] = __ldg(reinterpret_cast<const uint4*>(src - mis) + vi);
+        for (int p = 0; p < kPlanes; ++p) {
+            sz[p] = 0;
+            if (p < planes) {
+                const uint8_t* s0 = plane_src(x, g, n, z0 + p, y0);
+                src[p] = s0 - (reinterpret_cast<uintptr_t>(s0) & 15);
+                const uintptr_t room = x_end - reinterpret_cast<uintptr_t>(src[p]);
+                sz[p] = (uint32_t)min((uintptr_t)g.raw_pitch, room);
+                total += sz[p];
             }
         }
-    }
-}
-__device__ __forceinline__ void raw_store(uint8_t* __restrict__ raw, const Geom& g, int gt, const uint4 (&q)[kRawVecs]) {
-    const int nv = g.raw_pitch >> 4;
+        tc::mbar_expect_tx(&raw_full[slot], total);
 #pragma unroll
-    for (int j = 0; j < kRawVecs; ++j) {
-        const int v = gt + j * 128;
-        if (v < kPlanes * nv) reinterpret_cast<uint4*>(raw)[v] = q[j];
+        for (int p = 0; p < kPlanes; ++p)
+            if (sz[p]) tc::bulk_load_1d(raws + (slot * kPlanes + p) * g.raw_pitch, src[p], sz[p], &raw_full[slot]);
     }
 }
 
@@ -99,8 +107,10 @@ __device__ __forceinline__ void build_lines(const uint8_t* __restrict__ x, const
     const int planes_ok = min(kPlanes, g.Di - z0);
     const uint32_t mis0 = (uint32_t)(reinterpret_cast<uintptr_t>(plane_src(x, g, n, z0, y0)) & 15);
     const uint32_t psz = (uint32_t)((size_t)g.Hi * g.Wi) & 15u;       // plane-to-plane change of the 16-byte misalignment
-#pragma unroll 1
-    for (int item = gt; item < kLines * 32; item += 128) {
+    static_assert(kLines * 32 == 3 * 128, "three items per staging thread");
+#pragma unroll
+    for (int it = 0; it < 3; ++it) {                       // fully unrolled: three independent load->convert->store chains in flight
+        const int item = gt + it * 128;
         const int i4 = item & 31, L = item >> 5;          // 4-byte group within the row, line (jd*4 + hl)
         const int jd = L >> 2, hl = L & 3;
         const int nvalid = min(4, max(0, g.Wi - 4 * i4));
@@ -129,35 +139,23 @@ __device__ __forceinline__ void build_lines(const uint8_t* __restrict__ x, const
     }
 }
 
-// staging warps (0-7): two groups alternate tiles; the next tile's global loads are in flight while the current one is built
-__device__ __forceinline__ void staging_loop(const uint8_t* __restrict__ x, const Geom& g, uint8_t* a_bufs, uint8_t* raws, uint64_t* a_full, uint64_t* a_empty) {
+// staging warps (0-7): two groups alternate tiles.  Raw bytes arrive by bulk copy kRawRing tiles ahead; a group converts
+// them into the line buffer `i % kARing` as soon as the MMAs that read that buffer kARing tiles ago have finished.
+__device__ __forceinline__ void staging_loop(const uint8_t* __restrict__ x, const Geom& g, uint8_t* a_bufs, uint8_t* raws, uint64_t* a_full, uint64_t* a_empty,
+                                             uint64_t* raw_full, uint64_t* raw_empty) {
     const int grp = threadIdx.x >> 7, gt = threadIdx.x & 127;
-    uint8_t* raw = raws + grp * kPlanes * g.raw_pitch;
-    uint8_t* a_buf = a_bufs + grp * kABytes;
-    uint4 q[kRawVecs];
-    int n, d, h0, lines;
-    int tile = blockIdx.x + grp * gridDim.x;
-    if (tile < g.total_tiles) {
+    for (int i = grp;; i += 2) {
+        const int tile = blockIdx.x + i * gridDim.x;
+        if (tile >= g.total_tiles) break;
+        const int buf = i % kARing, slot = i % kRawRing;
+        int n, d, h0, lines;
         decode_tile(g, tile, n, d, h0, lines);
-        raw_prefetch(x, g, n, d, h0, gt, q);
-    }
-    for (int i = grp; tile < g.total_tiles; i += 2) {
-        const uint32_t u = i >> 1;
-        decode_tile(g, tile, n, d, h0, lines);
-        const int next = tile + 2 * gridDim.x;
-        raw_store(raw, g, gt, q);
-        named_bar(1 + grp, 128);
-        if (next < g.total_tiles) {
-            int n2, d2, h2, l2;
-            decode_tile(g, next, n2, d2, h2, l2);
-            raw_prefetch(x, g, n2, d2, h2, gt, q);
-        }
-        tc::mbar_wait(&a_empty[grp], (u & 1) ^ 1);      // the MMAs of this group's previous tile have read the lines
-        build_lines(x, raw, a_buf, g, n, d, h0, gt);
+        tc::mbar_wait(&raw_full[slot], (i / kRawRing) & 1);
+        tc::mbar_wait(&a_empty[buf], ((i / kARing) & 1) ^ 1);
+        build_lines(x, raws + slot * kPlanes * g.raw_pitch, a_bufs + buf * kABytes, g, n, d, h0, gt);
         tc::fence_proxy_async_smem();
-        tc::mbar_arrive(&a_full[grp]);
-        named_bar(1 + grp, 128);                         // raw is rewritten at the top of the next iteration
-        tile = next;
+        tc::mbar_arrive(&a_full[buf]);
+        tc::mbar_arrive(&raw_empty[slot]);
     }
 }
 
@@ -168,10 +166,11 @@ __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __r
     if ((tc::smem_u32(smem) & 1023u) != 0u) __trap();
     uint8_t* staging = smem;                              // [2][128 rows][128 B] swizzled (TMA store source), one per epilogue group
     uint8_t* b_tile = staging + 2 * kT16;                 // [36 K-chunks][64 co][16 B]  (no swizzle)
-    uint8_t* a_bufs = b_tile + 36 * 1024;                 // [2][kABytes]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(a_bufs + 2 * kABytes);
-    uint64_t *a_full = bars, *a_empty = bars + 2, *t_full = bars + 4, *t_empty = bars + 6;
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 8);
+    uint8_t* a_bufs = b_tile + 36 * 1024;                 // [kARing][kABytes]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(a_bufs + kARing * kABytes);
+    uint64_t *a_full = bars, *a_empty = bars + kARing, *t_full = bars + 2 * kARing, *t_empty = t_full + 2;
+    uint64_t *raw_full = t_empty + 2, *raw_empty = raw_full + kRawRing;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(raw_empty + kRawRing);
     float* sbias = reinterpret_cast<float*>(tmem_ptr + 4);    // [64]
     float* red = sbias + 64;                                   // [2 groups][16 parts][2][64]
     uint8_t* raws = reinterpret_cast<uint8_t*>(red + 2 * 16 * 2 * 64);
@@ -185,15 +184,14 @@ __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __r
         const float v = (kd < 5 && kh < 5 && kw < 5) ? w[co * 125 + (kd * 5 + kh) * 5 + kw] : 0.f;
         reinterpret_cast<__nv_bfloat16*>(b_tile)[idx] = __float2bfloat16(v);
     }
-    for (int i = threadIdx.x; i < 2 * kABytes / 16; i += kFpThreads) reinterpret_cast<uint4*>(a_bufs)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = threadIdx.x; i < kARing * kABytes / 16; i += kFpThreads) reinterpret_cast<uint4*>(a_bufs)[i] = make_uint4(0, 0, 0, 0);
     if (threadIdx.x < 64) sbias[threadIdx.x] = bias != nullptr ? bias[threadIdx.x] : 0.f;
     tc::fence_proxy_async_smem();
     if (threadIdx.x == 0) {
         tc::tma_prefetch_desc(&tm_y);
-        for (int i = 0; i < 2; ++i) {
-            tc::mbar_init(&a_full[i], 128); tc::mbar_init(&a_empty[i], 1);
-            tc::mbar_init(&t_full[i], 1);   tc::mbar_init(&t_empty[i], 128);
-        }
+        for (int i = 0; i < kARing; ++i) { tc::mbar_init(&a_full[i], 128); tc::mbar_init(&a_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { tc::mbar_init(&t_full[i], 1); tc::mbar_init(&t_empty[i], 128); }
+        for (int i = 0; i < kRawRing; ++i) { tc::mbar_init(&raw_full[i], 1); tc::mbar_init(&raw_empty[i], 128); }
         tc::mbar_fence_init();
     }
     if (warp == 8) tc::tmem_alloc<128>(tmem_ptr);
@@ -203,7 +201,9 @@ __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __r
     const uint32_t tmem_base = *tmem_ptr;
 
     if (warp < 8) {
-        staging_loop(x, g, a_bufs, raws, a_full, a_empty);
+        staging_loop(x, g, a_bufs, raws, a_full, a_empty, raw_full, raw_empty);
+    } else if (warp == 17) {
+        if (lane == 0) raw_producer_loop(x, g, raws, raw_full, raw_empty);
     } else if (warp == 8) {
         if (lane == 0) {
             constexpr uint32_t idesc = tc::make_idesc_bf16(128, 64, 0, 0);
@@ -211,12 +211,12 @@ __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __r
             for (int i = 0;; ++i) {
                 const int tile = blockIdx.x + i * gridDim.x;
                 if (tile >= g.total_tiles) break;
-                const int b = i & 1;
+                const int b = i & 1, buf = i % kARing;
                 const uint32_t u = i >> 1;
-                tc::mbar_wait(&a_full[b], u & 1);
+                tc::mbar_wait(&a_full[buf], (i / kARing) & 1);
                 tc::mbar_wait(&t_empty[b], (u & 1) ^ 1);
                 tc::tc_fence_after();
-                const uint32_t a_addr = tc::smem_u32(a_bufs + b * kABytes);
+                const uint32_t a_addr = tc::smem_u32(a_bufs + buf * kABytes);
 #pragma unroll
                 for (int t = 0; t < 9; ++t) {            // (jd, jh)
                     const int jd = t / 3, jh = t % 3;
@@ -227,7 +227,7 @@ __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __r
                         tc::umma_bf16(tmem_base + b * 64, da, db, idesc, (t | pr) != 0);
                     }
                 }
-                tc::umma_commit(&a_empty[b]);
+                tc::umma_commit(&a_empty[buf]);
                 tc::umma_commit(&t_full[b]);
             }
         }
@@ -316,62 +316,67 @@ __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __r
 }
 
 // ======================================================================================= wgrad
-// D_t[co][jw*8 + c] (t = (jd,jh), 9 accumulators of 32 columns) += dY^T[co][pos] * line_t[pos + jw][c]
+// D_jw[L*8 + c][co] (jw = 0..2, three accumulators of 64 columns) += line_L[pos + jw][c] * dY[pos][co]
+// A = the s2d lines as an MN-major operand: M chunk = one line L = (jd, y' line) (stride 1 KiB), K = positions (16 B apart);
+// line chunk (jd, hl) is the tap (jd, jh = hl) because rows 64..127 of the K range run into the next line, exactly like fprop.
 __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __restrict__ x, const __grid_constant__ CUtensorMap tm_dy,
-                                                            float* __restrict__ partials /* [grid][9][64][32] */, const Geom g) {
+                                                            float* __restrict__ partials /* [grid][3][128][64] */, const Geom g) {
     extern __shared__ __align__(1024) uint8_t smem[];
     if ((tc::smem_u32(smem) & 1023u) != 0u) __trap();
-    uint8_t* dy_tiles = smem;                              // [2][128 pos][64 co] swizzled; rows 59..63 / 123..127 stay zero
-    uint8_t* a_bufs = dy_tiles + 2 * kT16;                 // [2][kABytes] s2d lines
-    uint64_t* bars = reinterpret_cast<uint64_t*>(a_bufs + 2 * kABytes);
-    uint64_t *a_full = bars, *a_empty = bars + 2, *dy_full = bars + 4, *t_full = bars + 6;
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 8);
-    uint8_t* raws = reinterpret_cast<uint8_t*>(tmem_ptr + 4);
+    uint8_t* dy_tiles = smem;                              // [kDyRing][128 pos][64 co] swizzled; rows 59..63 / 123..127 stay zero
+    uint8_t* a_bufs = dy_tiles + kDyRing * kT16;           // [kARing][kABytes] s2d lines
+    uint64_t* bars = reinterpret_cast<uint64_t*>(a_bufs + kARing * kABytes);
+    uint64_t *a_full = bars, *a_empty = bars + kARing, *t_full = bars + 2 * kARing, *dy_full = t_full + 1, *dy_empty = dy_full + kDyRing;
+    uint64_t *raw_full = dy_empty + kDyRing, *raw_empty = raw_full + kRawRing;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(raw_empty + kRawRing);
+    uint8_t* raws = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(tmem_ptr + 4) + 15) & ~(uintptr_t)15);   // 16-byte vector stores
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-    for (int i = threadIdx.x; i < (2 * kT16 + 2 * kABytes) / 16; i += kThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = threadIdx.x; i < (kDyRing * kT16 + kARing * kABytes) / 16; i += kThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
     tc::fence_proxy_async_smem();
     if (threadIdx.x == 0) {
         tc::tma_prefetch_desc(&tm_dy);
-        for (int i = 0; i < 2; ++i) { tc::mbar_init(&a_full[i], 128); tc::mbar_init(&a_empty[i], 1); tc::mbar_init(&dy_full[i], 1); }
+        for (int i = 0; i < kARing; ++i) { tc::mbar_init(&a_full[i], 128); tc::mbar_init(&a_empty[i], 1); }
+        for (int i = 0; i < kDyRing; ++i) { tc::mbar_init(&dy_full[i], 1); tc::mbar_init(&dy_empty[i], 1); }
+        for (int i = 0; i < kRawRing; ++i) { tc::mbar_init(&raw_full[i], 1); tc::mbar_init(&raw_empty[i], 128); }
         tc::mbar_init(t_full, 1);
         tc::mbar_fence_init();
     }
-    if (warp == 8) tc::tmem_alloc<512>(tmem_ptr);
+    if (warp == 8) tc::tmem_alloc<256>(tmem_ptr);
     tc::tc_fence_before();
     __syncthreads();
     tc::tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
 
     if (warp < 8) {
-        staging_loop(x, g, a_bufs, raws, a_full, a_empty);
+        staging_loop(x, g, a_bufs, raws, a_full, a_empty, raw_full, raw_empty);
     } else if (warp == 8) {
         if (lane == 0) {
-            constexpr uint32_t idesc = tc::make_idesc_bf16(128, 32, 1, 1);
+            constexpr uint32_t idesc = tc::make_idesc_bf16(128, 64, 1, 1);
             int i = 0;
             for (;; ++i) {
                 const int tile = blockIdx.x + i * gridDim.x;
                 if (tile >= g.total_tiles) break;
-                const int b = i & 1;
-                const uint32_t u = i >> 1;
-                tc::mbar_wait(&a_full[b], u & 1);
-                tc::mbar_wait(&dy_full[b], u & 1);
+                const int b = i % kARing;
+                const int slot = i % kDyRing;
+                tc::mbar_wait(&a_full[b], (i / kARing) & 1);
+                tc::mbar_wait(&dy_full[slot], (i / kDyRing) & 1);
                 tc::tc_fence_after();
-                const uint32_t dy_addr = tc::smem_u32(dy_tiles + b * kT16);
+                const uint32_t dy_addr = tc::smem_u32(dy_tiles + slot * kT16);
                 const uint32_t a_addr = tc::smem_u32(a_bufs + b * kABytes);
 #pragma unroll 1
                 for (int ks = 0; ks < 8; ++ks) {          // 16 positions per MMA
-                    // A = dY^T, MN-major SW128: M chunk 1 (rows 64..127 of D) aliases chunk 0 (LBO = 0); K groups 1024 B apart
-                    const uint64_t da = tc::make_smem_desc_sw128(dy_addr + ks * 2048, 0, 1024);
+                    // B = dY, MN-major SW128 (N = 64 co = one chunk; 8-position groups 1 KiB apart)
+                    const uint64_t db = tc::make_smem_desc_sw128(dy_addr + ks * 2048, kT16, 1024);
 #pragma unroll
-                    for (int t = 0; t < 9; ++t) {
-                        const int jd = t / 3, jh = t % 3;
-                        // B = s2d lines, MN-major no swizzle: N chunks (jw) 16 B apart, K groups (8 positions) 128 B apart
-                        const uint64_t db = desc_noswz(a_addr + (jd * 4 + jh) * kLineBytes + ks * 256, 128, 16);
-                        tc::umma_bf16(tmem_base + t * 32, da, db, idesc, (i | ks) != 0);
+                    for (int jw = 0; jw < 3; ++jw) {
+                        // A = lines, MN-major no swizzle: M chunks (lines) 1 KiB apart (SBO), K groups (8 positions) 128 B apart (LBO)
+                        const uint64_t da = desc_noswz(a_addr + jw * 16 + ks * 256, 128, kLineBytes);
+                        tc::umma_bf16(tmem_base + jw * 64, da, db, idesc, (i | ks) != 0);
                     }
                 }
                 tc::umma_commit(&a_empty[b]);
+                tc::umma_commit(&dy_empty[slot]);
             }
             tc::umma_commit(t_full);
         }
@@ -380,33 +385,31 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __res
             for (int i = 0;; ++i) {
                 const int tile = blockIdx.x + i * gridDim.x;
                 if (tile >= g.total_tiles) break;
-                const int b = i & 1;
-                const uint32_t u = i >> 1;
+                const int slot = i % kDyRing;
                 int n, d, h0, lines;
                 decode_tile(g, tile, n, d, h0, lines);
-                tc::mbar_wait(&a_empty[b], (u & 1) ^ 1);
+                tc::mbar_wait(&dy_empty[slot], ((i / kDyRing) & 1) ^ 1);     // dY runs kDyRing tiles ahead of the MMAs
                 // one box per output line (rows 0..Wo-1 and 64..64+Wo-1); a line past Ho is zero-filled by the hardware
-                tc::mbar_expect_tx(&dy_full[b], (uint32_t)(2 * g.Wo * 128));
-                tc::tma_load_5d(&tm_dy, &dy_full[b], dy_tiles + b * kT16, 0, 0, h0, d, n);
-                tc::tma_load_5d(&tm_dy, &dy_full[b], dy_tiles + b * kT16 + 64 * 128, 0, 0, h0 + 1, d, n);
+                tc::mbar_expect_tx(&dy_full[slot], (uint32_t)(2 * g.Wo * 128));
+                tc::tma_load_5d(&tm_dy, &dy_full[slot], dy_tiles + slot * kT16, 0, 0, h0, d, n);
+                tc::tma_load_5d(&tm_dy, &dy_full[slot], dy_tiles + slot * kT16 + 64 * 128, 0, 0, h0 + 1, d, n);
             }
         }
+        if (warp == 10 && lane == 0) raw_producer_loop(x, g, raws, raw_full, raw_empty);
         __syncwarp();
         const int q = warp & 3;
-        const int co = q * 32 + lane;                     // D rows 64..127 duplicate 0..63
+        const int mrow = q * 32 + lane;                   // D row = line*8 + channel
         tc::mbar_wait(t_full, 0);
         tc::tc_fence_after();
 #pragma unroll 1
-        for (int t = 0; t < 9; ++t) {
+        for (int jw = 0; jw < 3; ++jw) {
+            float* dst = partials + (((size_t)blockIdx.x * 3 + jw) * 128 + mrow) * 64;
 #pragma unroll 1
-            for (int c = 0; c < 32; c += 16) {
+            for (int c = 0; c < 64; c += 16) {
                 float v[16];
-                tc::tmem_ld16(tmem_base + t * 32 + c + ((uint32_t)(q * 32) << 16), v);
-                if (co < 64) {
-                    float* dst = partials + (((size_t)blockIdx.x * 9 + t) * 64 + co) * 32 + c;
+                tc::tmem_ld16(tmem_base + jw * 64 + c + ((uint32_t)(q * 32) << 16), v);
 #pragma unroll
-                    for (int j = 0; j < 16; j += 4) st4(dst + j, make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]));
-                }
+                for (int j = 0; j < 16; j += 4) st4(dst + c + j, make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]));
             }
         }
     }
@@ -414,21 +417,21 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __res
     __syncthreads();
     if (warp == 8) {
         tc::tc_fence_after();
-        tc::tmem_dealloc<512>(tmem_base);
+        tc::tmem_dealloc<256>(tmem_base);
     }
 }
 
-// dW[co][kd][kh][kw] = sum_cta partials[cta][(jd,jh)][co][jw*8 + c]   with kd = 2jd+pd, kh = 2jh+ph, kw = 2jw+pw
+// dW[co][kd][kh][kw] = sum_cta partials[cta][jw][(jd*4+jh)*8 + c][co]   with kd = 2jd+pd, kh = 2jh+ph, kw = 2jw+pw, c = pd*4+ph*2+pw
 __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ partials, int n_cta, float* __restrict__ grad, float* __restrict__ grad_bias) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < 64 && grad_bias != nullptr) grad_bias[i] = 0.f;   // BatchNorm follows this conv: the bias gradient is identically zero
     if (i >= 64 * 125) return;
     const int co = i / 125, tap = i % 125;
     const int kd = tap / 25, kh = (tap / 5) % 5, kw = tap % 5;
-    const int t = (kd >> 1) * 3 + (kh >> 1);
-    const int col = (kw >> 1) * 8 + ((kd & 1) << 2) + ((kh & 1) << 1) + (kw & 1);
+    const int row = ((kd >> 1) * 4 + (kh >> 1)) * 8 + ((kd & 1) << 2) + ((kh & 1) << 1) + (kw & 1);
+    const int jw = kw >> 1;
     float acc = 0.f;
-    for (int c = 0; c < n_cta; ++c) acc += partials[(((size_t)c * 9 + t) * 64 + co) * 32 + col];
+    for (int c = 0; c < n_cta; ++c) acc += partials[(((size_t)c * 3 + jw) * 128 + row) * 64 + co];
     grad[i] = acc;
 }
 
@@ -439,11 +442,11 @@ static int make_geom(Geom& g, int N, int Di, int Hi, int Wi, float scale) {
     g.h_tiles = (g.Ho + 1) / 2;
     g.total_tiles = N * g.Do * g.h_tiles;
     g.raw_pitch = ((kRows * Wi + 15 + 15) / 16 + 1) * 16;
-    if (kPlanes * (g.raw_pitch >> 4) > 128 * kRawVecs) { nidt_set_error("conv_in_s2d: input rows of %d bytes are too wide for the staging registers", Wi); return 1; }
+    g.in_bytes = (long long)N * Di * Hi * Wi;
     return 0;
 }
-static size_t smem_fprop(const Geom& g) { return 2 * (size_t)kT16 + 36 * 1024 + 2 * (size_t)kABytes + 64 + 16 + 256 + 2 * 16 * 2 * 64 * 4 + 2 * (size_t)kPlanes * g.raw_pitch + 64; }
-static size_t smem_wgrad(const Geom& g) { return 2 * (size_t)kT16 + 2 * (size_t)kABytes + 64 + 16 + 2 * (size_t)kPlanes * g.raw_pitch + 64; }
+static size_t smem_fprop(const Geom& g) { return 2 * (size_t)kT16 + 36 * 1024 + kARing * (size_t)kABytes + 8 * (2 * kARing + 4 + 2 * kRawRing) + 16 + 256 + 2 * 16 * 2 * 64 * 4 + kRawRing * (size_t)kPlanes * g.raw_pitch + 64; }
+static size_t smem_wgrad(const Geom& g) { return kDyRing * (size_t)kT16 + kARing * (size_t)kABytes + 8 * (2 * kARing + 1 + 2 * kDyRing + 2 * kRawRing) + 32 + kRawRing * (size_t)kPlanes * g.raw_pitch + 64; }
 
 }  // namespace s2d
 }  // namespace nidt
@@ -453,7 +456,7 @@ NIDT_API int nidt_conv_in_s2d_supported(int Di, int Hi, int Wi, int k, int strid
     s2d::Geom g;
     return (k == 5 && stride == 2 && pad == 0 && s2d::make_geom(g, 1, Di, Hi, Wi, 1.f) == 0) ? 1 : 0;
 }
-NIDT_API int64_t nidt_conv_in_s2d_wgrad_scratch_floats() { return (int64_t)kNumSMs * 9 * 64 * 32; }
+NIDT_API int64_t nidt_conv_in_s2d_wgrad_scratch_floats() { return (int64_t)kNumSMs * 3 * 128 * 64; }
 
 // same contract as nidt_conv_in_fprop, for k = 5, stride = 2, pad = 0
 NIDT_API int nidt_conv_in_s2d_fprop(const void* x, const float* w, const float* bias, void* y, float* stats_partials, int N, int Di, int Hi, int Wi,

@@ -130,7 +130,7 @@ class B200Engine:
         self.profile = None
         self._tag = ""
         self.use_s2d = use_s2d
-        self.s2d_wgrad = False     # the im2col wgrad (one 128x64 MMA per 16 positions) beats 9 narrow MMAs re-reading dY from smem
+        self.s2d_wgrad = True
         self._alloc(wgrad_ctas)
 
     # ----------------------------------------------------------------------------- buffers
