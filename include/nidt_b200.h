@@ -113,6 +113,34 @@ int nidt_conv_in_fprop(const void* x, const float* w, const float* bias, void* y
 int nidt_conv_in_wgrad(const void* x, const void* dy, float* grad, float* grad_bias, float* scratch, int N, int Di, int Hi, int Wi,
                        int k, int stride, int pad, float scale, void* stream);
 
+/* Same layer for the flagship shape (k = 5, stride 2, no padding) WITHOUT im2col: the 8-bit volume is staged as
+ * space-to-depth lines (8 parity channels = one 16-byte UMMA core-matrix row) that tcgen05.mma reads directly through
+ * descriptors whose K-chunk stride equals the position stride (conv_in_s2d.cu).  Same contracts as the two above. */
+int nidt_conv_in_s2d_supported(int Di, int Hi, int Wi, int k, int stride, int pad);
+int64_t nidt_conv_in_s2d_wgrad_scratch_floats(void);
+int nidt_conv_in_s2d_fprop(const void* x, const float* w, const float* bias, void* y, float* stats_partials, int N, int Di, int Hi,
+                           int Wi, float scale, void* stream);
+int nidt_conv_in_s2d_wgrad(const void* x, const void* dy, float* grad, float* grad_bias, float* scratch, int N, int Di, int Hi,
+                           int Wi, float scale, void* stream);
+
+/* ------------------------------------- compute fused with its collective over NVLink symmetric memory (sym_agg.cu) */
+/* All ranks call these with the same arguments order; the kernels wait for each other through release/acquire flags.
+ * partial_ptrs / result_ptrs / flag_ptrs: HOST arrays of `world` peer-mapped device pointers (identical order on every rank);
+ * flag pads hold nidt_sym_flag_words() uint32, zero before the first call; `epoch` grows by 1 per call on every rank.
+ * mc_*: NVLS multicast addresses of the same buffers (or null); use_multimem selects multimem.ld_reduce / multimem.st. */
+int nidt_sym_max_ranks(void);
+int nidt_sym_flag_words(void);
+/* W1: out = mask * sum_ranks partial.  reduce-scatter (P2P loads in rank order, or in-switch reduction) + SalientGrads mask +
+ * all-gather (P2P / multicast stores) + write-back, one launch per rank.  ref: sailentgrads_api.py:212-227 (CPU dict loop). */
+int nidt_sym_reduce_mask_broadcast(void* const* partial_ptrs, void* const* result_ptrs, void* const* flag_ptrs, void* mc_partial,
+                                   void* mc_result, int rank, int world, const float* mask, int64_t n_mask, int64_t n,
+                                   float* out_local, uint32_t epoch, int use_multimem, void* stream);
+/* W2: cross-rank saliency all-reduce fused with the global top-k threshold and the mask emission.  ref: snip.py:80-140. */
+int nidt_sym_saliency_topk_mask(void* const* partial_ptrs, void* const* result_ptrs, void* const* flag_ptrs, void* mc_partial,
+                                void* mc_result, int rank, int world, int64_t n, const unsigned char* flags, float* mask,
+                                unsigned long long k, void* scratch, float* scores_out, uint32_t epoch, int use_multimem,
+                                void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -43,7 +43,8 @@ class EvalCounters:
 
 
 class TorchEngine:
-    def __init__(self, model: nn.Module, device, loss_kind: str = "bce", volumetric: bool = True, input_scale: float = 1.0 / 255.0):
+    def __init__(self, model: nn.Module, device, loss_kind: str = "bce", volumetric: bool = True, input_scale: float = 1.0 / 255.0,
+                 amp: bool = False):
         self.device = torch.device(device)
         self.model = model.to(self.device)
         self.layout = SlabLayout.from_module(self.model)
@@ -55,6 +56,7 @@ class TorchEngine:
         self.loss_acc = torch.zeros((), dtype=torch.float32, device=self.device)
         self.loss_steps = 0
         self.native = False
+        self.amp = bool(amp) and self.device.type == "cuda"     # bf16 autocast (library kernels) for models without a native plan
 
     # -- parameter binding ---------------------------------------------------------------
     def new_slab(self) -> ParamSlab:
@@ -97,7 +99,9 @@ class TorchEngine:
         for name, p in self.model.named_parameters():   # autograd may have replaced .grad; re-pin cheaply
             if p.grad is None or p.grad.data_ptr() != self.grad.view(name).data_ptr():
                 p.grad = self.grad.view(name)
-        loss = self._loss(self.model(self._prep(x)), y)
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.amp):
+            out = self.model(self._prep(x))
+        loss = self._loss(out.float() if torch.is_tensor(out) else [o.float() for o in out], y)
         loss.backward()
         return loss.detach()
 
