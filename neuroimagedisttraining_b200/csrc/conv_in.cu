@@ -465,12 +465,12 @@ __global__ void __launch_bounds__(kInThreads, 1) conv_in_wgrad_kernel(
     }
 }
 
-// dW[co][tap] = sum_cta partials[cta][tap][co] ; dbias[co] = sum_cta partials[cta][taps][co]
+// dW[co][tap] = sum_cta partials[cta][tap][co] ; dbias[co] = sum_cta partials[cta][taps][co]   (co fastest: coalesced reads)
 __global__ void __launch_bounds__(256) conv_in_wgrad_reduce_kernel(const float* __restrict__ partials, int n_cta, int taps, float* __restrict__ grad,
                                                                    float* __restrict__ grad_bias) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= 64 * (taps + 1)) return;
-    const int co = i / (taps + 1), t = i % (taps + 1);
+    const int co = i & 63, t = i >> 6;
     float acc = 0.f;
     for (int c = 0; c < n_cta; ++c) acc += partials[((size_t)c * 128 + t) * 64 + co];
     if (t < taps) grad[co * taps + t] = acc;

@@ -13,6 +13,7 @@
 // The staging warps only convert the 8-bit volume (u8 * scale -> bf16) into parity-interleaved lines.
 // Reference op: nn.Conv3d(1,64,5,stride=2) + its weight gradient, fedml_api/model/cv/salient_models.py:147 (cuDNN fp32).
 #include "tc_common.cuh"
+#include <stdlib.h>
 
 namespace nidt {
 namespace s2d {
@@ -25,6 +26,7 @@ struct Geom {
     int raw_pitch;         // bytes per plane of the raw staging buffer (8 input rows + misalignment, multiple of 16)
     long long in_bytes;    // size of the input tensor (bulk copies never read past its 16-byte-rounded end)
     float scale;
+    int dbg;               // profiling aid (NIDT_S2D_DEBUG): bit0 skip line building, bit1 skip MMAs, bit2 skip dY loads, bit3 skip raw copies
 };
 
 constexpr int kThreads = 13 * 32;        // wgrad: warps 0-3 / 4-7 staging groups, warp 8 MMA, warps 9-12 producers (dY TMA, raw bulk copies) + final epilogue
@@ -36,6 +38,10 @@ constexpr int kPlanes = 6, kRows = 8;    // raw input planes / rows per tile
 constexpr int kT16 = 16384;
 constexpr int kRawRing = 4;               // raw u8 tiles in flight (bulk copies issued by one producer thread)
 constexpr int kARing = 4;                 // line buffers: each staging group runs one of its own tiles ahead of the MMAs
+constexpr int kWgPitch = 65;              // wgrad: positions per line.  65 (not 64) skews consecutive lines by 16 B so that the 16 line-chunks of one
+                                          // MN-major A row fall into different shared-memory banks (a 1 KiB pitch would be a 16-way conflict)
+constexpr int kWgLineBytes = kWgPitch * 16;
+constexpr int kWgABytes = 16 * kWgLineBytes + 2048 + 256;
 constexpr int kDyRing = 4;                // dY tiles in flight ahead of the wgrad MMAs
 
 __device__ __forceinline__ void named_bar(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
@@ -50,6 +56,35 @@ __device__ __forceinline__ uint64_t desc_noswz(uint32_t addr, uint32_t lbo, uint
     d |= (uint64_t)1 << 46;
     return d;
 }
+
+// Tile walker without per-tile integer divisions: tiles advance by a fixed stride, so (ht, d, n) advance by fixed deltas with carries.
+struct TileIter {
+    int tile, ht, d, n;
+    int s_ht, s_d, s_n, stride;
+    __device__ __forceinline__ TileIter(const Geom& g, int first, int stride_) : tile(first), stride(stride_) {
+        ht = first % g.h_tiles;
+        const int t2 = first / g.h_tiles;
+        d = t2 % g.Do;
+        n = t2 / g.Do;
+        s_ht = stride_ % g.h_tiles;
+        const int q = stride_ / g.h_tiles;
+        s_d = q % g.Do;
+        s_n = q / g.Do;
+    }
+    __device__ __forceinline__ bool valid(const Geom& g) const { return tile < g.total_tiles; }
+    __device__ __forceinline__ int h0() const { return ht * 2; }
+    __device__ __forceinline__ int lines(const Geom& g) const { return min(2, g.Ho - ht * 2); }
+    __device__ __forceinline__ void next(const Geom& g) {
+        tile += stride;
+        ht += s_ht;
+        int c = 0;
+        if (ht >= g.h_tiles) { ht -= g.h_tiles; c = 1; }
+        d += s_d + c;
+        c = 0;
+        if (d >= g.Do) { d -= g.Do; c = 1; }
+        n += s_n + c;
+    }
+};
 
 __device__ __forceinline__ void decode_tile(const Geom& g, int tile, int& n, int& d, int& h0, int& lines) {
     const int ht = tile % g.h_tiles;
@@ -68,14 +103,12 @@ __device__ __forceinline__ const uint8_t* plane_src(const uint8_t* __restrict__ 
 // (aligned superset of the run) into raw slot `tile_seq % kRawRing`
 __device__ __forceinline__ void raw_producer_loop(const uint8_t* __restrict__ x, const Geom& g, uint8_t* raws, uint64_t* raw_full, uint64_t* raw_empty) {
     const uintptr_t x_end = (reinterpret_cast<uintptr_t>(x) + (uintptr_t)g.in_bytes + 15) & ~(uintptr_t)15;
-    for (int i = 0;; ++i) {
-        const int tile = blockIdx.x + i * gridDim.x;
-        if (tile >= g.total_tiles) break;
+    TileIter t(g, blockIdx.x, gridDim.x);
+    for (int i = 0; t.valid(g); ++i, t.next(g)) {
         const int slot = i % kRawRing;
-        int n, d, h0, lines;
-        decode_tile(g, tile, n, d, h0, lines);
+        const int n = t.n;
         tc::mbar_wait(&raw_empty[slot], ((i / kRawRing) & 1) ^ 1);
-        const int z0 = 2 * d, y0 = 2 * h0;
+        const int z0 = 2 * t.d, y0 = 2 * t.h0();
         const int planes = min(kPlanes, g.Di - z0);
         uint32_t total = 0, sz[kPlanes];
         const uint8_t* src[kPlanes];
@@ -90,6 +123,7 @@ __device__ __forceinline__ void raw_producer_loop(const uint8_t* __restrict__ x,
                 total += sz[p];
             }
         }
+        if (g.dbg & 8) { tc::mbar_arrive(&raw_full[slot]); continue; }
         tc::mbar_expect_tx(&raw_full[slot], total);
 #pragma unroll
         for (int p = 0; p < kPlanes; ++p)
@@ -100,40 +134,51 @@ __device__ __forceinline__ void raw_producer_loop(const uint8_t* __restrict__ x,
 // raw u8 rows -> 12 parity-interleaved bf16 lines.  One item = TWO adjacent s2d positions (32 bytes): for each of the
 // 4 (pd,ph) input rows one unaligned 4-byte read (two aligned words + funnel shift) yields x[4i .. 4i+3]; bytes become
 // floats without the slow I2F path: float(0x4B000000 | b) - 2^23 = b exactly (one PRMT + one FADD), then the scale multiply.
-__device__ __forceinline__ void build_lines(const uint8_t* __restrict__ x, const uint8_t* __restrict__ raw, uint8_t* __restrict__ a_buf,
-                                            const Geom& g, int n, int d, int h0, int gt) {
-    const int z0 = 2 * d, y0 = 2 * h0;
-    const int rows_ok = min(kRows, g.Hi - y0);
-    const int planes_ok = min(kPlanes, g.Di - z0);
-    const uint32_t mis0 = (uint32_t)(reinterpret_cast<uintptr_t>(plane_src(x, g, n, z0, y0)) & 15);
-    const uint32_t psz = (uint32_t)((size_t)g.Hi * g.Wi) & 15u;       // plane-to-plane change of the 16-byte misalignment
-    static_assert(kLines * 32 == 3 * 128, "three items per staging thread");
+// A thread always handles the same three items, so everything that does not depend on the tile is computed once (LineCtx).
+struct LineCtx {
+    uint32_t base[3][4];     // plane*raw_pitch + row*Wi + 4*i4   per (item, pp)
+    uint32_t dst[3];         // byte offset of the item inside a line buffer
+    uint32_t bmask[3];       // valid bytes of the 4-byte group (row end)
+    uint32_t psz;            // plane-to-plane change of the 16-byte misalignment
+    __device__ __forceinline__ LineCtx(const Geom& g, int gt, int line_bytes) {
+        psz = (uint32_t)((size_t)g.Hi * g.Wi) & 15u;
+#pragma unroll
+        for (int it = 0; it < 3; ++it) {
+            const int item = gt + it * 128;
+            const int i4 = item & 31, L = item >> 5, jd = L >> 2, hl = L & 3;
+            const int nvalid = min(4, max(0, g.Wi - 4 * i4));
+            bmask[it] = nvalid >= 4 ? 0xffffffffu : ((1u << (8 * nvalid)) - 1u);
+            dst[it] = L * line_bytes + i4 * 32;
+#pragma unroll
+            for (int pp = 0; pp < 4; ++pp) base[it][pp] = (2 * jd + (pp >> 1)) * g.raw_pitch + (2 * hl + (pp & 1)) * g.Wi + 4 * i4;
+        }
+    }
+};
+
+__device__ __forceinline__ void build_lines(const LineCtx& c, uint32_t mis0, int rows_ok, int planes_ok, const uint8_t* __restrict__ raw,
+                                            uint8_t* __restrict__ a_buf, float scale, int gt) {
 #pragma unroll
     for (int it = 0; it < 3; ++it) {                       // fully unrolled: three independent load->convert->store chains in flight
-        const int item = gt + it * 128;
-        const int i4 = item & 31, L = item >> 5;          // 4-byte group within the row, line (jd*4 + hl)
-        const int jd = L >> 2, hl = L & 3;
-        const int nvalid = min(4, max(0, g.Wi - 4 * i4));
-        const uint32_t bmask = nvalid >= 4 ? 0xffffffffu : ((1u << (8 * nvalid)) - 1u);
+        const int L = (gt + it * 128) >> 5, jd = L >> 2, hl = L & 3;
         uint32_t lo[4], hi[4];
 #pragma unroll
         for (int pp = 0; pp < 4; ++pp) {                   // pp = pd*2 + ph  -> channels (pd,ph,0), (pd,ph,1)
             const int plane = 2 * jd + (pp >> 1), row = 2 * hl + (pp & 1);
             uint32_t four = 0;
             if (plane < planes_ok && row < rows_ok) {
-                const uint32_t a = plane * g.raw_pitch + ((mis0 + plane * psz) & 15u) + row * g.Wi + 4 * i4;
+                const uint32_t a = c.base[it][pp] + ((mis0 + plane * c.psz) & 15u);
                 const uint32_t* rw = reinterpret_cast<const uint32_t*>(raw + (a & ~3u));
-                four = __funnelshift_r(rw[0], rw[1], (a & 3u) * 8) & bmask;
+                four = __funnelshift_r(rw[0], rw[1], (a & 3u) * 8) & c.bmask[it];
             }
-            const float f0 = (__uint_as_float(__byte_perm(four, 0x4B000000u, 0x7650)) - 8388608.f) * g.scale;
-            const float f1 = (__uint_as_float(__byte_perm(four, 0x4B000000u, 0x7651)) - 8388608.f) * g.scale;
-            const float f2 = (__uint_as_float(__byte_perm(four, 0x4B000000u, 0x7652)) - 8388608.f) * g.scale;
-            const float f3 = (__uint_as_float(__byte_perm(four, 0x4B000000u, 0x7653)) - 8388608.f) * g.scale;
+            const float f0 = (__uint_as_float(__byte_perm(four, 0x4B000000u, 0x7650)) - 8388608.f) * scale;
+            const float f1 = (__uint_as_float(__byte_perm(four, 0x4B000000u, 0x7651)) - 8388608.f) * scale;
+            const float f2 = (__uint_as_float(__byte_perm(four, 0x4B000000u, 0x7652)) - 8388608.f) * scale;
+            const float f3 = (__uint_as_float(__byte_perm(four, 0x4B000000u, 0x7653)) - 8388608.f) * scale;
             __nv_bfloat162 p0 = __floats2bfloat162_rn(f0, f1), p1 = __floats2bfloat162_rn(f2, f3);
             lo[pp] = *reinterpret_cast<uint32_t*>(&p0);
             hi[pp] = *reinterpret_cast<uint32_t*>(&p1);
         }
-        uint4* dst = reinterpret_cast<uint4*>(a_buf + L * kLineBytes + i4 * 32);
+        uint4* dst = reinterpret_cast<uint4*>(a_buf + c.dst[it]);
         dst[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
         dst[1] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
     }
@@ -142,20 +187,23 @@ __device__ __forceinline__ void build_lines(const uint8_t* __restrict__ x, const
 // staging warps (0-7): two groups alternate tiles.  Raw bytes arrive by bulk copy kRawRing tiles ahead; a group converts
 // them into the line buffer `i % kARing` as soon as the MMAs that read that buffer kARing tiles ago have finished.
 __device__ __forceinline__ void staging_loop(const uint8_t* __restrict__ x, const Geom& g, uint8_t* a_bufs, uint8_t* raws, uint64_t* a_full, uint64_t* a_empty,
-                                             uint64_t* raw_full, uint64_t* raw_empty) {
+                                             uint64_t* raw_full, uint64_t* raw_empty, int line_bytes, int a_bytes) {
     const int grp = threadIdx.x >> 7, gt = threadIdx.x & 127;
-    for (int i = grp;; i += 2) {
-        const int tile = blockIdx.x + i * gridDim.x;
-        if (tile >= g.total_tiles) break;
+    const LineCtx ctx(g, gt, line_bytes);
+    TileIter t(g, blockIdx.x + grp * gridDim.x, 2 * gridDim.x);
+    for (int i = grp; t.valid(g); i += 2, t.next(g)) {
         const int buf = i % kARing, slot = i % kRawRing;
-        int n, d, h0, lines;
-        decode_tile(g, tile, n, d, h0, lines);
+        const int z0 = 2 * t.d, y0 = 2 * t.h0();
+        const uint32_t mis0 = (uint32_t)(reinterpret_cast<uintptr_t>(plane_src(x, g, t.n, z0, y0)) & 15);
         tc::mbar_wait(&raw_full[slot], (i / kRawRing) & 1);
         tc::mbar_wait(&a_empty[buf], ((i / kARing) & 1) ^ 1);
-        build_lines(x, raws + slot * kPlanes * g.raw_pitch, a_bufs + buf * kABytes, g, n, d, h0, gt);
-        tc::fence_proxy_async_smem();
-        tc::mbar_arrive(&a_full[buf]);
-        tc::mbar_arrive(&raw_empty[slot]);
+        if (!(g.dbg & 1)) build_lines(ctx, mis0, min(kRows, g.Hi - y0), min(kPlanes, g.Di - z0), raws + slot * kPlanes * g.raw_pitch, a_bufs + buf * a_bytes, g.scale, gt);
+        if (!(g.dbg & 16)) tc::fence_proxy_async_smem();
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) {                   // one arrival per warp (128 same-address shared atomics per tile were a bottleneck)
+            tc::mbar_arrive(&a_full[buf]);
+            tc::mbar_arrive(&raw_empty[slot]);
+        }
     }
 }
 
@@ -189,9 +237,9 @@ __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __r
     tc::fence_proxy_async_smem();
     if (threadIdx.x == 0) {
         tc::tma_prefetch_desc(&tm_y);
-        for (int i = 0; i < kARing; ++i) { tc::mbar_init(&a_full[i], 128); tc::mbar_init(&a_empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { tc::mbar_init(&t_full[i], 1); tc::mbar_init(&t_empty[i], 128); }
-        for (int i = 0; i < kRawRing; ++i) { tc::mbar_init(&raw_full[i], 1); tc::mbar_init(&raw_empty[i], 128); }
+        for (int i = 0; i < kARing; ++i) { tc::mbar_init(&a_full[i], 4); tc::mbar_init(&a_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { tc::mbar_init(&t_full[i], 1); tc::mbar_init(&t_empty[i], 4); }
+        for (int i = 0; i < kRawRing; ++i) { tc::mbar_init(&raw_full[i], 1); tc::mbar_init(&raw_empty[i], 4); }
         tc::mbar_fence_init();
     }
     if (warp == 8) tc::tmem_alloc<128>(tmem_ptr);
@@ -201,7 +249,7 @@ __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __r
     const uint32_t tmem_base = *tmem_ptr;
 
     if (warp < 8) {
-        staging_loop(x, g, a_bufs, raws, a_full, a_empty, raw_full, raw_empty);
+        staging_loop(x, g, a_bufs, raws, a_full, a_empty, raw_full, raw_empty, kLineBytes, kABytes);
     } else if (warp == 17) {
         if (lane == 0) raw_producer_loop(x, g, raws, raw_full, raw_empty);
     } else if (warp == 8) {
@@ -242,12 +290,10 @@ __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __r
         float s1[8], s2[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) s1[j] = s2[j] = 0.f;
-        for (int i = e;; i += 2) {
-            const int tile = blockIdx.x + i * gridDim.x;
-            if (tile >= g.total_tiles) break;
+        TileIter t(g, blockIdx.x + e * gridDim.x, 2 * gridDim.x);
+        for (int i = e; t.valid(g); i += 2, t.next(g)) {
             const uint32_t u = i >> 1;
-            int n, d, h0, lines;
-            decode_tile(g, tile, n, d, h0, lines);
+            const int n = t.n, d = t.d, h0 = t.h0(), lines = t.lines(g);
             if (et == 0) tc::tma_store_wait_read();      // this group's previous store has drained the staging buffer
             named_bar(3 + e, 128);
             tc::mbar_wait(&t_full[e], u & 1);
@@ -256,7 +302,8 @@ __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __r
                 float v[64];
                 tc::tmem_ld64(tmem_base + e * 64 + ((uint32_t)(q * 32) << 16), v);
                 tc::tc_fence_before();
-                tc::mbar_arrive(&t_empty[e]);            // accumulator is in registers: the next MMA may start
+                __syncwarp();
+                if (lane == 0) tc::mbar_arrive(&t_empty[e]);   // accumulator is in registers: the next MMA may start
                 uint8_t* blk = stg + row * 128;
 #pragma unroll
                 for (int c = 0; c < 64; c += 8) {
@@ -323,22 +370,22 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __res
                                                             float* __restrict__ partials /* [grid][3][128][64] */, const Geom g) {
     extern __shared__ __align__(1024) uint8_t smem[];
     if ((tc::smem_u32(smem) & 1023u) != 0u) __trap();
-    uint8_t* dy_tiles = smem;                              // [kDyRing][128 pos][64 co] swizzled; rows 59..63 / 123..127 stay zero
-    uint8_t* a_bufs = dy_tiles + kDyRing * kT16;           // [kARing][kABytes] s2d lines
-    uint64_t* bars = reinterpret_cast<uint64_t*>(a_bufs + kARing * kABytes);
+    uint8_t* dy_tiles = smem;                              // [kDyRing][128 pos][64 co] swizzled; K row = line*65 + w, the other rows stay zero
+    uint8_t* a_bufs = dy_tiles + kDyRing * kT16;           // [kARing][kWgABytes] s2d lines
+    uint64_t* bars = reinterpret_cast<uint64_t*>(a_bufs + kARing * kWgABytes);
     uint64_t *a_full = bars, *a_empty = bars + kARing, *t_full = bars + 2 * kARing, *dy_full = t_full + 1, *dy_empty = dy_full + kDyRing;
     uint64_t *raw_full = dy_empty + kDyRing, *raw_empty = raw_full + kRawRing;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(raw_empty + kRawRing);
     uint8_t* raws = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(tmem_ptr + 4) + 15) & ~(uintptr_t)15);   // 16-byte vector stores
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-    for (int i = threadIdx.x; i < (kDyRing * kT16 + kARing * kABytes) / 16; i += kThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = threadIdx.x; i < (kDyRing * kT16 + kARing * kWgABytes) / 16; i += kThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
     tc::fence_proxy_async_smem();
     if (threadIdx.x == 0) {
         tc::tma_prefetch_desc(&tm_dy);
-        for (int i = 0; i < kARing; ++i) { tc::mbar_init(&a_full[i], 128); tc::mbar_init(&a_empty[i], 1); }
+        for (int i = 0; i < kARing; ++i) { tc::mbar_init(&a_full[i], 4); tc::mbar_init(&a_empty[i], 1); }
         for (int i = 0; i < kDyRing; ++i) { tc::mbar_init(&dy_full[i], 1); tc::mbar_init(&dy_empty[i], 1); }
-        for (int i = 0; i < kRawRing; ++i) { tc::mbar_init(&raw_full[i], 1); tc::mbar_init(&raw_empty[i], 128); }
+        for (int i = 0; i < kRawRing; ++i) { tc::mbar_init(&raw_full[i], 1); tc::mbar_init(&raw_empty[i], 4); }
         tc::mbar_init(t_full, 1);
         tc::mbar_fence_init();
     }
@@ -349,7 +396,7 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __res
     const uint32_t tmem_base = *tmem_ptr;
 
     if (warp < 8) {
-        staging_loop(x, g, a_bufs, raws, a_full, a_empty, raw_full, raw_empty);
+        staging_loop(x, g, a_bufs, raws, a_full, a_empty, raw_full, raw_empty, kWgLineBytes, kWgABytes);
     } else if (warp == 8) {
         if (lane == 0) {
             constexpr uint32_t idesc = tc::make_idesc_bf16(128, 64, 1, 1);
@@ -363,15 +410,15 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __res
                 tc::mbar_wait(&dy_full[slot], (i / kDyRing) & 1);
                 tc::tc_fence_after();
                 const uint32_t dy_addr = tc::smem_u32(dy_tiles + slot * kT16);
-                const uint32_t a_addr = tc::smem_u32(a_bufs + b * kABytes);
+                const uint32_t a_addr = tc::smem_u32(a_bufs + b * kWgABytes);
 #pragma unroll 1
                 for (int ks = 0; ks < 8; ++ks) {          // 16 positions per MMA
                     // B = dY, MN-major SW128 (N = 64 co = one chunk; 8-position groups 1 KiB apart)
                     const uint64_t db = tc::make_smem_desc_sw128(dy_addr + ks * 2048, kT16, 1024);
 #pragma unroll
-                    for (int jw = 0; jw < 3; ++jw) {
+                    for (int jw = 0; jw < ((g.dbg & 2) ? (ks == 0 ? 1 : 0) : 3); ++jw) {
                         // A = lines, MN-major no swizzle: M chunks (lines) 1 KiB apart (SBO), K groups (8 positions) 128 B apart (LBO)
-                        const uint64_t da = desc_noswz(a_addr + jw * 16 + ks * 256, 128, kLineBytes);
+                        const uint64_t da = desc_noswz(a_addr + jw * 16 + ks * 256, 128, kWgLineBytes);
                         tc::umma_bf16(tmem_base + jw * 64, da, db, idesc, (i | ks) != 0);
                     }
                 }
@@ -382,17 +429,16 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __res
         }
     } else {
         if (warp == 9 && lane == 0) {
-            for (int i = 0;; ++i) {
-                const int tile = blockIdx.x + i * gridDim.x;
-                if (tile >= g.total_tiles) break;
+            TileIter t(g, blockIdx.x, gridDim.x);
+            for (int i = 0; t.valid(g); ++i, t.next(g)) {
                 const int slot = i % kDyRing;
-                int n, d, h0, lines;
-                decode_tile(g, tile, n, d, h0, lines);
+                const int n = t.n, d = t.d, h0 = t.h0();
                 tc::mbar_wait(&dy_empty[slot], ((i / kDyRing) & 1) ^ 1);     // dY runs kDyRing tiles ahead of the MMAs
                 // one box per output line (rows 0..Wo-1 and 64..64+Wo-1); a line past Ho is zero-filled by the hardware
+                if (g.dbg & 4) { tc::mbar_arrive(&dy_full[slot]); continue; }
                 tc::mbar_expect_tx(&dy_full[slot], (uint32_t)(2 * g.Wo * 128));
                 tc::tma_load_5d(&tm_dy, &dy_full[slot], dy_tiles + slot * kT16, 0, 0, h0, d, n);
-                tc::tma_load_5d(&tm_dy, &dy_full[slot], dy_tiles + slot * kT16 + 64 * 128, 0, 0, h0 + 1, d, n);
+                tc::tma_load_5d(&tm_dy, &dy_full[slot], dy_tiles + slot * kT16 + kWgPitch * 128, 0, 0, h0 + 1, d, n);   // K rows 65.. = second line
             }
         }
         if (warp == 10 && lane == 0) raw_producer_loop(x, g, raws, raw_full, raw_empty);
@@ -421,18 +467,20 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __res
     }
 }
 
-// dW[co][kd][kh][kw] = sum_cta partials[cta][jw][(jd*4+jh)*8 + c][co]   with kd = 2jd+pd, kh = 2jh+ph, kw = 2jw+pw, c = pd*4+ph*2+pw
+// dW[co][kd][kh][kw] = sum_cta partials[cta][jw][(jd*4+jh)*8 + c][co]   with kd = 2jd+pd, kh = 2jh+ph, kw = 2jw+pw, c = pd*4+ph*2+pw.
+// Threads run over the partial layout (co fastest) so the reads of every CTA's slab are coalesced; the 8000 results scatter.
 __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ partials, int n_cta, float* __restrict__ grad, float* __restrict__ grad_bias) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < 64 && grad_bias != nullptr) grad_bias[i] = 0.f;   // BatchNorm follows this conv: the bias gradient is identically zero
-    if (i >= 64 * 125) return;
-    const int co = i / 125, tap = i % 125;
-    const int kd = tap / 25, kh = (tap / 5) % 5, kw = tap % 5;
-    const int row = ((kd >> 1) * 4 + (kh >> 1)) * 8 + ((kd & 1) << 2) + ((kh & 1) << 1) + (kw & 1);
-    const int jw = kw >> 1;
+    if (i >= 3 * 128 * 64) return;
+    const int co = i & 63, row = (i >> 6) & 127, jw = i >> 13;
+    const int L = row >> 3, c = row & 7;
+    const int jd = L >> 2, jh = L & 3;
+    const int kd = 2 * jd + (c >> 2), kh = 2 * jh + ((c >> 1) & 1), kw = 2 * jw + (c & 1);
+    if (jd > 2 || jh > 2 || kd > 4 || kh > 4 || kw > 4) return;
     float acc = 0.f;
-    for (int c = 0; c < n_cta; ++c) acc += partials[(((size_t)c * 3 + jw) * 128 + row) * 64 + co];
-    grad[i] = acc;
+    for (int q = 0; q < n_cta; ++q) acc += partials[(size_t)q * (3 * 128 * 64) + i];
+    grad[co * 125 + (kd * 5 + kh) * 5 + kw] = acc;
 }
 
 static int make_geom(Geom& g, int N, int Di, int Hi, int Wi, float scale) {
@@ -443,10 +491,11 @@ static int make_geom(Geom& g, int N, int Di, int Hi, int Wi, float scale) {
     g.total_tiles = N * g.Do * g.h_tiles;
     g.raw_pitch = ((kRows * Wi + 15 + 15) / 16 + 1) * 16;
     g.in_bytes = (long long)N * Di * Hi * Wi;
+    { const char* e = getenv("NIDT_S2D_DEBUG"); g.dbg = e ? atoi(e) : 0; }
     return 0;
 }
 static size_t smem_fprop(const Geom& g) { return 2 * (size_t)kT16 + 36 * 1024 + kARing * (size_t)kABytes + 8 * (2 * kARing + 4 + 2 * kRawRing) + 16 + 256 + 2 * 16 * 2 * 64 * 4 + kRawRing * (size_t)kPlanes * g.raw_pitch + 64; }
-static size_t smem_wgrad(const Geom& g) { return kDyRing * (size_t)kT16 + kARing * (size_t)kABytes + 8 * (2 * kARing + 1 + 2 * kDyRing + 2 * kRawRing) + 32 + kRawRing * (size_t)kPlanes * g.raw_pitch + 64; }
+static size_t smem_wgrad(const Geom& g) { return kDyRing * (size_t)kT16 + kARing * (size_t)kWgABytes + 8 * (2 * kARing + 1 + 2 * kDyRing + 2 * kRawRing) + 32 + kRawRing * (size_t)kPlanes * g.raw_pitch + 64; }
 
 }  // namespace s2d
 }  // namespace nidt
@@ -491,7 +540,7 @@ NIDT_API int nidt_conv_in_s2d_wgrad(const void* x, const void* dy, float* grad, 
     NIDT_CUDA_CHECK(cudaFuncSetAttribute(s2d::wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     s2d::wgrad_kernel<<<grid, s2d::kThreads, smem, s>>>((const uint8_t*)x, tdy, scratch, g);
     NIDT_LAUNCH_CHECK();
-    s2d::wgrad_reduce_kernel<<<(64 * 125 + 255) / 256, 256, 0, s>>>(scratch, grid, grad, grad_bias);
+    s2d::wgrad_reduce_kernel<<<(3 * 128 * 64 + 255) / 256, 256, 0, s>>>(scratch, grid, grad, grad_bias);
     NIDT_LAUNCH_CHECK();
     return 0;
 }

@@ -388,15 +388,16 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv3d_wgrad_tc_kernel(
 // optional saliency epilogue: scores[co][ci][tap] += scale * |dW * W|   (ref K11: snip.py:60-71)
 __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ partials, int splits, int taps, int Cout, int Cin,
                                                            float* __restrict__ grad) {
+    // threads follow the partial layout [tap][co][ci] (ci fastest): coalesced reads of every split, strided writes of the result
     const int64_t total = (int64_t)Cout * Cin * taps;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int t = (int)(i % taps);
-        const int64_t r = i / taps;
-        const int ci = (int)(r % Cin);
-        const int co = (int)(r / Cin);
+        const int ci = (int)(i % Cin);
+        const int64_t r = i / Cin;
+        const int co = (int)(r % Cout);
+        const int t = (int)(r / Cout);
         float acc = 0.f;
-        for (int s = 0; s < splits; ++s) acc += partials[(((size_t)s * taps + t) * Cout + co) * Cin + ci];
-        grad[i] = acc;
+        for (int s = 0; s < splits; ++s) acc += partials[(size_t)s * total + i];
+        grad[((size_t)co * Cin + ci) * taps + t] = acc;
     }
 }
 
