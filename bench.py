@@ -229,10 +229,17 @@ def make_device_stager(store, device, batch):
             self.h2d_bytes = 0
             self.vol = store._cache.to(device)
             self.lab = torch.from_numpy(store.labels).to(device)
+            # index batches go through a ring of pinned buffers: a pageable H2D copy would make the host wait for the stream
+            self.ring = [torch.empty(batch, dtype=torch.int64).pin_memory() for _ in range(128)]
+            self.k = 0
 
         def iterate(self, loader):
             for b in loader:
-                idx = torch.sort(b[0])[0].to(self.device, non_blocking=True)
+                n = b[0].numel()
+                buf = self.ring[self.k % len(self.ring)]
+                self.k += 1
+                buf[:n] = torch.sort(b[0])[0]
+                idx = buf[:n].to(self.device, non_blocking=True)
                 yield self.vol.index_select(0, idx), self.lab.index_select(0, idx)
 
     return DeviceStager()
