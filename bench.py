@@ -47,6 +47,7 @@ def parse():
     p.add_argument("--agg", default="auto", choices=["auto", "fused", "nccl"])
     p.add_argument("--shape", default="121,145,121")
     p.add_argument("--skip-e2e", action="store_true")
+    p.add_argument("--algo", default="salientgrads", choices=["salientgrads", "fedavg"], help="fedavg = BASELINE.json config 2 (ours arm only)")
     return p.parse_args()
 
 
@@ -101,7 +102,7 @@ def make_fl_args(a, world):
         epochs=a.epochs, client_num_in_total=a.clients, client_num_per_round=a.clients, frac=1.0, momentum=0.0,
         comm_round=a.steps + a.warmup, frequency_of_the_test=1, gpu=0, ci=0, dense_ratio=a.dense_ratio, anneal_factor=0.5,
         seed=1024, cs="v0", itersnip_iteration=1, stratified_sampling=False, active=1.0, snip_mask=True, erk_power_scale=1.0,
-        final_finetune=False)
+        final_finetune=False, loss_sync="round")
 
 
 def build_store(a, shape, pin):
@@ -154,12 +155,14 @@ def run_ours(a):
             if a.engine == "b200":
                 raise
     trainer = SlabTrainer(model, fl_args, logger, device=device, store=store, engine=engine)
-    api = SalientGradsAPI(dataset, device, fl_args, trainer, logger, dist=ctx, agg_mode=a.agg)
+    from neuroimagedisttraining_b200.fl import FedAvgAPI
+    api = (SalientGradsAPI if a.algo == "salientgrads" else FedAvgAPI)(dataset, device, fl_args, trainer, logger, dist=ctx, agg_mode=a.agg)
     api.w_init = api.w_global.clone()
 
     torch.cuda.synchronize(device)
     t0 = time.perf_counter()
-    api.mask = api.generate_global_mask_snip()
+    if a.algo == "salientgrads":
+        api.mask = api.generate_global_mask_snip()
     torch.cuda.synchronize(device)
     mask_s = time.perf_counter() - t0
 
@@ -198,12 +201,12 @@ def run_ours(a):
     stat = api.finalize_stats()
     if ctx.is_main:
         out = {
-            "metric": "samples_per_s_salientgrads_alexnet3d_abcd_round", "value": samples_per_round * a.steps / t_dev,
+            "metric": "samples_per_s_%s_alexnet3d_abcd_round" % a.algo, "value": samples_per_round * a.steps / t_dev,
             "unit": "samples/s", "n_gpus": ctx.world_size, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": 1e3 * t_dev / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "bf16" if engine_name == "b200" else "fp32(tf32 conv)", "data": "synthetic 8-bit ABCD-shape volumes, random-init weights",
             "impl": "ours", "engine": engine_name,
-            "config": {"model": "AlexNet3D_Dropout(1 logit)", "algorithm": "SalientGrads dense_ratio=%g" % a.dense_ratio,
+            "config": {"model": "AlexNet3D_Dropout(1 logit)", "algorithm": ("SalientGrads dense_ratio=%g" % a.dense_ratio) if a.algo == "salientgrads" else "FedAvg",
                        "clients": a.clients, "clients_per_round": a.clients, "local_epochs": a.epochs, "batch": a.batch,
                        "global_batch": a.batch, "seq_len": "x".join(map(str, shape)), "train_samples_per_round": samples_per_round,
                        "sgd_steps_per_round": samples_per_round // a.batch, "eval_samples_per_round": 2 * a.clients * (a.per_site // 5),

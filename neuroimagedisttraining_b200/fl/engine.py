@@ -114,11 +114,12 @@ class TorchEngine:
             self.grad.flat.mul_(grad_mask)
         ops.masked_sgd_step(self.slab.params_flat, self.grad.flat, mom, mask, hp.lr, hp.momentum, hp.wd, hp.clip_norm, first_step)
 
-    def pop_mean_loss(self) -> float:
-        v = float(self.loss_acc.item()) / max(1, self.loss_steps)
-        self.loss_acc.zero_()
+    def pop_mean_loss(self, sync: bool = True):
+        """Mean loss since the last call; ``sync=False`` returns a 0-d device tensor (no host synchronisation)."""
+        mean = self.loss_acc / max(1, self.loss_steps)
+        self.loss_acc = torch.zeros_like(self.loss_acc)
         self.loss_steps = 0
-        return v
+        return float(mean.item()) if sync else mean
 
     # -- evaluation -----------------------------------------------------------------------------
     @torch.no_grad()

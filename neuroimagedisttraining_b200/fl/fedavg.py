@@ -28,6 +28,7 @@ class FedAvgAPI(FedAPIBase):
                 self.stat_info["sum_training_flops"] += training_flops
                 self._add_comm_params(num_comm_params)
         self._aggregate(w_locals, training_num, mask=None)
+        self.model_trainer.flush_losses()
         if evaluate and round_idx % max(1, int(getattr(args, "frequency_of_the_test", 1))) == 0:
             self._test_on_all_clients(self.w_global, self.personal_slabs(), round_idx)
         self._maybe_checkpoint(round_idx)

@@ -100,6 +100,7 @@ class SlabTrainer(ModelTrainer):
         self._stagers: Dict[int, BatchStager] = {}
         self.double_sigmoid_eval = True
         self.step_counter = 0
+        self.pending_losses = []
 
     # ------------------------------------------------------------------ slab plumbing
     @property
@@ -265,10 +266,9 @@ class SlabTrainer(ModelTrainer):
         n_epochs = int(epochs if epochs is not None else args.epochs)
 
         def end_epoch(epoch):
-            mean_loss = self.engine.pop_mean_loss()
-            losses.append(mean_loss)
-            if self.logger is not None:
-                self.logger.info('Client Index = {}\tEpoch: {}\tLoss: {:.6f}'.format(self.id, epoch, mean_loss))
+            # the per-epoch loss stays on the device; it is read (one sync) after the client's last epoch, or at the end of the
+            # round when args.loss_sync == "round" (the reference syncs on loss.item() every step, my_model_trainer.py:226)
+            losses.append((self.id, epoch, self.engine.pop_mean_loss(sync=False)))
 
         # all epochs are one batch stream, so the host->device prefetch runs across epoch boundaries
         cur = 0
@@ -286,7 +286,23 @@ class SlabTrainer(ModelTrainer):
             self.step_counter += 1
         if n_epochs > 0:
             end_epoch(cur)
+        self.pending_losses.extend(losses)
+        if getattr(args, "loss_sync", "client") != "round":
+            return self.flush_losses()
         return losses
+
+    def flush_losses(self):
+        """Read the queued per-epoch losses (one host sync) and log them in the reference's format."""
+        if not self.pending_losses:
+            return []
+        vals = torch.stack([l.detach().float().reshape(()) for _, _, l in self.pending_losses]).tolist()
+        out = []
+        for (cid, epoch, _), v in zip(self.pending_losses, vals):
+            out.append(v)
+            if self.logger is not None:
+                self.logger.info('Client Index = {}\tEpoch: {}\tLoss: {:.6f}'.format(cid, epoch, v))
+        self.pending_losses = []
+        return out
 
     # --------------------------------------------------------------------------- test
     def test(self, test_data, device=None, args=None):

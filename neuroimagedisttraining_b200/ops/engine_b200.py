@@ -356,11 +356,12 @@ class B200Engine:
         flat_ops.masked_sgd_step(self.slab.params_flat, self.grad.flat, mom, mask, hp.lr, hp.momentum, hp.wd, hp.clip_norm, first_step)
         self._packed_dirty = True
 
-    def pop_mean_loss(self) -> float:
-        v = float(self.loss_acc.item()) / max(1, self.loss_steps)
-        self.loss_acc.zero_()
+    def pop_mean_loss(self, sync: bool = True):
+        """Mean loss since the last call; ``sync=False`` returns a 0-d device tensor (no host synchronisation)."""
+        mean = self.loss_acc / max(1, self.loss_steps)
+        self.loss_acc = torch.zeros_like(self.loss_acc)
         self.loss_steps = 0
-        return v
+        return float(mean.item()) if sync else mean
 
     def eval_batch(self, x, y, counters, double_sigmoid: bool = True) -> None:
         y = y.to(self.device, torch.float32).contiguous()
