@@ -52,16 +52,60 @@ def parse():
 
 
 class ClockSampler:
-    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    """Samples SM clocks / throttle reasons while the timed region runs.
+
+    NVML is polled from a thread every 20 ms (a timed region at 8 GPUs can be shorter than one `nvidia-smi -lms 200`
+    period); if NVML cannot be initialised the nvidia-smi loop of the profiling recipe is used instead."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    REASON_BITS = (("sw_power_cap", 0x4), ("hw_slowdown", 0x8), ("sw_thermal_slowdown", 0x20), ("hw_thermal_slowdown", 0x40),
+                   ("hw_power_brake_slowdown", 0x80))
 
     def __init__(self, gpu_index: int):
         self.gpu = gpu_index
-        self.rows = []
+        self.rows = []          # (sm_mhz, max_mhz, [reasons])
         self.proc = None
+        self.nvml = None
+        self.stop_flag = threading.Event()
+        self.thr = None
+
+    def _nvml_handle(self):
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            uuid = str(torch.cuda.get_device_properties(self.gpu).uuid)
+            uuid = uuid if uuid.startswith("GPU-") else "GPU-" + uuid
+            h = pynvml.nvmlDeviceGetHandleByUUID(uuid)
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.gpu)
+        self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+        return pynvml, h
+
+    def _nvml_sample(self):
+        p, h = self.nvml
+        sm = float(p.nvmlDeviceGetClockInfo(h, p.NVML_CLOCK_SM))
+        try:
+            bits = int(p.nvmlDeviceGetCurrentClocksEventReasons(h))
+        except Exception:
+            bits = int(p.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+        self.rows.append((sm, self.max_mhz, [n for n, b in self.REASON_BITS if bits & b]))
+
+    def _nvml_loop(self):
+        while not self.stop_flag.is_set():
+            try:
+                self._nvml_sample()
+            except Exception:
+                pass
+            self.stop_flag.wait(0.02)
 
     def start(self):
+        try:
+            self.nvml = self._nvml_handle()
+            self.thr = threading.Thread(target=self._nvml_loop, daemon=True)
+            self.thr.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
                                           "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -71,29 +115,37 @@ class ClockSampler:
             self.proc = None
 
     def _read(self):
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
-
-    def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        for r in self.rows:
+            r = [c.strip() for c in line.split(",")]
             try:
-                sm.append(float(r[1])); mx.append(float(r[2]))
-                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
-                    if v.lower().startswith("active"):
-                        reasons.add(name)
+                self.rows.append((float(r[1]), float(r[2]), [n for n, v in zip(names, r[4:8]) if v.lower().startswith("active")]))
             except Exception:
                 pass
+
+    def stop(self):
+        """Call BEFORE the closing synchronize so the last sample is still under load."""
+        if self.nvml is not None:
+            try:
+                self._nvml_sample()
+            except Exception:
+                pass
+            self.stop_flag.set()
+            self.thr.join(timeout=1)
+        elif self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+        else:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml and nvidia-smi unavailable"], "samples": 0}
+        sm = [r[0] for r in self.rows]
+        mx = [r[1] for r in self.rows]
+        reasons = sorted({n for r in self.rows for n in r[2]})
         load = [s for s in sm if s > 0.5 * max(sm)] if sm else []
         return {"sm_mhz": statistics.median(load) if load else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
 def make_fl_args(a, world):
