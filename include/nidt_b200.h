@@ -123,6 +123,24 @@ int nidt_conv_in_s2d_fprop(const void* x, const float* w, const float* bias, voi
 int nidt_conv_in_s2d_wgrad(const void* x, const void* dy, float* grad, float* grad_bias, float* scratch, int N, int Di, int Hi,
                            int Wi, float scale, void* stream);
 
+/* ------------------------------------------------------- residual-network glue (resnet_ops.cu) */
+/* ref: ResNet_l3 / BasicBlock, fedml_api/model/cv/salient_models.py:13-139 (ATen / cuDNN / cuBLAS under autograd there). */
+/* mode 0: out = relu(a + b); 1: out = b > 0 ? a : 0 (ReLU gate, b = forward output); 2: out = a + b.  bf16, n % 8 == 0. */
+int nidt_ew_bf16(const void* a, const void* b, void* out, int64_t n, int mode, void* stream);
+/* MaxPool3d(k, s, p) with overlapping windows; idx = uint8 tap of the first maximum per output element. */
+int nidt_maxpool3d_fwd(const void* x, void* out, void* idx, int N, int D, int H, int W, int C, int k, int s, int p, void* stream);
+int nidt_maxpool3d_bwd(const void* dout, const void* idx, void* dx, int N, int D, int H, int W, int C, int k, int s, int p, void* stream);
+/* u = dy with s-1 zeros between neighbours: dgrad of a stride-s conv = stride-1 nidt_conv3d_fprop_tc over u with the `wd` weights. */
+int nidt_upsample_zero(const void* dy, void* u, int N, int D, int H, int W, int C, int Du, int Hu, int Wu, int s, void* stream);
+/* AvgPool3d(k): bf16 NDHWC -> fp32 features in the NCDHW flatten order of the reference's fc weights, and its backward. */
+int nidt_avgpool3d_fwd(const void* x, float* feat, int N, int D, int H, int W, int C, int k, void* stream);
+int nidt_avgpool3d_bwd(const float* dfeat, void* dx, int N, int D, int H, int W, int C, int k, void* stream);
+/* Linear(F,Hd) -> Linear(Hd,1) -> BCEWithLogits forward, loss / eval counters and full backward.  hidden, dhidden: B*Hd floats. */
+int nidt_linear_head_fwd_bwd(const float* feat, const float* y, const float* W1, const float* b1, const float* W2, const float* b2,
+                             float* gW1, float* gb1, float* gW2, float* gb2, float* dfeat, float* hidden, float* dhidden,
+                             float* loss_acc, double* eval_counters, float* logits_out, int B, int F, int Hd, int train,
+                             int double_sigmoid, void* stream);
+
 /* ------------------------------------- compute fused with its collective over NVLink symmetric memory (sym_agg.cu) */
 /* All ranks call these with the same arguments order; the kernels wait for each other through release/acquire flags.
  * partial_ptrs / result_ptrs / flag_ptrs: HOST arrays of `world` peer-mapped device pointers (identical order on every rank);

