@@ -39,25 +39,39 @@ __device__ __forceinline__ uint4 pack8(const float* f) {
 }
 
 // ------------------------------------------------------------------------------- finalize
-// partials: [T][2][C] (sum, sumsq) per conv tile.  One block per 32 channels, 8 tile-slices.
-__global__ void __launch_bounds__(256) bn_finalize_kernel(
+// partials: [T][2][C] (sum, sumsq) per conv tile.  One block per 16 channels, 64 tile-slices (T reaches a few thousand
+// for the wide early layers; double accumulation keeps the result independent of the slicing to fp32 round-off).
+constexpr int kFinCh = 16, kFinSlices = 64;
+__global__ void __launch_bounds__(kFinCh * kFinSlices) bn_finalize_kernel(
     const float* __restrict__ partials, int T, int C, double count, const float* __restrict__ gamma, const float* __restrict__ beta,
     float* __restrict__ running_mean, float* __restrict__ running_var, float* __restrict__ num_batches, float momentum, float eps,
     float* __restrict__ scale, float* __restrict__ shift, float* __restrict__ mean_out, float* __restrict__ invstd_out) {
-    __shared__ double s1[8][32], s2[8][32];
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const int c = blockIdx.x * 32 + tx;
+    __shared__ double s1[kFinSlices][kFinCh], s2[kFinSlices][kFinCh];
+    const int tx = threadIdx.x % kFinCh, ty = threadIdx.x / kFinCh;
+    const int c = blockIdx.x * kFinCh + tx;
     double a = 0.0, b = 0.0;
-    if (c < C)
-        for (int t = ty; t < T; t += 8) {
+    if (c < C) {
+        int t = ty;
+        for (; t + 3 * kFinSlices < T; t += 4 * kFinSlices) {      // 8 independent loads in flight
+            float v[8];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                v[2 * u] = partials[((size_t)(t + u * kFinSlices) * 2 + 0) * C + c];
+                v[2 * u + 1] = partials[((size_t)(t + u * kFinSlices) * 2 + 1) * C + c];
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { a += (double)v[2 * u]; b += (double)v[2 * u + 1]; }
+        }
+        for (; t < T; t += kFinSlices) {
             a += (double)partials[((size_t)t * 2 + 0) * C + c];
             b += (double)partials[((size_t)t * 2 + 1) * C + c];
         }
+    }
     s1[ty][tx] = a;
     s2[ty][tx] = b;
     __syncthreads();
     if (ty == 0 && c < C) {
-        for (int i = 1; i < 8; ++i) { a += s1[i][tx]; b += s2[i][tx]; }
+        for (int i = 1; i < kFinSlices; ++i) { a += s1[i][tx]; b += s2[i][tx]; }
         const double mean = a / count;
         double var = b / count - mean * mean;
         if (var < 0.0) var = 0.0;
@@ -526,7 +540,7 @@ NIDT_API int nidt_bn_bwd_grid() { return 4 * kNumSMs; }
 NIDT_API int nidt_bn_finalize(const float* partials, int T, int C, double count, const float* gamma, const float* beta,
                               float* running_mean, float* running_var, float* num_batches, float momentum, float eps,
                               float* scale, float* shift, float* mean, float* invstd, void* stream) {
-    bn_finalize_kernel<<<(C + 31) / 32, 256, 0, (cudaStream_t)stream>>>(partials, T, C, count, gamma, beta, running_mean, running_var,
+    bn_finalize_kernel<<<(C + kFinCh - 1) / kFinCh, kFinCh * kFinSlices, 0, (cudaStream_t)stream>>>(partials, T, C, count, gamma, beta, running_mean, running_var,
                                                                         num_batches, momentum, eps, scale, shift, mean, invstd);
     NIDT_LAUNCH_CHECK();
     return 0;

@@ -304,14 +304,33 @@ __global__ void __launch_bounds__(256) lin_bwd_w_kernel(const float* __restrict_
         gW1[t] = g;
     }
 }
-// df[n][k] = sum_j dh[n][j] W1[j][k]
+// df[n][k] = sum_j dh[n][j] W1[j][k]: a block owns 32 columns k; 8 warps split j, every W1 element is read once
 __global__ void __launch_bounds__(256) lin_bwd_x_kernel(const float* __restrict__ dh, const float* __restrict__ W1, float* __restrict__ df, int B, int F, int Hd) {
-    const int64_t total = (int64_t)B * F;
-    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-        const int n = (int)(t / F), k = (int)(t % F);
-        float g = 0.f;
-        for (int j = 0; j < Hd; ++j) g = fmaf(dh[(int64_t)n * Hd + j], W1[(int64_t)j * F + k], g);
-        df[t] = g;
+    __shared__ float red[8][kHeadMaxB][33];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int k = blockIdx.x * 32 + lane;
+    float acc[kHeadMaxB];
+#pragma unroll
+    for (int n = 0; n < kHeadMaxB; ++n) acc[n] = 0.f;
+    if (k < F)
+        for (int j = wid; j < Hd; j += 8) {
+            const float w = W1[(int64_t)j * F + k];
+#pragma unroll
+            for (int n = 0; n < kHeadMaxB; ++n)
+                if (n < B) acc[n] = fmaf(dh[(int64_t)n * Hd + j], w, acc[n]);
+        }
+#pragma unroll
+    for (int n = 0; n < kHeadMaxB; ++n)
+        if (n < B) red[wid][n][lane] = acc[n];
+    __syncthreads();
+    for (int i = threadIdx.x; i < B * 32; i += blockDim.x) {
+        const int n = i >> 5, l = i & 31;
+        if (blockIdx.x * 32 + l < F) {
+            float s = 0.f;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) s += red[w][n][l];
+            df[(int64_t)n * F + blockIdx.x * 32 + l] = s;
+        }
     }
 }
 
@@ -405,7 +424,7 @@ NIDT_API int nidt_linear_head_fwd_bwd(const float* feat, const float* y, const f
         lin_bwd_w_kernel<<<grid_for((int64_t)Hd * F, 256), 256, 0, s>>>(dhidden, feat, gW1, B, F, Hd);
         NIDT_LAUNCH_CHECK();
         if (dfeat != nullptr) {
-            lin_bwd_x_kernel<<<grid_for((int64_t)B * F, 256), 256, 0, s>>>(dhidden, W1, dfeat, B, F, Hd);
+            lin_bwd_x_kernel<<<(F + 31) / 32, 256, 0, s>>>(dhidden, W1, dfeat, B, F, Hd);
             NIDT_LAUNCH_CHECK();
         }
     }
