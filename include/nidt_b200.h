@@ -105,6 +105,15 @@ int nidt_conv3d_wgrad_tc_static(const void* dy, const void* x, float* grad, int 
 /* fp32 [Cout][Cin][taps] -> bf16 wf [Cout][taps][Cin] and wd [Cin][taps (flipped)][Cout]. */
 int nidt_pack_conv_weights(const float* w, int Cout, int Cin, int taps, void* wf, void* wd, void* stream);
 
+/* ----------------------------- 3x3x3 / stride-1 convolution with the input halo resident in shared memory (conv_halo.cu) */
+/* Same math and layouts as nidt_conv3d_fprop_tc (k = 3, stride = 1; dgrad = the `wd` weights with pad' = 2 - pad), but three
+ * input depth-planes stay in shared memory while the CTA slides along the depth axis and the 27 taps are shifted descriptors
+ * into them: L2 -> SM traffic per output row drops ~5-9x.  stats_partials: nidt_conv3d_halo_stats_rows() x 2 x Cout floats. */
+int nidt_conv3d_halo_stats_rows(void);
+int nidt_conv3d_halo_supported(int N, int Do, int Ho, int Wo, int Cin, int Cout, int pad, int block_n);
+int nidt_conv3d_halo_fprop(const void* x, const void* w, const float* bias, void* y, float* stats_partials, int N, int Di, int Hi, int Wi,
+                           int Cin, int Do, int Ho, int Wo, int Cout, int pad, int block_n, int debug_flags, void* stream);
+
 /* ------------------------------------------------------- first layer, Cin = 1 -> 64 (conv_in.cu) */
 /* ref: nn.Conv3d(1,64,5,stride 2) at salient_models.py:147.  x is the 8-bit volume; normalisation x*scale is fused. */
 int nidt_conv_in_grid(void);

@@ -68,6 +68,9 @@ def _declare(lib) -> None:
         "nidt_avgpool3d_fwd": [vp, vp] + [i32] * 6 + [vp],
         "nidt_avgpool3d_bwd": [vp, vp] + [i32] * 6 + [vp],
         "nidt_linear_head_fwd_bwd": [vp] * 16 + [i32] * 5 + [vp],
+        "nidt_conv3d_halo_stats_rows": [],
+        "nidt_conv3d_halo_supported": [i32] * 8,
+        "nidt_conv3d_halo_fprop": [vp, vp, vp, vp, vp] + [i32] * 12 + [vp],
     }.items():
         fn = getattr(lib, name)
         fn.argtypes = argtypes

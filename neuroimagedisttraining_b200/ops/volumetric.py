@@ -246,3 +246,20 @@ def linear_head_fwd_bwd(feat, y, W1, b1, W2, b2, train: bool = True, counters=No
                                               logits.data_ptr(), B, Fdim, Hd, int(train), int(double_sigmoid), _st(feat)), "linear_head")
     g.update(logits=logits, loss=loss, hidden=hidden.view(B, Hd))
     return g
+
+
+def conv3d_halo_fprop(x: torch.Tensor, wf: torch.Tensor, bias: Optional[torch.Tensor], pad: int, block_n: Optional[int] = None,
+                      stats: bool = False, debug_flags: int = 0):
+    """3x3x3 / stride-1 conv through the halo-resident kernel (csrc/conv_halo.cu).  Same contract as :func:`conv3d_fprop`;
+    the partials have ``nidt_conv3d_halo_stats_rows()`` rows.  dgrad: pass ``wd`` and ``pad = 2 - pad``."""
+    lib = _lib()
+    N, D, H, W, Cin = x.shape
+    Cout = wf.shape[0]
+    Do, Ho, Wo = D + 2 * pad - 2, H + 2 * pad - 2, W + 2 * pad - 2
+    block_n = block_n or (128 if Cout % 128 == 0 else 64)
+    y = torch.empty((N, Do, Ho, Wo, Cout), dtype=torch.bfloat16, device=x.device)
+    part = torch.empty((lib.nidt_conv3d_halo_stats_rows(), 2, Cout), dtype=torch.float32, device=x.device) if stats else None
+    native.check(lib.nidt_conv3d_halo_fprop(x.data_ptr(), wf.data_ptr(), bias.data_ptr() if bias is not None else None, y.data_ptr(),
+                                            part.data_ptr() if stats else None, N, D, H, W, Cin, Do, Ho, Wo, Cout, pad, block_n, debug_flags,
+                                            _st(x)), "conv3d_halo_fprop")
+    return (y, part) if stats else y

@@ -123,3 +123,40 @@ def test_linear_head_matches_torch(B, Fdim, Hd):
     assert counters[2].item() == B
     ref_loss = F.binary_cross_entropy_with_logits(pr, y, reduction="sum")      # the reference's double sigmoid
     assert counters[1].item() == pytest.approx(ref_loss.item(), rel=1e-4)
+
+
+HALO_CASES = [
+    # N, Cin, D,H,W, Cout, pad, block_n
+    (1, 64, 4, 5, 6, 64, 1, 64),
+    (2, 64, 6, 14, 32, 64, 1, 64),          # ResNet layer1 row pitch (34), several row blocks
+    (2, 64, 9, 13, 11, 128, 0, 128),        # AlexNet conv2 style (no padding, 128 output channels)
+    (2, 64, 9, 13, 11, 128, 0, 64),         # two N tiles
+    (2, 128, 7, 9, 9, 64, 2, 64),           # dgrad geometry: pad' = 2, two Cin blocks
+    (3, 256, 4, 5, 4, 256, 1, 128),
+]
+
+
+@pytest.mark.parametrize("N,Cin,D,H,W,Cout,pad,block_n", HALO_CASES)
+def test_conv3d_halo_resident_kernel(N, Cin, D, H, W, Cout, pad, block_n):
+    """Halo-resident 3x3x3 conv (shifted SWIZZLE_128B descriptors into planes kept in shared memory)."""
+    from neuroimagedisttraining_b200.ops import volumetric as V
+    torch.manual_seed(9)
+    x = torch.randn(N, Cin, D, H, W, device=DEV).bfloat16()
+    w = (torch.randn(Cout, Cin, 3, 3, 3, device=DEV) / (Cin * 27) ** 0.5).bfloat16().float()
+    bias = torch.randn(Cout, device=DEV) * 0.1
+    ref = F.conv3d(x.float(), w, bias, stride=1, padding=pad)
+    wf, wd = V.pack_conv_weights(w)
+    y, part = V.conv3d_halo_fprop(_cl(x), wf, bias, pad, block_n=block_n, stats=True)
+    torch.cuda.synchronize()
+    _close(_cf(y), ref, what="halo fprop")
+    yb = y.float().reshape(-1, Cout)
+    torch.testing.assert_close(part[:, 0].sum(0), yb.sum(0), rtol=1e-3, atol=1e-2)
+    torch.testing.assert_close(part[:, 1].sum(0), (yb * yb).sum(0), rtol=1e-3, atol=1e-2)
+    # as dgrad: dX of a conv with padding p is the halo conv of dY with the flipped weights and pad' = 2 - p
+    xf = x.float().requires_grad_(True)
+    out = F.conv3d(xf, w, None, stride=1, padding=pad)
+    dy = torch.randn_like(out).bfloat16()
+    out.backward(dy.float())
+    if Cout % 64 == 0 and V._lib().nidt_conv3d_halo_supported(N, D, H, W, Cout, Cin, 2 - pad, 64):
+        dx = V.conv3d_halo_fprop(_cl(dy), wd, None, 2 - pad, block_n=64)
+        _close(_cf(dx), xf.grad, what="halo dgrad")
