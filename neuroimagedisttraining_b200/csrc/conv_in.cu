@@ -250,7 +250,7 @@ __global__ void __launch_bounds__(kInThreads, 1) conv_in_fprop_kernel(
     uint8_t* raws = reinterpret_cast<uint8_t*>(red + 512);
     __nv_bfloat16* patches = reinterpret_cast<__nv_bfloat16*>(raws + 2 * KS * g.raw_pitch);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp-uniform for the compiler: no per-MMA lane-election loops
     // weights (+ bias in K slot kTaps) -> bf16 K-major swizzled B tile (rows = co)
     for (int idx = threadIdx.x; idx < 64 * 128; idx += kInThreads) {
         const int co = idx >> 7, kk = idx & 127;
@@ -278,7 +278,8 @@ __global__ void __launch_bounds__(kInThreads, 1) conv_in_fprop_kernel(
     if (warp < 8) {
         builder_loop<KS, PHT, PWT, ST>(x, g, a_tiles, raws, patches, a_full, a_empty);
     } else if (warp == 8) {
-        if (lane == 0) {
+        const bool leader = tc::elect_one();      // the whole warp walks the schedule, one lane issues
+        {
             constexpr uint32_t idesc = tc::make_idesc_bf16(128, 64, 0, 0);
             for (int i = 0;; ++i) {
                 const int tile = blockIdx.x + i * gridDim.x;
@@ -294,10 +295,12 @@ __global__ void __launch_bounds__(kInThreads, 1) conv_in_fprop_kernel(
                 for (int k = 0; k < 8; ++k) {
                     const uint64_t da = tc::make_smem_desc_sw128(a_addr + (k >> 2) * kT16 + (k & 3) * 32, 16, 1024);
                     const uint64_t db = tc::make_smem_desc_sw128(b_addr + (k >> 2) * (kT16 / 2) + (k & 3) * 32, 16, 1024);
-                    tc::umma_bf16(tmem_base + b * 64, da, db, idesc, k != 0);
+                    if (leader) tc::umma_bf16(tmem_base + b * 64, da, db, idesc, k != 0);
                 }
-                tc::umma_commit(&a_empty[b]);
-                tc::umma_commit(&t_full[b]);
+                if (leader) {
+                    tc::umma_commit(&a_empty[b]);
+                    tc::umma_commit(&t_full[b]);
+                }
             }
         }
     } else {
@@ -386,7 +389,7 @@ __global__ void __launch_bounds__(kInThreads, 1) conv_in_wgrad_kernel(
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 8);
     uint8_t* raws = reinterpret_cast<uint8_t*>(tmem_ptr + 4);
     __nv_bfloat16* patches = reinterpret_cast<__nv_bfloat16*>(raws + 2 * KS * g.raw_pitch);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp-uniform for the compiler: no per-MMA lane-election loops
 
     for (int i = threadIdx.x; i < 2 * kT16 / 16; i += kInThreads) reinterpret_cast<uint4*>(dy_tiles)[i] = make_uint4(0, 0, 0, 0);
     tc::fence_proxy_async_smem();
@@ -405,7 +408,8 @@ __global__ void __launch_bounds__(kInThreads, 1) conv_in_wgrad_kernel(
     if (warp < 8) {
         builder_loop<KS, PHT, PWT, ST>(x, g, a_tiles, raws, patches, a_full, a_empty);
     } else if (warp == 8) {
-        if (lane == 0) {
+        const bool leader = tc::elect_one();
+        {
             constexpr uint32_t idesc = tc::make_idesc_bf16(128, 64, 1, 1);
             int i = 0;
             for (;; ++i) {
@@ -422,11 +426,11 @@ __global__ void __launch_bounds__(kInThreads, 1) conv_in_wgrad_kernel(
                 for (int k = 0; k < 8; ++k) {
                     const uint64_t da = tc::make_smem_desc_sw128(a_addr + k * 2048, kT16, 1024);
                     const uint64_t db = tc::make_smem_desc_sw128(b_addr + k * 2048, kT16, 1024);
-                    tc::umma_bf16(tmem_base, da, db, idesc, (i | k) != 0);
+                    if (leader) tc::umma_bf16(tmem_base, da, db, idesc, (i | k) != 0);
                 }
-                tc::umma_commit(&a_empty[b]);
+                if (leader) tc::umma_commit(&a_empty[b]);
             }
-            tc::umma_commit(t_full);
+            if (leader) tc::umma_commit(t_full);
         }
     } else {
         if (warp == 9 && lane == 0) {

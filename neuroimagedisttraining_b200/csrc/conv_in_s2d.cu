@@ -222,7 +222,7 @@ __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __r
     float* sbias = reinterpret_cast<float*>(tmem_ptr + 4);    // [64]
     float* red = sbias + 64;                                   // [2 groups][16 parts][2][64]
     uint8_t* raws = reinterpret_cast<uint8_t*>(red + 2 * 16 * 2 * 64);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp-uniform for the compiler: no per-MMA lane-election loops
 
     // s2d weights: chunk kc = ((jd*3+jh)*4 + jw), channel c = pd*4+ph*2+pw  ->  W[co][2jd+pd][2jh+ph][2jw+pw] (0 when a tap index is 5+)
     for (int idx = threadIdx.x; idx < 36 * 64 * 8; idx += kFpThreads) {
@@ -253,7 +253,8 @@ __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __r
     } else if (warp == 17) {
         if (lane == 0) raw_producer_loop(x, g, raws, raw_full, raw_empty);
     } else if (warp == 8) {
-        if (lane == 0) {
+        const bool leader = tc::elect_one();      // the whole warp walks the schedule, one lane issues
+        {
             constexpr uint32_t idesc = tc::make_idesc_bf16(128, 64, 0, 0);
             const uint32_t b_addr = tc::smem_u32(b_tile);
             for (int i = 0;; ++i) {
@@ -272,11 +273,13 @@ __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __r
                     for (int pr = 0; pr < 2; ++pr) {     // K = 16: taps (jw, jw+1) = 2 consecutive positions, LBO = 16 B
                         const uint64_t da = desc_noswz(a_addr + (jd * 4 + jh) * kLineBytes + pr * 32, 16, 128);
                         const uint64_t db = desc_noswz(b_addr + (t * 4 + pr * 2) * 1024, 1024, 128);
-                        tc::umma_bf16(tmem_base + b * 64, da, db, idesc, (t | pr) != 0);
+                        if (leader) tc::umma_bf16(tmem_base + b * 64, da, db, idesc, (t | pr) != 0);
                     }
                 }
-                tc::umma_commit(&a_empty[buf]);
-                tc::umma_commit(&t_full[b]);
+                if (leader) {
+                    tc::umma_commit(&a_empty[buf]);
+                    tc::umma_commit(&t_full[b]);
+                }
             }
         }
     } else {
@@ -377,7 +380,7 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __res
     uint64_t *raw_full = dy_empty + kDyRing, *raw_empty = raw_full + kRawRing;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(raw_empty + kRawRing);
     uint8_t* raws = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(tmem_ptr + 4) + 15) & ~(uintptr_t)15);   // 16-byte vector stores
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp-uniform for the compiler: no per-MMA lane-election loops
 
     for (int i = threadIdx.x; i < (kDyRing * kT16 + kARing * kWgABytes) / 16; i += kThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
     tc::fence_proxy_async_smem();
@@ -398,7 +401,8 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __res
     if (warp < 8) {
         staging_loop(x, g, a_bufs, raws, a_full, a_empty, raw_full, raw_empty, kWgLineBytes, kWgABytes);
     } else if (warp == 8) {
-        if (lane == 0) {
+        const bool leader = tc::elect_one();
+        {
             constexpr uint32_t idesc = tc::make_idesc_bf16(128, 64, 1, 1);
             int i = 0;
             for (;; ++i) {
@@ -419,13 +423,15 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __res
                     for (int jw = 0; jw < ((g.dbg & 2) ? (ks == 0 ? 1 : 0) : 3); ++jw) {
                         // A = lines, MN-major no swizzle: M chunks (lines) 1 KiB apart (SBO), K groups (8 positions) 128 B apart (LBO)
                         const uint64_t da = desc_noswz(a_addr + jw * 16 + ks * 256, 128, kWgLineBytes);
-                        tc::umma_bf16(tmem_base + jw * 64, da, db, idesc, (i | ks) != 0);
+                        if (leader) tc::umma_bf16(tmem_base + jw * 64, da, db, idesc, (i | ks) != 0);
                     }
                 }
-                tc::umma_commit(&a_empty[b]);
-                tc::umma_commit(&dy_empty[slot]);
+                if (leader) {
+                    tc::umma_commit(&a_empty[b]);
+                    tc::umma_commit(&dy_empty[slot]);
+                }
             }
-            tc::umma_commit(t_full);
+            if (leader) tc::umma_commit(t_full);
         }
     } else {
         if (warp == 9 && lane == 0) {

@@ -102,7 +102,9 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv3d_fprop_tc_kernel(
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
     uint8_t* row_valid = reinterpret_cast<uint8_t*>(tmem_ptr + 2);   // [128]
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // shuffled warp index = provably warp-uniform: the producer / MMA schedules then live in uniform registers and UTMALDG /
+    // UTCHMMA are issued without a per-instruction lane-election loop (the whole warp walks the schedule, one lane issues)
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int taps = g.k * g.k * g.k;
     const int num_kb = taps * g.cin_blocks;
 
@@ -130,55 +132,55 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv3d_fprop_tc_kernel(
     };
 
     if (warp == 0) {
-        if (lane == 0) {
-            // ===== TMA producer =====
-            uint32_t it = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                int n_tile, w0, h0, d0, n0;
-                decode(tile, n_tile, w0, h0, d0, n0);
-                for (int kb = 0; kb < num_kb; ++kb, ++it) {
-                    const int s = it % Cfg::kStages;
-                    const uint32_t ph = (it / Cfg::kStages) & 1;
-                    tc::mbar_wait(&empty[s], ph ^ 1);
-                    const int tap = kb / g.cin_blocks, cb = kb - tap * g.cin_blocks;
-                    const int kd = tap / (g.k * g.k), kh = (tap / g.k) % g.k, kw = tap % g.k;
-                    uint8_t* a_dst = stage_base + s * Cfg::kStageBytes;
-                    uint8_t* b_dst = a_dst + kATileBytes;
-                    tc::mbar_expect_tx(&full[s], (uint32_t)(g.box_rows * 128 + Cfg::kBTileBytes));
-                    tc::tma_load_5d(&tm_x, &full[s], a_dst, cb * 64, w0 * g.stride - g.pad + kw, h0 * g.stride - g.pad + kh,
-                                    d0 * g.stride - g.pad + kd, n0);
-                    tc::tma_load_2d(&tm_w, &full[s], b_dst, kb * 64, n_tile * BLOCK_N);
-                }
-            }
+        // ===== TMA producer (no divisions inside the k loop: a lone warp pays ~5-10 cycles per scalar instruction) =====
+        const bool leader = tc::elect_one();
+        uint32_t s = 0, ph = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            int n_tile, w0, h0, d0, n0;
+            decode(tile, n_tile, w0, h0, d0, n0);
+            const int x0 = w0 * g.stride - g.pad, y0 = h0 * g.stride - g.pad, z0 = d0 * g.stride - g.pad;
+            int kb = 0;
+            for (int kd = 0; kd < g.k; ++kd)
+                for (int kh = 0; kh < g.k; ++kh)
+                    for (int kw = 0; kw < g.k; ++kw)
+                        for (int cb = 0; cb < g.cin_blocks; ++cb, ++kb) {
+                            tc::mbar_wait(&empty[s], ph ^ 1);
+                            if (leader) {
+                                uint8_t* a_dst = stage_base + s * Cfg::kStageBytes;
+                                tc::mbar_expect_tx(&full[s], (uint32_t)(g.box_rows * 128 + Cfg::kBTileBytes));
+                                tc::tma_load_5d(&tm_x, &full[s], a_dst, cb * 64, x0 + kw, y0 + kh, z0 + kd, n0);
+                                tc::tma_load_2d(&tm_w, &full[s], a_dst + kATileBytes, kb * 64, n_tile * BLOCK_N);
+                            }
+                            if (++s == (uint32_t)Cfg::kStages) { s = 0; ph ^= 1; }
+                        }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ===== MMA issuer =====
-            constexpr uint32_t idesc = tc::make_idesc_bf16(128, BLOCK_N, 0, 0);
-            uint32_t it = 0, local = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
-                const int buf = local & 1;
-                const uint32_t aph = (local >> 1) & 1;
-                tc::mbar_wait(&tmem_empty[buf], aph ^ 1);
+        // ===== MMA issuer =====
+        const bool leader = tc::elect_one();
+        constexpr uint32_t idesc = tc::make_idesc_bf16(128, BLOCK_N, 0, 0);
+        constexpr uint32_t kDescHi = tc::desc_hi_sw128(1024);
+        const uint32_t stage_lo = tc::desc_lo_sw128(tc::smem_u32(stage_base));
+        uint32_t s = 0, ph = 0, local = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
+            const int buf = local & 1;
+            tc::mbar_wait(&tmem_empty[buf], ((local >> 1) & 1) ^ 1);
+            tc::tc_fence_after();
+            const uint32_t d_tmem = tmem_base + buf * BLOCK_N;
+            for (int kb = 0; kb < num_kb; ++kb) {
+                tc::mbar_wait(&full[s], ph);
                 tc::tc_fence_after();
-                const uint32_t d_tmem = tmem_base + buf * BLOCK_N;
-                for (int kb = 0; kb < num_kb; ++kb, ++it) {
-                    const int s = it % Cfg::kStages;
-                    const uint32_t ph = (it / Cfg::kStages) & 1;
-                    tc::mbar_wait(&full[s], ph);
-                    tc::tc_fence_after();
-                    const uint32_t a_addr = tc::smem_u32(stage_base + s * Cfg::kStageBytes);
-                    const uint32_t b_addr = a_addr + kATileBytes;
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const uint64_t da = tc::make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
-                        const uint64_t db = tc::make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
-                        tc::umma_bf16(d_tmem, da, db, idesc, (kb | k) != 0);
-                    }
+                const uint32_t a_lo = stage_lo + s * (Cfg::kStageBytes >> 4);
+                const uint32_t b_lo = a_lo + (kATileBytes >> 4);
+                if (leader) {
+                    tc::umma_bf16_lohi(d_tmem, a_lo, b_lo, kDescHi, idesc, kb != 0);
+                    tc::umma_bf16_lohi(d_tmem, a_lo + 2, b_lo + 2, kDescHi, idesc, 1);
+                    tc::umma_bf16_lohi(d_tmem, a_lo + 4, b_lo + 4, kDescHi, idesc, 1);
+                    tc::umma_bf16_lohi(d_tmem, a_lo + 6, b_lo + 6, kDescHi, idesc, 1);
                     tc::umma_commit(&empty[s]);
                 }
-                tc::umma_commit(&tmem_full[buf]);
+                if (++s == (uint32_t)Cfg::kStages) { s = 0; ph ^= 1; }
             }
+            if (leader) tc::umma_commit(&tmem_full[buf]);
         }
     } else {
         // ===== epilogue: warps 2..5; TMEM lane quarter = warp % 4 =====
@@ -283,7 +285,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv3d_wgrad_tc_kernel(
     uint64_t* empty = bars + kWgStages;
     uint64_t* tmem_full = empty + kWgStages;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full + 1);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;     // warp-uniform (see fprop)
     const int taps = g.k * g.k * g.k;
 
     // work item decode: ci block fastest, then co tile, then tap, then split
@@ -314,17 +316,18 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv3d_wgrad_tc_kernel(
     const uint32_t tmem_base = *tmem_ptr;
 
     if (warp == 0) {
-        if (lane == 0) {
-            uint32_t it = 0;
-            for (int mt = mt_begin; mt < mt_end; ++mt, ++it) {
-                int m = mt;
-                const int w0 = (m % g.tw) * g.bw; m /= g.tw;
-                const int h0 = (m % g.th) * g.bh; m /= g.th;
-                const int d0 = (m % g.td) * g.bd; m /= g.td;
-                const int n0 = m * g.bn;
-                const int s = it % kWgStages;
-                const uint32_t ph = (it / kWgStages) & 1;
-                tc::mbar_wait(&empty[s], ph ^ 1);
+        const bool leader = tc::elect_one();
+        uint32_t s = 0, ph = 0;
+        // running tile coordinates instead of a division chain per tile
+        int m = mt_begin;
+        int iw = m % g.tw; m /= g.tw;
+        int ih = m % g.th; m /= g.th;
+        int id = m % g.td;
+        int in = m / g.td;
+        for (int mt = mt_begin; mt < mt_end; ++mt) {
+            const int w0 = iw * g.bw, h0 = ih * g.bh, d0 = id * g.bd, n0 = in * g.bn;
+            tc::mbar_wait(&empty[s], ph ^ 1);
+            if (leader) {
                 uint8_t* a_dst = smem + s * kWgStageBytes;
                 tc::mbar_expect_tx(&full[s], (uint32_t)(3 * g.box_rows * 128));
                 tc::tma_load_5d(&tm_dy, &full[s], a_dst, cot * 128, w0, h0, d0, n0);
@@ -332,28 +335,29 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv3d_wgrad_tc_kernel(
                 tc::tma_load_5d(&tm_x, &full[s], a_dst + 2 * kATileBytes, cib * 64, w0 * g.stride - g.pad + kw, h0 * g.stride - g.pad + kh,
                                 d0 * g.stride - g.pad + kd, n0);
             }
+            if (++s == (uint32_t)kWgStages) { s = 0; ph ^= 1; }
+            if (++iw == g.tw) { iw = 0; if (++ih == g.th) { ih = 0; if (++id == g.td) { id = 0; ++in; } } }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            constexpr uint32_t idesc = tc::make_idesc_bf16(128, 64, 1, 1);
-            uint32_t it = 0;
-            for (int mt = mt_begin; mt < mt_end; ++mt, ++it) {
-                const int s = it % kWgStages;
-                const uint32_t ph = (it / kWgStages) & 1;
-                tc::mbar_wait(&full[s], ph);
-                tc::tc_fence_after();
-                const uint32_t a_addr = tc::smem_u32(smem + s * kWgStageBytes);
-                const uint32_t b_addr = a_addr + 2 * kATileBytes;
+        const bool leader = tc::elect_one();
+        constexpr uint32_t idesc = tc::make_idesc_bf16(128, 64, 1, 1);
+        constexpr uint32_t kDescHi = tc::desc_hi_sw128(1024);
+        const uint32_t stage_lo = tc::desc_lo_sw128(tc::smem_u32(smem), kATileBytes);     // MN-major: LBO = the 64-channel half (16 KB)
+        uint32_t s = 0, ph = 0;
+        for (int mt = mt_begin; mt < mt_end; ++mt) {
+            tc::mbar_wait(&full[s], ph);
+            tc::tc_fence_after();
+            const uint32_t a_lo = stage_lo + s * (kWgStageBytes >> 4);
+            const uint32_t b_lo = a_lo + (2 * kATileBytes >> 4);
+            if (leader) {
 #pragma unroll
-                for (int k = 0; k < 8; ++k) {   // 16 positions per MMA: two 8-row swizzle groups (SBO = 1024 B)
-                    const uint64_t da = tc::make_smem_desc_sw128(a_addr + k * 2048, kATileBytes, 1024);
-                    const uint64_t db = tc::make_smem_desc_sw128(b_addr + k * 2048, kATileBytes, 1024);
-                    tc::umma_bf16(tmem_base, da, db, idesc, (it | (uint32_t)k) != 0);
-                }
+                for (int k = 0; k < 8; ++k)     // 16 positions per MMA: two 8-row swizzle groups (SBO = 1024 B); +2048 B per step
+                    tc::umma_bf16_lohi(tmem_base, a_lo + k * 128, b_lo + k * 128, kDescHi, idesc, (k != 0) || (mt != mt_begin));
                 tc::umma_commit(&empty[s]);
             }
-            tc::umma_commit(tmem_full);
+            if (++s == (uint32_t)kWgStages) { s = 0; ph ^= 1; }
         }
+        if (leader) tc::umma_commit(tmem_full);
     } else {
         const int q = warp & 3;
         const int co = cot * 128 + q * 32 + lane;

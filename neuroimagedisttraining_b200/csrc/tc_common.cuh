@@ -109,7 +109,7 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint
 // The same instruction with the two shared-memory descriptors given as (low word, shared high word): the issue loop then
 // advances an operand by adding (byte offset >> 4) to a 32-bit register instead of rebuilding 64-bit descriptors
 // (measured: ~100 cycles of uniform-datapath work per MMA otherwise, against 48-64 cycles of tensor-core time).
-__device__ __forceinline__ uint32_t desc_lo_sw128(uint32_t smem_addr) { return ((smem_addr >> 4) & 0x3FFFu) | (1u << 16); }   // LBO = 16 B
+__device__ __forceinline__ uint32_t desc_lo_sw128(uint32_t smem_addr, uint32_t lbo_bytes = 16) { return ((smem_addr >> 4) & 0x3FFFu) | (((lbo_bytes >> 4) & 0x3FFFu) << 16); }
 __device__ __forceinline__ constexpr uint32_t desc_hi_sw128(uint32_t sbo_bytes) { return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29); }
 __device__ __forceinline__ void umma_bf16_lohi(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t hi, uint32_t idesc, uint32_t accumulate) {
     asm volatile(

@@ -132,14 +132,24 @@ HALO_CASES = [
     (2, 64, 9, 13, 11, 128, 0, 128),        # AlexNet conv2 style (no padding, 128 output channels)
     (2, 64, 9, 13, 11, 128, 0, 64),         # two N tiles
     (2, 128, 7, 9, 9, 64, 2, 64),           # dgrad geometry: pad' = 2, two Cin blocks
-    (3, 256, 4, 5, 4, 256, 1, 128),
+    (3, 192, 4, 5, 4, 128, 1, 64),          # three Cin blocks
 ]
+
+
+def test_conv3d_halo_reports_unsupported_shapes():
+    from neuroimagedisttraining_b200.ops import volumetric as V
+    lib = V._lib()
+    assert lib.nidt_conv3d_halo_supported(3, 4, 5, 4, 256, 256, 1, 128) == 0      # four Cin blocks of planes do not fit in shared memory
+    assert lib.nidt_conv3d_halo_supported(2, 8, 8, 200, 64, 64, 1, 64) == 0        # row pitch above 128
+    assert lib.nidt_conv3d_halo_supported(2, 8, 8, 8, 32, 64, 1, 64) == 0          # Cin not a multiple of 64
 
 
 @pytest.mark.parametrize("N,Cin,D,H,W,Cout,pad,block_n", HALO_CASES)
 def test_conv3d_halo_resident_kernel(N, Cin, D, H, W, Cout, pad, block_n):
     """Halo-resident 3x3x3 conv (shifted SWIZZLE_128B descriptors into planes kept in shared memory)."""
     from neuroimagedisttraining_b200.ops import volumetric as V
+    Do, Ho, Wo = D + 2 * pad - 2, H + 2 * pad - 2, W + 2 * pad - 2
+    assert V._lib().nidt_conv3d_halo_supported(N, Do, Ho, Wo, Cin, Cout, pad, block_n) == 1
     torch.manual_seed(9)
     x = torch.randn(N, Cin, D, H, W, device=DEV).bfloat16()
     w = (torch.randn(Cout, Cin, 3, 3, 3, device=DEV) / (Cin * 27) ** 0.5).bfloat16().float()
