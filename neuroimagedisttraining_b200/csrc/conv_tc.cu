@@ -82,7 +82,7 @@ struct FpropCfg {
     static constexpr int kStageBytes = kATileBytes + kBTileBytes;
     static constexpr int kStagingBytes = (BLOCK_N / 64) * kATileBytes;
     static constexpr int kTmemCols = 2 * BLOCK_N;   // double-buffered accumulator (power of two: 128 / 256)
-    static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers, flags*/ + 128;
+    static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers, flags*/ + 128 + 512 /*stats halves*/;
 };
 
 template <int BLOCK_N>
@@ -101,6 +101,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv3d_fprop_tc_kernel(
     uint64_t* tmem_empty = tmem_full + 2;        // [2]
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
     uint8_t* row_valid = reinterpret_cast<uint8_t*>(tmem_ptr + 2);   // [128]
+    float* stat_red = reinterpret_cast<float*>(row_valid + 128);      // [2][64]: second half of the rows when BLOCK_N == 64
 
     // shuffled warp index = provably warp-uniform: the producer / MMA schedules then live in uniform registers and UTMALDG /
     // UTCHMMA are issued without a per-instruction lane-election loop (the whole warp walks the schedule, one lane issues)
@@ -234,18 +235,27 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv3d_fprop_tc_kernel(
                 tc::tma_store_commit();
             }
             if (stats_partials != nullptr) {
-                // per-channel (sum, sum^2) over the valid rows of this tile, from the bf16 values just staged
-                for (int ch = et; ch < BLOCK_N; ch += 128) {
-                    if (co0 + ch >= g.Cout) continue;
+                // per-channel (sum, sum^2) over the valid rows of this tile, from the bf16 values just staged; with 64 channels the
+                // 128 threads split the rows in two halves (this loop sits on the critical path of short K loops)
+                constexpr int kParts = 128 / BLOCK_N;
+                const int ch = et % BLOCK_N, part = et / BLOCK_N;
+                float s1 = 0.f, s2 = 0.f;
+                if (co0 + ch < g.Cout) {
                     const uint8_t* blk = staging + (ch >> 6) * kATileBytes;
                     const int chunk = (ch & 63) >> 3, within = (ch & 7) * 2;
-                    float s1 = 0.f, s2 = 0.f;
-                    for (int r = 0; r < g.box_rows; ++r) {
+                    for (int r = part; r < g.box_rows; r += kParts) {
                         if (!row_valid[r]) continue;
                         const float x = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(blk + r * 128 + ((chunk ^ (r & 7)) << 4) + within));
                         s1 += x;
                         s2 = fmaf(x, x, s2);
                     }
+                }
+                if (kParts == 2) {
+                    if (part == 1) { stat_red[ch] = s1; stat_red[64 + ch] = s2; }
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                    if (part == 0) { s1 += stat_red[ch]; s2 += stat_red[64 + ch]; }
+                }
+                if (part == 0 && co0 + ch < g.Cout) {
                     const int m_tile = tile / g.n_tiles;
                     stats_partials[((size_t)m_tile * 2 + 0) * g.Cout + co0 + ch] = s1;
                     stats_partials[((size_t)m_tile * 2 + 1) * g.Cout + co0 + ch] = s2;

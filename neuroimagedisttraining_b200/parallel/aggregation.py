@@ -30,6 +30,8 @@ class Aggregator:
         self.device = torch.device(device)
         if mode == "auto":
             mode = "fused" if (ctx.is_distributed and self.device.type == "cuda") else "nccl"
+        if not ctx.is_distributed:
+            mode = "local"       # one rank: the weighted-aggregate kernel writes the global slab, nothing crosses a link
         self.mode = mode
         self.partial = torch.zeros(layout.total_numel, dtype=torch.float32, device=self.device)
         self._fused = None
