@@ -47,6 +47,8 @@ def parse():
     p.add_argument("--agg", default="auto", choices=["auto", "fused", "nccl"])
     p.add_argument("--shape", default="121,145,121")
     p.add_argument("--skip-e2e", action="store_true")
+    p.add_argument("--model", default="alexnet3d", choices=["alexnet3d", "resnet3d"],
+                   help="resnet3d = BASELINE.json config 4 (use with --clients 84 --batch 8 --dense-ratio 0.1 --per-site 10; ours arm only)")
     p.add_argument("--algo", default="salientgrads", choices=["salientgrads", "fedavg"], help="fedavg = BASELINE.json config 2 (ours arm only)")
     return p.parse_args()
 
@@ -195,17 +197,24 @@ def run_ours(a):
     torch.manual_seed(fl_args.seed)
     store = build_store(a, shape, pin=True)
     dataset = load_partition_data_abcd(store, client_number=a.clients, batch_size=a.batch)
-    model = AlexNet3D_Dropout(num_classes=1, in_shape=shape)
+    if a.model == "resnet3d":
+        from neuroimagedisttraining_b200.models.volumetric import resnet3d_18
+        model = resnet3d_18(1, shape)
+        fl_args.model = "3DResNet"
+    else:
+        model = AlexNet3D_Dropout(num_classes=1, in_shape=shape)
     engine = None
-    engine_name = "torch(scaffold)+flat-kernels"
+    engine_name = "torch(cudnn, bf16 autocast)+flat-kernels" if a.model == "resnet3d" else "torch(scaffold)+flat-kernels"
     if a.engine in ("auto", "b200"):
         try:
-            from neuroimagedisttraining_b200.ops.engine_b200 import B200Engine
-            engine = B200Engine(model, device, max_batch=a.batch, input_scale=store.scale)
+            from neuroimagedisttraining_b200.ops.engines import make_native_engine
+            engine = make_native_engine(model, device, max_batch=a.batch, input_scale=store.scale)
             engine_name = "b200"
         except ImportError:
             if a.engine == "b200":
                 raise
+    if engine is None and a.model == "resnet3d":
+        fl_args.amp = True
     trainer = SlabTrainer(model, fl_args, logger, device=device, store=store, engine=engine)
     from neuroimagedisttraining_b200.fl import FedAvgAPI
     api = (SalientGradsAPI if a.algo == "salientgrads" else FedAvgAPI)(dataset, device, fl_args, trainer, logger, dist=ctx, agg_mode=a.agg)
@@ -253,12 +262,12 @@ def run_ours(a):
     stat = api.finalize_stats()
     if ctx.is_main:
         out = {
-            "metric": "samples_per_s_%s_alexnet3d_abcd_round" % a.algo, "value": samples_per_round * a.steps / t_dev,
+            "metric": "samples_per_s_%s_%s_abcd_round" % (a.algo, a.model), "value": samples_per_round * a.steps / t_dev,
             "unit": "samples/s", "n_gpus": ctx.world_size, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": 1e3 * t_dev / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "bf16" if engine_name == "b200" else "fp32(tf32 conv)", "data": "synthetic 8-bit ABCD-shape volumes, random-init weights",
             "impl": "ours", "engine": engine_name,
-            "config": {"model": "AlexNet3D_Dropout(1 logit)", "algorithm": ("SalientGrads dense_ratio=%g" % a.dense_ratio) if a.algo == "salientgrads" else "FedAvg",
+            "config": {"model": "AlexNet3D_Dropout(1 logit)" if a.model == "alexnet3d" else "ResNet3D_l3(BasicBlock,[2,2,2], 1 logit, FC sized from the input)", "algorithm": ("SalientGrads dense_ratio=%g" % a.dense_ratio) if a.algo == "salientgrads" else "FedAvg",
                        "clients": a.clients, "clients_per_round": a.clients, "local_epochs": a.epochs, "batch": a.batch,
                        "global_batch": a.batch, "seq_len": "x".join(map(str, shape)), "train_samples_per_round": samples_per_round,
                        "sgd_steps_per_round": samples_per_round // a.batch, "eval_samples_per_round": 2 * a.clients * (a.per_site // 5),
@@ -403,7 +412,7 @@ def run_reference(a):
             "unit": "samples/s", "n_gpus": ctx.world_size, "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * t / a.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "fp32 (TF32 conv, cudnn.deterministic=True)",
             "data": "synthetic 8-bit ABCD-shape volumes served as fp32, random-init weights",
-            "config": {"model": "AlexNet3D_Dropout(1 logit)", "algorithm": "SalientGrads dense_ratio=%g" % a.dense_ratio,
+            "config": {"model": "AlexNet3D_Dropout(1 logit)" if a.model == "alexnet3d" else "ResNet3D_l3(BasicBlock,[2,2,2], 1 logit, FC sized from the input)", "algorithm": "SalientGrads dense_ratio=%g" % a.dense_ratio,
                        "clients": a.clients, "local_epochs": a.epochs, "batch": a.batch, "global_batch": a.batch,
                        "seq_len": "x".join(map(str, shape)), "train_samples_per_round": samples_per_round,
                        "parallelism": "reference loop verbatim" if ctx.world_size == 1 else "reference Client.train per rank + NCCL all_reduce wrapper x%d" % ctx.world_size},

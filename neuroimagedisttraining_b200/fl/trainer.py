@@ -90,7 +90,7 @@ class SlabTrainer(ModelTrainer):
         self.store = store
         self.engine = engine if engine is not None else TorchEngine(
             model, self.device, loss_kind=loss_kind, volumetric=store is not None,
-            input_scale=getattr(store, "scale", 1.0))
+            input_scale=getattr(store, "scale", 1.0), amp=bool(getattr(args, "amp", False)))
         self.layout = self.engine.layout
         self.clip_norm = clip_norm
         self.work = self.engine.new_slab()         # the slab API-compat calls operate on
