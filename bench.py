@@ -297,7 +297,7 @@ def make_device_stager(store, device, batch):
             self.ring = [torch.empty(batch, dtype=torch.int64).pin_memory() for _ in range(128)]
             self.k = 0
 
-        def iterate(self, loader):
+        def iterate(self, loader, lookahead=None):
             for b in loader:
                 n = b[0].numel()
                 buf = self.ring[self.k % len(self.ring)]

@@ -20,10 +20,13 @@ class FedAvgAPI(FedAPIBase):
         training_num = sum(self.client_list[int(c)].get_sample_number() for c in client_indexes)
         w_locals = []
         with self.timer.phase("train"):
-            for cur_clnt in self.local_clients(client_indexes):
+            mine = list(self.local_clients(client_indexes))
+            for pos, cur_clnt in enumerate(mine):
                 self.logger.info('@@@@@@@@@@@@@@@@ Training Client CM({}): {}'.format(round_idx, cur_clnt))
                 client = self.client_list[cur_clnt]
-                slab, training_flops, num_comm_params = client.train(self.w_global, round_idx, mask)
+                # the next client's first batch is staged while this one finishes (no exposed copy at client boundaries)
+                nxt = self.client_list[mine[pos + 1]].local_training_data if pos + 1 < len(mine) else None
+                slab, training_flops, num_comm_params = client.train(self.w_global, round_idx, mask, lookahead_data=nxt)
                 w_locals.append((client.get_sample_number(), slab))
                 self.stat_info["sum_training_flops"] += training_flops
                 self._add_comm_params(num_comm_params)

@@ -125,17 +125,31 @@ class SlabTrainer(ModelTrainer):
             for batch in data:
                 yield batch[0], batch[1]
 
-    def _batches_epochs(self, data, epochs: int):
-        """``(epoch, x, y)`` over ``epochs`` passes of ``data`` as ONE staged stream."""
-        if self.store is not None and hasattr(data, "indices"):
-            tags = []
+    def _epoch_stream(self, data, epochs: int):
+        """(index-batch generator over ``epochs`` passes of ``data``, list that receives the epoch tag of every batch)."""
+        tags = []
 
-            def index_stream():
-                for e in range(epochs):
-                    for b in data:
-                        tags.append(e)
-                        yield b
-            for i, (x, y) in enumerate(self._stager(data.batch_size).iterate(index_stream())):
+        def index_stream():
+            for e in range(epochs):
+                for b in data:
+                    tags.append(e)
+                    yield b
+        return index_stream(), tags
+
+    def _batches_epochs(self, data, epochs: int, lookahead_data=None):
+        """``(epoch, x, y)`` over ``epochs`` passes of ``data`` as ONE staged stream.  ``lookahead_data``: the loader the next
+        call will train on; its first batch is copied while this client's last steps still run (see BatchStager.iterate)."""
+        if self.store is not None and hasattr(data, "indices"):
+            prepared, self._prepared = getattr(self, "_prepared", None), None
+            if prepared is not None and prepared[0] is data and prepared[1] == epochs:
+                stream, tags = prepared[2], prepared[3]
+            else:
+                stream, tags = self._epoch_stream(data, epochs)
+            la_stream = None
+            if lookahead_data is not None and hasattr(lookahead_data, "indices") and lookahead_data.batch_size == data.batch_size:
+                la_stream, la_tags = self._epoch_stream(lookahead_data, epochs)
+                self._prepared = (lookahead_data, epochs, la_stream, la_tags)
+            for i, (x, y) in enumerate(self._stager(data.batch_size).iterate(stream, lookahead=la_stream)):
                 yield tags[i], x, y
         else:
             for e in range(epochs):
@@ -248,7 +262,7 @@ class SlabTrainer(ModelTrainer):
     # -------------------------------------------------------------------------- train
     def train(self, train_data, device=None, args=None, round_idx: int = 0, masks: MaskLike = None,
               prox_ref: Optional[ParamSlab] = None, lamda: float = 0.0, epochs: Optional[int] = None,
-              apply_mask: Optional[bool] = None, grad_mask: bool = False):
+              apply_mask: Optional[bool] = None, grad_mask: bool = False, lookahead_data=None):
         """``epochs`` of local SGD on the attached slab.  A fresh optimizer per call (momentum
         buffers reset), ``lr * lr_decay**round``, grad-clip 10, weight decay on every parameter and
         ``w *= mask`` after every step when ``snip_mask`` (``my_model_trainer.py:201-235``)."""
@@ -272,7 +286,7 @@ class SlabTrainer(ModelTrainer):
 
         # all epochs are one batch stream, so the host->device prefetch runs across epoch boundaries
         cur = 0
-        for epoch, x, y in self._batches_epochs(train_data, n_epochs):
+        for epoch, x, y in self._batches_epochs(train_data, n_epochs, lookahead_data):
             if epoch != cur:
                 end_epoch(cur)
                 cur = epoch

@@ -59,9 +59,13 @@ class BatchStager:
         self.h2d_bytes += b * int(np.prod(self.store.shape)) + 4 * b
         return b
 
-    def iterate(self, loader) -> Iterator[Tuple[torch.Tensor, torch.Tensor]]:
+    def iterate(self, loader, lookahead=None) -> Iterator[Tuple[torch.Tensor, torch.Tensor]]:
         """Yields ``(x_u8 [b,D,H,W], y [b])`` on the device; the tensors of one iteration stay valid
-        until the next-but-one iteration (ring depth 2)."""
+        until the next-but-one iteration (ring depth 2).
+
+        ``lookahead``: the index stream the NEXT call will iterate (the next client's batches).  When this stream
+        runs dry its first batch is copied right away, so the next call starts with its data already on the way
+        instead of exposing one host->device copy per client."""
         if not self.cuda:
             for batch in loader:
                 ids = np.asarray(batch[0]).astype(np.int64)
@@ -70,24 +74,37 @@ class BatchStager:
                 x, y = self.store.fetch(ids)
                 yield x, y
             return
-        it = iter(loader)
-        pending = []
-        slot = 0
+        carry, self._carry = getattr(self, "_carry", None), None
         cur = torch.cuda.current_stream(self.device)
-        for _ in range(self.depth - 1):
-            try:
-                b = next(it)
-            except StopIteration:
-                break
-            pending.append((slot, self._issue(slot, b[0])))
-            slot = (slot + 1) % self.depth
-        while pending:
-            try:
-                b = next(it)
+        if carry is not None and carry[0] is loader:
+            _, it, pending, slot = carry
+        else:
+            it = iter(loader)
+            pending = []
+            slot = 0
+            for _ in range(self.depth - 1):
+                try:
+                    b = next(it)
+                except StopIteration:
+                    break
                 pending.append((slot, self._issue(slot, b[0])))
                 slot = (slot + 1) % self.depth
-            except StopIteration:
-                pass
+        dry = False
+        while pending:
+            if not dry:
+                try:
+                    b = next(it)
+                    pending.append((slot, self._issue(slot, b[0])))
+                    slot = (slot + 1) % self.depth
+                except StopIteration:
+                    dry = True
+                    if lookahead is not None:
+                        la_it = iter(lookahead)
+                        try:
+                            b = next(la_it)
+                            self._carry = (lookahead, la_it, [(slot, self._issue(slot, b[0]))], (slot + 1) % self.depth)
+                        except StopIteration:
+                            pass
             s, n = pending.pop(0)
             cur.wait_event(self.ready[s])
             yield self.dev_x[s][:n], self.dev_y[s][:n]
