@@ -285,6 +285,7 @@ def run_ours(a):
 
 def make_device_stager(store, device, batch):
     """Stager variant with the whole synthetic dataset resident on the device."""
+    from neuroimagedisttraining_b200 import ops
     from neuroimagedisttraining_b200.runtime.staging import BatchStager
 
     class DeviceStager(BatchStager):
@@ -304,7 +305,7 @@ def make_device_stager(store, device, batch):
                 self.k += 1
                 buf[:n] = torch.sort(b[0])[0]
                 idx = buf[:n].to(self.device, non_blocking=True)
-                yield self.vol.index_select(0, idx), self.lab.index_select(0, idx)
+                yield ops.gather_rows_u8(self.vol, idx), self.lab.index_select(0, idx)
 
     return DeviceStager()
 

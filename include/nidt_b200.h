@@ -52,6 +52,9 @@ int nidt_topk_read_result(const void* scratch, float* threshold, float* norm, un
 int nidt_count_nonzero(const float* a, int64_t n, unsigned long long* out, void* stream);
 int nidt_hamming(const float* a, const float* b, int64_t n, unsigned long long* out, void* stream);
 int nidt_sq_dist(const float* a, const float* b, int64_t n, float* scratch, float* out, void* stream);
+/* dst[j] = src[idx[j]] for `rows` rows of row_bytes bytes each (any length / alignment): assembles device batches of 8-bit volumes
+ * from a device-resident dataset.  idx: int64 on the device. */
+int nidt_gather_rows_u8(const void* src, const int64_t* idx, void* dst, int rows, int64_t row_bytes, void* stream);
 /* Ditto proximal pull w -= coef*(w - ref).  ref: fedml_api/standalone/ditto/my_model_trainer.py:63-64. */
 int nidt_prox_pull(float* w, const float* ref, int64_t n, float coef, void* stream);
 

@@ -172,3 +172,20 @@ def squared_distance(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
                                   native.stream_ptr(a.device)), "nidt_sq_dist")
     native.count_launches(2)
     return out
+
+
+def gather_rows_u8(src: torch.Tensor, idx: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``src[idx]`` for a contiguous uint8 tensor ``[N, ...]`` and an int64 device index vector: one native launch that moves
+    16 bytes per thread regardless of the (odd) row length; ``torch.index_select`` on CPU."""
+    if not src.is_cuda:
+        return src.index_select(0, idx)
+    lib = native.load()
+    rows = int(idx.numel())
+    row_bytes = int(src[0].numel())
+    out = torch.empty((rows,) + tuple(src.shape[1:]), dtype=torch.uint8, device=src.device) if out is None else out
+    lib.nidt_gather_rows_u8.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_void_p]
+    lib.nidt_gather_rows_u8.restype = C.c_int
+    native.check(lib.nidt_gather_rows_u8(native.ptr(src), native.ptr(idx), native.ptr(out), rows, row_bytes, native.stream_ptr(src.device)),
+                 "nidt_gather_rows_u8")
+    native.count_launches(1)
+    return out

@@ -57,6 +57,28 @@ for s, e, n in ev:
         cur_end = e
     prev = short
 print(f"mode={mode} clients={clients}: span {(t1-t0)/1e3:.2f} ms, GPU busy (union) {union/1e3:.2f} ms, idle {(t1-t0-union)/1e3:.2f} ms, {len(ev)} activities")
+def union(iv):
+    iv = sorted(iv); tot = 0.0; ce = None; cs = None; out = []
+    for a, b in iv:
+        if ce is None or a > ce:
+            if ce is not None: out.append((cs, ce))
+            cs, ce = a, b
+        else:
+            ce = max(ce, b)
+    if ce is not None: out.append((cs, ce))
+    return out
+def length(u): return sum(b - a for a, b in u)
+def inter(u, v):
+    i = j = 0; tot = 0.0
+    while i < len(u) and j < len(v):
+        a, b = max(u[i][0], v[j][0]), min(u[i][1], v[j][1])
+        if b > a: tot += b - a
+        if u[i][1] < v[j][1]: i += 1
+        else: j += 1
+    return tot
+ku = union([(s_, e_) for s_, e_, n_ in ev if not n_.startswith("Memcpy") and not n_.startswith("Memset")])
+mu = union([(s_, e_) for s_, e_, n_ in ev if n_.startswith("Memcpy HtoD")])
+print(f"kernels busy {length(ku)/1e3:.2f} ms, H2D copies busy {length(mu)/1e3:.2f} ms, of which under a kernel {inter(ku, mu)/1e3:.2f} ms")
 print("--- busy time by kernel (ms, launches)")
 for n, t in busy.most_common(28):
     print(f"{t/1e3:9.3f}  {cnt[n]:5d}  {n}")

@@ -143,3 +143,23 @@ def test_count_hamming_sqdist_kernels():
     R.prox_sgd_pull(w2, ref.cpu(), 0.1, 0.5)
     ops.prox_pull(w, ref, 0.1, 0.5)
     torch.testing.assert_close(w.cpu(), w2, rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("row_shape", [(121, 145, 121), (5, 7, 3), (4, 4, 4), (33,)])
+def test_gather_rows_u8_matches_index_select(row_shape):
+    """Odd row lengths: neither source nor destination rows are 16-byte aligned."""
+    from neuroimagedisttraining_b200 import ops
+    g = torch.Generator().manual_seed(3)
+    n = 9
+    src = torch.randint(0, 256, (n,) + row_shape, dtype=torch.uint8, generator=g).cuda()
+    for idx in ([0], [8, 8, 1], [3, 0, 7, 7, 2, 5, 1]):
+        ix = torch.tensor(idx, dtype=torch.int64, device="cuda")
+        out = ops.gather_rows_u8(src, ix)
+        assert torch.equal(out, src.index_select(0, ix))
+    # destination that does not start on a 16-byte boundary
+    buf = torch.zeros(4 * src[0].numel() + 64, dtype=torch.uint8, device="cuda")
+    view = buf[5:5 + 3 * src[0].numel()].view((3,) + row_shape)
+    ix = torch.tensor([6, 2, 4], dtype=torch.int64, device="cuda")
+    ops.gather_rows_u8(src, ix, out=view)
+    assert torch.equal(view, src.index_select(0, ix)) and int(buf[:5].sum()) == 0 and int(buf[5 + 3 * src[0].numel():].sum()) == 0
