@@ -55,6 +55,8 @@ int nidt_sq_dist(const float* a, const float* b, int64_t n, float* scratch, floa
 /* dst[j] = src[idx[j]] for `rows` rows of row_bytes bytes each (any length / alignment): assembles device batches of 8-bit volumes
  * from a device-resident dataset.  idx: int64 on the device. */
 int nidt_gather_rows_u8(const void* src, const int64_t* idx, void* dst, int rows, int64_t row_bytes, void* stream);
+/* n asynchronous host->device row copies (rows: HOST int64 array of source row numbers; host_base should be pinned) in one call. */
+int nidt_copy_rows_h2d(const void* host_base, const int64_t* rows, int n, int64_t row_bytes, void* dst, void* stream);
 /* Ditto proximal pull w -= coef*(w - ref).  ref: fedml_api/standalone/ditto/my_model_trainer.py:63-64. */
 int nidt_prox_pull(float* w, const float* ref, int64_t n, float coef, void* stream);
 

@@ -38,6 +38,18 @@ class BatchStager:
             self._pinned_cache = cache if (cache is not None and cache.is_pinned()) else None
             if self._pinned_cache is None:
                 self.pin_x = [torch.empty(shp, dtype=torch.uint8).pin_memory() for _ in range(depth)]
+            self._native = None
+            self._row_bytes = int(np.prod(store.shape))
+            if self._pinned_cache is not None and self._pinned_cache.is_contiguous():
+                try:
+                    import ctypes as C
+                    from ..ops import native
+                    lib = native.load()
+                    lib.nidt_copy_rows_h2d.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p]
+                    lib.nidt_copy_rows_h2d.restype = C.c_int
+                    self._native = lib
+                except Exception:
+                    self._native = None
 
     def _issue(self, slot: int, idx: torch.Tensor) -> int:
         """Enqueue the H2D copies of one batch on the copy stream; returns the batch size."""
@@ -48,8 +60,15 @@ class BatchStager:
         with torch.cuda.stream(self.copy_stream):
             self.copy_stream.wait_event(self.consumed[slot])
             if self._pinned_cache is not None:
-                for j, i in enumerate(ids):
-                    self.dev_x[slot][j].copy_(self._pinned_cache[int(i)], non_blocking=True)
+                if self._native is not None:      # one native call issues the per-sample copies (no per-copy framework overhead)
+                    rows = np.ascontiguousarray(ids, dtype=np.int64)
+                    rc = self._native.nidt_copy_rows_h2d(self._pinned_cache.data_ptr(), rows.ctypes.data, b, self._row_bytes,
+                                                         self.dev_x[slot].data_ptr(), self.copy_stream.cuda_stream)
+                    if rc != 0:
+                        raise RuntimeError("nidt_copy_rows_h2d failed")
+                else:
+                    for j, i in enumerate(ids):
+                        self.dev_x[slot][j].copy_(self._pinned_cache[int(i)], non_blocking=True)
             else:
                 self.store.fetch(ids, out=self.pin_x[slot])
                 self.dev_x[slot][:b].copy_(self.pin_x[slot][:b], non_blocking=True)

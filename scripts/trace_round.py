@@ -79,6 +79,29 @@ def inter(u, v):
 ku = union([(s_, e_) for s_, e_, n_ in ev if not n_.startswith("Memcpy") and not n_.startswith("Memset")])
 mu = union([(s_, e_) for s_, e_, n_ in ev if n_.startswith("Memcpy HtoD")])
 print(f"kernels busy {length(ku)/1e3:.2f} ms, H2D copies busy {length(mu)/1e3:.2f} ms, of which under a kernel {inter(ku, mu)/1e3:.2f} ms")
+# where are the exposed copies?  walk the timeline: for every H2D interval part not under a kernel, name the last kernel that ended before it
+kern_ev = sorted([(s_, e_, n_) for s_, e_, n_ in ev if not n_.startswith("Mem")])
+import bisect
+starts = [k[0] for k in kern_ev]
+exp = collections.Counter(); expn = collections.Counter()
+for a, b in mu:
+    # subtract kernel union
+    segs = [(a, b)]
+    for ka, kb in ku:
+        if kb <= a or ka >= b: continue
+        ns = []
+        for x, y_ in segs:
+            if ka > x: ns.append((x, min(y_, ka)))
+            if kb < y_: ns.append((max(x, kb), y_))
+        segs = [(x, y_) for x, y_ in ns if y_ > x]
+    for x, y_ in segs:
+        i = bisect.bisect_right(starts, x) - 1
+        prevk = kern_ev[i][2].split("(")[0].split("<")[0][-40:] if i >= 0 else "<start>"
+        nxt = kern_ev[i + 1][2].split("(")[0].split("<")[0][-40:] if i + 1 < len(kern_ev) else "<end>"
+        exp[(prevk, nxt)] += y_ - x; expn[(prevk, nxt)] += 1
+print("--- exposed H2D time by (kernel before -> kernel after) (ms, count)")
+for k_, v in exp.most_common(8):
+    print(f"{v/1e3:9.3f}  {expn[k_]:5d}  {k_[0]}  ->  {k_[1]}")
 print("--- busy time by kernel (ms, launches)")
 for n, t in busy.most_common(28):
     print(f"{t/1e3:9.3f}  {cnt[n]:5d}  {n}")

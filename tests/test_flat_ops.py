@@ -163,3 +163,27 @@ def test_gather_rows_u8_matches_index_select(row_shape):
     ix = torch.tensor([6, 2, 4], dtype=torch.int64, device="cuda")
     ops.gather_rows_u8(src, ix, out=view)
     assert torch.equal(view, src.index_select(0, ix)) and int(buf[:5].sum()) == 0 and int(buf[5 + 3 * src[0].numel():].sum()) == 0
+
+
+@pytest.mark.gpu
+def test_batch_stager_delivers_the_stored_volumes_with_lookahead():
+    """Pinned 8-bit store -> device ring through the native row-copy call; the lookahead stream is resumed by the next iterate()."""
+    from neuroimagedisttraining_b200.data import SyntheticABCD
+    from neuroimagedisttraining_b200.data.loaders import IndexLoader
+    from neuroimagedisttraining_b200.runtime.staging import BatchStager
+    store = SyntheticABCD(24, (9, 11, 7), n_sites=2, seed=3, pin=True)
+    st = BatchStager(store, torch.device("cuda"), 4)
+    a = IndexLoader(np.arange(0, 10), store.labels[:10], store.sites[:10], 4, shuffle=False)
+    b = IndexLoader(np.arange(10, 24), store.labels[10:24], store.sites[10:24], 4, shuffle=False)
+    seen = []
+    for x, y in st.iterate(a, lookahead=b):
+        seen.append((x.clone(), y.clone()))
+    assert st._carry is not None
+    for x, y in st.iterate(b):
+        seen.append((x.clone(), y.clone()))
+    ids = np.concatenate([np.arange(0, 10), np.arange(10, 24)])
+    got = torch.cat([x for x, _ in seen]).cpu()
+    want, labels = store.fetch(ids)
+    assert torch.equal(got, torch.as_tensor(want).cpu())
+    assert torch.allclose(torch.cat([y for _, y in seen]).cpu(), torch.as_tensor(labels).float().cpu())
+    assert [x.shape[0] for x, _ in seen] == [4, 4, 2, 4, 4, 4, 2]
