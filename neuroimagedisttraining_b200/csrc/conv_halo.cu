@@ -149,6 +149,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv3d_halo_kernel(
             const uint32_t planes_lo = tc::desc_lo_sw128(tc::smem_u32(planes)), bring_lo = tc::desc_lo_sw128(tc::smem_u32(bring));
             long long w_b = 0, w_plane = 0, w_tmem = 0, t_all = clock64(), t0;
             const bool prof = (g.debug & 2) != 0;
+            const int64_t iters_total = (int64_t)(s_end - s_begin) * 27 * g.cin_blocks;      // weight tiles this CTA consumes
+            int64_t iter = 0;
+            bool waited = false;
             for (int s = s_begin; s < s_end; ++s, ++local) {
                 int nt, n, hb, d;
                 decode(s, nt, n, hb, d);
@@ -179,14 +182,35 @@ __global__ void __launch_bounds__(kThreads, 1) conv3d_halo_kernel(
                     for (int kh = 0; kh < 3; ++kh, tap_lo += (g.Wbox - 3) * 8)
                         for (int kw = 0; kw < 3; ++kw, tap_lo += 8) {
                             uint32_t a_lo = tap_lo;
-                            for (int cb = 0; cb < g.cin_blocks; ++cb, a_lo += plane_bytes >> 4) {
-                                if (prof) t0 = clock64();
-                                tc::mbar_wait(&b_full[st], ph);
-                                if (prof) w_b += clock64() - t0;
-                                tc::tc_fence_after();
+                            for (int cb = 0; cb < g.cin_blocks; ++cb, a_lo += plane_bytes >> 4, ++iter) {
+                                if (!waited) {      // first tile of the CTA / of a new column: nothing could be checked ahead
+                                    if (prof) t0 = clock64();
+                                    tc::mbar_wait(&b_full[st], ph);
+                                    if (prof) w_b += clock64() - t0;
+                                    tc::tc_fence_after();
+                                }
                                 const uint32_t b_lo = bring_lo + st * (kBTileBytes >> 4);
+                                uint32_t st1 = st + 1, ph1 = ph;
+                                if (st1 == (uint32_t)g.b_stages) { st1 = 0; ph1 ^= 1; }
                                 if (leader) {
-                                    for (int t = 0; t < T; ++t) {        // tile t starts 128 rows = 16 KB further: +1024 in the low word
+                                    tc::umma_bf16_lohi(d_tmem0, a_lo, b_lo, kDescHi, idesc, acc);
+                                    tc::umma_bf16_lohi(d_tmem0, a_lo + 2, b_lo + 2, kDescHi, idesc, 1);
+                                }
+                                // the NEXT weight tile's barrier is checked in the middle of this tap's MMAs (in front of a group it
+                                // would idle the tensor pipe for ~100 cycles: scripts/bench_native/mma_rate.cu, modes 2 / 3)
+                                // (not across a column change: the producer loads the new column's planes first, and the last of
+                                // their slots is only released by the commit that follows this very tap)
+                                waited = (iter + 1 < iters_total) && !(last_of_col && kd == 2 && kh == 2 && kw == 2 && cb + 1 == g.cin_blocks);
+                                if (waited) {
+                                    if (prof) t0 = clock64();
+                                    tc::mbar_wait(&b_full[st1], ph1);
+                                    if (prof) w_b += clock64() - t0;
+                                    tc::tc_fence_after();
+                                }
+                                if (leader) {
+                                    tc::umma_bf16_lohi(d_tmem0, a_lo + 4, b_lo + 4, kDescHi, idesc, 1);
+                                    tc::umma_bf16_lohi(d_tmem0, a_lo + 6, b_lo + 6, kDescHi, idesc, 1);
+                                    for (int t = 1; t < T; ++t) {        // tile t starts 128 rows = 16 KB further: +1024 in the low word
                                         const uint32_t d_tmem = d_tmem0 + t * BLOCK_N;
                                         tc::umma_bf16_lohi(d_tmem, a_lo + t * 1024, b_lo, kDescHi, idesc, acc);
                                         tc::umma_bf16_lohi(d_tmem, a_lo + t * 1024 + 2, b_lo + 2, kDescHi, idesc, 1);
@@ -196,7 +220,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv3d_halo_kernel(
                                     tc::umma_commit(&b_empty[st]);
                                 }
                                 acc = 1;
-                                if (++st == (uint32_t)g.b_stages) { st = 0; ph ^= 1; }
+                                st = st1; ph = ph1;
                             }
                         }
                     if (leader && (kd == 0 || last_of_col)) tc::umma_commit(&plane_empty[slot]);

@@ -161,25 +161,39 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv3d_fprop_tc_kernel(
         constexpr uint32_t idesc = tc::make_idesc_bf16(128, BLOCK_N, 0, 0);
         constexpr uint32_t kDescHi = tc::desc_hi_sw128(1024);
         const uint32_t stage_lo = tc::desc_lo_sw128(tc::smem_u32(stage_base));
+        // The wait for the NEXT stage's operands is placed in the middle of the current stage's MMAs: an mbarrier wait +
+        // tcgen05.fence in front of a group of MMAs leaves the tensor pipe idle for ~100 cycles (the MMA queue is shallow),
+        // in the middle of a group it is free (scripts/bench_native/mma_rate.cu, modes 2 / 3).
         uint32_t s = 0, ph = 0, local = 0;
+        if ((int)blockIdx.x < total_tiles) {
+            tc::mbar_wait(&full[0], 0);
+            tc::tc_fence_after();
+        }
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++local) {
             const int buf = local & 1;
             tc::mbar_wait(&tmem_empty[buf], ((local >> 1) & 1) ^ 1);
             tc::tc_fence_after();
             const uint32_t d_tmem = tmem_base + buf * BLOCK_N;
+            const bool more_tiles = tile + (int)gridDim.x < total_tiles;
             for (int kb = 0; kb < num_kb; ++kb) {
-                tc::mbar_wait(&full[s], ph);
-                tc::tc_fence_after();
                 const uint32_t a_lo = stage_lo + s * (Cfg::kStageBytes >> 4);
                 const uint32_t b_lo = a_lo + (kATileBytes >> 4);
+                uint32_t s1 = s + 1, ph1 = ph;
+                if (s1 == (uint32_t)Cfg::kStages) { s1 = 0; ph1 ^= 1; }
                 if (leader) {
                     tc::umma_bf16_lohi(d_tmem, a_lo, b_lo, kDescHi, idesc, kb != 0);
                     tc::umma_bf16_lohi(d_tmem, a_lo + 2, b_lo + 2, kDescHi, idesc, 1);
+                }
+                if (kb + 1 < num_kb || more_tiles) {
+                    tc::mbar_wait(&full[s1], ph1);
+                    tc::tc_fence_after();
+                }
+                if (leader) {
                     tc::umma_bf16_lohi(d_tmem, a_lo + 4, b_lo + 4, kDescHi, idesc, 1);
                     tc::umma_bf16_lohi(d_tmem, a_lo + 6, b_lo + 6, kDescHi, idesc, 1);
                     tc::umma_commit(&empty[s]);
                 }
-                if (++s == (uint32_t)Cfg::kStages) { s = 0; ph ^= 1; }
+                s = s1; ph = ph1;
             }
             if (leader) tc::umma_commit(&tmem_full[buf]);
         }
@@ -354,18 +368,31 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv3d_wgrad_tc_kernel(
         constexpr uint32_t kDescHi = tc::desc_hi_sw128(1024);
         const uint32_t stage_lo = tc::desc_lo_sw128(tc::smem_u32(smem), kATileBytes);     // MN-major: LBO = the 64-channel half (16 KB)
         uint32_t s = 0, ph = 0;
-        for (int mt = mt_begin; mt < mt_end; ++mt) {
-            tc::mbar_wait(&full[s], ph);
+        if (mt_begin < mt_end) {
+            tc::mbar_wait(&full[0], 0);
             tc::tc_fence_after();
+        }
+        for (int mt = mt_begin; mt < mt_end; ++mt) {
             const uint32_t a_lo = stage_lo + s * (kWgStageBytes >> 4);
             const uint32_t b_lo = a_lo + (2 * kATileBytes >> 4);
+            uint32_t s1 = s + 1, ph1 = ph;
+            if (s1 == (uint32_t)kWgStages) { s1 = 0; ph1 ^= 1; }
             if (leader) {
 #pragma unroll
-                for (int k = 0; k < 8; ++k)     // 16 positions per MMA: two 8-row swizzle groups (SBO = 1024 B); +2048 B per step
+                for (int k = 0; k < 4; ++k)     // 16 positions per MMA: two 8-row swizzle groups (SBO = 1024 B); +2048 B per step
                     tc::umma_bf16_lohi(tmem_base, a_lo + k * 128, b_lo + k * 128, kDescHi, idesc, (k != 0) || (mt != mt_begin));
+            }
+            if (mt + 1 < mt_end) {              // next stage's wait in the middle of this stage's MMAs (see fprop)
+                tc::mbar_wait(&full[s1], ph1);
+                tc::tc_fence_after();
+            }
+            if (leader) {
+#pragma unroll
+                for (int k = 4; k < 8; ++k)
+                    tc::umma_bf16_lohi(tmem_base, a_lo + k * 128, b_lo + k * 128, kDescHi, idesc, 1);
                 tc::umma_commit(&empty[s]);
             }
-            if (++s == (uint32_t)kWgStages) { s = 0; ph ^= 1; }
+            s = s1; ph = ph1;
         }
         if (leader) tc::umma_commit(tmem_full);
     } else {

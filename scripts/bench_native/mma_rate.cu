@@ -74,7 +74,20 @@ __global__ void __launch_bounds__(128, 1) group_kernel(long long* out, int group
         const uint32_t a_lo = tc::desc_lo_sw128(tc::smem_u32(smem)), b_lo = tc::desc_lo_sw128(tc::smem_u32(smem) + 80 * 1024);
         long long t0 = clock64();
         for (int gi = 0; gi < groups; ++gi) {
-            if (kMode >= 2) { tc::mbar_wait(&done_bar, 0); tc::tc_fence_after(); }
+            if (kMode == 2) { tc::mbar_wait(&done_bar, 0); tc::tc_fence_after(); }
+            if (kMode == 3) {       // the wait for the NEXT group's operands sits in the middle of this group's MMAs
+                if (leader) {
+#pragma unroll
+                    for (int m = 0; m < kGroup / 2; ++m) tc::umma_bf16_lohi(tmem + (m >> 2) * N % 256, a_lo + (m >> 2) * 1024 + (m & 3) * 2, b_lo + (m & 3) * 2, hi, idesc, 1);
+                }
+                tc::mbar_wait(&done_bar, 0); tc::tc_fence_after();
+                if (leader) {
+#pragma unroll
+                    for (int m = kGroup / 2; m < kGroup; ++m) tc::umma_bf16_lohi(tmem + (m >> 2) * N % 256, a_lo + (m >> 2) * 1024 + (m & 3) * 2, b_lo + (m & 3) * 2, hi, idesc, 1);
+                    tc::umma_commit(&bars[gi & 7]);
+                }
+                continue;
+            }
             if (leader) {
 #pragma unroll
                 for (int m = 0; m < kGroup; ++m) tc::umma_bf16_lohi(tmem + (m >> 2) * N % 256, a_lo + (m >> 2) * 1024 + (m & 3) * 2, b_lo + (m & 3) * 2, hi, idesc, 1);
@@ -102,7 +115,7 @@ void run_group(int grid) {
     long long h[148]; cudaMemcpy(h, d, sizeof(long long) * grid, cudaMemcpyDeviceToHost);
     long long mx = 0; for (int i = 0; i < grid; ++i) mx = h[i] > mx ? h[i] : mx;
     printf("N=%d groups of %d MMAs, mode %d (%s): %.1f cycles per group = %.1f per MMA   [%s]\n", N, G, M,
-           M == 0 ? "no commit" : M == 1 ? "commit per group" : "wait+fence, commit per group", (double)mx / groups, (double)mx / groups / G, cudaGetErrorString(e));
+           M == 0 ? "no commit" : M == 1 ? "commit per group" : M == 2 ? "wait+fence before the group, commit" : "wait+fence in the middle of the group, commit", (double)mx / groups, (double)mx / groups / G, cudaGetErrorString(e));
     cudaFree(d);
 }
 
@@ -124,6 +137,7 @@ void run(const char* tag, int grid, int shift = 0) {
 int main() {
     run_group<64, 8, 0>(148); run_group<64, 8, 1>(148); run_group<64, 8, 2>(148); run_group<64, 12, 1>(148); run_group<64, 12, 2>(148);
     run_group<128, 8, 1>(148); run_group<128, 8, 2>(148); run_group<64, 4, 2>(148);
+    run_group<64, 4, 3>(148); run_group<64, 8, 3>(148); run_group<128, 4, 3>(148); run_group<128, 4, 2>(148);
     run<64, 0>("same A ", 148); run<128, 0>("same A ", 148); run<256, 0>("same A ", 148);
     run<64, 1>("4 A tiles", 148); run<128, 1>("4 A tiles", 148); run<256, 1>("4 A tiles", 148);
     for (int sh : {1, 2, 4, 7, 34, 35}) { run<64, 1>("4 A tiles", 148, sh); run<128, 1>("4 A tiles", 148, sh); }

@@ -43,6 +43,9 @@ for ci, (N, Cin, D, H, W, Cout, pad, bn) in enumerate(CASES):
         serr = (part[:, 0].sum(0) - yb.sum(0)).abs().max().item() / (yb.sum(0).abs().max().item() + 1e-6)
         s2err = (part[:, 1].sum(0) - (yb * yb).sum(0)).abs().max().item() / (yb * yb).sum(0).abs().max().item()
         print(f"case {ci} {(N,Cin,D,H,W,Cout,pad,bn)} base_offset={'off' if flags == 0 else 'on'}: rel err {err:.4f} stats err {serr:.2e} {s2err:.2e}", flush=True)
+    if os.environ.get("HALO_ZERO"): xc = torch.zeros_like(xc)
+    if os.environ.get("HALO_NOSTATS"):
+        print(f"      halo without stats/bias {t_ms(lambda: V.conv3d_halo_fprop(xc, wf, None, pad, block_n=bn, stats=False))*1e3:.1f} us", flush=True)
     t_new = t_ms(lambda: V.conv3d_halo_fprop(xc, wf, bias, pad, block_n=bn, stats=True))
     t_old = t_ms(lambda: V.conv3d_fprop(xc, wf, bias, 3, 1, pad, block_n=bn, stats=True))
     flops = 2.0 * ref.numel() * Cin * 27
