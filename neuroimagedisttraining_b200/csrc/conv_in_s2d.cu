@@ -256,27 +256,45 @@ __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __r
         const bool leader = tc::elect_one();      // the whole warp walks the schedule, one lane issues
         {
             constexpr uint32_t idesc = tc::make_idesc_bf16(128, 64, 0, 0);
-            const uint32_t b_addr = tc::smem_u32(b_tile);
+            // no-swizzle K-major descriptors as (low word, constant high word): SBO = 128 B for both operands,
+            // LBO = 16 B (A: the two K chunks are consecutive positions) / 1024 B (B)
+            constexpr uint32_t kHi = ((128u >> 4) & 0x3FFF) | (1u << 14);
+            const uint32_t a_lo_base = tc::desc_lo_sw128(tc::smem_u32(a_bufs), 16);
+            const uint32_t b_lo = tc::desc_lo_sw128(tc::smem_u32(b_tile), 1024);
+            if ((int)blockIdx.x < g.total_tiles) {
+                tc::mbar_wait(&a_full[0], 0);
+                tc::mbar_wait(&t_empty[0], 1);
+                tc::tc_fence_after();
+            }
             for (int i = 0;; ++i) {
                 const int tile = blockIdx.x + i * gridDim.x;
                 if (tile >= g.total_tiles) break;
                 const int b = i & 1, buf = i % kARing;
-                const uint32_t u = i >> 1;
-                tc::mbar_wait(&a_full[buf], (i / kARing) & 1);
-                tc::mbar_wait(&t_empty[b], (u & 1) ^ 1);
-                tc::tc_fence_after();
-                const uint32_t a_addr = tc::smem_u32(a_bufs + buf * kABytes);
+                const uint32_t a_lo = a_lo_base + buf * (kABytes >> 4);
+                const uint32_t d_tmem = tmem_base + b * 64;
+                if (leader) {
 #pragma unroll
-                for (int t = 0; t < 9; ++t) {            // (jd, jh)
-                    const int jd = t / 3, jh = t % 3;
+                    for (int t = 0; t < 5; ++t) {            // (jd, jh)
+                        const int jd = t / 3, jh = t % 3;
 #pragma unroll
-                    for (int pr = 0; pr < 2; ++pr) {     // K = 16: taps (jw, jw+1) = 2 consecutive positions, LBO = 16 B
-                        const uint64_t da = desc_noswz(a_addr + (jd * 4 + jh) * kLineBytes + pr * 32, 16, 128);
-                        const uint64_t db = desc_noswz(b_addr + (t * 4 + pr * 2) * 1024, 1024, 128);
-                        if (leader) tc::umma_bf16(tmem_base + b * 64, da, db, idesc, (t | pr) != 0);
+                        for (int pr = 0; pr < 2; ++pr)       // K = 16: taps (jw, jw+1) = 2 consecutive positions
+                            tc::umma_bf16_lohi(d_tmem, a_lo + (((jd * 4 + jh) * kLineBytes + pr * 32) >> 4), b_lo + (t * 4 + pr * 2) * 64, kHi, idesc, (t | pr) != 0);
                     }
                 }
+                if (tile + (int)gridDim.x < g.total_tiles) {  // next tile's lines / accumulator, checked in the middle of this tile's MMAs
+                    const int i1 = i + 1;
+                    tc::mbar_wait(&a_full[i1 % kARing], (i1 / kARing) & 1);
+                    tc::mbar_wait(&t_empty[i1 & 1], (((uint32_t)i1 >> 1) & 1) ^ 1);
+                    tc::tc_fence_after();
+                }
                 if (leader) {
+#pragma unroll
+                    for (int t = 5; t < 9; ++t) {
+                        const int jd = t / 3, jh = t % 3;
+#pragma unroll
+                        for (int pr = 0; pr < 2; ++pr)
+                            tc::umma_bf16_lohi(d_tmem, a_lo + (((jd * 4 + jh) * kLineBytes + pr * 32) >> 4), b_lo + (t * 4 + pr * 2) * 64, kHi, idesc, 1);
+                    }
                     tc::umma_commit(&a_empty[buf]);
                     tc::umma_commit(&t_full[b]);
                 }
@@ -404,29 +422,47 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __res
         const bool leader = tc::elect_one();
         {
             constexpr uint32_t idesc = tc::make_idesc_bf16(128, 64, 1, 1);
+            // descriptors as (low word, constant high word): one 32-bit add per MMA, no 64-bit rebuild
+            // A = lines, MN-major no swizzle: M chunks (lines) kWgLineBytes apart (SBO), K groups (8 positions) 128 B apart (LBO)
+            // B = dY, MN-major SW128 (N = 64 co = one chunk; 8-position groups 1 KiB apart)
+            constexpr uint32_t a_hi = ((kWgLineBytes >> 4) & 0x3FFF) | (1u << 14);
+            constexpr uint32_t b_hi = tc::desc_hi_sw128(1024);
+            const uint32_t a_lo_base = tc::desc_lo_sw128(tc::smem_u32(a_bufs), 128);
+            const uint32_t b_lo_base = tc::desc_lo_sw128(tc::smem_u32(dy_tiles), kT16);
+            const bool any = (int)blockIdx.x < g.total_tiles;
+            if (any) {
+                tc::mbar_wait(&a_full[0], 0);
+                tc::mbar_wait(&dy_full[0], 0);
+                tc::tc_fence_after();
+            }
             int i = 0;
             for (;; ++i) {
                 const int tile = blockIdx.x + i * gridDim.x;
                 if (tile >= g.total_tiles) break;
                 const int b = i % kARing;
                 const int slot = i % kDyRing;
-                tc::mbar_wait(&a_full[b], (i / kARing) & 1);
-                tc::mbar_wait(&dy_full[slot], (i / kDyRing) & 1);
-                tc::tc_fence_after();
-                const uint32_t dy_addr = tc::smem_u32(dy_tiles + slot * kT16);
-                const uint32_t a_addr = tc::smem_u32(a_bufs + b * kWgABytes);
-#pragma unroll 1
-                for (int ks = 0; ks < 8; ++ks) {          // 16 positions per MMA
-                    // B = dY, MN-major SW128 (N = 64 co = one chunk; 8-position groups 1 KiB apart)
-                    const uint64_t db = tc::make_smem_desc_sw128(dy_addr + ks * 2048, kT16, 1024);
+                const uint32_t a_lo = a_lo_base + b * (kWgABytes >> 4);
+                const uint32_t b_lo = b_lo_base + slot * (kT16 >> 4);
+                const uint32_t acc0 = i != 0;
+                if (leader) {
 #pragma unroll
-                    for (int jw = 0; jw < ((g.dbg & 2) ? (ks == 0 ? 1 : 0) : 3); ++jw) {
-                        // A = lines, MN-major no swizzle: M chunks (lines) 1 KiB apart (SBO), K groups (8 positions) 128 B apart (LBO)
-                        const uint64_t da = desc_noswz(a_addr + jw * 16 + ks * 256, 128, kWgLineBytes);
-                        if (leader) tc::umma_bf16(tmem_base + jw * 64, da, db, idesc, (i | ks) != 0);
-                    }
+                    for (int ks = 0; ks < 4; ++ks)            // 16 positions per MMA; +256 B (A) / +2048 B (B) per step
+#pragma unroll
+                        for (int jw = 0; jw < 3; ++jw)
+                            tc::umma_bf16_lohi2(tmem_base + jw * 64, a_lo + jw + ks * 16, a_hi, b_lo + ks * 128, b_hi, idesc, ks == 0 ? acc0 : 1u);
+                }
+                if (tile + (int)gridDim.x < g.total_tiles) {   // next tile's operands, checked in the middle of this tile's MMAs
+                    const int i1 = i + 1;
+                    tc::mbar_wait(&a_full[i1 % kARing], (i1 / kARing) & 1);
+                    tc::mbar_wait(&dy_full[i1 % kDyRing], (i1 / kDyRing) & 1);
+                    tc::tc_fence_after();
                 }
                 if (leader) {
+#pragma unroll
+                    for (int ks = 4; ks < 8; ++ks)
+#pragma unroll
+                        for (int jw = 0; jw < 3; ++jw)
+                            tc::umma_bf16_lohi2(tmem_base + jw * 64, a_lo + jw + ks * 16, a_hi, b_lo + ks * 128, b_hi, idesc, 1u);
                     tc::umma_commit(&a_empty[b]);
                     tc::umma_commit(&dy_empty[slot]);
                 }
