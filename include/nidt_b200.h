@@ -55,6 +55,8 @@ int nidt_sq_dist(const float* a, const float* b, int64_t n, float* scratch, floa
 /* dst[j] = src[idx[j]] for `rows` rows of row_bytes bytes each (any length / alignment): assembles device batches of 8-bit volumes
  * from a device-resident dataset.  idx: int64 on the device. */
 int nidt_gather_rows_u8(const void* src, const int64_t* idx, void* dst, int rows, int64_t row_bytes, void* stream);
+/* the same with at most max_blocks CTAs; src and idx may be pinned host memory (the kernel reads it over PCIe) */
+int nidt_gather_rows_u8_capped(const void* src, const int64_t* idx, void* dst, int rows, int64_t row_bytes, int max_blocks, void* stream);
 /* n asynchronous host->device row copies (rows: HOST int64 array of source row numbers; host_base should be pinned) in one call. */
 int nidt_copy_rows_h2d(const void* host_base, const int64_t* rows, int n, int64_t row_bytes, void* dst, void* stream);
 /* Ditto proximal pull w -= coef*(w - ref).  ref: fedml_api/standalone/ditto/my_model_trainer.py:63-64. */
@@ -154,6 +156,41 @@ int nidt_linear_head_fwd_bwd(const float* feat, const float* y, const float* W1,
                              float* gW1, float* gb1, float* gW2, float* gb2, float* dfeat, float* hidden, float* dhidden,
                              float* loss_acc, double* eval_counters, float* logits_out, int B, int F, int Hd, int train,
                              int double_sigmoid, void* stream);
+
+/* ------------------------------------------------------- native step executor (executor.cu) */
+/* One call runs a whole forward / training step / evaluation batch of a conv-BN-ReLU-pool stack + the classifier head: the
+ * ~45 kernel launches of a step are issued from native code instead of one Python -> C transition each (host time per step
+ * 0.5 ms -> < 0.1 ms, which is what small evaluation batches and the end-to-end path are bound by).  The plan holds shapes,
+ * parameter offsets (in floats) into the flat slab and the caller-allocated activation / scratch buffers; nothing is allocated. */
+typedef struct {
+    int cin, cout, k, stride, pad, pool_k, pool_s, relu, has_bias;
+    int in_d, in_h, in_w, c_d, c_h, c_w;                  /* input extents, conv-output extents */
+    int64_t off_w, off_b, off_gamma, off_beta, off_rm, off_rv, off_nbt;
+    void *y, *dy, *a, *da, *ymax;                         /* conv output, its gradient, block output, its gradient, arg-max values */
+    float *scale, *shift, *mean, *invstd, *c12, *bwd_partials, *stats;
+    void *wf, *wd;                                        /* packed bf16 weights (blocks >= 1) */
+    float* wg_scratch;
+    int stats_tiles, s2d, block_n, dgrad_block_n, splits;
+    int box[4], dbox[4];                                  /* M-tile boxes (bw,bh,bd,bn) of fprop/wgrad and of dgrad at max_batch */
+} nidt_block_t;
+typedef struct {
+    int n_blocks, max_batch;
+    nidt_block_t blocks[8];
+    int64_t off_fc1_w, off_fc1_b, off_fc2_w, off_fc2_b;
+    int head_s, head_c, head_hidden;
+    float p_drop, input_scale;
+    float *loss_acc, *eval_logits, *norm_scratch;
+} nidt_plan_t;
+/* weights of the attached slab -> bf16 packed copies (call when the slab changed outside a training step) */
+int nidt_plan_pack_weights(const nidt_plan_t* plan, const float* slab, void* stream);
+/* forward + head + backward (gradients into `grad`, params-first layout of the slab) and, when do_update != 0, the masked SGD
+ * update + re-pack of the weights.  Returns the number of kernel launches through *launches. */
+int nidt_plan_train_step(const nidt_plan_t* plan, const void* x_u8, const float* y, int batch, float* slab, float* grad, float* mom,
+                         const float* mask, int64_t n_params, float lr, float momentum, float wd, float clip_norm, int first_step,
+                         uint64_t seed, int do_update, int* launches, void* stream);
+/* eval-mode forward + eval head (counters may be null: logits only) */
+int nidt_plan_eval(const nidt_plan_t* plan, const void* x_u8, const float* y, int batch, const float* slab, double* counters,
+                   int double_sigmoid, int* launches, void* stream);
 
 /* ------------------------------------- compute fused with its collective over NVLink symmetric memory (sym_agg.cu) */
 /* All ranks call these with the same arguments order; the kernels wait for each other through release/acquire flags.

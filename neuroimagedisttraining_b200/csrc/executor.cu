@@ -1,0 +1,190 @@
+// Native step executor: walks a plan (conv-BN-ReLU-pool blocks + classifier head) and issues every kernel of a forward /
+// training step / evaluation batch from native code.  Same launch sequence as ops/engine_b200.py (which keeps a Python path
+// for per-kernel profiling); the reference has no counterpart -- its step is autograd over ATen / cuDNN / cuBLAS calls
+// (fedml_api/standalone/sailentgrads/my_model_trainer.py:201-235).
+#include "common.cuh"
+#include "../../include/nidt_b200.h"
+#include <mutex>
+#include <map>
+#include <tuple>
+
+namespace {
+
+struct Box { int bw, bh, bd, bn; };
+
+// box of output positions (bw*bh*bd*bn <= 128) maximising valid rows / (tiles * 128); ties prefer wider boxes
+// (the same search as ops/engine_b200.py::choose_box, cached per shape)
+Box choose_box(int W, int H, int D, int N) {
+    static std::mutex mu;
+    static std::map<std::tuple<int, int, int, int>, Box> cache;
+    std::lock_guard<std::mutex> lock(mu);
+    auto key = std::make_tuple(W, H, D, N);
+    auto it = cache.find(key);
+    if (it != cache.end()) return it->second;
+    Box best{1, 1, 1, 1};
+    long best_util = -1;
+    int best_tie = 0;
+    const double total = (double)W * H * D * N;
+    for (int bw = 1; bw <= (W < 128 ? W : 128); ++bw) {
+        const int tw = (W + bw - 1) / bw;
+        for (int bh = 1; bh <= (H < 128 / bw ? H : 128 / bw); ++bh) {
+            const int th = (H + bh - 1) / bh;
+            for (int bd = 1; bd <= (D < 128 / (bw * bh) ? D : 128 / (bw * bh)); ++bd) {
+                const int td = (D + bd - 1) / bd;
+                int bn = 128 / (bw * bh * bd);
+                if (bn > N) bn = N;
+                if (bn < 1) continue;
+                const int tn = (N + bn - 1) / bn;
+                const double util = total / ((double)tw * th * td * tn * 128.0);
+                const long u = (long)(util * 10000.0 + 0.5);      // round(util, 4)
+                const int tie = bw * 1000 + bh;
+                if (u > best_util || (u == best_util && tie > best_tie)) { best = Box{bw, bh, bd, bn}; best_util = u; best_tie = tie; }
+            }
+        }
+    }
+    cache[key] = best;
+    return best;
+}
+
+inline float* at(float* slab, int64_t off) { return off >= 0 ? slab + off : nullptr; }
+inline const float* at(const float* slab, int64_t off) { return off >= 0 ? slab + off : nullptr; }
+
+#define NIDT_TRY(expr)                 \
+    do {                               \
+        const int rc_ = (expr);        \
+        if (rc_ != 0) return rc_;      \
+    } while (0)
+
+struct Ctx {
+    const nidt_plan_t* p;
+    int B;
+    void* st;
+    int launches = 0;
+    Box cur_box[8];
+};
+
+int pack_weights(Ctx& c, const float* slab) {
+    for (int i = 1; i < c.p->n_blocks; ++i) {
+        const nidt_block_t& b = c.p->blocks[i];
+        NIDT_TRY(nidt_pack_conv_weights(at(slab, b.off_w), b.cout, b.cin, b.k * b.k * b.k, b.wf, b.wd, c.st));
+        ++c.launches;
+    }
+    return 0;
+}
+
+int forward(Ctx& c, const void* x, float* slab, bool train) {
+    const nidt_plan_t* p = c.p;
+    const int B = c.B;
+    const void* prev = nullptr;
+    for (int i = 0; i < p->n_blocks; ++i) {
+        const nidt_block_t& b = p->blocks[i];
+        float* stats = train ? b.stats : nullptr;
+        const float* bias = b.has_bias ? at((const float*)slab, b.off_b) : nullptr;
+        int tiles = b.stats_tiles;
+        if (i == 0) {
+            if (b.s2d) NIDT_TRY(nidt_conv_in_s2d_fprop(x, at(slab, b.off_w), bias, b.y, stats, B, b.in_d, b.in_h, b.in_w, p->input_scale, c.st));
+            else NIDT_TRY(nidt_conv_in_fprop(x, at(slab, b.off_w), bias, b.y, stats, B, b.in_d, b.in_h, b.in_w, b.k, b.stride, b.pad, p->input_scale, c.st));
+        } else {
+            const Box bx = B == p->max_batch ? Box{b.box[0], b.box[1], b.box[2], b.box[3]} : choose_box(b.c_w, b.c_h, b.c_d, B);
+            c.cur_box[i] = bx;
+            NIDT_TRY(nidt_conv3d_fprop_tc(prev, b.wf, bias, b.y, stats, B, b.in_d, b.in_h, b.in_w, b.cin, b.c_d, b.c_h, b.c_w, b.cout, b.k, b.stride,
+                                          b.pad, bx.bw, bx.bh, bx.bd, bx.bn, b.block_n, c.st));
+            if (B != p->max_batch) tiles = nidt_conv3d_m_tiles(B, b.c_d, b.c_h, b.c_w, bx.bw, bx.bh, bx.bd, bx.bn);
+        }
+        if (train)
+            NIDT_TRY(nidt_bn_finalize(b.stats, tiles, b.cout, (double)B * b.c_d * b.c_h * b.c_w, at(slab, b.off_gamma), at(slab, b.off_beta),
+                                      at(slab, b.off_rm), at(slab, b.off_rv), at(slab, b.off_nbt), 0.1f, 1e-5f, b.scale, b.shift, b.mean, b.invstd, c.st));
+        else
+            NIDT_TRY(nidt_bn_eval_prepare(b.cout, at(slab, b.off_gamma), at(slab, b.off_beta), at(slab, b.off_rm), at(slab, b.off_rv), 1e-5f, b.scale,
+                                          b.shift, c.st));
+        NIDT_TRY(nidt_bn_relu_pool_fwd(b.y, b.a, (train && b.ymax != nullptr) ? b.ymax : nullptr, B, b.c_d, b.c_h, b.c_w, b.cout, b.pool_k, b.pool_s,
+                                       b.scale, b.shift, b.relu, c.st));
+        c.launches += 3;
+        prev = b.a;
+    }
+    return 0;
+}
+
+int head(Ctx& c, const float* y, const float* slab, float* grad, bool train, double* counters, int double_sigmoid, uint64_t seed) {
+    const nidt_plan_t* p = c.p;
+    const nidt_block_t& last = p->blocks[p->n_blocks - 1];
+    const bool g = train && grad != nullptr;
+    NIDT_TRY(nidt_head_fwd_bwd(last.a, y, at(slab, p->off_fc1_w), at(slab, p->off_fc1_b), at(slab, p->off_fc2_w), at(slab, p->off_fc2_b),
+                               g ? at(grad, p->off_fc1_w) : nullptr, g ? at(grad, p->off_fc1_b) : nullptr, g ? at(grad, p->off_fc2_w) : nullptr,
+                               g ? at(grad, p->off_fc2_b) : nullptr, train ? last.da : nullptr, train ? p->loss_acc : nullptr, counters, p->eval_logits,
+                               c.B, p->head_s, p->head_c, p->head_hidden, p->p_drop, seed, train ? 1 : 0, double_sigmoid, c.st));
+    ++c.launches;
+    return 0;
+}
+
+int backward(Ctx& c, const void* x, float* grad) {
+    const nidt_plan_t* p = c.p;
+    const int B = c.B;
+    for (int i = p->n_blocks - 1; i >= 0; --i) {
+        const nidt_block_t& b = p->blocks[i];
+        NIDT_TRY(nidt_bn_relu_pool_bwd(b.y, b.ymax, b.da, b.dy, B, b.c_d, b.c_h, b.c_w, b.cout, b.pool_k, b.pool_s, b.scale, b.shift, b.mean, b.invstd,
+                                       b.bwd_partials, b.c12, at(grad, b.off_gamma), at(grad, b.off_beta), b.relu, c.st));
+        c.launches += 3;
+        if (i == 0) {
+            float* gb = b.has_bias ? at(grad, b.off_b) : nullptr;
+            if (b.s2d) NIDT_TRY(nidt_conv_in_s2d_wgrad(x, b.dy, at(grad, b.off_w), gb, b.wg_scratch, B, b.in_d, b.in_h, b.in_w, p->input_scale, c.st));
+            else NIDT_TRY(nidt_conv_in_wgrad(x, b.dy, at(grad, b.off_w), gb, b.wg_scratch, B, b.in_d, b.in_h, b.in_w, b.k, b.stride, b.pad, p->input_scale, c.st));
+            c.launches += 2;
+        } else {
+            const nidt_block_t& prev = p->blocks[i - 1];
+            const Box bx = c.cur_box[i];
+            int splits = b.splits;
+            if (B != p->max_batch) {
+                const int mt = nidt_conv3d_m_tiles(B, b.c_d, b.c_h, b.c_w, bx.bw, bx.bh, bx.bd, bx.bn);
+                if (splits > mt) splits = mt;
+                if (splits < 1) splits = 1;
+            }
+            NIDT_TRY(nidt_conv3d_wgrad_tc(b.dy, prev.a, at(grad, b.off_w), b.wg_scratch, B, b.in_d, b.in_h, b.in_w, b.cin, b.c_d, b.c_h, b.c_w, b.cout,
+                                          b.k, b.stride, b.pad, bx.bw, bx.bh, bx.bd, bx.bn, splits, c.st));
+            // dgrad = fprop of dY with the transposed, tap-flipped weights and pad' = k-1-pad
+            const Box db = B == p->max_batch ? Box{b.dbox[0], b.dbox[1], b.dbox[2], b.dbox[3]} : choose_box(b.in_w, b.in_h, b.in_d, B);
+            NIDT_TRY(nidt_conv3d_fprop_tc(b.dy, b.wd, nullptr, prev.da, nullptr, B, b.c_d, b.c_h, b.c_w, b.cout, b.in_d, b.in_h, b.in_w, b.cin, b.k, 1,
+                                          b.k - 1 - b.pad, db.bw, db.bh, db.bd, db.bn, b.dgrad_block_n, c.st));
+            c.launches += 3;
+        }
+    }
+    return 0;
+}
+
+}  // namespace
+
+NIDT_API int nidt_plan_pack_weights(const nidt_plan_t* plan, const float* slab, void* stream) {
+    NIDT_REQUIRE(plan != nullptr && plan->n_blocks >= 1 && plan->n_blocks <= 8, "nidt_plan: bad plan");
+    Ctx c{plan, plan->max_batch, stream};
+    return pack_weights(c, slab);
+}
+
+NIDT_API int nidt_plan_train_step(const nidt_plan_t* plan, const void* x_u8, const float* y, int batch, float* slab, float* grad, float* mom,
+                                  const float* mask, int64_t n_params, float lr, float momentum, float wd, float clip_norm, int first_step,
+                                  uint64_t seed, int do_update, int* launches, void* stream) {
+    NIDT_REQUIRE(plan != nullptr && plan->n_blocks >= 1 && plan->n_blocks <= 8, "nidt_plan: bad plan");
+    NIDT_REQUIRE(batch >= 1 && batch <= plan->max_batch, "nidt_plan_train_step: batch %d exceeds the plan's %d", batch, plan->max_batch);
+    Ctx c{plan, batch, stream};
+    NIDT_TRY(forward(c, x_u8, slab, true));
+    NIDT_TRY(head(c, y, slab, grad, true, nullptr, 1, seed));
+    NIDT_TRY(backward(c, x_u8, grad));
+    if (do_update) {
+        NIDT_TRY(nidt_masked_sgd_step(slab, grad, momentum != 0.f ? mom : nullptr, mask, n_params, lr, momentum, wd, clip_norm, first_step,
+                                      plan->norm_scratch, nullptr, stream));
+        c.launches += 2;
+        NIDT_TRY(pack_weights(c, slab));
+    }
+    if (launches != nullptr) *launches = c.launches;
+    return 0;
+}
+
+NIDT_API int nidt_plan_eval(const nidt_plan_t* plan, const void* x_u8, const float* y, int batch, const float* slab, double* counters,
+                            int double_sigmoid, int* launches, void* stream) {
+    NIDT_REQUIRE(plan != nullptr && plan->n_blocks >= 1 && plan->n_blocks <= 8, "nidt_plan: bad plan");
+    NIDT_REQUIRE(batch >= 1 && batch <= plan->max_batch, "nidt_plan_eval: batch %d exceeds the plan's %d", batch, plan->max_batch);
+    Ctx c{plan, batch, stream};
+    NIDT_TRY(forward(c, x_u8, const_cast<float*>(slab), false));
+    NIDT_TRY(head(c, y, slab, nullptr, false, counters, double_sigmoid, 0));
+    if (launches != nullptr) *launches = c.launches;
+    return 0;
+}

@@ -365,12 +365,21 @@ __global__ void __launch_bounds__(256) gather_rows_u8_kernel(const uint8_t* __re
 
 // idx: int64 device array of `rows` source row numbers.  The source allocation must be readable up to the next 16-byte boundary
 // past its last row (true for any cudaMalloc'ed / PyTorch buffer: allocations are padded to at least 256 bytes).
+static int gather_rows_launch(const void* src, const int64_t* idx, void* dst, int rows, int64_t row_bytes, int max_blocks, void* stream);
 NIDT_API int nidt_gather_rows_u8(const void* src, const int64_t* idx, void* dst, int rows, int64_t row_bytes, void* stream) {
-    NIDT_REQUIRE(rows >= 0 && row_bytes >= 16, "nidt_gather_rows_u8: rows=%d row_bytes=%lld", rows, (long long)row_bytes);
+    return gather_rows_launch(src, idx, dst, rows, row_bytes, kNumSMs * 16, stream);
+}
+// Same gather with a capped grid: src / idx may be PINNED HOST memory (read over PCIe by the kernel itself), so a batch is
+// staged by a few CTAs next to the compute kernels instead of by the copy engine.
+NIDT_API int nidt_gather_rows_u8_capped(const void* src, const int64_t* idx, void* dst, int rows, int64_t row_bytes, int max_blocks, void* stream) {
+    return gather_rows_launch(src, idx, dst, rows, row_bytes, max_blocks, stream);
+}
+static int gather_rows_launch(const void* src, const int64_t* idx, void* dst, int rows, int64_t row_bytes, int max_blocks, void* stream) {
+    NIDT_REQUIRE(rows >= 0 && row_bytes >= 16 && max_blocks >= 1, "nidt_gather_rows_u8: rows=%d row_bytes=%lld", rows, (long long)row_bytes);
     if (rows == 0) return 0;
     const int64_t nvec = ((int64_t)rows * row_bytes) >> 4;
     int64_t grid = (nvec + 255) / 256;
-    if (grid > (int64_t)kNumSMs * 16) grid = (int64_t)kNumSMs * 16;
+    if (grid > (int64_t)max_blocks) grid = (int64_t)max_blocks;
     if (grid < 1) grid = 1;
     gather_rows_u8_kernel<<<(int)grid, 256, 0, (cudaStream_t)stream>>>((const uint8_t*)src, idx, (uint8_t*)dst, rows, row_bytes);
     NIDT_LAUNCH_CHECK();

@@ -13,6 +13,7 @@ optimizer state are fp32 in the slab.  Interface-compatible with :class:`fl.engi
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional, Tuple
 
 import torch
@@ -60,6 +61,12 @@ def _declare(lib) -> None:
     lib.nidt_conv_in_s2d_wgrad.restype = i32
     lib.nidt_conv3d_wgrad_scratch_floats.argtypes = [i32, i32, i32, i32]
     lib.nidt_conv3d_wgrad_scratch_floats.restype = i64
+    lib.nidt_plan_pack_weights.argtypes = [vp, vp, vp]
+    lib.nidt_plan_pack_weights.restype = i32
+    lib.nidt_plan_train_step.argtypes = [vp, vp, vp, i32, vp, vp, vp, vp, i64, f32, f32, f32, f32, i32, u64, i32, vp, vp]
+    lib.nidt_plan_train_step.restype = i32
+    lib.nidt_plan_eval.argtypes = [vp, vp, vp, i32, vp, vp, i32, vp, vp]
+    lib.nidt_plan_eval.restype = i32
     for name, argtypes in {
         "nidt_ew_bf16": [vp, vp, vp, i64, i32, vp],
         "nidt_maxpool3d_fwd": [vp, vp, vp] + [i32] * 8 + [vp],
@@ -79,6 +86,25 @@ def _declare(lib) -> None:
 
 
 import functools
+
+
+class _BlockC(C.Structure):
+    """Mirror of ``nidt_block_t`` (include/nidt_b200.h)."""
+    _fields_ = ([(n, C.c_int) for n in ("cin", "cout", "k", "stride", "pad", "pool_k", "pool_s", "relu", "has_bias",
+                                        "in_d", "in_h", "in_w", "c_d", "c_h", "c_w")]
+                + [(n, C.c_int64) for n in ("off_w", "off_b", "off_gamma", "off_beta", "off_rm", "off_rv", "off_nbt")]
+                + [(n, C.c_void_p) for n in ("y", "dy", "a", "da", "ymax", "scale", "shift", "mean", "invstd", "c12", "bwd_partials", "stats",
+                                             "wf", "wd", "wg_scratch")]
+                + [(n, C.c_int) for n in ("stats_tiles", "s2d", "block_n", "dgrad_block_n", "splits")]
+                + [("box", C.c_int * 4), ("dbox", C.c_int * 4)])
+
+
+class _PlanC(C.Structure):
+    """Mirror of ``nidt_plan_t``."""
+    _fields_ = [("n_blocks", C.c_int), ("max_batch", C.c_int), ("blocks", _BlockC * 8),
+                ("off_fc1_w", C.c_int64), ("off_fc1_b", C.c_int64), ("off_fc2_w", C.c_int64), ("off_fc2_b", C.c_int64),
+                ("head_s", C.c_int), ("head_c", C.c_int), ("head_hidden", C.c_int), ("p_drop", C.c_float), ("input_scale", C.c_float),
+                ("loss_acc", C.c_void_p), ("eval_logits", C.c_void_p), ("norm_scratch", C.c_void_p)]
 
 
 @functools.lru_cache(maxsize=None)
@@ -147,6 +173,11 @@ class B200Engine:
         self.use_s2d = use_s2d
         self.s2d_wgrad = True
         self._alloc(wgrad_ctas)
+        # native step executor (csrc/executor.cu): one C call per step instead of one per kernel; NIDT_PY_EXEC=1 keeps the
+        # Python launch loop (it is also what start_profile() switches to, for per-kernel timings)
+        self.native_exec = os.environ.get("NIDT_PY_EXEC", "0") != "1"
+        self._plan = self._build_plan()
+        self._launches = C.c_int(0)
 
     # ----------------------------------------------------------------------------- buffers
     def _alloc(self, wgrad_ctas: int) -> None:
@@ -200,6 +231,51 @@ class B200Engine:
         self.head_C = self.plan[-1].cout
         assert self.head_S * self.head_C == self.head.in_features
         self.eval_logits = torch.zeros(B, dtype=torch.float32, device=dev)
+
+    def _build_plan(self) -> _PlanC:
+        from .flat import _norm_scratch
+        lay = self.layout
+        off = lambda name: int(lay[name].offset) if name in lay else -1
+        ptr = lambda t: (t.data_ptr() if t is not None else None)
+        p = _PlanC()
+        p.n_blocks, p.max_batch = len(self.blocks), self.max_batch
+        assert len(self.blocks) <= 8
+        for i, b in enumerate(self.blocks):
+            s, c = b.spec, p.blocks[i]
+            c.cin, c.cout, c.k, c.stride, c.pad = s.cin, s.cout, s.k, s.stride, s.pad
+            c.pool_k, c.pool_s, c.relu, c.has_bias = int(s.pool_k or 0), int(s.pool_s or 0), int(s.relu), int(bool(s.bias))
+            (c.in_d, c.in_h, c.in_w), (c.c_d, c.c_h, c.c_w) = b.in_dhw, b.c_dhw
+            c.off_w, c.off_b = off(s.conv + ".weight"), (off(s.conv + ".bias") if s.bias else -1)
+            c.off_gamma, c.off_beta = off(s.bn + ".weight"), off(s.bn + ".bias")
+            c.off_rm, c.off_rv, c.off_nbt = off(s.bn + ".running_mean"), off(s.bn + ".running_var"), off(s.bn + ".num_batches_tracked")
+            c.y, c.dy, c.a, c.da, c.ymax = ptr(b.y), ptr(b.dy), ptr(b.a), ptr(b.da), ptr(b.ymax)
+            c.scale, c.shift, c.mean, c.invstd = ptr(b.scale), ptr(b.shift), ptr(b.mean), ptr(b.invstd)
+            c.c12, c.bwd_partials, c.stats, c.wg_scratch = ptr(b.c12), ptr(b.bwd_partials), ptr(b.stats), ptr(b.wg_scratch)
+            c.stats_tiles = int(b.stats_tiles)
+            if i == 0:
+                c.s2d = int(b.s2d and self.s2d_wgrad)
+            else:
+                c.wf, c.wd = ptr(b.wf), ptr(b.wd)
+                c.block_n, c.dgrad_block_n, c.splits = b.block_n, b.dgrad_block_n, b.splits
+                for j in range(4):
+                    c.box[j], c.dbox[j] = b.box[j], b.dbox[j]
+        h = self.head
+        p.off_fc1_w, p.off_fc1_b, p.off_fc2_w, p.off_fc2_b = off(h.fc1 + ".weight"), off(h.fc1 + ".bias"), off(h.fc2 + ".weight"), off(h.fc2 + ".bias")
+        p.head_s, p.head_c, p.head_hidden, p.p_drop, p.input_scale = self.head_S, self.head_C, h.hidden, float(h.p_drop), self.input_scale
+        p.eval_logits = self.eval_logits.data_ptr()
+        p.norm_scratch = _norm_scratch(self.device).data_ptr()
+        return p
+
+    def _native_ready(self) -> bool:
+        """Native executor usable for this call; packs the weights of a newly attached slab."""
+        if not self.native_exec or self.profile is not None:
+            return False
+        self._plan.loss_acc = self.loss_acc.data_ptr()      # pop_mean_loss() replaces the accumulator tensor
+        if self._packed_dirty:
+            native.check(self.lib.nidt_plan_pack_weights(C.byref(self._plan), self.slab.flat.data_ptr(), self._stream()), "nidt_plan_pack_weights")
+            native.count_launches(len(self.blocks) - 1)
+            self._packed_dirty = False
+        return True
 
     # ------------------------------------------------------------------------- slab plumbing
     def new_slab(self) -> ParamSlab:
@@ -356,14 +432,42 @@ class B200Engine:
         if not train_mode:
             raise NotImplementedError("eval-mode gradient screening runs on the TorchEngine")
         y = y.to(self.device, torch.float32).contiguous()
+        if self._native_ready():
+            self._native_step(x, y, None, None, None, False, do_update=False)
+            return self.loss_acc
         B = self._forward(x, train=True)
         self._head(B, y, train=True)
         self._backward(B)
         self.step += 1
         return self.loss_acc
 
+    def _check_x(self, x: torch.Tensor) -> torch.Tensor:
+        assert x.dtype == torch.uint8 and x.is_cuda and x.dim() == 4, "B200Engine consumes 8-bit volumes [B,D,H,W]"
+        x = x.contiguous()
+        assert x.shape[0] <= self.max_batch and tuple(x.shape[1:]) == self.in_shape
+        return x
+
+    def _native_step(self, x, y, hp, mask, mom, first_step: bool, do_update: bool) -> None:
+        x = self._check_x(x)
+        self._x = x
+        n = self.layout.param_numel
+        native.check(self.lib.nidt_plan_train_step(
+            C.byref(self._plan), x.data_ptr(), y.data_ptr(), int(x.shape[0]), self.slab.flat.data_ptr(), self.grad.flat.data_ptr(),
+            native.ptr(mom) if (do_update and hp.momentum != 0) else None, native.ptr(mask) if do_update else None, n,
+            float(hp.lr) if do_update else 0.0, float(hp.momentum) if do_update else 0.0, float(hp.wd) if do_update else 0.0,
+            float(hp.clip_norm) if do_update else 0.0, int(first_step), self.seed + 7919 * self.step, int(do_update),
+            C.byref(self._launches), self._stream()), "nidt_plan_train_step")
+        native.count_launches(self._launches.value)
+        self.step += 1
+
     def train_step(self, x, y, hp, mask: Optional[torch.Tensor], mom: Optional[torch.Tensor], first_step: bool,
                    grad_mask: Optional[torch.Tensor] = None) -> None:
+        if grad_mask is None and self._native_ready():
+            if mask is not None:
+                assert mask.numel() >= self.layout.param_numel
+            self._native_step(x, y.to(self.device, torch.float32).contiguous(), hp, mask, mom, first_step, do_update=True)
+            self.loss_steps += 1
+            return
         self.compute_grads(x, y, True)
         self.loss_steps += 1
         if grad_mask is not None:
@@ -380,6 +484,13 @@ class B200Engine:
 
     def eval_batch(self, x, y, counters, double_sigmoid: bool = True) -> None:
         y = y.to(self.device, torch.float32).contiguous()
+        if self._native_ready():
+            x = self._check_x(x)
+            native.check(self.lib.nidt_plan_eval(C.byref(self._plan), x.data_ptr(), y.data_ptr(), int(x.shape[0]), self.slab.flat.data_ptr(),
+                                                 counters.buf.data_ptr() if counters is not None else None, int(double_sigmoid),
+                                                 C.byref(self._launches), self._stream()), "nidt_plan_eval")
+            native.count_launches(self._launches.value)
+            return
         B = self._forward(x, train=False)
         self._head(B, y, train=False, counters=counters, double_sigmoid=double_sigmoid)
 

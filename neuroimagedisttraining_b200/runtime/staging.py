@@ -9,6 +9,8 @@ from __future__ import annotations
 
 from typing import Iterator, Optional, Tuple
 
+import os
+
 import numpy as np
 import torch
 
@@ -39,6 +41,8 @@ class BatchStager:
             if self._pinned_cache is None:
                 self.pin_x = [torch.empty(shp, dtype=torch.uint8).pin_memory() for _ in range(depth)]
             self._native = None
+            self._kernel_blocks = int(os.environ.get("NIDT_STAGER_BLOCKS", "0"))      # > 0: stage with a copy kernel instead of the copy engine
+            self.pin_idx = [torch.empty(batch_size, dtype=torch.int64).pin_memory() for _ in range(depth)]
             self._row_bytes = int(np.prod(store.shape))
             if self._pinned_cache is not None and self._pinned_cache.is_contiguous():
                 try:
@@ -47,6 +51,8 @@ class BatchStager:
                     lib = native.load()
                     lib.nidt_copy_rows_h2d.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p]
                     lib.nidt_copy_rows_h2d.restype = C.c_int
+                    lib.nidt_gather_rows_u8_capped.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_int, C.c_void_p]
+                    lib.nidt_gather_rows_u8_capped.restype = C.c_int
                     self._native = lib
                 except Exception:
                     self._native = None
@@ -60,7 +66,14 @@ class BatchStager:
         with torch.cuda.stream(self.copy_stream):
             self.copy_stream.wait_event(self.consumed[slot])
             if self._pinned_cache is not None:
-                if self._native is not None:      # one native call issues the per-sample copies (no per-copy framework overhead)
+                if self._native is not None and self._kernel_blocks > 0:
+                    # a few CTAs read the pinned host rows over PCIe themselves (no copy-engine traffic next to the compute kernels)
+                    self.pin_idx[slot][:b] = torch.from_numpy(np.ascontiguousarray(ids, dtype=np.int64))
+                    rc = self._native.nidt_gather_rows_u8_capped(self._pinned_cache.data_ptr(), self.pin_idx[slot].data_ptr(), self.dev_x[slot].data_ptr(),
+                                                                 b, self._row_bytes, self._kernel_blocks, self.copy_stream.cuda_stream)
+                    if rc != 0:
+                        raise RuntimeError("nidt_gather_rows_u8_capped failed")
+                elif self._native is not None:      # one native call issues the per-sample copies (no per-copy framework overhead)
                     rows = np.ascontiguousarray(ids, dtype=np.int64)
                     rc = self._native.nidt_copy_rows_h2d(self._pinned_cache.data_ptr(), rows.ctypes.data, b, self._row_bytes,
                                                          self.dev_x[slot].data_ptr(), self.copy_stream.cuda_stream)
