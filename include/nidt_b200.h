@@ -111,6 +111,9 @@ int nidt_conv3d_wgrad_tc_static(const void* dy, const void* x, float* grad, int 
                                 void* stream);
 /* fp32 [Cout][Cin][taps] -> bf16 wf [Cout][taps][Cin] and wd [Cin][taps (flipped)][Cout]. */
 int nidt_pack_conv_weights(const float* w, int Cout, int Cin, int taps, void* wf, void* wd, void* stream);
+/* the same for up to 8 layers in one launch; the arrays are HOST arrays */
+int nidt_pack_conv_weights_multi(int n, const float* const* w, const int* Cout, const int* Cin, const int* taps, void* const* wf,
+                                 void* const* wd, void* stream);
 
 /* ----------------------------- 3x3x3 / stride-1 convolution with the input halo resident in shared memory (conv_halo.cu) */
 /* Same math and layouts as nidt_conv3d_fprop_tc (k = 3, stride = 1; dgrad = the `wd` weights with pad' = 2 - pad), but three

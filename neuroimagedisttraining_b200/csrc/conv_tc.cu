@@ -460,8 +460,58 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restri
     }
 }
 
+// all conv layers of a model in ONE launch (a step re-packs every layer after the SGD update; four ~10 us launches otherwise)
+struct PackMulti {
+    const float* w[8];
+    __nv_bfloat16* wf[8];
+    __nv_bfloat16* wd[8];
+    int Cout[8], Cin[8], taps[8];
+    int block_end[8];       // exclusive prefix of blocks per layer
+    int n;
+};
+__global__ void __launch_bounds__(256) pack_weights_multi_kernel(const PackMulti p) {
+    int l = 0;
+    while (l + 1 < p.n && (int)blockIdx.x >= p.block_end[l]) ++l;
+    const int b0 = l == 0 ? 0 : p.block_end[l - 1];
+    const int nb = p.block_end[l] - b0;
+    const int Cout = p.Cout[l], Cin = p.Cin[l], taps = p.taps[l];
+    const float* __restrict__ w = p.w[l];
+    __nv_bfloat16* __restrict__ wf = p.wf[l];
+    __nv_bfloat16* __restrict__ wd = p.wd[l];
+    const int64_t total = (int64_t)Cout * Cin * taps;
+    for (int64_t i = (int64_t)(blockIdx.x - b0) * blockDim.x + threadIdx.x; i < total; i += (int64_t)nb * blockDim.x) {
+        const int ci = (int)(i % Cin);
+        const int64_t r = i / Cin;
+        const int t = (int)(r % taps);
+        const int co = (int)(r / taps);
+        const __nv_bfloat16 v = __float2bfloat16(w[((size_t)co * Cin + ci) * taps + t]);
+        wf[i] = v;
+        if (wd != nullptr) wd[((size_t)ci * taps + (taps - 1 - t)) * Cout + co] = v;
+    }
+}
+
 }  // namespace nidt
 using namespace nidt;
+
+// n <= 8 layers; arrays are HOST arrays of device pointers / shapes
+NIDT_API int nidt_pack_conv_weights_multi(int n, const float* const* w, const int* Cout, const int* Cin, const int* taps, void* const* wf,
+                                          void* const* wd, void* stream) {
+    NIDT_REQUIRE(n >= 1 && n <= 8, "nidt_pack_conv_weights_multi: %d layers (1..8)", n);
+    PackMulti p;
+    int blocks = 0;
+    for (int l = 0; l < n; ++l) {
+        p.w[l] = w[l]; p.wf[l] = (__nv_bfloat16*)wf[l]; p.wd[l] = (__nv_bfloat16*)wd[l];
+        p.Cout[l] = Cout[l]; p.Cin[l] = Cin[l]; p.taps[l] = taps[l];
+        int64_t nb = ((int64_t)Cout[l] * Cin[l] * taps[l] + 255) / 256;
+        if (nb > kNumSMs * 4) nb = kNumSMs * 4;
+        blocks += (int)nb;
+        p.block_end[l] = blocks;
+    }
+    p.n = n;
+    pack_weights_multi_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(p);
+    NIDT_LAUNCH_CHECK();
+    return 0;
+}
 
 static int pick_tiles(int n, int b) { return (n + b - 1) / b; }
 

@@ -64,11 +64,17 @@ struct Ctx {
 };
 
 int pack_weights(Ctx& c, const float* slab) {
-    for (int i = 1; i < c.p->n_blocks; ++i) {
+    const float* w[8];
+    void *wf[8], *wd[8];
+    int Cout[8], Cin[8], taps[8], n = 0;
+    for (int i = 1; i < c.p->n_blocks; ++i, ++n) {
         const nidt_block_t& b = c.p->blocks[i];
-        NIDT_TRY(nidt_pack_conv_weights(at(slab, b.off_w), b.cout, b.cin, b.k * b.k * b.k, b.wf, b.wd, c.st));
-        ++c.launches;
+        w[n] = at(slab, b.off_w); wf[n] = b.wf; wd[n] = b.wd;
+        Cout[n] = b.cout; Cin[n] = b.cin; taps[n] = b.k * b.k * b.k;
     }
+    if (n == 0) return 0;
+    NIDT_TRY(nidt_pack_conv_weights_multi(n, w, Cout, Cin, taps, wf, wd, c.st));
+    ++c.launches;
     return 0;
 }
 

@@ -273,7 +273,7 @@ class B200Engine:
         self._plan.loss_acc = self.loss_acc.data_ptr()      # pop_mean_loss() replaces the accumulator tensor
         if self._packed_dirty:
             native.check(self.lib.nidt_plan_pack_weights(C.byref(self._plan), self.slab.flat.data_ptr(), self._stream()), "nidt_plan_pack_weights")
-            native.count_launches(len(self.blocks) - 1)
+            native.count_launches(1)
             self._packed_dirty = False
         return True
 
