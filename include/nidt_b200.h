@@ -62,6 +62,14 @@ int nidt_copy_rows_h2d(const void* host_base, const int64_t* rows, int n, int64_
 /* Ditto proximal pull w -= coef*(w - ref).  ref: fedml_api/standalone/ditto/my_model_trainer.py:63-64. */
 int nidt_prox_pull(float* w, const float* ref, int64_t n, float coef, void* stream);
 
+/* ------------------------------------------------- DisPFL prune / regrow on one tensor (mask_select.cu) */
+/* mask (fp32 0/1) in place: mode 0 clears the k active entries with the smallest |v|, mode 1 sets the k inactive entries with the
+ * largest |v| (ties at the threshold in index order: exactly min(k, #candidates) entries change).  One cooperative kernel
+ * (4-pass radix select + ordered tie resolution).  ref: fedml_api/standalone/DisPFL/client.py:71-99 (torch.sort per layer). */
+int nidt_mask_select_scratch_bytes(void);
+int nidt_mask_select_k(const float* v, float* mask, int64_t n, int64_t k, int mode, void* scratch, void* stream);
+int nidt_mask_select_read_changed(const void* scratch, unsigned int* changed, void* stream);
+
 /* ------------------------------------------------- BatchNorm3d + ReLU + MaxPool3d, fused (bn_pool.cu) */
 /* ref: fedml_api/model/cv/salient_models.py:147-168 (cuDNN BN, ATen ReLU/MaxPool3d there). */
 int nidt_bn_bwd_grid(void);

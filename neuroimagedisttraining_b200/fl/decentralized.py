@@ -119,6 +119,15 @@ class DisPFLAPI(_PerClientModels):
         """Magnitude prune per tensor with the cosine-annealed drop ratio (``DisPFL/client.py:71-82``)."""
         drop = cosine_annealing(self.args, round_idx)
         new, removed = mask.clone(), {}
+        if mask.flat.is_cuda:
+            # one host sync for all per-tensor counts, then one radix-select kernel per tensor (csrc/mask_select.cu)
+            names = list(self.layout.param_names)
+            nnz = torch.stack([mask.view(n).sum() for n in names]).tolist()
+            for name, cnt in zip(names, nnz):
+                k = math.ceil(drop * int(cnt))
+                ops.mask_select_k(weights.view(name), new.view(name), k, "fire")
+                removed[name] = k
+            return new, removed
         for name in self.layout.param_names:
             nm, k = ops.reference.fire_mask(weights.view(name), mask.view(name), drop)
             new.view(name).copy_(nm)
@@ -129,7 +138,10 @@ class DisPFLAPI(_PerClientModels):
         new = mask.clone()
         for name in self.layout.param_names:
             g = grad.view(name) if grad is not None else None
-            new.view(name).copy_(ops.reference.regrow_mask(mask.view(name), removed[name], g))
+            if g is not None and new.flat.is_cuda:
+                ops.mask_select_k(g, new.view(name), removed[name], "regrow")
+            else:
+                new.view(name).copy_(ops.reference.regrow_mask(mask.view(name), removed[name], g))
         return new
 
     def _aggregate_func(self, cid: int, nei: Sequence[int], last: List[ParamSlab], masks: List[ParamSlab], shared: List[ParamSlab]):

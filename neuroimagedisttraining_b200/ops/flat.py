@@ -189,3 +189,33 @@ def gather_rows_u8(src: torch.Tensor, idx: torch.Tensor, out: Optional[torch.Ten
                  "nidt_gather_rows_u8")
     native.count_launches(1)
     return out
+
+
+def mask_select_k(values: torch.Tensor, mask: torch.Tensor, k: int, mode: str) -> torch.Tensor:
+    """DisPFL prune / regrow on one tensor, in place on ``mask`` (fp32 0/1, contiguous): ``mode="fire"`` clears the ``k`` active
+    entries with the smallest ``|values|``, ``mode="regrow"`` sets the ``k`` inactive entries with the largest ``|values|``.
+    CUDA: one cooperative radix-select kernel; CPU: the sort-based restatement."""
+    assert mode in ("fire", "regrow") and mask.is_contiguous() and values.numel() == mask.numel()
+    k = int(k)
+    if not mask.is_cuda:
+        flat, v = mask.view(-1), values.reshape(-1).abs()
+        if k > 0:
+            if mode == "fire":
+                score = torch.where(flat > 0, v, torch.full_like(v, float("inf")))
+                idx = torch.sort(score, stable=True)[1][:min(k, int((flat > 0).sum()))]
+                flat[idx] = 0
+            else:
+                score = torch.where(flat == 0, v, torch.full_like(v, -1.0))
+                idx = torch.sort(score, descending=True, stable=True)[1][:min(k, int((flat == 0).sum()))]
+                flat[idx] = 1
+        return mask
+    lib = native.load()
+    lib.nidt_mask_select_scratch_bytes.restype = C.c_int
+    lib.nidt_mask_select_k.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_void_p, C.c_void_p]
+    lib.nidt_mask_select_k.restype = C.c_int
+    scratch = _get_scratch("mask_select", mask.device, lib.nidt_mask_select_scratch_bytes())
+    v = values.contiguous().float()
+    native.check(lib.nidt_mask_select_k(native.ptr(v), native.ptr(mask), mask.numel(), k, 0 if mode == "fire" else 1, native.ptr(scratch),
+                                        native.stream_ptr(mask.device)), "nidt_mask_select_k")
+    native.count_launches(1)
+    return mask

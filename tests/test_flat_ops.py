@@ -187,3 +187,46 @@ def test_batch_stager_delivers_the_stored_volumes_with_lookahead():
     assert torch.equal(got, torch.as_tensor(want).cpu())
     assert torch.allclose(torch.cat([y for _, y in seen]).cpu(), torch.as_tensor(labels).float().cpu())
     assert [x.shape[0] for x, _ in seen] == [4, 4, 2, 4, 4, 4, 2]
+
+
+def test_mask_select_k_cpu_semantics():
+    torch.manual_seed(0)
+    w = torch.randn(1000)
+    m = (torch.rand(1000) > 0.4).float()
+    n_act = int(m.sum())
+    m2 = ops.mask_select_k(w, m.clone(), 37, "fire")
+    assert int(m2.sum()) == n_act - 37
+    removed = (m == 1) & (m2 == 0)
+    assert w.abs()[removed].max() <= w.abs()[(m2 == 1)].min()
+    g = torch.randn(1000)
+    m3 = ops.mask_select_k(g, m2.clone(), 37, "regrow")
+    assert int(m3.sum()) == n_act
+    grown = (m2 == 0) & (m3 == 1)
+    assert g.abs()[grown].min() >= g.abs()[(m3 == 0)].max()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,k", [(1000, 37), (1_769_472, 300_000), (257, 256), (4096, 0), (50_000, 49_999)])
+def test_mask_select_k_matches_sort_reference(n, k):
+    """Radix-select prune / regrow against the sort-based restatement (no ties: identical masks; with ties: identical counts)."""
+    g = torch.Generator().manual_seed(n)
+    w = torch.randn(n, generator=g)
+    m = (torch.rand(n, generator=g) > 0.4).float()
+    k_f = min(k, int(m.sum()))
+    ref = ops.mask_select_k(w, m.clone(), k_f, "fire")
+    got = ops.mask_select_k(w.cuda(), m.clone().cuda(), k_f, "fire")
+    assert torch.equal(got.cpu(), ref)
+    k_r = min(k, int((ref == 0).sum()))
+    gr = torch.randn(n, generator=g)
+    ref2 = ops.mask_select_k(gr, ref.clone(), k_r, "regrow")
+    got2 = ops.mask_select_k(gr.cuda(), got.clone(), k_r, "regrow")
+    assert torch.equal(got2.cpu(), ref2)
+    # heavy ties: quantised values; index-ordered tie-breaking = stable sort
+    wq = torch.round(w * 2) / 2
+    ref3 = ops.mask_select_k(wq, m.clone(), k_f, "fire")
+    got3 = ops.mask_select_k(wq.cuda(), m.clone().cuda(), k_f, "fire")
+    assert int(got3.sum()) == int(ref3.sum()) == int(m.sum()) - k_f
+    assert torch.equal(got3.cpu(), ref3)
+    # k larger than the number of candidates: every candidate changes
+    got4 = ops.mask_select_k(w.cuda(), m.clone().cuda(), n, "fire")
+    assert int(got4.sum()) == 0
