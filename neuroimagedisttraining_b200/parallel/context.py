@@ -58,6 +58,30 @@ class DistContext:
         return self.owner(client_idx) == self.rank
 
 
+def bind_to_gpu_numa(dev: torch.device) -> Optional[int]:
+    """Restrict this process to the CPUs NVML reports as local to ``dev`` (its NUMA node), so that the pinned host buffers
+    allocated afterwards -- the volume cache every batch is copied from -- sit next to the GPU's PCIe root: with 8 ranks
+    pulling ~50 GB/s each, remote-socket memory halves the host->device rate.  Returns the number of CPUs kept, or None when
+    nothing was changed (no NVML, affinity not supported, ``NIDT_NO_NUMA_BIND=1``)."""
+    if os.environ.get("NIDT_NO_NUMA_BIND", "0") == "1" or not hasattr(os, "sched_setaffinity"):
+        return None
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        uuid = str(torch.cuda.get_device_properties(dev).uuid)
+        h = pynvml.nvmlDeviceGetHandleByUUID(uuid if uuid.startswith("GPU-") else "GPU-" + uuid)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        local = {i for i in range(ncpu) if (int(words[i // 64]) >> (i % 64)) & 1}
+        keep = os.sched_getaffinity(0) & local
+        if not keep or keep == os.sched_getaffinity(0):
+            return None
+        os.sched_setaffinity(0, keep)
+        return len(keep)
+    except Exception:
+        return None
+
+
 def init_distributed(device: Optional[str] = None, backend: Optional[str] = None) -> DistContext:
     """Read RANK/LOCAL_RANK/WORLD_SIZE/MASTER_* (torchrun) and join the process group."""
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -67,6 +91,8 @@ def init_distributed(device: Optional[str] = None, backend: Optional[str] = None
     dev = torch.device(f"cuda:{local_rank}") if use_cuda else torch.device("cpu")
     if use_cuda:
         torch.cuda.set_device(dev)
+        if world > 1:
+            bind_to_gpu_numa(dev)
     if world == 1:
         return DistContext(0, 1, local_rank, dev, None)
     backend = backend or ("nccl" if use_cuda else "gloo")
