@@ -61,6 +61,8 @@ def _declare(lib) -> None:
     lib.nidt_conv_in_s2d_wgrad.restype = i32
     lib.nidt_conv3d_wgrad_scratch_floats.argtypes = [i32, i32, i32, i32]
     lib.nidt_conv3d_wgrad_scratch_floats.restype = i64
+    lib.nidt_pack_conv_weights_multi.argtypes = [i32, vp, vp, vp, vp, vp, vp, vp]
+    lib.nidt_pack_conv_weights_multi.restype = i32
     lib.nidt_plan_pack_weights.argtypes = [vp, vp, vp]
     lib.nidt_plan_pack_weights.restype = i32
     lib.nidt_plan_train_step.argtypes = [vp, vp, vp, i32, vp, vp, vp, vp, i64, f32, f32, f32, f32, i32, u64, i32, vp, vp]

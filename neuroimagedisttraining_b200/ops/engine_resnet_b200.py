@@ -15,6 +15,7 @@ Reference model: ``ResNet_l3(BasicBlock, [2,2,2])``, fedml_api/model/cv/salient_
 """
 from __future__ import annotations
 
+import ctypes as C
 from typing import List, Optional
 
 import torch
@@ -200,10 +201,19 @@ class ResNet3DEngine:
 
     # ------------------------------------------------------------------------------ pieces
     def _pack_weights(self) -> None:
+        """fp32 master weights -> bf16 GEMM operands for every tcgen05 conv, eight layers per launch."""
         lib, st = self.lib, self._stream()
-        for c in self.convs[1:]:
-            self._chk(lib.nidt_pack_conv_weights(self._p(self.slab, c.conv + ".weight"), c.cout, c.cin, c.k ** 3, c.wf.data_ptr(),
-                                                 c.wd.data_ptr(), st), "pack_conv_weights")
+        convs = self.convs[1:]
+        for g0 in range(0, len(convs), 8):
+            grp = convs[g0:g0 + 8]
+            n = len(grp)
+            w = (C.c_void_p * n)(*[self._p(self.slab, c.conv + ".weight") for c in grp])
+            wf = (C.c_void_p * n)(*[c.wf.data_ptr() for c in grp])
+            wd = (C.c_void_p * n)(*[c.wd.data_ptr() for c in grp])
+            co = (C.c_int * n)(*[c.cout for c in grp])
+            ci = (C.c_int * n)(*[c.cin for c in grp])
+            tp = (C.c_int * n)(*[c.k ** 3 for c in grp])
+            self._chk(lib.nidt_pack_conv_weights_multi(n, w, co, ci, tp, wf, wd, st), "pack_conv_weights")
         self._packed_dirty = False
 
     def _conv_bn(self, c: _Conv, x: torch.Tensor, B: int, train: bool) -> None:
