@@ -199,6 +199,10 @@ int nidt_plan_pack_weights(const nidt_plan_t* plan, const float* slab, void* str
 int nidt_plan_train_step(const nidt_plan_t* plan, const void* x_u8, const float* y, int batch, float* slab, float* grad, float* mom,
                          const float* mask, int64_t n_params, float lr, float momentum, float wd, float clip_norm, int first_step,
                          uint64_t seed, int do_update, int* launches, void* stream);
+/* struct layout probes for bindings: sizeof, and offsetof for a few fields (see executor.cu for the field numbers) */
+int nidt_plan_sizeof(void);
+int nidt_block_sizeof(void);
+int nidt_plan_offsetof(int field);
 /* eval-mode forward + eval head (counters may be null: logits only) */
 int nidt_plan_eval(const nidt_plan_t* plan, const void* x_u8, const float* y, int batch, const float* slab, double* counters,
                    int double_sigmoid, int* launches, void* stream);

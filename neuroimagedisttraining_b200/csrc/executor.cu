@@ -7,6 +7,7 @@
 #include <mutex>
 #include <map>
 #include <tuple>
+#include <cstddef>
 
 namespace {
 
@@ -193,4 +194,25 @@ NIDT_API int nidt_plan_eval(const nidt_plan_t* plan, const void* x_u8, const flo
     NIDT_TRY(head(c, y, slab, nullptr, false, counters, double_sigmoid, 0));
     if (launches != nullptr) *launches = c.launches;
     return 0;
+}
+
+// layout probes for foreign-language bindings (tests compare them with the ctypes mirror in ops/engine_b200.py)
+NIDT_API int nidt_plan_sizeof() { return (int)sizeof(nidt_plan_t); }
+NIDT_API int nidt_block_sizeof() { return (int)sizeof(nidt_block_t); }
+NIDT_API int nidt_plan_offsetof(int field) {
+    switch (field) {
+        case 0: return (int)offsetof(nidt_plan_t, blocks);
+        case 1: return (int)offsetof(nidt_plan_t, off_fc1_w);
+        case 2: return (int)offsetof(nidt_plan_t, head_s);
+        case 3: return (int)offsetof(nidt_plan_t, p_drop);
+        case 4: return (int)offsetof(nidt_plan_t, loss_acc);
+        case 5: return (int)offsetof(nidt_plan_t, norm_scratch);
+        case 10: return (int)offsetof(nidt_block_t, off_w);
+        case 11: return (int)offsetof(nidt_block_t, y);
+        case 12: return (int)offsetof(nidt_block_t, wf);
+        case 13: return (int)offsetof(nidt_block_t, stats_tiles);
+        case 14: return (int)offsetof(nidt_block_t, box);
+        case 15: return (int)offsetof(nidt_block_t, dbox);
+        default: return -1;
+    }
 }

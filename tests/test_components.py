@@ -127,3 +127,20 @@ def test_preprocessing_pipeline(tmp_path):
     P.save_npz(store, str(tmp_path / "abcd.npz"))
     back = P.load_npz(str(tmp_path / "abcd.npz"))
     assert torch.equal(back.volumes, store.volumes) and list(back.labels) == list(store.labels)
+
+
+def test_executor_plan_ctypes_mirror_matches_the_c_structs():
+    """The ctypes mirror of nidt_plan_t / nidt_block_t (ops/engine_b200.py) must have the C layout (the library loads without a GPU)."""
+    import ctypes as C
+    from neuroimagedisttraining_b200.ops import native
+    from neuroimagedisttraining_b200.ops.engine_b200 import _BlockC, _PlanC
+    lib = native.load()
+    for fn in (lib.nidt_plan_sizeof, lib.nidt_block_sizeof, lib.nidt_plan_offsetof):
+        fn.restype = C.c_int
+    lib.nidt_plan_offsetof.argtypes = [C.c_int]
+    assert C.sizeof(_PlanC) == lib.nidt_plan_sizeof()
+    assert C.sizeof(_BlockC) == lib.nidt_block_sizeof()
+    for field, attr in ((0, _PlanC.blocks), (1, _PlanC.off_fc1_w), (2, _PlanC.head_s), (3, _PlanC.p_drop), (4, _PlanC.loss_acc),
+                        (5, _PlanC.norm_scratch), (10, _BlockC.off_w), (11, _BlockC.y), (12, _BlockC.wf), (13, _BlockC.stats_tiles),
+                        (14, _BlockC.box), (15, _BlockC.dbox)):
+        assert attr.offset == lib.nidt_plan_offsetof(field), field
