@@ -203,6 +203,8 @@ int nidt_plan_train_step(const nidt_plan_t* plan, const void* x_u8, const float*
 int nidt_plan_sizeof(void);
 int nidt_block_sizeof(void);
 int nidt_plan_offsetof(int field);
+/* the box of output positions (bw,bh,bd,bn; product <= 128) the executor uses for a conv output of extent WxHxD at batch N */
+int nidt_choose_box(int W, int H, int D, int N, int* out);
 /* eval-mode forward + eval head (counters may be null: logits only) */
 int nidt_plan_eval(const nidt_plan_t* plan, const void* x_u8, const float* y, int batch, const float* slab, double* counters,
                    int double_sigmoid, int* launches, void* stream);

@@ -216,3 +216,11 @@ NIDT_API int nidt_plan_offsetof(int field) {
         default: return -1;
     }
 }
+
+// the M-tile box the executor picks for a partial batch (same search as ops/engine_b200.py::choose_box); out = {bw, bh, bd, bn}
+NIDT_API int nidt_choose_box(int W, int H, int D, int N, int* out) {
+    NIDT_REQUIRE(W >= 1 && H >= 1 && D >= 1 && N >= 1 && out != nullptr, "nidt_choose_box: bad arguments");
+    const Box b = choose_box(W, H, D, N);
+    out[0] = b.bw; out[1] = b.bh; out[2] = b.bd; out[3] = b.bn;
+    return 0;
+}

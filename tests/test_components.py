@@ -144,3 +144,23 @@ def test_executor_plan_ctypes_mirror_matches_the_c_structs():
                         (5, _PlanC.norm_scratch), (10, _BlockC.off_w), (11, _BlockC.y), (12, _BlockC.wf), (13, _BlockC.stats_tiles),
                         (14, _BlockC.box), (15, _BlockC.dbox)):
         assert attr.offset == lib.nidt_plan_offsetof(field), field
+
+
+def test_native_choose_box_matches_python_and_partial_batches_fit_the_buffers():
+    """The executor picks M-tile boxes for ragged last batches itself: same choice as the Python search, and never more
+    tiles than the full batch (the BN-statistics buffers are sized for the full batch)."""
+    import ctypes as C
+    from neuroimagedisttraining_b200.ops import native
+    from neuroimagedisttraining_b200.ops.engine_b200 import choose_box
+    lib = native.load()
+    lib.nidt_choose_box.argtypes = [C.c_int] * 4 + [C.POINTER(C.c_int)]
+    lib.nidt_choose_box.restype = C.c_int
+    out = (C.c_int * 4)()
+    tiles = lambda W, H, D, N, b: -(-W // b[0]) * -(-H // b[1]) * -(-D // b[2]) * -(-N // b[3])
+    for (W, H, D) in ((17, 21, 17), (19, 23, 19), (5, 7, 5), (32, 38, 32), (16, 19, 16), (8, 10, 8), (3, 4, 3), (1, 2, 1)):
+        for full in (16, 8, 4):
+            t_full = tiles(W, H, D, full, choose_box(W, H, D, full))
+            for n in range(1, full + 1):
+                assert lib.nidt_choose_box(W, H, D, n, out) == 0
+                assert tuple(out) == choose_box(W, H, D, n), (W, H, D, n)
+                assert tiles(W, H, D, n, tuple(out)) <= t_full, (W, H, D, n, full)
