@@ -164,3 +164,13 @@ def test_native_choose_box_matches_python_and_partial_batches_fit_the_buffers():
                 assert lib.nidt_choose_box(W, H, D, n, out) == 0
                 assert tuple(out) == choose_box(W, H, D, n), (W, H, D, n)
                 assert tiles(W, H, D, n, tuple(out)) <= t_full, (W, H, D, n, full)
+
+
+def test_halo_kernel_shape_support_query_runs_without_a_gpu():
+    from neuroimagedisttraining_b200.ops import volumetric as V
+    lib = V._lib()
+    assert lib.nidt_conv3d_halo_supported(8, 32, 38, 32, 64, 64, 1, 64) == 1       # ResNet layer1
+    assert lib.nidt_conv3d_halo_supported(16, 17, 21, 17, 64, 128, 0, 128) == 1    # AlexNet conv2
+    assert lib.nidt_conv3d_halo_supported(3, 4, 5, 4, 256, 256, 1, 128) == 0       # four Cin blocks of planes exceed shared memory
+    assert lib.nidt_conv3d_halo_supported(2, 8, 8, 200, 64, 64, 1, 64) == 0        # row pitch above 128
+    assert lib.nidt_conv3d_halo_supported(2, 8, 8, 8, 32, 64, 1, 64) == 0          # Cin not a multiple of 64
