@@ -328,11 +328,22 @@ class SlabTrainer(ModelTrainer):
     # --------------------------------------------------------------- gradient screening
     def screen_gradients(self, train_data, device=None) -> ParamSlab:
         """Dense gradient of one batch in eval mode (``DisPFL/my_model_trainer.py:166-189``)."""
+        src = self.engine
         for x, y in self._batches(train_data):
-            self.engine.compute_grads(x, y, train_mode=False)
+            try:
+                self.engine.compute_grads(x, y, train_mode=False)
+            except NotImplementedError:
+                # the sm_100a engines implement batch-statistics BatchNorm backward only; this once-per-round eval-mode
+                # gradient goes through the PyTorch engine on the same slab
+                if getattr(self, "_screen_engine", None) is None:
+                    self._screen_engine = TorchEngine(self.model, self.device, loss_kind=getattr(self.engine, "loss_kind", "bce"),
+                                                      volumetric=self.store is not None, input_scale=getattr(self.store, "scale", 1.0))
+                src = self._screen_engine
+                src.attach(self.slab)
+                src.compute_grads(x, y, train_mode=False)
             break
         g = ParamSlab(self.layout, device=self.device, params_only=True)
-        g.flat.copy_(self.engine.grad.flat)
+        g.flat.copy_(src.grad.flat)
         return g
 
     def saliency_batch(self, x, y, scores: ParamSlab, scale: float = 1.0) -> None:
