@@ -112,7 +112,9 @@ def build_identity(args, prefix: str, extra: Optional[list] = None) -> str:
 
 def setup(args, prefix: str, extra_identity: Optional[list] = None, loss_kind: Optional[str] = None, val_split: float = 0.0):
     """-> (ctx, device, logger, dataset 8-tuple, trainer).  Everything an entry point needs before building its API."""
-    args.client_num_per_round = int(args.client_num_in_total * args.frac)
+    # the reference computes int(total * frac) (main_sailentgrads.py:234), which is 0 for e.g. 4 clients at frac 0.1 and then
+    # fails in the first aggregation; at least one client is sampled here
+    args.client_num_per_round = max(1, int(args.client_num_in_total * args.frac))
     args.identity = build_identity(args, prefix, extra_identity)
     ctx = init_distributed(device=args.device)
     device = ctx.device
