@@ -101,3 +101,39 @@ def test_fedavg_matches_reference_cpu():
     sd = ours.w_global.state_dict(cast_int=False)
     for k, v in captured["w"].items():
         torch.testing.assert_close(sd[k].float(), v.float(), rtol=2e-4, atol=2e-5, msg=lambda m: f"{k}: {m}")
+
+
+def test_dispfl_prune_regrow_match_reference_client_methods():
+    """DisPFL mask evolution: the reference's ``Client.fire_mask`` / ``regrow_mask`` (DisPFL/client.py:71-99, full sorts) against
+    the select-k op the GPU kernel restates (``ops.mask_select_k``) and the per-tensor helpers, on tie-free random tensors."""
+    import logging
+    import math
+    import types
+    from neuroimagedisttraining_b200 import ops
+    from neuroimagedisttraining_b200.utils.slim import cosine_annealing
+    ref_harness.import_reference()
+    from fedml_api.standalone.DisPFL.client import Client as RefClient
+
+    args = types.SimpleNamespace(anneal_factor=0.5, comm_round=10, dis_gradient_check=False, static=False)
+    log = logging.getLogger("ref-dispfl"); log.setLevel(logging.ERROR)
+    rc = RefClient(0, None, None, 5, args, "cpu", None, log)
+    g = torch.Generator().manual_seed(7)
+    shapes = {"features.0.weight": (8, 1, 3, 3, 3), "features.4.weight": (16, 8, 3, 3, 3), "classifier.1.weight": (16, 32)}
+    w = {n: torch.randn(*s, generator=g) for n, s in shapes.items()}
+    grad = {n: torch.randn(*s, generator=g) for n, s in shapes.items()}
+    masks = {n: (torch.rand(*s, generator=g) > 0.5).float() for n, s in shapes.items()}
+    for rnd in (0, 3, 9):
+        ref_fired, ref_removed = rc.fire_mask(masks, w, rnd)
+        ref_grown = rc.regrow_mask(ref_fired, ref_removed, grad)
+        drop = cosine_annealing(args, rnd)
+        for n in shapes:
+            k = math.ceil(drop * int(masks[n].sum()))
+            assert k == ref_removed[n]
+            fired = ops.mask_select_k(w[n], masks[n].clone(), k, "fire")
+            assert torch.equal(fired, ref_fired[n]), (n, rnd)
+            fired2, k2 = ops.reference.fire_mask(w[n], masks[n], drop)
+            assert k2 == k and torch.equal(fired2, ref_fired[n])
+            grown = ops.mask_select_k(grad[n], fired.clone(), k, "regrow")
+            assert torch.equal(grown, ref_grown[n]), (n, rnd)
+            assert torch.equal(ops.reference.regrow_mask(fired, k, grad[n]), ref_grown[n])
+            assert int(grown.sum()) == int(masks[n].sum())          # density preserved
