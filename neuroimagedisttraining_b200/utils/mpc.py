@@ -88,9 +88,12 @@ def BGW_decoding(f_eval: np.ndarray, worker_idx: Sequence[int], p: int) -> np.nd
 
 
 def _lcc_points(N: int, K: int, T: int, p: int) -> Tuple[List[int], List[int]]:
-    # interpolation points beta (K data + T random blocks) and evaluation points alpha (N workers), all distinct
-    beta = list(range(1, K + T + 1))
-    alpha = list(range(K + T + 1, K + T + 1 + N))
+    """Interpolation points beta (K data + T random blocks) and evaluation points alpha (N workers): the reference's centred
+    ranges reduced mod p (``mpc_function.py:121-125``), so shares are interchangeable with its encoder / decoder."""
+    n_beta = K + T
+    stt_b, stt_a = -(n_beta // 2), -(N // 2)
+    beta = [int(v % p) for v in range(stt_b, stt_b + n_beta)]
+    alpha = [int(v % p) for v in range(stt_a, stt_a + N)]
     return alpha, beta
 
 
