@@ -119,3 +119,68 @@ def test_mpc_primitives_match_reference():
     np.testing.assert_array_equal(np.asarray(dec_o).astype(np.int64).reshape(X.shape) % p, X % p)
     # (small keys: the reference raises to the power BEFORE reducing, which overflows for realistic ones; ours uses modular pow)
     assert int(M.my_key_agreement(2, M.my_pk_gen(3, p, 3), p, 3)) == int(R.my_key_agreement(2, int(R.my_pk_gen(3, p, 3)), p, 3)) == 729
+
+
+def test_erk_sparsities_and_random_masks_match_reference_trainer():
+    """``calculate_sparsities`` (ERK with the densify-and-retry loop) and the nnz of ``init_masks`` against the reference's
+    SalientGrads trainer (``my_model_trainer.py:32-130``) on the 3-D AlexNet parameter shapes."""
+    import logging
+    ref = ref_harness.import_reference()
+    from neuroimagedisttraining_b200.fl import SlabTrainer
+    from neuroimagedisttraining_b200.models import AlexNet3D_Dropout
+    log = logging.getLogger("erk"); log.setLevel(logging.ERROR)
+    for dense_ratio, power in ((0.5, 1.0), (0.2, 1.0), (0.1, 0.5), (0.8, 1.0)):
+        args = types.SimpleNamespace(dense_ratio=dense_ratio, erk_power_scale=power, lr=0.01, wd=0.0, client_optimizer="sgd", batch_size=2)
+        model = AlexNet3D_Dropout(num_classes=1)
+        rt = ref.sg_trainer.MyModelTrainer(model, args, log)
+        params = rt.get_trainable_params()
+        ref_sp = rt.calculate_sparsities(params, sparse=dense_ratio)
+        tr = SlabTrainer(AlexNet3D_Dropout(num_classes=1), args, log, device="cpu")
+        ours_sp = tr.calculate_sparsities(sparse=dense_ratio)
+        assert set(ours_sp) == set(ref_sp)
+        for n in ref_sp:
+            assert ours_sp[n] == pytest.approx(float(ref_sp[n]), rel=1e-9, abs=1e-12), (n, dense_ratio)
+        ref_masks = rt.init_masks(params, ref_sp)
+        ours_masks = tr.init_masks(None, ours_sp)
+        for n in ref_sp:
+            m = ours_masks.view(n) if hasattr(ours_masks, "view") else ours_masks[n]
+            assert int(m.sum()) == int(ref_masks[n].sum()), n          # same density per tensor (positions are random)
+
+
+def test_lda_partition_matches_reference_stream():
+    """Same seed -> the same per-client index lists as FedML's LDA partitioner (fedml_core/non_iid_partition/noniid_partition.py:6-91)."""
+    ref_harness.import_reference()
+    from fedml_core.non_iid_partition.noniid_partition import non_iid_partition_with_dirichlet_distribution as ref_lda
+    from neuroimagedisttraining_b200.data.partition import hetero_dirichlet_partition
+    y = np.random.RandomState(1).randint(0, 10, size=3000)
+    for seed, alpha, n_clients in ((5, 0.5, 8), (9, 0.1, 5)):
+        np.random.seed(seed)
+        ref = ref_lda(y, n_clients, 10, alpha)
+        ours = hetero_dirichlet_partition(y, n_clients, alpha, np.random.RandomState(seed))
+        assert set(ref) == set(ours)
+        for c in ref:
+            np.testing.assert_array_equal(np.asarray(ref[c]), ours[c])
+
+
+def test_flop_counter_matches_reference_on_2d_models():
+    """Sparse FLOP counts (non-zero weights only) of the reference's counter (fedml_api/utils/main_flops_counter.py:38-163, Conv2d /
+    Linear hooks) on a CIFAR model, dense and with half of the weights zeroed."""
+    ref_harness.import_reference()
+    try:
+        from fedml_api.utils import main_flops_counter as R
+    except Exception as e:
+        pytest.skip(f"reference FLOP counter not importable: {e}")
+    from neuroimagedisttraining_b200.models import create_model
+    from neuroimagedisttraining_b200.utils import flops as Fl
+    torch.manual_seed(0)
+    model = create_model("cnn_cifar10", 10)
+    for sparsify in (False, True):
+        if sparsify:
+            with torch.no_grad():
+                for p in model.parameters():
+                    if p.dim() in (2, 4):
+                        p.mul_((torch.rand_like(p) > 0.5).float())
+        ours = float(Fl.count_model_param_flops(model, "cifar10"))
+        ref = float(R.count_model_param_flops(model, "cifar10"))
+        assert ours == pytest.approx(ref, rel=1e-6), (sparsify, ours, ref)      # the reference sums in float32
+        assert float(Fl.count_training_flops(model, "cifar10")) == pytest.approx(float(R.count_training_flops(model, "cifar10")), rel=1e-6)
