@@ -45,6 +45,8 @@ class LocalAPI(FedAPIBase):
         stats = {'person_test_acc': acc.sum() / len(ids), 'person_test_loss': loss.sum() / len(ids)}
         self.stat_info["person_test_acc"].append(stats["person_test_acc"])
         self.stat_info["person_test_loss"].append(stats["person_test_loss"])
+        # the key the reference's Local / Ditto / D-PSGD / FedFomo / Sub-FedAvg APIs record (e.g. ditto_api.py:149-150)
+        self.stat_info.setdefault("test_acc", []).append(stats["person_test_acc"])
         self.logger.info(stats)
         return stats
 

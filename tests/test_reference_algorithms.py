@@ -1,0 +1,83 @@
+"""End-to-end parity of further algorithms against the UNMODIFIED reference APIs on CPU: same initial weights, same tensors,
+unshuffled loaders, a dropout-free CIFAR-shape CNN.  (SalientGrads / FedAvg on the 3-D model: tests/test_reference_parity.py.)"""
+import copy
+import logging
+import types
+
+import numpy as np
+import pytest
+import torch
+from torch.utils.data import DataLoader, TensorDataset
+
+from baseline import ref_harness
+
+pytestmark = pytest.mark.skipif(ref_harness.reference_available() is not None, reason="reference not installed")
+
+
+def _log():
+    log = logging.getLogger("ref-algo")
+    log.setLevel(logging.ERROR)
+    return log
+
+
+def _image_dataset(n_clients=3, n_train=16, n_test=8, batch=8, seed=0):
+    """The FedML 8-tuple over fixed random CIFAR-shape tensors; identical loaders are handed to both implementations."""
+    g = torch.Generator().manual_seed(seed)
+    trl, tel, num = {}, {}, {}
+    for c in range(n_clients):
+        x, y = torch.randn(n_train, 3, 32, 32, generator=g), torch.randint(0, 10, (n_train,), generator=g)
+        xt, yt = torch.randn(n_test, 3, 32, 32, generator=g), torch.randint(0, 10, (n_test,), generator=g)
+        trl[c] = DataLoader(TensorDataset(x, y), batch_size=batch, shuffle=False)
+        tel[c] = DataLoader(TensorDataset(xt, yt), batch_size=batch, shuffle=False)
+        num[c] = n_train
+    return [n_clients * n_train, n_clients * n_test, None, None, num, trl, tel, 10]
+
+
+def _args(**kw):
+    d = dict(model="cnn_cifar10", dataset="cifar10", batch_size=8, client_optimizer="sgd", lr=0.05, lr_decay=0.998, wd=5e-4, momentum=0.0,
+             epochs=1, local_epochs=2, lamda=0.5, client_num_in_total=3, client_num_per_round=3, frac=1.0, comm_round=2,
+             frequency_of_the_test=1, ci=0, seed=0, gpu=0)
+    d.update(kw)
+    return types.SimpleNamespace(**d)
+
+
+def _model(seed=4):
+    from neuroimagedisttraining_b200.models import create_model
+    torch.manual_seed(seed)
+    return create_model("cnn_cifar10", 10)
+
+
+def _assert_state_close(slab, state, rtol=2e-4, atol=2e-5, what=""):
+    sd = slab.state_dict(cast_int=False)
+    for k, v in state.items():
+        torch.testing.assert_close(sd[k].float(), v.float().cpu(), rtol=rtol, atol=atol, msg=lambda m: f"{what} {k}: {m}")
+
+
+def test_ditto_matches_reference_cpu():
+    ref_harness.import_reference()
+    from fedml_api.standalone.ditto.ditto_api import DittoAPI as RefAPI
+    from fedml_api.standalone.ditto.my_model_trainer import MyModelTrainer as RefTrainer
+    from neuroimagedisttraining_b200.fl import DittoAPI, SlabTrainer
+    args, ds = _args(), _image_dataset()
+    init = copy.deepcopy(_model().state_dict())
+
+    rmodel = _model()
+    rmodel.load_state_dict(init)
+    rapi = RefAPI(ds, torch.device("cpu"), args, RefTrainer(rmodel, args, _log()), _log())
+    cap = {}
+    orig_agg, orig_test = rapi._aggregate, rapi._local_test_on_all_clients
+    rapi._aggregate = lambda w: cap.__setitem__("g", orig_agg(w)) or cap["g"]
+    rapi._local_test_on_all_clients = lambda w_pers, r: (cap.__setitem__("p", copy.deepcopy(w_pers)), orig_test(w_pers, r))[1]
+    rapi.train()
+
+    model = _model()
+    model.load_state_dict(init)
+    tr = SlabTrainer(model, args, _log(), device="cpu", loss_kind="ce")
+    api = DittoAPI(ds, "cpu", args, tr, _log())
+    api.train()
+    _assert_state_close(api.w_global, cap["g"], what="global")
+    for c in range(args.client_num_in_total):
+        _assert_state_close(api.client_list[c].slab, cap["p"][c], what=f"personal[{c}]")
+    assert len(api.stat_info["test_acc"]) == len(rapi.stat_info["test_acc"]) == 2
+    for a, b in zip(api.stat_info["test_acc"], rapi.stat_info["test_acc"]):
+        assert abs(float(a) - float(b)) < 1e-6
