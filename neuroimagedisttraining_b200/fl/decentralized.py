@@ -26,13 +26,17 @@ from ..utils.slim import cosine_annealing
 from .local import LocalAPI
 
 
-def choose_neighbors(cs: str, cur: int, total: int, per_round: int, active: Optional[np.ndarray] = None) -> np.ndarray:
+def choose_neighbors(cs: str, cur: int, total: int, per_round: int, active: Optional[np.ndarray] = None,
+                     seed: Optional[int] = None) -> np.ndarray:
     """``_benefit_choose`` (``dpsgd_api.py:116-139``): everyone when ``per_round == total``; else random peers
-    (never ``cur``), the two ring neighbours, or all active clients."""
+    (never ``cur``), the two ring neighbours, or all active clients.  ``seed``: D-PSGD re-seeds numpy with
+    ``round + client`` before drawing (``dpsgd_api.py:122-123``); DisPFL draws from the running stream (``dispfl_api.py:203-208``)."""
     if total == per_round:
         return np.arange(total)
     if cs == "random":
         k = min(per_round, total)
+        if seed is not None:
+            np.random.seed(seed)
         idx = np.random.choice(range(total), k, replace=False)
         while cur in idx:
             idx = np.random.choice(range(total), k, replace=False)
@@ -83,7 +87,7 @@ class DPSGDAPI(_PerClientModels):
             with self.timer.phase("train"):
                 for cid in range(n):
                     self.logger.info('@@@@@@@@@@@@@@@@ Training Client CM({}): {}'.format(round_idx, cid))
-                    nei = choose_neighbors(getattr(args, "cs", "ring"), cid, n, args.client_num_per_round)
+                    nei = choose_neighbors(getattr(args, "cs", "ring"), cid, n, args.client_num_per_round, seed=round_idx + cid)
                     if n != args.client_num_per_round:
                         nei = np.append(nei, cid)
                     nei = np.sort(nei)

@@ -36,7 +36,7 @@ def _image_dataset(n_clients=3, n_train=16, n_test=8, batch=8, seed=0):
 def _args(**kw):
     d = dict(model="cnn_cifar10", dataset="cifar10", batch_size=8, client_optimizer="sgd", lr=0.05, lr_decay=0.998, wd=5e-4, momentum=0.0,
              epochs=1, local_epochs=2, lamda=0.5, client_num_in_total=3, client_num_per_round=3, frac=1.0, comm_round=2,
-             frequency_of_the_test=1, ci=0, seed=0, gpu=0)
+             frequency_of_the_test=1, ci=0, seed=0, gpu=0, type="epoch")
     d.update(kw)
     return types.SimpleNamespace(**d)
 
@@ -81,3 +81,35 @@ def test_ditto_matches_reference_cpu():
     assert len(api.stat_info["test_acc"]) == len(rapi.stat_info["test_acc"]) == 2
     for a, b in zip(api.stat_info["test_acc"], rapi.stat_info["test_acc"]):
         assert abs(float(a) - float(b)) < 1e-6
+
+
+@pytest.mark.parametrize("cs,per_round", [("ring", 2), ("random", 2), ("full", 5)])
+def test_dpsgd_matches_reference_cpu(cs, per_round):
+    """Neighbour choice (ring / seeded random / everyone), neighbour averaging, local training and the plain-mean global model."""
+    ref_harness.import_reference()
+    from fedml_api.standalone.dpsgd.dpsgd_api import DPSGDAPI as RefAPI
+    from fedml_api.standalone.dpsgd.my_model_trainer import MyModelTrainer as RefTrainer
+    from neuroimagedisttraining_b200.fl import DPSGDAPI, SlabTrainer
+    n = 5
+    args, ds = _args(client_num_in_total=n, client_num_per_round=per_round, cs=cs, comm_round=2), _image_dataset(n_clients=n)
+    init = copy.deepcopy(_model().state_dict())
+
+    rmodel = _model()
+    rmodel.load_state_dict(init)
+    rapi = RefAPI(ds, torch.device("cpu"), args, RefTrainer(rmodel, args), _log())
+    cap = {}
+    orig = rapi._test_on_all_clients
+    rapi._test_on_all_clients = lambda wg, wp, r: (cap.update(g=copy.deepcopy(wg), p=copy.deepcopy(wp)), orig(wg, wp, r))[1]
+    rapi.train()
+
+    model = _model()
+    model.load_state_dict(init)
+    api = DPSGDAPI(ds, "cpu", args, SlabTrainer(model, args, _log(), device="cpu", loss_kind="ce"), _log())
+    api.train()
+    _assert_state_close(api.w_global, cap["g"], what="global")
+    for c in range(n):
+        _assert_state_close(api.client_list[c].slab, cap["p"][c], what=f"personal[{c}]")
+    for key in ("global_test_acc", "person_test_acc"):
+        assert len(api.stat_info[key]) == len(rapi.stat_info[key]) == 2
+        for a, b in zip(api.stat_info[key], rapi.stat_info[key]):
+            assert abs(float(a) - float(b)) < 1e-6, key
