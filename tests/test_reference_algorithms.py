@@ -113,3 +113,35 @@ def test_dpsgd_matches_reference_cpu(cs, per_round):
         assert len(api.stat_info[key]) == len(rapi.stat_info[key]) == 2
         for a, b in zip(api.stat_info[key], rapi.stat_info[key]):
             assert abs(float(a) - float(b)) < 1e-6, key
+
+
+def test_local_only_matches_reference_cpu():
+    """No communication: every client keeps training its own model (the reference's test bookkeeping only works when all clients
+    train every round, local_api.py:105-121, which is also what ours does)."""
+    ref_harness.import_reference()
+    from fedml_api.standalone.local.local_api import LocalAPI as RefAPI
+    from fedml_api.standalone.local.my_model_trainer import MyModelTrainer as RefTrainer
+    from neuroimagedisttraining_b200.fl import LocalAPI, SlabTrainer
+    args, ds = _args(comm_round=3), _image_dataset()
+    init = copy.deepcopy(_model().state_dict())
+    rmodel = _model()
+    rmodel.load_state_dict(init)
+    rtrainer = RefTrainer(rmodel, args, _log())
+    rapi = RefAPI(ds, torch.device("cpu"), args, rtrainer, _log())
+    rapi.record_information = lambda *a, **k: None          # the reference pickles into ../../results (crashes without the directory)
+    finals = {}
+    for c in rapi.client_list:
+        orig = c.train
+        c.train = (lambda o, cid: (lambda w, r: (lambda out: (finals.__setitem__(cid, copy.deepcopy(out[0])), out)[1])(o(w, r))))(orig, c.client_idx)
+    rapi.train()
+
+    model = _model()
+    model.load_state_dict(init)
+    api = LocalAPI(ds, "cpu", args, SlabTrainer(model, args, _log(), device="cpu", loss_kind="ce"), _log())
+    api.record_information = lambda *a, **k: None
+    api.train()
+    for c in range(args.client_num_in_total):
+        _assert_state_close(api.client_list[c].slab, finals[c], what=f"personal[{c}]")
+    assert len(api.stat_info["test_acc"]) == len(rapi.stat_info["test_acc"]) == 3
+    for a, b in zip(api.stat_info["test_acc"], rapi.stat_info["test_acc"]):
+        assert abs(float(a) - float(b)) < 1e-6
