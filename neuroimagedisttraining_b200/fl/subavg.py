@@ -150,5 +150,8 @@ class SubAvgAPI(LocalAPI):
                 losses.append(m["test_loss"] / max(m["test_total"], 1))
         stats = {'person_test_acc': float(np.mean(accs)), 'person_test_loss': float(np.mean(losses))}
         self.stat_info["person_test_acc"].append(stats["person_test_acc"])
+        self.stat_info.setdefault("person_test_loss", []).append(stats["person_test_loss"])
+        self.stat_info.setdefault("test_acc", []).append(stats["person_test_acc"])        # the reference's key (subavg_api.py)
+        self.eval_masks = [m.clone() for m in mask_pers]                                    # masks the evaluation used
         self.logger.info(stats)
         return stats

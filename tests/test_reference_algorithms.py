@@ -145,3 +145,43 @@ def test_local_only_matches_reference_cpu():
     assert len(api.stat_info["test_acc"]) == len(rapi.stat_info["test_acc"]) == 3
     for a, b in zip(api.stat_info["test_acc"], rapi.stat_info["test_acc"]):
         assert abs(float(a) - float(b)) < 1e-6
+
+
+def test_subavg_matches_reference_cpu():
+    """Sub-FedAvg: masked local training, percentile pruning after the first / last epoch, accept-if-accurate rule, mask-count-weighted
+    aggregation.  Thresholds are set so that clients really prune (dense > dense_ratio, acc > acc_thresh = 0)."""
+    ref_harness.import_reference()
+    from fedml_api.standalone.subavg.subavg_api import SubAvgAPI as RefAPI
+    from fedml_api.standalone.subavg.my_model_trainer import MyModelTrainer as RefTrainer
+    from neuroimagedisttraining_b200.fl import SlabTrainer, SubAvgAPI
+    args = _args(comm_round=3, epochs=2, each_prune_ratio=0.2, dense_ratio=0.3, dist_thresh=1e-4, acc_thresh=-1.0)
+    ds = _image_dataset()
+    init = copy.deepcopy(_model().state_dict())
+    rmodel = _model()
+    rmodel.load_state_dict(init)
+    rapi = RefAPI(ds, torch.device("cpu"), args, RefTrainer(rmodel, args, _log()), _log())
+    rapi.record_information = lambda *a, **k: None
+    rapi.record_avg_inference_flops = lambda *a, **k: None
+    cap = {}
+    orig_agg = rapi._aggregate
+    rapi._aggregate = lambda ws, wl: cap.__setitem__("g", copy.deepcopy(orig_agg(ws, wl))) or cap["g"]
+    orig_test = rapi._local_test_on_all_clients
+    rapi._local_test_on_all_clients = lambda wg, mp, r: (cap.__setitem__("masks", copy.deepcopy(mp)), orig_test(wg, mp, r))[1]
+    rapi.train()
+
+    model = _model()
+    model.load_state_dict(init)
+    api = SubAvgAPI(ds, "cpu", args, SlabTrainer(model, args, _log(), device="cpu", loss_kind="ce"), _log())
+    api.record_information = lambda *a, **k: None
+    api.train()
+    _assert_state_close(api.w_global, cap["g"], what="global")
+    pruned = 0
+    for c in range(args.client_num_in_total):          # masks as they were when the last evaluation ran
+        for name, m in cap["masks"][c].items():
+            ours = api.eval_masks[c].view(name) if hasattr(api, "eval_masks") else None
+            if ours is not None:
+                assert torch.equal(ours, m.float()), (c, name)
+            pruned += int((m == 0).sum())
+    assert pruned > 0, "the configuration must exercise pruning"
+    for a, b in zip(api.stat_info["test_acc"], rapi.stat_info["test_acc"]):
+        assert abs(float(a) - float(b)) < 1e-6
