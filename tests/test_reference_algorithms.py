@@ -185,3 +185,45 @@ def test_subavg_matches_reference_cpu():
     assert pruned > 0, "the configuration must exercise pruning"
     for a, b in zip(api.stat_info["test_acc"], rapi.stat_info["test_acc"]):
         assert abs(float(a) - float(b)) < 1e-6
+
+
+@pytest.mark.parametrize("per_round", [4, 2])
+def test_fedfomo_matches_reference_cpu(per_round):
+    """FedFomo: first-order weights (validation-loss gain / model distance), positive-part normalised neighbour mix, the benefit-driven
+    neighbour choice (python + numpy RNG streams, re-seeded identically for both runs) and both accuracy series."""
+    import random
+    ref_harness.import_reference()
+    from fedml_api.standalone.fedfomo.fedfomo_api import FEDFOMOAPI as RefAPI
+    from fedml_api.standalone.fedfomo.my_model_trainer import MyModelTrainer as RefTrainer
+    from neuroimagedisttraining_b200.fl import FedFomoAPI, SlabTrainer
+    n = 4
+    args = _args(client_num_in_total=n, client_num_per_round=per_round, comm_round=3)
+    ds = _image_dataset(n_clients=n)
+    g = torch.Generator().manual_seed(123)
+    val = {c: DataLoader(TensorDataset(torch.randn(8, 3, 32, 32, generator=g), torch.randint(0, 10, (8,), generator=g)), batch_size=8)
+           for c in range(n)}
+    init = copy.deepcopy(_model().state_dict())
+
+    rmodel = _model()
+    rmodel.load_state_dict(init)
+    rapi = RefAPI(ds[:6] + [val] + ds[6:], torch.device("cpu"), args, RefTrainer(rmodel, args, _log()), _log())
+    rapi.record_information = lambda *a, **k: None
+    finals = {}
+    for c in rapi.client_list:      # the last local_test of a client in a round sees its post-aggregation personal model
+        orig = c.local_test
+        c.local_test = (lambda o, cid: (lambda w, b=True: (finals.__setitem__(cid, copy.deepcopy(w)), o(w, b))[1]))(orig, c.client_idx)
+    random.seed(7); np.random.seed(7)
+    rapi.train()
+
+    model = _model()
+    model.load_state_dict(init)
+    api = FedFomoAPI(ds + [val], "cpu", args, SlabTrainer(model, args, _log(), device="cpu", loss_kind="ce"), _log())
+    api.record_information = lambda *a, **k: None
+    random.seed(7); np.random.seed(7)
+    api.train()
+    for c in range(n):
+        _assert_state_close(api.client_list[c].slab, finals[c], rtol=1e-3, atol=1e-4, what=f"personal[{c}]")
+    for key in ("old_mask_test_acc", "new_mask_test_acc"):
+        assert len(api.stat_info[key]) == len(rapi.stat_info[key]) == 3
+        for a, b in zip(api.stat_info[key], rapi.stat_info[key]):
+            assert abs(float(a) - float(b)) < 1e-6, key

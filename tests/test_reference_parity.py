@@ -137,3 +137,62 @@ def test_dispfl_prune_regrow_match_reference_client_methods():
             assert torch.equal(grown, ref_grown[n]), (n, rnd)
             assert torch.equal(ops.reference.regrow_mask(fired, k, grad[n]), ref_grown[n])
             assert int(grown.sum()) == int(masks[n].sum())          # density preserved
+
+
+@pytest.mark.parametrize("active,static", [(1.0, False), (0.7, False), (1.0, True)])
+def test_dispfl_matches_reference_cpu(active, static):
+    """DisPFL end to end through the reference's unmodified ``dispflAPI`` / ``Client`` / ``MyModelTrainer``: ERK random masks from the
+    same torch RNG stream, masked local SGD, eval-mode gradient screening, cosine-annealed prune / regrow, seeded client drop-out,
+    both accuracy series and the final mask Hamming matrix.  The model is the small 3-D CNN at 32^3 (the reference trainer takes any
+    module; its only ABCD-specific part is the HDF5 fetch, replaced by the synthetic source as in the other parity tests)."""
+    import copy
+    from neuroimagedisttraining_b200.fl import DisPFLAPI
+    from neuroimagedisttraining_b200.models import Tiny3DCNN
+    ref_harness.import_reference()
+    from fedml_api.standalone.DisPFL import my_model_trainer as dp_trainer
+    from fedml_api.standalone.DisPFL.dispfl_api import dispflAPI as RefAPI
+
+    n, per_site = 3, 10
+    store = SyntheticABCD(n * per_site, shape=(32, 32, 32), n_sites=n, seed=5, pool=3, site_sizes=[per_site] * n)
+    train, test, _ = site_partition(store.sites)
+    args = make_args(client_num_in_total=n, batch_size=4, epochs=1, comm_round=3, lr=0.02, dense_ratio=0.5, anneal_factor=0.3, cs="random",
+                     active=active, static=static, uniform=False, different_initial=True, diff_spa=False, dis_gradient_check=False,
+                     save_masks=True, record_mask_diff=False)
+    torch.manual_seed(11)
+    init = copy.deepcopy(Tiny3DCNN(1, in_shape=(32, 32, 32)).state_dict())
+
+    source = ref_harness.SyntheticSource(store, "cpu")
+    dp_trainer.MyModelTrainer.load_data_chunks_batch = lambda self, idx: source.batch(idx)
+    rmodel = Tiny3DCNN(1, in_shape=(32, 32, 32))
+    rmodel.load_state_dict(init)
+    ds = ref_harness.build_dataset(store, train, test, args.batch_size, shuffle=False)
+    rapi = RefAPI(ds, torch.device("cpu"), args, dp_trainer.MyModelTrainer(rmodel, args, quiet_logger()), quiet_logger())
+    finals = {}
+    for c in rapi.client_list:
+        orig = c.train
+        c.train = (lambda o, cid: (lambda w, m, r: (lambda out: (finals.__setitem__(cid, copy.deepcopy(out[1])), out)[1])(o(w, m, r))))(orig, c.client_idx)
+    torch.manual_seed(3); np.random.seed(3)
+    rapi.train()
+
+    model = Tiny3DCNN(1, in_shape=(32, 32, 32))
+    model.load_state_dict(init)
+    tr = SlabTrainer(model, args, quiet_logger(), device="cpu", store=store)
+    trl = {c: IndexLoader(t, store.labels[t], store.sites[t], args.batch_size, shuffle=False) for c, t in enumerate(train)}
+    tel = {c: IndexLoader(t, store.labels[t], store.sites[t], args.batch_size, shuffle=False) for c, t in enumerate(test)}
+    api = DisPFLAPI([None, None, None, None, {c: len(t) for c, t in enumerate(train)}, trl, tel, 2], "cpu", args, tr, quiet_logger())
+    torch.manual_seed(3); np.random.seed(3)
+    api.train()
+
+    for c in range(n):
+        sd = api.client_list[c].slab.state_dict(cast_int=False)
+        for k, v in finals[c].items():
+            torch.testing.assert_close(sd[k].float(), v.float(), rtol=2e-4, atol=2e-5, msg=lambda m: f"client {c} {k}: {m}")
+        for name, m in rapi.stat_info["final_masks"][c].items():
+            assert torch.equal(api.stat_info["final_masks"][c][name], m), (c, name)
+    assert api.stat_info["mask_dis_matrix"] == [[int(v) for v in row] for row in rapi.stat_info["mask_dis_matrix"]]
+    if not static:
+        assert any(v > 0 for row in api.stat_info["mask_dis_matrix"] for v in row), "masks must have evolved"
+    for key in ("old_mask_test_acc", "new_mask_test_acc"):
+        assert len(api.stat_info[key]) == len(rapi.stat_info[key]) == 3
+        for a, b in zip(api.stat_info[key], rapi.stat_info[key]):
+            assert abs(float(a) - float(b)) < 1e-6, key
