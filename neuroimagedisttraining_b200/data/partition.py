@@ -87,6 +87,9 @@ def non_iid_partition_with_dirichlet_distribution(label_list, client_num, classe
     return hetero_dirichlet_partition(np.asarray(label_list), client_num, alpha, np.random.RandomState(seed))
 
 
+_MAX_CLASS_REDRAWS = 10_000
+
+
 def _lognormal_sizes(n: int, n_clients: int, rng: np.random.RandomState, sigma: float = 0.0) -> np.ndarray:
     sizes = rng.lognormal(mean=np.log(n / n_clients), sigma=sigma, size=n_clients)
     return (sizes / sizes.sum() * n).astype(int)
@@ -108,12 +111,20 @@ def dir_partition(y: np.ndarray, n_clients: int, alpha: float, rng: np.random.Ra
         if sizes[j] <= 0:
             continue
         sizes[j] -= 1
+        redraws = 0
         while True:
             c = int(np.argmax(rng.uniform() <= cum[j]))
             if remaining[c] <= 0:
                 if remaining.sum() <= 0:
                     break
-                continue
+                redraws += 1
+                if redraws < _MAX_CLASS_REDRAWS:
+                    continue
+                # The reference redraws for ever here; when the client's prior has (next to) no mass on the classes that still
+                # have samples that never ends.  Same stream up to this point, then the prior restricted to what is left.
+                left = np.where(remaining > 0)[0]
+                pr = priors[j][left]
+                c = int(left[rng.choice(len(left), p=pr / pr.sum())]) if pr.sum() > 0 else int(left[rng.randint(len(left))])
             remaining[c] -= 1
             out[j].append(pools[c][remaining[c]])
             break
