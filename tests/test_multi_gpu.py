@@ -25,6 +25,15 @@ def test_salientgrads_two_ranks_cpu_matches_single_process():
     assert "RESULT ok=True" in r.stdout, r.stdout[-2000:]
 
 
+@pytest.mark.parametrize("world", [2, 3])
+def test_depth_slab_decomposition_matches_the_unsplit_module(world):
+    """One client's volumes split along depth over ranks (halo exchange per layer, BatchNorm statistics across ranks): outputs, all
+    gradients and running statistics equal the single-process module, also when the last layers leave some ranks without planes."""
+    r = _torchrun("dist_worker_spatial.py", world, {"CUDA_VISIBLE_DEVICES": ""}, timeout=300)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "RESULT ok=True" in r.stdout, r.stdout[-2000:]
+
+
 @pytest.mark.gpu
 def test_fused_symmetric_aggregation_matches_nccl():
     n = torch.cuda.device_count()
