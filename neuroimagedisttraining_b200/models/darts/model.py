@@ -67,3 +67,52 @@ class NetworkCIFAR(nn.Module):
                 aux = self.auxiliary_head(s1)
         out = self.classifier(self.global_pooling(s1).flatten(1))
         return (out, aux) if (self._auxiliary and self.training) else out
+
+
+def _aux_head(C, num_classes, pool_stride, first_pad_free=True):
+    """Auxiliary classifier at 2/3 depth: 8x8 inputs for CIFAR (pool stride 3), 14x14 for ImageNet (stride 2)."""
+    return nn.Sequential(nn.ReLU(inplace=True), nn.AvgPool2d(5, pool_stride, 0, count_include_pad=False), nn.Conv2d(C, 128, 1, bias=False),
+                         nn.BatchNorm2d(128), nn.ReLU(inplace=True), nn.Conv2d(128, 768, 2, bias=False), nn.BatchNorm2d(768),
+                         nn.ReLU(inplace=True), nn.Flatten(), nn.Linear(768, num_classes))
+
+
+class NetworkImageNet(nn.Module):
+    """ImageNet-resolution variant (``darts/model.py:161-216``): two stride-2 stems bring 224x224 down to 28x28 before the cells,
+    the first cell therefore sees a reduced ``s0``; 7x7 average pool before the classifier."""
+
+    def __init__(self, C=48, num_classes=1000, layers=14, auxiliary=False, genotype=None, drop_path_prob=0.0):
+        super().__init__()
+        from .genotypes import DARTS_V2
+        genotype = genotype or DARTS_V2
+        self._layers, self._auxiliary, self.drop_path_prob = layers, auxiliary, drop_path_prob
+        self.stem0 = nn.Sequential(nn.Conv2d(3, C // 2, 3, 2, 1, bias=False), nn.BatchNorm2d(C // 2), nn.ReLU(inplace=True),
+                                   nn.Conv2d(C // 2, C, 3, 2, 1, bias=False), nn.BatchNorm2d(C))
+        self.stem1 = nn.Sequential(nn.ReLU(inplace=True), nn.Conv2d(C, C, 3, 2, 1, bias=False), nn.BatchNorm2d(C))
+        C_pp, C_p, C_curr = C, C, C
+        self.cells = nn.ModuleList()
+        reduction_prev = True
+        for i in range(layers):
+            reduction = i in [layers // 3, 2 * layers // 3]
+            if reduction:
+                C_curr *= 2
+            cell = Cell(genotype, C_pp, C_p, C_curr, reduction, reduction_prev)
+            reduction_prev = reduction
+            self.cells.append(cell)
+            C_pp, C_p = C_p, cell.multiplier * C_curr
+            if i == 2 * layers // 3:
+                C_aux = C_p
+        if auxiliary:
+            self.auxiliary_head = _aux_head(C_aux, num_classes, 2)
+        self.global_pooling = nn.AdaptiveAvgPool2d(1)        # == AvgPool2d(7) at 224x224, and still defined at other resolutions
+        self.classifier = nn.Linear(C_p, num_classes)
+
+    def forward(self, x):
+        aux = None
+        s0 = self.stem0(x)
+        s1 = self.stem1(s0)
+        for i, cell in enumerate(self.cells):
+            s0, s1 = s1, cell(s0, s1, self.drop_path_prob)
+            if i == 2 * self._layers // 3 and self._auxiliary and self.training:
+                aux = self.auxiliary_head(s1)
+        out = self.classifier(self.global_pooling(s1).flatten(1))
+        return (out, aux) if (self._auxiliary and self.training) else out
