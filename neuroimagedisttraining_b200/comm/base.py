@@ -7,8 +7,8 @@
 * :class:`GrpcCommManager` -- unary RPC with raw-bytes payloads on port ``base_port + rank``
   (``gRPC/grpc_comm_manager.py:20-106``; the reference's JSON-string payload and broken imports are not reproduced).
 
-MQTT (``mqtt/mqtt_comm_manager.py``) needs ``paho-mqtt`` and a live broker; :class:`MqttCommManager` raises a clear
-ImportError when the package is missing (it is not in this image).
+MQTT (``mqtt/mqtt_comm_manager.py``): :class:`MqttCommManager` runs on ``paho-mqtt`` when installed, else on the built-in
+MQTT 3.1.1 client of :mod:`.mqtt_mini`, which also provides a small broker (the image has neither paho nor a broker).
 """
 from __future__ import annotations
 
@@ -169,28 +169,46 @@ class GrpcCommManager(BaseCommunicationManager):
 
 
 class MqttCommManager(BaseCommunicationManager):
-    """Pub/sub transport (topic ``fedml<id>``, ``mqtt_comm_manager.py:99-120``); needs paho-mqtt and a broker."""
+    """Pub/sub transport: every participant subscribes to ``<topic><its id>`` and publishes to the receiver's topic
+    (``mqtt_comm_manager.py:99-120``).  ``impl="auto"`` uses ``paho-mqtt`` when it is installed and otherwise the built-in MQTT 3.1.1
+    client (:mod:`.mqtt_mini`, same wire protocol); a broker must be reachable -- :class:`.mqtt_mini.MiniMqttBroker` is one."""
 
-    def __init__(self, host: str, port: int, client_id: int, client_num: int, topic: str = "fedml"):
+    def __init__(self, host: str, port: int, client_id: int, client_num: int, topic: str = "fedml", impl: str = "auto"):
         super().__init__()
-        try:
-            import paho.mqtt.client as mqtt  # type: ignore
-        except ImportError as e:
-            raise ImportError("MqttCommManager needs the `paho-mqtt` package and a reachable broker; neither ships with this image. "
-                              "Use InProcessCommManager, TorchDistCommManager or GrpcCommManager.") from e
         self.client_id, self.client_num, self.topic = client_id, client_num, topic
         self._q: "queue.Queue[bytes]" = queue.Queue()
-        self.client = mqtt.Client(client_id=str(client_id))
-        self.client.on_message = lambda c, u, m: self._q.put(m.payload)
-        self.client.connect(host, port)
-        self.client.subscribe(f"{topic}{client_id}")
-        self.client.loop_start()
+        mqtt = None
+        if impl in ("auto", "paho"):
+            try:
+                import paho.mqtt.client as mqtt  # type: ignore
+            except ImportError as e:
+                if impl == "paho":
+                    raise ImportError("impl='paho' needs the `paho-mqtt` package, which does not ship with this image; "
+                                      "impl='auto' falls back to the built-in client") from e
+        if mqtt is not None:
+            self.client = mqtt.Client(client_id=str(client_id))
+            self.client.on_message = lambda c, u, m: self._q.put(m.payload)
+            self.client.connect(host, port)
+            self.client.subscribe(f"{topic}{client_id}")
+            self.client.loop_start()
+            self._publish = lambda t, b: self.client.publish(t, payload=b)
+            self._close = lambda: (self.client.loop_stop(), self.client.disconnect())
+        else:
+            from .mqtt_mini import MiniMqttClient
+            self.client = MiniMqttClient(f"{topic}-{client_id}", on_message=lambda t, b: self._q.put(b)).connect(host, port)
+            self.client.subscribe(f"{topic}{client_id}")
+            self._publish = self.client.publish
+            self._close = self.client.disconnect
 
     def send_message(self, msg: Message):
-        self.client.publish(f"{self.topic}{int(msg.get_receiver_id())}", payload=msg.to_bytes())
+        self._publish(f"{self.topic}{int(msg.get_receiver_id())}", msg.to_bytes())
 
     def _poll(self, timeout):
         try:
             return Message.from_bytes(self._q.get(timeout=timeout))
         except queue.Empty:
             return None
+
+    def stop_receive_message(self):
+        super().stop_receive_message()
+        self._close()

@@ -22,7 +22,7 @@ def make_comm_manager(backend: str, rank: int, size: int, **kw) -> BaseCommunica
     if backend == "GRPC":
         return GrpcCommManager(kw.get("host", "127.0.0.1"), int(kw.get("base_port", 50000)), rank, size, kw.get("ip_table"))
     if backend == "MQTT":
-        return MqttCommManager(kw.get("host", "127.0.0.1"), int(kw.get("port", 1883)), rank, size - 1)
+        return MqttCommManager(kw.get("host", "127.0.0.1"), int(kw.get("port", 1883)), rank, size - 1, kw.get("topic", "fedml"), kw.get("impl", "auto"))
     raise ValueError(f"unknown communication backend {backend!r}")
 
 

@@ -55,10 +55,48 @@ def test_fedavg_over_grpc_loopback():
     _run_fedavg(lambda r, s: GrpcCommManager("127.0.0.1", 52310, r, s), n_clients=2, rounds=1)
 
 
-def test_mqtt_backend_reports_missing_dependency():
+def test_fedavg_over_mqtt_with_the_builtin_broker():
+    """MQTT transport end to end: the in-tree broker on a free loopback port, one topic per participant (``fedml<id>``), model-sized
+    payloads (multi-byte remaining-length field) and the same FedAvg result as the other transports."""
+    from neuroimagedisttraining_b200.comm import MiniMqttBroker
+    broker = MiniMqttBroker("127.0.0.1", 0).start()
+    try:
+        _run_fedavg(lambda r, s: MqttCommManager("127.0.0.1", broker.port, r, s - 1), n_clients=3, rounds=2)
+        assert broker.published >= 2 * 3 * 2
+    finally:
+        broker.stop()
+
+
+def test_mqtt_wire_format_and_fanout():
+    import queue
+    from neuroimagedisttraining_b200.comm import MiniMqttBroker, MiniMqttClient
+    from neuroimagedisttraining_b200.comm import mqtt_mini as M
+    assert M._encode_len(0) == b"\x00" and M._encode_len(127) == b"\x7f" and M._encode_len(128) == b"\x80\x01" and M._encode_len(16384) == b"\x80\x80\x01"
+    assert M._publish_packet("a/b", b"hi") == b"\x30\x07\x00\x03a/bhi"            # fixed header, topic length, topic, payload
+    broker = MiniMqttBroker("127.0.0.1", 0).start()
+    try:
+        got = [queue.Queue(), queue.Queue()]
+        subs = [MiniMqttClient(f"s{i}", on_message=lambda t, b, i=i: got[i].put((t, b)), keepalive=0).connect("127.0.0.1", broker.port) for i in range(2)]
+        for c in subs:
+            c.subscribe("room")
+        subs[1].subscribe("only1")
+        pub = MiniMqttClient("p", keepalive=0).connect("127.0.0.1", broker.port)
+        big = bytes(range(256)) * 1200                                             # 307 200 bytes -> 3-byte length field
+        pub.publish("room", big)
+        pub.publish("only1", b"x")
+        pub.publish("nobody", b"dropped")
+        assert got[0].get(timeout=5) == ("room", big) and got[1].get(timeout=5) == ("room", big)
+        assert got[1].get(timeout=5) == ("only1", b"x") and got[0].empty()
+        for c in subs + [pub]:
+            c.disconnect()
+    finally:
+        broker.stop()
+
+
+def test_mqtt_paho_request_reports_missing_dependency():
     try:
         import paho.mqtt.client  # noqa: F401
         pytest.skip("paho-mqtt is installed")
     except ImportError:
         with pytest.raises(ImportError, match="paho-mqtt"):
-            MqttCommManager("127.0.0.1", 1883, 0, 1)
+            MqttCommManager("127.0.0.1", 1883, 0, 1, impl="paho")
