@@ -56,13 +56,47 @@ class IndexLoader:
         self._gen.set_state(s)
 
 
-class TensorBatchLoader:
-    """``(x, y)`` mini-batches over in-memory tensors (image datasets)."""
+class BatchAugment:
+    """The reference's training transform for CIFAR / Tiny-ImageNet -- ``RandomCrop(size, padding=4)`` + ``RandomHorizontalFlip``
+    (``cifar10/data_loader.py:43-60``), plus the ``Cutout(16)`` it keeps commented out -- as one batched tensor op on the already
+    normalised images.  The crop pads with zeros in normalised space (torchvision pads the raw image with black, i.e. ``-mean/std``
+    after normalisation); the stream is the loader's own seeded generator, so runs are reproducible."""
 
-    def __init__(self, x: torch.Tensor, y: torch.Tensor, batch_size: int, shuffle: bool, seed: int = 0):
+    def __init__(self, padding: int = 4, flip: bool = True, cutout: int = 0):
+        self.padding, self.flip, self.cutout = int(padding), bool(flip), int(cutout)
+
+    def __call__(self, x: torch.Tensor, gen: torch.Generator) -> torch.Tensor:
+        n, _, h, w = x.shape
+        if self.padding:
+            p = self.padding
+            xp = torch.nn.functional.pad(x, (p, p, p, p))
+            dy = torch.randint(0, 2 * p + 1, (n,), generator=gen)
+            dx = torch.randint(0, 2 * p + 1, (n,), generator=gen)
+            rows = (dy.view(n, 1) + torch.arange(h).view(1, h)).view(n, 1, h, 1).expand(n, x.shape[1], h, w + 2 * p)
+            xp = xp.gather(2, rows)
+            cols = (dx.view(n, 1) + torch.arange(w).view(1, w)).view(n, 1, 1, w).expand(n, x.shape[1], h, w)
+            x = xp.gather(3, cols)
+        if self.flip:
+            f = torch.rand(n, generator=gen) < 0.5
+            x = torch.where(f.view(n, 1, 1, 1), x.flip(3), x)
+        if self.cutout:
+            c = self.cutout
+            cy = torch.randint(0, h, (n,), generator=gen).view(n, 1, 1)
+            cx = torch.randint(0, w, (n,), generator=gen).view(n, 1, 1)
+            yy, xx = torch.arange(h).view(1, h, 1), torch.arange(w).view(1, 1, w)
+            hole = ((yy >= cy - c // 2) & (yy < cy + c // 2) & (xx >= cx - c // 2) & (xx < cx + c // 2)).view(n, 1, h, w)
+            x = x.masked_fill(hole, 0.0)
+        return x
+
+
+class TensorBatchLoader:
+    """``(x, y)`` mini-batches over in-memory tensors (image datasets); ``augment`` is applied to training batches."""
+
+    def __init__(self, x: torch.Tensor, y: torch.Tensor, batch_size: int, shuffle: bool, seed: int = 0, augment: Optional[BatchAugment] = None):
         self.x, self.y = x, y
         self.batch_size = int(batch_size)
         self.shuffle = shuffle
+        self.augment = augment
         self._gen = torch.Generator()
         self._gen.manual_seed(int(seed))
         self.dataset = y
@@ -79,7 +113,8 @@ class TensorBatchLoader:
         order = torch.randperm(n, generator=self._gen) if self.shuffle else torch.arange(n)
         for b in range(len(self)):
             sel = order[b * self.batch_size:(b + 1) * self.batch_size]
-            yield self.x[sel], self.y[sel]
+            xb = self.x[sel]
+            yield (self.augment(xb, self._gen) if self.augment is not None else xb), self.y[sel]
 
 
 def _abcd_tuple(store: VolumeStore, train: Sequence[np.ndarray], test: Sequence[np.ndarray], batch_size: int, seed: int):
@@ -150,10 +185,12 @@ def _load_torchvision(dataset: str, data_dir: str):
 
 def load_partition_data_images(dataset: str, data_dir: Optional[str], partition_method: str, partition_alpha: float,
                                client_number: int, batch_size: int, logger=None, seed: int = 0,
-                               val_split: float = 0.0, synthetic_size: Tuple[int, int] = (2000, 500)):
+                               val_split: float = 0.0, synthetic_size: Tuple[int, int] = (2000, 500), augment: bool = False,
+                               cutout: int = 0):
     """CIFAR-10/100/Tiny-ImageNet 8-tuple (``cifar10/data_loader.py:208-249``; the ``_val`` variant
     with a 10 % validation split, ``cifar10/data_val_loader.py:260-326``, via ``val_split``).
-    Test data of a client follows the client's own label distribution, as in the reference."""
+    Test data of a client follows the client's own label distribution, as in the reference.  ``augment`` turns the reference's
+    training transform on (random crop with 4-pixel padding + horizontal flip, optional Cutout) for the clients' training loaders."""
     n_cls = {"cifar10": 10, "cifar100": 100, "tiny": 200}[dataset]
     shape = (3, 64, 64) if dataset == "tiny" else (3, 32, 32)
     try:
@@ -172,6 +209,7 @@ def load_partition_data_images(dataset: str, data_dir: Optional[str], partition_
     rng = np.random.RandomState(seed + 1)
     local_num, train_local, test_local, val_local = {}, {}, {}, {}
     te_pools = {c: np.where(yte_np == c)[0] for c in range(n_cls)}
+    aug = BatchAugment(4, True, cutout) if augment else None
     for cid in range(client_number):
         idx = idx_map[cid]
         if val_split > 0:
@@ -182,7 +220,7 @@ def load_partition_data_images(dataset: str, data_dir: Optional[str], partition_
         n_te = max(1, int(len(yte_np) / client_number))
         te_idx = np.concatenate([rng.choice(te_pools[c], max(1, int(n_te * cnt / total)), replace=True)
                                  for c, cnt in stats[cid].items()]) if stats[cid] else np.arange(0)
-        train_local[cid] = TensorBatchLoader(xtr[idx], ytr[idx], batch_size, True, seed=seed * 100003 + cid)
+        train_local[cid] = TensorBatchLoader(xtr[idx], ytr[idx], batch_size, True, seed=seed * 100003 + cid, augment=aug)
         test_local[cid] = TensorBatchLoader(xte[te_idx], yte[te_idx], batch_size, False)
         local_num[cid] = len(idx)
     train_global = TensorBatchLoader(xtr, ytr, batch_size, True, seed)

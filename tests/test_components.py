@@ -174,3 +174,22 @@ def test_halo_kernel_shape_support_query_runs_without_a_gpu():
     assert lib.nidt_conv3d_halo_supported(3, 4, 5, 4, 256, 256, 1, 128) == 0       # four Cin blocks of planes exceed shared memory
     assert lib.nidt_conv3d_halo_supported(2, 8, 8, 200, 64, 64, 1, 64) == 0        # row pitch above 128
     assert lib.nidt_conv3d_halo_supported(2, 8, 8, 8, 32, 64, 1, 64) == 0          # Cin not a multiple of 64
+
+
+def test_batch_augment_crops_flips_and_cuts_reproducibly():
+    import itertools
+    from neuroimagedisttraining_b200.data.loaders import BatchAugment, TensorBatchLoader, load_partition_data_images
+    x = torch.arange(3 * 2 * 6 * 6).float().view(3, 2, 6, 6) + 1
+    y = BatchAugment(2, True, 0)(x, torch.Generator().manual_seed(0))
+    for i in range(3):                                   # each output is a shifted, maybe mirrored window of the zero-padded input
+        xp = torch.nn.functional.pad(x[i], (2, 2, 2, 2))
+        wins = [xp[:, dy:dy + 6, dx:dx + 6] for dy, dx in itertools.product(range(5), range(5))]
+        assert any(torch.equal(w, y[i]) or torch.equal(w.flip(2), y[i]) for w in wins)
+    holes = (BatchAugment(0, False, 4)(torch.ones(4, 2, 8, 8), torch.Generator().manual_seed(1)) == 0).sum(dim=(1, 2, 3))
+    assert ((holes > 0) & (holes <= 2 * 16)).all()
+    a = [b[0] for b in TensorBatchLoader(x, torch.arange(3), 2, True, seed=5, augment=BatchAugment())]
+    b = [b[0] for b in TensorBatchLoader(x, torch.arange(3), 2, True, seed=5, augment=BatchAugment())]
+    assert all(torch.equal(p, q) for p, q in zip(a, b))
+    ds = load_partition_data_images("cifar10", None, "homo", 0, 2, 8, synthetic_size=(64, 16), augment=True, cutout=8)
+    xb, yb = next(iter(ds[5][0]))
+    assert xb.shape == (8, 3, 32, 32) and ds[5][0].augment is not None and ds[6][0].augment is None
