@@ -218,8 +218,9 @@ def load_partition_data_images(dataset: str, data_dir: Optional[str], partition_
             val_local[cid] = TensorBatchLoader(xtr[vidx], ytr[vidx], batch_size, False)
         total = max(1, sum(stats[cid].values()))
         n_te = max(1, int(len(yte_np) / client_number))
-        te_idx = np.concatenate([rng.choice(te_pools[c], max(1, int(n_te * cnt / total)), replace=True)
-                                 for c, cnt in stats[cid].items()]) if stats[cid] else np.arange(0)
+        picks = [rng.choice(te_pools[c], max(1, int(n_te * cnt / total)), replace=True)
+                 for c, cnt in stats[cid].items() if len(te_pools[c])]         # a class may be absent from a small test set
+        te_idx = np.concatenate(picks) if picks else np.arange(min(n_te, len(yte_np)))
         train_local[cid] = TensorBatchLoader(xtr[idx], ytr[idx], batch_size, True, seed=seed * 100003 + cid, augment=aug)
         test_local[cid] = TensorBatchLoader(xte[te_idx], yte[te_idx], batch_size, False)
         local_num[cid] = len(idx)
