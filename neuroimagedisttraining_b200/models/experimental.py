@@ -41,21 +41,20 @@ def group_norm(input, group, running_mean, running_var, weight=None, bias=None, 
     else:
         shape = (1, g) + (1,) * (x.dim() - 2)
         mean, var = running_mean.view(shape), running_var.view(shape)
-    y = ((x - mean) / torch.sqrt(var + eps)).reshape(input.shape)
-    if weight is not None:
-        shp = (1, c) + (1,) * (input.dim() - 2)
+    y = (x - mean) / torch.sqrt(var + eps)
+    if weight is not None:              # one scale / shift per group, as in the reference (its batch_norm "channels" are the groups)
+        shp = (1, g) + (1,) * (x.dim() - 2)
         y = y * weight.view(shp) + bias.view(shp)
-    return y
+    return y.reshape(input.shape)
 
 
 class _GroupNorm(_BatchNorm):
     def __init__(self, num_features, num_groups=1, eps=1e-5, momentum=0.1, affine=False, track_running_stats=False):
         self.num_groups = num_groups
         self.track_running_stats = track_running_stats
+        # `num_groups` is the number of CHANNELS PER GROUP (the reference's naming); statistics and the affine pair are per group,
+        # so parameters / buffers have num_features / num_groups entries and checkpoints are interchangeable with the reference's
         super().__init__(int(num_features / num_groups), eps, momentum, affine, track_running_stats)
-        if affine:   # affine parameters are per channel, statistics per group
-            self.weight = nn.Parameter(torch.ones(num_features))
-            self.bias = nn.Parameter(torch.zeros(num_features))
 
     def _check_input_dim(self, input):
         return NotImplemented

@@ -1,0 +1,83 @@
+"""Model drop-in parity with the reference's model zoo: the same ``state_dict`` keys and shapes (checkpoints are interchangeable) and,
+with the reference's weights loaded, the same outputs in eval mode.  3-D: ``salient_models.py``; 2-D: ``resnet.py``, ``vgg.py``,
+``cnn_cifar10.py``, ``lenet5.py``, ``cnn.py``, ``resnet_gn.py``, ``group_normalization.py``."""
+import pytest
+import torch
+
+from baseline import ref_harness
+from neuroimagedisttraining_b200.models import create_model, experimental as E, planar as P, volumetric as V
+
+pytestmark = pytest.mark.skipif(ref_harness.reference_available() is not None, reason="reference not installed")
+
+
+def _same(ours, ref, x, atol=1e-5, pick=None):
+    rs = ref.state_dict()
+    os_ = ours.state_dict()
+    assert list(os_.keys()) == list(rs.keys()), (sorted(set(os_) ^ set(rs))[:6])
+    for k in rs:
+        assert os_[k].shape == rs[k].shape, k
+    ours.load_state_dict(rs)
+    ours.eval(); ref.eval()
+    with torch.no_grad():
+        a, b = ours(x), ref(x)
+    if pick is not None:
+        b = pick(b)
+    torch.testing.assert_close(a, b, rtol=1e-4, atol=atol)
+
+
+def test_2d_models_are_drop_in():
+    ref_harness.import_reference()
+    from fedml_api.model.cv import cnn as r_cnn, cnn_cifar10 as r_c10, lenet5 as r_lenet, resnet as r_resnet, vgg as r_vgg
+    torch.manual_seed(0)
+    x32, x64, x28 = torch.randn(2, 3, 32, 32), torch.randn(2, 3, 64, 64), torch.randn(2, 1, 28, 28)
+    _same(P.customized_resnet18(10), r_resnet.customized_resnet18(class_num=10), x32)
+    _same(P.original_resnet18(10), r_resnet.original_resnet18(class_num=10), x32)
+    _same(P.tiny_resnet18(200), r_resnet.tiny_resnet18(class_num=200), x64)
+    _same(P.vgg11(10), r_vgg.vgg11(10), x32)
+    _same(P.vgg16(10), r_vgg.vgg16(10), x32)
+    _same(P.cnn_cifar10(), r_c10.cnn_cifar10(), x32)
+    _same(P.cnn_cifar100(), r_c10.cnn_cifar100(), x32)
+    _same(P.LeNet5(10), r_lenet.LeNet5(10), x28)
+    _same(P.CNN_OriginalFedAvg(True), r_cnn.CNN_OriginalFedAvg(True), x28.squeeze(1))
+    _same(P.CNN_DropOut(True), r_cnn.CNN_DropOut(True), x28.squeeze(1))
+
+
+def test_3d_models_are_drop_in():
+    ref_harness.import_reference()
+    from fedml_api.model.cv import salient_models as R
+    torch.manual_seed(1)
+    x = torch.randn(1, 1, 121, 145, 121)
+    _same(V.AlexNet3D_Dropout(1), R.AlexNet3D_Dropout(1), x)
+    first = lambda out: out[0] if isinstance(out, (list, tuple)) else out     # the reference returns [logits, logits / features] for these
+    _same(V.AlexNet3D_Deeper_Dropout(1), R.AlexNet3D_Deeper_Dropout(1), x, pick=first)
+    _same(V.AlexNet3D_Dropout_Regression(1), R.AlexNet3D_Dropout_Regression(1), x, pick=first)
+    # ResNet_l3: the reference hard-codes a 9216-feature FC (salient_models.py:99); 9216 = 256 * 4*3*3 is what a 193x160x160 volume
+    # leaves after the stem, three stages and AvgPool3d(3), so that is the shape at which the two can be compared
+    x9216 = torch.randn(1, 1, 193, 160, 160)
+    ours = V.resnet3d_18(1, in_shape=(193, 160, 160))
+    ref = R.ResNet_l3(R.BasicBlock, [2, 2, 2], num_classes=1)
+    _same(ours, ref, x9216, atol=1e-4, pick=first)
+
+
+def test_group_norm_layers_match_reference():
+    ref_harness.import_reference()
+    from fedml_api.model.cv import group_normalization as G, resnet_gn as RG
+    torch.manual_seed(2)
+    x = torch.randn(3, 8, 5, 6)
+    a, b = E.GroupNorm2d(8, 4, affine=True), G.GroupNorm2d(8, 4, affine=True)
+    with torch.no_grad():
+        b.weight.uniform_(0.5, 1.5); b.bias.uniform_(-0.5, 0.5)
+    a.load_state_dict(b.state_dict())
+    torch.testing.assert_close(a(x), b(x), rtol=1e-5, atol=1e-6)
+    x3 = torch.randn(2, 8, 3, 4, 5)
+    a3, b3 = E.GroupNorm3d(8, 2, affine=True), G.GroupNorm3d(8, 2, affine=True)
+    a3.load_state_dict(b3.state_dict())
+    torch.testing.assert_close(a3(x3), b3(x3), rtol=1e-5, atol=1e-6)
+    _same(E.resnet18_gn(num_classes=10, group_norm=2), RG.resnet18(num_classes=10, group_norm=2), torch.randn(2, 3, 32, 32), atol=1e-4)   # AvgPool2d(1) head: 32x32 inputs
+
+
+def test_registry_names_cover_the_reference_create_model():
+    """Every model name the reference's entry scripts accept builds here too (``main_*.py: create_model``)."""
+    for name, ds in [("3DCNN", "ABCD"), ("resnet18", "cifar10"), ("resnet18", "tiny"), ("vgg11", "cifar10"), ("cnn_cifar10", "cifar10"),
+                     ("cnn_cifar100", "cifar100"), ("lenet5", "cifar10")]:
+        assert create_model(name, {"ABCD": 1, "cifar10": 10, "cifar100": 100, "tiny": 200}[ds], dataset=ds) is not None
