@@ -3,16 +3,17 @@
 * ``GroupNorm2d`` / ``GroupNorm3d`` with running statistics (``group_normalization.py:7-53``: group norm expressed as a
   reshaped batch norm) and the ImageNet-style ``resnet*_gn`` family built on them (``resnet_gn.py``);
 * ``per_batch_norm`` -- BatchNorm whose affine parameters are supplied per call -- and the CIFAR bottleneck ResNets
-  ``resnet29_ip / 56 / 110`` (``resnet_ip.py``);
+  ``resnet29_ip / 56 / 110`` whose every tensor is a shared ``*_g`` + personal ``*_v`` pair (``resnet_ip.py``);
 * ``Meta_net`` (a small hyper-network mapping a mask to weights, imported by most reference trainers but never used) and
   ``cnn_cifar10_meta`` (``cnn_meta.py``);
 * CIFAR bottleneck ``resnet20 / resnet29`` with an optional feature output for distillation (``resnet_meta.py``; the
-  reference's ``Meta_net(nn.module)`` typo at ``:148`` is not reproduced) and the slimmable ``ResNet20`` whose stage
-  widths are chosen per call by scale ids (``resnet_meta_2.py``).
+  reference's ``Meta_net(nn.module)`` typo at ``:148`` is not reproduced), the slimmable ``ResNet20`` whose block widths are
+  chosen per call by scale ids, and ``MetaPruningResNet20`` -- the working form of ``resnet_meta_2.py``: hyper-networks emit every
+  convolution weight from the requested width ratios (31 scales), one statistics-only BatchNorm per width.
 """
 from __future__ import annotations
 
-from typing import List, Optional, Sequence
+from typing import Dict, List, Optional, Sequence
 
 import torch
 import torch.nn as nn
@@ -247,16 +248,112 @@ def resnet29(class_num=10, **kw):
     return CifarBottleneckResNet([3, 3, 3], class_num, **kw)
 
 
+# "ip" networks (``resnet_ip.py:98-300``): every learnable tensor exists twice, a shared part ``*_g`` (what federated averaging
+# exchanges) and a personal variation ``*_v`` (kept by the client); the layer runs with their SUM.  Normalisation layers keep no
+# running statistics (``track_running_stats=False``) and take the summed affine pair per call.
+def _pair_conv(g: nn.Conv2d, v: nn.Conv2d, x):
+    return F.conv2d(x, g.weight + v.weight, None, g.stride, g.padding, g.dilation, g.groups)
+
+
+def _pair_bn(g: per_batch_norm, v: per_batch_norm, x):
+    return g(x, g.weight + v.weight, g.bias + v.bias)
+
+
+def _ip_pair(mod: nn.Module, tag: str, cin: int, cout: int, k: int, stride: int = 1, bn_first: bool = False):
+    """Registers ``conv<tag>_g/_v`` and ``bn<tag>_g/_v`` on ``mod`` in the reference's order (checkpoints stay interchangeable)."""
+    mk_conv = lambda: nn.Conv2d(cin, cout, k, stride, k // 2, bias=False)
+    mk_bn = lambda: per_batch_norm(cout, track_running_stats=False)
+    order = ([("conv", "g"), ("bn", "g"), ("conv", "v"), ("bn", "v")] if bn_first else [("conv", "g"), ("conv", "v"), ("bn", "g"), ("bn", "v")])
+    for kind, part in order:
+        mod.add_module(f"{kind}{tag}_{part}", mk_conv() if kind == "conv" else mk_bn())
+
+
+class _IPBottleneck(nn.Module):
+    expansion = 4
+
+    def __init__(self, inplanes, planes, stride=1, downsample=None):
+        super().__init__()
+        _ip_pair(self, "1", inplanes, planes, 1)
+        _ip_pair(self, "2", planes, planes, 3, stride)
+        _ip_pair(self, "3", planes, planes * 4, 1)
+        self.relu = nn.ReLU(inplace=True)
+        self.downsample = downsample
+
+    def forward(self, x):
+        r = x
+        y = self.relu(_pair_bn(self.bn1_g, self.bn1_v, _pair_conv(self.conv1_g, self.conv1_v, x)))
+        y = self.relu(_pair_bn(self.bn2_g, self.bn2_v, _pair_conv(self.conv2_g, self.conv2_v, y)))
+        y = _pair_bn(self.bn3_g, self.bn3_v, _pair_conv(self.conv3_g, self.conv3_v, y))
+        if self.downsample is not None:
+            d = self.downsample
+            r = _pair_bn(d.bn1_g, d.bn1_v, _pair_conv(d.conv1_g, d.conv1_v, x))
+        return self.relu(y + r)
+
+
+class ResNet_ip(nn.Module):
+    """16-32-64 CIFAR bottleneck ResNet with shared + personal parameter pairs; ``KD=True`` also returns the pooled features.
+    ``shared_parameters()`` / ``personal_parameters()`` split the two halves for aggregation."""
+
+    def __init__(self, layers: Sequence[int], num_classes=10, KD=False, zero_init_residual=False):
+        super().__init__()
+        self.inplanes, self.KD = 16, KD
+        _ip_pair(self, "1", 3, 16, 3)
+        self.relu = nn.ReLU(inplace=True)
+        self.layer1 = self._make(16, layers[0], 1)
+        self.layer2 = self._make(32, layers[1], 2)
+        self.layer3 = self._make(64, layers[2], 2)
+        self.avgpool = nn.AdaptiveAvgPool2d((1, 1))
+        self.fc_g = nn.Linear(64 * 4, num_classes)
+        self.fc_v = nn.Linear(64 * 4, num_classes)
+        for m in self.modules():
+            if isinstance(m, nn.Conv2d):
+                nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
+            elif isinstance(m, per_batch_norm):        # both halves start at 1: the effective scale is 2, as in the reference
+                nn.init.ones_(m.weight)
+                nn.init.zeros_(m.bias)
+            elif isinstance(m, nn.Linear):
+                nn.init.zeros_(m.weight)
+                nn.init.zeros_(m.bias)
+        if zero_init_residual:
+            for m in self.modules():
+                if isinstance(m, _IPBottleneck):
+                    nn.init.zeros_(m.bn3_g.weight)
+                    nn.init.zeros_(m.bn3_v.weight)
+
+    def _make(self, planes, n, stride):
+        ds = None
+        if stride != 1 or self.inplanes != planes * 4:
+            ds = nn.Sequential()
+            _ip_pair(ds, "1", self.inplanes, planes * 4, 1, stride, bn_first=True)
+        blocks = [_IPBottleneck(self.inplanes, planes, stride, ds)]
+        self.inplanes = planes * 4
+        blocks += [_IPBottleneck(self.inplanes, planes) for _ in range(1, n)]
+        return nn.Sequential(*blocks)
+
+    def shared_parameters(self):
+        return [p for n, p in self.named_parameters() if n.rsplit(".", 1)[0].endswith("_g")]
+
+    def personal_parameters(self):
+        return [p for n, p in self.named_parameters() if n.rsplit(".", 1)[0].endswith("_v")]
+
+    def forward(self, x):
+        x = self.relu(_pair_bn(self.bn1_g, self.bn1_v, _pair_conv(self.conv1_g, self.conv1_v, x)))
+        x = self.layer3(self.layer2(self.layer1(x)))
+        f = torch.flatten(self.avgpool(x), 1)
+        out = F.linear(f, self.fc_g.weight + self.fc_v.weight, self.fc_g.bias + self.fc_v.bias)
+        return (f, out) if self.KD else out
+
+
 def resnet29_ip(class_num=10, **kw):
-    return CifarBottleneckResNet([3, 3, 3], class_num, norm=per_batch_norm, **kw)
+    return ResNet_ip([3, 3, 3], class_num, **kw)
 
 
 def resnet56_ip(class_num=10, **kw):
-    return CifarBottleneckResNet([6, 6, 6], class_num, norm=per_batch_norm, **kw)
+    return ResNet_ip([6, 6, 6], class_num, **kw)
 
 
 def resnet110_ip(class_num=10, **kw):
-    return CifarBottleneckResNet([12, 12, 12], class_num, norm=per_batch_norm, **kw)
+    return ResNet_ip([12, 12, 12], class_num, **kw)
 
 
 # ------------------------------------------------------------------------------------- cnn_meta
@@ -281,44 +378,55 @@ class Meta_net(nn.Module):
 
 
 class cnn_cifar10_meta(nn.Module):
-    """The CIFAR CNN with per-conv binary masks (random, ``dense_ratio`` kept) and optional hyper-networks that re-weight
-    the masked kernels."""
+    """Bias-free CIFAR CNN whose three learnable layers are named ``meta_*`` (``cnn_meta.py:12-70``): conv 3->64 k5, conv 64->64 k5,
+    3x3 / stride-2 max-pools, linear 1024->10.  ``init_masks()`` draws one random binary mask per ``meta_*`` weight keeping
+    ``dense_ratio`` of the entries (the reference hard-codes 0.2 there); ``set_masks`` makes the forward pass use ``w * mask``,
+    and with ``used_meta`` a :class:`Meta_net` per layer turns the mask into a multiplicative re-weighting of the kept weights."""
 
-    def __init__(self, dense_ratio: float = 0.2, used_meta: bool = False, n_cls: int = 10):
+    def __init__(self, dense_ratio: float = 0.2, used_meta: bool = False):
         super().__init__()
         self.dense_ratio, self.used_meta = dense_ratio, used_meta
-        self.conv1 = nn.Conv2d(3, 64, 5)
-        self.conv2 = nn.Conv2d(64, 64, 5)
-        self.pool = nn.MaxPool2d(2, 2)
-        self.fc1 = nn.Linear(64 * 5 * 5, 384)
-        self.fc2 = nn.Linear(384, 192)
-        self.fc3 = nn.Linear(192, n_cls)
-        self.init_masks()
-        if used_meta:
-            self.meta1, self.meta2 = Meta_net(self.mask1[0, 0]), Meta_net(self.mask2[0, 0])
+        self.meta_conv1 = nn.Conv2d(3, 64, 5, bias=False)
+        self.meta_conv2 = nn.Conv2d(64, 64, 5, bias=False)
+        self.pool = nn.MaxPool2d(3, 2)
+        self.meta_fc1 = nn.Linear(64 * 4 * 4, 10, bias=False)
+        self.raw_conv_masks: Optional[Dict[str, torch.Tensor]] = None
+        self.hyper: Optional[nn.ModuleDict] = None        # created by set_masks when used_meta (adds keys to the state_dict)
 
     def init_conv_masks(self, size, dense_ratio):
         m = torch.zeros(size)
         k = int(dense_ratio * m.numel())
-        m.view(-1)[torch.randperm(m.numel())[:k]] = 1
+        if k > 0:
+            m.view(-1)[torch.randperm(m.numel())[:k]] = 1
         return m
 
     def init_masks(self):
-        self.register_buffer("mask1", self.init_conv_masks(self.conv1.weight.shape, self.dense_ratio))
-        self.register_buffer("mask2", self.init_conv_masks(self.conv2.weight.shape, self.dense_ratio))
+        return {name + ".weight": self.init_conv_masks(mod.weight.shape, self.dense_ratio)
+                for name, mod in self.named_modules() if "meta" in name and hasattr(mod, "weight")}
+
+    def set_masks(self, masks: Optional[Dict[str, torch.Tensor]]):
+        self.raw_conv_masks = masks
+        if masks is not None and self.used_meta and self.hyper is None:
+            # hyper-networks work on one kernel slice (conv) / one row (linear) so their size stays small
+            self.hyper = nn.ModuleDict({k.replace(".", "_"): Meta_net(m[0, 0] if m.dim() == 4 else m[0]) for k, m in masks.items()})
 
     def get_masks(self):
-        return {"conv1.weight": self.mask1, "conv2.weight": self.mask2}
+        return self.raw_conv_masks
+
+    def _weight(self, name: str, w: torch.Tensor) -> torch.Tensor:
+        if self.raw_conv_masks is None:
+            return w
+        m = self.raw_conv_masks[name + ".weight"].to(w.device)
+        w = w * m
+        if self.used_meta and self.hyper is not None:
+            probe = m[0, 0] if m.dim() == 4 else m[0]
+            w = w * (1 + self.hyper[(name + ".weight").replace(".", "_")](probe))
+        return w
 
     def forward(self, x):
-        w1, w2 = self.conv1.weight * self.mask1, self.conv2.weight * self.mask2
-        if self.used_meta:
-            w1 = w1 * (1 + self.meta1(self.mask1[0, 0]))
-            w2 = w2 * (1 + self.meta2(self.mask2[0, 0]))
-        x = self.pool(F.relu(F.conv2d(x, w1, self.conv1.bias)))
-        x = self.pool(F.relu(F.conv2d(x, w2, self.conv2.bias)))
-        x = F.relu(self.fc1(x.flatten(1)))
-        return self.fc3(F.relu(self.fc2(x)))
+        x = self.pool(F.relu(F.conv2d(x, self._weight("meta_conv1", self.meta_conv1.weight))))
+        x = self.pool(F.relu(F.conv2d(x, self._weight("meta_conv2", self.meta_conv2.weight))))
+        return F.linear(x.reshape(-1, 64 * 4 * 4), self._weight("meta_fc1", self.meta_fc1.weight))
 
 
 # ------------------------------------------------------------------------ slimmable ResNet20 (resnet_meta_2)
@@ -360,3 +468,96 @@ class ResNet20(nn.Module):
         for b, i in zip(self.blocks, ids):
             x = b(x, int(i))
         return self.fc(F.adaptive_avg_pool2d(x, 1).flatten(1))
+
+
+# ------------------------------------------------------------- MetaPruning-style ResNet (resnet_meta_2, hyper-network weights)
+# The reference's version (``resnet_meta_2.py:9-200``) cannot be constructed (``stage_repeat[3]`` with a 3-element list, blocks whose
+# widths do not chain: 16 -> 32 -> Bottleneck(256, 256) ...).  This is the working form of the same idea: no block owns convolution
+# weights; two-layer hyper-networks map the requested (mid, in, out) width ratios to the full weight tensor, of which the leading
+# channels are used, and every width has its own statistics-only BatchNorm.  Module / parameter names follow the reference's.
+META_CHANNEL_SCALES = [(10 + 3 * i) / 100 for i in range(31)]          # 0.10 .. 1.00
+
+
+def _scaled_bns(max_c: int) -> nn.ModuleList:
+    return nn.ModuleList(nn.BatchNorm2d(max(1, int(max_c * s)), affine=False) for s in META_CHANNEL_SCALES)
+
+
+class first_conv_block(nn.Module):
+    def __init__(self, base_inplanes, base_planes, stride, kernel: int = 3, pool: bool = False):
+        super().__init__()
+        self.max_inp, self.max_oup, self.stride, self.kernel = base_inplanes, base_planes, stride, kernel
+        self.fc11 = nn.Linear(1, 32)
+        self.fc12 = nn.Linear(32, base_planes * base_inplanes * kernel * kernel)
+        self.first_bn = _scaled_bns(base_planes)
+        self.maxpool = nn.MaxPool2d(3, 2, 1) if pool else nn.Identity()
+
+    def forward(self, x, oup_scale_id: int):
+        s = META_CHANNEL_SCALES[oup_scale_id]
+        oup = max(1, int(self.max_oup * s))
+        w = self.fc12(F.relu(self.fc11(x.new_tensor([s])))).view(self.max_oup, self.max_inp, self.kernel, self.kernel)
+        y = F.conv2d(x, w[:oup], None, self.stride, self.kernel // 2)
+        return self.maxpool(F.relu(self.first_bn[oup_scale_id](y)))
+
+
+class MetaBottleneck(nn.Module):
+    expansion = 4
+
+    def __init__(self, base_inplanes, base_planes, stride=1, is_downsample=False):
+        super().__init__()
+        self.max_inp, self.max_oup, self.max_mid, self.stride = base_inplanes, base_planes, max(1, base_planes // self.expansion), stride
+        mid, inp, oup = self.max_mid, self.max_inp, self.max_oup
+        self.fc11, self.fc12 = nn.Linear(3, 32), nn.Linear(32, mid * inp)
+        self.fc21, self.fc22 = nn.Linear(3, 32), nn.Linear(32, mid * mid * 9)
+        self.fc31, self.fc32 = nn.Linear(3, 32), nn.Linear(32, oup * mid)
+        self.bn1, self.bn2, self.bn3 = _scaled_bns(mid), _scaled_bns(mid), _scaled_bns(oup)
+        self.is_downsample = is_downsample
+        if is_downsample:
+            self.fc11_downsample, self.fc12_downsample = nn.Linear(3, 32), nn.Linear(32, oup * inp)
+            self.bn_downsample = _scaled_bns(oup)
+
+    def forward(self, x, mid_scale_id: int, inp_scale_id: int, oup_scale_id: int):
+        ms, is_, os_ = (META_CHANNEL_SCALES[i] for i in (mid_scale_id, inp_scale_id, oup_scale_id))
+        mid, oup = max(1, int(self.max_mid * ms)), max(1, int(self.max_oup * os_))
+        inp = x.shape[1]                                    # whatever the previous block produced at its chosen width
+        r = x.new_tensor([ms, is_, os_])
+        w1 = self.fc12(F.relu(self.fc11(r))).view(self.max_mid, self.max_inp, 1, 1)
+        w2 = self.fc22(F.relu(self.fc21(r))).view(self.max_mid, self.max_mid, 3, 3)
+        w3 = self.fc32(F.relu(self.fc31(r))).view(self.max_oup, self.max_mid, 1, 1)
+        y = F.relu(self.bn1[mid_scale_id](F.conv2d(x, w1[:mid, :inp])))
+        y = F.relu(self.bn2[mid_scale_id](F.conv2d(y, w2[:mid, :mid], None, self.stride, 1)))
+        y = self.bn3[oup_scale_id](F.conv2d(y, w3[:oup, :mid]))
+        if self.is_downsample:
+            wd = self.fc12_downsample(F.relu(self.fc11_downsample(r))).view(self.max_oup, self.max_inp, 1, 1)
+            x = self.bn_downsample[oup_scale_id](F.conv2d(x, wd[:oup, :inp], None, self.stride))
+        return F.relu(y + x)
+
+
+class MetaPruningResNet20(nn.Module):
+    """``forward(x, stage_oup_scale_ids, mid_scale_ids)``: ``stage_oup_scale_ids[i]`` is the output width (index into the 31 scales) of
+    layer ``i`` (stem + one per block; blocks without a projection keep their input width, so repeated blocks of a stage must be given
+    the stage's id), ``mid_scale_ids[i-1]`` the bottleneck width of block ``i``."""
+
+    def __init__(self, num_classes=10, stage_repeat=(2, 2, 2), widths=(64, 128, 256)):
+        super().__init__()
+        self.layers = nn.ModuleList([first_conv_block(3, 16, stride=1)])
+        inp = 16
+        for si, (rep, w) in enumerate(zip(stage_repeat, widths)):
+            self.layers.append(MetaBottleneck(inp, w, stride=1 if si == 0 else 2, is_downsample=True))
+            self.layers.extend(MetaBottleneck(w, w) for _ in range(1, rep))
+            inp = w
+        self.avgpool = nn.AdaptiveAvgPool2d((1, 1))
+        self.fc = nn.Linear(inp, num_classes)
+        self.max_width = inp
+
+    @property
+    def num_blocks(self):
+        return len(self.layers) - 1
+
+    def forward(self, x, stage_oup_scale_ids: Optional[Sequence[int]] = None, mid_scale_ids: Optional[Sequence[int]] = None):
+        full = len(META_CHANNEL_SCALES) - 1
+        oup_ids = list(stage_oup_scale_ids) if stage_oup_scale_ids is not None else [full] * len(self.layers)
+        mid_ids = list(mid_scale_ids) if mid_scale_ids is not None else [full] * self.num_blocks
+        for i, block in enumerate(self.layers):
+            x = block(x, oup_ids[0]) if i == 0 else block(x, mid_ids[i - 1], oup_ids[i - 1], oup_ids[i])
+        f = self.avgpool(x).flatten(1)
+        return F.linear(f, self.fc.weight[:, :f.shape[1]], self.fc.bias)        # narrower last stage -> leading classifier columns

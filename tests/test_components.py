@@ -102,6 +102,12 @@ def test_experimental_models_and_darts():
     for f in (E.resnet20, E.resnet29_ip, E.cnn_cifar10_meta, E.ResNet20):
         assert f()(x).shape == (2, 10)
     assert E.ResNet20()(x, [0] * 9).shape == (2, 10)
+    mp = E.MetaPruningResNet20(10)                       # hyper-network generated weights, widths picked per call
+    assert mp(x).shape == (2, 10) and len(E.META_CHANNEL_SCALES) == 31 and mp.num_blocks == 6
+    y = mp(x, [30, 10, 10, 20, 20, 5, 5], [3, 7, 11, 15, 19, 23])
+    y.sum().backward()
+    assert y.shape == (2, 10) and all(p.grad is not None for p in mp.parameters())
+    assert not any(k.endswith("conv1.weight") for k in mp.state_dict())      # no block owns a convolution weight
     ref = torch.nn.GroupNorm(2, 8)
     xx = torch.randn(2, 8, 5, 5)
     torch.testing.assert_close(E.GroupNorm2d(8, 4, affine=True)(xx), ref(xx), rtol=1e-4, atol=1e-5)

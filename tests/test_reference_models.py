@@ -81,3 +81,42 @@ def test_registry_names_cover_the_reference_create_model():
     for name, ds in [("3DCNN", "ABCD"), ("resnet18", "cifar10"), ("resnet18", "tiny"), ("vgg11", "cifar10"), ("cnn_cifar10", "cifar10"),
                      ("cnn_cifar100", "cifar100"), ("lenet5", "cifar10")]:
         assert create_model(name, {"ABCD": 1, "cifar10": 10, "cifar100": 100, "tiny": 200}[ds], dataset=ds) is not None
+
+
+def test_experimental_ip_and_meta_models_are_drop_in(monkeypatch):
+    """``resnet_ip`` (shared ``*_g`` + personal ``*_v`` pairs, statistics-free BatchNorm) and ``cnn_meta``.  The reference calls
+    ``Conv2d._conv_forward(x, weight=...)`` without the ``bias`` argument newer torch versions require; the shim below only restores
+    that call signature so its forward pass can run."""
+    import torch.nn as nn
+    ref_harness.import_reference()
+    from fedml_api.model.cv import cnn_meta as CM, resnet_ip as RI
+    orig = nn.Conv2d._conv_forward
+    monkeypatch.setattr(nn.Conv2d, "_conv_forward", lambda self, x, weight, bias=None: orig(self, x, weight, bias))
+    torch.manual_seed(4)
+    x = torch.randn(2, 3, 32, 32)
+    for ours, ref in ((E.resnet29_ip(10), RI.resnet29_ip(10)), (E.resnet56_ip(10, KD=True), RI.resnet56_ip(10, KD=True))):
+        sd = ref.state_dict()
+        for k in sd:                                    # the classifier pair is zero-initialised: give it values
+            if k.startswith("fc_"):
+                sd[k] = torch.randn_like(sd[k]) * 0.1
+        ref.load_state_dict(sd)
+        assert list(ours.state_dict()) == list(sd)
+        ours.load_state_dict(sd)
+        for mode in (True, False):
+            ours.train(mode); ref.train(mode)
+            a, b = ours(x), ref(x)
+            a, b = (a, b) if not isinstance(a, tuple) else (torch.cat([a[0], a[1]], 1), torch.cat([b[0], b[1]], 1))
+            torch.testing.assert_close(a, b, rtol=1e-5, atol=1e-6)
+        assert len(ours.shared_parameters()) == len(ours.personal_parameters()) == len(list(ours.parameters())) // 2
+    _same(E.cnn_cifar10_meta(), CM.cnn_cifar10_meta(), x)
+    probe = torch.rand(5, 5)
+    _same(E.Meta_net(probe), CM.Meta_net(probe), probe)
+    m = E.cnn_cifar10_meta(dense_ratio=0.2, used_meta=True)
+    masks = m.init_masks()
+    assert set(masks) == set(CM.cnn_cifar10_meta().init_masks()) == {"meta_conv1.weight", "meta_conv2.weight", "meta_fc1.weight"}
+    assert all(abs(float(v.mean()) - 0.2) < 0.01 for v in masks.values())
+    m.set_masks(masks)
+    out = m(x)
+    out.sum().backward()
+    assert out.shape == (2, 10) and m.hyper is not None and all(p.grad is not None for p in m.hyper.parameters())
+    assert float((m.meta_conv1.weight.grad[masks["meta_conv1.weight"] == 0]).abs().max()) == 0.0     # masked weights get no gradient
