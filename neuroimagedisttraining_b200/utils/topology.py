@@ -72,7 +72,8 @@ class AsymmetricTopologyManager(BaseTopologyManager):
         self.n = n
         self.undirected_neighbor_num = undirected_neighbor_num
         self.out_directed_neighbor = out_directed_neighbor
-        self.rng = np.random.RandomState(seed)
+        # no seed: numpy's global stream, exactly what the reference draws from; a seed gives a private, reproducible stream
+        self.rng = np.random.RandomState(seed) if seed is not None else np.random
         self.topology = np.zeros((n, n), dtype=np.float32)
 
     def generate_topology(self):

@@ -184,3 +184,28 @@ def test_flop_counter_matches_reference_on_2d_models():
         ref = float(R.count_model_param_flops(model, "cifar10"))
         assert ours == pytest.approx(ref, rel=1e-6), (sparsify, ours, ref)      # the reference sums in float32
         assert float(Fl.count_training_flops(model, "cifar10")) == pytest.approx(float(R.count_training_flops(model, "cifar10")), rel=1e-6)
+
+
+def test_topology_managers_match_reference(monkeypatch):
+    """Mixing matrices of the ring + extra-links topologies.  The reference calls ``networkx.to_numpy_matrix``, removed in networkx 3;
+    the shim maps it to ``to_numpy_array`` (same values) so the reference code can run."""
+    import networkx as nx
+    import numpy as np
+    ref_harness.import_reference()
+    if not hasattr(nx, "to_numpy_matrix"):
+        monkeypatch.setattr(nx, "to_numpy_matrix", nx.to_numpy_array, raising=False)
+    from fedml_core.distributed.topology.asymmetric_topology_manager import AsymmetricTopologyManager as RefA
+    from fedml_core.distributed.topology.symmetric_topology_manager import SymmetricTopologyManager as RefS
+    from neuroimagedisttraining_b200.utils.topology import AsymmetricTopologyManager, SymmetricTopologyManager
+    for n, k in [(6, 2), (8, 4), (10, 2), (12, 6)]:
+        r, o = RefS(n, k), SymmetricTopologyManager(n, k)
+        r.generate_topology(); o.generate_topology()
+        np.testing.assert_allclose(np.asarray(o.topology), np.asarray(r.topology), atol=1e-7)
+        for i in range(n):
+            assert o.get_in_neighbor_idx_list(i) == r.get_in_neighbor_idx_list(i) and o.get_out_neighbor_idx_list(i) == r.get_out_neighbor_idx_list(i)
+    for n, u, d in [(6, 2, 2), (8, 4, 2), (16, 4, 3)]:
+        np.random.seed(n); r = RefA(n, u, d); r.generate_topology()
+        np.random.seed(n); o = AsymmetricTopologyManager(n, u, d); o.generate_topology()
+        np.testing.assert_allclose(np.asarray(o.topology), np.asarray(r.topology), atol=1e-7)
+        for i in range(n):
+            assert o.get_in_neighbor_idx_list(i) == r.get_in_neighbor_idx_list(i) and o.get_out_neighbor_idx_list(i) == r.get_out_neighbor_idx_list(i)
