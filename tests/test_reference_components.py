@@ -209,3 +209,29 @@ def test_topology_managers_match_reference(monkeypatch):
         np.testing.assert_allclose(np.asarray(o.topology), np.asarray(r.topology), atol=1e-7)
         for i in range(n):
             assert o.get_in_neighbor_idx_list(i) == r.get_in_neighbor_idx_list(i) and o.get_out_neighbor_idx_list(i) == r.get_out_neighbor_idx_list(i)
+
+
+@pytest.mark.parametrize("method,alpha,n", [("dir", 0.3, 4), ("n_cls", 3, 10), ("my_part", 2, 10), ("n_cls", 2, 7), ("my_part", 5, 10)])
+def test_label_skew_partitions_match_reference_draw_for_draw(method, alpha, n):
+    """``partition_data`` of the reference's CIFAR loader (numpy + python RNG streams seeded like its entry scripts) against ours on the
+    same labels: identical index lists per client, including the refill-on-exhaustion of ``n_cls`` / ``my_part`` and the long redraw
+    tails of ``dir`` (taken in rewound blocks here, one uniform at a time there)."""
+    import logging
+    import random
+    import numpy as np
+    ref_harness.import_reference()
+    from fedml_api.data_preprocessing.cifar10 import data_loader as RL
+    from neuroimagedisttraining_b200.data.partition import partition_labels
+    y = np.random.RandomState(5).randint(0, 10, size=1500)
+    X = np.zeros((1500, 1))
+    orig = RL.load_cifar10_data
+    RL.load_cifar10_data = lambda d: (X, y, X[:100], y[:100])       # the reference would download CIFAR-10 here
+    try:
+        log = logging.getLogger("ref-part"); log.setLevel(logging.ERROR)
+        np.random.seed(11); random.seed(11)
+        ref = RL.partition_data(None, method, n, alpha, log)[4]
+    finally:
+        RL.load_cifar10_data = orig
+    ours = partition_labels(y, method, n, alpha, seed=11)
+    for c in range(n):
+        assert np.array_equal(np.asarray(ref[c]), ours[c]), (method, c)
