@@ -8,6 +8,7 @@ local_num_dict, train_local_dict, test_local_dict, class_num]`` whose local load
 """
 from __future__ import annotations
 
+import math
 from typing import Dict, Iterator, List, Optional, Sequence, Tuple
 
 import numpy as np
@@ -204,11 +205,12 @@ def load_partition_data_images(dataset: str, data_dir: Optional[str], partition_
     except Exception:
         (xtr, ytr), (xte, yte) = synthetic_image_dataset(synthetic_size[0], synthetic_size[1], n_cls, shape, seed)
     ytr_np, yte_np = ytr.numpy(), yte.numpy()
-    idx_map = partition_labels(ytr_np, partition_method, client_number, partition_alpha, seed)
+    rng = np.random.RandomState(seed)                 # one stream for the partition and the test subsets, like the reference's global one
+    idx_map = partition_labels(ytr_np, partition_method, client_number, partition_alpha, seed, rng=rng)
     stats = {c: {int(k): int(v) for k, v in zip(*np.unique(ytr_np[i], return_counts=True))} for c, i in idx_map.items()}
-    rng = np.random.RandomState(seed + 1)
     local_num, train_local, test_local, val_local = {}, {}, {}, {}
     te_pools = {c: np.where(yte_np == c)[0] for c in range(n_cls)}
+    n_te = math.ceil(len(yte_np) / client_number)
     aug = BatchAugment(4, True, cutout) if augment else None
     for cid in range(client_number):
         idx = idx_map[cid]
@@ -216,11 +218,17 @@ def load_partition_data_images(dataset: str, data_dir: Optional[str], partition_
             nv = int(len(idx) * val_split)
             vidx, idx = idx[:nv], idx[nv:]
             val_local[cid] = TensorBatchLoader(xtr[vidx], ytr[vidx], batch_size, False)
-        total = max(1, sum(stats[cid].values()))
-        n_te = max(1, int(len(yte_np) / client_number))
-        picks = [rng.choice(te_pools[c], max(1, int(n_te * cnt / total)), replace=True)
-                 for c, cnt in stats[cid].items() if len(te_pools[c])]         # a class may be absent from a small test set
-        te_idx = np.concatenate(picks) if picks else np.arange(min(n_te, len(yte_np)))
+        # test subset with the client's own label mix (cifar10/data_loader.py:222-236): per label, the first
+        # ceil(share * ceil(n_test / clients)) entries of a fresh permutation of that label's test samples
+        total = sum(stats[cid].values())
+        picks = []
+        for c in range(n_cls):
+            want = math.ceil(stats[cid].get(c, 0) / total * n_te) if total else 0
+            perm = rng.permutation(len(te_pools[c]))
+            picks.append(te_pools[c][perm[:want]])
+        te_idx = np.concatenate(picks).astype(np.int64)
+        if len(te_idx) == 0:                              # a tiny test set without any of the client's classes
+            te_idx = np.arange(min(n_te, len(yte_np)))
         train_local[cid] = TensorBatchLoader(xtr[idx], ytr[idx], batch_size, True, seed=seed * 100003 + cid, augment=aug)
         test_local[cid] = TensorBatchLoader(xte[te_idx], yte[te_idx], batch_size, False)
         local_num[cid] = len(idx)

@@ -196,8 +196,11 @@ def my_part_partition(y: np.ndarray, n_clients: int, n_shards: int, rng: np.rand
     return _draw_by_prior(y, priors, sizes, rng, "full")
 
 
-def partition_labels(y: np.ndarray, method: str, n_clients: int, alpha: float, seed: int = 0) -> Dict[int, np.ndarray]:
-    rng = np.random.RandomState(seed)
+def partition_labels(y: np.ndarray, method: str, n_clients: int, alpha: float, seed: int = 0,
+                     rng: Optional[np.random.RandomState] = None) -> Dict[int, np.ndarray]:
+    """``rng``: continue an existing numpy stream (the loaders go on to draw the clients' test subsets from it, as the reference
+    does from the global stream); default: a fresh ``RandomState(seed)`` == ``np.random.seed(seed)``."""
+    rng = rng if rng is not None else np.random.RandomState(seed)
     if method == "homo":
         return homo_partition(len(y), n_clients, rng)
     if method == "hetero":

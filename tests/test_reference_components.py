@@ -235,3 +235,36 @@ def test_label_skew_partitions_match_reference_draw_for_draw(method, alpha, n):
     ours = partition_labels(y, method, n, alpha, seed=11)
     for c in range(n):
         assert np.array_equal(np.asarray(ref[c]), ours[c]), (method, c)
+
+
+def test_image_loader_test_subsets_match_reference():
+    """``load_partition_data_cifar10``: after partitioning, each client's test subset follows its own label mix, drawn from the same
+    numpy stream.  The reference's torchvision dataset / DataLoader construction is replaced by recorders (no CIFAR files here)."""
+    import logging
+    import random
+    import types
+    import numpy as np
+    ref_harness.import_reference()
+    from fedml_api.data_preprocessing.cifar10 import data_loader as RL
+    from neuroimagedisttraining_b200.data import loaders as L
+    (xtr, ytr), (xte, yte) = L.synthetic_image_dataset(800, 200, 10, (3, 32, 32), seed=3)
+    saved = (RL.load_cifar10_data, RL.CIFAR10, RL.get_dataloader_cifar10)
+    RL.load_cifar10_data = lambda d: (xtr.numpy(), ytr.numpy(), xte.numpy(), yte.numpy())
+    RL.CIFAR10 = lambda *a, **k: range(len(yte))
+    RL.get_dataloader_cifar10 = lambda d, b1, b2, dataidxs, test_idxs, **kw: (types.SimpleNamespace(dataset=dataidxs), np.asarray(test_idxs))
+    try:
+        log = logging.getLogger("ref-img"); log.setLevel(logging.ERROR)
+        np.random.seed(3); random.seed(3)
+        ref = RL.load_partition_data_cifar10(None, "n_cls", 3, 5, 16, log)
+    finally:
+        RL.load_cifar10_data, RL.CIFAR10, RL.get_dataloader_cifar10 = saved
+    orig = L.synthetic_image_dataset
+    L.synthetic_image_dataset = lambda *a, **k: ((xtr, ytr), (xte, yte))
+    try:
+        ours = L.load_partition_data_images("cifar10", None, "n_cls", 3, 5, 16, seed=3)
+    finally:
+        L.synthetic_image_dataset = orig
+    for c in range(5):
+        assert ours[4][c] == ref[4][c] == len(ref[5][c].dataset)
+        assert torch.equal(ours[5][c].y, ytr[np.asarray(ref[5][c].dataset)])
+        assert torch.equal(ours[6][c].y, yte[ref[6][c]]) and torch.equal(ours[6][c].x, xte[ref[6][c]])
