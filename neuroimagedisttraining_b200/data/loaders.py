@@ -9,6 +9,7 @@ local_num_dict, train_local_dict, test_local_dict, class_num]`` whose local load
 from __future__ import annotations
 
 import math
+import random
 from typing import Dict, Iterator, List, Optional, Sequence, Tuple
 
 import numpy as np
@@ -206,18 +207,26 @@ def load_partition_data_images(dataset: str, data_dir: Optional[str], partition_
         (xtr, ytr), (xte, yte) = synthetic_image_dataset(synthetic_size[0], synthetic_size[1], n_cls, shape, seed)
     ytr_np, yte_np = ytr.numpy(), yte.numpy()
     rng = np.random.RandomState(seed)                 # one stream for the partition and the test subsets, like the reference's global one
-    idx_map = partition_labels(ytr_np, partition_method, client_number, partition_alpha, seed, rng=rng)
+    py_rng = random.Random(seed)
+    idx_map = partition_labels(ytr_np, partition_method, client_number, partition_alpha, seed, rng=rng, py_rng=py_rng)
     stats = {c: {int(k): int(v) for k, v in zip(*np.unique(ytr_np[i], return_counts=True))} for c, i in idx_map.items()}
     local_num, train_local, test_local, val_local = {}, {}, {}, {}
     te_pools = {c: np.where(yte_np == c)[0] for c in range(n_cls)}
     n_te = math.ceil(len(yte_np) / client_number)
     aug = BatchAugment(4, True, cutout) if augment else None
+    val_idx = {}
+    if val_split > 0:
+        # data_val_loader.py:271-274: a python-random sample of int(0.1 * len(client 0's data)) indices per client becomes its
+        # validation set, the rest (as a set, so repeats collapse) stays for training
+        for cid in range(client_number):
+            nv = int(val_split * len(idx_map[0]))          # evaluated per client as in the reference: client 0 has shrunk by then
+            pool = [int(i) for i in idx_map[cid]]
+            val_idx[cid] = np.asarray(py_rng.sample(pool, min(nv, len(pool))), dtype=np.int64)
+            idx_map[cid] = np.asarray(sorted(set(pool) - set(val_idx[cid].tolist())), dtype=np.int64)
     for cid in range(client_number):
         idx = idx_map[cid]
         if val_split > 0:
-            nv = int(len(idx) * val_split)
-            vidx, idx = idx[:nv], idx[nv:]
-            val_local[cid] = TensorBatchLoader(xtr[vidx], ytr[vidx], batch_size, False)
+            val_local[cid] = TensorBatchLoader(xtr[val_idx[cid]], ytr[val_idx[cid]], batch_size, False)
         # test subset with the client's own label mix (cifar10/data_loader.py:222-236): per label, the first
         # ceil(share * ceil(n_test / clients)) entries of a fresh permutation of that label's test samples
         total = sum(stats[cid].values())

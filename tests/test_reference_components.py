@@ -268,3 +268,40 @@ def test_image_loader_test_subsets_match_reference():
         assert ours[4][c] == ref[4][c] == len(ref[5][c].dataset)
         assert torch.equal(ours[5][c].y, ytr[np.asarray(ref[5][c].dataset)])
         assert torch.equal(ours[6][c].y, yte[ref[6][c]]) and torch.equal(ours[6][c].x, xte[ref[6][c]])
+
+
+def test_image_val_loader_matches_reference():
+    """The FedFomo loader (``data_val_loader.py``): same partition, a python-random validation sample of int(0.1 * len(client 0))
+    indices per client, the remainder for training, test subsets from the continuing numpy stream."""
+    import logging
+    import random
+    import types
+    import numpy as np
+    ref_harness.import_reference()
+    from fedml_api.data_preprocessing.cifar10 import data_val_loader as RL
+    from neuroimagedisttraining_b200.data import loaders as L
+    (xtr, ytr), (xte, yte) = L.synthetic_image_dataset(900, 200, 10, (3, 32, 32), seed=4)
+    xtr = xtr + torch.arange(900).view(-1, 1, 1, 1) * 1e-3          # make every training image identifiable
+    saved = (RL.load_cifar10_data, RL.CIFAR10, RL.get_dataloader_cifar10)
+    RL.load_cifar10_data = lambda d: (xtr.numpy(), ytr.numpy(), xte.numpy(), yte.numpy())
+    RL.CIFAR10 = lambda *a, **k: range(len(yte))
+    RL.get_dataloader_cifar10 = lambda d, b1, b2, dataidxs, test_idxs, **kw: (types.SimpleNamespace(dataset=list(dataidxs)),
+                                                                             types.SimpleNamespace(dataset=np.asarray(test_idxs)))
+    try:
+        log = logging.getLogger("ref-img"); log.setLevel(logging.ERROR)
+        np.random.seed(9); random.seed(9)
+        ref = RL.load_partition_data_cifar10(None, "dir", 0.5, 4, 16, log)
+    finally:
+        RL.load_cifar10_data, RL.CIFAR10, RL.get_dataloader_cifar10 = saved
+    orig = L.synthetic_image_dataset
+    L.synthetic_image_dataset = lambda *a, **k: ((xtr, ytr), (xte, yte))
+    try:
+        ours = L.load_partition_data_images("cifar10", None, "dir", 0.5, 4, 16, seed=9, val_split=0.1)
+    finally:
+        L.synthetic_image_dataset = orig
+    ident = lambda x: sorted((x[:, 0, 0, 0] * 0 + x.flatten(1).sum(1)).tolist())
+    for c in range(4):
+        assert ours[4][c] == ref[4][c]
+        assert ident(ours[5][c].x) == ident(xtr[np.asarray(ref[5][c].dataset)])                # training set (as a set)
+        assert torch.equal(ours[8][c].x, xtr[np.asarray(ref[6][c].dataset)])                    # validation sample, same order
+        assert torch.equal(ours[6][c].x, xte[ref[7][c].dataset])                                # test subset
