@@ -305,3 +305,25 @@ def test_image_val_loader_matches_reference():
         assert ident(ours[5][c].x) == ident(xtr[np.asarray(ref[5][c].dataset)])                # training set (as a set)
         assert torch.equal(ours[8][c].x, xtr[np.asarray(ref[6][c].dataset)])                    # validation sample, same order
         assert torch.equal(ours[6][c].x, xte[ref[7][c].dataset])                                # test subset
+
+
+def test_message_is_wire_compatible_with_reference():
+    """Same keys, constants and JSON text as ``fedml_core/distributed/communication/message.py``; each side parses the other's."""
+    ref_harness.import_reference()
+    from fedml_core.distributed.communication.message import Message as Ref
+    from neuroimagedisttraining_b200.comm import Message
+    a, b = Ref("sync", 2, 5), Message("sync", 2, 5)
+    for m in (a, b):
+        m.add_params("num_samples", 17)
+        m.add("round", 3)
+    assert a.get_params() == b.get_params() and a.to_json() == b.to_json()
+    assert (b.get_type(), b.get_sender_id(), b.get_receiver_id()) == (a.get_type(), a.get_sender_id(), a.get_receiver_id())
+    for name in dir(Ref):
+        if name.startswith("MSG_"):
+            assert getattr(Message, name) == getattr(Ref, name), name
+    back = Ref()
+    back.init_from_json_string(b.to_json())
+    assert back.get_params() == b.get_params()
+    ours = Message()
+    ours.init_from_json_string(a.to_json())
+    assert ours.get_params() == a.get_params() and ours.get("round") == 3
