@@ -25,6 +25,14 @@ def test_salientgrads_two_ranks_cpu_matches_single_process():
     assert "RESULT ok=True" in r.stdout, r.stdout[-2000:]
 
 
+def test_syncbn_over_ranks_matches_full_batch_batchnorm():
+    """SyncBN (the reference's only collective call site, batchnorm_utils.py:150-237) as two all-reduces: a batch split unevenly
+    over 3 ranks gives the full-batch BatchNorm3d outputs, gradients and running statistics."""
+    r = _torchrun("dist_worker_syncbn.py", 3, {"CUDA_VISIBLE_DEVICES": ""}, timeout=300)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "RESULT ok=True" in r.stdout, r.stdout[-2000:]
+
+
 @pytest.mark.parametrize("world", [2, 3])
 def test_depth_slab_decomposition_matches_the_unsplit_module(world):
     """One client's volumes split along depth over ranks (halo exchange per layer, BatchNorm statistics across ranks): outputs, all
