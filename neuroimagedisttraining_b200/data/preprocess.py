@@ -2,8 +2,8 @@
 121x145x121 voxels -> brain mask where the group mean exceeds 0.2 -> per-subject min-max normalisation -> 8-bit quantisation
 -> one container with ``X`` (uint8 volumes), ``y`` (``female``), ``site`` (label-encoded ``abcd_site``).
 
-NIfTI / HDF5 I/O needs ``nibabel`` / ``h5py`` (neither is in this image): the numerical steps are plain numpy and the
-``.npz`` container works everywhere."""
+NIfTI files are read with ``nibabel`` when present, else with the built-in single-file NIfTI-1 reader; the reference's HDF5 layout
+needs ``h5py`` (not in this image); the numerical steps are plain numpy and the ``.npz`` container works everywhere."""
 from __future__ import annotations
 
 from typing import Iterable, Optional, Sequence, Tuple
@@ -52,12 +52,87 @@ def build_store(volumes: Sequence[np.ndarray], labels: Sequence, site_names: Seq
     return InMemoryVolumeStore(torch.from_numpy(x), np.asarray(labels, dtype=np.float32), sites)
 
 
-def load_nifti(path: str) -> np.ndarray:  # pragma: no cover - optional dependency
+# ------------------------------------------------------------------------------------------------------ NIfTI-1
+_NIFTI_DTYPES = {2: np.uint8, 4: np.int16, 8: np.int32, 16: np.float32, 64: np.float64, 256: np.int8, 512: np.uint16, 768: np.uint32,
+                 1024: np.int64, 1280: np.uint64}
+
+
+def _read_nifti1(raw: bytes) -> np.ndarray:
+    """Single-file NIfTI-1 (``.nii``): 348-byte header (dims at 40, datatype at 70, vox_offset at 108, scl_slope / scl_inter at 112 /
+    116, magic ``n+1`` at 344), voxels in Fortran order from ``vox_offset``.  Either byte order; the intensity scaling is applied
+    when the slope is set, which is what ``nibabel``'s ``get_fdata()`` returns."""
+    if len(raw) < 348:
+        raise ValueError("not a NIfTI-1 file: shorter than its header")
+    endian = "<" if int(np.frombuffer(raw, "<i4", 1, 0)[0]) == 348 else ">"
+    if int(np.frombuffer(raw, endian + "i4", 1, 0)[0]) != 348 or raw[344:347] not in (b"n+1", b"ni1"):
+        raise ValueError("not a NIfTI-1 file (sizeof_hdr / magic)")
+    if raw[344:347] == b"ni1":
+        raise ValueError("two-file NIfTI (.hdr/.img) is not supported; convert to single-file .nii")
+    dim = np.frombuffer(raw, endian + "i2", 8, 40)
+    shape = tuple(int(d) for d in dim[1:1 + int(dim[0])])
+    code = int(np.frombuffer(raw, endian + "i2", 1, 70)[0])
+    if code not in _NIFTI_DTYPES:
+        raise ValueError(f"unsupported NIfTI datatype code {code}")
+    dt = np.dtype(_NIFTI_DTYPES[code]).newbyteorder(endian)
+    vox_offset, slope, inter = (float(v) for v in np.frombuffer(raw, endian + "f4", 3, 108))
+    off = int(vox_offset) if vox_offset >= 348 else 352
+    n = int(np.prod(shape))
+    data = np.frombuffer(raw, dt, n, off).reshape(shape, order="F").astype(np.float32)
+    if slope != 0.0 and np.isfinite(slope) and np.isfinite(inter) and (slope != 1.0 or inter != 0.0):
+        data = data * np.float32(slope) + np.float32(inter)
+    while data.ndim > 3 and data.shape[-1] == 1:          # SPM writes 3-D maps with trailing singleton dims
+        data = data[..., 0]
+    return data
+
+
+def load_nifti(path: str) -> np.ndarray:
+    """Volume of a ``.nii`` / ``.nii.gz`` file as float32 (the notebook's ``nib.load(p).get_fdata()``, cells 6-11).  Uses ``nibabel``
+    when it is installed, otherwise the built-in NIfTI-1 reader."""
     try:
         import nibabel as nib  # type: ignore
-    except ImportError as e:
-        raise ImportError("reading NIfTI files needs nibabel") from e
-    return np.asarray(nib.load(path).get_fdata(), dtype=np.float32)
+        return np.asarray(nib.load(path).get_fdata(), dtype=np.float32)
+    except ImportError:
+        pass
+    import gzip
+    with open(path, "rb") as f:
+        raw = f.read()
+    if raw[:2] == b"\x1f\x8b":
+        raw = gzip.decompress(raw)
+    return _read_nifti1(raw)
+
+
+def save_nifti(volume: np.ndarray, path: str, voxel_size=(1.5, 1.5, 1.5)) -> None:
+    """Minimal single-file NIfTI-1 writer (float32 / uint8 / int16 volumes; ``.gz`` suffix compresses) -- enough to exchange
+    preprocessed maps and to test the reader."""
+    v = np.asarray(volume)
+    code = {np.dtype(np.float32): 16, np.dtype(np.uint8): 2, np.dtype(np.int16): 4, np.dtype(np.float64): 64}.get(v.dtype)
+    if code is None:
+        v, code = v.astype(np.float32), 16
+    hdr = bytearray(352)
+    hdr[0:4] = np.int32(348).tobytes()
+    dim = np.ones(8, np.int16)
+    dim[0] = v.ndim
+    dim[1:1 + v.ndim] = v.shape
+    hdr[40:56] = dim.tobytes()
+    hdr[70:72] = np.int16(code).tobytes()
+    hdr[72:74] = np.int16(v.dtype.itemsize * 8).tobytes()
+    pix = np.ones(8, np.float32)
+    pix[1:4] = voxel_size
+    hdr[76:108] = pix.tobytes()
+    hdr[108:112] = np.float32(352).tobytes()
+    hdr[112:116] = np.float32(1.0).tobytes()
+    hdr[344:348] = b"n+1\x00"
+    blob = bytes(hdr) + v.astype(v.dtype.newbyteorder("<")).tobytes(order="F")
+    if path.endswith(".gz"):
+        import gzip
+        blob = gzip.compress(blob, 1)
+    with open(path, "wb") as f:
+        f.write(blob)
+
+
+def build_store_from_nifti(paths: Sequence[str], labels: Sequence, site_names: Sequence, threshold: float = 0.2) -> InMemoryVolumeStore:
+    """The notebook end to end: read every subject's map, group-mean mask, per-subject min-max, 8-bit, label-encoded sites."""
+    return build_store([load_nifti(p) for p in paths], labels, site_names, threshold)
 
 
 def save_npz(store: InMemoryVolumeStore, path: str) -> None:

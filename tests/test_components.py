@@ -203,3 +203,34 @@ def test_batch_augment_crops_flips_and_cuts_reproducibly():
     ds = load_partition_data_images("cifar10", None, "homo", 0, 2, 8, synthetic_size=(64, 16), augment=True, cutout=8)
     xb, yb = next(iter(ds[5][0]))
     assert xb.shape == (8, 3, 32, 32) and ds[5][0].augment is not None and ds[6][0].augment is None
+
+
+def test_nifti_reader_roundtrip_scaling_and_byte_order(tmp_path):
+    rng = np.random.RandomState(0)
+    vol = rng.rand(7, 9, 5).astype(np.float32)
+    for name in ("a.nii", "a.nii.gz"):
+        P.save_nifti(vol, str(tmp_path / name))
+        assert np.array_equal(P.load_nifti(str(tmp_path / name)), vol)
+    # big-endian int16 file with an intensity scaling and a trailing singleton dimension, written by hand
+    q = rng.randint(-500, 500, size=(4, 3, 2, 1)).astype(">i2")
+    hdr = bytearray(352)
+    hdr[0:4] = np.array(348, ">i4").tobytes()
+    hdr[40:56] = np.array([4, 4, 3, 2, 1, 1, 1, 1], ">i2").tobytes()
+    hdr[70:72] = np.array(4, ">i2").tobytes()
+    hdr[72:74] = np.array(16, ">i2").tobytes()
+    hdr[108:120] = np.array([352, 0.5, 10.0], ">f4").tobytes()
+    hdr[344:348] = b"n+1\x00"
+    (tmp_path / "be.nii").write_bytes(bytes(hdr) + q.tobytes(order="F"))
+    got = P.load_nifti(str(tmp_path / "be.nii"))
+    assert got.shape == (4, 3, 2) and np.allclose(got, q[..., 0].astype(np.float32) * 0.5 + 10.0)
+    with pytest.raises(ValueError, match="NIfTI"):
+        (tmp_path / "bad.nii").write_bytes(b"\x00" * 400)
+        P.load_nifti(str(tmp_path / "bad.nii"))
+    paths = []
+    for i in range(4):
+        v = np.clip(rng.rand(6, 7, 6) + 0.3 * (i % 2), 0, None).astype(np.float32)
+        v[0] = 0
+        P.save_nifti(v, str(tmp_path / f"s{i}.nii.gz"))
+        paths.append(str(tmp_path / f"s{i}.nii.gz"))
+    store = P.build_store_from_nifti(paths, [0, 1, 0, 1], ["b", "a", "b", "a"])
+    assert store.volumes.shape == (4, 6, 7, 6) and store.volumes.dtype == torch.uint8 and list(store.sites) == [1, 0, 1, 0]
