@@ -175,6 +175,46 @@ class FedAPIBase:
         total = self.layout.numel_real()
         return 100.0 * (total - nz) / total
 
+    # ---- helpers the reference orchestrator carries without calling them (``sailentgrads_api.py:165-209,319-331``)
+    def _benefit_choose(self, round_idx, cur_clnt, client_num_in_total, client_num_per_round, dist_local=None, total_dist=None,
+                        cs=False, active_ths_rnd=None):
+        """Neighbour choice for decentralised variants: everyone, seeded-stream random peers, the ring neighbours or all active clients."""
+        from .decentralized import choose_neighbors
+        if client_num_in_total == client_num_per_round:
+            return [i for i in range(client_num_in_total)]
+        return choose_neighbors(cs, cur_clnt, client_num_in_total, client_num_per_round, active_ths_rnd)
+
+    def average_weights(self, weights_list: Sequence) -> ParamSlab:
+        """Plain (unweighted) mean of models given as slabs or state_dicts -- the sanity-check aggregate."""
+        slabs = []
+        for w in weights_list:
+            if isinstance(w, ParamSlab):
+                slabs.append(w)
+            else:
+                s = self.model_trainer.engine.new_slab()
+                s.load_state_dict(w)
+                slabs.append(s)
+        out = self.model_trainer.engine.new_slab()
+        ops.weighted_aggregate(out.flat, [s.flat for s in slabs], [1.0 / len(slabs)] * len(slabs))
+        return out
+
+    def record_avg_inference_flops(self, w_global: ParamSlab, mask_pers: Optional[Dict[int, ParamSlab]] = None) -> float:
+        """Mean inference FLOPs over clients of the (optionally per-client masked) global model; zero weights are not counted."""
+        flops = []
+        for cid in range(self.args.client_num_in_total):
+            if mask_pers is None:
+                w = w_global
+            else:
+                w = w_global.clone()
+                n = mask_pers[cid].flat.numel()
+                w.flat[:n] *= mask_pers[cid].flat
+            flops.append(self.model_trainer.count_inference_flops(w.state_dict()))
+            if mask_pers is None:
+                flops = flops * self.args.client_num_in_total      # identical for every client
+                break
+        self.stat_info["avg_inference_flops"] = sum(flops) / len(flops)
+        return self.stat_info["avg_inference_flops"]
+
     # ------------------------------------------------------------------- checkpointing
     def personal_slabs(self) -> Dict[int, ParamSlab]:
         return {c.client_idx: c.slab for c in self.client_list if c.slab is not None}

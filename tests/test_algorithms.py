@@ -63,6 +63,26 @@ def test_salientgrads_mask_density_and_masked_weights():
     assert float(api.mask.flat.sum()) == lay.numel_real(params_only=True)
 
 
+def test_orchestrator_helper_methods_of_the_reference_api():
+    """``_benefit_choose`` / ``average_weights`` / ``record_avg_inference_flops``: carried (uncalled) by the reference's orchestrator
+    (``sailentgrads_api.py:165-209,319-331``) and therefore part of the surface a user may call."""
+    ds, args, tr = _vol_setup(dense_ratio=0.5)
+    api = SalientGradsAPI(ds, "cpu", args, tr, quiet_logger())
+    assert api._benefit_choose(0, 1, 5, 5) == [0, 1, 2, 3, 4]
+    assert list(api._benefit_choose(0, 0, 5, 2, cs="ring")) == [4, 1]
+    active = np.array([1, 0, 1, 1, 1])
+    assert list(api._benefit_choose(0, 2, 5, 2, cs="full", active_ths_rnd=active)) == [0, 3, 4]
+    np.random.seed(0)
+    assert 3 not in api._benefit_choose(0, 3, 5, 2, cs="random")
+    a, b = api.w_global.clone(), api.w_global.clone()
+    b.flat.mul_(3.0)
+    torch.testing.assert_close(api.average_weights([a, b.state_dict()]).flat, 2.0 * a.flat)
+    mask = api.generate_global_mask_snip()
+    dense = api.record_avg_inference_flops(api.w_global)
+    sparse = api.record_avg_inference_flops(api.w_global, {c: mask for c in range(args.client_num_in_total)})
+    assert 0 < sparse < dense and api.stat_info["avg_inference_flops"] == sparse
+
+
 def test_salientgrads_stratified_and_ci_flag():
     ds, args, tr = _vol_setup(stratified_sampling=True, ci=1)
     api = SalientGradsAPI(ds, "cpu", args, tr, quiet_logger())
