@@ -73,3 +73,34 @@ def test_other_algorithms_cli_on_synthetic_cifar(tmp_path, algo):
             "--epochs", "1", "--comm_round", "1", "--device", "cpu", "--lr", "0.05", "--partition_method", "homo", "--synthetic_subjects", "240"] + _dirs(tmp_path)
     stat = main_others.main(argv)
     assert isinstance(stat, dict) and "round_time_s" in stat
+
+
+def test_reference_job_matrix_parses_with_our_entry_points(tmp_path):
+    """Every launcher of the reference (87 scripts, ``scripts/jobs/job_matrix.py``) maps to a command our argument parsers accept."""
+    import importlib.util
+    import sys
+    spec = importlib.util.spec_from_file_location("job_matrix", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                                                                             "scripts", "jobs", "job_matrix.py"))
+    jm = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(jm)
+    assert len(jm.JOBS) == 87 and len({r[0] for r in jm.JOBS}) == 87
+    assert {r[1] for r in jm.JOBS} == {"salientgrads", "fedavg", "dispfl", "ditto", "dpsgd", "fedfomo", "local", "subavg"}
+    for row in jm.JOBS:
+        cmd = jm.command(row)
+        assert cmd[:2] == [sys.executable, "-m"]
+        mod, flags = cmd[2], cmd[3:]
+        if mod.endswith("main_others"):
+            algo, flags = flags[0], flags[1:]
+            ns = main_others.add_args(argparse.ArgumentParser(), algo).parse_args(flags)
+        else:
+            ns = {"main_sailentgrads": main_sailentgrads, "main_fedavg": main_fedavg, "main_dispfl": main_dispfl}[mod.rsplit(".", 1)[1]] \
+                .add_args(argparse.ArgumentParser()).parse_args(flags)
+        assert ns.model == "resnet18" and ns.client_num_in_total == 100 and ns.seed == 2022 and ns.dataset in ("cifar10", "cifar100", "tiny")
+    row = jm.find("salientgradssparsitywith20iteration90sps")
+    f = jm.flags_of(row)
+    assert (f["dense_ratio"], f["itersnip_iteration"], f["batch_size"]) == ("0.1", "20", "16")
+    multi = jm.command(row, gpus=8)
+    assert "torch.distributed.run" in multi and "--nproc-per-node=8" in multi
+    assert "frac" not in jm.flags_of(jm.find("DisPFL/dispfljob"))          # that script leaves --frac to the default
+    jm.main(["--emit-slurm", str(tmp_path / "slurm"), "--algo", "subavg"])
+    assert len(os.listdir(tmp_path / "slurm")) == 15
