@@ -104,3 +104,12 @@ def test_reference_job_matrix_parses_with_our_entry_points(tmp_path):
     assert "frac" not in jm.flags_of(jm.find("DisPFL/dispfljob"))          # that script leaves --frac to the default
     jm.main(["--emit-slurm", str(tmp_path / "slurm"), "--algo", "subavg"])
     assert len(os.listdir(tmp_path / "slurm")) == 15
+
+
+@pytest.mark.parametrize("mod,extra", [(main_sailentgrads, ["--dense_ratio", "0.5"]), (main_fedavg, []), (main_dispfl, ["--dense_ratio", "0.5"])])
+def test_main_entry_points_also_take_image_datasets(tmp_path, mod, extra):
+    """The reference's job scripts run SalientGrads / FedAvg / DisPFL on CIFAR (its SalientGrads entry point then forces ABCD,
+    ``main_sailentgrads.py:272``; here the dataset flag is honoured)."""
+    stat = mod.main(["--model", "cnn_cifar10", "--dataset", "cifar10", "--client_num_in_total", "4", "--frac", "0.5", "--batch_size", "16",
+                     "--epochs", "1", "--comm_round", "1", "--device", "cpu", "--lr", "0.05", "--synthetic_subjects", "160"] + extra + _dirs(tmp_path))
+    assert "round_time_s" in stat and len(stat["round_time_s"]) >= 1
