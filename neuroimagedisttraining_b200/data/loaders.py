@@ -118,6 +118,12 @@ class TensorBatchLoader:
             xb = self.x[sel]
             yield (self.augment(xb, self._gen) if self.augment is not None else xb), self.y[sel]
 
+    def state(self):
+        return self._gen.get_state()
+
+    def set_state(self, s):
+        self._gen.set_state(s)
+
 
 def _abcd_tuple(store: VolumeStore, train: Sequence[np.ndarray], test: Sequence[np.ndarray], batch_size: int, seed: int):
     local_num, train_local, test_local = {}, {}, {}

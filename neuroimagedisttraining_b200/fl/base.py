@@ -219,13 +219,32 @@ class FedAPIBase:
     def personal_slabs(self) -> Dict[int, ParamSlab]:
         return {c.client_idx: c.slab for c in self.client_list if c.slab is not None}
 
+    def _loader_states(self) -> Dict[int, torch.Tensor]:
+        """Shuffle-generator state of every client's training loader, from the rank that iterates it (all ranks take part)."""
+        mine = {c.client_idx: c.local_training_data.state() for c in self.client_list
+                if self.dist.owns(c.client_idx) and hasattr(c.local_training_data, "state")}
+        if not self.dist.is_distributed:
+            return mine
+        import torch.distributed as dist
+        parts = [None] * self.dist.world_size
+        dist.all_gather_object(parts, mine)
+        return {k: v for part in parts for k, v in part.items()}
+
     def save(self, path: str, round_idx: int) -> None:
+        loaders = self._loader_states()
         if self.dist.is_main:
             save_checkpoint(path, round_idx, self.w_global, self.mask, self.args, self.stat_info,
-                            personal=self.personal_slabs() if getattr(self.args, "save_personal", False) else None)
+                            personal=self.personal_slabs() if getattr(self.args, "save_personal", False) else None, loaders=loaders)
 
     def resume(self, path: str) -> int:
-        ck = load_checkpoint(path, map_location=self.device)
+        """Continue after the checkpointed round.  On one rank the continuation is bit-identical to an uninterrupted run: the
+        loaders' shuffle streams and the python / numpy / torch RNG states come back too (with several ranks only rank 0's global
+        RNG state is in the file, so it is not restored; the loader streams are)."""
+        ck = load_checkpoint(path, map_location=self.device, restore_rng=not self.dist.is_distributed)
+        for cid, st in (ck.get("loaders") or {}).items():
+            loader = self.client_list[int(cid)].local_training_data
+            if hasattr(loader, "set_state"):
+                loader.set_state(st)
         self.w_global.load_state_dict(ck["state_dict"])
         if ck.get("mask") is not None:
             self.mask = self.model_trainer.mask_slab(ck["mask"])

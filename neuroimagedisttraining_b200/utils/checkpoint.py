@@ -1,6 +1,7 @@
 """Checkpoint / resume.  The reference has none on any live path; the format here is
 ``torch.save`` of ``{'round', 'state_dict' (reference keys, incl. BN buffers), 'mask'
-(param-name -> tensor), 'args', RNG states, 'stat_info', optional per-client state_dicts}``."""
+(param-name -> tensor), 'args', RNG states, the training loaders' shuffle-generator states, 'stat_info', optional per-client
+state_dicts}``."""
 from __future__ import annotations
 
 import os
@@ -11,7 +12,8 @@ import numpy as np
 import torch
 
 
-def save_checkpoint(path: str, round_idx: int, w_global, mask, args, stat_info, personal: Optional[Dict] = None) -> None:
+def save_checkpoint(path: str, round_idx: int, w_global, mask, args, stat_info, personal: Optional[Dict] = None,
+                    loaders: Optional[Dict] = None) -> None:
     os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
     ck = {
         "round": int(round_idx),
@@ -20,6 +22,7 @@ def save_checkpoint(path: str, round_idx: int, w_global, mask, args, stat_info, 
         "args": dict(vars(args)) if hasattr(args, "__dict__") else args,
         "rng": {"python": random.getstate(), "numpy": np.random.get_state(), "torch": torch.get_rng_state()},
         "stat_info": {k: v for k, v in stat_info.items() if k != "phase_time_s"},
+        "loaders": ({int(c): st.cpu().clone() for c, st in loaders.items()} if loaders else None),
         "personal": ({int(c): {k: v.cpu() for k, v in s.state_dict().items()} for c, s in personal.items()} if personal else None),
     }
     tmp = path + ".tmp"

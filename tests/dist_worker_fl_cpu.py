@@ -14,7 +14,7 @@ from neuroimagedisttraining_b200.models import create_model
 from neuroimagedisttraining_b200.parallel import DistContext, init_distributed, shutdown
 
 
-def run(ctx):
+def run(ctx, ck=None):
     torch.manual_seed(0)
     logger = logging.getLogger("w"); logger.setLevel(logging.ERROR)
     store = SyntheticABCD(40, (32, 32, 32), n_sites=4, seed=1, site_sizes=[10, 10, 10, 10])
@@ -24,6 +24,8 @@ def run(ctx):
     ds = load_partition_data_abcd(store, client_number=4, batch_size=8)
     model = create_model("tiny3DCNN", 1, (32, 32, 32))
     tr = SlabTrainer(model, args, logger, device="cpu", store=store)
+    if ck is not None:                 # every rank contributes the shuffle state of the loaders it iterates
+        args.checkpoint_every, args.checkpoint_path = 1, ck
     api = SalientGradsAPI(ds, "cpu", args, tr, logger, dist=ctx)
     st = api.train()
     return api.w_global.flat.clone(), api.mask.flat.clone(), st
@@ -32,12 +34,17 @@ def run(ctx):
 def main():
     torch.set_num_threads(2)
     ctx = init_distributed(device="cpu")
-    w2, m2, st2 = run(ctx)
+    import tempfile
+    ck = os.path.join(tempfile.gettempdir(), f"nidt_ck_{os.environ.get('MASTER_PORT', '0')}.pt")
+    w2, m2, st2 = run(ctx, ck)
     w1, m1, st1 = run(DistContext(device=torch.device("cpu")))     # same thing, single process
     ok = torch.equal(m1, m2) and torch.allclose(w1, w2, rtol=1e-5, atol=1e-6)
     ok = ok and abs(st1["global_test_acc"][-1] - st2["global_test_acc"][-1]) < 1e-9
     ok = ok and st1["sum_comm_params"] == st2["sum_comm_params"]
     if ctx.rank == 0:
+        saved = torch.load(ck, weights_only=False)
+        ok = ok and sorted(saved["loaders"]) == [0, 1, 2, 3] and saved["round"] == 1
+        os.remove(ck)
         print(f"RESULT ok={ok} maxdiff={(w1 - w2).abs().max().item():.3e} comm={st1['sum_comm_params']},{st2['sum_comm_params']}")
     shutdown()
     sys.exit(0 if ok else 1)

@@ -204,3 +204,35 @@ def test_checkpoint_resume_roundtrip(tmp_path):
     ck = torch.load(args.checkpoint_path, weights_only=False)
     ref_keys = list(create_model("tiny3DCNN", 1, (32, 32, 32)).state_dict().keys())
     assert list(ck["state_dict"].keys()) == ref_keys and ck["state_dict"]["features.1.num_batches_tracked"].dtype == torch.int64
+
+
+def test_resumed_run_is_bit_identical_to_an_uninterrupted_one(tmp_path):
+    """2 rounds + checkpoint + resume for 2 more == 4 rounds in one go: global model, mask and accuracy series, with dropout active
+    (global torch RNG) and shuffled loaders (private generators) -- both streams are part of the checkpoint."""
+    from neuroimagedisttraining_b200.models import Tiny3DCNN
+
+    store = SyntheticABCD(40, (32, 32, 32), n_sites=4, seed=1, site_sizes=[10] * 4)
+
+    def build(comm_round, ck=None):
+        args = make_args(client_num_in_total=4, batch_size=4, epochs=1, comm_round=comm_round, lr=0.01, dense_ratio=0.5)
+        ds = load_partition_data_abcd(store, client_number=4, batch_size=4)
+        torch.manual_seed(5)
+        model = Tiny3DCNN(1, in_shape=(32, 32, 32), p_drop=0.3)
+        tr = SlabTrainer(model, args, quiet_logger(), device="cpu", store=store)
+        args.checkpoint_every, args.checkpoint_path, args.save_personal, args.final_finetune = 1, ck, True, False
+        return SalientGradsAPI(ds, "cpu", args, tr, quiet_logger())
+
+    torch.manual_seed(9); np.random.seed(9)
+    full = build(4, str(tmp_path / "full.pt"))
+    full.train()
+    torch.manual_seed(9); np.random.seed(9)
+    first = build(2, str(tmp_path / "part.pt"))
+    first.train()
+    torch.manual_seed(12345); np.random.seed(777)        # a fresh process would start from unrelated RNG states
+    second = build(4, str(tmp_path / "part.pt"))
+    assert second.resume(str(tmp_path / "part.pt")) == 2
+    second.train()
+    assert torch.equal(second.mask.flat, full.mask.flat)
+    assert torch.equal(second.w_global.flat, full.w_global.flat)
+    assert second.stat_info["global_test_acc"] == full.stat_info["global_test_acc"]
+    assert second.stat_info["person_test_acc"] == full.stat_info["person_test_acc"]
