@@ -21,6 +21,8 @@ def main(argv=None):
              "-g" if args.global_test else "", "-RSM" if args.static else "-DST"]
     ctx, device, logger, dataset, trainer = setup(args, "DisPFL", extra)
     api = DisPFLAPI(dataset, device, args, trainer, logger, dist=ctx)
+    if args.resume:
+        api.resume(args.resume)
     api.train()
     return finish(api, args, logger, ctx)
 

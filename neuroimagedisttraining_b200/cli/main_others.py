@@ -42,6 +42,8 @@ def main(argv=None):
         kw["agg_mode"] = args.agg
         args.final_finetune = False
     api = ALGOS[algo](dataset, device, args, trainer, logger, **kw)
+    if args.resume:
+        api.resume(args.resume)
     api.train()
     return finish(api, args, logger, ctx)
 

@@ -27,6 +27,7 @@ from .trainer import SlabTrainer
 
 class FedAPIBase:
     NAME = "fed"
+    PERSONAL_IN_CHECKPOINT = False     # algorithms whose result IS the per-client models set this
 
     def __init__(self, dataset, device, args, model_trainer: SlabTrainer, logger, dist: Optional[DistContext] = None,
                  agg_mode: str = "auto"):
@@ -57,6 +58,7 @@ class FedAPIBase:
         self.start_round = 0
         self.mask: Optional[ParamSlab] = None
         self.w_init: Optional[ParamSlab] = None   # personalised model of a client that never trained
+        self._resumed_extra: dict = {}
 
     # ------------------------------------------------------------------------- set-up
     def _setup_clients(self, train_data_local_num_dict, train_data_local_dict, test_data_local_dict, model_trainer):
@@ -233,8 +235,20 @@ class FedAPIBase:
     def save(self, path: str, round_idx: int) -> None:
         loaders = self._loader_states()
         if self.dist.is_main:
+            keep_personal = self.PERSONAL_IN_CHECKPOINT or getattr(self.args, "save_personal", False)
+            extra = dict(self.extra_state())
+            if self.w_init is not None:
+                extra["w_init"] = {k: v.cpu() for k, v in self.w_init.state_dict().items()}
             save_checkpoint(path, round_idx, self.w_global, self.mask, self.args, self.stat_info,
-                            personal=self.personal_slabs() if getattr(self.args, "save_personal", False) else None, loaders=loaders)
+                            personal=self.personal_slabs() if keep_personal else None, loaders=loaders, extra=extra)
+
+    def extra_state(self) -> dict:
+        """Algorithm-specific state a resumed run needs beyond the global model, the mask and the personal models (CPU tensors /
+        plain python).  Counterpart: :meth:`load_extra_state`."""
+        return {}
+
+    def load_extra_state(self, state: dict) -> None:
+        self._resumed_extra = state
 
     def resume(self, path: str) -> int:
         """Continue after the checkpointed round.  On one rank the continuation is bit-identical to an uninterrupted run: the
@@ -253,6 +267,11 @@ class FedAPIBase:
         for cid, sd in (ck.get("personal") or {}).items():
             c = self.client_list[int(cid)]
             c.ensure_slab(self.w_global).load_state_dict(sd)
+        extra = dict(ck.get("extra") or {})
+        if "w_init" in extra:
+            self.w_init = self.model_trainer.engine.new_slab()
+            self.w_init.load_state_dict(extra.pop("w_init"))
+        self.load_extra_state(extra)
         self.start_round = int(ck["round"]) + 1
         self.logger.info("resumed from %s at round %d" % (path, self.start_round))
         return self.start_round

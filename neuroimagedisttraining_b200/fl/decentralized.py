@@ -56,10 +56,23 @@ class _PerClientModels(LocalAPI):
     def _init_models(self) -> List[ParamSlab]:
         if self.dist.is_distributed:
             raise NotImplementedError(f"{self.NAME} mixes arbitrary clients' models and runs on one rank")
-        self.w_init = self.w_global.clone()
+        if self.w_init is None:
+            self.w_init = self.w_global.clone()
         for c in self.client_list:
-            c.slab = self.w_global.clone()
+            if c.slab is None:                      # a resumed run brings the personal models along
+                c.slab = self.w_global.clone()
         return [c.slab for c in self.client_list]
+
+    def _slabs_to_state(self, slabs: Sequence[ParamSlab]) -> list:
+        return [s.flat.detach().cpu().clone() for s in slabs]
+
+    def _slabs_from_state(self, flats, like: ParamSlab) -> List[ParamSlab]:
+        out = []
+        for f in flats:
+            s = like.zeros_like()
+            s.flat.copy_(f.to(s.flat.device))
+            out.append(s)
+        return out
 
     def _mean_of(self, slabs: Sequence[ParamSlab], out: ParamSlab) -> ParamSlab:
         w = 1.0 / len(slabs)
@@ -118,6 +131,12 @@ class DPSGDAPI(_PerClientModels):
 class DisPFLAPI(_PerClientModels):
     NAME = "dispfl"
 
+    def extra_state(self) -> dict:
+        if not hasattr(self, "masks_per_client"):
+            return {}
+        return {"dispfl_masks": self._slabs_to_state(self.masks_per_client), "dispfl_shared": self._slabs_to_state(self._shared_masks),
+                "dispfl_dist": self._dist_locals.tolist(), "dispfl_w_spa": list(self._w_spa)}
+
     # ------------------------------------------------------------------ mask evolution
     def fire_mask(self, mask: ParamSlab, weights: ParamSlab, round_idx: int):
         """Magnitude prune per tensor with the cosine-annealed drop ratio (``DisPFL/client.py:71-82``)."""
@@ -175,23 +194,30 @@ class DisPFLAPI(_PerClientModels):
         def make(sparse):
             sp = tr.calculate_sparsities(names, distribution="uniform" if getattr(args, "uniform", False) else "ERK", sparse=sparse)
             return tr.init_masks(names, sp)
-        if not getattr(args, "different_initial", False):
-            base = make(args.dense_ratio)
-            masks = [base.clone() for _ in range(n)]
-        elif not getattr(args, "diff_spa", False):
-            masks = [make(args.dense_ratio) for _ in range(n)]
-        else:
-            levels = [0.2, 0.4, 0.6, 0.8, 1.0]
-            masks = []
-            for i in range(n):
-                masks.append(make(levels[i % 5]))
-                w_spa[i] = levels[i % 5]
         P = self.layout.param_numel
-        for i in range(n):
-            models[i].flat[:P] *= masks[i].flat
-        shared = [m.clone() for m in masks]
-        dist_locals = np.zeros((n, n))
-        self.masks_per_client = masks
+        if self._resumed_extra.get("dispfl_masks") is not None:     # continue with the evolved masks (no RNG draw for fresh ones)
+            st = self._resumed_extra
+            like = ParamSlab(self.layout, device=self.device, params_only=True)
+            masks = self._slabs_from_state(st["dispfl_masks"], like)
+            shared = self._slabs_from_state(st["dispfl_shared"], like)
+            dist_locals, w_spa = np.asarray(st["dispfl_dist"]), list(st["dispfl_w_spa"])
+        else:
+            if not getattr(args, "different_initial", False):
+                base = make(args.dense_ratio)
+                masks = [base.clone() for _ in range(n)]
+            elif not getattr(args, "diff_spa", False):
+                masks = [make(args.dense_ratio) for _ in range(n)]
+            else:
+                levels = [0.2, 0.4, 0.6, 0.8, 1.0]
+                masks = []
+                for i in range(n):
+                    masks.append(make(levels[i % 5]))
+                    w_spa[i] = levels[i % 5]
+            shared = [m.clone() for m in masks]
+            dist_locals = np.zeros((n, n))
+            for i in range(n):          # (not on resume: a model keeps its just-pruned weights until its next SGD step)
+                models[i].flat[:P] *= masks[i].flat
+        self.masks_per_client, self._shared_masks, self._dist_locals, self._w_spa = masks, shared, dist_locals, w_spa
         for round_idx in range(self.start_round, args.comm_round):
             t0 = time.time()
             self.logger.info("################Communication round : {}".format(round_idx))
@@ -258,6 +284,11 @@ class DisPFLAPI(_PerClientModels):
 class FedFomoAPI(_PerClientModels):
     NAME = "fedfomo"
 
+    def extra_state(self) -> dict:
+        if not hasattr(self, "_fomo_state"):
+            return {}
+        return {"fomo_weights": self._fomo_state[0].tolist(), "fomo_p_choose": self._fomo_state[1].tolist()}
+
     def _val_loss(self, cid: int, slab: ParamSlab) -> float:
         client = self.client_list[cid]
         data = self.val_data_local_dict[cid] if self.val_data_local_dict is not None else client.local_test_data
@@ -283,6 +314,9 @@ class FedFomoAPI(_PerClientModels):
         models = self._init_models()
         weights_locals = np.full((n, n), 1.0 / n)
         p_choose = np.ones((n, n))
+        if self._resumed_extra.get("fomo_weights") is not None:
+            weights_locals, p_choose = np.asarray(self._resumed_extra["fomo_weights"]), np.asarray(self._resumed_extra["fomo_p_choose"])
+        self._fomo_state = (weights_locals, p_choose)
         trained = self.w_global.clone()
         for round_idx in range(self.start_round, args.comm_round):
             t0 = time.time()

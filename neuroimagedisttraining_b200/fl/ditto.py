@@ -15,7 +15,8 @@ class DittoAPI(LocalAPI):
 
     def train(self):
         args = self.args
-        self.w_init = self.w_global.clone()
+        if self.w_init is None:
+            self.w_init = self.w_global.clone()
         lamda = float(getattr(args, "lamda", 0.5))
         local_epochs = int(getattr(args, "local_epochs", 3))
         for round_idx in range(self.start_round, args.comm_round):
@@ -30,7 +31,8 @@ class DittoAPI(LocalAPI):
                     self.logger.info('@@@@@@@@@@@@@@@@ Training Client CM({}): {}'.format(round_idx, cid))
                     if not hasattr(client, "global_copy"):
                         client.global_copy = self.w_global.clone()
-                        client.slab = self.w_init.clone()         # personal model starts at the initial weights
+                        if client.slab is None:                   # (a resumed run already has the personal model)
+                            client.slab = self.w_init.clone()     # personal model starts at the initial weights
                     # (1) the client's contribution to the global model: plain local training from w_global
                     tr = self.model_trainer
                     client.global_copy.copy_(self.w_global)

@@ -13,10 +13,12 @@ from .base import FedAPIBase
 
 class LocalAPI(FedAPIBase):
     NAME = "local"
+    PERSONAL_IN_CHECKPOINT = True
 
     def train(self):
         args = self.args
-        self.w_init = self.w_global.clone()
+        if self.w_init is None:
+            self.w_init = self.w_global.clone()
         for c in self.client_list:
             c.ensure_slab(self.w_global)
         for round_idx in range(self.start_round, args.comm_round):

@@ -58,6 +58,9 @@ def print_pruning(weights: ParamSlab) -> Tuple[float, int]:
 class SubAvgAPI(LocalAPI):
     NAME = "subavg"
 
+    def extra_state(self) -> dict:
+        return {"subavg_masks": [m.flat.detach().cpu().clone() for m in self.mask_pers]} if hasattr(self, "mask_pers") else {}
+
     def _client_train(self, client, mask: ParamSlab, round_idx: int):
         args, tr = self.args, self.model_trainer
         slab = client.ensure_slab(self.w_global)
@@ -103,8 +106,12 @@ class SubAvgAPI(LocalAPI):
     def train(self):
         args = self.args
         n = args.client_num_in_total
-        self.w_init = self.w_global.clone()
+        if self.w_init is None:
+            self.w_init = self.w_global.clone()
         mask_pers = [make_mask_slab(self.layout, self.device) for _ in range(n)]
+        if self._resumed_extra.get("subavg_masks") is not None:
+            for m, f in zip(mask_pers, self._resumed_extra["subavg_masks"]):
+                m.flat.copy_(f.to(m.flat.device))
         self.mask_pers = mask_pers
         if self.dist.is_distributed:
             raise NotImplementedError("Sub-FedAvg keeps per-client masks on one rank")

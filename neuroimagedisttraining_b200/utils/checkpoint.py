@@ -13,7 +13,7 @@ import torch
 
 
 def save_checkpoint(path: str, round_idx: int, w_global, mask, args, stat_info, personal: Optional[Dict] = None,
-                    loaders: Optional[Dict] = None) -> None:
+                    loaders: Optional[Dict] = None, extra: Optional[Dict] = None) -> None:
     os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
     ck = {
         "round": int(round_idx),
@@ -23,6 +23,7 @@ def save_checkpoint(path: str, round_idx: int, w_global, mask, args, stat_info, 
         "rng": {"python": random.getstate(), "numpy": np.random.get_state(), "torch": torch.get_rng_state()},
         "stat_info": {k: v for k, v in stat_info.items() if k != "phase_time_s"},
         "loaders": ({int(c): st.cpu().clone() for c, st in loaders.items()} if loaders else None),
+        "extra": extra or None,
         "personal": ({int(c): {k: v.cpu() for k, v in s.state_dict().items()} for c, s in personal.items()} if personal else None),
     }
     tmp = path + ".tmp"

@@ -236,3 +236,56 @@ def test_resumed_run_is_bit_identical_to_an_uninterrupted_one(tmp_path):
     assert torch.equal(second.w_global.flat, full.w_global.flat)
     assert second.stat_info["global_test_acc"] == full.stat_info["global_test_acc"]
     assert second.stat_info["person_test_acc"] == full.stat_info["person_test_acc"]
+
+
+@pytest.mark.parametrize("API,extra", [(LocalAPI, {}), (DittoAPI, dict(lamda=0.5, local_epochs=1)), (DPSGDAPI, dict(cs="random")),
+                                       (FedFomoAPI, {}), (SubAvgAPI, dict(each_prune_ratio=0.2, dist_thresh=1e-4, acc_thresh=-1.0, dense_ratio=0.3)),
+                                       (DisPFLAPI, dict(dense_ratio=0.5, different_initial=True, cs="random", active=0.8))])
+def test_per_client_algorithms_resume_bit_identically(tmp_path, API, extra):
+    """Personal models, the initial model, per-client masks (DisPFL, Sub-FedAvg) and FedFomo's mixing weights travel in the
+    checkpoint: 2 rounds + resume + 2 rounds equals 4 rounds, bit for bit, for every algorithm that keeps per-client state."""
+    import random
+
+    def build(comm_round, ck):
+        ds, args, tr = _img_setup(n_clients=4, val=(API is FedFomoAPI), frac=0.5, **extra)
+        args.comm_round, args.client_num_per_round, args.epochs = comm_round, 2, 1
+        args.checkpoint_every, args.checkpoint_path, args.final_finetune = 1, ck, False
+        api = API(ds, "cpu", args, tr, quiet_logger())
+        api.record_information = lambda *a, **k: None
+        return api
+
+    def seed(v):
+        random.seed(v); np.random.seed(v); torch.manual_seed(v)
+
+    seed(3)
+    full = build(4, str(tmp_path / "full.pt"))
+    full.train()
+    class Killed(Exception):
+        pass
+
+    seed(3)
+    first = build(4, str(tmp_path / "part.pt"))          # same job (schedules depend on comm_round), killed after round 1's checkpoint
+    orig = first._maybe_checkpoint
+
+    def checkpoint_then_die(r):
+        orig(r)
+        if r == 1:
+            raise Killed
+    first._maybe_checkpoint = checkpoint_then_die
+    with pytest.raises(Killed):
+        first.train()
+    seed(999)
+    second = build(4, str(tmp_path / "part.pt"))
+    assert second.resume(str(tmp_path / "part.pt")) == 2
+    second.train()
+    assert torch.equal(second.w_global.flat, full.w_global.flat)
+    for a, b in zip(second.client_list, full.client_list):
+        assert (a.slab is None) == (b.slab is None)
+        if a.slab is not None:
+            assert torch.equal(a.slab.flat, b.slab.flat), a.client_idx
+    for key in ("test_acc", "person_test_acc", "old_mask_test_acc", "new_mask_test_acc", "global_test_acc"):
+        assert [float(v) for v in second.stat_info.get(key, [])] == [float(v) for v in full.stat_info.get(key, [])], key
+    if API is DisPFLAPI:
+        assert all(torch.equal(x.flat, y.flat) for x, y in zip(second.masks_per_client, full.masks_per_client))
+    if API is SubAvgAPI:
+        assert all(torch.equal(x.flat, y.flat) for x, y in zip(second.mask_pers, full.mask_pers))
