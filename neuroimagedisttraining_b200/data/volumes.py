@@ -136,7 +136,7 @@ class HDF5VolumeStore(VolumeStore):
     def __init__(self, volumes_path: str, labels_path: Optional[str] = None, scale: Optional[float] = None):
         try:
             import h5py  # type: ignore
-        except ImportError as e:  # pragma: no cover - h5py is absent in the build image
+        except ImportError as e:
             raise ImportError("HDF5VolumeStore needs h5py; use SyntheticABCD or InMemoryVolumeStore instead") from e
         self._f = h5py.File(volumes_path, "r")
         self._X = self._f["X"]
@@ -150,9 +150,11 @@ class HDF5VolumeStore(VolumeStore):
         elif not self._is_u8:
             self.scale = 1.0 / 255.0
 
-    def fetch(self, indices, out=None):  # pragma: no cover
-        idx = np.sort(np.asarray(indices).astype(np.int64))
-        xb = self._X[idx]
+    def fetch(self, indices, out=None):
+        """Rows in the order requested.  HDF5 fancy indexing wants increasing, unique indices: read sorted, then un-permute."""
+        idx = np.asarray(indices).astype(np.int64)
+        uniq, inverse = np.unique(idx, return_inverse=True)
+        xb = np.asarray(self._X[uniq])[inverse]
         if not self._is_u8:
             xb = np.clip(np.rint(xb * 255.0), 0, 255).astype(np.uint8)
         x = torch.from_numpy(xb)

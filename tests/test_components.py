@@ -234,3 +234,42 @@ def test_nifti_reader_roundtrip_scaling_and_byte_order(tmp_path):
         paths.append(str(tmp_path / f"s{i}.nii.gz"))
     store = P.build_store_from_nifti(paths, [0, 1, 0, 1], ["b", "a", "b", "a"])
     assert store.volumes.shape == (4, 6, 7, 6) and store.volumes.dtype == torch.uint8 and list(store.sites) == [1, 0, 1, 0]
+
+
+def test_hdf5_volume_store_against_a_stand_in_h5py(monkeypatch):
+    """h5py is not in this image; a dict-backed stand-in with h5py's indexing rules (increasing unique indices only) exercises the
+    reader: volumes in one file, labels / sites in another (the reference's two files), rows returned in the requested order."""
+    import sys
+    import types
+    from neuroimagedisttraining_b200.data import HDF5VolumeStore
+    from neuroimagedisttraining_b200.data.loaders import load_partition_data_abcd
+
+    class DS:
+        def __init__(self, a):
+            self.a, self.shape, self.dtype = a, a.shape, a.dtype
+
+        def __getitem__(self, k):
+            if isinstance(k, tuple) and k == ():
+                return self.a
+            k = np.asarray(k)
+            if k.ndim == 1 and (np.diff(k) <= 0).any():
+                raise TypeError("Indexing elements must be in increasing order")
+            return self.a[k]
+
+    rng = np.random.RandomState(0)
+    files = {"x.h5": {"X": DS(rng.randint(0, 256, size=(12, 4, 5, 3)).astype(np.uint8))},
+             "l.h5": {"y": DS((rng.rand(12) > 0.5).astype(np.float64)), "site": DS(np.repeat(np.arange(3), 4))}}
+    monkeypatch.setitem(sys.modules, "h5py", types.SimpleNamespace(File=lambda path, mode="r": files[path]))
+    store = HDF5VolumeStore("x.h5", "l.h5")
+    assert store.shape == (4, 5, 3) and store.labels.dtype == np.float32 and list(store.sites[:5]) == [0, 0, 0, 0, 1]
+    x, y = store.fetch([7, 2, 2, 11])
+    assert torch.equal(x, torch.from_numpy(files["x.h5"]["X"].a[[7, 2, 2, 11]])) and list(y) == list(store.labels[[7, 2, 2, 11]])
+    out = torch.zeros(6, 4, 5, 3, dtype=torch.uint8)
+    x2, _ = store.fetch([5, 0], out=out)
+    assert x2.data_ptr() == out.data_ptr() and torch.equal(out[1], torch.from_numpy(files["x.h5"]["X"].a[0]))
+    ds = load_partition_data_abcd(store, batch_size=2)
+    assert len(ds[5]) == 3 and sum(ds[4].values()) == 3 * 4 - 0 - 0       # 4 per site, int(4 * 0.2) = 0 test samples each
+    files["f.h5"] = {"X": DS(rng.rand(3, 2, 2, 2).astype(np.float32)), "y": DS(np.zeros(3))}      # float volumes are quantised on the fly
+    fs = HDF5VolumeStore("f.h5")
+    xf, _ = fs.fetch([2, 0])
+    assert xf.dtype == torch.uint8 and torch.equal(xf[0], torch.from_numpy(np.rint(files["f.h5"]["X"].a[2] * 255).astype(np.uint8)))
