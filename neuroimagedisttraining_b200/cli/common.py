@@ -65,6 +65,8 @@ def add_common_args(p: argparse.ArgumentParser, *, model="3DCNN", dataset="ABCD"
     g.add_argument("--in_shape", default="121,145,121", help="volume shape D,H,W")
     g.add_argument("--augment", action="store_true", help="image datasets: random crop (padding 4) + horizontal flip on training batches, as the reference's transforms")
     g.add_argument("--cutout", type=int, default=0, help="with --augment: side of the Cutout square (the reference keeps Cutout(16) commented out)")
+    g.add_argument("--labels_file", default=None, help="ABCD: HDF5 file with y / site when they are not in --data_dir (the reference keeps "
+                                                       "volumes in alldatain8bitsnormalized.h5 and labels in dataset_all_labels_site.h5)")
     g.add_argument("--rescale", action="store_true", help="ABCD: cut the site-ordered data into client_num_in_total equal shards")
     g.add_argument("--correct_eval_loss", action="store_true", help="evaluate BCEWithLogits(logit) instead of the reference's BCEWithLogits(sigmoid(logit))")
     return p
@@ -129,7 +131,7 @@ def setup(args, prefix: str, extra_identity: Optional[list] = None, loss_kind: O
     store = None
     if args.dataset == "ABCD":
         if args.data_dir:
-            store = HDF5VolumeStore(args.data_dir)
+            store = HDF5VolumeStore(args.data_dir, args.labels_file)
         else:
             n = args.synthetic_subjects or 20 * args.client_num_in_total
             n_sites = args.client_num_in_total if not args.rescale else min(21, args.client_num_in_total)
