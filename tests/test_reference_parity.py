@@ -196,3 +196,44 @@ def test_dispfl_matches_reference_cpu(active, static):
         assert len(api.stat_info[key]) == len(rapi.stat_info[key]) == 3
         for a, b in zip(api.stat_info[key], rapi.stat_info[key]):
             assert abs(float(a) - float(b)) < 1e-6, key
+
+
+@pytest.mark.slow
+def test_salientgrads_two_rounds_with_partial_participation_matches_reference_cpu():
+    """Two rounds, 3 site clients of which 2 are sampled per round (``np.random.seed(round)`` sampler), lr decay by round, the
+    personalised models of clients that did / did not train, and both accuracy series incl. the closing ``round = -1`` evaluation."""
+    store, train, test = _setup(n_clients=3, per_site=5)
+    args = make_args(client_num_in_total=3, frac=0.67, batch_size=2, epochs=1, comm_round=2, dense_ratio=0.3, lr=0.02)
+    assert args.client_num_per_round == 2
+    torch.manual_seed(77)
+    init = AlexNet3D_Dropout(num_classes=1).state_dict()
+    ref_api, ref_model, _ = ref_harness.build_reference_api("salientgrads", store, train, test, args, "cpu", shuffle=False,
+                                                           model_state=init, p_drop=0.0)
+    captured = []
+    orig_agg, orig_sample = ref_api._aggregate, ref_api._client_sampling
+    ref_api._aggregate = lambda w: (captured.append({k: v.clone() for k, v in orig_agg(w).items()}), captured[-1])[1]
+    sampled = []
+    ref_api._client_sampling = lambda r, n, k: (sampled.append(sorted(int(c) for c in orig_sample(r, n, k))), orig_sample(r, n, k))[1]
+    ref_api.train()
+
+    # Round by round, re-synchronising our global model to the reference's after each comparison: a batch-2 BatchNorm network
+    # amplifies the 1e-6 round-off of one round a hundredfold in the next (ReLU / max-pool decisions flip), which would hide what
+    # is pinned here -- the per-round semantics (sampling, lr decay, masking, aggregation weights, personal models).
+    ours = _ours("salientgrads", store, train, test, args, init)
+    ours_sampled = []
+    orig_ours = ours._client_sampling
+    ours._client_sampling = lambda r, n, k: (ours_sampled.append(sorted(int(c) for c in orig_ours(r, n, k))), orig_ours(r, n, k))[1]
+    ours.mask = ours.generate_global_mask_snip()
+    ours.w_init = ours.w_global.clone()
+    for r in range(2):
+        ours.run_round(r, mask=ours.mask)
+        sd = ours.w_global.state_dict(cast_int=False)
+        for k, v in captured[r].items():
+            torch.testing.assert_close(sd[k].float(), v.float(), rtol=2e-4, atol=2e-5, msg=lambda m: f"round {r} {k}: {m}")
+        ours.w_global.load_state_dict(captured[r])
+    ours._test_on_all_clients(ours.w_global, ours.personal_slabs(), -1)
+    assert ours_sampled == sampled and len(sampled) == 2 and all(len(s) == 2 for s in sampled)
+    for key in ("global_test_acc", "person_test_acc"):
+        assert len(ours.stat_info[key]) == len(ref_api.stat_info[key]) == 3
+        for a, b in zip(ours.stat_info[key], ref_api.stat_info[key]):
+            assert abs(float(a) - float(b)) < 1e-6, key
