@@ -237,3 +237,34 @@ def test_salientgrads_two_rounds_with_partial_participation_matches_reference_cp
         assert len(ours.stat_info[key]) == len(ref_api.stat_info[key]) == 3
         for a, b in zip(ours.stat_info[key], ref_api.stat_info[key]):
             assert abs(float(a) - float(b)) < 1e-6, key
+
+
+@pytest.mark.slow
+def test_fedavg_final_finetune_round_matches_reference_cpu():
+    """FedAvg's closing fine-tune (``fedavg_api.py:79-88``): every client trains once more from the final global model with
+    ``round = -1`` (lr * decay^-1) and is evaluated with that personal model.  Our global model is set to the reference's before the
+    fine-tune so that only this step's semantics are compared (see the two-round SalientGrads test on error amplification)."""
+    import copy
+    store, train, test = _setup(n_clients=2, per_site=5)
+    args = make_args(client_num_in_total=2, batch_size=2, epochs=1, comm_round=1, lr=0.01, lr_decay=0.9)
+    torch.manual_seed(5)
+    init = AlexNet3D_Dropout(num_classes=1).state_dict()
+    ref_api, _, _ = ref_harness.build_reference_api("fedavg", store, train, test, args, "cpu", shuffle=False, model_state=init, p_drop=0.0)
+    cap = {}
+    orig_test = ref_api._test_on_all_clients
+    ref_api._test_on_all_clients = lambda wg, wp, r: (cap.__setitem__(r, (copy.deepcopy(wg), copy.deepcopy(wp))), orig_test(wg, wp, r))[1]
+    ref_api.train()
+    assert sorted(cap) == [-1, 0]
+    ours = _ours("fedavg", store, train, test, args, init)
+    args.final_finetune = False
+    ours.train()
+    ours.w_global.load_state_dict(cap[-1][0])
+    ours.finetune_round()
+    for c in range(2):
+        sd = ours.client_list[c].slab.state_dict(cast_int=False)
+        for k, v in cap[-1][1][c].items():
+            torch.testing.assert_close(sd[k].float(), v.float(), rtol=2e-4, atol=2e-5, msg=lambda m: f"personal[{c}] {k}: {m}")
+    assert len(ours.stat_info["person_test_acc"]) == len(ref_api.stat_info["person_test_acc"]) == 2
+    for key in ("global_test_acc", "person_test_acc"):
+        for a, b in zip(ours.stat_info[key], ref_api.stat_info[key]):
+            assert abs(float(a) - float(b)) < 1e-6, key
