@@ -1,0 +1,314 @@
+"""A small reader / writer for the plain subset of HDF5 that ``h5py.File(...).create_dataset(name, data=array)`` produces with its
+default settings: version-0 superblock, old-style groups (symbol table: v1 B-tree + local heap), version-1 object headers, and
+numeric datasets stored contiguously (or compactly) without filters.  That is the layout of the reference's data files
+(``Preprocess_ABCD.ipynb`` cell 30: ``dataset_all_labels_site.h5``; ``alldatain8bitsnormalized.h5`` with ``X`` / ``y``).
+
+It exists because ``h5py`` is not available everywhere this framework runs; :class:`~.volumes.HDF5VolumeStore` and
+``preprocess.save_hdf5`` use ``h5py`` when it is installed and this module otherwise.  Datasets are memory-mapped, so indexing a
+24 GB volume file reads only the requested rows.  Anything outside the subset (chunked or filtered datasets, new-style groups
+from ``libver='latest'``, compound / string types) raises :class:`UnsupportedHDF5` with the reason, not garbage.
+
+NOTE: no HDF5 library exists in the image this was developed in, so the reader has only been exercised against files from the
+writer below, which follows the published file-format specification (HDF5 File Format Specification, version 1.1 structures).
+"""
+from __future__ import annotations
+
+import struct
+from typing import Dict, Iterator, List, Optional, Tuple
+
+import numpy as np
+
+SIGNATURE = b"\x89HDF\r\n\x1a\n"
+UNDEF = 0xFFFFFFFFFFFFFFFF
+MSG_NIL, MSG_DATASPACE, MSG_DATATYPE, MSG_FILL, MSG_LAYOUT, MSG_CONTINUATION, MSG_SYMBOL_TABLE = 0x0, 0x1, 0x3, 0x5, 0x8, 0x10, 0x11
+
+
+class UnsupportedHDF5(ValueError):
+    pass
+
+
+# ------------------------------------------------------------------------------------------------ datatype message
+def _encode_dtype(dt: np.dtype) -> bytes:
+    dt = np.dtype(dt)
+    if dt.byteorder == ">":
+        raise UnsupportedHDF5("the writer stores little-endian data only")
+    if dt.kind in "iu":
+        bits0 = 0x08 if dt.kind == "i" else 0x00
+        return struct.pack("<BBBBI", 0x10, bits0, 0, 0, dt.itemsize) + struct.pack("<HH", 0, 8 * dt.itemsize)
+    if dt.kind == "f" and dt.itemsize in (4, 8):
+        sign, eloc, esz, msz, bias = (31, 23, 8, 23, 127) if dt.itemsize == 4 else (63, 52, 11, 52, 1023)
+        return struct.pack("<BBBBI", 0x11, 0x20, sign, 0, dt.itemsize) + struct.pack("<HHBBBBI", 0, 8 * dt.itemsize, eloc, esz, 0, msz, bias)
+    raise UnsupportedHDF5(f"dtype {dt} is outside the supported subset (integers, float32, float64)")
+
+
+def _decode_dtype(body: bytes) -> np.dtype:
+    cls, size = body[0] & 0x0F, struct.unpack_from("<I", body, 4)[0]
+    order = ">" if body[1] & 0x01 else "<"
+    if cls == 0:
+        kind = "i" if body[1] & 0x08 else "u"
+        if size not in (1, 2, 4, 8):
+            raise UnsupportedHDF5(f"{size}-byte integers")
+        return np.dtype(f"{order}{kind}{size}")
+    if cls == 1:
+        if size not in (2, 4, 8):
+            raise UnsupportedHDF5(f"{size}-byte floats")
+        return np.dtype(f"{order}f{size}")
+    names = {2: "time", 3: "string", 4: "bitfield", 5: "opaque", 6: "compound", 7: "reference", 8: "enum", 9: "variable-length", 10: "array"}
+    raise UnsupportedHDF5(f"datatype class {cls} ({names.get(cls, '?')}) is outside the supported subset (integers and floats)")
+
+
+# ------------------------------------------------------------------------------------------------------- reader
+class Dataset:
+    """Read-only, numpy-like view of one dataset (``shape``, ``dtype``, ``ds[()]``, ``ds[i]``, ``ds[a:b]``, ``ds[sorted_indices]``)."""
+
+    def __init__(self, name: str, array: np.ndarray):
+        self.name, self._a = name, array
+        self.shape, self.dtype = array.shape, array.dtype
+
+    def __len__(self):
+        return self.shape[0]
+
+    def __getitem__(self, key):
+        if isinstance(key, tuple) and key == ():
+            return np.array(self._a)
+        if isinstance(key, (list, np.ndarray)):
+            k = np.asarray(key)
+            if k.ndim == 1 and k.dtype != bool and (np.diff(k) <= 0).any():
+                raise TypeError("Indexing elements must be in increasing order")        # h5py's rule, kept so code stays portable
+        return np.array(self._a[key])
+
+    def __array__(self, dtype=None, copy=None):
+        return np.asarray(self._a, dtype=dtype)
+
+
+class File:
+    """``File(path)[name]`` -> :class:`Dataset`; also ``keys()``, ``in``, iteration, context manager.  Read-only."""
+
+    def __init__(self, path: str, mode: str = "r"):
+        if mode != "r":
+            raise UnsupportedHDF5("hdf5_mini.File opens files read-only; use write_file() to create one")
+        self.path = path
+        self._f = open(path, "rb")
+        self._datasets: Dict[str, Dataset] = {}
+        self._parse()
+
+    # -- low-level helpers
+    def _read(self, off: int, n: int) -> bytes:
+        self._f.seek(off)
+        b = self._f.read(n)
+        if len(b) != n:
+            raise UnsupportedHDF5(f"truncated file: wanted {n} bytes at offset {off}")
+        return b
+
+    def _parse(self) -> None:
+        head = self._read(0, 8)
+        if head != SIGNATURE:
+            raise UnsupportedHDF5("not an HDF5 file (signature; user blocks are not supported)")
+        sb_version = self._read(8, 1)[0]
+        if sb_version not in (0, 1):
+            raise UnsupportedHDF5(f"superblock version {sb_version} (written with libver='latest'?); only the default old-style layout is supported")
+        size_off, size_len = self._read(13, 1)[0], self._read(14, 1)[0]
+        if (size_off, size_len) != (8, 8):
+            raise UnsupportedHDF5(f"{size_off}-byte offsets / {size_len}-byte lengths")
+        p = 24 + (4 if sb_version == 1 else 0)            # v1 adds indexed-storage K + reserved
+        base, _free, _eof, _drv = struct.unpack("<4Q", self._read(p, 32))
+        self._base = base
+        _name_off, root_header, _cache, _res = struct.unpack("<QQII", self._read(p + 32, 24))
+        btree, heap = self._symbol_table_of(root_header)
+        heap_data = self._heap_data(heap)
+        for name, header in self._walk_group(btree, heap_data):
+            ds = self._dataset(name, header)
+            if ds is not None:
+                self._datasets[name] = ds
+
+    def _messages(self, header_addr: int) -> List[Tuple[int, bytes]]:
+        a = self._base + header_addr
+        version, _, nmsgs, _refs, size = struct.unpack("<BBHII", self._read(a, 12))
+        if version != 1:
+            raise UnsupportedHDF5(f"object header version {version}; only version-1 headers are supported")
+        blocks, out = [(a + 16, size)], []
+        while blocks and len(out) < nmsgs:
+            off, length = blocks.pop(0)
+            raw, q = self._read(off, length), 0
+            while q + 8 <= length and len(out) < nmsgs:
+                mtype, msize, _flags = struct.unpack_from("<HHB", raw, q)
+                body = raw[q + 8:q + 8 + msize]
+                if mtype == MSG_CONTINUATION:
+                    c_off, c_len = struct.unpack_from("<QQ", body)
+                    blocks.append((self._base + c_off, c_len))
+                out.append((mtype, body))
+                q += 8 + msize
+        return out
+
+    def _symbol_table_of(self, header_addr: int) -> Tuple[int, int]:
+        for mtype, body in self._messages(header_addr):
+            if mtype == MSG_SYMBOL_TABLE:
+                return struct.unpack_from("<QQ", body)
+        raise UnsupportedHDF5("group without a symbol table (new-style group); only old-style groups are supported")
+
+    def _heap_data(self, heap_addr: int) -> bytes:
+        a = self._base + heap_addr
+        if self._read(a, 4) != b"HEAP":
+            raise UnsupportedHDF5("bad local heap signature")
+        seg_size, _free, seg_addr = struct.unpack("<QQQ", self._read(a + 8, 24))
+        return self._read(self._base + seg_addr, seg_size)
+
+    def _walk_group(self, node_addr: int, heap: bytes) -> Iterator[Tuple[str, int]]:
+        a = self._base + node_addr
+        sig = self._read(a, 4)
+        if sig == b"TREE":
+            node_type, _level, used = struct.unpack("<BBH", self._read(a + 4, 4))
+            if node_type != 0:
+                raise UnsupportedHDF5("unexpected B-tree node type in a group")
+            body = self._read(a + 24, 8 + 16 * used)      # key0, (child, key) * used
+            for i in range(used):
+                child = struct.unpack_from("<Q", body, 8 + 16 * i)[0]
+                yield from self._walk_group(child, heap)
+        elif sig == b"SNOD":
+            count = struct.unpack("<H", self._read(a + 6, 2))[0]
+            for i in range(count):
+                name_off, header = struct.unpack("<QQ", self._read(a + 8 + 40 * i, 16))
+                end = heap.index(b"\x00", name_off)
+                yield heap[name_off:end].decode(), header
+        else:
+            raise UnsupportedHDF5(f"unexpected group node signature {sig!r}")
+
+    def _dataset(self, name: str, header_addr: int) -> Optional[Dataset]:
+        shape = dtype = layout = None
+        for mtype, body in self._messages(header_addr):
+            if mtype == MSG_SYMBOL_TABLE:
+                return None                                # a sub-group: not part of the flat files this reads
+            if mtype == MSG_DATASPACE:
+                version, rank = body[0], body[1]
+                if version == 1:
+                    shape = struct.unpack_from(f"<{rank}Q", body, 8) if rank else ()
+                elif version == 2:
+                    shape = struct.unpack_from(f"<{rank}Q", body, 4) if rank else ()
+                else:
+                    raise UnsupportedHDF5(f"dataspace message version {version}")
+            elif mtype == MSG_DATATYPE:
+                dtype = _decode_dtype(body)
+            elif mtype == MSG_LAYOUT:
+                layout = body
+            elif mtype == 0x0B:
+                raise UnsupportedHDF5(f"dataset {name!r} uses a filter pipeline (compression); only unfiltered data is supported")
+        if shape is None or dtype is None or layout is None:
+            return None
+        version, cls = layout[0], layout[1]
+        if version != 3:
+            raise UnsupportedHDF5(f"dataset {name!r}: data layout message version {version}")
+        n = int(np.prod(shape, dtype=np.int64)) if len(shape) else 1
+        if cls == 1:
+            addr, _size = struct.unpack_from("<QQ", layout, 2)
+            if addr == UNDEF or n == 0:
+                arr = np.zeros(shape, dtype)
+            else:
+                arr = np.memmap(self.path, dtype=dtype, mode="r", offset=self._base + addr, shape=tuple(int(s) for s in shape), order="C")
+        elif cls == 0:
+            size = struct.unpack_from("<H", layout, 2)[0]
+            arr = np.frombuffer(layout[4:4 + size], dtype=dtype, count=n).reshape(shape)
+        else:
+            raise UnsupportedHDF5(f"dataset {name!r} is chunked; rewrite it contiguously (h5py: create_dataset(name, data=a) without chunks / compression)")
+        return Dataset(name, arr)
+
+    # -- mapping face
+    def keys(self):
+        return self._datasets.keys()
+
+    def __iter__(self):
+        return iter(self._datasets)
+
+    def __contains__(self, name):
+        return name in self._datasets
+
+    def __getitem__(self, name) -> Dataset:
+        return self._datasets[name]
+
+    def close(self):
+        self._f.close()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
+# ------------------------------------------------------------------------------------------------------- writer
+def _pad8(b: bytes) -> bytes:
+    return b + b"\x00" * (-len(b) % 8)
+
+
+def _message(mtype: int, body: bytes, flags: int = 0) -> bytes:
+    body = _pad8(body)
+    return struct.pack("<HHBBBB", mtype, len(body), flags, 0, 0, 0) + body
+
+
+def _object_header(messages: List[bytes]) -> bytes:
+    data = b"".join(messages)
+    return struct.pack("<BBHII", 1, 0, len(messages), 1, len(data)) + b"\x00" * 4 + data
+
+
+def write_file(path: str, datasets: Dict[str, np.ndarray], leaf_k: int = 4, internal_k: int = 16) -> None:
+    """Writes a flat file (root group with one contiguous dataset per entry) in the layout described in the module docstring.
+    Up to ``2 * leaf_k`` datasets (one symbol-table node) -- the data files of this project hold two or three."""
+    names = sorted(datasets)
+    if not 0 < len(names) <= 2 * leaf_k:
+        raise UnsupportedHDF5(f"write_file handles 1..{2 * leaf_k} datasets per file")
+    arrays = {n: np.asarray(datasets[n], order="C") for n in names}
+    for n, a in arrays.items():
+        if a.dtype.byteorder == ">":
+            arrays[n] = a.astype(a.dtype.newbyteorder("<"))
+    # local heap data segment: "" at offset 0, then the names, each NUL-terminated and 8-byte aligned
+    heap_data, name_off = bytearray(8), {}
+    for n in names:
+        name_off[n] = len(heap_data)
+        heap_data += _pad8(n.encode() + b"\x00")
+    free_off = len(heap_data)
+    heap_data += struct.pack("<QQ", 1, 16) + b"\x00" * 16          # one free block: (next = 1 "none", size), then room to grow
+    heap_data = bytes(heap_data)
+
+    sb_size, root_hdr_size = 96, 16 + 8 + 16
+    btree_size = 24 + (2 * internal_k + 1) * 8 + 2 * internal_k * 8
+    snod_size = 8 + 2 * leaf_k * 40
+    a_root = sb_size
+    a_btree = a_root + root_hdr_size
+    a_heap = a_btree + btree_size
+    a_heap_data = a_heap + 32
+    a_snod = a_heap_data + len(heap_data)
+    cursor = a_snod + snod_size
+    headers, a_header, a_data = {}, {}, {}
+    for n in names:                                                   # object headers first, raw data after them
+        a = arrays[n]
+        dataspace = struct.pack("<BBBBI", 1, a.ndim, 0, 0, 0) + b"".join(struct.pack("<Q", s) for s in a.shape)
+        fill = struct.pack("<BBBB", 2, 2, 2, 0)                       # version 2, late allocation, fill never written, undefined
+        headers[n] = [_message(MSG_DATASPACE, dataspace), _message(MSG_DATATYPE, _encode_dtype(a.dtype), flags=1), _message(MSG_FILL, fill), None]
+        a_header[n] = cursor
+        cursor += 16 + sum(len(m) for m in headers[n][:3]) + 8 + 24
+    for n in names:
+        cursor += -cursor % 8
+        a_data[n] = cursor
+        cursor += arrays[n].nbytes
+    eof = cursor
+
+    with open(path, "wb") as f:
+        f.write(SIGNATURE + struct.pack("<BBBBBBBB", 0, 0, 0, 0, 0, 8, 8, 0) + struct.pack("<HHI", leaf_k, internal_k, 0))
+        f.write(struct.pack("<QQQQ", 0, UNDEF, eof, UNDEF))
+        f.write(struct.pack("<QQII", 0, a_root, 1, 0) + struct.pack("<QQ", a_btree, a_heap))      # root entry caches B-tree / heap
+        f.write(_object_header([_message(MSG_SYMBOL_TABLE, struct.pack("<QQ", a_btree, a_heap))]))
+        node = b"TREE" + struct.pack("<BBHQQ", 0, 0, 1, UNDEF, UNDEF) + struct.pack("<QQQ", 0, a_snod, name_off[names[-1]])
+        f.write(node + b"\x00" * (btree_size - len(node)))
+        f.write(b"HEAP" + struct.pack("<BBBBQQQ", 0, 0, 0, 0, len(heap_data), free_off, a_heap_data))
+        f.write(heap_data)
+        snod = b"SNOD" + struct.pack("<BBH", 1, 0, len(names))
+        for n in names:
+            snod += struct.pack("<QQII", name_off[n], a_header[n], 0, 0) + b"\x00" * 16
+        f.write(snod + b"\x00" * (snod_size - len(snod)))
+        for n in names:
+            assert f.tell() == a_header[n]
+            layout = struct.pack("<BBQQ", 3, 1, a_data[n] if arrays[n].nbytes else UNDEF, arrays[n].nbytes)
+            f.write(_object_header(headers[n][:3] + [_message(MSG_LAYOUT, layout)]))
+        for n in names:
+            f.write(b"\x00" * (a_data[n] - f.tell()))
+            f.write(arrays[n].tobytes(order="C"))
+        assert f.tell() == eof

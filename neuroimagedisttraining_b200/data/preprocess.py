@@ -2,8 +2,8 @@
 121x145x121 voxels -> brain mask where the group mean exceeds 0.2 -> per-subject min-max normalisation -> 8-bit quantisation
 -> one container with ``X`` (uint8 volumes), ``y`` (``female``), ``site`` (label-encoded ``abcd_site``).
 
-NIfTI files are read with ``nibabel`` when present, else with the built-in single-file NIfTI-1 reader; the reference's HDF5 layout
-needs ``h5py`` (not in this image); the numerical steps are plain numpy and the ``.npz`` container works everywhere."""
+NIfTI files are read with ``nibabel`` when present, else with the built-in single-file NIfTI-1 reader; the reference's HDF5 container is
+read / written with ``h5py`` when present, else with :mod:`.hdf5_mini` (plain contiguous files); the numerical steps are plain numpy and the ``.npz`` container works everywhere."""
 from __future__ import annotations
 
 from typing import Iterable, Optional, Sequence, Tuple
@@ -144,11 +144,15 @@ def load_npz(path: str, pin: bool = False) -> InMemoryVolumeStore:
     return InMemoryVolumeStore(torch.from_numpy(d["X"]), d["y"], d["site"], pin=pin)
 
 
-def save_hdf5(store: InMemoryVolumeStore, path: str) -> None:  # pragma: no cover - optional dependency
+def save_hdf5(store: InMemoryVolumeStore, path: str) -> None:
+    """``X`` / ``y`` / ``site`` in one HDF5 file, the container the reference's loaders read (``ABCD/data_loader.py:105-141``).
+    With ``h5py``: one chunk per volume, LZF-compressed.  Without: the built-in writer (contiguous, uncompressed)."""
     try:
         import h5py  # type: ignore
-    except ImportError as e:
-        raise ImportError("writing the reference's HDF5 layout needs h5py") from e
+    except ImportError:
+        from .hdf5_mini import write_file
+        write_file(path, {"X": store.volumes.numpy(), "y": np.asarray(store.labels), "site": np.asarray(store.sites)})
+        return
     with h5py.File(path, "w") as f:
         f.create_dataset("X", data=store.volumes.numpy(), chunks=(1,) + tuple(store.shape), compression="lzf")
         f.create_dataset("y", data=store.labels)

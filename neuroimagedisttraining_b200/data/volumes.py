@@ -131,13 +131,14 @@ class SyntheticABCD(VolumeStore):
 class HDF5VolumeStore(VolumeStore):
     """Reader for the reference's files: ``X`` volumes in one HDF5 (``alldatain8bitsnormalized.h5``),
     ``y``/``site`` in another (``dataset_all_labels_site.h5``; ``ABCD/data_loader.py:105-141``).
-    The file is opened once, not per batch.  Needs ``h5py`` (not in this image -> clear error)."""
+    The file is opened once, not per batch.  Uses ``h5py`` when installed, else the built-in reader for plain contiguous files
+    (:mod:`.hdf5_mini`)."""
 
     def __init__(self, volumes_path: str, labels_path: Optional[str] = None, scale: Optional[float] = None):
         try:
             import h5py  # type: ignore
-        except ImportError as e:
-            raise ImportError("HDF5VolumeStore needs h5py; use SyntheticABCD or InMemoryVolumeStore instead") from e
+        except ImportError:
+            from . import hdf5_mini as h5py     # plain contiguous files (what the reference's notebook writes) without the library
         self._f = h5py.File(volumes_path, "r")
         self._X = self._f["X"]
         lab = h5py.File(labels_path, "r") if labels_path else self._f

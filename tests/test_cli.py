@@ -49,6 +49,8 @@ def test_fedavg_cli_config1_with_checkpoint_and_resume(tmp_path):
     assert line["global_test_acc"] == [float(a) for a in stat["global_test_acc"]] and "phase_time_s" in line
     ckpt = torch.load(ck, weights_only=False)
     assert ckpt["round"] == 1 and any(k.startswith("features.0.") for k in ckpt["state_dict"]) and "stat_info" in ckpt
+    from neuroimagedisttraining_b200.models import Tiny3DCNN
+    Tiny3DCNN(1, in_shape=(32, 32, 32)).load_state_dict(ckpt["state_dict"], strict=True)      # a plain torch state_dict of the module
     # one more round from the checkpoint: starts at round 2, does not repeat rounds 0-1
     stat2 = main_fedavg.main(TINY[:-6] + ["--epochs", "1", "--comm_round", "3", "--device", "cpu", "--frac", "1.0"] + _dirs(tmp_path)
                              + ["--resume", ck, "--lr", "0.01"])

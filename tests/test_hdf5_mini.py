@@ -1,0 +1,84 @@
+"""Built-in HDF5 subset (``data/hdf5_mini.py``): round trips, memory-mapped row access, the volume store and the SalientGrads entry
+point on a file, and clear errors for what lies outside the subset.  (No HDF5 library is available here: reader and writer are
+checked against each other and against byte-level expectations from the format specification.)"""
+import struct
+
+import numpy as np
+import pytest
+import torch
+
+from neuroimagedisttraining_b200.data import HDF5VolumeStore, SyntheticABCD
+from neuroimagedisttraining_b200.data import hdf5_mini as H
+from neuroimagedisttraining_b200.data import preprocess as P
+from neuroimagedisttraining_b200.data.volumes import InMemoryVolumeStore
+
+
+def test_round_trip_dtypes_shapes_and_row_access(tmp_path):
+    rng = np.random.RandomState(0)
+    data = {"X": rng.randint(0, 256, size=(9, 4, 5, 3)).astype(np.uint8), "y": (rng.rand(9) > 0.5).astype(np.float64),
+            "site": np.repeat(np.arange(3), 3).astype(np.int64), "f32": rng.rand(2, 3).astype(np.float32), "i16": np.arange(-3, 4, dtype=np.int16),
+            "scalar": np.float64(2.5), "empty": np.zeros((0, 4), np.float32)}
+    path = str(tmp_path / "t.h5")
+    H.write_file(path, data)
+    raw = open(path, "rb").read()
+    assert raw[:8] == b"\x89HDF\r\n\x1a\n" and raw[8] == 0 and raw[13:15] == b"\x08\x08"           # signature, superblock v0, 8-byte offsets
+    assert struct.unpack_from("<Q", raw, 40)[0] == len(raw)                                           # end-of-file address
+    assert raw.count(b"TREE") >= 1 and raw.count(b"SNOD") >= 1 and raw.count(b"HEAP") >= 1
+    with H.File(path) as f:
+        assert sorted(f.keys()) == sorted(data) and "X" in f and "nope" not in f
+        for k, v in data.items():
+            got = f[k][()]
+            assert got.dtype == np.asarray(v).dtype and got.shape == np.asarray(v).shape and np.array_equal(got, v), k
+        X = f["X"]
+        assert X.shape == (9, 4, 5, 3) and len(X) == 9 and X.dtype == np.uint8
+        assert np.array_equal(X[[1, 4, 8]], data["X"][[1, 4, 8]]) and np.array_equal(X[2:5], data["X"][2:5]) and np.array_equal(X[7], data["X"][7])
+        with pytest.raises(TypeError, match="increasing order"):
+            X[[4, 1]]
+        assert isinstance(X._a, np.memmap)                                                            # rows are read on demand
+
+
+def test_volume_store_and_cli_on_a_file(tmp_path):
+    src = SyntheticABCD(24, (32, 32, 32), n_sites=3, seed=2, site_sizes=[8, 8, 8])
+    mem = InMemoryVolumeStore(src.fetch(np.arange(24))[0], src.labels, src.sites)
+    path = str(tmp_path / "abcd.h5")
+    P.save_hdf5(mem, path)
+    store = HDF5VolumeStore(path)
+    assert store.shape == (32, 32, 32) and np.array_equal(store.labels, src.labels) and np.array_equal(store.sites, src.sites)
+    x, y = store.fetch([20, 3, 11])
+    want, _ = src.fetch([20, 3, 11])
+    assert torch.equal(x, want) and list(y) == list(src.labels[[20, 3, 11]])
+    # volumes and labels in separate files, as the reference keeps them
+    H.write_file(str(tmp_path / "vol.h5"), {"X": mem.volumes.numpy()})
+    H.write_file(str(tmp_path / "lab.h5"), {"y": src.labels.astype(np.float64), "site": src.sites})
+    two = HDF5VolumeStore(str(tmp_path / "vol.h5"), str(tmp_path / "lab.h5"))
+    assert torch.equal(two.fetch([5])[0], src.fetch([5])[0]) and np.array_equal(two.sites, src.sites)
+    from neuroimagedisttraining_b200.cli import main_sailentgrads
+    stat = main_sailentgrads.main(["--model", "tiny3DCNN", "--in_shape", "32,32,32", "--data_dir", str(tmp_path / "vol.h5"), "--labels_file",
+                                   str(tmp_path / "lab.h5"), "--client_num_in_total", "3", "--batch_size", "4", "--epochs", "1", "--comm_round", "1",
+                                   "--device", "cpu", "--log_dir", str(tmp_path / "LOG")])
+    assert len(stat["global_test_acc"]) == 2
+
+
+def test_features_outside_the_subset_are_refused_with_a_reason(tmp_path):
+    path = str(tmp_path / "t.h5")
+    H.write_file(path, {"X": np.arange(12, dtype=np.int32).reshape(3, 4)})
+    raw = bytearray(open(path, "rb").read())
+    with pytest.raises(H.UnsupportedHDF5, match="not an HDF5 file"):
+        (tmp_path / "junk.h5").write_bytes(b"junk" * 40)
+        H.File(str(tmp_path / "junk.h5"))
+    v2 = bytearray(raw); v2[8] = 2
+    (tmp_path / "v2.h5").write_bytes(bytes(v2))
+    with pytest.raises(H.UnsupportedHDF5, match="superblock version 2"):
+        H.File(str(tmp_path / "v2.h5"))
+    # flip the layout class of the dataset from contiguous (1) to chunked (2): version 3 layout message = type 8, body starts 03 01
+    i = bytes(raw).index(struct.pack("<HH", 8, 24)) + 8
+    assert raw[i] == 3 and raw[i + 1] == 1
+    ch = bytearray(raw); ch[i + 1] = 2
+    (tmp_path / "chunked.h5").write_bytes(bytes(ch))
+    with pytest.raises(H.UnsupportedHDF5, match="chunked"):
+        H.File(str(tmp_path / "chunked.h5"))
+    (tmp_path / "short.h5").write_bytes(bytes(raw[:200]))
+    with pytest.raises(H.UnsupportedHDF5, match="truncated"):
+        H.File(str(tmp_path / "short.h5"))
+    with pytest.raises(H.UnsupportedHDF5, match="subset"):
+        H.write_file(path, {"s": np.array(["a", "b"])})
