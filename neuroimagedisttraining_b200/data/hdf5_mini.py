@@ -249,9 +249,11 @@ def _object_header(messages: List[bytes]) -> bytes:
     return struct.pack("<BBHII", 1, 0, len(messages), 1, len(data)) + b"\x00" * 4 + data
 
 
-def write_file(path: str, datasets: Dict[str, np.ndarray], leaf_k: int = 4, internal_k: int = 16) -> None:
+def write_file(path: str, datasets: Dict[str, np.ndarray], leaf_k: int = 4, internal_k: int = 16, split_headers: bool = False) -> None:
     """Writes a flat file (root group with one contiguous dataset per entry) in the layout described in the module docstring.
-    Up to ``2 * leaf_k`` datasets (one symbol-table node) -- the data files of this project hold two or three."""
+    Up to ``2 * leaf_k`` datasets (one symbol-table node) -- the data files of this project hold two or three.
+    ``split_headers`` moves every dataset's layout message into an object-header continuation block, the form headers take in
+    files that were modified after creation (exercises that reader path)."""
     names = sorted(datasets)
     if not 0 < len(names) <= 2 * leaf_k:
         raise UnsupportedHDF5(f"write_file handles 1..{2 * leaf_k} datasets per file")
@@ -284,7 +286,12 @@ def write_file(path: str, datasets: Dict[str, np.ndarray], leaf_k: int = 4, inte
         fill = struct.pack("<BBBB", 2, 2, 2, 0)                       # version 2, late allocation, fill never written, undefined
         headers[n] = [_message(MSG_DATASPACE, dataspace), _message(MSG_DATATYPE, _encode_dtype(a.dtype), flags=1), _message(MSG_FILL, fill), None]
         a_header[n] = cursor
-        cursor += 16 + sum(len(m) for m in headers[n][:3]) + 8 + 24
+        cursor += 16 + sum(len(m) for m in headers[n][:3]) + (8 + 16 if split_headers else 8 + 24)
+    a_cont = {}
+    if split_headers:
+        for n in names:
+            a_cont[n] = cursor
+            cursor += 8 + 24
     for n in names:
         cursor += -cursor % 8
         a_data[n] = cursor
@@ -306,8 +313,17 @@ def write_file(path: str, datasets: Dict[str, np.ndarray], leaf_k: int = 4, inte
         f.write(snod + b"\x00" * (snod_size - len(snod)))
         for n in names:
             assert f.tell() == a_header[n]
-            layout = struct.pack("<BBQQ", 3, 1, a_data[n] if arrays[n].nbytes else UNDEF, arrays[n].nbytes)
-            f.write(_object_header(headers[n][:3] + [_message(MSG_LAYOUT, layout)]))
+            layout = _message(MSG_LAYOUT, struct.pack("<BBQQ", 3, 1, a_data[n] if arrays[n].nbytes else UNDEF, arrays[n].nbytes))
+            if split_headers:
+                first = headers[n][:3] + [_message(MSG_CONTINUATION, struct.pack("<QQ", a_cont[n], len(layout)))]
+                data = b"".join(first)
+                f.write(struct.pack("<BBHII", 1, 0, len(first) + 1, 1, len(data)) + b"\x00" * 4 + data)     # message count spans both blocks
+            else:
+                f.write(_object_header(headers[n][:3] + [layout]))
+        if split_headers:
+            for n in names:
+                assert f.tell() == a_cont[n]
+                f.write(_message(MSG_LAYOUT, struct.pack("<BBQQ", 3, 1, a_data[n] if arrays[n].nbytes else UNDEF, arrays[n].nbytes)))
         for n in names:
             f.write(b"\x00" * (a_data[n] - f.tell()))
             f.write(arrays[n].tobytes(order="C"))

@@ -35,6 +35,9 @@ def test_round_trip_dtypes_shapes_and_row_access(tmp_path):
         with pytest.raises(TypeError, match="increasing order"):
             X[[4, 1]]
         assert isinstance(X._a, np.memmap)                                                            # rows are read on demand
+    H.write_file(path, data, split_headers=True)            # layout messages in object-header continuation blocks
+    with H.File(path) as f:
+        assert all(np.array_equal(f[k][()], v) for k, v in data.items())
 
 
 def test_volume_store_and_cli_on_a_file(tmp_path):
