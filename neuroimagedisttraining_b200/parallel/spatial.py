@@ -309,3 +309,35 @@ def halo_bytes(layers: Sequence[Tuple[int, int, int, int]], in_shape: Tuple[int,
         out.append(extra * h * w * cin * batch * elem_bytes)
         d, h, w = do, out_depth(h, k, s, p), out_depth(w, k, s, p)
     return out
+
+
+class SpatialParallelModel(nn.Module):
+    """A ``features`` + head model (the AlexNet3D family, Tiny3DCNN) trained by ALL ranks on the SAME batch, each rank holding a depth
+    slab of the activations.  Parameters are replicated; after ``loss.backward()`` call :meth:`reduce_gradients` and step the
+    optimizer on every rank -- the replicas stay identical because every rank then applies the same gradients (with dropout in
+    the head, seed torch identically on all ranks so that they draw the same masks).
+
+        spm = SpatialParallelModel(model)              # model.features: nn.Sequential, head: model.classifier / model.regressor
+        loss = criterion(spm(x_full_batch), y); loss.backward(); spm.reduce_gradients(); optimizer.step()
+    """
+
+    def __init__(self, model: nn.Module, group=None):
+        super().__init__()
+        self.model = model
+        self.group = group
+        self.slab_features = SlabParallelFeatures(model.features, group)
+        head = getattr(model, "classifier", None) or getattr(model, "regressor", None)
+        if head is None:
+            raise ValueError("expected a model with `features` and a `classifier` / `regressor` head")
+        self.head = head
+
+    def forward(self, x_full: torch.Tensor) -> torch.Tensor:
+        world, rank = self.slab_features._world_rank()
+        xs, part = scatter_depth(x_full, world, rank)
+        f = self.slab_features(xs, part)
+        return self.head(f.flatten(1))
+
+    def reduce_gradients(self) -> None:
+        """Feature-extractor gradients are per-slab shares -> summed over ranks.  The head saw the full feature map on every rank, so
+        its gradients are already complete and identical."""
+        allreduce_gradients(list(self.model.features.parameters()), self.group)

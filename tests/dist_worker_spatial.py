@@ -10,7 +10,8 @@ import torch.distributed as dist
 import torch.nn as nn
 
 from neuroimagedisttraining_b200.models import Tiny3DCNN
-from neuroimagedisttraining_b200.parallel.spatial import SlabParallelFeatures, allreduce_gradients, halo_bytes, scatter_depth
+from neuroimagedisttraining_b200.parallel.spatial import (SlabParallelFeatures, SpatialParallelModel, allreduce_gradients, halo_bytes,
+                                                          scatter_depth)
 
 
 def resnet_like():
@@ -65,6 +66,25 @@ def main():
     ok = ok and good
     if not good:
         print(rank, errs, flush=True)
+    # three SGD steps of the whole model in spatial-parallel mode == three single-process steps (weights and BN statistics)
+    torch.manual_seed(3)
+    ref_model = Tiny3DCNN(1, in_shape=(32, 30, 29), p_drop=0.0).double()
+    sp_model = copy.deepcopy(ref_model)
+    spm = SpatialParallelModel(sp_model)
+    opt_r = torch.optim.SGD(ref_model.parameters(), lr=0.05, momentum=0.9, weight_decay=5e-4)
+    opt_s = torch.optim.SGD(sp_model.parameters(), lr=0.05, momentum=0.9, weight_decay=5e-4)
+    crit = nn.BCEWithLogitsLoss()
+    for step in range(3):
+        xb = torch.randn(4, 1, 32, 30, 29, dtype=torch.float64)
+        yb = (torch.rand(4, 1) > 0.5).double()
+        opt_r.zero_grad(); crit(ref_model(xb), yb).backward(); opt_r.step()
+        opt_s.zero_grad(); crit(spm(xb), yb).backward(); spm.reduce_gradients(); opt_s.step()
+    worst = max(float((a.double() - b.double()).abs().max()) for a, b in zip(sp_model.state_dict().values(), ref_model.state_dict().values()))
+    t = torch.tensor([worst], dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        print(f"spatial-parallel training: world={world} worst abs err after 3 steps {float(t):.3e}", flush=True)
+    ok = ok and float(t) < 1e-9
     hb = halo_bytes([(1, 5, 2, 0), (64, 3, 3, 0), (64, 3, 1, 0)], (121, 145, 121), 16, max(world, 2))
     ok = ok and len(hb) == 3 and hb[0] > 0
     t = torch.tensor([1.0 if ok else 0.0])
