@@ -53,8 +53,10 @@ class _PerClientModels(LocalAPI):
     """Base for algorithms that keep one model per client and mix them.  Decentralised mixing reads other clients'
     models, so these run single-rank (the reference simulates them on one GPU as well)."""
 
+    MULTI_RANK = False      # DisPFL sets this: its clients train independently and the owners publish their results once per round
+
     def _init_models(self) -> List[ParamSlab]:
-        if self.dist.is_distributed:
+        if self.dist.is_distributed and not self.MULTI_RANK:
             raise NotImplementedError(f"{self.NAME} mixes arbitrary clients' models and runs on one rank")
         if self.w_init is None:
             self.w_init = self.w_global.clone()
@@ -129,7 +131,12 @@ class DPSGDAPI(_PerClientModels):
 
 
 class DisPFLAPI(_PerClientModels):
+    """Several ranks: every rank keeps all clients' models and masks (tens of MB) and replays the cheap bookkeeping of all clients
+    -- so the numpy streams that pick active clients and neighbours stay aligned with the single-process run -- but trains,
+    screens and prunes only the clients it owns; at the end of a round every owner broadcasts its clients' new model and mask.
+    Identical to one process when masks regrow by gradient and the model has no dropout (those draw from torch's per-rank stream)."""
     NAME = "dispfl"
+    MULTI_RANK = True
 
     def extra_state(self) -> dict:
         if not hasattr(self, "masks_per_client"):
@@ -247,11 +254,13 @@ class DisPFLAPI(_PerClientModels):
                         start = last[cid]
                     shared[cid].copy_(masks[cid])
                     client = self.client_list[cid]
-                    before.append(client.local_test(start, True))
+                    if not self.dist.owns(cid):
+                        continue                                  # its owner trains it; the result arrives with the round's broadcast
+                    before.append((cid, client.local_test(start, True)))
                     # local training with the personal mask applied after every step
                     _, flops, comm = client.train(start, round_idx, masks[cid], apply_mask=True)
                     m_after = client.local_test(client.slab, True)
-                    after.append(m_after)
+                    after.append((cid, m_after))
                     self.logger.info("test acc on this client after {} / {} : {:.2f}".format(m_after['test_correct'], m_after['test_total'], m_after['test_acc']))
                     if not getattr(args, "static", False):
                         grad = None
@@ -262,6 +271,10 @@ class DisPFLAPI(_PerClientModels):
                         masks[cid] = self.regrow_mask(fired, removed, grad)
                     self.stat_info["sum_training_flops"] += flops
                     self._add_comm_params(comm)
+            if self.dist.is_distributed:                        # owners publish what they trained / pruned this round
+                for cid in range(n):
+                    self.dist.broadcast(models[cid].flat, src=self.dist.owner(cid))
+                    self.dist.broadcast(masks[cid].flat, src=self.dist.owner(cid))
             self._log_round(after, round_idx, "old_mask_test_acc")
             self._log_round(before, round_idx, "new_mask_test_acc")
             self.stat_info["round_time_s"].append(time.time() - t0)
@@ -273,8 +286,16 @@ class DisPFLAPI(_PerClientModels):
         return self.finalize_stats()
 
     def _log_round(self, results, round_idx, key):
-        acc = sum(r["test_correct"] / max(r["test_total"], 1) for r in results) / max(len(results), 1)
-        loss = sum(r["test_loss"] / max(r["test_total"], 1) for r in results) / max(len(results), 1)
+        """``results``: (client, metrics) pairs of the clients this rank evaluated; means are over all clients of all ranks."""
+        n = self.args.client_num_in_total
+        acc, loss, seen = np.zeros(n), np.zeros(n), np.zeros(n)
+        for cid, r in results:
+            acc[cid] = r["test_correct"] / max(r["test_total"], 1)
+            loss[cid] = r["test_loss"] / max(r["test_total"], 1)
+            seen[cid] = 1.0
+        acc, loss, seen = self._reduce_metric(acc, loss, seen)
+        denom = max(float(seen.sum()), 1.0)
+        acc, loss = float(acc.sum() / denom), float(loss.sum() / denom)
         self.logger.info({'test_acc': acc, 'test_loss': loss})
         self.stat_info[key].append(acc)
         if key == "old_mask_test_acc":
