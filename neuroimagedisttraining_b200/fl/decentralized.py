@@ -86,7 +86,10 @@ class _PerClientModels(LocalAPI):
 
 
 class DPSGDAPI(_PerClientModels):
+    """Several ranks: every rank keeps all clients' models; a client's neighbour average and local training run on its owner, which
+    broadcasts the result at the end of the round (the neighbour draw is re-seeded per round and client, so ranks agree on it)."""
     NAME = "dpsgd"
+    MULTI_RANK = True
 
     def train(self):
         args = self.args
@@ -100,7 +103,7 @@ class DPSGDAPI(_PerClientModels):
             for i in range(n):
                 last[i].copy_(models[i])
             with self.timer.phase("train"):
-                for cid in range(n):
+                for cid in self.local_clients(range(n)):
                     self.logger.info('@@@@@@@@@@@@@@@@ Training Client CM({}): {}'.format(round_idx, cid))
                     nei = choose_neighbors(getattr(args, "cs", "ring"), cid, n, args.client_num_per_round, seed=round_idx + cid)
                     if n != args.client_num_per_round:
@@ -111,6 +114,9 @@ class DPSGDAPI(_PerClientModels):
                     _, flops, comm = self.client_list[cid].train(mixed, round_idx, None)
                     self.stat_info["sum_training_flops"] += flops
                     self._add_comm_params(comm)
+            if self.dist.is_distributed:
+                for cid in range(n):
+                    self.dist.broadcast(models[cid].flat, src=self.dist.owner(cid))
             self._mean_of(models, self.w_global)                               # _avg_aggregate
             self._test_global_and_personal(round_idx)
             if round_idx % 100 == 99:
@@ -122,11 +128,12 @@ class DPSGDAPI(_PerClientModels):
     def _finetune(self, round_idx):
         """Every 100 rounds: one extra training pass from the averaged model, evaluated but not kept."""
         self.logger.info("################Communication round Fine Tune Round After CM({})".format(round_idx))
-        keep = {c.client_idx: c.slab.clone() for c in self.client_list}
-        for c in self.client_list:
+        mine = [c for c in self.client_list if self.dist.owns(c.client_idx)]
+        keep = {c.client_idx: c.slab.clone() for c in mine}
+        for c in mine:
             c.train(self.w_global, -1, None)
         self._test_on_all_clients(self.w_global, self.personal_slabs(), -1)
-        for c in self.client_list:
+        for c in mine:
             c.slab.copy_(keep[c.client_idx])
 
 

@@ -33,6 +33,12 @@ def test_dispfl_over_three_ranks_matches_single_process():
     assert "RESULT ok=True" in r.stdout, r.stdout[-2000:]
 
 
+def test_dpsgd_over_three_ranks_matches_single_process():
+    r = _torchrun("dist_worker_dpsgd_cpu.py", 3, {"CUDA_VISIBLE_DEVICES": ""}, timeout=400)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "RESULT ok=True" in r.stdout, r.stdout[-2000:]
+
+
 def test_syncbn_over_ranks_matches_full_batch_batchnorm():
     """SyncBN (the reference's only collective call site, batchnorm_utils.py:150-237) as two all-reduces: a batch split unevenly
     over 3 ranks gives the full-batch BatchNorm3d outputs, gradients and running statistics."""
