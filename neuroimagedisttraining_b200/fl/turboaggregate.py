@@ -68,7 +68,15 @@ class TurboAggregateAPI(FedAvgAPI):
         groups = self.TA_topology_vanilla(order, group_size)
         dropped = set(getattr(self, "dropped_clients", ()))
         with self.timer.phase("aggregate"):
-            total = self._secure_sum(updates, groups, order, dropped, p, rng)
+            if updates:
+                total = self._secure_sum(updates, groups, order, dropped, p, rng)
+            else:                                        # this rank owns none of the sampled clients
+                total = np.zeros(self.w_global.flat.numel(), dtype=np.int64)
+            if self.dist.is_distributed:
+                # the ranks' masked partial aggregates are field elements too: the ring continues across ranks as one more sum mod p
+                t = torch.from_numpy(total).to(self.device)
+                self.dist.all_reduce_sum(t)
+                total = np.mod(t.cpu().numpy(), p)
         out = out if out is not None else self.w_global
         res = torch.from_numpy(mpc.dequantize(total, scale, p)).to(self.device, torch.float32)
         if mask is not None:
