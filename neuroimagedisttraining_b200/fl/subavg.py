@@ -97,10 +97,14 @@ class SubAvgAPI(LocalAPI):
         for mask, slab in w_locals:
             cnt += mask.flat
             acc += slab.flat
+        n_models = torch.tensor([float(len(w_locals))], device=self.device)
         with self.timer.phase("aggregate"):
+            if self.dist.is_distributed:                 # sums of the ranks' sampled clients
+                for t in (cnt, acc, n_models):
+                    self.dist.all_reduce_sum(t)
             keep = cnt > 0
             self.w_global.flat[:P] = torch.where(keep, acc[:P] / cnt.clamp(min=1.0), self.w_global.flat[:P])
-            self.w_global.flat[P:] = acc[P:] / len(w_locals)
+            self.w_global.flat[P:] = acc[P:] / n_models.clamp(min=1.0)
         return self.w_global
 
     def train(self):
@@ -113,8 +117,6 @@ class SubAvgAPI(LocalAPI):
             for m, f in zip(mask_pers, self._resumed_extra["subavg_masks"]):
                 m.flat.copy_(f.to(m.flat.device))
         self.mask_pers = mask_pers
-        if self.dist.is_distributed:
-            raise NotImplementedError("Sub-FedAvg keeps per-client masks on one rank")
         for round_idx in range(self.start_round, args.comm_round):
             t0 = time.time()
             self.logger.info("################Communication round : {}".format(round_idx))
@@ -122,8 +124,7 @@ class SubAvgAPI(LocalAPI):
             client_indexes = self._client_sampling(round_idx, n, args.client_num_per_round)
             w_locals, next_masks = [], []
             with self.timer.phase("train"):
-                for cid in client_indexes:
-                    cid = int(cid)
+                for cid in self.local_clients(client_indexes):
                     new_mask, slab, flops, comm = self._client_train(self.client_list[cid], mask_pers[cid], round_idx)
                     w_locals.append((mask_pers[cid].clone(), slab))
                     next_masks.append((cid, new_mask))
@@ -134,6 +135,9 @@ class SubAvgAPI(LocalAPI):
                 self._local_test_masked(mask_pers, round_idx)
             for cid, m in next_masks:
                 mask_pers[cid] = m
+            if self.dist.is_distributed:                 # every rank keeps all masks (mask statistics, checkpoints): owners publish
+                for cid in client_indexes:
+                    self.dist.broadcast(mask_pers[int(cid)].flat, src=self.dist.owner(int(cid)))
             self.stat_info["round_time_s"].append(time.time() - t0)
             self._maybe_checkpoint(round_idx)
         self.record_information()
@@ -147,14 +151,16 @@ class SubAvgAPI(LocalAPI):
         self.logger.info("mask difference to client 0: " + str(d))
 
     def _local_test_masked(self, mask_pers, round_idx):
-        accs, losses = [], []
+        n = len(self.client_list)
+        accs, losses = np.zeros(n), np.zeros(n)
         with self.timer.phase("eval"):
-            for cid, client in enumerate(self.client_list):
+            for cid in self.local_clients(range(n)):
                 w = self.w_global.clone()
                 real_prune(w, mask_pers[cid])
-                m = client.local_test(w, True)
-                accs.append(m["test_correct"] / max(m["test_total"], 1))
-                losses.append(m["test_loss"] / max(m["test_total"], 1))
+                m = self.client_list[cid].local_test(w, True)
+                accs[cid] = m["test_correct"] / max(m["test_total"], 1)
+                losses[cid] = m["test_loss"] / max(m["test_total"], 1)
+            accs, losses = self._reduce_metric(accs, losses)
         stats = {'person_test_acc': float(np.mean(accs)), 'person_test_loss': float(np.mean(losses))}
         self.stat_info["person_test_acc"].append(stats["person_test_acc"])
         self.stat_info.setdefault("person_test_loss", []).append(stats["person_test_loss"])

@@ -1,4 +1,4 @@
-"""torchrun worker (gloo, CPU): Local, Ditto, FedAvg and TurboAggregate on an image dataset with clients spread over ranks == the
+"""torchrun worker (gloo, CPU): Local, Ditto, FedAvg, TurboAggregate and Sub-FedAvg on an image dataset with clients spread over ranks == the
 single-process runs (global model and accuracy series)."""
 import logging
 import os
@@ -10,7 +10,7 @@ import numpy as np
 import torch
 
 from neuroimagedisttraining_b200.data import load_partition_data_images
-from neuroimagedisttraining_b200.fl import DittoAPI, FedAvgAPI, LocalAPI, SlabTrainer, TurboAggregateAPI
+from neuroimagedisttraining_b200.fl import DittoAPI, FedAvgAPI, LocalAPI, SlabTrainer, SubAvgAPI, TurboAggregateAPI
 from neuroimagedisttraining_b200.models import create_model
 from neuroimagedisttraining_b200.parallel import DistContext, init_distributed, shutdown
 
@@ -21,7 +21,8 @@ def run(ctx, API):
     n = 5
     args = types.SimpleNamespace(client_num_in_total=n, client_num_per_round=3, comm_round=2, epochs=1, lr=0.05, lr_decay=0.998, momentum=0.0,
                                  wd=5e-4, client_optimizer="sgd", batch_size=16, ci=0, frequency_of_the_test=1, dataset="cifar10", lamda=0.5,
-                                 local_epochs=1, final_finetune=False, ta_group_size=2, ta_scale=1 << 16)
+                                 local_epochs=1, final_finetune=False, ta_group_size=2, ta_scale=1 << 16, each_prune_ratio=0.2, dense_ratio=0.3,
+                                 dist_thresh=1e-4, acc_thresh=-1.0)
     ds = load_partition_data_images("cifar10", None, "dir", 0.5, n, 16, synthetic_size=(300, 100))
     model = create_model("lenet5_cifar", 10)
     api = API(ds, "cpu", args, SlabTrainer(model, args, logger, device="cpu", loss_kind="ce"), logger, dist=ctx)
@@ -34,7 +35,7 @@ def main():
     torch.set_num_threads(2)
     ctx = init_distributed(device="cpu")
     ok = True
-    for API in (LocalAPI, DittoAPI, FedAvgAPI, TurboAggregateAPI):
+    for API in (LocalAPI, DittoAPI, FedAvgAPI, TurboAggregateAPI, SubAvgAPI):
         multi, sm = run(ctx, API)
         single, ss = run(DistContext(device=torch.device("cpu")), API)
         tol = dict(rtol=1e-3, atol=1e-4) if API is TurboAggregateAPI else dict(rtol=1e-5, atol=1e-6)     # fixed-point field arithmetic
@@ -43,6 +44,9 @@ def main():
             a, b = sm.get(key, []), ss.get(key, [])
             good = good and len(a) == len(b) and all(abs(float(p) - float(q)) < (2e-2 if API is TurboAggregateAPI else 1e-9) for p, q in zip(a, b))
         good = good and (len(sm.get("person_test_acc", [])) > 0)
+        if API is SubAvgAPI:
+            good = good and all(torch.equal(a.flat, b.flat) for a, b in zip(multi.mask_pers, single.mask_pers))
+            good = good and any(float(m.flat.sum()) < m.flat.numel() for m in single.mask_pers)       # pruning did happen
         if ctx.rank == 0:
             print(f"{API.__name__}: world={ctx.world_size} match={good}", flush=True)
         ok = ok and good
