@@ -310,7 +310,10 @@ class DisPFLAPI(_PerClientModels):
 
 
 class FedFomoAPI(_PerClientModels):
+    """Several ranks: all ranks replay every client's neighbour draw (its RNG consumption does not depend on per-client state), the
+    owner trains, weighs and mixes, then broadcasts the client's model and its rows of the weight / preference matrices."""
     NAME = "fedfomo"
+    MULTI_RANK = True
 
     def extra_state(self) -> dict:
         if not hasattr(self, "_fomo_state"):
@@ -354,10 +357,13 @@ class FedFomoAPI(_PerClientModels):
             with self.timer.phase("train"):
                 for cid in range(n):
                     client = self.client_list[cid]
+                    if not self.dist.owns(cid):              # keep the python / numpy streams in step with the owner's draw
+                        self._benefit_choose(cid, n, args.client_num_per_round, p_choose[cid].copy())
+                        continue
                     self.logger.info('@@@@@@@@@@@@@@@@ Training Client CM({}): {}'.format(round_idx, cid))
                     _, flops, comm = client.train(last[cid], round_idx, None)
                     trained.copy_(client.slab)
-                    after_train.append(client.local_test(trained, True))
+                    after_train.append((cid, client.local_test(trained, True)))
                     nei = self._benefit_choose(cid, n, args.client_num_per_round, p_choose[cid])
                     if n != args.client_num_per_round:
                         nei = np.append(nei, cid)
@@ -385,11 +391,21 @@ class FedFomoAPI(_PerClientModels):
                         ops.weighted_aggregate(client.slab.flat, srcs, coefs)
                     m = client.local_test(client.slab, True)
                     self.logger.info("test acc on this client after agg {} / {} : {:.2f}".format(m['test_correct'], m['test_total'], m['test_acc']))
-                    after_agg.append(m)
+                    after_agg.append((cid, m))
                     self.stat_info["sum_training_flops"] += flops
                     self._add_comm_params(comm)
+            if self.dist.is_distributed:
+                for cid in range(n):
+                    src = self.dist.owner(cid)
+                    self.dist.broadcast(models[cid].flat, src=src)
+                    rows = torch.tensor(np.stack([weights_locals[cid], p_choose[cid]]), dtype=torch.float64, device=self.device)
+                    self.dist.broadcast(rows, src=src)
+                    weights_locals[cid], p_choose[cid] = rows[0].cpu().numpy(), rows[1].cpu().numpy()
             for key, res in (("old_mask_test_acc", after_train), ("new_mask_test_acc", after_agg)):
-                acc = sum(r["test_correct"] / max(r["test_total"], 1) for r in res) / n
+                accs = np.zeros(n)
+                for cid, r in res:
+                    accs[cid] = r["test_correct"] / max(r["test_total"], 1)
+                acc = float(self._reduce_metric(accs)[0].sum() / n)
                 self.stat_info[key].append(acc)
                 self.logger.info({'test_acc': acc})
             self.stat_info["person_test_acc"].append(self.stat_info["new_mask_test_acc"][-1])

@@ -33,7 +33,7 @@ def test_dispfl_over_three_ranks_matches_single_process():
     assert "RESULT ok=True" in r.stdout, r.stdout[-2000:]
 
 
-def test_dpsgd_over_three_ranks_matches_single_process():
+def test_dpsgd_and_fedfomo_over_three_ranks_match_single_process():
     r = _torchrun("dist_worker_dpsgd_cpu.py", 3, {"CUDA_VISIBLE_DEVICES": ""}, timeout=400)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "RESULT ok=True" in r.stdout, r.stdout[-2000:]
