@@ -147,11 +147,10 @@ def load_npz(path: str, pin: bool = False) -> InMemoryVolumeStore:
 def save_hdf5(store: InMemoryVolumeStore, path: str) -> None:
     """``X`` / ``y`` / ``site`` in one HDF5 file, the container the reference's loaders read (``ABCD/data_loader.py:105-141``).
     With ``h5py``: one chunk per volume, LZF-compressed.  Without: the built-in writer (contiguous, uncompressed)."""
-    try:
-        import h5py  # type: ignore
-    except ImportError:
-        from .hdf5_mini import write_file
-        write_file(path, {"X": store.volumes.numpy(), "y": np.asarray(store.labels), "site": np.asarray(store.sites)})
+    from .volumes import hdf5_backend
+    h5py = hdf5_backend()
+    if not hasattr(h5py, "special_dtype"):               # the in-tree subset
+        h5py.write_file(path, {"X": store.volumes.numpy(), "y": np.asarray(store.labels), "site": np.asarray(store.sites)})
         return
     with h5py.File(path, "w") as f:
         f.create_dataset("X", data=store.volumes.numpy(), chunks=(1,) + tuple(store.shape), compression="lzf")

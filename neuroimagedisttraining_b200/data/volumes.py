@@ -128,6 +128,19 @@ class SyntheticABCD(VolumeStore):
         return x, y
 
 
+def hdf5_backend():
+    """``h5py`` when a working one is installed, else the in-tree reader for plain contiguous files (what the reference's notebook
+    writes).  (A module named h5py without ``File`` -- e.g. an import stub put into ``sys.modules`` -- does not count.)"""
+    try:
+        import h5py  # type: ignore
+        if hasattr(h5py, "File"):
+            return h5py
+    except ImportError:
+        pass
+    from . import hdf5_mini
+    return hdf5_mini
+
+
 class HDF5VolumeStore(VolumeStore):
     """Reader for the reference's files: ``X`` volumes in one HDF5 (``alldatain8bitsnormalized.h5``),
     ``y``/``site`` in another (``dataset_all_labels_site.h5``; ``ABCD/data_loader.py:105-141``).
@@ -135,10 +148,7 @@ class HDF5VolumeStore(VolumeStore):
     (:mod:`.hdf5_mini`)."""
 
     def __init__(self, volumes_path: str, labels_path: Optional[str] = None, scale: Optional[float] = None):
-        try:
-            import h5py  # type: ignore
-        except ImportError:
-            from . import hdf5_mini as h5py     # plain contiguous files (what the reference's notebook writes) without the library
+        h5py = hdf5_backend()
         self._f = h5py.File(volumes_path, "r")
         self._X = self._f["X"]
         lab = h5py.File(labels_path, "r") if labels_path else self._f
