@@ -67,6 +67,10 @@ def add_common_args(p: argparse.ArgumentParser, *, model="3DCNN", dataset="ABCD"
     g.add_argument("--cutout", type=int, default=0, help="with --augment: side of the Cutout square (the reference keeps Cutout(16) commented out)")
     g.add_argument("--labels_file", default=None, help="ABCD: HDF5 file with y / site when they are not in --data_dir (the reference keeps "
                                                        "volumes in alldatain8bitsnormalized.h5 and labels in dataset_all_labels_site.h5)")
+    g.add_argument("--defense_type", default="none", choices=["none", "norm_diff_clipping", "weak_dp"],
+                   help="FedAvg / SalientGrads: robust-aggregation defence applied to every client upload")
+    g.add_argument("--norm_bound", type=float, default=5.0)
+    g.add_argument("--stddev", type=float, default=0.025)
     g.add_argument("--rescale", action="store_true", help="ABCD: cut the site-ordered data into client_num_in_total equal shards")
     g.add_argument("--correct_eval_loss", action="store_true", help="evaluate BCEWithLogits(logit) instead of the reference's BCEWithLogits(sigmoid(logit))")
     return p

@@ -27,6 +27,7 @@ class FedAvgAPI(FedAPIBase):
                 # the next client's first batch is staged while this one finishes (no exposed copy at client boundaries)
                 nxt = self.client_list[mine[pos + 1]].local_training_data if pos + 1 < len(mine) else None
                 slab, training_flops, num_comm_params = client.train(self.w_global, round_idx, mask, lookahead_data=nxt)
+                self._defend(slab)
                 w_locals.append((client.get_sample_number(), slab))
                 self.stat_info["sum_training_flops"] += training_flops
                 self._add_comm_params(num_comm_params)
@@ -35,6 +36,23 @@ class FedAvgAPI(FedAPIBase):
         if evaluate and round_idx % max(1, int(getattr(args, "frequency_of_the_test", 1))) == 0:
             self._test_on_all_clients(self.w_global, self.personal_slabs(), round_idx)
         self._maybe_checkpoint(round_idx)
+
+    def _defend(self, slab) -> None:
+        """Optional robust-aggregation defence on a client's upload (``--defense_type``; the reference ships the routines without a
+        caller, ``fedml_core/robustness/robust_aggregation.py:32-55``): clip the update's norm to ``--norm_bound`` around the global
+        model, and for ``weak_dp`` also add N(0, ``--stddev``^2) noise to the parameters."""
+        kind = getattr(self.args, "defense_type", None)
+        if not kind or kind == "none":
+            return
+        if getattr(self, "_robust", None) is None:
+            from ..utils.robust import RobustAggregator
+            self._robust = RobustAggregator(self.args)
+        self._robust.norm_diff_clipping(slab, self.w_global)
+        if kind == "weak_dp":
+            P = slab.layout.param_numel
+            slab.flat[:P] = self._robust.add_noise(slab.flat[:P])
+        elif kind != "norm_diff_clipping":
+            raise ValueError(f"unknown defense_type {kind!r} (none | norm_diff_clipping | weak_dp)")
 
     def train(self):
         args = self.args

@@ -289,3 +289,32 @@ def test_per_client_algorithms_resume_bit_identically(tmp_path, API, extra):
         assert all(torch.equal(x.flat, y.flat) for x, y in zip(second.masks_per_client, full.masks_per_client))
     if API is SubAvgAPI:
         assert all(torch.equal(x.flat, y.flat) for x, y in zip(second.mask_pers, full.mask_pers))
+
+
+def test_fedavg_with_norm_clipping_and_weak_dp_defences():
+    """``--defense_type``: every upload is pulled back to within ``norm_bound`` of the global model before it is averaged."""
+    ds, args, tr = _vol_setup()
+    args.final_finetune, args.comm_round = False, 1
+    plain = FedAvgAPI(ds, "cpu", args, tr, quiet_logger())
+    start = plain.w_global.clone()
+    plain.train()
+    P = plain.layout.param_numel
+    moved = float((plain.w_global.flat[:P] - start.flat[:P]).norm())
+    ds, args, tr = _vol_setup()
+    args.final_finetune, args.comm_round, args.defense_type, args.norm_bound = False, 1, "norm_diff_clipping", moved / 4
+    clipped = FedAvgAPI(ds, "cpu", args, tr, quiet_logger())
+    clipped.train()
+    for c in clipped.client_list:
+        assert float((c.slab.flat[:P] - start.flat[:P]).norm()) <= moved / 4 * (1 + 1e-4)
+    assert float((clipped.w_global.flat[:P] - start.flat[:P]).norm()) <= moved / 4 * (1 + 1e-4) < moved
+    ds, args, tr = _vol_setup()
+    args.final_finetune, args.comm_round, args.defense_type, args.norm_bound, args.stddev = False, 1, "weak_dp", 100.0, 0.01
+    torch.manual_seed(1)
+    noisy = FedAvgAPI(ds, "cpu", args, tr, quiet_logger())
+    noisy.train()
+    d = noisy.w_global.flat[:P] - plain.w_global.flat[:P]
+    real = d[plain.w_global.flat[:P] != 0]
+    assert 0.001 < float(real.std()) < 0.01              # mean of 4 clients' N(0, 0.01^2) noise: 0.005
+    with pytest.raises(ValueError, match="defense_type"):
+        args.defense_type = "bogus"
+        FedAvgAPI(ds, "cpu", args, tr, quiet_logger()).train()
