@@ -162,14 +162,24 @@ def setup(args, prefix: str, extra_identity: Optional[list] = None, loss_kind: O
             logger.info(f"native engine unavailable for {args.model}: {e}; using the PyTorch engine for forward/backward")
     trainer = SlabTrainer(model, args, logger, device=device, store=store, engine=engine, loss_kind=loss_kind)
     trainer.double_sigmoid_eval = not args.correct_eval_loss
+    args.metrics_path = os.path.join(args.log_dir, args.dataset, args.identity + ".jsonl")
     return ctx, device, logger, dataset, trainer
+
+
+def attach_metrics(api, args, ctx):
+    """One JSON line per evaluation while the run is going (``event: eval``), plus the summary line :func:`finish` appends."""
+    if ctx.is_main:
+        api._jsonl = JsonlMetrics(args.metrics_path)
+        api.metrics_sink = api._jsonl.write
+    return api
 
 
 def finish(api, args, logger, ctx) -> dict:
     stat = api.finalize_stats() if "phase_time_s" not in api.stat_info else api.stat_info
     if ctx.is_main:
-        JsonlMetrics(os.path.join(args.log_dir, args.dataset, args.identity + ".jsonl")).write(
-            identity=args.identity, global_test_acc=[float(x) for x in stat.get("global_test_acc", [])],
+        sink = getattr(api, "_jsonl", None) or JsonlMetrics(os.path.join(args.log_dir, args.dataset, args.identity + ".jsonl"))
+        sink.write(
+            event="summary", identity=args.identity, global_test_acc=[float(x) for x in stat.get("global_test_acc", [])],
             person_test_acc=[float(x) for x in stat.get("person_test_acc", [])], sum_comm_params=int(stat.get("sum_comm_params", 0)),
             sum_training_flops=float(stat.get("sum_training_flops", 0)), phase_time_s=stat.get("phase_time_s"))
         logger.info({"sum_comm_params": stat.get("sum_comm_params"), "sum_training_flops": stat.get("sum_training_flops"),

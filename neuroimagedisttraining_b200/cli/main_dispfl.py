@@ -3,7 +3,7 @@
 import argparse
 
 from ..fl import DisPFLAPI
-from .common import add_common_args, add_sparse_args, finish, setup
+from .common import add_common_args, attach_metrics, add_sparse_args, finish, setup
 
 
 def add_args(parser):
@@ -21,6 +21,7 @@ def main(argv=None):
              "-g" if args.global_test else "", "-RSM" if args.static else "-DST"]
     ctx, device, logger, dataset, trainer = setup(args, "DisPFL", extra)
     api = DisPFLAPI(dataset, device, args, trainer, logger, dist=ctx)
+    attach_metrics(api, args, ctx)
     if args.resume:
         api.resume(args.resume)
     api.train()

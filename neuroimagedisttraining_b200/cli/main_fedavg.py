@@ -3,7 +3,7 @@ epochs 5, frac 0.9, seed 0).  Unlike the reference (``:203``) it also runs witho
 import argparse
 
 from ..fl import FedAvgAPI
-from .common import add_common_args, finish, setup
+from .common import add_common_args, attach_metrics, finish, setup
 
 
 def add_args(parser):
@@ -14,6 +14,7 @@ def main(argv=None):
     args = add_args(argparse.ArgumentParser(description="FedAvg-standalone")).parse_args(argv)
     ctx, device, logger, dataset, trainer = setup(args, "fedavg")
     api = FedAvgAPI(dataset, device, args, trainer, logger, dist=ctx, agg_mode=args.agg)
+    attach_metrics(api, args, ctx)
     if args.resume:
         api.resume(args.resume)
     api.train()

@@ -4,7 +4,7 @@ import argparse
 import sys
 
 from ..fl import DittoAPI, DPSGDAPI, FedFomoAPI, LocalAPI, SubAvgAPI, TurboAggregateAPI
-from .common import add_common_args, finish, setup
+from .common import add_common_args, attach_metrics, finish, setup
 
 ALGOS = {"ditto": DittoAPI, "dpsgd": DPSGDAPI, "fedfomo": FedFomoAPI, "local": LocalAPI, "subavg": SubAvgAPI, "turboaggregate": TurboAggregateAPI}
 
@@ -42,6 +42,7 @@ def main(argv=None):
         kw["agg_mode"] = args.agg
         args.final_finetune = False
     api = ALGOS[algo](dataset, device, args, trainer, logger, **kw)
+    attach_metrics(api, args, ctx)
     if args.resume:
         api.resume(args.resume)
     api.train()

@@ -4,7 +4,7 @@
 import argparse
 
 from ..fl import SalientGradsAPI
-from .common import add_common_args, add_sparse_args, finish, setup, str2bool
+from .common import add_common_args, attach_metrics, add_sparse_args, finish, setup, str2bool
 
 
 def add_args(parser):
@@ -24,6 +24,7 @@ def main(argv=None):
     ctx, device, logger, dataset, trainer = setup(args, "SailentGrads", extra)
     args.identity += f"-iteration{args.itersnip_iteration}-stratified{args.stratified_sampling}"
     api = SalientGradsAPI(dataset, device, args, trainer, logger, dist=ctx, agg_mode=args.agg)
+    attach_metrics(api, args, ctx)
     if args.resume:
         api.resume(args.resume)
     api.train()

@@ -59,6 +59,7 @@ class FedAPIBase:
         self.mask: Optional[ParamSlab] = None
         self.w_init: Optional[ParamSlab] = None   # personalised model of a client that never trained
         self._resumed_extra: dict = {}
+        self.metrics_sink = None                 # callable(**metrics): the entry points plug a JSONL writer in (one line per evaluation)
 
     # ------------------------------------------------------------------------- set-up
     def _setup_clients(self, train_data_local_num_dict, train_data_local_dict, test_data_local_dict, model_trainer):
@@ -153,7 +154,12 @@ class FedAPIBase:
         self.stat_info["person_test_acc"].append(pstats['person_test_acc'])
         self.stat_info["person_test_loss"].append(pstats['person_test_loss'])
         self.logger.info(pstats)
+        self._emit(round=int(round_idx), **{k: float(v) for k, v in {**stats, **pstats}.items()})
         return stats, pstats
+
+    def _emit(self, **metrics) -> None:
+        if self.metrics_sink is not None and self.dist.is_main:
+            self.metrics_sink(event="eval", algorithm=self.NAME, **metrics)
 
     # ------------------------------------------------------------------------- stats
     def _add_comm_params(self, n) -> None:

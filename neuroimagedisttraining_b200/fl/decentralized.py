@@ -304,6 +304,7 @@ class DisPFLAPI(_PerClientModels):
         denom = max(float(seen.sum()), 1.0)
         acc, loss = float(acc.sum() / denom), float(loss.sum() / denom)
         self.logger.info({'test_acc': acc, 'test_loss': loss})
+        self._emit(round=int(round_idx), series=key, test_acc=acc, test_loss=loss)
         self.stat_info[key].append(acc)
         if key == "old_mask_test_acc":
             self.stat_info["person_test_acc"].append(acc)
@@ -408,6 +409,7 @@ class FedFomoAPI(_PerClientModels):
                 acc = float(self._reduce_metric(accs)[0].sum() / n)
                 self.stat_info[key].append(acc)
                 self.logger.info({'test_acc': acc})
+                self._emit(round=int(round_idx), series=key, test_acc=acc)
             self.stat_info["person_test_acc"].append(self.stat_info["new_mask_test_acc"][-1])
             self.stat_info["round_time_s"].append(time.time() - t0)
             self._maybe_checkpoint(round_idx)

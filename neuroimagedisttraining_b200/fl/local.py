@@ -50,6 +50,7 @@ class LocalAPI(FedAPIBase):
         # the key the reference's Local / Ditto / D-PSGD / FedFomo / Sub-FedAvg APIs record (e.g. ditto_api.py:149-150)
         self.stat_info.setdefault("test_acc", []).append(stats["person_test_acc"])
         self.logger.info(stats)
+        self._emit(round=int(round_idx), **{k: float(v) for k, v in stats.items()})
         return stats
 
     def record_information(self):

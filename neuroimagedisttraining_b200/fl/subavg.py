@@ -167,4 +167,5 @@ class SubAvgAPI(LocalAPI):
         self.stat_info.setdefault("test_acc", []).append(stats["person_test_acc"])        # the reference's key (subavg_api.py)
         self.eval_masks = [m.clone() for m in mask_pers]                                    # masks the evaluation used
         self.logger.info(stats)
+        self._emit(round=int(round_idx), **stats)
         return stats

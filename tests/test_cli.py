@@ -45,8 +45,10 @@ def test_fedavg_cli_config1_with_checkpoint_and_resume(tmp_path):
     assert len(stat["global_test_acc"]) >= 2 and all(0.0 <= a <= 1.0 for a in stat["global_test_acc"])
     logs = os.listdir(tmp_path / "LOG" / "ABCD")
     assert any(f.endswith(".log") for f in logs) and any(f.endswith(".jsonl") for f in logs)
-    line = json.loads(open(tmp_path / "LOG" / "ABCD" / next(f for f in logs if f.endswith(".jsonl"))).readline())
-    assert line["global_test_acc"] == [float(a) for a in stat["global_test_acc"]] and "phase_time_s" in line
+    lines = [json.loads(l) for l in open(tmp_path / "LOG" / "ABCD" / next(f for f in logs if f.endswith(".jsonl")))]
+    evals, line = [l for l in lines if l["event"] == "eval"], lines[-1]
+    assert [e["round"] for e in evals] == [0, 1, -1] and [e["global_test_acc"] for e in evals] == [float(a) for a in stat["global_test_acc"]]
+    assert line["event"] == "summary" and line["global_test_acc"] == [float(a) for a in stat["global_test_acc"]] and "phase_time_s" in line
     ckpt = torch.load(ck, weights_only=False)
     assert ckpt["round"] == 1 and any(k.startswith("features.0.") for k in ckpt["state_dict"]) and "stat_info" in ckpt
     from neuroimagedisttraining_b200.models import Tiny3DCNN
