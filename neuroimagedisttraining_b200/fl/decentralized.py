@@ -97,6 +97,7 @@ class DPSGDAPI(_PerClientModels):
         n = args.client_num_in_total
         last = [m.clone() for m in models]
         mixed = self.w_global.clone()
+        topology = self._mixing_matrix(n)
         for round_idx in range(self.start_round, args.comm_round):
             t0 = time.time()
             self.logger.info("################Communication round : {}".format(round_idx))
@@ -105,12 +106,18 @@ class DPSGDAPI(_PerClientModels):
             with self.timer.phase("train"):
                 for cid in self.local_clients(range(n)):
                     self.logger.info('@@@@@@@@@@@@@@@@ Training Client CM({}): {}'.format(round_idx, cid))
-                    nei = choose_neighbors(getattr(args, "cs", "ring"), cid, n, args.client_num_per_round, seed=round_idx + cid)
-                    if n != args.client_num_per_round:
-                        nei = np.append(nei, cid)
-                    nei = np.sort(nei)
-                    self.logger.info("client_indexes = " + str(nei))
-                    self._mean_of([last[int(j)] for j in nei], mixed)          # neighbour averaging (K: _aggregate_func)
+                    if topology is not None:                                   # row of a mixing matrix instead of a plain mean
+                        row = topology[cid]
+                        nei = np.nonzero(row)[0]
+                        self.logger.info("client_indexes = " + str(nei))
+                        ops.weighted_aggregate(mixed.flat, [last[int(j)].flat for j in nei], [float(row[j]) for j in nei])
+                    else:
+                        nei = choose_neighbors(getattr(args, "cs", "ring"), cid, n, args.client_num_per_round, seed=round_idx + cid)
+                        if n != args.client_num_per_round:
+                            nei = np.append(nei, cid)
+                        nei = np.sort(nei)
+                        self.logger.info("client_indexes = " + str(nei))
+                        self._mean_of([last[int(j)] for j in nei], mixed)      # neighbour averaging (K: _aggregate_func)
                     _, flops, comm = self.client_list[cid].train(mixed, round_idx, None)
                     self.stat_info["sum_training_flops"] += flops
                     self._add_comm_params(comm)
@@ -124,6 +131,23 @@ class DPSGDAPI(_PerClientModels):
             self.stat_info["round_time_s"].append(time.time() - t0)
             self._maybe_checkpoint(round_idx)
         return self.finalize_stats()
+
+    def _mixing_matrix(self, n: int):
+        """``--cs topology_sym`` / ``topology_asym``: gossip with the row-stochastic mixing matrix of the FedML topology managers
+        (ring plus ``client_num_per_round`` extra links; ``fedml_core/distributed/topology/*.py``, which the reference never wires
+        up).  None for the reference's own ring / random / full neighbour rules."""
+        cs = str(getattr(self.args, "cs", "ring"))
+        if not cs.startswith("topology"):
+            return None
+        from ..utils.topology import AsymmetricTopologyManager, SymmetricTopologyManager
+        k = max(2, int(self.args.client_num_per_round))
+        k -= k % 2                                                             # ring lattices need an even neighbour count
+        if cs == "topology_asym":
+            tm = AsymmetricTopologyManager(n, k, max(1, k // 2), seed=int(getattr(self.args, "seed", 0)))
+        else:
+            tm = SymmetricTopologyManager(n, k)
+        tm.generate_topology()
+        return np.asarray(tm.topology, dtype=np.float64)
 
     def _finetune(self, round_idx):
         """Every 100 rounds: one extra training pass from the averaged model, evaluated but not kept."""

@@ -318,3 +318,21 @@ def test_fedavg_with_norm_clipping_and_weak_dp_defences():
     with pytest.raises(ValueError, match="defense_type"):
         args.defense_type = "bogus"
         FedAvgAPI(ds, "cpu", args, tr, quiet_logger()).train()
+
+
+@pytest.mark.parametrize("cs", ["topology_sym", "topology_asym"])
+def test_dpsgd_gossip_with_topology_manager_mixing_matrix(cs):
+    """D-PSGD whose neighbour step is a row of the FedML topology managers' mixing matrix: one round from identical models leaves the
+    plain-mean global model where row-stochastic mixing of identical models must leave it, and models stay finite / distinct."""
+    ds, args, tr = _img_setup(n_clients=6, cs=cs, frac=0.5)
+    args.client_num_per_round, args.comm_round = 2, 2
+    api = DPSGDAPI(ds, "cpu", args, tr, quiet_logger())
+    W = api._mixing_matrix(6)
+    assert W.shape == (6, 6) and np.allclose(W.sum(1), 1.0) and (np.diag(W) > 0).all()
+    if cs == "topology_sym":
+        assert np.allclose(W, W.T)
+    st = api.train()
+    assert len(st["global_test_acc"]) == 2 and torch.isfinite(api.w_global.flat).all()
+    assert not torch.equal(api.client_list[0].slab.flat, api.client_list[3].slab.flat)
+    mean = sum(c.slab.flat for c in api.client_list) / 6
+    torch.testing.assert_close(api.w_global.flat, mean, rtol=1e-5, atol=1e-6)
