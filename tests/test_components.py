@@ -273,3 +273,22 @@ def test_hdf5_volume_store_against_a_stand_in_h5py(monkeypatch):
     fs = HDF5VolumeStore("f.h5")
     xf, _ = fs.fetch([2, 0])
     assert xf.dtype == torch.uint8 and torch.equal(xf[0], torch.from_numpy(np.rint(files["f.h5"]["X"].a[2] * 255).astype(np.uint8)))
+
+
+def test_c_abi_header_matches_the_exported_symbols():
+    """``include/nidt_b200.h`` declares exactly the entry points the library exports (and the library exports nothing else)."""
+    import glob
+    import os
+    import re
+    import subprocess
+    from neuroimagedisttraining_b200.ops import native
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    header = set(re.findall(r"\b(nidt_\w+)\s*\(", open(os.path.join(root, "include", "nidt_b200.h")).read()))
+    defined = set()
+    for f in glob.glob(os.path.join(root, "neuroimagedisttraining_b200", "csrc", "*.cu")):
+        defined |= set(m.group(1) for m in re.finditer(r"NIDT_API\s+[\w\s\*]+?\b(nidt_\w+)\s*\(", open(f).read()))
+    assert header == defined and len(header) > 50
+    if native.available():
+        out = subprocess.run(["nm", "-D", "--defined-only", str(native.lib_path())], capture_output=True, text=True).stdout
+        exported = {line.split()[-1] for line in out.splitlines() if " T " in line}
+        assert exported == header
