@@ -8,7 +8,6 @@ paths with a synthetic in-memory source, and construction of the FedML 8-tuple.
 from __future__ import annotations
 
 import logging
-import os
 import sys
 import types
 from pathlib import Path

@@ -14,7 +14,6 @@ from __future__ import annotations
 
 import queue
 import threading
-import time
 from abc import ABC, abstractmethod
 from concurrent import futures
 from typing import Dict, List, Optional

@@ -7,7 +7,6 @@ import logging
 import threading
 from typing import Callable, Dict, Optional
 
-import torch
 
 from .base import BaseCommunicationManager, GrpcCommManager, InProcessCommManager, MqttCommManager, Observer, TorchDistCommManager
 from .message import Message

@@ -10,7 +10,7 @@ from __future__ import annotations
 
 import math
 import random
-from typing import Dict, Iterator, List, Optional, Sequence, Tuple
+from typing import Iterator, Optional, Sequence, Tuple
 
 import numpy as np
 import torch
@@ -177,7 +177,6 @@ def synthetic_image_dataset(n_train: int, n_test: int, n_cls: int, shape=(3, 32,
 
 def _load_torchvision(dataset: str, data_dir: str):
     import torchvision  # local import: optional dependency
-    import torchvision.transforms as T
     stats = {"cifar10": ((0.4914, 0.4822, 0.4465), (0.2470, 0.2435, 0.2616)),
              "cifar100": ((0.5071, 0.4865, 0.4409), (0.2673, 0.2564, 0.2762))}[dataset]
     cls = {"cifar10": torchvision.datasets.CIFAR10, "cifar100": torchvision.datasets.CIFAR100}[dataset]

@@ -8,8 +8,6 @@ client's personal model and the mask are device-resident slabs; clients are plac
 """
 from __future__ import annotations
 
-import time
-from collections import defaultdict
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import numpy as np

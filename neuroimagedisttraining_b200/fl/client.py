@@ -7,7 +7,6 @@ from __future__ import annotations
 from typing import Optional
 
 import numpy as np
-import torch
 
 from ..runtime.slab import ParamSlab
 from .trainer import SlabTrainer

@@ -6,7 +6,6 @@ import os
 import pickle
 import time
 
-import numpy as np
 
 from .base import FedAPIBase
 

@@ -8,9 +8,7 @@ one shared binary mask, and FedAvg then runs with ``w *= mask`` fused into every
 from __future__ import annotations
 
 import time
-from typing import Optional
 
-import torch
 
 from .. import ops
 from ..runtime.slab import ParamSlab, make_mask_slab

@@ -4,7 +4,7 @@
 from __future__ import annotations
 
 import time
-from typing import Dict, Optional, Tuple
+from typing import Tuple
 
 import numpy as np
 import torch

@@ -10,7 +10,6 @@ is tolerated by re-sharing within the surviving members.  The result equals plai
 """
 from __future__ import annotations
 
-import time
 from typing import List, Sequence
 
 import numpy as np

@@ -15,9 +15,8 @@ Differences from the reference, on purpose:
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import List, Optional, Sequence, Tuple
+from typing import List, Sequence, Tuple
 
-import torch
 import torch.nn as nn
 
 ABCD_SHAPE = (121, 145, 121)

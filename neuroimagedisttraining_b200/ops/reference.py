@@ -8,7 +8,7 @@ native library and raises if it is missing (``ops/native.py``).
 from __future__ import annotations
 
 import math
-from typing import List, Optional, Sequence, Tuple
+from typing import Optional, Sequence, Tuple
 
 import torch
 

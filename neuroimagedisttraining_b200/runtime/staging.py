@@ -7,7 +7,7 @@ stream into a ring of device buffers, so the copy of batch i+1 overlaps the comp
 """
 from __future__ import annotations
 
-from typing import Iterator, Optional, Tuple
+from typing import Iterator, Tuple
 
 import os
 

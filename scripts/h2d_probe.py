@@ -1,5 +1,5 @@
 """Host->device copy bandwidth from pinned memory for the transfer sizes the stager uses."""
-import torch, time
+import torch
 dev = "cuda"
 vol = 121 * 145 * 121
 src = torch.randint(0, 255, (64, vol), dtype=torch.uint8).pin_memory()

@@ -6,11 +6,11 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 os.environ.setdefault("MASTER_ADDR", "127.0.0.1"); os.environ.setdefault("MASTER_PORT", "29577")
 os.environ.setdefault("RANK", "0"); os.environ.setdefault("WORLD_SIZE", "1"); os.environ.setdefault("LOCAL_RANK", "0")
 import torch
-from neuroimagedisttraining_b200.fl.engine import StepHParams, EvalCounters
+from neuroimagedisttraining_b200.fl.engine import StepHParams
 from neuroimagedisttraining_b200.models import AlexNet3D_Dropout
 from neuroimagedisttraining_b200.ops.engine_b200 import B200Engine
 from neuroimagedisttraining_b200.ops import flat as flat_ops
-from neuroimagedisttraining_b200.parallel import init_distributed, shutdown
+from neuroimagedisttraining_b200.parallel import init_distributed
 from neuroimagedisttraining_b200.parallel.symmetric import SymmetricAggregator
 
 B = 16

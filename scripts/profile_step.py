@@ -5,7 +5,6 @@ import torch
 from neuroimagedisttraining_b200.fl.engine import StepHParams
 from neuroimagedisttraining_b200.models import AlexNet3D_Dropout
 from neuroimagedisttraining_b200.ops.engine_b200 import B200Engine
-from neuroimagedisttraining_b200 import ops
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 16
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 5

@@ -1,4 +1,4 @@
-import os, sys, subprocess
+import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from neuroimagedisttraining_b200.ops import volumetric as V

@@ -6,7 +6,6 @@ import types
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
-import torch.distributed as dist
 
 from neuroimagedisttraining_b200.data import SyntheticABCD, load_partition_data_abcd
 from neuroimagedisttraining_b200.fl import SalientGradsAPI, SlabTrainer

@@ -1,7 +1,6 @@
 import logging
 import types
 
-import torch
 
 
 def quiet_logger(name="test"):

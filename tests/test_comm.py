@@ -5,7 +5,6 @@ import time
 import pytest
 import torch
 
-from neuroimagedisttraining_b200 import ops
 from neuroimagedisttraining_b200.comm import (FedAvgClientManager, FedAvgServerManager, GrpcCommManager, InProcessCommManager, Message,
                                               MqttCommManager)
 

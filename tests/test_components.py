@@ -3,11 +3,10 @@ import numpy as np
 import pytest
 import torch
 
-from neuroimagedisttraining_b200.data import (SyntheticABCD, hetero_dirichlet_partition, load_partition_data_abcd_rescale,
-                                              partition_labels, rescale_partition, site_partition)
+from neuroimagedisttraining_b200.data import (SyntheticABCD, load_partition_data_abcd_rescale, partition_labels, rescale_partition, site_partition)
 from neuroimagedisttraining_b200.data import preprocess as P
 from neuroimagedisttraining_b200.models import AlexNet3D_Dropout, create_model, experimental as E, MODEL_NAMES
-from neuroimagedisttraining_b200.models.darts import DARTS_V2, NetworkCIFAR, SearchNetwork, search
+from neuroimagedisttraining_b200.models.darts import DARTS_V2, NetworkCIFAR, search
 from neuroimagedisttraining_b200.runtime.slab import ParamSlab
 from neuroimagedisttraining_b200.utils import (AsymmetricTopologyManager, RobustAggregator, SymmetricTopologyManager, count_inference_flops,
                                                count_training_flops, cosine_annealing, hamming_distance, model_difference)

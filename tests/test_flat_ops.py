@@ -1,6 +1,5 @@
 """Flat-slab ops: CPU restatements vs. hand formulas (always) and sm_100a kernels vs. the fp32
 PyTorch restatements (``-m gpu``)."""
-import math
 
 import numpy as np
 import pytest
@@ -9,7 +8,7 @@ import torch
 from neuroimagedisttraining_b200 import ops
 from neuroimagedisttraining_b200.models import AlexNet3D_Dropout, Tiny3DCNN
 from neuroimagedisttraining_b200.ops import reference as R
-from neuroimagedisttraining_b200.runtime.slab import ParamSlab, SlabLayout
+from neuroimagedisttraining_b200.runtime.slab import SlabLayout
 
 
 def _rand(n, seed=0, device="cpu"):
