@@ -236,27 +236,44 @@ class SlabParallelFeatures(nn.Module):
     def forward(self, x_slab: torch.Tensor, part: DepthPartition) -> torch.Tensor:
         world, rank = self._world_rank()
         assert part.world == world
-        x = x_slab
-        for m in self.features:
-            if isinstance(m, nn.Conv3d):
-                assert m.dilation == (1, 1, 1) and m.groups == 1 and m.padding_mode == "zeros", "plain Conv3d only"
-                x, part = slab_conv3d(x, part, rank, m.weight, m.bias, m.stride, m.padding, self.group)
-            elif isinstance(m, nn.modules.batchnorm._BatchNorm):
-                x = self._batchnorm(m, x)
-            elif isinstance(m, nn.MaxPool3d):
-                assert not m.ceil_mode and _triple(m.dilation) == (1, 1, 1)
-                x, part = slab_max_pool3d(x, part, rank, m.kernel_size, m.stride, m.padding, self.group)
-            elif isinstance(m, nn.AvgPool3d):
-                assert not m.ceil_mode and m.count_include_pad
-                x, part = slab_avg_pool3d(x, part, rank, m.kernel_size, m.stride, m.padding, self.group)
-            elif isinstance(m, (nn.ReLU, nn.Dropout, nn.Identity, nn.LeakyReLU, nn.Sigmoid, nn.Tanh)):
-                x = m(x) if not (isinstance(m, nn.ReLU) and m.inplace) else F.relu(x)
-            else:
-                raise NotImplementedError(f"{type(m).__name__} has no slab-parallel form")
+        x, part = self._run(self.features, x_slab, part, rank)
         out = gather_depth(x, part, rank, self.group)
         if world > 1 and out.requires_grad:
             out.register_hook(lambda g: g / world)
         return out
+
+    def _run(self, m: nn.Module, x: torch.Tensor, part: DepthPartition, rank: int) -> Tuple[torch.Tensor, DepthPartition]:
+        """One module on a slab -> (output slab, its partition).  Containers recurse; residual blocks (``conv1/bn1/conv2/bn2[/conv3/bn3]``
+        + optional ``downsample``, the 3-D ResNet's BasicBlock / Bottleneck) run both branches on slabs and add them."""
+        if isinstance(m, nn.Sequential):
+            for child in m:
+                x, part = self._run(child, x, part, rank)
+            return x, part
+        if all(hasattr(m, a) for a in ("conv1", "bn1", "conv2", "bn2", "downsample")):
+            idt, ipart = (x, part) if m.downsample is None else self._run(m.downsample, x, part, rank)
+            y, p = self._run(m.conv1, x, part, rank)
+            y = F.relu(self._batchnorm(m.bn1, y))
+            y, p = self._run(m.conv2, y, p, rank)
+            y = self._batchnorm(m.bn2, y)
+            if hasattr(m, "conv3"):
+                y, p = self._run(m.conv3, F.relu(y), p, rank)
+                y = self._batchnorm(m.bn3, y)
+            assert p.bounds == ipart.bounds, "the two branches of a residual block must end on the same slabs"
+            return F.relu(y + idt), p
+        if isinstance(m, nn.Conv3d):
+            assert m.dilation == (1, 1, 1) and m.groups == 1 and m.padding_mode == "zeros", "plain Conv3d only"
+            return slab_conv3d(x, part, rank, m.weight, m.bias, m.stride, m.padding, self.group)
+        if isinstance(m, nn.modules.batchnorm._BatchNorm):
+            return self._batchnorm(m, x), part
+        if isinstance(m, nn.MaxPool3d):
+            assert not m.ceil_mode and _triple(m.dilation) == (1, 1, 1)
+            return slab_max_pool3d(x, part, rank, m.kernel_size, m.stride, m.padding, self.group)
+        if isinstance(m, nn.AvgPool3d):
+            assert not m.ceil_mode and m.count_include_pad
+            return slab_avg_pool3d(x, part, rank, m.kernel_size, m.stride, m.padding, self.group)
+        if isinstance(m, (nn.ReLU, nn.Dropout, nn.Identity, nn.LeakyReLU, nn.Sigmoid, nn.Tanh)):
+            return (F.relu(x) if isinstance(m, nn.ReLU) else m(x)), part
+        raise NotImplementedError(f"{type(m).__name__} has no slab-parallel form")
 
     def _batchnorm(self, m, x):
         if not m.training:
@@ -312,7 +329,7 @@ def halo_bytes(layers: Sequence[Tuple[int, int, int, int]], in_shape: Tuple[int,
 
 
 class SpatialParallelModel(nn.Module):
-    """A ``features`` + head model (the AlexNet3D family, Tiny3DCNN) trained by ALL ranks on the SAME batch, each rank holding a depth
+    """A ``features`` + head model (the AlexNet3D family, Tiny3DCNN) or the 3-D ResNet trained by ALL ranks on the SAME batch, each rank holding a depth
     slab of the activations.  Parameters are replicated; after ``loss.backward()`` call :meth:`reduce_gradients` and step the
     optimizer on every rank -- the replicas stay identical because every rank then applies the same gradients (with dropout in
     the head, seed torch identically on all ranks so that they draw the same masks).
@@ -325,10 +342,19 @@ class SpatialParallelModel(nn.Module):
         super().__init__()
         self.model = model
         self.group = group
-        self.slab_features = SlabParallelFeatures(model.features, group)
-        head = getattr(model, "classifier", None) or getattr(model, "regressor", None)
-        if head is None:
-            raise ValueError("expected a model with `features` and a `classifier` / `regressor` head")
+        if hasattr(model, "features"):
+            features = model.features
+            head = getattr(model, "classifier", None) or getattr(model, "regressor", None)
+        elif all(hasattr(model, a) for a in ("conv1", "bn1", "maxpool", "layer1", "layer2", "layer3", "avgpool", "fc", "fc2")):
+            # the 3-D ResNet (models.volumetric.ResNet3D_l3): stem + three stages + average pool, then fc -> fc2
+            features = nn.Sequential(model.conv1, model.bn1, model.relu, model.maxpool, model.layer1, model.layer2, model.layer3, model.avgpool)
+            head = nn.Sequential(model.fc, model.fc2)
+        else:
+            features = head = None
+        if features is None or head is None:
+            raise ValueError("expected `features` + `classifier` / `regressor`, or the 3-D ResNet layout")
+        self._features = features
+        self.slab_features = SlabParallelFeatures(features, group)
         self.head = head
 
     def forward(self, x_full: torch.Tensor) -> torch.Tensor:
@@ -340,4 +366,4 @@ class SpatialParallelModel(nn.Module):
     def reduce_gradients(self) -> None:
         """Feature-extractor gradients are per-slab shares -> summed over ranks.  The head saw the full feature map on every rank, so
         its gradients are already complete and identical."""
-        allreduce_gradients(list(self.model.features.parameters()), self.group)
+        allreduce_gradients(list(self._features.parameters()), self.group)

@@ -85,6 +85,24 @@ def main():
     if rank == 0:
         print(f"spatial-parallel training: world={world} worst abs err after 3 steps {float(t):.3e}", flush=True)
     ok = ok and float(t) < 1e-9
+    # the 3-D ResNet (residual blocks, strided 1x1x1 projections, padded max-pool, average pool) in spatial-parallel mode
+    from neuroimagedisttraining_b200.models.volumetric import resnet3d_18
+    torch.manual_seed(4)
+    ref_res = resnet3d_18(1, in_shape=(45, 41, 43)).double()
+    sp_res = copy.deepcopy(ref_res)
+    spr = SpatialParallelModel(sp_res)
+    xb = torch.randn(2, 1, 45, 41, 43, dtype=torch.float64)
+    yb = (torch.rand(2, 1) > 0.5).double()
+    crit(ref_res(xb), yb).backward()
+    crit(spr(xb), yb).backward()
+    spr.reduce_gradients()
+    worst = max(float((p.grad - q.grad).abs().max()) for p, q in zip(sp_res.parameters(), ref_res.parameters()))
+    worst = max(worst, max(float((a.double() - b.double()).abs().max()) for a, b in zip(sp_res.buffers(), ref_res.buffers())))
+    t = torch.tensor([worst], dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        print(f"spatial-parallel 3-D ResNet: world={world} worst abs err (gradients, BN statistics) {float(t):.3e}", flush=True)
+    ok = ok and float(t) < 1e-9
     hb = halo_bytes([(1, 5, 2, 0), (64, 3, 3, 0), (64, 3, 1, 0)], (121, 145, 121), 16, max(world, 2))
     ok = ok and len(hb) == 3 and hb[0] > 0
     t = torch.tensor([1.0 if ok else 0.0])
