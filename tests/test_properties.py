@@ -18,7 +18,7 @@ from neuroimagedisttraining_b200.utils.topology import AsymmetricTopologyManager
 
 from helpers import quiet_logger
 
-FAST = settings(max_examples=25, deadline=None)
+FAST = settings(max_examples=25, deadline=None, derandomize=True, database=None)      # same examples on every run
 
 
 # ------------------------------------------------------------------------------ partitioners
