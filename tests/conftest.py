@@ -3,6 +3,9 @@ import sys
 
 import pytest
 
+# no test may hang a run: pytest-timeout (when installed) reads this unless --timeout is given on the command line
+os.environ.setdefault("PYTEST_TIMEOUT", "1200")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
