@@ -315,6 +315,8 @@ def run_reference(a):
     sys.path.insert(0, ROOT)
     from baseline import ref_harness
     why = ref_harness.reference_available()
+    if not why and not torch.cuda.is_available():
+        why = "no CUDA device on this machine (the reference's trainers need one)"
     if why:
         print(json.dumps({"impl": "reference", "unavailable": why}))
         return
