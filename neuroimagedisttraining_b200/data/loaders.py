@@ -213,7 +213,7 @@ def load_partition_data_images(dataset: str, data_dir: Optional[str], partition_
     ytr_np, yte_np = ytr.numpy(), yte.numpy()
     rng = np.random.RandomState(seed)                 # one stream for the partition and the test subsets, like the reference's global one
     py_rng = random.Random(seed)
-    idx_map = partition_labels(ytr_np, partition_method, client_number, partition_alpha, seed, rng=rng, py_rng=py_rng)
+    idx_map = partition_labels(ytr_np, partition_method, client_number, partition_alpha, seed, rng=rng, py_rng=py_rng, n_cls=n_cls)
     stats = {c: {int(k): int(v) for k, v in zip(*np.unique(ytr_np[i], return_counts=True))} for c, i in idx_map.items()}
     local_num, train_local, test_local, val_local = {}, {}, {}, {}
     te_pools = {c: np.where(yte_np == c)[0] for c in range(n_cls)}

@@ -197,19 +197,20 @@ def my_part_partition(y: np.ndarray, n_clients: int, n_shards: int, rng: np.rand
 
 
 def partition_labels(y: np.ndarray, method: str, n_clients: int, alpha: float, seed: int = 0,
-                     rng: Optional[np.random.RandomState] = None, py_rng: Optional[random.Random] = None) -> Dict[int, np.ndarray]:
+                     rng: Optional[np.random.RandomState] = None, py_rng: Optional[random.Random] = None, n_cls: Optional[int] = None) -> Dict[int, np.ndarray]:
     """``rng``: continue an existing numpy stream (the loaders go on to draw the clients' test subsets from it, as the reference
     does from the global stream); default: a fresh ``RandomState(seed)`` == ``np.random.seed(seed)``.  ``py_rng``: likewise for python's
-    ``random`` (``n_cls`` picks classes with it, the validation split samples with it)."""
+    ``random`` (``n_cls`` picks classes with it, the validation split samples with it).  ``n_cls``: number of classes of the dataset
+    (the reference hard-codes 10 / 100 / 200); default: largest label + 1."""
     rng = rng if rng is not None else np.random.RandomState(seed)
     if method == "homo":
         return homo_partition(len(y), n_clients, rng)
     if method == "hetero":
         return hetero_dirichlet_partition(y, n_clients, alpha, rng)
     if method == "dir":
-        return dir_partition(y, n_clients, alpha, rng)
+        return dir_partition(y, n_clients, alpha, rng, n_cls)
     if method == "n_cls":
-        return n_cls_partition(y, n_clients, int(alpha), rng, py_rng=py_rng or random.Random(seed))
+        return n_cls_partition(y, n_clients, int(alpha), rng, n_cls, py_rng=py_rng or random.Random(seed))
     if method == "my_part":
-        return my_part_partition(y, n_clients, int(alpha), rng)
+        return my_part_partition(y, n_clients, int(alpha), rng, n_cls)
     raise ValueError(f"unknown partition method {method!r}")
