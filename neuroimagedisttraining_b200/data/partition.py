@@ -147,6 +147,10 @@ def _draw_by_prior(y: np.ndarray, priors: np.ndarray, sizes: np.ndarray, rng, re
                 elif refill == "full" and len(pools[c]):
                     remaining[c] = len(pools[c])
                 if refill != "none":
+                    # (a class without any sample can never be refilled: give up on this draw when the client's prior
+                    # only covers such classes -- the reference would raise / spin there)
+                    if len(pools[c]) == 0 and not any(priors[j][k] > 0 and len(pools[k]) for k in range(n_cls)):
+                        break
                     if redraws < _MAX_CLASS_REDRAWS:
                         continue
                     break
