@@ -291,3 +291,37 @@ def test_c_abi_header_matches_the_exported_symbols():
         out = subprocess.run(["nm", "-D", "--defined-only", str(native.lib_path())], capture_output=True, text=True).stdout
         exported = {line.split()[-1] for line in out.splitlines() if " T " in line}
         assert exported == header
+
+
+def test_tiny_imagenet_folder_reader_and_loader(tmp_path):
+    """The Tiny-ImageNet folder layout (train/<wnid>/images/*.JPEG, val/images + val_annotations.txt) is decoded once, cached, and
+    feeds the 200-class loader path (``tiny_imagenet/datasets.py:20-145``); 3 classes x 4 images of 64x64 stand in for the dataset."""
+    from PIL import Image
+    from neuroimagedisttraining_b200.data.loaders import load_partition_data_images
+    from neuroimagedisttraining_b200.data.tiny_imagenet import TinyImageNet
+    rng = np.random.RandomState(0)
+    root = tmp_path / "tiny"
+    wnids = ["n01", "n02", "n03"]
+    ann = []
+    for ci, w in enumerate(wnids):
+        (root / "train" / w / "images").mkdir(parents=True)
+        for i in range(4):
+            Image.fromarray(np.full((64, 64, 3), 40 * ci + i, np.uint8)).save(root / "train" / w / "images" / f"{w}_{i}.JPEG", quality=100)
+    (root / "val" / "images").mkdir(parents=True)
+    for i in range(6):
+        Image.fromarray(rng.randint(0, 255, (64, 64, 3)).astype(np.uint8)).save(root / "val" / "images" / f"val_{i}.JPEG")
+        ann.append(f"val_{i}.JPEG\t{wnids[i % 3]}\t0\t0\t10\t10")
+    (root / "val" / "val_annotations.txt").write_text("\n".join(ann) + "\n")
+    tr = TinyImageNet(str(root), True)
+    assert len(tr) == 12 and sorted(set(tr.targets.tolist())) == [0, 1, 2] and tr.data.shape == (12, 64, 64, 3)
+    assert (root / "train_cache.pkl").exists()
+    x, y = tr.tensors()
+    assert x.shape == (12, 3, 64, 64) and x.dtype == torch.float32 and y.dtype == torch.int64
+    again = TinyImageNet(str(root), True, dataidxs=np.array([0, 5, 11]))                     # from the cache, truncated
+    assert len(again) == 3 and np.array_equal(again.data, tr.data[[0, 5, 11]])
+    va = TinyImageNet(str(root), False)
+    assert va.targets.tolist() == [0, 1, 2, 0, 1, 2]
+    ds = load_partition_data_images("tiny", str(root), "homo", 0, 2, 4)
+    assert ds[0] == 12 and ds[1] == 6 and sum(ds[4].values()) == 12
+    xb, yb = next(iter(ds[5][0]))
+    assert xb.shape[1:] == (3, 64, 64)
