@@ -175,19 +175,37 @@ def synthetic_image_dataset(n_train: int, n_test: int, n_cls: int, shape=(3, 32,
     return make(n_train), make(n_test)
 
 
-def _load_torchvision(dataset: str, data_dir: str):
-    import torchvision  # local import: optional dependency
-    stats = {"cifar10": ((0.4914, 0.4822, 0.4465), (0.2470, 0.2435, 0.2616)),
-             "cifar100": ((0.5071, 0.4865, 0.4409), (0.2673, 0.2564, 0.2762))}[dataset]
-    cls = {"cifar10": torchvision.datasets.CIFAR10, "cifar100": torchvision.datasets.CIFAR100}[dataset]
-    tr = cls(data_dir, train=True, download=False)
-    te = cls(data_dir, train=False, download=False)
-    def conv(ds):
-        x = torch.from_numpy(ds.data).permute(0, 3, 1, 2).float() / 255.0
-        m = torch.tensor(stats[0]).view(1, 3, 1, 1)
-        s = torch.tensor(stats[1]).view(1, 3, 1, 1)
-        return (x - m) / s, torch.tensor(ds.targets, dtype=torch.int64)
-    return conv(tr), conv(te)
+_CIFAR_STATS = {"cifar10": ((0.49139968, 0.48215827, 0.44653124), (0.24703233, 0.24348505, 0.26158768)),
+                "cifar100": ((0.5071, 0.4865, 0.4409), (0.2673, 0.2564, 0.2762))}
+
+
+def _load_cifar(dataset: str, data_dir: str):
+    """The python-pickle distribution of CIFAR-10 / CIFAR-100 (``cifar-10-batches-py/{data_batch_1..5,test_batch}``,
+    ``cifar-100-python/{train,test}``; what torchvision downloads for the reference, ``cifar10/datasets.py``), read directly:
+    uint8 ``[N, 3072]`` rows -> float ``[N, 3, 32, 32]`` normalised with the reference's channel statistics
+    (``cifar10/data_loader.py:44-45``).  ``data_dir`` may be the dataset folder itself or its parent."""
+    import os
+    import pickle
+    sub = "cifar-10-batches-py" if dataset == "cifar10" else "cifar-100-python"
+    root = os.path.join(data_dir, sub) if os.path.isdir(os.path.join(data_dir, sub)) else data_dir
+    train_files = [f"data_batch_{i}" for i in range(1, 6)] if dataset == "cifar10" else ["train"]
+    test_files = ["test_batch"] if dataset == "cifar10" else ["test"]
+    label_key = b"labels" if dataset == "cifar10" else b"fine_labels"
+    mean, std = (torch.tensor(v).view(1, 3, 1, 1) for v in _CIFAR_STATS[dataset])
+
+    def read(files):
+        xs, ys = [], []
+        for name in files:
+            path = os.path.join(root, name)
+            if not os.path.exists(path):
+                raise FileNotFoundError(f"{dataset}: {path} not found (expected the python-pickle layout {sub}/{name})")
+            with open(path, "rb") as f:
+                d = pickle.load(f, encoding="bytes")
+            xs.append(np.asarray(d[b"data"], dtype=np.uint8).reshape(-1, 3, 32, 32))
+            ys.append(np.asarray(d[label_key], dtype=np.int64))
+        x = torch.from_numpy(np.concatenate(xs)).float() / 255.0
+        return (x - mean) / std, torch.from_numpy(np.concatenate(ys))
+    return read(train_files), read(test_files)
 
 
 def load_partition_data_images(dataset: str, data_dir: Optional[str], partition_method: str, partition_alpha: float,
@@ -200,16 +218,13 @@ def load_partition_data_images(dataset: str, data_dir: Optional[str], partition_
     training transform on (random crop with 4-pixel padding + horizontal flip, optional Cutout) for the clients' training loaders."""
     n_cls = {"cifar10": 10, "cifar100": 100, "tiny": 200}[dataset]
     shape = (3, 64, 64) if dataset == "tiny" else (3, 32, 32)
-    try:
-        if data_dir is None:
-            raise FileNotFoundError
-        if dataset == "tiny":
-            from .tiny_imagenet import TinyImageNet
-            (xtr, ytr), (xte, yte) = TinyImageNet(data_dir, True).tensors(), TinyImageNet(data_dir, False).tensors()
-        else:
-            (xtr, ytr), (xte, yte) = _load_torchvision(dataset, data_dir)
-    except Exception:
+    if data_dir is None:                                 # no files: seeded synthetic stand-in of the same shape
         (xtr, ytr), (xte, yte) = synthetic_image_dataset(synthetic_size[0], synthetic_size[1], n_cls, shape, seed)
+    elif dataset == "tiny":                              # a given directory must load -- never a silent switch to synthetic data
+        from .tiny_imagenet import TinyImageNet
+        (xtr, ytr), (xte, yte) = TinyImageNet(data_dir, True).tensors(), TinyImageNet(data_dir, False).tensors()
+    else:
+        (xtr, ytr), (xte, yte) = _load_cifar(dataset, data_dir)
     ytr_np, yte_np = ytr.numpy(), yte.numpy()
     rng = np.random.RandomState(seed)                 # one stream for the partition and the test subsets, like the reference's global one
     py_rng = random.Random(seed)

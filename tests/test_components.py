@@ -325,3 +325,32 @@ def test_tiny_imagenet_folder_reader_and_loader(tmp_path):
     assert ds[0] == 12 and ds[1] == 6 and sum(ds[4].values()) == 12
     xb, yb = next(iter(ds[5][0]))
     assert xb.shape[1:] == (3, 64, 64)
+
+
+def test_cifar_pickle_reader_and_no_silent_fallback(tmp_path):
+    """CIFAR-10 / 100 from the python-pickle layout; a given but wrong ``data_dir`` raises instead of switching to synthetic data."""
+    import pickle
+    from neuroimagedisttraining_b200.data.loaders import load_partition_data_images
+    rng = np.random.RandomState(0)
+    d10 = tmp_path / "c10" / "cifar-10-batches-py"
+    d10.mkdir(parents=True)
+    rows = {}
+    for name in [f"data_batch_{i}" for i in range(1, 6)] + ["test_batch"]:
+        rows[name] = (rng.randint(0, 256, (20, 3072)).astype(np.uint8), rng.randint(0, 10, 20).tolist())
+        with open(d10 / name, "wb") as f:
+            pickle.dump({b"data": rows[name][0], b"labels": rows[name][1]}, f)
+    ds = load_partition_data_images("cifar10", str(tmp_path / "c10"), "homo", 0, 4, 8)
+    assert ds[0] == 100 and ds[1] == 20 and sum(ds[4].values()) == 100
+    x0 = ds[2].x[0]                                       # first training image, normalised with the reference's statistics
+    mean, std = torch.tensor([0.49139968, 0.48215827, 0.44653124]).view(3, 1, 1), torch.tensor([0.24703233, 0.24348505, 0.26158768]).view(3, 1, 1)
+    want = (torch.from_numpy(rows["data_batch_1"][0][0].reshape(3, 32, 32)).float() / 255 - mean) / std
+    torch.testing.assert_close(x0, want)
+    d100 = tmp_path / "cifar-100-python"
+    d100.mkdir()
+    for name, n in (("train", 60), ("test", 30)):
+        with open(d100 / name, "wb") as f:
+            pickle.dump({b"data": rng.randint(0, 256, (n, 3072)).astype(np.uint8), b"fine_labels": rng.randint(0, 100, n).tolist()}, f)
+    ds = load_partition_data_images("cifar100", str(d100), "homo", 0, 3, 8)          # the dataset folder itself also works
+    assert ds[0] == 60 and ds[1] == 30
+    with pytest.raises(FileNotFoundError, match="python-pickle layout"):
+        load_partition_data_images("cifar10", str(tmp_path / "nowhere"), "homo", 0, 2, 8)
