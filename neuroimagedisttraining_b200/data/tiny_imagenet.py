@@ -13,7 +13,7 @@ import torch
 class TinyImageNet:
     """``root/train/<wnid>/images/*.JPEG`` and ``root/val/images/*.JPEG`` + ``val_annotations.txt``.  ``tensors()`` returns
     ``(x float [N,3,64,64] normalised, y int64 [N])``; decoded arrays are cached as ``<root>/<split>_cache.pkl``."""
-    MEAN, STD = (0.4802, 0.4481, 0.3975), (0.2770, 0.2691, 0.2821)
+    MEAN, STD = (0.5, 0.5, 0.5), (0.5, 0.5, 0.5)        # the reference's normalisation (tiny_imagenet/data_loader.py:48-49)
 
     def __init__(self, root: str, train: bool = True, dataidxs: Optional[np.ndarray] = None):
         self.root, self.split, self.dataidxs = root, "train" if train else "val", dataidxs
