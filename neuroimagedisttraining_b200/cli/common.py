@@ -63,7 +63,9 @@ def add_common_args(p: argparse.ArgumentParser, *, model="3DCNN", dataset="ABCD"
     g.add_argument("--results_dir", default="results")
     g.add_argument("--synthetic_subjects", type=int, default=0, help="without --data_dir: number of synthetic subjects / training images (default 20 per client for ABCD, 2000 images)")
     g.add_argument("--in_shape", default="121,145,121", help="volume shape D,H,W")
-    g.add_argument("--augment", action="store_true", help="image datasets: random crop (padding 4) + horizontal flip on training batches, as the reference's transforms")
+    g.add_argument("--augment", action="store_true", help="image datasets: random crop (padding 4) + horizontal flip on training batches, as the "
+                                                          "reference's transforms; on by default when --data_dir points at real images")
+    g.add_argument("--no_augment", action="store_true", help="image datasets: no training augmentation even on real data")
     g.add_argument("--cutout", type=int, default=0, help="with --augment: side of the Cutout square (the reference keeps Cutout(16) commented out)")
     g.add_argument("--labels_file", default=None, help="ABCD: HDF5 file with y / site when they are not in --data_dir (the reference keeps "
                                                        "volumes in alldatain8bitsnormalized.h5 and labels in dataset_all_labels_site.h5)")
@@ -145,7 +147,7 @@ def setup(args, prefix: str, extra_identity: Optional[list] = None, loss_kind: O
         class_num, loss_kind = 1, loss_kind or "bce"
     else:
         dataset = load_partition_data_images(args.dataset, args.data_dir, args.partition_method if args.partition_method != "site" else "dir",
-                                             args.partition_alpha, args.client_num_in_total, args.batch_size, logger, seed=args.seed, val_split=val_split, augment=args.augment, cutout=args.cutout,
+                                             args.partition_alpha, args.client_num_in_total, args.batch_size, logger, seed=args.seed, val_split=val_split, augment=(args.augment or bool(args.data_dir)) and not args.no_augment, cutout=args.cutout,
                                              **({"synthetic_size": (args.synthetic_subjects, max(args.synthetic_subjects // 4, args.client_num_in_total))}
                                                 if args.synthetic_subjects else {}))
         class_num, loss_kind = {"cifar10": 10, "cifar100": 100, "tiny": 200}[args.dataset], loss_kind or "ce"
