@@ -11,3 +11,4 @@ from .turboaggregate import TurboAggregateAPI  # noqa: F401
 
 dispflAPI = DisPFLAPI   # the reference's class names
 dpsgdAPI = DPSGDAPI
+FEDFOMOAPI = FedFomoAPI
