@@ -354,3 +354,28 @@ def test_cifar_pickle_reader_and_no_silent_fallback(tmp_path):
     assert ds[0] == 60 and ds[1] == 30
     with pytest.raises(FileNotFoundError, match="python-pickle layout"):
         load_partition_data_images("cifar10", str(tmp_path / "nowhere"), "homo", 0, 2, 8)
+
+
+def test_phase_timer_and_cpu_batch_stager():
+    import time
+    from neuroimagedisttraining_b200.data.loaders import IndexLoader
+    from neuroimagedisttraining_b200.runtime.staging import BatchStager
+    from neuroimagedisttraining_b200.utils.timing import PhaseTimer
+    t = PhaseTimer("cpu")
+    for _ in range(3):
+        with t.phase("train"):
+            time.sleep(0.01)
+    with pytest.raises(RuntimeError):
+        with t.phase("eval"):                              # a phase that raises is still accounted for
+            raise RuntimeError("boom")
+    s = t.summary()
+    assert s["train"]["calls"] == 3 and s["train"]["total_s"] >= 0.03 and s["eval"]["calls"] == 1
+    store = SyntheticABCD(12, (6, 7, 5), n_sites=2, seed=0, site_sizes=[6, 6])
+    stager = BatchStager(store, torch.device("cpu"), batch_size=4)
+    idx = np.array([9, 2, 7, 0, 11, 5])
+    loader = IndexLoader(idx, store.labels[idx], store.sites[idx], 4, shuffle=False)
+    got = list(stager.iterate(loader))
+    assert [len(y) for _, y in got] == [4, 2]
+    first = np.sort(idx[:4])                               # volumes come in sorted-index order, labels re-read to match (as the reference)
+    want_x, want_y = store.fetch(first)
+    assert torch.equal(got[0][0], want_x) and torch.equal(got[0][1], want_y)
