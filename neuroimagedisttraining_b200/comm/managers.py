@@ -7,6 +7,7 @@ import logging
 import threading
 from typing import Callable, Dict, Optional
 
+import torch
 
 from .base import BaseCommunicationManager, GrpcCommManager, InProcessCommManager, MqttCommManager, Observer, TorchDistCommManager
 from .message import Message
@@ -136,3 +137,88 @@ class FedAvgClientManager(ClientManager):
     def _on_finish(self, msg: Message):
         self.final_state = msg.get(Message.MSG_ARG_KEY_MODEL_PARAMS)
         self.finish()
+
+
+# ---------------------------------------------------------------------- message-passing SalientGrads
+MSG_SCORE_REQUEST, MSG_SCORES, MSG_MASK = "s2c_score_request", "c2s_scores", "s2c_mask"
+
+
+class SalientGradsServerManager(FedAvgServerManager):
+    """SalientGrads over messages (``sailentgrads_api.py:47-66,86-147`` as a protocol): first every client scores the initial model
+    and uploads ``|dL/dw * w|`` per prunable tensor; the server averages the scores unweighted, keeps the global top
+    ``dense_ratio`` fraction (ties kept, as ``snip.get_mask_from_grads``) and sends the mask; then FedAvg rounds run, with the
+    aggregated model multiplied by the mask before it goes out again."""
+
+    def __init__(self, state_dict, rounds: int, dense_ratio: float, prunable: Optional[Callable[[str], bool]] = None, **kw):
+        super().__init__(state_dict, rounds, **kw)
+        self.dense_ratio = float(dense_ratio)
+        self.prunable = prunable or (lambda k: k.endswith("weight") and self.state[k].dim() > 1)
+        self.scores: Dict[int, dict] = {}
+        self.mask: Optional[dict] = None
+
+    def register_message_receive_handlers(self):
+        super().register_message_receive_handlers()
+        self.register_message_receive_handler(MSG_SCORES, self._on_scores)
+
+    def start(self):
+        for c in range(1, self.size):
+            m = Message(MSG_SCORE_REQUEST, 0, c)
+            m.add_params(Message.MSG_ARG_KEY_MODEL_PARAMS, self.state)
+            self.send_message(m)
+
+    def _on_scores(self, msg: Message):
+        self.scores[msg.get_sender_id()] = msg.get("scores")
+        if len(self.scores) < self.size - 1:
+            return
+        names = [k for k in self.state if self.prunable(k)]
+        mean = {k: sum(self.scores[c][k].float() for c in sorted(self.scores)) / len(self.scores) for k in names}
+        flat = torch.cat([mean[k].flatten() for k in names])
+        norm = flat.sum()
+        flat = flat / norm
+        k = int(flat.numel() * self.dense_ratio)
+        thr = torch.topk(flat, k, sorted=True)[0][-1] if k > 0 else torch.tensor(float("inf"))
+        self.mask = {n: ((mean[n] / norm) >= thr).float() for n in names}
+        for c in range(1, self.size):
+            m = Message(MSG_MASK, 0, c)
+            m.add_params("mask", self.mask)
+            m.add_params(Message.MSG_ARG_KEY_MODEL_PARAMS, self.state)
+            self.send_message(m)
+
+    def _on_upload(self, msg: Message):
+        before = self.round
+        super()._on_upload(msg)
+        if self.round != before and self.mask is not None:
+            # every upload is already masked (clients multiply after each step), so the average is too up to round-off; pin the zeros
+            for k, m in self.mask.items():
+                self.state[k] = self.state[k] * m
+
+
+class SalientGradsClientManager(FedAvgClientManager):
+    """``score_fn(state_dict) -> {name: |g*w| tensor}`` for the saliency phase; ``train_fn(state_dict, mask) -> (n, new_state_dict)``
+    afterwards (the client applies the mask after every step, as the reference's trainer does)."""
+
+    def __init__(self, score_fn, train_fn, **kw):
+        super().__init__(train_fn, **kw)
+        self.score_fn = score_fn
+        self.mask = None
+
+    def register_message_receive_handlers(self):
+        super().register_message_receive_handlers()
+        self.register_message_receive_handler(MSG_SCORE_REQUEST, self._on_score_request)
+        self.register_message_receive_handler(MSG_MASK, self._on_mask)
+
+    def _on_score_request(self, msg: Message):
+        up = Message(MSG_SCORES, self.rank, 0)
+        up.add_params("scores", self.score_fn(msg.get(Message.MSG_ARG_KEY_MODEL_PARAMS)))
+        self.send_message(up)
+
+    def _on_mask(self, msg: Message):
+        self.mask = msg.get("mask")
+        self._on_model(msg)
+
+    def _on_model(self, msg: Message):
+        n, state = self.train_fn(msg.get(Message.MSG_ARG_KEY_MODEL_PARAMS), self.mask)
+        up = Message(MSG_UPLOAD, self.rank, 0)
+        up.add_params("num_samples", n)
+        up.add_params(Message.MSG_ARG_KEY_MODEL_PARAMS, state)
+        self.send_message(up)

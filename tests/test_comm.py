@@ -99,3 +99,70 @@ def test_mqtt_paho_request_reports_missing_dependency():
     except ImportError:
         with pytest.raises(ImportError, match="paho-mqtt"):
             MqttCommManager("127.0.0.1", 1883, 0, 1, impl="paho")
+
+
+def test_salientgrads_over_messages_matches_a_sequential_oracle():
+    """Saliency phase (clients upload |g*w|, server emits the global top-k mask) + masked FedAvg rounds over the message runtime."""
+    import copy
+    import torch.nn as nn
+    from neuroimagedisttraining_b200.comm import SalientGradsClientManager, SalientGradsServerManager
+    from neuroimagedisttraining_b200.ops import reference
+    torch.manual_seed(0)
+    net = nn.Sequential(nn.Linear(10, 8), nn.ReLU(), nn.Linear(8, 1))
+    init = copy.deepcopy(net.state_dict())
+    data = [(torch.randn(12 + 4 * i, 10), torch.randn(12 + 4 * i, 1)) for i in range(3)]
+
+    def score_fn(i):
+        def fn(sd):
+            m = copy.deepcopy(net); m.load_state_dict(sd)
+            nn.functional.mse_loss(m(data[i][0]), data[i][1]).backward()
+            return {k: (p.grad * p).abs().detach() for k, p in m.named_parameters() if p.dim() > 1}
+        return fn
+
+    def train_fn(i):
+        def fn(sd, mask):
+            m = copy.deepcopy(net); m.load_state_dict(sd)
+            opt = torch.optim.SGD(m.parameters(), lr=0.05)
+            for _ in range(2):
+                opt.zero_grad(); nn.functional.mse_loss(m(data[i][0]), data[i][1]).backward(); opt.step()
+                with torch.no_grad():
+                    for k, p in m.named_parameters():
+                        if k in mask:
+                            p.mul_(mask[k])
+            return len(data[i][0]), {k: v.detach().clone() for k, v in m.state_dict().items()}
+        return fn
+
+    size, rounds, dense = 4, 2, 0.5
+    server = SalientGradsServerManager(init, rounds, dense, comm=InProcessCommManager(0, size, network="sg"), rank=0, size=size)
+    clients = [SalientGradsClientManager(score_fn(i), train_fn(i), comm=InProcessCommManager(i + 1, size, network="sg"), rank=i + 1, size=size)
+               for i in range(3)]
+    threads = [threading.Thread(target=m.run, daemon=True) for m in [server] + clients]
+    for t in threads:
+        t.start()
+    time.sleep(0.2)
+    server.start()
+    assert server.done.wait(30)
+    for t in threads:
+        t.join(10)
+    # oracle: the same protocol, sequentially
+    scores = [score_fn(i)(init) for i in range(3)]
+    names = list(scores[0])
+    mean = torch.cat([sum(s[k] for s in scores).flatten() / 3 for k in names])
+    mask_flat = torch.empty_like(mean)
+    reference.global_topk_mask(mean, [(0, mean.numel())], dense, mask_flat)
+    off, mask = 0, {}
+    for k in names:
+        mask[k] = mask_flat[off:off + scores[0][k].numel()].view_as(scores[0][k]); off += scores[0][k].numel()
+    state = init
+    for _ in range(rounds):
+        ups = [train_fn(i)(state, mask) for i in range(3)]
+        total = sum(n for n, _ in ups)
+        state = {k: sum(w[k] * (n / total) for n, w in ups) for k in state}
+    for k in names:
+        assert torch.equal(server.mask[k], mask[k])
+        assert float((server.state[k] * (1 - mask[k])).abs().sum()) == 0.0
+    kept = sum(float(m.sum()) for m in server.mask.values())
+    assert kept >= int(mean.numel() * dense)
+    for k in state:
+        torch.testing.assert_close(server.state[k], state[k], rtol=1e-5, atol=1e-6)
+        torch.testing.assert_close(clients[1].final_state[k], state[k], rtol=1e-5, atol=1e-6)
