@@ -379,3 +379,16 @@ def test_phase_timer_and_cpu_batch_stager():
     first = np.sort(idx[:4])                               # volumes come in sorted-index order, labels re-read to match (as the reference)
     want_x, want_y = store.fetch(first)
     assert torch.equal(got[0][0], want_x) and torch.equal(got[0][1], want_y)
+
+
+def test_roofline_script_on_the_committed_step_profile():
+    import importlib.util
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("roofline", os.path.join(root, "scripts", "roofline.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    L = mod.layer_table(16)
+    assert [r["M"] for r in L] == [16 * 247151, 16 * 6069, 16 * 175, 16 * 175, 16 * 175] and [r["K"] for r in L] == [125, 1728, 3456, 5184, 5184]
+    text = mod.main([os.path.join(root, "profiles", "profile_step_v18.txt")])
+    assert "| `conv3d_fprop_tc[1]` |" in text and "| math |" in text and "| memory |" in text
