@@ -73,6 +73,9 @@ def add_common_args(p: argparse.ArgumentParser, *, model="3DCNN", dataset="ABCD"
                    help="FedAvg / SalientGrads: robust-aggregation defence applied to every client upload")
     g.add_argument("--norm_bound", type=float, default=5.0)
     g.add_argument("--stddev", type=float, default=0.025)
+    g.add_argument("--spatial_parallel", action="store_true",
+                   help="under torchrun: all ranks train every client together, each holding a depth slab of the activations "
+                        "(for volumes / batches that do not fit one device); PyTorch engine")
     g.add_argument("--rescale", action="store_true", help="ABCD: cut the site-ordered data into client_num_in_total equal shards")
     g.add_argument("--correct_eval_loss", action="store_true", help="evaluate BCEWithLogits(logit) instead of the reference's BCEWithLogits(sigmoid(logit))")
     return p
@@ -127,8 +130,13 @@ def setup(args, prefix: str, extra_identity: Optional[list] = None, loss_kind: O
     args.client_num_per_round = max(1, int(args.client_num_in_total * args.frac))
     args.identity = build_identity(args, prefix, extra_identity)
     ctx = init_distributed(device=args.device)
+    spatial = bool(getattr(args, "spatial_parallel", False)) and ctx.is_distributed
+    if spatial:
+        from ..parallel import ReplicatedContext
+        ctx = ReplicatedContext.of(ctx)
     device = ctx.device
-    log_path = os.path.join(args.log_dir, args.dataset, args.identity + (f".rank{ctx.rank}" if ctx.rank else "") + ".log")
+    real_rank = getattr(ctx, "real_rank", ctx.rank)
+    log_path = os.path.join(args.log_dir, args.dataset, args.identity + (f".rank{real_rank}" if real_rank else "") + ".log")
     logger = logger_config(log_path=log_path, logging_name=args.identity, console=ctx.is_main)
     logger.info(args)
     logger.info(device)
@@ -154,7 +162,10 @@ def setup(args, prefix: str, extra_identity: Optional[list] = None, loss_kind: O
     model = create_model(args.model, class_num, in_shape, args.dataset)
     logger.info(model)
     engine = None
-    if device.type == "cuda" and args.engine in ("auto", "b200") and store is not None:
+    if spatial:
+        from ..fl.engine import SpatialTorchEngine
+        engine = SpatialTorchEngine(model, device, loss_kind=loss_kind, volumetric=store is not None, input_scale=getattr(store, "scale", 1.0))
+    elif device.type == "cuda" and args.engine in ("auto", "b200") and store is not None:
         try:
             from ..ops.engines import make_native_engine
             engine = make_native_engine(model, device, max_batch=args.batch_size, input_scale=store.scale, seed=args.seed)

@@ -136,3 +136,41 @@ class TorchEngine:
             loss = F.cross_entropy(logits, y.long(), reduction="sum")
             correct = (logits.argmax(1) == y.long()).float().sum()
         counters.buf += torch.stack([correct.double(), loss.double(), torch.tensor(float(y.shape[0]), dtype=torch.float64, device=self.device)])
+
+
+class SpatialTorchEngine(TorchEngine):
+    """:class:`TorchEngine` whose forward / backward run depth-slab parallel over ALL ranks of the default process group
+    (:class:`~..parallel.spatial.SpatialParallelModel`): every rank executes the same FL programme on the same clients, holds a slab
+    of each activation, and ends every step with identical gradients (feature-extractor shares are summed over ranks), so the
+    replicas of the model never diverge.  For one client whose activations do not fit a single device."""
+
+    def __init__(self, model: nn.Module, device, **kw):
+        super().__init__(model, device, **kw)
+        from ..parallel.spatial import SpatialParallelModel
+        self.spm = SpatialParallelModel(self.model)
+
+    def compute_grads(self, x, y, train_mode: bool = True) -> torch.Tensor:
+        self.model.train(train_mode)
+        self.grad.flat.zero_()
+        for name, p in self.model.named_parameters():
+            if p.grad is None or p.grad.data_ptr() != self.grad.view(name).data_ptr():
+                p.grad = self.grad.view(name)
+        out = self.spm(self._prep(x))
+        loss = self._loss(out.float() if torch.is_tensor(out) else [o.float() for o in out], y)
+        loss.backward()
+        self.spm.reduce_gradients()
+        return loss.detach()
+
+    @torch.no_grad()
+    def eval_batch(self, x, y, counters: EvalCounters, double_sigmoid: bool = True) -> None:
+        self.model.eval()
+        logits = self.spm(self._prep(x))
+        if isinstance(logits, (list, tuple)):
+            logits = logits[0]
+        y = y.to(self.device)
+        if self.loss_kind == "bce":
+            correct, loss = ops.reference.bce_eval_counters(logits, y, double_sigmoid)
+        else:
+            loss = F.cross_entropy(logits, y.long(), reduction="sum")
+            correct = (logits.argmax(1) == y.long()).float().sum()
+        counters.buf += torch.stack([correct.double(), loss.double(), torch.tensor(float(y.shape[0]), dtype=torch.float64, device=self.device)])

@@ -82,6 +82,23 @@ def bind_to_gpu_numa(dev: torch.device) -> Optional[int]:
         return None
 
 
+@dataclass
+class ReplicatedContext(DistContext):
+    """Every rank runs the SAME federated programme on the same clients (the ranks cooperate inside each client's forward /
+    backward, see :mod:`.spatial`): for the orchestrators this is a one-rank world -- no client placement, no cross-rank
+    aggregation -- but only the real rank 0 writes logs, metrics and checkpoints."""
+    real_rank: int = 0
+    real_world_size: int = 1
+
+    @property
+    def is_main(self) -> bool:
+        return self.real_rank == 0
+
+    @classmethod
+    def of(cls, ctx: DistContext) -> "ReplicatedContext":
+        return cls(0, 1, ctx.local_rank, ctx.device, ctx.backend, ctx.group, real_rank=ctx.rank, real_world_size=ctx.world_size)
+
+
 def init_distributed(device: Optional[str] = None, backend: Optional[str] = None) -> DistContext:
     """Read RANK/LOCAL_RANK/WORLD_SIZE/MASTER_* (torchrun) and join the process group."""
     world = int(os.environ.get("WORLD_SIZE", "1"))

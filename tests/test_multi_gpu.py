@@ -70,3 +70,32 @@ def test_fused_symmetric_aggregation_matches_nccl():
     r = _torchrun("dist_worker_sym_agg.py", min(n, 8))
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "RESULT ok=True" in r.stdout, r.stdout[-2000:]
+
+
+def test_spatial_parallel_cli_run_equals_the_single_process_run(tmp_path):
+    """``--spatial_parallel`` under torchrun (2 gloo ranks): both ranks train every client together on depth slabs; the checkpointed
+    global model and the accuracy series equal the plain one-process run; only the real rank 0 writes files."""
+    import json
+    common = ["--model", "tiny3DCNN", "--in_shape", "32,32,32", "--client_num_in_total", "3", "--synthetic_subjects", "30", "--batch_size", "4",
+              "--epochs", "1", "--comm_round", "2", "--device", "cpu", "--frac", "1.0", "--lr", "0.02", "--checkpoint_every", "1"]
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
+    outs = {}
+    for tag, launcher in (("one", [sys.executable, "-m"]),
+                          ("two", [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                                   "--master-port", str(29800 + os.getpid() % 100), "-m"])):
+        d = tmp_path / tag
+        cmd = launcher + ["neuroimagedisttraining_b200.cli.main_sailentgrads"] + common + ["--log_dir", str(d / "LOG"), "--checkpoint_path", str(d / "ck.pt")]
+        if tag == "two":
+            cmd.append("--spatial_parallel")
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=400, env=env, cwd=ROOT)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+        files = os.listdir(d / "LOG" / "ABCD")
+        assert sum(f.endswith(".jsonl") for f in files) == 1
+        summary = [json.loads(l) for l in open(d / "LOG" / "ABCD" / next(f for f in files if f.endswith(".jsonl")))][-1]
+        outs[tag] = (torch.load(d / "ck.pt", weights_only=False), summary)
+    (ck1, s1), (ck2, s2) = outs["one"], outs["two"]
+    assert ck1["round"] == ck2["round"] == 1
+    for k, v in ck1["state_dict"].items():
+        torch.testing.assert_close(ck2["state_dict"][k].float(), v.float(), rtol=1e-4, atol=1e-5, msg=lambda m: f"{k}: {m}")
+    assert all(torch.equal(ck1["mask"][k], ck2["mask"][k]) for k in ck1["mask"])
+    assert s1["global_test_acc"] == s2["global_test_acc"] and s1["person_test_acc"] == s2["person_test_acc"]
