@@ -181,12 +181,80 @@ def timed_rounds(fn, k, ctx, device):
     return float(t.item())
 
 
+def config_dict(a, shape, samples_per_round):
+    """The benchmark configuration, identical for both arms (what differs between them -- engine, staging, aggregation,
+    parallelism -- is reported beside it, not inside)."""
+    return {"model": "AlexNet3D_Dropout(1 logit)" if a.model == "alexnet3d" else "ResNet3D_l3(BasicBlock,[2,2,2], 1 logit, FC sized from the input)",
+            "algorithm": ("SalientGrads dense_ratio=%g" % a.dense_ratio) if a.algo == "salientgrads" else "FedAvg",
+            "clients": a.clients, "clients_per_round": a.clients, "local_epochs": a.epochs, "batch": a.batch, "global_batch": a.batch,
+            "seq_len": "x".join(map(str, shape)), "train_samples_per_round": samples_per_round,
+            "sgd_steps_per_round": a.epochs * a.clients * (-(-(a.per_site - a.per_site // 5) // a.batch)),
+            "eval_samples_per_round": 2 * a.clients * (a.per_site // 5),
+            "step_definition": "one FL communication round (train + aggregate + eval of all clients)",
+            "l2_policy": "inputs larger than L2 (506 MB conv1 activations per SGD step)"}
+
+
+def agg_check(api, ctx, device):
+    """Outside the timed region: the fused symmetric-memory collectives against (a) the same sums formed in rank order from
+    all-gathered partials -- what the P2P kernel computes, so the difference must be exactly 0 there -- and (b) the NCCL
+    all_reduce path.  Returns the dict that goes into the JSON line; ``ok`` False makes the run exit 1."""
+    import torch.distributed as dist
+    from neuroimagedisttraining_b200 import ops
+    from neuroimagedisttraining_b200.parallel.aggregation import Aggregator
+    from neuroimagedisttraining_b200.runtime.slab import ParamSlab
+    fused = getattr(api.aggregator, "_fused", None)
+    if fused is None:
+        return None
+    lay = api.layout
+    mine = [c for c in api.local_clients(range(api.args.client_num_in_total)) if api.client_list[c].slab is not None]
+    total = float(sum(api.client_list[c].get_sample_number() for c in range(api.args.client_num_in_total)))
+    pairs = [(api.client_list[c].get_sample_number() / total, api.client_list[c].slab) for c in mine]
+    out_f, out_n = api.model_trainer.engine.new_slab(), api.model_trainer.engine.new_slab()
+    api.aggregator.aggregate(out_f, pairs, api.mask)
+    part = api.aggregator.partial.clone()
+    nccl = Aggregator(ctx, lay, device, "nccl")
+    nccl.aggregate(out_n, pairs, api.mask)
+    parts = [torch.empty_like(part) for _ in range(ctx.world_size)]
+    dist.all_gather(parts, part)
+    ordered = parts[0].clone()
+    for p in parts[1:]:
+        ordered += p
+    if api.mask is not None:
+        ordered[:api.mask.flat.numel()] *= api.mask.flat
+    d_ord = (out_f.flat - ordered).abs().max()
+    d_nccl = (out_f.flat - out_n.flat).abs().max()
+    res = {"agg_path": "multimem" if fused.use_multimem_for(lay.total_numel) else "p2p"}
+    masks_equal = None
+    if getattr(api, "scores", None) is not None:
+        n = lay.param_numel
+        sc = api.scores.flat.clone()
+        sc[:n] *= (1.0 + ctx.rank) / ctx.world_size
+        m_f = ParamSlab(lay, device=device, params_only=True)
+        m_n = ParamSlab(lay, device=device, params_only=True)
+        flags = ops.prunable_flags(lay, device)
+        s_f = sc.clone()
+        fused.saliency_topk_mask(s_f, lay, float(api.args.dense_ratio), m_f.flat, flags)
+        s_n = sc.clone()
+        dist.all_reduce(s_n)
+        ops.global_topk_mask(s_n, lay, float(api.args.dense_ratio), m_n.flat)
+        diff = (m_f.flat != m_n.flat).sum().double()
+        dist.all_reduce(diff, op=dist.ReduceOp.MAX)
+        masks_equal = int(diff.item())
+    t = torch.stack([d_ord.double(), d_nccl.double()])
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    res.update({"max_abs_diff": float(t[0].item()), "max_abs_diff_vs_nccl_allreduce": float(t[1].item()), "mask_entries_differing_vs_nccl": masks_equal})
+    tol = 0.0 if res["agg_path"] == "p2p" else 1e-5
+    res["ok"] = bool(res["max_abs_diff"] <= tol and res["max_abs_diff_vs_nccl_allreduce"] <= 1e-5 and (masks_equal is None or masks_equal <= 2))
+    return res
+
+
 def run_ours(a):
     from neuroimagedisttraining_b200.data import load_partition_data_abcd
     from neuroimagedisttraining_b200.fl import SalientGradsAPI, SlabTrainer
     from neuroimagedisttraining_b200.models import AlexNet3D_Dropout
     from neuroimagedisttraining_b200.ops import native
     from neuroimagedisttraining_b200.parallel import init_distributed, shutdown
+    from neuroimagedisttraining_b200.runtime import xfer
 
     ctx = init_distributed()
     device = ctx.device
@@ -206,16 +274,14 @@ def run_ours(a):
     engine = None
     engine_name = "torch(cudnn, bf16 autocast)+flat-kernels" if a.model == "resnet3d" else "torch(scaffold)+flat-kernels"
     if a.engine in ("auto", "b200"):
-        try:
-            from neuroimagedisttraining_b200.ops.engines import make_native_engine
-            engine = make_native_engine(model, device, max_batch=a.batch, input_scale=store.scale)
-            engine_name = "b200"
-        except ImportError:
-            if a.engine == "b200":
-                raise
+        # both bench models have a native plan: a missing library or an engine that fails to construct is an error, never a
+        # silent fall-back to the PyTorch engine (``--engine torch`` asks for that one explicitly)
+        from neuroimagedisttraining_b200.ops.engines import make_native_engine
+        engine = make_native_engine(model, device, max_batch=a.batch, input_scale=store.scale)
+        engine_name = "b200"
     if engine is None and a.model == "resnet3d":
         fl_args.amp = True
-    trainer = SlabTrainer(model, fl_args, logger, device=device, store=store, engine=engine)
+    trainer = SlabTrainer(model, fl_args, logger, device=device, store=store, engine=engine, staging="client")
     from neuroimagedisttraining_b200.fl import FedAvgAPI
     api = (SalientGradsAPI if a.algo == "salientgrads" else FedAvgAPI)(dataset, device, fl_args, trainer, logger, dist=ctx, agg_mode=a.agg)
     api.w_init = api.w_global.clone()
@@ -236,21 +302,18 @@ def run_ours(a):
 
     for _ in range(a.warmup):
         one_round(0)
-    # ---- e2e: public API, pinned host -> device copies every batch, metrics read back every round
+    # ---- e2e: the public API as a user runs it (staging="client"): every volume a round touches is copied host -> device from
+    # pinned memory inside the round (once per client-round, not once per epoch / per evaluated model), metrics are read back
     e2e = None
-    stager = trainer._stager(a.batch)
     if not a.skip_e2e:
-        h0 = stager.h2d_bytes
-        n0 = native.LAUNCH_COUNT
+        h0, d0, c0 = trainer.h2d_bytes, xfer.D2H_BYTES, xfer.D2H_COPIES
         t_e2e = timed_rounds(one_round, a.steps, ctx, device)
-        h2d = (stager.h2d_bytes - h0) / a.steps
-        steps_local = sum(len(api.client_list[c].local_training_data) for c in api.local_clients(range(a.clients))) * a.epochs
-        # D2H per round: one fp32 mean loss per client-epoch + 3 fp64 counters per evaluated (client, model)
-        d2h = 4 * a.epochs * len(api.local_clients(range(a.clients))) + 2 * 24 * len(api.local_clients(range(a.clients)))
-        e2e = {"value": samples_per_round * a.steps / t_e2e, "unit": "samples/s", "h2d_bytes_per_step": h2d,
-               "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * t_e2e / a.steps}
-    # ---- device-timed: inputs resident on the device (no H2D inside the timed region)
-    trainer._stagers[a.batch] = make_device_stager(store, device, a.batch)
+        e2e = {"value": samples_per_round * a.steps / t_e2e, "unit": "samples/s", "h2d_bytes_per_step": (trainer.h2d_bytes - h0) / a.steps,
+               "d2h_bytes_per_step": (xfer.D2H_BYTES - d0) / a.steps, "d2h_copies_per_step": (xfer.D2H_COPIES - c0) / a.steps,
+               "ms_per_step": 1e3 * t_e2e / a.steps, "staging": "client (per-client-round device cache, uploads queued ahead on a copy stream)",
+               "bytes_scope": "rank 0" if ctx.world_size > 1 else "all"}
+    # ---- device-timed: the same API with staging="resident" (whole store uploaded once, outside the timed region)
+    trainer.set_staging("resident")
     one_round(0)
     clk = ClockSampler(ctx.local_rank)
     if ctx.is_main:
@@ -260,6 +323,7 @@ def run_ours(a):
     launches = native.LAUNCH_COUNT - n0
     clocks = clk.stop() if ctx.is_main else None
     stat = api.finalize_stats()
+    check = agg_check(api, ctx, device) if ctx.world_size > 1 else None
     if ctx.is_main:
         out = {
             "metric": "samples_per_s_%s_%s_abcd_round" % (a.algo, a.model), "value": samples_per_round * a.steps / t_dev,
@@ -267,47 +331,17 @@ def run_ours(a):
             "ms_per_step": 1e3 * t_dev / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "bf16" if engine_name == "b200" else "fp32(tf32 conv)", "data": "synthetic 8-bit ABCD-shape volumes, random-init weights",
             "impl": "ours", "engine": engine_name,
-            "config": {"model": "AlexNet3D_Dropout(1 logit)" if a.model == "alexnet3d" else "ResNet3D_l3(BasicBlock,[2,2,2], 1 logit, FC sized from the input)", "algorithm": ("SalientGrads dense_ratio=%g" % a.dense_ratio) if a.algo == "salientgrads" else "FedAvg",
-                       "clients": a.clients, "clients_per_round": a.clients, "local_epochs": a.epochs, "batch": a.batch,
-                       "global_batch": a.batch, "seq_len": "x".join(map(str, shape)), "train_samples_per_round": samples_per_round,
-                       "sgd_steps_per_round": samples_per_round // a.batch, "eval_samples_per_round": 2 * a.clients * (a.per_site // 5),
-                       "parallelism": "client-parallel x%d (one process per GPU)" % ctx.world_size,
-                       "step_definition": "one FL communication round (train + aggregate + eval of all clients)",
-                       "l2_policy": "inputs larger than L2 (506 MB conv1 activations per SGD step)",
-                       "aggregation": api.aggregator.mode},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "mask_generation_s": mask_s,
+            "config": config_dict(a, shape, samples_per_round),
+            "parallelism": "client-parallel x%d (one process per GPU)" % ctx.world_size, "aggregation": api.aggregator.mode,
+            "value_staging": "resident (SlabTrainer.set_staging('resident'): store uploaded once before the timed region)",
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "mask_generation_s": mask_s, "agg_check": check,
             "global_test_acc": float(stat["global_test_acc"][-1]) if stat["global_test_acc"] else None,
             "phase_time_s": {k: round(v["total_s"], 4) for k, v in stat["phase_time_s"].items()},
         }
         print(json.dumps(out))
     shutdown()
-
-
-def make_device_stager(store, device, batch):
-    """Stager variant with the whole synthetic dataset resident on the device."""
-    from neuroimagedisttraining_b200 import ops
-    from neuroimagedisttraining_b200.runtime.staging import BatchStager
-
-    class DeviceStager(BatchStager):
-        def __init__(self):
-            self.store, self.device, self.batch_size, self.cuda = store, torch.device(device), batch, True
-            self.h2d_bytes = 0
-            self.vol = store._cache.to(device)
-            self.lab = torch.from_numpy(store.labels).to(device)
-            # index batches go through a ring of pinned buffers: a pageable H2D copy would make the host wait for the stream
-            self.ring = [torch.empty(batch, dtype=torch.int64).pin_memory() for _ in range(128)]
-            self.k = 0
-
-        def iterate(self, loader, lookahead=None):
-            for b in loader:
-                n = b[0].numel()
-                buf = self.ring[self.k % len(self.ring)]
-                self.k += 1
-                buf[:n] = torch.sort(b[0])[0]
-                idx = buf[:n].to(self.device, non_blocking=True)
-                yield ops.gather_rows_u8(self.vol, idx), self.lab.index_select(0, idx)
-
-    return DeviceStager()
+    if check is not None and not check["ok"]:
+        sys.exit(1)
 
 
 # ------------------------------------------------------------------------------- reference arm
@@ -415,10 +449,8 @@ def run_reference(a):
             "unit": "samples/s", "n_gpus": ctx.world_size, "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * t / a.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "fp32 (TF32 conv, cudnn.deterministic=True)",
             "data": "synthetic 8-bit ABCD-shape volumes served as fp32, random-init weights",
-            "config": {"model": "AlexNet3D_Dropout(1 logit)" if a.model == "alexnet3d" else "ResNet3D_l3(BasicBlock,[2,2,2], 1 logit, FC sized from the input)", "algorithm": "SalientGrads dense_ratio=%g" % a.dense_ratio,
-                       "clients": a.clients, "local_epochs": a.epochs, "batch": a.batch, "global_batch": a.batch,
-                       "seq_len": "x".join(map(str, shape)), "train_samples_per_round": samples_per_round,
-                       "parallelism": "reference loop verbatim" if ctx.world_size == 1 else "reference Client.train per rank + NCCL all_reduce wrapper x%d" % ctx.world_size},
+            "config": config_dict(a, shape, samples_per_round),
+            "parallelism": "reference loop verbatim" if ctx.world_size == 1 else "reference Client.train per rank + NCCL all_reduce wrapper x%d" % ctx.world_size,
             "clocks": clocks, "e2e": {"value": samples_per_round * a.steps / t, "unit": "samples/s", "h2d_bytes_per_step": h2d,
                                       "d2h_bytes_per_step": None, "note": "the reference has no device-resident mode: its only path is end to end"},
             "gpu_launches": 0, "mask_generation_s": mask_s}))

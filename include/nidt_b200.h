@@ -57,8 +57,15 @@ int nidt_sq_dist(const float* a, const float* b, int64_t n, float* scratch, floa
 int nidt_gather_rows_u8(const void* src, const int64_t* idx, void* dst, int rows, int64_t row_bytes, void* stream);
 /* the same with at most max_blocks CTAs; src and idx may be pinned host memory (the kernel reads it over PCIe) */
 int nidt_gather_rows_u8_capped(const void* src, const int64_t* idx, void* dst, int rows, int64_t row_bytes, int max_blocks, void* stream);
-/* n asynchronous host->device row copies (rows: HOST int64 array of source row numbers; host_base should be pinned) in one call. */
+/* the same with the row numbers passed by value in the kernel parameters (idx: HOST array, rows <= 64) and, when ysrc != NULL, the
+ * fp32 labels gathered by the same launch (ydst[j] = ysrc[idx[j]]): one launch per batch from a device-resident cache, no index
+ * traffic.  Replaces the reference's per-batch HDF5 read + fp32 upload, sailentgrads/my_model_trainer.py:185-199. */
+int nidt_gather_rows_u8_args(const void* src, const int64_t* idx, void* dst, int rows, int64_t row_bytes,
+                             const float* ysrc, float* ydst, void* stream);
+/* asynchronous host->device row copies (rows: HOST int64 array of source row numbers; host_base should be pinned) in one call;
+ * runs of consecutive row numbers are merged into one copy each.  _counted also reports how many copies were issued. */
 int nidt_copy_rows_h2d(const void* host_base, const int64_t* rows, int n, int64_t row_bytes, void* dst, void* stream);
+int nidt_copy_rows_h2d_counted(const void* host_base, const int64_t* rows, int n, int64_t row_bytes, void* dst, void* stream, int* n_copies);
 /* Ditto proximal pull w -= coef*(w - ref).  ref: fedml_api/standalone/ditto/my_model_trainer.py:63-64. */
 int nidt_prox_pull(float* w, const float* ref, int64_t n, float coef, void* stream);
 

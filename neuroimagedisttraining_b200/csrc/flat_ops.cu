@@ -313,8 +313,10 @@ namespace nidt {
 __device__ __forceinline__ uint32_t funnel_bytes(uint32_t lo, uint32_t hi, uint32_t byte_shift) {
     return __funnelshift_r(lo, hi, byte_shift * 8);
 }
-__global__ void __launch_bounds__(256) gather_rows_u8_kernel(const uint8_t* __restrict__ src, const int64_t* __restrict__ idx, uint8_t* __restrict__ dst,
-                                                             int rows, int64_t row_bytes) {
+constexpr int kGatherArgRows = 64;
+struct RowArgs { int64_t v[kGatherArgRows]; __device__ __forceinline__ int64_t operator[](int j) const { return v[j]; } };
+template <class Idx>
+__device__ __forceinline__ void gather_rows_body(const uint8_t* __restrict__ src, const Idx& idx, uint8_t* __restrict__ dst, int rows, int64_t row_bytes) {
     const int64_t total = (int64_t)rows * row_bytes;
     const uintptr_t d0 = reinterpret_cast<uintptr_t>(dst);
     const int64_t head = (int64_t)((16 - (d0 & 15)) & 15) < total ? (int64_t)((16 - (d0 & 15)) & 15) : total;
@@ -361,6 +363,17 @@ __global__ void __launch_bounds__(256) gather_rows_u8_kernel(const uint8_t* __re
         dst[off] = src[idx[j] * row_bytes + (off - (int64_t)j * row_bytes)];
     }
 }
+__global__ void __launch_bounds__(256) gather_rows_u8_kernel(const uint8_t* __restrict__ src, const int64_t* __restrict__ idx, uint8_t* __restrict__ dst,
+                                                             int rows, int64_t row_bytes) {
+    gather_rows_body(src, idx, dst, rows, row_bytes);
+}
+// Row numbers travel in the kernel parameters (no index buffer on the device, no host->device copy of it); the labels of the
+// batch are gathered by the same launch.
+__global__ void __launch_bounds__(256) gather_rows_u8_args_kernel(const uint8_t* __restrict__ src, const __grid_constant__ RowArgs idx, uint8_t* __restrict__ dst,
+                                                                  int rows, int64_t row_bytes, const float* __restrict__ ysrc, float* __restrict__ ydst) {
+    gather_rows_body(src, idx, dst, rows, row_bytes);
+    if (ysrc != nullptr && blockIdx.x == 0 && threadIdx.x < rows) ydst[threadIdx.x] = ysrc[idx[threadIdx.x]];
+}
 }  // namespace nidt
 
 // idx: int64 device array of `rows` source row numbers.  The source allocation must be readable up to the next 16-byte boundary
@@ -386,12 +399,43 @@ static int gather_rows_launch(const void* src, const int64_t* idx, void* dst, in
     return 0;
 }
 
-// dst[j] = host_base[rows[j]] (row_bytes each) as `n` asynchronous copies on `stream`, issued from native code: one call per batch
-// instead of one framework-level copy per sample (~20 us of host time each).  host_base should be pinned; rows is a HOST array.
-NIDT_API int nidt_copy_rows_h2d(const void* host_base, const int64_t* rows, int n, int64_t row_bytes, void* dst, void* stream) {
-    NIDT_REQUIRE(n >= 0 && row_bytes > 0, "nidt_copy_rows_h2d: n=%d row_bytes=%lld", n, (long long)row_bytes);
-    for (int j = 0; j < n; ++j)
-        NIDT_CUDA_CHECK(cudaMemcpyAsync((uint8_t*)dst + (size_t)j * row_bytes, (const uint8_t*)host_base + (size_t)rows[j] * row_bytes, (size_t)row_bytes,
-                                        cudaMemcpyHostToDevice, (cudaStream_t)stream));
+// Gather with the row numbers passed by value (rows <= 64; `idx` is a HOST array) + optional fp32 label gather ydst[j] = ysrc[idx[j]].
+NIDT_API int nidt_gather_rows_u8_args(const void* src, const int64_t* idx, void* dst, int rows, int64_t row_bytes,
+                                      const float* ysrc, float* ydst, void* stream) {
+    NIDT_REQUIRE(rows >= 0 && rows <= kGatherArgRows && row_bytes >= 16, "nidt_gather_rows_u8_args: rows=%d (max %d) row_bytes=%lld", rows,
+                 kGatherArgRows, (long long)row_bytes);
+    if (rows == 0) return 0;
+    RowArgs a;
+    for (int j = 0; j < kGatherArgRows; ++j) a.v[j] = j < rows ? idx[j] : 0;
+    const int64_t nvec = ((int64_t)rows * row_bytes) >> 4;
+    int64_t grid = (nvec + 255) / 256;
+    if (grid > (int64_t)kNumSMs * 16) grid = (int64_t)kNumSMs * 16;
+    if (grid < 1) grid = 1;
+    gather_rows_u8_args_kernel<<<(int)grid, 256, 0, (cudaStream_t)stream>>>((const uint8_t*)src, a, (uint8_t*)dst, rows, row_bytes, ysrc, ydst);
+    NIDT_LAUNCH_CHECK();
     return 0;
+}
+
+// dst[j] = host_base[rows[j]] (row_bytes each) as asynchronous copies on `stream`, issued from native code.  Runs of consecutive
+// row numbers (a site's subjects are adjacent in the store) become ONE copy each, so a sorted batch costs a handful of large
+// transfers instead of one per sample.  host_base should be pinned; rows is a HOST array.  *n_copies (optional) = copies issued.
+static int copy_rows_h2d(const void* host_base, const int64_t* rows, int n, int64_t row_bytes, void* dst, void* stream, int* n_copies) {
+    NIDT_REQUIRE(n >= 0 && row_bytes > 0, "nidt_copy_rows_h2d: n=%d row_bytes=%lld", n, (long long)row_bytes);
+    int copies = 0;
+    for (int j = 0; j < n;) {
+        int e = j + 1;
+        while (e < n && rows[e] == rows[e - 1] + 1) ++e;
+        NIDT_CUDA_CHECK(cudaMemcpyAsync((uint8_t*)dst + (size_t)j * row_bytes, (const uint8_t*)host_base + (size_t)rows[j] * row_bytes,
+                                        (size_t)(e - j) * row_bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+        ++copies;
+        j = e;
+    }
+    if (n_copies) *n_copies = copies;
+    return 0;
+}
+NIDT_API int nidt_copy_rows_h2d(const void* host_base, const int64_t* rows, int n, int64_t row_bytes, void* dst, void* stream) {
+    return copy_rows_h2d(host_base, rows, n, row_bytes, dst, stream, nullptr);
+}
+NIDT_API int nidt_copy_rows_h2d_counted(const void* host_base, const int64_t* rows, int n, int64_t row_bytes, void* dst, void* stream, int* n_copies) {
+    return copy_rows_h2d(host_base, rows, n, row_bytes, dst, stream, n_copies);
 }

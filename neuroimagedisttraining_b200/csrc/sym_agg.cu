@@ -19,6 +19,7 @@
 #include "common.cuh"
 #include "topk.cuh"
 #include <cooperative_groups.h>
+#include <stdlib.h>
 
 namespace nidt {
 
@@ -32,6 +33,8 @@ struct SymPeers {
     float* mc_partial;              // multicast address of `partial` (nullptr = unavailable)
     float* mc_result;               // multicast address of `result`
     int rank, world;
+    long long timeout_cycles;       // a peer that has not arrived after this many SM clocks ends the kernel in a trap (hang detector only:
+                                    // the host aligns the ranks before the launch, see parallel/symmetric.py)
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -56,7 +59,7 @@ __device__ __forceinline__ void cross_rank_barrier(cg::grid_group& grid, const S
         const uint32_t* mine = sp.flags[sp.rank] + slot * kMaxRanks + peer;
         const long long t0 = clock64();
         while ((int32_t)(ld_acquire_sys(mine) - value) < 0) {
-            if (clock64() - t0 > 20000000000LL) {   // ~10 s
+            if (clock64() - t0 > sp.timeout_cycles) {
                 printf("nidt: cross-rank barrier timed out (rank %d waiting for %d, value %u)\n", sp.rank, peer, value);
                 __trap();
             }
@@ -174,6 +177,17 @@ __global__ void __launch_bounds__(kSymThreads) sym_saliency_topk_kernel(const Sy
         for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) scores_out[i] = scores[i];
 }
 
+// NIDT_SYM_TIMEOUT_S (default 300 s) at the nominal 1.965 GHz SM clock.
+static long long sym_timeout_cycles() {
+    static long long cached = 0;
+    if (cached == 0) {
+        double sec = 300.0;
+        if (const char* e = getenv("NIDT_SYM_TIMEOUT_S")) { const double v = atof(e); if (v > 0.0) sec = v; }
+        cached = (long long)(sec * 1.965e9);
+    }
+    return cached;
+}
+
 static int fill_peers(SymPeers& sp, void* const* partial_ptrs, void* const* result_ptrs, void* const* flag_ptrs, void* mc_partial, void* mc_result,
                       int rank, int world) {
     NIDT_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world, "sym: bad rank %d / world %d", rank, world);
@@ -186,6 +200,7 @@ static int fill_peers(SymPeers& sp, void* const* partial_ptrs, void* const* resu
     sp.mc_result = (float*)mc_result;
     sp.rank = rank;
     sp.world = world;
+    sp.timeout_cycles = sym_timeout_cycles();
     return 0;
 }
 
@@ -243,15 +258,7 @@ NIDT_API int nidt_sym_reduce_mask_broadcast(void* const* partial_ptrs, void* con
     NIDT_REQUIRE(n % 4 == 0 && n_mask % 4 == 0, "sym_reduce: n and n_mask must be multiples of 4");
     NIDT_REQUIRE(!use_multimem || (mc_partial != nullptr && mc_result != nullptr), "sym_reduce: multimem requested without multicast addresses");
     SymPeers sp;
-    for (int p = 0; p < kMaxRanks; ++p) {
-        sp.partial[p] = p < world ? (float*)partial_ptrs[p] : nullptr;
-        sp.result[p] = p < world ? (float*)result_ptrs[p] : nullptr;
-        sp.flags[p] = p < world ? (uint32_t*)flag_ptrs[p] : nullptr;
-    }
-    sp.mc_partial = (float*)mc_partial;
-    sp.mc_result = (float*)mc_result;
-    sp.rank = rank;
-    sp.world = world;
+    if (int rc = fill_peers(sp, partial_ptrs, result_ptrs, flag_ptrs, mc_partial, mc_result, rank, world)) return rc;
     int dev = 0, sms = 0, per_sm = 0;
     NIDT_CUDA_CHECK(cudaGetDevice(&dev));
     NIDT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));

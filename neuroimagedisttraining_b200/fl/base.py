@@ -91,6 +91,20 @@ class FedAPIBase:
         self.logger.info("client_indexes = %s" % str(client_indexes))
         return client_indexes
 
+    def peek_client_sampling(self, round_idx) -> np.ndarray:
+        """The (sorted) clients round ``round_idx`` will sample under the stock rule, computed without side effects (numpy's global
+        stream, which the sampler re-seeds, is put back; nothing is logged; the ``_client_sampling`` hook is not called).  Only a
+        prefetch hint: a mispredicted upload is evicted by the stager."""
+        total, per_round = self.args.client_num_in_total, self.args.client_num_per_round
+        if total == per_round:
+            return np.arange(total)
+        state = np.random.get_state()
+        try:
+            np.random.seed(round_idx)
+            return np.sort(np.random.choice(range(total), min(per_round, total), replace=False))
+        finally:
+            np.random.set_state(state)
+
     def local_clients(self, indexes: Sequence[int]) -> List[int]:
         return [int(c) for c in indexes if self.dist.owns(int(c))]
 
@@ -109,24 +123,34 @@ class FedAPIBase:
         return out
 
     # --------------------------------------------------------------------- evaluation
-    def _evaluate_clients(self, slabs: Dict[int, ParamSlab], client_ids: Sequence[int]) -> Tuple[np.ndarray, np.ndarray]:
-        """Per-client (accuracy, loss/sample) for the locally owned ``client_ids``; zeros elsewhere."""
+    def _metrics_arrays(self, client_ids: Sequence[int], results) -> Tuple[np.ndarray, np.ndarray]:
         n = self.args.client_num_in_total
         acc = np.zeros(n)
         loss = np.zeros(n)
-        results = self.model_trainer.test_many([(slabs[cid], self.client_list[cid].local_test_data) for cid in client_ids])
         for cid, m in zip(client_ids, results):
             tot = max(m["test_total"], 1.0)
             acc[cid] = m["test_correct"] / tot
             loss[cid] = m["test_loss"] / tot
         return acc, loss
 
+    def _evaluate_clients(self, slabs: Dict[int, ParamSlab], client_ids: Sequence[int]) -> Tuple[np.ndarray, np.ndarray]:
+        """Per-client (accuracy, loss/sample) for the locally owned ``client_ids``; zeros elsewhere."""
+        results = self.model_trainer.test_many([(slabs[cid], self.client_list[cid].local_test_data) for cid in client_ids])
+        return self._metrics_arrays(client_ids, results)
+
+    def eval_loaders(self, ids: Optional[Sequence[int]] = None) -> list:
+        """Test loaders of the locally evaluated clients, in evaluation order (what :meth:`_test_on_all_clients` stages as one group)."""
+        if ids is None:
+            ids = [0] if getattr(self.args, "ci", 0) == 1 else list(range(self.args.client_num_in_total))
+        return [self.client_list[c].local_test_data for c in self.local_clients(ids)]
+
     def _reduce_metric(self, *arrays: np.ndarray) -> List[np.ndarray]:
         if not self.dist.is_distributed:
             return list(arrays)
         t = torch.tensor(np.stack(arrays), dtype=torch.float64, device=self.device)
         self.dist.all_reduce_sum(t)
-        return [a for a in t.cpu().numpy()]
+        from ..runtime import xfer
+        return [a for a in xfer.to_host(t).numpy()]
 
     def _test_on_all_clients(self, w_global: ParamSlab, w_per_mdls: Optional[Dict[int, ParamSlab]], round_idx):
         """Global model and personalised models on every client's test split; metrics are
@@ -137,11 +161,14 @@ class FedAPIBase:
         ids = [0] if getattr(self.args, "ci", 0) == 1 else list(range(n_total))
         mine = self.local_clients(ids)
         with self.timer.phase("eval"):
-            g_acc, g_loss = self._evaluate_clients({c: w_global for c in mine}, mine)
+            # every test split is staged once and evaluated by both models (the reference stages it once per model)
+            loaders = [self.client_list[c].local_test_data for c in mine]
+            sets = [[w_global] * len(mine)]
             if w_per_mdls is not None:
-                p_acc, p_loss = self._evaluate_clients({c: (w_per_mdls.get(c) or self.w_init or w_global) for c in mine}, mine)
-            else:
-                p_acc, p_loss = g_acc.copy(), g_loss.copy()
+                sets.append([(w_per_mdls.get(c) or self.w_init or w_global) for c in mine])
+            res = self.model_trainer.test_multi(loaders, sets)
+            g_acc, g_loss = self._metrics_arrays(mine, res[0])
+            p_acc, p_loss = self._metrics_arrays(mine, res[1]) if w_per_mdls is not None else (g_acc.copy(), g_loss.copy())
             g_acc, g_loss, p_acc, p_loss = self._reduce_metric(g_acc, g_loss, p_acc, p_loss)
         denom = len(ids)
         stats = {'global_test_acc': g_acc.sum() / denom, 'global_test_loss': g_loss.sum() / denom}

@@ -31,14 +31,20 @@ class EvalCounters:
     """Device-side accumulators (correct, loss_sum, total): no per-batch ``.item()`` syncs
     (the reference does three per batch, ``my_model_trainer.py:270-273``)."""
 
-    def __init__(self, device):
-        self.buf = torch.zeros(3, dtype=torch.float64, device=device)
+    def __init__(self, device, buf: Optional[torch.Tensor] = None):
+        """``buf``: a 3-element float64 view to accumulate into (several counters can share one tensor, read back in one copy)."""
+        self.buf = torch.zeros(3, dtype=torch.float64, device=device) if buf is None else buf
 
     def reset(self):
         self.buf.zero_()
 
+    @staticmethod
+    def as_result(c, l, t):
+        return {"test_correct": c, "test_loss": l, "test_total": t, "test_acc": (c / t if t else 0.0)}
+
     def result(self):
-        c, l, t = self.buf.tolist()
+        from ..runtime import xfer
+        c, l, t = xfer.to_host(self.buf).tolist()
         return {"test_correct": c, "test_loss": l, "test_total": t, "test_acc": (c / t if t else 0.0)}
 
 

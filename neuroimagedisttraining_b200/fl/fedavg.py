@@ -19,21 +19,33 @@ class FedAvgAPI(FedAPIBase):
         self.logger.info("client_indexes = " + str(client_indexes))
         training_num = sum(self.client_list[int(c)].get_sample_number() for c in client_indexes)
         w_locals = []
+        will_eval = evaluate and round_idx % max(1, int(getattr(args, "frequency_of_the_test", 1))) == 0
+        tr = self.model_trainer
         with self.timer.phase("train"):
             mine = list(self.local_clients(client_indexes))
+            # the whole round's data plan is known up front: this round's clients in order, then every test split (one group, staged
+            # once for both evaluations), then the first clients of the next round -- uploads run behind the compute stream
+            tr.plan_data([self.client_list[c].local_training_data for c in mine])
+            if will_eval:
+                tr.plan_data(self.eval_loaders(), kind="eval", group=True)
+            if round_idx + 1 < int(getattr(args, "comm_round", 0)):
+                nxt_round = self.peek_client_sampling(round_idx + 1)
+                tr.plan_data([self.client_list[c].local_training_data for c in self.local_clients(nxt_round)[:2]])
             for pos, cur_clnt in enumerate(mine):
                 self.logger.info('@@@@@@@@@@@@@@@@ Training Client CM({}): {}'.format(round_idx, cur_clnt))
                 client = self.client_list[cur_clnt]
-                # the next client's first batch is staged while this one finishes (no exposed copy at client boundaries)
+                # stream staging: the next client's first batch is copied while this one finishes
                 nxt = self.client_list[mine[pos + 1]].local_training_data if pos + 1 < len(mine) else None
                 slab, training_flops, num_comm_params = client.train(self.w_global, round_idx, mask, lookahead_data=nxt)
                 self._defend(slab)
                 w_locals.append((client.get_sample_number(), slab))
                 self.stat_info["sum_training_flops"] += training_flops
                 self._add_comm_params(num_comm_params)
-        self._aggregate(w_locals, training_num, mask=None)
+        # the shared mask rides along in the aggregation kernel (a no-op on already-masked client weights, as in the reference
+        # where the multiply at sailentgrads_api.py:109 is commented out; it keeps the global model exactly sparse)
+        self._aggregate(w_locals, training_num, mask=mask)
         self.model_trainer.flush_losses()
-        if evaluate and round_idx % max(1, int(getattr(args, "frequency_of_the_test", 1))) == 0:
+        if will_eval:
             self._test_on_all_clients(self.w_global, self.personal_slabs(), round_idx)
         self._maybe_checkpoint(round_idx)
 

@@ -18,7 +18,8 @@ import torch.nn as nn
 
 from .. import ops
 from ..runtime.slab import ParamSlab, make_mask_slab
-from ..runtime.staging import BatchStager
+from ..runtime import xfer
+from ..runtime.staging import BatchStager, make_stager
 from .engine import EvalCounters, StepHParams, TorchEngine
 
 
@@ -83,7 +84,10 @@ class SlabTrainer(ModelTrainer):
     reference, ``sailentgrads_api.py:36-45``); per-client state is the slab it is attached to."""
 
     def __init__(self, model: nn.Module, args=None, logger=None, device=None, store=None, engine=None,
-                 loss_kind: str = "bce", clip_norm: float = 10.0):
+                 loss_kind: str = "bce", clip_norm: float = 10.0, staging: str = "auto"):
+        """``staging``: how index batches reach the device -- ``client`` (each loader's volumes uploaded once per use, batches
+        gathered on the device; the default on CUDA), ``stream`` (batch-by-batch copies), ``resident`` (whole store on the device);
+        see :mod:`..runtime.staging`.  ``args.staging`` / ``--staging`` overrides ``auto``."""
         super().__init__(model, args)
         self.logger = logger
         self.device = torch.device(device) if device is not None else next(model.parameters()).device
@@ -98,6 +102,9 @@ class SlabTrainer(ModelTrainer):
         self.mom = ParamSlab(self.layout, device=self.device, params_only=True)
         self.masks: Optional[ParamSlab] = None
         self._stagers: Dict[int, BatchStager] = {}
+        if staging == "auto":
+            staging = getattr(args, "staging", None) or "auto"
+        self.staging = "client" if staging == "auto" else staging
         self.double_sigmoid_eval = True
         self.step_counter = 0
         self.pending_losses = []
@@ -113,9 +120,40 @@ class SlabTrainer(ModelTrainer):
     def _stager(self, batch_size: int) -> BatchStager:
         st = self._stagers.get(batch_size)
         if st is None:
-            st = BatchStager(self.store, self.device, batch_size)
+            st = make_stager(self.staging, self.store, self.device, batch_size)
             self._stagers[batch_size] = st
         return st
+
+    def set_staging(self, mode: str) -> None:
+        """Switch the staging mode (``client`` | ``stream`` | ``resident``); existing device buffers are dropped."""
+        if mode != self.staging:
+            if self.device.type == "cuda":
+                torch.cuda.synchronize(self.device)
+            self._stagers.clear()
+            self._prepared = None
+            self.staging = mode
+
+    @property
+    def h2d_bytes(self) -> int:
+        """Bytes copied host -> device by this trainer's stagers so far."""
+        return sum(st.h2d_bytes for st in self._stagers.values())
+
+    def _cached(self, data) -> bool:
+        return (self.staging != "stream" and self.store is not None and hasattr(data, "indices")
+                and self._stager(data.batch_size).cacheable(data))
+
+    def plan_data(self, loaders, kind: str = "train", group: bool = False) -> None:
+        """Tell the stager which loaders come next (in order) so their volumes are uploaded ahead of use, behind the compute
+        stream: the round's clients, then its test splits (``group=True``: one slot for all of them), then the first clients of
+        the next round.  A no-op for tensor loaders and in ``stream`` / ``resident`` mode."""
+        loaders = [l for l in loaders if self._cached(l)]
+        if not loaders:
+            return
+        by_bs: Dict[int, list] = {}
+        for l in loaders:
+            by_bs.setdefault(l.batch_size if not group else max(x.batch_size for x in loaders), []).append(l)
+        for bs, ls in by_bs.items():
+            self._stager(bs).want(ls, kind=kind, group=group)
 
     def _batches(self, data):
         """Uniform ``(x, y)`` stream: index loaders go through the volume store, tensor loaders pass through."""
@@ -137,9 +175,15 @@ class SlabTrainer(ModelTrainer):
         return index_stream(), tags
 
     def _batches_epochs(self, data, epochs: int, lookahead_data=None):
-        """``(epoch, x, y)`` over ``epochs`` passes of ``data`` as ONE staged stream.  ``lookahead_data``: the loader the next
-        call will train on; its first batch is copied while this client's last steps still run (see BatchStager.iterate)."""
-        if self.store is not None and hasattr(data, "indices"):
+        """``(epoch, x, y)`` over ``epochs`` passes of ``data``.  Client staging: the loader's volumes are uploaded once (ahead of
+        time when :meth:`plan_data` announced them) and every epoch's batches are gathered on the device.  Stream staging: ONE
+        staged stream over all epochs.  ``lookahead_data``: the loader the next call will train on; its upload (client mode) / first
+        batch (stream mode) is started while this client's steps still run."""
+        if self._cached(data):
+            if lookahead_data is not None:
+                self.plan_data([lookahead_data])
+            yield from self._stager(data.batch_size).cached_batches(data, epochs)
+        elif self.store is not None and hasattr(data, "indices"):
             prepared, self._prepared = getattr(self, "_prepared", None), None
             if prepared is not None and prepared[0] is data and prepared[1] == epochs:
                 stream, tags = prepared[2], prepared[3]
@@ -155,6 +199,32 @@ class SlabTrainer(ModelTrainer):
             for e in range(epochs):
                 for batch in data:
                     yield e, batch[0], batch[1]
+
+    def test_multi(self, loaders, slab_sets):
+        """Evaluate several models on the same test loaders with the data staged ONCE: ``slab_sets[p][j]`` is the slab of pass
+        ``p`` for ``loaders[j]`` (pass 0 = the global model on every client, pass 1 = the personalised models; the reference stages
+        each client's test split once per pass, ``sailentgrads_api.py:247-256``).  Returns ``results[p][j]`` metric dicts."""
+        loaders = list(loaders)
+        if not loaders:
+            return [[] for _ in slab_sets]
+        if not all(self._cached(l) for l in loaders):
+            return [self.test_many(list(zip(slabs, loaders))) for slabs in slab_sets]
+        bs = max(l.batch_size for l in loaders)
+        st = self._stager(bs)
+        ent = st.open(loaders, kind="eval")
+        acc = torch.zeros((len(slab_sets), len(loaders), 3), dtype=torch.float64, device=self.device)
+        try:
+            for p, slabs in enumerate(slab_sets):
+                counters = [EvalCounters(self.device, acc[p, j]) for j in range(len(loaders))]
+                for j, loader in enumerate(loaders):
+                    self.attach(slabs[j])
+                    for b in loader:
+                        x, y = st.batch_from(ent, loader, b[0])
+                        self.engine.eval_batch(x, y, counters[j], double_sigmoid=self.double_sigmoid_eval)
+        finally:
+            st.close(ent)
+        host = xfer.to_host(acc).tolist()                      # ONE device->host read for all (pass, client) counters
+        return [[EvalCounters.as_result(*host[p][j]) for j in range(len(loaders))] for p in range(len(slab_sets))]
 
     def test_many(self, jobs):
         """Evaluate ``[(slab, loader), ...]`` back to back as one staged stream (the copy of the next client's test
@@ -309,7 +379,7 @@ class SlabTrainer(ModelTrainer):
         """Read the queued per-epoch losses (one host sync) and log them in the reference's format."""
         if not self.pending_losses:
             return []
-        vals = torch.stack([l.detach().float().reshape(()) for _, _, l in self.pending_losses]).tolist()
+        vals = xfer.to_host(torch.stack([l.detach().float().reshape(()) for _, _, l in self.pending_losses])).tolist()
         out = []
         for (cid, epoch, _), v in zip(self.pending_losses, vals):
             out.append(v)

@@ -28,7 +28,8 @@ class Aggregator:
         self.ctx = ctx
         self.layout = layout
         self.device = torch.device(device)
-        if mode == "auto":
+        auto = mode == "auto"
+        if auto:
             mode = "fused" if (ctx.is_distributed and self.device.type == "cuda") else "nccl"
         if not ctx.is_distributed:
             mode = "local"       # one rank: the weighted-aggregate kernel writes the global slab, nothing crosses a link
@@ -36,9 +37,33 @@ class Aggregator:
         self.partial = torch.zeros(layout.total_numel, dtype=torch.float32, device=self.device)
         self._fused = None
         if ctx.is_distributed and mode == "fused":
+            self._fused = self._make_fused(ctx, layout.total_numel, strict=not auto)
+            if self._fused is None:
+                self.mode = "nccl"
+            else:
+                self.partial = self._fused.local_partial   # the staging buffer peers read from
+
+    def _make_fused(self, ctx: DistContext, numel: int, strict: bool):
+        """The symmetric-memory aggregator, or -- when it was only chosen by ``auto`` and any rank cannot set it up (no P2P /
+        NVLink between the GPUs, several nodes, more ranks than the kernel supports) -- None on EVERY rank, so the job runs on
+        the NCCL path instead of failing to start.  An explicit ``fused`` request still raises."""
+        fused, err = None, None
+        try:
             from .symmetric import SymmetricAggregator
-            self._fused = SymmetricAggregator(ctx, layout.total_numel, self.device)
-            self.partial = self._fused.local_partial   # the staging buffer peers read from
+            fused = SymmetricAggregator(ctx, numel, self.device)
+        except Exception as e:           # noqa: BLE001 -- any set-up failure demotes `auto` to NCCL
+            if strict:
+                raise
+            err = e
+        ok = torch.tensor([0.0 if fused is None else 1.0], device=self.device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if ok.item() < 1.0:
+            if strict:
+                raise RuntimeError("fused aggregation could not be set up on every rank")
+            import logging
+            logging.getLogger(__name__).warning("fused symmetric-memory aggregation unavailable (%s); using the NCCL path", err or "a peer failed")
+            return None
+        return fused
 
     def aggregate(self, out: ParamSlab, local: Sequence[Tuple[float, ParamSlab]], mask: Optional[ParamSlab] = None) -> ParamSlab:
         """``out = mask * sum_{all ranks} sum_{local} weight * slab``; ``local`` holds this rank's

@@ -75,18 +75,50 @@ class SymmetricAggregator:
             mc = 0
         self.mc_partial = mc or None
         self.mc_result = (mc + 4 * self.pad) if mc else None
+        # NVLS multimem (in-switch reduction) vs plain P2P loads/stores: chosen by size unless forced (use_multimem= or
+        # NIDT_AGG_MULTIMEM=0/1).  Measured at 2/4/8 GPUs (profiles/agg_sweep_*): multimem wins up to 256 MB, P2P above.
         env = os.environ.get("NIDT_AGG_MULTIMEM")
-        if use_multimem is None:
+        if use_multimem is None and env in ("0", "1"):
             use_multimem = (env == "1")
-        self.use_multimem = bool(use_multimem and mc)
+        self._mm_forced = use_multimem
+        self.has_multicast = bool(mc)
+        self.multimem_max_bytes = int(os.environ.get("NIDT_AGG_MULTIMEM_MAX_BYTES", str(256 << 20)))
+        self._align = torch.zeros(1, dtype=torch.float32, device=self.device)
         self.local_partial = self.buf[:self.numel]
         self.local_result = self.buf[self.pad:self.pad + self.numel]
         self.epoch = 0
 
-    def reduce_mask_broadcast(self, out: torch.Tensor, mask: Optional[torch.Tensor]) -> torch.Tensor:
-        """``out = mask * sum_ranks partial`` on every rank; one kernel launch per rank."""
+    def use_multimem_for(self, numel: int) -> bool:
+        if not self.has_multicast:
+            return False
+        if self._mm_forced is not None:
+            return bool(self._mm_forced)
+        return 4 * int(numel) <= self.multimem_max_bytes
+
+    @property
+    def use_multimem(self) -> bool:
+        return self.use_multimem_for(self.numel)
+
+    @use_multimem.setter
+    def use_multimem(self, force: Optional[bool]) -> None:
+        """True / False forces the path for every size; None returns to the choice by size."""
+        self._mm_forced = force
+
+    def align_ranks(self) -> None:
+        """Stream-ordered line-up of the ranks before a fused launch: a one-element NCCL all-reduce on the launching stream.
+        The fused kernels spin on flags their peers write; ranks reach an aggregation with arbitrary skew (uneven client counts,
+        a rank with no sampled client this round), and NCCL waits without a deadline where our device-side barrier is a bounded
+        hang detector (``NIDT_SYM_TIMEOUT_S``).  After this call every rank's stream has passed the same point, so the kernels
+        start within one collective's skew of each other.  No host synchronisation."""
+        dist.all_reduce(self._align)
+
+    def reduce_mask_broadcast(self, out: torch.Tensor, mask: Optional[torch.Tensor], align: bool = True) -> torch.Tensor:
+        """``out = mask * sum_ranks partial`` on every rank; one kernel launch per rank (``align``: see :meth:`align_ranks`;
+        benchmarks that time the kernel alone line the ranks up themselves)."""
         n = self.numel
         assert out.numel() == n and out.is_cuda
+        if align:
+            self.align_ranks()
         self.epoch += 1
         n_mask = 0 if mask is None else min(mask.numel(), n)
         native.check(self.lib.nidt_sym_reduce_mask_broadcast(
@@ -103,13 +135,14 @@ class SymmetricAggregator:
         n = layout.param_numel
         k = int(layout.prunable_numel() * keep_ratio)
         self.local_partial[:n].copy_(scores[:n])
+        self.align_ranks()
         if not hasattr(self, "_topk_scratch"):
             self._topk_scratch = torch.zeros(self.lib.nidt_topk_scratch_bytes(), dtype=torch.uint8, device=self.device)
         self.epoch += 1
         native.check(self.lib.nidt_sym_saliency_topk_mask(
             self._partial, self._result, self._flags, self.mc_partial, self.mc_result, self.ctx.rank, self.ctx.world_size, n,
             native.ptr(flags), native.ptr(mask_out), k, native.ptr(self._topk_scratch), native.ptr(scores), self.epoch,
-            int(self.use_multimem), native.stream_ptr(self.device)), "nidt_sym_saliency_topk_mask")
+            int(self.use_multimem_for(n)), native.stream_ptr(self.device)), "nidt_sym_saliency_topk_mask")
         native.count_launches(1)
         thr, norm, kept = C.c_float(), C.c_float(), C.c_uint()
         native.check(self.lib.nidt_topk_read_result(native.ptr(self._topk_scratch), C.byref(thr), C.byref(norm), C.byref(kept),

@@ -1,24 +1,74 @@
 """Host -> device batch staging.
 
 The reference builds every batch with a blocking ``torch.tensor(numpy, device="cuda")`` of fp32
-volumes (``sailentgrads/my_model_trainer.py:185-199``: 8.5 MB/sample, pageable memory).  Here batches
-are 8-bit, copied sample-by-sample straight out of the store's pinned cache on a dedicated copy
-stream into a ring of device buffers, so the copy of batch i+1 overlaps the compute of batch i.
+volumes (``sailentgrads/my_model_trainer.py:185-199``: 8.5 MB/sample, pageable memory), again for
+every epoch, and stages each client's test split twice per round (global, then personalised model:
+``sailentgrads_api.py:247-256``).  Here volumes stay 8-bit (2.1 MB/sample) and
+
+* ``stream``   mode copies batch by batch out of the store's pinned cache on a dedicated copy stream into a
+               ring of device buffers (the copy of batch i+1.. overlaps the compute of batch i);
+* ``client``   mode (default for index loaders) uploads the *set* of volumes a loader draws from once into a
+               device slot -- every epoch's shuffled batches, and both evaluation passes, are then assembled
+               on the device by one gather launch.  Uploads are queued ahead (:meth:`BatchStager.want`) so the
+               next clients' data and the round's test splits cross PCIe while the current client trains;
+* ``resident`` mode (:class:`ResidentStager`) keeps the whole store on the device: no copies at all inside a
+               round (datasets that fit in HBM: 21 x 40 ABCD volumes are 1.8 GB of 180 GB).
 """
 from __future__ import annotations
 
-from typing import Iterator, Tuple
-
+import ctypes as C
 import os
+from typing import Dict, Iterator, List, Optional, Sequence, Tuple
 
 import numpy as np
 import torch
 
 from ..data.volumes import VolumeStore
 
+_GATHER_ARG_ROWS = 64       # nidt_gather_rows_u8_args passes at most this many row numbers by value
+
+
+class _Slot:
+    """One device buffer of ``cap`` volumes + labels, filled by the copy stream, read by the compute stream."""
+
+    def __init__(self, cap: int, shape, device, need_pin_x: bool):
+        self.cap = cap
+        self.x = torch.empty((cap,) + tuple(shape), dtype=torch.uint8, device=device)
+        self.y = torch.empty(cap, dtype=torch.float32, device=device)
+        self.pin_y = torch.empty(cap, dtype=torch.float32).pin_memory()
+        self.pin_x = torch.empty((cap,) + tuple(shape), dtype=torch.uint8).pin_memory() if need_pin_x else None
+        self.ready = torch.cuda.Event()
+        self.consumed = torch.cuda.Event()
+        self.busy = False
+
+
+class _Entry:
+    """The volumes of one loader (or of a group of loaders) on their way to / resident in a slot."""
+
+    def __init__(self, loaders: Sequence, kind: str):
+        self.loaders = tuple(loaders)
+        self.kind = kind
+        self.ids: Dict[int, np.ndarray] = {}
+        self.base: Dict[int, int] = {}
+        rows = []
+        off = 0
+        for l in self.loaders:
+            u = np.unique(np.asarray(l.indices).astype(np.int64))
+            self.ids[id(l)] = u
+            self.base[id(l)] = off
+            rows.append(u)
+            off += len(u)
+        self.rows = np.ascontiguousarray(np.concatenate(rows) if rows else np.zeros(0, np.int64))
+        self.slot: Optional[_Slot] = None
+        self.opened = False
+
+    def holds(self, loader) -> bool:
+        return id(loader) in self.base
+
 
 class BatchStager:
-    def __init__(self, store: VolumeStore, device: torch.device, batch_size: int, depth: int = 2, sort_indices: bool = True):
+    def __init__(self, store: VolumeStore, device: torch.device, batch_size: int, depth: int = 4, sort_indices: bool = True,
+                 train_slots: int = 3, eval_slots: int = 2, max_cache_bytes: int = 8 << 30):
         self.store = store
         self.device = torch.device(device)
         self.batch_size = batch_size
@@ -26,74 +76,99 @@ class BatchStager:
         self.sort_indices = sort_indices
         self.cuda = self.device.type == "cuda"
         self.h2d_bytes = 0
+        self.h2d_copies = 0
+        self.gather_launches = 0
+        self._row_bytes = int(np.prod(store.shape))
+        self.max_cache_rows = max(1, max_cache_bytes // self._row_bytes)
+        self._pool_depth = {"train": train_slots, "eval": eval_slots}
+        self._pools: Dict[str, List[_Slot]] = {"train": [], "eval": []}
+        self._queue: List[_Entry] = []          # wanted, in upload order; entries leave when they are closed
+        self._ring_ready = False
+        self._native = None
+        self._pinned_cache = None
         if self.cuda:
             self.copy_stream = torch.cuda.Stream(device=self.device)
-            shp = (batch_size,) + tuple(store.shape)
-            self.dev_x = [torch.empty(shp, dtype=torch.uint8, device=self.device) for _ in range(depth)]
-            self.dev_y = [torch.empty(batch_size, dtype=torch.float32, device=self.device) for _ in range(depth)]
-            self.pin_y = [torch.empty(batch_size, dtype=torch.float32).pin_memory() for _ in range(depth)]
-            self.ready = [torch.cuda.Event() for _ in range(depth)]
-            self.consumed = [torch.cuda.Event() for _ in range(depth)]
             cache = getattr(store, "_cache", None)
             if cache is None:
                 cache = getattr(store, "volumes", None)
-            self._pinned_cache = cache if (cache is not None and cache.is_pinned()) else None
-            if self._pinned_cache is None:
-                self.pin_x = [torch.empty(shp, dtype=torch.uint8).pin_memory() for _ in range(depth)]
-            self._native = None
+            self._pinned_cache = cache if (cache is not None and cache.is_pinned() and cache.is_contiguous()) else None
             self._kernel_blocks = int(os.environ.get("NIDT_STAGER_BLOCKS", "0"))      # > 0: stage with a copy kernel instead of the copy engine
-            self.pin_idx = [torch.empty(batch_size, dtype=torch.int64).pin_memory() for _ in range(depth)]
-            self._row_bytes = int(np.prod(store.shape))
-            if self._pinned_cache is not None and self._pinned_cache.is_contiguous():
-                try:
-                    import ctypes as C
-                    from ..ops import native
-                    lib = native.load()
-                    lib.nidt_copy_rows_h2d.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p]
-                    lib.nidt_copy_rows_h2d.restype = C.c_int
-                    lib.nidt_gather_rows_u8_capped.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_int, C.c_void_p]
-                    lib.nidt_gather_rows_u8_capped.restype = C.c_int
-                    self._native = lib
-                except Exception:
-                    self._native = None
+            from ..ops import native
+            lib = native.load()
+            i32, i64, vp = C.c_int, C.c_int64, C.c_void_p
+            lib.nidt_copy_rows_h2d_counted.argtypes = [vp, vp, i32, i64, vp, vp, C.POINTER(i32)]
+            lib.nidt_copy_rows_h2d_counted.restype = i32
+            lib.nidt_gather_rows_u8_capped.argtypes = [vp, vp, vp, i32, i64, i32, vp]
+            lib.nidt_gather_rows_u8_capped.restype = i32
+            lib.nidt_gather_rows_u8_args.argtypes = [vp, vp, vp, i32, i64, vp, vp, vp]
+            lib.nidt_gather_rows_u8_args.restype = i32
+            self._native = lib
+            self._gx = [torch.empty((batch_size,) + tuple(store.shape), dtype=torch.uint8, device=self.device) for _ in range(2)]
+            self._gy = [torch.empty(batch_size, dtype=torch.float32, device=self.device) for _ in range(2)]
+            self._gk = 0
+
+    # ------------------------------------------------------------------ copies
+    def _copy_rows(self, ids: np.ndarray, dst_x: torch.Tensor, pin_x: Optional[torch.Tensor]) -> None:
+        """Enqueue ``dst_x[j] = volume ids[j]`` on the copy stream (the caller holds the stream context)."""
+        from ..ops import native
+        n = len(ids)
+        if n == 0:
+            return
+        if self._pinned_cache is not None:
+            cnt = C.c_int(0)
+            rows = np.ascontiguousarray(ids, dtype=np.int64)
+            native.check(self._native.nidt_copy_rows_h2d_counted(self._pinned_cache.data_ptr(), rows.ctypes.data, n, self._row_bytes,
+                                                                 dst_x.data_ptr(), self.copy_stream.cuda_stream, C.byref(cnt)), "nidt_copy_rows_h2d")
+            self.h2d_copies += cnt.value
+        else:
+            self.store.fetch(ids, out=pin_x)
+            dst_x[:n].copy_(pin_x[:n], non_blocking=True)
+            self.h2d_copies += 1
+        self.h2d_bytes += n * self._row_bytes
+
+    # ------------------------------------------------------------------ stream mode (ring of batch buffers)
+    def _ring_init(self) -> None:
+        shp = (self.batch_size,) + tuple(self.store.shape)
+        d = self.depth
+        self.dev_x = [torch.empty(shp, dtype=torch.uint8, device=self.device) for _ in range(d)]
+        self.dev_y = [torch.empty(self.batch_size, dtype=torch.float32, device=self.device) for _ in range(d)]
+        self.pin_y = [torch.empty(self.batch_size, dtype=torch.float32).pin_memory() for _ in range(d)]
+        self.pin_x = [torch.empty(shp, dtype=torch.uint8).pin_memory() for _ in range(d)] if self._pinned_cache is None else [None] * d
+        self.pin_idx = [torch.empty(self.batch_size, dtype=torch.int64).pin_memory() for _ in range(d)]
+        self.ready = [torch.cuda.Event() for _ in range(d)]
+        self.consumed = [torch.cuda.Event() for _ in range(d)]
+        self._ring_ready = True
 
     def _issue(self, slot: int, idx: torch.Tensor) -> int:
         """Enqueue the H2D copies of one batch on the copy stream; returns the batch size."""
+        from ..ops import native
         ids = idx.numpy().astype(np.int64)
         if self.sort_indices:
             ids = np.sort(ids)
         b = len(ids)
         with torch.cuda.stream(self.copy_stream):
             self.copy_stream.wait_event(self.consumed[slot])
-            if self._pinned_cache is not None:
-                if self._native is not None and self._kernel_blocks > 0:
-                    # a few CTAs read the pinned host rows over PCIe themselves (no copy-engine traffic next to the compute kernels)
-                    self.pin_idx[slot][:b] = torch.from_numpy(np.ascontiguousarray(ids, dtype=np.int64))
-                    rc = self._native.nidt_gather_rows_u8_capped(self._pinned_cache.data_ptr(), self.pin_idx[slot].data_ptr(), self.dev_x[slot].data_ptr(),
-                                                                 b, self._row_bytes, self._kernel_blocks, self.copy_stream.cuda_stream)
-                    if rc != 0:
-                        raise RuntimeError("nidt_gather_rows_u8_capped failed")
-                elif self._native is not None:      # one native call issues the per-sample copies (no per-copy framework overhead)
-                    rows = np.ascontiguousarray(ids, dtype=np.int64)
-                    rc = self._native.nidt_copy_rows_h2d(self._pinned_cache.data_ptr(), rows.ctypes.data, b, self._row_bytes,
-                                                         self.dev_x[slot].data_ptr(), self.copy_stream.cuda_stream)
-                    if rc != 0:
-                        raise RuntimeError("nidt_copy_rows_h2d failed")
-                else:
-                    for j, i in enumerate(ids):
-                        self.dev_x[slot][j].copy_(self._pinned_cache[int(i)], non_blocking=True)
+            if self._pinned_cache is not None and self._kernel_blocks > 0:
+                # a few CTAs read the pinned host rows over PCIe themselves (no copy-engine traffic next to the compute kernels)
+                self.pin_idx[slot][:b] = torch.from_numpy(np.ascontiguousarray(ids, dtype=np.int64))
+                native.check(self._native.nidt_gather_rows_u8_capped(self._pinned_cache.data_ptr(), self.pin_idx[slot].data_ptr(), self.dev_x[slot].data_ptr(),
+                                                                     b, self._row_bytes, self._kernel_blocks, self.copy_stream.cuda_stream),
+                             "nidt_gather_rows_u8_capped")
+                self.h2d_bytes += b * self._row_bytes
+                self.h2d_copies += 1
             else:
-                self.store.fetch(ids, out=self.pin_x[slot])
-                self.dev_x[slot][:b].copy_(self.pin_x[slot][:b], non_blocking=True)
+                if self.pin_x[slot] is not None:
+                    self.ready[slot].synchronize()         # the pinned bounce buffer is about to be overwritten by the host
+                self._copy_rows(ids, self.dev_x[slot], self.pin_x[slot])
             self.pin_y[slot][:b] = torch.from_numpy(self.store.labels[ids])
             self.dev_y[slot][:b].copy_(self.pin_y[slot][:b], non_blocking=True)
             self.ready[slot].record(self.copy_stream)
-        self.h2d_bytes += b * int(np.prod(self.store.shape)) + 4 * b
+        self.h2d_bytes += 4 * b
         return b
 
     def iterate(self, loader, lookahead=None) -> Iterator[Tuple[torch.Tensor, torch.Tensor]]:
         """Yields ``(x_u8 [b,D,H,W], y [b])`` on the device; the tensors of one iteration stay valid
-        until the next-but-one iteration (ring depth 2).
+        until ``depth - 1`` further iterations have been drawn.
 
         ``lookahead``: the index stream the NEXT call will iterate (the next client's batches).  When this stream
         runs dry its first batch is copied right away, so the next call starts with its data already on the way
@@ -106,6 +181,8 @@ class BatchStager:
                 x, y = self.store.fetch(ids)
                 yield x, y
             return
+        if not self._ring_ready:
+            self._ring_init()
         carry, self._carry = getattr(self, "_carry", None), None
         cur = torch.cuda.current_stream(self.device)
         if carry is not None and carry[0] is loader:
@@ -141,3 +218,197 @@ class BatchStager:
             cur.wait_event(self.ready[s])
             yield self.dev_x[s][:n], self.dev_y[s][:n]
             self.consumed[s].record(cur)
+
+    # ------------------------------------------------------------------ client mode (device slot per loader / loader group)
+    def cacheable(self, loader) -> bool:
+        return self.cuda and hasattr(loader, "indices") and 0 < len(loader.indices) <= self.max_cache_rows
+
+    def want(self, loaders: Sequence, kind: str = "train", group: bool = False) -> None:
+        """Declare loaders that will be iterated soon, in order.  Their volumes are uploaded as slots become free
+        (``train_slots`` / ``eval_slots`` deep), behind whatever the compute stream is doing.  ``group=True`` uploads
+        all of them into ONE slot (the round's test splits, evaluated by several models)."""
+        if not self.cuda:
+            return
+        loaders = [l for l in loaders if self.cacheable(l)]
+        if not loaders:
+            return
+        if group:
+            if not any(e.loaders == tuple(loaders) and not e.opened for e in self._queue):
+                ent = _Entry(loaders, kind)
+                if len(ent.rows) <= self.max_cache_rows:
+                    self._queue.append(ent)
+        else:
+            for l in loaders:
+                if not any(len(e.loaders) == 1 and e.holds(l) and not e.opened for e in self._queue):
+                    self._queue.append(_Entry([l], kind))
+        self._pump()
+
+    def _free_slot(self, kind: str, rows: int, force: bool) -> Optional[_Slot]:
+        pool = self._pools[kind]
+        for s in pool:
+            if not s.busy and s.cap >= rows:
+                return s
+        for i, s in enumerate(pool):
+            if not s.busy:                                   # free but too small: replace it once the GPU is done with it
+                s.consumed.synchronize()
+                pool[i] = _Slot(rows, self.store.shape, self.device, self._pinned_cache is None)
+                return pool[i]
+        if len(pool) < self._pool_depth[kind]:
+            cap = max([rows] + [len(e.rows) for e in self._queue if e.kind == kind])
+            pool.append(_Slot(cap, self.store.shape, self.device, self._pinned_cache is None))
+            return pool[-1]
+        if force:
+            # every slot is held by an upload nobody has opened (a mispredicted prefetch): evict the oldest and take its slot
+            for e in self._queue:
+                if e.kind == kind and e.slot is not None and not e.opened:
+                    slot, e.slot = e.slot, None
+                    self._queue.remove(e)
+                    slot.busy = False
+                    if slot.cap < rows:
+                        slot.ready.synchronize()
+                        pool[pool.index(slot)] = slot = _Slot(rows, self.store.shape, self.device, self._pinned_cache is None)
+                    return slot
+            pool.append(_Slot(rows, self.store.shape, self.device, self._pinned_cache is None))
+            return pool[-1]
+        return None
+
+    def _pump(self, force_entry: Optional[_Entry] = None) -> None:
+        """Issue queued uploads, oldest first, while slots are free."""
+        for ent in list(self._queue):
+            if ent.slot is not None or ent not in self._queue:
+                continue
+            slot = self._free_slot(ent.kind, len(ent.rows), force=ent is force_entry)
+            if slot is None:
+                if force_entry is None or ent is force_entry:
+                    break
+                continue
+            slot.busy = True
+            ent.slot = slot
+            n = len(ent.rows)
+            with torch.cuda.stream(self.copy_stream):
+                self.copy_stream.wait_event(slot.consumed)
+                if slot.pin_x is not None:
+                    slot.ready.synchronize()
+                self._copy_rows(ent.rows, slot.x, slot.pin_x)
+                slot.pin_y[:n] = torch.from_numpy(self.store.labels[ent.rows])
+                slot.y[:n].copy_(slot.pin_y[:n], non_blocking=True)
+                slot.ready.record(self.copy_stream)
+            self.h2d_bytes += 4 * n
+            self.h2d_copies += 1
+
+    def open(self, loaders, kind: str = "train") -> _Entry:
+        """The entry holding ``loaders`` (one loader, or the exact group passed to ``want(group=True)``), uploaded or on its
+        way; the current stream waits for the upload.  Pair with :meth:`close`."""
+        group = isinstance(loaders, (list, tuple))
+        key = tuple(loaders) if group else (loaders,)
+        ent = next((e for e in self._queue if e.loaders == key and not e.opened), None)
+        if ent is None:
+            ent = _Entry(key, kind)
+            self._queue.append(ent)
+        if ent.slot is None:
+            self._pump(force_entry=ent)
+        ent.opened = True
+        torch.cuda.current_stream(self.device).wait_event(ent.slot.ready)
+        return ent
+
+    def close(self, ent: _Entry) -> None:
+        ent.slot.consumed.record(torch.cuda.current_stream(self.device))
+        ent.slot.busy = False
+        self._queue.remove(ent)
+        self._pump()
+
+    def _positions(self, ent: _Entry, loader, ids: np.ndarray) -> np.ndarray:
+        return ent.base[id(loader)] + np.searchsorted(ent.ids[id(loader)], ids)
+
+    def batch_from(self, ent: _Entry, loader, batch_idx) -> Tuple[torch.Tensor, torch.Tensor]:
+        """One index batch of ``loader`` assembled from its slot: a view when the (sorted) rows are adjacent in the slot,
+        otherwise one gather launch (volumes + labels, row numbers passed in the kernel parameters)."""
+        from ..ops import native
+        ids = np.asarray(batch_idx).astype(np.int64)
+        if self.sort_indices:
+            ids = np.sort(ids)
+        pos = self._positions(ent, loader, ids)
+        n = len(pos)
+        slot = ent.slot
+        if n > 0 and int(pos[-1]) - int(pos[0]) == n - 1 and (n == 1 or bool(np.all(np.diff(pos) == 1))):
+            p0 = int(pos[0])
+            return slot.x[p0:p0 + n], slot.y[p0:p0 + n]
+        k = self._gk = (self._gk + 1) % len(self._gx)
+        if n > self._gx[k].shape[0]:
+            self._gx = [torch.empty((n,) + tuple(self.store.shape), dtype=torch.uint8, device=self.device) for _ in self._gx]
+            self._gy = [torch.empty(n, dtype=torch.float32, device=self.device) for _ in self._gy]
+        gx, gy = self._gx[k][:n], self._gy[k][:n]
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        for o in range(0, n, _GATHER_ARG_ROWS):
+            m = min(_GATHER_ARG_ROWS, n - o)
+            part = np.ascontiguousarray(pos[o:o + m], dtype=np.int64)
+            native.check(self._native.nidt_gather_rows_u8_args(slot.x.data_ptr(), part.ctypes.data, gx[o:o + m].data_ptr(), m, self._row_bytes,
+                                                               slot.y.data_ptr(), gy[o:o + m].data_ptr(), st), "nidt_gather_rows_u8_args")
+            native.count_launches(1)
+            self.gather_launches += 1
+        return gx, gy
+
+    def cached_batches(self, loader, epochs: int = 1) -> Iterator[Tuple[int, torch.Tensor, torch.Tensor]]:
+        """``(epoch, x, y)`` over ``epochs`` passes of ``loader`` with its volumes uploaded once."""
+        ent = self.open(loader)
+        try:
+            for e in range(epochs):
+                for b in loader:
+                    x, y = self.batch_from(ent, loader, b[0])
+                    yield e, x, y
+        finally:
+            self.close(ent)
+
+
+class ResidentStager(BatchStager):
+    """The whole store lives on the device (uploaded once, at construction): batches are views / gathers of it and
+    nothing crosses PCIe afterwards.  For datasets that fit in HBM next to the activations."""
+
+    def __init__(self, store: VolumeStore, device: torch.device, batch_size: int, **kw):
+        super().__init__(store, device, batch_size, **kw)
+        if not self.cuda:
+            return
+        n = len(store.labels)
+        cache = getattr(store, "_cache", None)
+        if cache is None:
+            cache = getattr(store, "volumes", None)
+        ent = _Entry([], "resident")
+        slot = _Slot.__new__(_Slot)
+        slot.cap = n
+        slot.x = cache.to(self.device) if cache is not None else store.fetch(np.arange(n))[0].to(self.device)
+        slot.y = torch.from_numpy(np.asarray(store.labels, dtype=np.float32)).to(self.device)
+        slot.ready, slot.consumed, slot.busy = torch.cuda.Event(), torch.cuda.Event(), True
+        slot.ready.record(torch.cuda.current_stream(self.device))
+        ent.slot = slot
+        self._all = ent
+
+    def cacheable(self, loader) -> bool:
+        return self.cuda and hasattr(loader, "indices")
+
+    def want(self, loaders, kind: str = "train", group: bool = False) -> None:
+        return None
+
+    def _positions(self, ent: _Entry, loader, ids: np.ndarray) -> np.ndarray:
+        return ids
+
+    def open(self, loaders, kind: str = "train") -> _Entry:
+        return self._all
+
+    def close(self, ent: _Entry) -> None:
+        return None
+
+    def iterate(self, loader, lookahead=None):
+        if not self.cuda:
+            yield from super().iterate(loader, lookahead)
+            return
+        for b in loader:
+            yield self.batch_from(self._all, None, b[0])
+
+
+def make_stager(mode: str, store: VolumeStore, device, batch_size: int) -> BatchStager:
+    """``stream`` | ``client`` (same class; the trainer decides per loader) | ``resident``."""
+    if mode == "resident":
+        return ResidentStager(store, device, batch_size)
+    if mode not in ("stream", "client", "auto"):
+        raise ValueError(f"unknown staging mode {mode!r} (stream | client | resident)")
+    return BatchStager(store, device, batch_size)

@@ -24,7 +24,7 @@ api.run_round(0, mask=api.mask)
 torch.cuda.synchronize()
 for mode in ("pinned-host", "device-resident"):
     if mode == "device-resident":
-        tr._stagers[a.batch] = bench.make_device_stager(store, dev, a.batch)
+        tr.set_staging("resident")
         api.run_round(1, mask=api.mask); torch.cuda.synchronize()
     pr = cProfile.Profile()
     t0 = time.perf_counter()

@@ -28,7 +28,7 @@ api = SalientGradsAPI(ds, dev, fl_args, tr, logger, dist=DistContext(device=dev)
 api.w_init = api.w_global.clone()
 api.mask = api.generate_global_mask_snip()
 if mode == "device":
-    tr._stagers[a.batch] = bench.make_device_stager(store, dev, a.batch)
+    tr.set_staging("resident")
 for r in range(3):
     api.run_round(r, mask=api.mask)
 torch.cuda.synchronize()

@@ -1,0 +1,114 @@
+"""Host -> device staging on a GPU: the per-client device cache (`client` mode) and the device-resident store (`resident`) hand the
+trainer exactly the batches the batch-by-batch copy ring (`stream`) does, with each volume crossing PCIe once per use of a loader."""
+import logging
+import types
+
+import numpy as np
+import pytest
+import torch
+
+from neuroimagedisttraining_b200.data import SyntheticABCD, load_partition_data_abcd
+from neuroimagedisttraining_b200.fl import SlabTrainer
+from neuroimagedisttraining_b200.models import Tiny3DCNN
+from neuroimagedisttraining_b200.runtime.staging import BatchStager, ResidentStager
+
+pytestmark = pytest.mark.gpu
+MODEL_SHAPE = (27, 29, 31)
+SHAPE = (9, 11, 13)       # 1287 bytes per volume: rows are not 16-byte aligned, like the 2 122 945-byte ABCD volumes
+
+
+def _setup(n_sites=4, per_site=15, batch=4, shape=SHAPE):
+    store = SyntheticABCD(n_sites * per_site, shape=shape, n_sites=n_sites, seed=1, pool=3, pin=True, site_sizes=[per_site] * n_sites)
+    ds = load_partition_data_abcd(store, client_number=n_sites, batch_size=batch)
+    return store, ds
+
+
+def _collect(gen):
+    return [(x.clone(), y.clone()) for x, y in gen]
+
+
+def test_client_cache_and_resident_batches_equal_the_stream_ring():
+    dev = torch.device("cuda:0")
+    store, ds = _setup()
+    train, test = ds[5], ds[6]
+    stream, client, resident = BatchStager(store, dev, 4), BatchStager(store, dev, 4, train_slots=2), ResidentStager(store, dev, 4)
+    client.want([train[c] for c in range(4)])            # more loaders than slots: uploads continue as slots are released
+    for c in range(4):
+        loader = train[c]
+        st0 = loader.state()
+        ref = _collect(stream.iterate(loader))
+        loader.set_state(st0)
+        got = [(x.clone(), y.clone()) for _, x, y in client.cached_batches(loader, 1)]
+        loader.set_state(st0)
+        res = _collect(resident.iterate(loader))
+        assert len(ref) == len(got) == len(res) == len(loader)
+        for (xr, yr), (xg, yg), (xs, ys) in zip(ref, got, res):
+            assert torch.equal(xr, xg) and torch.equal(yr, yg)
+            assert torch.equal(xr, xs) and torch.equal(yr, ys)
+    torch.cuda.synchronize()
+    n_train = sum(train[c].num_samples for c in range(4))
+    row = int(np.prod(SHAPE))
+    assert client.h2d_bytes == n_train * (row + 4)       # one upload per volume (+ its label)
+    assert not client._queue                             # everything that was wanted has been consumed
+    # two epochs draw from ONE upload; the ring copies every batch again
+    c0, s0 = client.h2d_bytes, stream.h2d_bytes
+    loader = train[0]
+    st0 = loader.state()
+    ref = _collect(stream.iterate(_Epochs(loader, 2)))
+    loader.set_state(st0)
+    got = [(e, x.clone(), y.clone()) for e, x, y in client.cached_batches(loader, 2)]
+    assert [e for e, _, _ in got] == [0] * len(loader) + [1] * len(loader)
+    assert all(torch.equal(a[0], b[1]) and torch.equal(a[1], b[2]) for a, b in zip(ref, got))
+    assert client.h2d_bytes - c0 == loader.num_samples * (row + 4)
+    assert stream.h2d_bytes - s0 == 2 * loader.num_samples * (row + 4)
+    # a group of test loaders in one slot (unshuffled batches are views of the slot: no gather launch)
+    g0 = client.gather_launches
+    loaders = [test[c] for c in range(4)]
+    client.want(loaders, kind="eval", group=True)
+    ent = client.open(loaders, kind="eval")
+    for l in loaders:
+        for b in l:
+            x, y = client.batch_from(ent, l, b[0])
+            xr, yr = store.fetch(np.sort(b[0].numpy()))
+            assert torch.equal(x.cpu(), xr) and torch.equal(y.cpu(), yr)
+    client.close(ent)
+    assert client.gather_launches == g0
+
+
+class _Epochs:
+    def __init__(self, loader, n):
+        self.loader, self.n = loader, n
+
+    def __iter__(self):
+        for _ in range(self.n):
+            yield from self.loader
+
+
+def _trainer(store, staging):
+    args = types.SimpleNamespace(lr=0.05, lr_decay=1.0, momentum=0.0, wd=0.0, epochs=2, batch_size=4, client_optimizer="sgd", snip_mask=False,
+                                 dataset="ABCD")
+    torch.manual_seed(0)
+    model = Tiny3DCNN(1, in_shape=MODEL_SHAPE, p_drop=0.0)
+    return SlabTrainer(model, args, logging.getLogger("t"), device=torch.device("cuda:0"), store=store, staging=staging)
+
+
+@pytest.mark.parametrize("staging", ["client", "resident"])
+def test_training_and_merged_evaluation_do_not_depend_on_the_staging_mode(staging):
+    outs = {}
+    for mode in ("stream", staging):
+        store2, ds2 = _setup(n_sites=3, per_site=10, shape=MODEL_SHAPE)       # fresh loaders: identical shuffle streams
+        tr = _trainer(store2, mode)
+        slabs = []
+        tr.plan_data([ds2[5][c] for c in range(3)])
+        for c in range(3):
+            s = tr.engine.new_slab()
+            tr.attach(s)
+            tr.train(ds2[5][c], round_idx=0, epochs=2)
+            slabs.append(s)
+        glob = tr.engine.new_slab()
+        res = tr.test_multi([ds2[6][c] for c in range(3)], [[glob] * 3, slabs])
+        ref0 = tr.test_many([(glob, ds2[6][c]) for c in range(3)])
+        assert res[0] == ref0
+        outs[mode] = (torch.stack([s.flat.clone() for s in slabs]), res)
+    assert torch.equal(outs["stream"][0], outs[staging][0])
+    assert outs["stream"][1] == outs[staging][1]
