@@ -26,10 +26,24 @@ int nidt_norm_scratch_floats(void);
 int nidt_topk_scratch_bytes(void);
 int nidt_max_agg_sources(void);
 
+/* Per-step scalars and result pointers read from DEVICE memory by the kernels that need them (the SGD update and the head), so
+ * that a captured CUDA graph of a step can be replayed with new values: a tiny kernel writes this struct in front of the replay.
+ * The reference re-creates its optimizer and re-reads its python scalars every step (my_model_trainer.py:209,224-231). */
+typedef struct {
+    float lr, momentum, wd, clip_norm;
+    int first_step, reserved;
+    uint64_t seed;
+    float* loss_acc;       /* training: += mean loss */
+    double* counters;      /* evaluation: correct, loss_sum, total */
+} nidt_dyn_t;
+
 /* clip_grad_norm_(clip) + SGD(momentum, wd) + `w *= mask` in two launches over the whole slab.
  * ref: fedml_api/standalone/sailentgrads/my_model_trainer.py:209,224-231.  scratch: nidt_norm_scratch_floats() floats. */
 int nidt_masked_sgd_step(float* w, const float* g, float* mom, const float* mask, int64_t n, float lr, float momentum,
                          float wd, float clip_norm, int first_step, float* scratch, float* norm_out, void* stream);
+/* the same update with lr / momentum / wd / clip / first_step read from *dyn (device memory); mom must be NULL when unused */
+int nidt_masked_sgd_step_dyn(float* w, const float* g, float* mom, const float* mask, int64_t n, float* scratch, const nidt_dyn_t* dyn,
+                             void* stream);
 int nidt_grad_norm(const float* g, int64_t n, float* scratch, float* norm_out, void* stream);
 
 /* out = sum_i weights[i]*srcs[i] in list order (separate mul/add: bit-identical to the reference loop), optional
@@ -100,6 +114,10 @@ int nidt_head_fwd_bwd(const void* feat, const float* y, const float* W1, const f
                       float* gW1, float* gb1, float* gW2, float* gb2, void* dfeat, float* loss_acc, double* eval_counters,
                       float* logits_out, int B, int S, int C, int Hd, float p_drop, uint64_t seed, int train,
                       int double_sigmoid, void* stream);
+/* the same head with the dropout seed and the loss accumulator (train) / eval counters (eval) read from *dyn (device memory) */
+int nidt_head_fwd_bwd_dyn(const void* feat, const float* y, const float* W1, const float* b1, const float* W2, const float* b2,
+                          float* gW1, float* gb1, float* gW2, float* gb2, void* dfeat, float* logits_out, int B, int S, int C, int Hd,
+                          float p_drop, int train, int double_sigmoid, const nidt_dyn_t* dyn, void* stream);
 
 /* ------------------------------------------------- tcgen05/TMA implicit-GEMM 3-D convolution (conv_tc.cu) */
 /* ref: nn.Conv3d forward/backward at salient_models.py:152-166 (cuDNN fp32).  Cin % 64 == 0; box = tile of output
@@ -199,6 +217,21 @@ typedef struct {
     float p_drop, input_scale;
     float *loss_acc, *eval_logits, *norm_scratch;
 } nidt_plan_t;
+/* nidt_plan_train_step / nidt_plan_eval as CUDA-graph replays: the launch sequence is captured once per distinct set of
+ * pointer arguments (plan, x, y, batch, slab, grad, mom, mask, do_update / double_sigmoid) and replayed afterwards; the scalars of
+ * the step (lr, momentum, wd, clip, first_step, seed) and the result pointers (loss_acc / counters) travel through `dyn`, a
+ * caller-allocated DEVICE nidt_dyn_t that a one-thread kernel fills in front of every replay.  Kernel-to-kernel dependencies are
+ * resolved on the device, so the ~48 launches of a step neither wait for the host nor for command fetches over a PCIe link that
+ * is busy with the next client's upload.  x / y must therefore be stable buffers (the stagers gather every batch into one).
+ * The reference has no counterpart (eager autograd, my_model_trainer.py:201-235). */
+int nidt_plan_train_step_graph(const nidt_plan_t* plan, const void* x_u8, const float* y, int batch, float* slab, float* grad, float* mom,
+                               const float* mask, int64_t n_params, float lr, float momentum, float wd, float clip_norm, int first_step,
+                               uint64_t seed, int do_update, float* loss_acc, nidt_dyn_t* dyn, int* launches, void* stream);
+int nidt_plan_eval_graph(const nidt_plan_t* plan, const void* x_u8, const float* y, int batch, const float* slab, double* counters,
+                         int double_sigmoid, nidt_dyn_t* dyn, int* launches, void* stream);
+/* drop the cached graphs of one plan (plan == NULL: all); the number of cached graphs */
+int nidt_plan_graph_clear(const nidt_plan_t* plan);
+int nidt_plan_graph_count(void);
 /* weights of the attached slab -> bf16 packed copies (call when the slab changed outside a training step) */
 int nidt_plan_pack_weights(const nidt_plan_t* plan, const float* slab, void* stream);
 /* forward + head + backward (gradients into `grad`, params-first layout of the slab) and, when do_update != 0, the masked SGD

@@ -62,6 +62,7 @@ struct Ctx {
     void* st;
     int launches = 0;
     Box cur_box[8];
+    const nidt_dyn_t* dyn = nullptr;      // graph capture: step scalars / result pointers come from device memory
 };
 
 int pack_weights(Ctx& c, const float* slab) {
@@ -116,6 +117,14 @@ int head(Ctx& c, const float* y, const float* slab, float* grad, bool train, dou
     const nidt_plan_t* p = c.p;
     const nidt_block_t& last = p->blocks[p->n_blocks - 1];
     const bool g = train && grad != nullptr;
+    if (c.dyn != nullptr) {
+        NIDT_TRY(nidt_head_fwd_bwd_dyn(last.a, y, at(slab, p->off_fc1_w), at(slab, p->off_fc1_b), at(slab, p->off_fc2_w), at(slab, p->off_fc2_b),
+                                       g ? at(grad, p->off_fc1_w) : nullptr, g ? at(grad, p->off_fc1_b) : nullptr, g ? at(grad, p->off_fc2_w) : nullptr,
+                                       g ? at(grad, p->off_fc2_b) : nullptr, train ? last.da : nullptr, p->eval_logits, c.B, p->head_s, p->head_c,
+                                       p->head_hidden, p->p_drop, train ? 1 : 0, double_sigmoid, c.dyn, c.st));
+        ++c.launches;
+        return 0;
+    }
     NIDT_TRY(nidt_head_fwd_bwd(last.a, y, at(slab, p->off_fc1_w), at(slab, p->off_fc1_b), at(slab, p->off_fc2_w), at(slab, p->off_fc2_b),
                                g ? at(grad, p->off_fc1_w) : nullptr, g ? at(grad, p->off_fc1_b) : nullptr, g ? at(grad, p->off_fc2_w) : nullptr,
                                g ? at(grad, p->off_fc2_b) : nullptr, train ? last.da : nullptr, train ? p->loss_acc : nullptr, counters, p->eval_logits,
@@ -158,7 +167,127 @@ int backward(Ctx& c, const void* x, float* grad) {
     return 0;
 }
 
+// ------------------------------------------------------------------------------------------------ CUDA-graph replays
+struct GraphKey {
+    const void* plan; const void* x; const void* y; const void* slab; const void* grad; const void* mom; const void* mask; const void* dyn;
+    int64_t n_params; int batch, kind, flag, device;
+    bool operator<(const GraphKey& o) const {
+        return std::tie(plan, x, y, slab, grad, mom, mask, dyn, n_params, batch, kind, flag, device) <
+               std::tie(o.plan, o.x, o.y, o.slab, o.grad, o.mom, o.mask, o.dyn, o.n_params, o.batch, o.kind, o.flag, o.device);
+    }
+};
+struct GraphVal { cudaGraphExec_t exec; int launches; };
+std::mutex g_graph_mu;
+std::map<GraphKey, GraphVal> g_graphs;
+std::map<int, cudaStream_t> g_capture_streams;        // per device: capture needs a non-default stream
+constexpr size_t kMaxGraphs = 1024;
+
+__global__ void set_dyn_kernel(nidt_dyn_t* dyn, const nidt_dyn_t v) { *dyn = v; }
+
+void drop_graphs(const void* plan) {
+    for (auto it = g_graphs.begin(); it != g_graphs.end();) {
+        if (plan == nullptr || it->first.plan == plan) { cudaGraphExecDestroy(it->second.exec); it = g_graphs.erase(it); }
+        else ++it;
+    }
+}
+
+// Records `body` (which launches on the given stream) into an executable graph.
+template <class Body>
+int capture(int device, GraphVal* out, Body body) {
+    cudaStream_t& cap = g_capture_streams[device];
+    if (cap == nullptr) NIDT_CUDA_CHECK(cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking));
+    NIDT_CUDA_CHECK(cudaStreamBeginCapture(cap, cudaStreamCaptureModeRelaxed));
+    int launches = 0;
+    const int rc = body((void*)cap, &launches);
+    cudaGraph_t graph = nullptr;
+    const cudaError_t e = cudaStreamEndCapture(cap, &graph);
+    if (rc != 0) { if (graph) cudaGraphDestroy(graph); return rc; }
+    if (e != cudaSuccess || graph == nullptr) { nidt_set_error("graph capture failed: %s", cudaGetErrorString(e)); cudaGetLastError(); return 1; }
+    cudaGraphExec_t exec = nullptr;
+    const cudaError_t ei = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ei != cudaSuccess) { nidt_set_error("cudaGraphInstantiate: %s", cudaGetErrorString(ei)); cudaGetLastError(); return 1; }
+    out->exec = exec;
+    out->launches = launches;
+    return 0;
+}
+
+template <class Body>
+int replay(const GraphKey& key, const nidt_dyn_t& values, nidt_dyn_t* dyn, int* launches, void* stream, Body body) {
+    std::lock_guard<std::mutex> lock(g_graph_mu);
+    auto it = g_graphs.find(key);
+    if (it == g_graphs.end()) {
+        if (g_graphs.size() >= kMaxGraphs) drop_graphs(nullptr);
+        GraphVal v{};
+        NIDT_TRY(capture(key.device, &v, body));
+        it = g_graphs.emplace(key, v).first;
+    }
+    set_dyn_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(dyn, values);
+    NIDT_LAUNCH_CHECK();
+    NIDT_CUDA_CHECK(cudaGraphLaunch(it->second.exec, (cudaStream_t)stream));
+    if (launches != nullptr) *launches = it->second.launches + 1;
+    return 0;
+}
+
 }  // namespace
+
+NIDT_API int nidt_plan_train_step_graph(const nidt_plan_t* plan, const void* x_u8, const float* y, int batch, float* slab, float* grad, float* mom,
+                                        const float* mask, int64_t n_params, float lr, float momentum, float wd, float clip_norm, int first_step,
+                                        uint64_t seed, int do_update, float* loss_acc, nidt_dyn_t* dyn, int* launches, void* stream) {
+    NIDT_REQUIRE(plan != nullptr && plan->n_blocks >= 1 && plan->n_blocks <= 8, "nidt_plan: bad plan");
+    NIDT_REQUIRE(batch >= 1 && batch <= plan->max_batch, "nidt_plan_train_step_graph: batch %d exceeds the plan's %d", batch, plan->max_batch);
+    NIDT_REQUIRE(dyn != nullptr, "nidt_plan_train_step_graph: dyn is null");
+    int device = 0;
+    NIDT_CUDA_CHECK(cudaGetDevice(&device));
+    float* mom_used = (do_update && momentum != 0.f) ? mom : nullptr;
+    const GraphKey key{plan, x_u8, y, slab, grad, mom_used, do_update ? mask : nullptr, dyn, n_params, batch, 0, do_update, device};
+    nidt_dyn_t v{lr, momentum, wd, clip_norm, first_step, 0, seed, loss_acc, nullptr};
+    const nidt_plan_t snap = *plan;       // the launch sequence bakes the plan's buffers in by value
+    return replay(key, v, dyn, launches, stream, [&](void* st, int* n) -> int {
+        Ctx c{&snap, batch, st};
+        c.dyn = dyn;
+        NIDT_TRY(forward(c, x_u8, slab, true));
+        NIDT_TRY(head(c, y, slab, grad, true, nullptr, 1, 0));
+        NIDT_TRY(backward(c, x_u8, grad));
+        if (do_update) {
+            NIDT_TRY(nidt_masked_sgd_step_dyn(slab, grad, mom_used, mask, n_params, snap.norm_scratch, dyn, st));
+            c.launches += 2;
+            NIDT_TRY(pack_weights(c, slab));
+        }
+        *n = c.launches;
+        return 0;
+    });
+}
+
+NIDT_API int nidt_plan_eval_graph(const nidt_plan_t* plan, const void* x_u8, const float* y, int batch, const float* slab, double* counters,
+                                  int double_sigmoid, nidt_dyn_t* dyn, int* launches, void* stream) {
+    NIDT_REQUIRE(plan != nullptr && plan->n_blocks >= 1 && plan->n_blocks <= 8, "nidt_plan: bad plan");
+    NIDT_REQUIRE(batch >= 1 && batch <= plan->max_batch, "nidt_plan_eval_graph: batch %d exceeds the plan's %d", batch, plan->max_batch);
+    NIDT_REQUIRE(dyn != nullptr && counters != nullptr, "nidt_plan_eval_graph: dyn / counters is null");
+    int device = 0;
+    NIDT_CUDA_CHECK(cudaGetDevice(&device));
+    const GraphKey key{plan, x_u8, y, slab, nullptr, nullptr, nullptr, dyn, 0, batch, 1, double_sigmoid, device};
+    nidt_dyn_t v{0.f, 0.f, 0.f, 0.f, 0, 0, 0, nullptr, counters};
+    const nidt_plan_t snap = *plan;
+    return replay(key, v, dyn, launches, stream, [&](void* st, int* n) -> int {
+        Ctx c{&snap, batch, st};
+        c.dyn = dyn;
+        NIDT_TRY(forward(c, x_u8, const_cast<float*>(slab), false));
+        NIDT_TRY(head(c, y, slab, nullptr, false, nullptr, double_sigmoid, 0));
+        *n = c.launches;
+        return 0;
+    });
+}
+
+NIDT_API int nidt_plan_graph_clear(const nidt_plan_t* plan) {
+    std::lock_guard<std::mutex> lock(g_graph_mu);
+    drop_graphs(plan);
+    return 0;
+}
+NIDT_API int nidt_plan_graph_count() {
+    std::lock_guard<std::mutex> lock(g_graph_mu);
+    return (int)g_graphs.size();
+}
 
 NIDT_API int nidt_plan_pack_weights(const nidt_plan_t* plan, const float* slab, void* stream) {
     NIDT_REQUIRE(plan != nullptr && plan->n_blocks >= 1 && plan->n_blocks <= 8, "nidt_plan: bad plan");

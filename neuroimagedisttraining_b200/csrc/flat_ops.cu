@@ -8,6 +8,7 @@
 //   nidt_global_topk_mask    sum -> /sum -> k-th largest -> mask      (ref: snip.py:80-116)
 //   nidt_count_nonzero / nidt_hamming / nidt_sq_dist                  (ref: model_trainer.py:49-53, slim_util.py:10-19)
 #include "common.cuh"
+#include "../../include/nidt_b200.h"
 #include "topk.cuh"
 #include <cooperative_groups.h>
 #include <stdarg.h>
@@ -48,8 +49,9 @@ __global__ void __launch_bounds__(kFlatThreads) sq_norm_partials_kernel(const fl
 __global__ void __launch_bounds__(kFlatThreads) masked_sgd_kernel(
     float* __restrict__ w, const float* __restrict__ g, float* __restrict__ mom, const float* __restrict__ mask,
     int64_t n, float lr, float mu, float wd, float clip, int first_step,
-    const float* __restrict__ partials, int n_partials, float* __restrict__ norm_out) {
+    const float* __restrict__ partials, int n_partials, float* __restrict__ norm_out, const nidt_dyn_t* __restrict__ dyn) {
     __shared__ float red[kFlatThreads / 32];
+    if (dyn != nullptr) { lr = dyn->lr; mu = dyn->momentum; wd = dyn->wd; clip = dyn->clip_norm; first_step = dyn->first_step; }
     float coef = 1.f;
     if (partials != nullptr) {
         float p = 0.f;
@@ -202,16 +204,29 @@ NIDT_API int nidt_topk_scratch_bytes() { return (int)sizeof(TopkScratch); }
 NIDT_API int nidt_max_agg_sources() { return kMaxAggSrc; }
 
 // scratch: >= nidt_norm_scratch_floats() floats.  norm_out may be null.
+static int masked_sgd_step(float* w, const float* g, float* mom, const float* mask, int64_t n, float lr, float momentum, float wd,
+                           float clip_norm, int first_step, float* scratch, float* norm_out, const nidt_dyn_t* dyn, void* stream);
 NIDT_API int nidt_masked_sgd_step(float* w, const float* g, float* mom, const float* mask, int64_t n,
                                     float lr, float momentum, float wd, float clip_norm, int first_step,
                                     float* scratch, float* norm_out, void* stream) {
+    return masked_sgd_step(w, g, mom, mask, n, lr, momentum, wd, clip_norm, first_step, scratch, norm_out, nullptr, stream);
+}
+// dyn (DEVICE pointer): lr / momentum / wd / clip / first_step are read from it by the kernel; `mom` must already be null when no
+// momentum buffer is to be used (the host cannot look at dyn->momentum).
+NIDT_API int nidt_masked_sgd_step_dyn(float* w, const float* g, float* mom, const float* mask, int64_t n, float* scratch, const nidt_dyn_t* dyn,
+                                        void* stream) {
+    NIDT_REQUIRE(dyn != nullptr, "nidt_masked_sgd_step_dyn: dyn is null");
+    return masked_sgd_step(w, g, mom, mask, n, 0.f, mom != nullptr ? 1.f : 0.f, 0.f, 0.f, 0, scratch, nullptr, dyn, stream);
+}
+static int masked_sgd_step(float* w, const float* g, float* mom, const float* mask, int64_t n, float lr, float momentum, float wd,
+                           float clip_norm, int first_step, float* scratch, float* norm_out, const nidt_dyn_t* dyn, void* stream) {
     NIDT_REQUIRE(n % 4 == 0, "nidt_masked_sgd_step: n=%lld must be a multiple of 4 (slab alignment)", (long long)n);
     NIDT_REQUIRE(scratch != nullptr, "nidt_masked_sgd_step: scratch is null");
     cudaStream_t s = (cudaStream_t)stream;
     sq_norm_partials_kernel<<<kNormBlocks, kFlatThreads, 0, s>>>(g, n, scratch);
     NIDT_LAUNCH_CHECK();
     masked_sgd_kernel<<<flat_grid(n / 4), kFlatThreads, 0, s>>>(w, g, momentum != 0.f ? mom : nullptr, mask, n, lr, momentum, wd,
-                                                                  clip_norm, first_step, scratch, kNormBlocks, norm_out);
+                                                                  clip_norm, first_step, scratch, kNormBlocks, norm_out, dyn);
     NIDT_LAUNCH_CHECK();
     return 0;
 }

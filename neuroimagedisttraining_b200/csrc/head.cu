@@ -9,6 +9,7 @@
 // Feature order: the reference flattens NCDHW (feature = c*S + s); activations here are NDHWC
 // (memory = s*C + c).  The kernel maps between the two so state_dict weights stay interchangeable.
 #include "common.cuh"
+#include "../../include/nidt_b200.h"
 
 namespace nidt {
 
@@ -37,12 +38,19 @@ struct HeadArgs {
     uint64_t seed;
     int train;                   // dropout on / backward
     int double_sigmoid;          // eval loss = BCEWithLogits(sigmoid(z)) as the reference does
+    const nidt_dyn_t* dyn;       // when set: seed, loss_acc (train) / eval_counters (eval) come from device memory (graph replays)
 };
 
 // one CTA, 1024 threads; dynamic smem: f[B][F] (post-dropout, fp32) | h[B][Hd] | dh[B][Hd] | z[B] | dz[B] | W1[Hd][F+1]
 // (W1 is staged once with coalesced loads; every later pass reads it from shared memory)
-__global__ void __launch_bounds__(1024) head_kernel(HeadArgs a) {
+__global__ void __launch_bounds__(1024) head_kernel(const __grid_constant__ HeadArgs args) {
     extern __shared__ float sm[];
+    HeadArgs a = args;
+    if (a.dyn != nullptr) {
+        a.seed = a.dyn->seed;
+        if (a.train) a.loss_acc = a.dyn->loss_acc;
+        else a.eval_counters = a.dyn->counters;
+    }
     const int F = a.S * a.C;
     float* f = sm;
     float* h = f + (size_t)a.B * F;
@@ -164,12 +172,31 @@ __global__ void __launch_bounds__(1024) head_kernel(HeadArgs a) {
 }  // namespace nidt
 using namespace nidt;
 
+static int head_launch(const void* feat, const float* y, const float* W1, const float* b1, const float* W2, const float* b2,
+                       float* gW1, float* gb1, float* gW2, float* gb2, void* dfeat, float* loss_acc, double* eval_counters,
+                       float* logits_out, int B, int S, int C, int Hd, float p_drop, uint64_t seed, int train,
+                       int double_sigmoid, const nidt_dyn_t* dyn, void* stream);
 NIDT_API int nidt_head_fwd_bwd(const void* feat, const float* y, const float* W1, const float* b1, const float* W2, const float* b2,
                                float* gW1, float* gb1, float* gW2, float* gb2, void* dfeat, float* loss_acc, double* eval_counters,
                                float* logits_out, int B, int S, int C, int Hd, float p_drop, uint64_t seed, int train,
                                int double_sigmoid, void* stream) {
+    return head_launch(feat, y, W1, b1, W2, b2, gW1, gb1, gW2, gb2, dfeat, loss_acc, eval_counters, logits_out, B, S, C, Hd, p_drop, seed, train,
+                       double_sigmoid, nullptr, stream);
+}
+// seed and the loss accumulator (train) / eval counters (eval) are read from *dyn (DEVICE memory) by the kernel
+NIDT_API int nidt_head_fwd_bwd_dyn(const void* feat, const float* y, const float* W1, const float* b1, const float* W2, const float* b2,
+                                   float* gW1, float* gb1, float* gW2, float* gb2, void* dfeat, float* logits_out, int B, int S, int C, int Hd,
+                                   float p_drop, int train, int double_sigmoid, const nidt_dyn_t* dyn, void* stream) {
+    NIDT_REQUIRE(dyn != nullptr, "nidt_head_fwd_bwd_dyn: dyn is null");
+    return head_launch(feat, y, W1, b1, W2, b2, gW1, gb1, gW2, gb2, dfeat, nullptr, nullptr, logits_out, B, S, C, Hd, p_drop, 0, train,
+                       double_sigmoid, dyn, stream);
+}
+static int head_launch(const void* feat, const float* y, const float* W1, const float* b1, const float* W2, const float* b2,
+                       float* gW1, float* gb1, float* gW2, float* gb2, void* dfeat, float* loss_acc, double* eval_counters,
+                       float* logits_out, int B, int S, int C, int Hd, float p_drop, uint64_t seed, int train,
+                       int double_sigmoid, const nidt_dyn_t* dyn, void* stream) {
     HeadArgs a{(const __nv_bfloat16*)feat, y, W1, b1, W2, b2, gW1, gb1, gW2, gb2, (__nv_bfloat16*)dfeat, loss_acc, eval_counters,
-               logits_out, B, S, C, Hd, p_drop, seed, train, double_sigmoid};
+               logits_out, B, S, C, Hd, p_drop, seed, train, double_sigmoid, dyn};
     const size_t smem = ((size_t)B * S * C + 2 * (size_t)B * Hd + 2 * (size_t)B + (size_t)Hd * (S * C + 1)) * sizeof(float);
     NIDT_REQUIRE(smem <= 220 * 1024, "nidt_head_fwd_bwd: B*F=%d with hidden %d does not fit one CTA", B * S * C, Hd);
     NIDT_REQUIRE(B <= 256, "nidt_head_fwd_bwd: batch %d > 256", B);

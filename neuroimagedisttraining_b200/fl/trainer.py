@@ -121,6 +121,7 @@ class SlabTrainer(ModelTrainer):
         st = self._stagers.get(batch_size)
         if st is None:
             st = make_stager(self.staging, self.store, self.device, batch_size)
+            st.fixed_output = bool(getattr(self.engine, "use_graphs", False))
             self._stagers[batch_size] = st
         return st
 

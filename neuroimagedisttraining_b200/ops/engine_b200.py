@@ -69,6 +69,14 @@ def _declare(lib) -> None:
     lib.nidt_plan_train_step.restype = i32
     lib.nidt_plan_eval.argtypes = [vp, vp, vp, i32, vp, vp, i32, vp, vp]
     lib.nidt_plan_eval.restype = i32
+    lib.nidt_plan_train_step_graph.argtypes = [vp, vp, vp, i32, vp, vp, vp, vp, i64, f32, f32, f32, f32, i32, u64, i32, vp, vp, vp, vp]
+    lib.nidt_plan_train_step_graph.restype = i32
+    lib.nidt_plan_eval_graph.argtypes = [vp, vp, vp, i32, vp, vp, i32, vp, vp, vp]
+    lib.nidt_plan_eval_graph.restype = i32
+    lib.nidt_plan_graph_clear.argtypes = [vp]
+    lib.nidt_plan_graph_clear.restype = i32
+    lib.nidt_plan_graph_count.argtypes = []
+    lib.nidt_plan_graph_count.restype = i32
     for name, argtypes in {
         "nidt_ew_bf16": [vp, vp, vp, i64, i32, vp],
         "nidt_maxpool3d_fwd": [vp, vp, vp] + [i32] * 8 + [vp],
@@ -180,6 +188,16 @@ class B200Engine:
         self.native_exec = os.environ.get("NIDT_PY_EXEC", "0") != "1"
         self._plan = self._build_plan()
         self._launches = C.c_int(0)
+        # CUDA-graph replays of the native step (csrc/executor.cu): one graph per (slab, batch buffers); NIDT_GRAPHS=0 turns it off.
+        # Needs stable batch buffers, so trainers make their stagers gather every batch into one buffer (``use_graphs``).
+        self.use_graphs = self.native_exec and os.environ.get("NIDT_GRAPHS", "1") != "0"
+        self._dyn = torch.zeros(64, dtype=torch.uint8, device=self.device)      # nidt_dyn_t (48 bytes)
+
+    def __del__(self):
+        try:
+            self.lib.nidt_plan_graph_clear(C.byref(self._plan))
+        except Exception:
+            pass
 
     # ----------------------------------------------------------------------------- buffers
     def _alloc(self, wgrad_ctas: int) -> None:
@@ -453,6 +471,16 @@ class B200Engine:
         x = self._check_x(x)
         self._x = x
         n = self.layout.param_numel
+        if self.use_graphs:
+            native.check(self.lib.nidt_plan_train_step_graph(
+                C.byref(self._plan), x.data_ptr(), y.data_ptr(), int(x.shape[0]), self.slab.flat.data_ptr(), self.grad.flat.data_ptr(),
+                native.ptr(mom) if (do_update and hp.momentum != 0) else None, native.ptr(mask) if do_update else None, n,
+                float(hp.lr) if do_update else 0.0, float(hp.momentum) if do_update else 0.0, float(hp.wd) if do_update else 0.0,
+                float(hp.clip_norm) if do_update else 0.0, int(first_step), self.seed + 7919 * self.step, int(do_update),
+                self.loss_acc.data_ptr(), self._dyn.data_ptr(), C.byref(self._launches), self._stream()), "nidt_plan_train_step_graph")
+            native.count_launches(self._launches.value)
+            self.step += 1
+            return
         native.check(self.lib.nidt_plan_train_step(
             C.byref(self._plan), x.data_ptr(), y.data_ptr(), int(x.shape[0]), self.slab.flat.data_ptr(), self.grad.flat.data_ptr(),
             native.ptr(mom) if (do_update and hp.momentum != 0) else None, native.ptr(mask) if do_update else None, n,
@@ -488,6 +516,12 @@ class B200Engine:
         y = y.to(self.device, torch.float32).contiguous()
         if self._native_ready():
             x = self._check_x(x)
+            if self.use_graphs and counters is not None:
+                native.check(self.lib.nidt_plan_eval_graph(C.byref(self._plan), x.data_ptr(), y.data_ptr(), int(x.shape[0]), self.slab.flat.data_ptr(),
+                                                           counters.buf.data_ptr(), int(double_sigmoid), self._dyn.data_ptr(),
+                                                           C.byref(self._launches), self._stream()), "nidt_plan_eval_graph")
+                native.count_launches(self._launches.value)
+                return
             native.check(self.lib.nidt_plan_eval(C.byref(self._plan), x.data_ptr(), y.data_ptr(), int(x.shape[0]), self.slab.flat.data_ptr(),
                                                  counters.buf.data_ptr() if counters is not None else None, int(double_sigmoid),
                                                  C.byref(self._launches), self._stream()), "nidt_plan_eval")

@@ -78,6 +78,7 @@ class BatchStager:
         self.h2d_bytes = 0
         self.h2d_copies = 0
         self.gather_launches = 0
+        self.fixed_output = False         # True: every batch is gathered into ONE buffer (stable addresses for CUDA-graph replays)
         self._row_bytes = int(np.prod(store.shape))
         self.max_cache_rows = max(1, max_cache_bytes // self._row_bytes)
         self._pool_depth = {"train": train_slots, "eval": eval_slots}
@@ -330,10 +331,10 @@ class BatchStager:
         pos = self._positions(ent, loader, ids)
         n = len(pos)
         slot = ent.slot
-        if n > 0 and int(pos[-1]) - int(pos[0]) == n - 1 and (n == 1 or bool(np.all(np.diff(pos) == 1))):
+        if not self.fixed_output and n > 0 and int(pos[-1]) - int(pos[0]) == n - 1 and (n == 1 or bool(np.all(np.diff(pos) == 1))):
             p0 = int(pos[0])
             return slot.x[p0:p0 + n], slot.y[p0:p0 + n]
-        k = self._gk = (self._gk + 1) % len(self._gx)
+        k = self._gk = 0 if self.fixed_output else (self._gk + 1) % len(self._gx)
         if n > self._gx[k].shape[0]:
             self._gx = [torch.empty((n,) + tuple(self.store.shape), dtype=torch.uint8, device=self.device) for _ in self._gx]
             self._gy = [torch.empty(n, dtype=torch.float32, device=self.device) for _ in self._gy]
