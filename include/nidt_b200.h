@@ -133,8 +133,8 @@ int nidt_conv3d_wgrad_tc(const void* dy, const void* x, float* grad, float* scra
                          int splits, void* stream);
 /* Same result as nidt_conv3d_wgrad_tc without a caller-provided scratch buffer: the split-K partials go to a 16 MiB
  * array built into the library (held by every GPU that loads it, until exit).  For callers that cannot allocate device
- * memory where the call happens (custom-call bodies inside another framework's executor, code inside a stream capture,
- * fixed-memory deployments).  Refuses problems needing more than nidt_conv3d_wgrad_static_capacity_floats() floats
+ * memory where the call happens (custom-call bodies inside another framework's executor, which owns the allocator;
+ * deployments whose memory is partitioned once at start-up).  Refuses problems needing more than nidt_conv3d_wgrad_static_capacity_floats() floats
  * (splits*k^3*Cout*Cin).  The first call on a device looks the array's address up: make it at start-up, before any
  * stream capture.  Calls share the array: do not let two of them overlap on the GPU.
  * This entry point has no counterpart in the reference. */

@@ -610,13 +610,13 @@ NIDT_API int nidt_pack_conv_weights(const float* w, int Cout, int Cin, int taps,
 //
 // It is meant for callers that hold device pointers but have no way to obtain more device memory at
 // the point of the call: a custom-call body inside another framework's executor (which owns the
-// allocator and hands the callee only its operands), code running between cudaStreamBeginCapture and
-// cudaStreamEndCapture (allocation is not a capturable operation), and deployments whose memory is
-// carved up once at start-up and where a late cudaMalloc is forbidden or may fail.  Such a caller passes
-// only the inputs (dy, x) and the output (grad).
+// allocator and hands the callee only its operands), and deployments whose memory is carved up once at
+// start-up and where a late cudaMalloc is forbidden or may fail.  Such a caller passes only the inputs
+// (dy, x) and the output (grad).
 //
-// Cost and limits: kWgradStaticFloats floats (16 MiB) of global memory are reserved on every GPU that
-// loads libnidt_b200.so, from load until the process exits, whether or not this entry point is used.
+// Cost and limits: kWgradStaticFloats floats (16 MiB) of global memory are held on every GPU on which the
+// library's device code gets loaded (with CUDA's lazy module loading: from the first use of the library
+// on that GPU, at the latest the cudaGetSymbolAddress below) until the process exits.
 // A problem needs splits*k^3*Cout*Cin floats; anything larger is refused (return code 2, message via
 // nidt_last_error()) -- use nidt_conv3d_wgrad_tc with your own buffer for those.
 //

@@ -26,6 +26,7 @@ from .trainer import SlabTrainer
 class FedAPIBase:
     NAME = "fed"
     PERSONAL_IN_CHECKPOINT = False     # algorithms whose result IS the per-client models set this
+    BALANCE_EVAL = False               # spread the round's evaluation jobs over ranks by load (FedAvg family)
 
     def __init__(self, dataset, device, args, model_trainer: SlabTrainer, logger, dist: Optional[DistContext] = None,
                  agg_mode: str = "auto"):
@@ -47,7 +48,12 @@ class FedAPIBase:
         self.class_counts = class_counts
         self.model_trainer = model_trainer
         self.layout = model_trainer.layout
+        if getattr(args, "placement", "lpt") == "lpt" and self.dist.is_distributed and hasattr(self.dist, "place_clients"):
+            self.dist.place_clients([train_data_local_num_dict[c] for c in range(args.client_num_in_total)])
         self.client_list: List[Client] = []
+        self._trained: set = set()               # clients that hold a personal model on their owner (the same on every rank)
+        self._train_load: List[float] = [0.0] * self.dist.world_size
+        self._eval_tmp: List[ParamSlab] = []
         self._setup_clients(train_data_local_num_dict, train_data_local_dict, test_data_local_dict, model_trainer)
         self.init_stat_info()
         self.w_global: ParamSlab = model_trainer.engine.new_slab()
@@ -138,11 +144,73 @@ class FedAPIBase:
         results = self.model_trainer.test_many([(slabs[cid], self.client_list[cid].local_test_data) for cid in client_ids])
         return self._metrics_arrays(client_ids, results)
 
+    def _eval_ids(self) -> List[int]:
+        return [0] if getattr(self.args, "ci", 0) == 1 else list(range(self.args.client_num_in_total))
+
+    def _eval_plan(self, ids: Optional[Sequence[int]] = None) -> List[List[Tuple[int, str]]]:
+        """Per rank, the ``(client, 'g' | 'p')`` evaluation jobs of a full evaluation (:mod:`..parallel.placement`)."""
+        from ..parallel.placement import plan_eval_jobs
+        ids = list(ids) if ids is not None else self._eval_ids()
+        W = self.dist.world_size
+        balance = bool(self.BALANCE_EVAL and self.dist.is_distributed and getattr(self.args, "balance_eval", True))
+        return plan_eval_jobs(ids, {c: self.dist.owner(c) for c in ids}, {c: self.client_list[c].local_test_data.num_samples
+                                                                          if hasattr(self.client_list[c].local_test_data, "num_samples")
+                                                                          else len(self.client_list[c].local_test_data) for c in ids},
+                              sorted(self._trained), self._train_load if balance else [0.0] * W, W, balance)
+
     def eval_loaders(self, ids: Optional[Sequence[int]] = None) -> list:
-        """Test loaders of the locally evaluated clients, in evaluation order (what :meth:`_test_on_all_clients` stages as one group)."""
-        if ids is None:
-            ids = [0] if getattr(self.args, "ci", 0) == 1 else list(range(self.args.client_num_in_total))
-        return [self.client_list[c].local_test_data for c in self.local_clients(ids)]
+        """Test loaders this rank's evaluation jobs draw from, in job order without repeats (what :meth:`_test_on_all_clients`
+        stages as one group)."""
+        mine = self._eval_plan(ids)[self.dist.rank]
+        seen, out = set(), []
+        for c, _ in mine:
+            if c not in seen:
+                seen.add(c)
+                out.append(self.client_list[c].local_test_data)
+        return out
+
+    def _note_training(self, client_indexes: Sequence[int]) -> None:
+        """Bookkeeping every rank does alike at the start of a round: who will hold a personal model after it, and how much
+        training each rank is about to do (the base load the evaluation jobs are balanced on top of)."""
+        from ..parallel.placement import train_cost
+        self._trained.update(int(c) for c in client_indexes)
+        load = [0.0] * self.dist.world_size
+        for c in client_indexes:
+            load[self.dist.owner(int(c))] += train_cost(self.client_list[int(c)].get_sample_number(), getattr(self.args, "epochs", 1))
+        self._train_load = load
+
+    def _sync_trained(self) -> None:
+        """Rebuild the every-rank-alike set of clients that hold a personal model from what the owners actually hold (after a resume)."""
+        n = self.args.client_num_in_total
+        t = torch.zeros(n, dtype=torch.float32, device=self.device)
+        for c in self.client_list:
+            if c.slab is not None and self.dist.owns(c.client_idx):
+                t[c.client_idx] = 1
+        self.dist.all_reduce_sum(t)
+        self._trained = set(int(i) for i in torch.nonzero(t > 0).flatten().tolist())
+
+    def _fetch_personal(self, plan, w_per_mdls: Dict[int, ParamSlab]) -> Dict[int, ParamSlab]:
+        """Personal models this rank evaluates for other owners: point-to-point copies owner -> evaluator (all ranks take part;
+        the plan is the same everywhere).  Returns client -> received slab."""
+        import torch.distributed as dist
+        ops_, got = [], {}
+        k = 0
+        for r, jobs in enumerate(plan):
+            for c, kind in jobs:
+                if kind != "p" or c not in self._trained or self.dist.owner(c) == r:
+                    continue
+                if self.dist.rank == self.dist.owner(c):
+                    ops_.append(dist.P2POp(dist.isend, w_per_mdls[c].flat, r))
+                elif self.dist.rank == r:
+                    while len(self._eval_tmp) <= k:
+                        self._eval_tmp.append(self.model_trainer.engine.new_slab())
+                    got[c] = self._eval_tmp[k]
+                    k += 1
+                    ops_.append(dist.P2POp(dist.irecv, got[c].flat, self.dist.owner(c)))
+        if ops_:
+            for req in dist.batch_isend_irecv(ops_):
+                req.wait()
+        return got
 
     def _reduce_metric(self, *arrays: np.ndarray) -> List[np.ndarray]:
         if not self.dist.is_distributed:
@@ -157,19 +225,28 @@ class FedAPIBase:
         client-uniform means (``sailentgrads_api.py:231-285``).  ``--ci 1`` evaluates only the first
         client (and, unlike the reference, averages over what was evaluated)."""
         self.logger.info("################global_test_on_all_clients : {}".format(round_idx))
-        n_total = self.args.client_num_in_total
-        ids = [0] if getattr(self.args, "ci", 0) == 1 else list(range(n_total))
-        mine = self.local_clients(ids)
+        ids = self._eval_ids()
         with self.timer.phase("eval"):
-            # every test split is staged once and evaluated by both models (the reference stages it once per model)
-            loaders = [self.client_list[c].local_test_data for c in mine]
-            sets = [[w_global] * len(mine)]
+            # every test split is staged once per rank however many models it is evaluated with (the reference stages it once per
+            # model); the jobs of all clients are spread over the ranks by load when BALANCE_EVAL
+            plan = self._eval_plan(ids)
+            mine = plan[self.dist.rank]
+            if w_per_mdls is None:
+                mine = [j for j in mine if j[1] == "g"]
+            foreign = self._fetch_personal(plan, w_per_mdls) if (w_per_mdls is not None and self.dist.is_distributed) else {}
+
+            def model_of(c, kind):
+                if kind == "g":
+                    return w_global
+                return foreign.get(c) or w_per_mdls.get(c) or self.w_init or w_global
+            res = self.model_trainer.test_jobs([(self.client_list[c].local_test_data, model_of(c, kind)) for c, kind in mine],
+                                               group=self.eval_loaders(ids) if w_per_mdls is not None else None)
+            g_acc, g_loss = self._metrics_arrays([c for c, k in mine if k == "g"], [m for (c, k), m in zip(mine, res) if k == "g"])
             if w_per_mdls is not None:
-                sets.append([(w_per_mdls.get(c) or self.w_init or w_global) for c in mine])
-            res = self.model_trainer.test_multi(loaders, sets)
-            g_acc, g_loss = self._metrics_arrays(mine, res[0])
-            p_acc, p_loss = self._metrics_arrays(mine, res[1]) if w_per_mdls is not None else (g_acc.copy(), g_loss.copy())
-            g_acc, g_loss, p_acc, p_loss = self._reduce_metric(g_acc, g_loss, p_acc, p_loss)
+                p_acc, p_loss = self._metrics_arrays([c for c, k in mine if k == "p"], [m for (c, k), m in zip(mine, res) if k == "p"])
+            g_acc, g_loss, p_acc, p_loss = self._reduce_metric(g_acc, g_loss, *((p_acc, p_loss) if w_per_mdls is not None else (g_acc * 0, g_loss * 0)))
+            if w_per_mdls is None:
+                p_acc, p_loss = g_acc.copy(), g_loss.copy()
         denom = len(ids)
         stats = {'global_test_acc': g_acc.sum() / denom, 'global_test_loss': g_loss.sum() / denom}
         self.stat_info["global_test_acc"].append(stats['global_test_acc'])
@@ -199,6 +276,7 @@ class FedAPIBase:
             self.dist.all_reduce_sum(t)
             self.stat_info["sum_comm_params"] += int(t.item())
             self._comm_params_dev = None
+        self._sync_flops()
         self.stat_info["phase_time_s"] = self.timer.summary()
         return self.stat_info
 
@@ -263,15 +341,47 @@ class FedAPIBase:
         dist.all_gather_object(parts, mine)
         return {k: v for part in parts for k, v in part.items()}
 
+    def _gather_personal_state(self) -> Dict[int, dict]:
+        """Every client's personal model as a CPU state_dict on rank 0, fetched from the rank that owns (= trained) it; all ranks
+        take part.  Rank 0's own view is not enough: the clients of other ranks exist there only as untrained clones."""
+        self._sync_trained()
+        out: Dict[int, dict] = {}
+        tmp = None
+        for c in sorted(self._trained):
+            slab = self.client_list[c].slab
+            if self.dist.is_distributed:
+                owner = self.dist.owner(c)
+                if self.dist.rank != owner:
+                    if tmp is None:
+                        tmp = self.model_trainer.engine.new_slab()
+                    slab = tmp
+                self.dist.broadcast(slab.flat, src=owner)
+            if self.dist.is_main:
+                out[c] = {k: v.detach().cpu().clone() for k, v in slab.state_dict().items()}
+        return out
+
+    def _sync_flops(self) -> None:
+        """``sum_training_flops`` is accumulated per rank; fold the ranks' shares since the last sync into one global value."""
+        if not self.dist.is_distributed:
+            return
+        base = getattr(self, "_flops_base", 0)
+        t = torch.tensor([float(self.stat_info["sum_training_flops"] - base)], dtype=torch.float64, device=self.device)
+        self.dist.all_reduce_sum(t)
+        delta = t.item()
+        self.stat_info["sum_training_flops"] = base + (int(round(delta)) if float(delta).is_integer() else delta)
+        self._flops_base = self.stat_info["sum_training_flops"]
+
     def save(self, path: str, round_idx: int) -> None:
         loaders = self._loader_states()
+        keep_personal = self.PERSONAL_IN_CHECKPOINT or getattr(self.args, "save_personal", False)
+        personal = self._gather_personal_state() if keep_personal else None
+        self._sync_flops()
         if self.dist.is_main:
-            keep_personal = self.PERSONAL_IN_CHECKPOINT or getattr(self.args, "save_personal", False)
             extra = dict(self.extra_state())
             if self.w_init is not None:
                 extra["w_init"] = {k: v.cpu() for k, v in self.w_init.state_dict().items()}
             save_checkpoint(path, round_idx, self.w_global, self.mask, self.args, self.stat_info,
-                            personal=self.personal_slabs() if keep_personal else None, loaders=loaders, extra=extra)
+                            personal=personal, loaders=loaders, extra=extra)
 
     def extra_state(self) -> dict:
         """Algorithm-specific state a resumed run needs beyond the global model, the mask and the personal models (CPU tensors /
@@ -295,6 +405,7 @@ class FedAPIBase:
             self.mask = self.model_trainer.mask_slab(ck["mask"])
         for k, v in ck.get("stat_info", {}).items():
             self.stat_info[k] = v
+        self._flops_base = self.stat_info.get("sum_training_flops", 0)
         for cid, sd in (ck.get("personal") or {}).items():
             c = self.client_list[int(cid)]
             c.ensure_slab(self.w_global).load_state_dict(sd)
@@ -303,6 +414,7 @@ class FedAPIBase:
             self.w_init = self.model_trainer.engine.new_slab()
             self.w_init.load_state_dict(extra.pop("w_init"))
         self.load_extra_state(extra)
+        self._sync_trained()
         self.start_round = int(ck["round"]) + 1
         self.logger.info("resumed from %s at round %d" % (path, self.start_round))
         return self.start_round

@@ -10,6 +10,7 @@ from .base import FedAPIBase
 
 class FedAvgAPI(FedAPIBase):
     NAME = "fedavg"
+    BALANCE_EVAL = True
 
     def run_round(self, round_idx: int, mask=None, evaluate: bool = True):
         """sample -> local training of the owned sampled clients -> weighted aggregation -> eval."""
@@ -21,6 +22,7 @@ class FedAvgAPI(FedAPIBase):
         w_locals = []
         will_eval = evaluate and round_idx % max(1, int(getattr(args, "frequency_of_the_test", 1))) == 0
         tr = self.model_trainer
+        self._note_training(client_indexes)
         with self.timer.phase("train"):
             mine = list(self.local_clients(client_indexes))
             # the whole round's data plan is known up front: this round's clients in order, then every test split (one group, staged
@@ -82,6 +84,7 @@ class FedAvgAPI(FedAPIBase):
         """Final round: *every* client trains once from the global model with ``round=-1``
         (lr * decay^-1) and the personalised accuracy is re-evaluated (``fedavg_api.py:79-88``)."""
         self.logger.info("################ final fine-tune round")
+        self._note_training(range(self.args.client_num_in_total))
         with self.timer.phase("train"):
             for cid in self.local_clients(range(self.args.client_num_in_total)):
                 self.client_list[cid].train(self.w_global, -1, None)

@@ -206,26 +206,35 @@ class SlabTrainer(ModelTrainer):
         ``p`` for ``loaders[j]`` (pass 0 = the global model on every client, pass 1 = the personalised models; the reference stages
         each client's test split once per pass, ``sailentgrads_api.py:247-256``).  Returns ``results[p][j]`` metric dicts."""
         loaders = list(loaders)
-        if not loaders:
-            return [[] for _ in slab_sets]
+        flat = self.test_jobs([(loaders[j], slabs[j]) for slabs in slab_sets for j in range(len(loaders))])
+        n = len(loaders)
+        return [flat[p * n:(p + 1) * n] for p in range(len(slab_sets))]
+
+    def test_jobs(self, jobs, group=None):
+        """Evaluate ``[(loader, slab), ...]`` in order; every distinct loader's volumes are uploaded once (one slot for the whole
+        group) however many jobs use it.  ``group``: the loader list announced with ``plan_data(..., group=True)`` (defaults to the
+        distinct loaders of ``jobs`` in order).  One device->host read returns all counters.  Returns one metrics dict per job."""
+        jobs = list(jobs)
+        if not jobs:
+            return []
+        loaders = list(group) if group is not None else list(dict((id(l), l) for l, _ in jobs).values())
         if not all(self._cached(l) for l in loaders):
-            return [self.test_many(list(zip(slabs, loaders))) for slabs in slab_sets]
+            return self.test_many([(slab, loader) for loader, slab in jobs])
         bs = max(l.batch_size for l in loaders)
         st = self._stager(bs)
         ent = st.open(loaders, kind="eval")
-        acc = torch.zeros((len(slab_sets), len(loaders), 3), dtype=torch.float64, device=self.device)
+        acc = torch.zeros((len(jobs), 3), dtype=torch.float64, device=self.device)
         try:
-            for p, slabs in enumerate(slab_sets):
-                counters = [EvalCounters(self.device, acc[p, j]) for j in range(len(loaders))]
-                for j, loader in enumerate(loaders):
-                    self.attach(slabs[j])
-                    for b in loader:
-                        x, y = st.batch_from(ent, loader, b[0])
-                        self.engine.eval_batch(x, y, counters[j], double_sigmoid=self.double_sigmoid_eval)
+            for j, (loader, slab) in enumerate(jobs):
+                self.attach(slab)
+                c = EvalCounters(self.device, acc[j])
+                for b in loader:
+                    x, y = st.batch_from(ent, loader, b[0])
+                    self.engine.eval_batch(x, y, c, double_sigmoid=self.double_sigmoid_eval)
         finally:
             st.close(ent)
-        host = xfer.to_host(acc).tolist()                      # ONE device->host read for all (pass, client) counters
-        return [[EvalCounters.as_result(*host[p][j]) for j in range(len(loaders))] for p in range(len(slab_sets))]
+        host = xfer.to_host(acc).tolist()                      # ONE device->host read for all jobs' counters
+        return [EvalCounters.as_result(*row) for row in host]
 
     def test_many(self, jobs):
         """Evaluate ``[(slab, loader), ...]`` back to back as one staged stream (the copy of the next client's test

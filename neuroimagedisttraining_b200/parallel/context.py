@@ -19,6 +19,7 @@ class DistContext:
     device: torch.device = torch.device("cpu")
     backend: Optional[str] = None
     group: Optional[object] = None
+    placement: Optional[list] = None      # client -> rank, set by place_clients(); None = round-robin
 
     @property
     def is_distributed(self) -> bool:
@@ -50,8 +51,17 @@ class DistContext:
             dist.broadcast(t, src=src)
         return t
 
+    def place_clients(self, sample_counts) -> None:
+        """Static client -> rank placement by longest-processing-time over the clients' training-set sizes (real ABCD sites are
+        uneven); equal sizes give round-robin.  The same on every rank: it only depends on the data partition."""
+        from .placement import lpt_assign
+        self.placement = lpt_assign(list(sample_counts), self.world_size) if self.world_size > 1 else None
+
     def owner(self, client_idx: int) -> int:
-        """Static client -> rank placement (round-robin keeps sorted sampled subsets balanced)."""
+        """Static client -> rank placement (a client's personal model lives on its owner): LPT by size after
+        :meth:`place_clients`, else round-robin (which keeps sorted sampled subsets balanced)."""
+        if self.placement is not None and int(client_idx) < len(self.placement):
+            return self.placement[int(client_idx)]
         return int(client_idx) % self.world_size
 
     def owns(self, client_idx: int) -> bool:

@@ -65,11 +65,16 @@ class SynchronizedBatchNorm(nn.modules.batchnorm._BatchNorm):
     def forward(self, x):
         if not self.training:
             return nn.functional.batch_norm(x, self.running_mean, self.running_var, self.weight, self.bias, False, 0.0, self.eps)
-        y, mean, var_unbiased = _SyncBNFn.apply(x, self.weight, self.bias, self.eps, self.process_group)
+        C = x.shape[1]
+        weight = self.weight if self.affine else torch.ones(C, dtype=x.dtype, device=x.device)
+        bias = self.bias if self.affine else torch.zeros(C, dtype=x.dtype, device=x.device)
+        y, mean, var_unbiased = _SyncBNFn.apply(x, weight, bias, self.eps, self.process_group)
         with torch.no_grad():
             self.num_batches_tracked += 1
-            self.running_mean.mul_(1 - self.momentum).add_(self.momentum * mean)
-            self.running_var.mul_(1 - self.momentum).add_(self.momentum * var_unbiased)
+            # momentum=None: cumulative moving average, as in torch.nn.BatchNorm
+            m = self.momentum if self.momentum is not None else 1.0 / float(self.num_batches_tracked)
+            self.running_mean.mul_(1 - m).add_(m * mean)
+            self.running_var.mul_(1 - m).add_(m * var_unbiased)
         return y
 
 

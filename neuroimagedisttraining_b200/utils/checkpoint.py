@@ -24,7 +24,8 @@ def save_checkpoint(path: str, round_idx: int, w_global, mask, args, stat_info, 
         "stat_info": {k: v for k, v in stat_info.items() if k != "phase_time_s"},
         "loaders": ({int(c): st.cpu().clone() for c, st in loaders.items()} if loaders else None),
         "extra": extra or None,
-        "personal": ({int(c): {k: v.cpu() for k, v in s.state_dict().items()} for c, s in personal.items()} if personal else None),
+        "personal": ({int(c): {k: v.cpu() for k, v in (s if isinstance(s, dict) else s.state_dict()).items()} for c, s in personal.items()}
+                     if personal else None),
     }
     tmp = path + ".tmp"
     torch.save(ck, tmp)

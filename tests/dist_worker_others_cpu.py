@@ -15,11 +15,11 @@ from neuroimagedisttraining_b200.models import create_model
 from neuroimagedisttraining_b200.parallel import DistContext, init_distributed, shutdown
 
 
-def run(ctx, API):
+def run(ctx, API, rounds=2, ck=None, resume=None):
     torch.manual_seed(0); np.random.seed(0)
     logger = logging.getLogger("w"); logger.setLevel(logging.ERROR)
     n = 5
-    args = types.SimpleNamespace(client_num_in_total=n, client_num_per_round=3, comm_round=2, epochs=1, lr=0.05, lr_decay=0.998, momentum=0.0,
+    args = types.SimpleNamespace(client_num_in_total=n, client_num_per_round=3, comm_round=rounds, epochs=1, lr=0.05, lr_decay=0.998, momentum=0.0,
                                  wd=5e-4, client_optimizer="sgd", batch_size=16, ci=0, frequency_of_the_test=1, dataset="cifar10", lamda=0.5,
                                  local_epochs=1, final_finetune=False, ta_group_size=2, ta_scale=1 << 16, each_prune_ratio=0.2, dense_ratio=0.3,
                                  dist_thresh=1e-4, acc_thresh=-1.0)
@@ -27,8 +27,34 @@ def run(ctx, API):
     model = create_model("lenet5_cifar", 10)
     api = API(ds, "cpu", args, SlabTrainer(model, args, logger, device="cpu", loss_kind="ce"), logger, dist=ctx)
     api.record_information = lambda *a, **k: None
+    if ck is not None:
+        args.checkpoint_every, args.checkpoint_path = 1, ck
+    if resume is not None:
+        api.resume(resume)
     st = api.train()
     return api, st
+
+
+def resume_check(ctx):
+    """Local-only training over 2 ranks, killed after round 1 and resumed from the checkpoint, against the uninterrupted 3-round run:
+    the checkpoint must hold EVERY client's personal model (fetched from its owner), not rank 0's untrained clones of them."""
+    import tempfile
+    ck = os.path.join(tempfile.gettempdir(), f"nidt_ck_local_{os.environ.get('MASTER_PORT', '0')}.pt")
+    full, sf = run(ctx, LocalAPI, rounds=3)
+    run(ctx, LocalAPI, rounds=2, ck=ck)
+    torch.distributed.barrier()
+    saved = torch.load(ck, weights_only=False)
+    good = sorted(saved["personal"]) == list(range(5)) and saved["round"] == 1
+    res, sr = run(ctx, LocalAPI, rounds=3, resume=ck)
+    for c in range(5):
+        if ctx.owns(c):
+            good = good and torch.allclose(res.client_list[c].slab.flat, full.client_list[c].slab.flat, rtol=1e-5, atol=1e-6)
+    good = good and abs(sr["person_test_acc"][-1] - sf["person_test_acc"][-1]) < 1e-9 and sr["sum_training_flops"] == sf["sum_training_flops"]
+    torch.distributed.barrier()
+    if ctx.rank == 0:
+        os.remove(ck)
+        print(f"LocalAPI save/resume over {ctx.world_size} ranks: match={good}", flush=True)
+    return good
 
 
 def main():
@@ -50,6 +76,7 @@ def main():
         if ctx.rank == 0:
             print(f"{API.__name__}: world={ctx.world_size} match={good}", flush=True)
         ok = ok and good
+    ok = resume_check(ctx) and ok
     t = torch.tensor([1.0 if ok else 0.0])
     torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MIN)
     if ctx.rank == 0:

@@ -71,6 +71,30 @@ def main():
             ok = False
         if ctx.rank == 0:
             print(f"saliency multimem={mm}: mask diff={nd} kept={fi['kept']} (ref {ri['kept']}) thr={fi['threshold']:.6e}")
+    # a rank that reaches the aggregation long after its peers (uneven client counts, a rank without a sampled client): the launch
+    # is preceded by a stream-ordered line-up of the ranks, so the late rank costs time, not a device-side time-out.  12 s is above
+    # the 10 s the kernel's own barrier used to allow.
+    if ctx.world_size <= 2 or os.environ.get("NIDT_TEST_SLEEP") == "1":
+        import time
+        agg.use_multimem = None
+        part = torch.randn(n, generator=torch.Generator().manual_seed(900 + ctx.rank)).to(dev)
+        agg.local_partial.copy_(part)
+        torch.cuda.synchronize()
+        if ctx.rank == ctx.world_size - 1:
+            time.sleep(12.0)
+        out = torch.empty(n, device=dev)
+        agg.reduce_mask_broadcast(out, mask)
+        parts = [torch.empty_like(part) for _ in range(ctx.world_size)]
+        dist.all_gather(parts, part)
+        ref = parts[0].clone()
+        for q in parts[1:]:
+            ref += q
+        ref[:nm] *= mask
+        torch.cuda.synchronize()
+        late_ok = (out - ref).abs().max().item() <= 2e-5
+        ok = ok and late_ok
+        if ctx.rank == 0:
+            print(f"late rank (12 s): result ok={late_ok}")
     part = torch.randn(n, device=dev)
     out = torch.empty(n, device=dev)
     agg.use_multimem = False

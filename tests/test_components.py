@@ -392,3 +392,23 @@ def test_roofline_script_on_the_committed_step_profile():
     assert [r["M"] for r in L] == [16 * 247151, 16 * 6069, 16 * 175, 16 * 175, 16 * 175] and [r["K"] for r in L] == [125, 1728, 3456, 5184, 5184]
     text = mod.main([os.path.join(root, "profiles", "profile_step_v18.txt")])
     assert "| `conv3d_fprop_tc[1]` |" in text and "| math |" in text and "| memory |" in text
+
+
+def test_syncbn_single_process_matches_batchnorm_with_cma_momentum_and_without_affine():
+    """momentum=None (cumulative moving average) and affine=False go through convert_sync_batchnorm unchanged and must behave like
+    torch.nn.BatchNorm3d (one process: the cross-rank reduction is the identity)."""
+    import copy
+    from neuroimagedisttraining_b200.parallel.syncbn import convert_sync_batchnorm
+    torch.manual_seed(0)
+    for kw in (dict(momentum=None), dict(affine=False), dict(momentum=None, affine=False), dict()):
+        ref = torch.nn.BatchNorm3d(5, **kw)
+        mod = convert_sync_batchnorm(copy.deepcopy(ref))
+        for _ in range(3):
+            x = torch.randn(4, 5, 3, 3, 3, requires_grad=True)
+            x2 = x.detach().clone().requires_grad_(True)
+            y, y2 = ref(x), mod(x2)
+            y.square().sum().backward(); y2.square().sum().backward()
+            torch.testing.assert_close(y2, y, rtol=1e-5, atol=1e-6)
+            torch.testing.assert_close(x2.grad, x.grad, rtol=1e-4, atol=1e-5)
+        torch.testing.assert_close(mod.running_mean, ref.running_mean, rtol=1e-5, atol=1e-6)
+        torch.testing.assert_close(mod.running_var, ref.running_var, rtol=1e-5, atol=1e-6)
