@@ -55,6 +55,12 @@ def add_common_args(p: argparse.ArgumentParser, *, model="3DCNN", dataset="ABCD"
     g = p.add_argument_group("b200")
     g.add_argument("--engine", default="auto", choices=["auto", "b200", "torch"], help="compute engine (auto: sm_100a kernels when the model has a plan)")
     g.add_argument("--agg", default="auto", choices=["auto", "fused", "nccl"], help="cross-rank aggregation: fused symmetric-memory kernel or NCCL baseline")
+    g.add_argument("--staging", default="auto", choices=["auto", "client", "stream", "resident"],
+                   help="how volumes reach the GPU: client = each loader's volumes uploaded once per use, batches gathered on the device "
+                        "(default on CUDA); stream = batch-by-batch copies; resident = whole store kept on the device")
+    g.add_argument("--placement", default="lpt", choices=["lpt", "roundrobin"], help="client -> rank placement: by training-set size or client_idx %% world")
+    g.add_argument("--balance_eval", type=int, default=0, help="1: spread the round's evaluation jobs over ranks by load (personal models are "
+                                                               "copied to the evaluating rank)")
     g.add_argument("--device", default=None, help="cpu | cuda (default: cuda if available)")
     g.add_argument("--resume", default=None, help="checkpoint to resume from")
     g.add_argument("--checkpoint_path", default=None)

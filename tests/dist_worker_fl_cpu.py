@@ -13,14 +13,14 @@ from neuroimagedisttraining_b200.models import create_model
 from neuroimagedisttraining_b200.parallel import DistContext, init_distributed, shutdown
 
 
-def run(ctx, ck=None, sizes=(10, 10, 10, 10), per_round=None):
+def run(ctx, ck=None, sizes=(10, 10, 10, 10), per_round=None, balance_eval=False):
     torch.manual_seed(0)
     logger = logging.getLogger("w"); logger.setLevel(logging.ERROR)
     n = len(sizes)
     store = SyntheticABCD(sum(sizes), (32, 32, 32), n_sites=n, seed=1, site_sizes=list(sizes))
     args = types.SimpleNamespace(client_num_in_total=n, client_num_per_round=per_round or n, comm_round=2, epochs=1, lr=0.01, lr_decay=0.998,
                                  momentum=0.9, wd=5e-4, client_optimizer="sgd", batch_size=8, dense_ratio=0.5, itersnip_iteration=2,
-                                 stratified_sampling=False, snip_mask=True, ci=0, frequency_of_the_test=1, dataset="ABCD")
+                                 stratified_sampling=False, snip_mask=True, ci=0, frequency_of_the_test=1, dataset="ABCD", balance_eval=balance_eval)
     ds = load_partition_data_abcd(store, client_number=n, batch_size=8)
     model = create_model("tiny3DCNN", 1, (32, 32, 32))
     tr = SlabTrainer(model, args, logger, device="cpu", store=store)
@@ -45,7 +45,7 @@ def main():
     ok = ok and st1["sum_comm_params"] == st2["sum_comm_params"]
     # uneven sites, 4 of 5 clients sampled per round: size-aware placement, evaluation jobs moved to the lighter rank (personal
     # models copied owner -> evaluator), a client that never trained evaluated with the shared fall-back model
-    w4, m4, st4 = run(ctx, None, sizes=(20, 10, 10, 10, 30), per_round=4)
+    w4, m4, st4 = run(ctx, None, sizes=(20, 10, 10, 10, 30), per_round=4, balance_eval=True)
     w3, m3, st3 = run(DistContext(device=torch.device("cpu")), None, sizes=(20, 10, 10, 10, 30), per_round=4)
     ok = ok and torch.equal(m3, m4) and torch.allclose(w3, w4, rtol=1e-5, atol=1e-6)
     for key in ("global_test_acc", "person_test_acc", "global_test_loss", "person_test_loss"):
