@@ -131,6 +131,11 @@ int64_t nidt_conv3d_wgrad_scratch_floats(int Cout, int Cin, int k, int splits);
 int nidt_conv3d_wgrad_tc(const void* dy, const void* x, float* grad, float* scratch, int N, int Di, int Hi, int Wi, int Cin,
                          int Do, int Ho, int Wo, int Cout, int k, int stride, int pad, int bw, int bh, int bd, int bn,
                          int splits, void* stream);
+/* nidt_conv3d_wgrad_tc with the SNIP saliency epilogue: the split-K reduction that writes dW also accumulates
+ * scores[co][ci][tap] += scale*|dW*w| (w = the layer's fp32 weights).  ref: snip.py:60-71. */
+int nidt_conv3d_wgrad_tc_saliency(const void* dy, const void* x, float* grad, float* scratch, int N, int Di, int Hi, int Wi, int Cin,
+                                  int Do, int Ho, int Wo, int Cout, int k, int stride, int pad, int bw, int bh, int bd, int bn,
+                                  int splits, const float* w, float* scores, float scale, void* stream);
 /* Same result as nidt_conv3d_wgrad_tc without a caller-provided scratch buffer: the split-K partials go to a 16 MiB
  * array built into the library (held by every GPU that loads it, until exit).  For callers that cannot allocate device
  * memory where the call happens (custom-call bodies inside another framework's executor, which owns the allocator;
@@ -174,6 +179,9 @@ int nidt_conv_in_s2d_fprop(const void* x, const float* w, const float* bias, voi
                            int Wi, float scale, void* stream);
 int nidt_conv_in_s2d_wgrad(const void* x, const void* dy, float* grad, float* grad_bias, float* scratch, int N, int Di, int Hi,
                            int Wi, float scale, void* stream);
+
+int nidt_conv_in_s2d_wgrad_saliency(const void* x, const void* dy, float* grad, float* grad_bias, float* scratch, int N, int Di, int Hi,
+                                    int Wi, float scale, const float* w, float* scores, float sal_scale, void* stream);
 
 /* ------------------------------------------------------- residual-network glue (resnet_ops.cu) */
 /* ref: ResNet_l3 / BasicBlock, fedml_api/model/cv/salient_models.py:13-139 (ATen / cuDNN / cuBLAS under autograd there). */
@@ -239,6 +247,12 @@ int nidt_plan_pack_weights(const nidt_plan_t* plan, const float* slab, void* str
 int nidt_plan_train_step(const nidt_plan_t* plan, const void* x_u8, const float* y, int batch, float* slab, float* grad, float* mom,
                          const float* mask, int64_t n_params, float lr, float momentum, float wd, float clip_norm, int first_step,
                          uint64_t seed, int do_update, int* launches, void* stream);
+/* One SNIP evaluation: forward (batch statistics, dropout on) + backward with the saliency epilogues -- the conv layers'
+ * scores += scale*|dW*w| leave their wgrad reductions directly, the classifier's by one flat pass over its slab segment.
+ * `scores` has the slab's parameter layout.  BN running statistics of `slab` ARE updated (callers that score a model without
+ * touching it save / restore that tail).  ref: snip.py:38-71. */
+int nidt_plan_saliency_step(const nidt_plan_t* plan, const void* x_u8, const float* y, int batch, float* slab, float* grad, float* scores,
+                            float scale, int64_t n_params, uint64_t seed, int* launches, void* stream);
 /* struct layout probes for bindings: sizeof, and offsetof for a few fields (see executor.cu for the field numbers) */
 int nidt_plan_sizeof(void);
 int nidt_block_sizeof(void);

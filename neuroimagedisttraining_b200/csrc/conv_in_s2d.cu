@@ -511,7 +511,8 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __res
 
 // dW[co][kd][kh][kw] = sum_cta partials[cta][jw][(jd*4+jh)*8 + c][co]   with kd = 2jd+pd, kh = 2jh+ph, kw = 2jw+pw, c = pd*4+ph*2+pw.
 // Threads run over the partial layout (co fastest) so the reads of every CTA's slab are coalesced; the 8000 results scatter.
-__global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ partials, int n_cta, float* __restrict__ grad, float* __restrict__ grad_bias) {
+__global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ partials, int n_cta, float* __restrict__ grad, float* __restrict__ grad_bias,
+                                                           const float* __restrict__ w, float* __restrict__ scores, float sal_scale) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < 64 && grad_bias != nullptr) grad_bias[i] = 0.f;   // BatchNorm follows this conv: the bias gradient is identically zero
     if (i >= 3 * 128 * 64) return;
@@ -522,7 +523,9 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restri
     if (jd > 2 || jh > 2 || kd > 4 || kh > 4 || kw > 4) return;
     float acc = 0.f;
     for (int q = 0; q < n_cta; ++q) acc += partials[(size_t)q * (3 * 128 * 64) + i];
-    grad[co * 125 + (kd * 5 + kh) * 5 + kw] = acc;
+    const int o = co * 125 + (kd * 5 + kh) * 5 + kw;
+    grad[o] = acc;
+    if (scores != nullptr) scores[o] += sal_scale * fabsf(acc * w[o]);      // SNIP |dL/dw * w| straight from the reduction
 }
 
 static int make_geom(Geom& g, int N, int Di, int Hi, int Wi, float scale) {
@@ -569,8 +572,20 @@ NIDT_API int nidt_conv_in_s2d_fprop(const void* x, const float* w, const float* 
 }
 
 // scratch: >= nidt_conv_in_s2d_wgrad_scratch_floats() floats
+static int s2d_wgrad_impl(const void* x, const void* dy, float* grad, float* grad_bias, float* scratch, int N, int Di, int Hi, int Wi,
+                          float scale, void* stream, const float* sal_w, float* sal_scores, float sal_scale);
 NIDT_API int nidt_conv_in_s2d_wgrad(const void* x, const void* dy, float* grad, float* grad_bias, float* scratch, int N, int Di, int Hi, int Wi,
                                     float scale, void* stream) {
+    return s2d_wgrad_impl(x, dy, grad, grad_bias, scratch, N, Di, Hi, Wi, scale, stream, nullptr, nullptr, 0.f);
+}
+// the same with the SNIP saliency epilogue in the split reduction: scores[co][125] += sal_scale * |dW * w|  (ref: snip.py:60-71)
+NIDT_API int nidt_conv_in_s2d_wgrad_saliency(const void* x, const void* dy, float* grad, float* grad_bias, float* scratch, int N, int Di, int Hi,
+                                             int Wi, float scale, const float* w, float* scores, float sal_scale, void* stream) {
+    NIDT_REQUIRE(w != nullptr && scores != nullptr, "conv_in_s2d_wgrad_saliency: w / scores is null");
+    return s2d_wgrad_impl(x, dy, grad, grad_bias, scratch, N, Di, Hi, Wi, scale, stream, w, scores, sal_scale);
+}
+static int s2d_wgrad_impl(const void* x, const void* dy, float* grad, float* grad_bias, float* scratch, int N, int Di, int Hi, int Wi,
+                          float scale, void* stream, const float* sal_w, float* sal_scores, float sal_scale) {
     s2d::Geom g;
     if (s2d::make_geom(g, N, Di, Hi, Wi, scale)) return 2;
     CUtensorMap tdy;
@@ -582,7 +597,7 @@ NIDT_API int nidt_conv_in_s2d_wgrad(const void* x, const void* dy, float* grad, 
     NIDT_CUDA_CHECK(cudaFuncSetAttribute(s2d::wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     s2d::wgrad_kernel<<<grid, s2d::kThreads, smem, s>>>((const uint8_t*)x, tdy, scratch, g);
     NIDT_LAUNCH_CHECK();
-    s2d::wgrad_reduce_kernel<<<(3 * 128 * 64 + 255) / 256, 256, 0, s>>>(scratch, grid, grad, grad_bias);
+    s2d::wgrad_reduce_kernel<<<(3 * 128 * 64 + 255) / 256, 256, 0, s>>>(scratch, grid, grad, grad_bias, sal_w, sal_scores, sal_scale);
     NIDT_LAUNCH_CHECK();
     return 0;
 }

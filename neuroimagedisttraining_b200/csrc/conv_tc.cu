@@ -428,7 +428,8 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv3d_wgrad_tc_kernel(
 // dW (PyTorch layout [co][ci][taps], fp32, in the gradient slab) = sum_splits partials[split][tap][co][ci];
 // optional saliency epilogue: scores[co][ci][tap] += scale * |dW * W|   (ref K11: snip.py:60-71)
 __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ partials, int splits, int taps, int Cout, int Cin,
-                                                           float* __restrict__ grad) {
+                                                           float* __restrict__ grad, const float* __restrict__ w, float* __restrict__ scores,
+                                                           float scale) {
     // threads follow the partial layout [tap][co][ci] (ci fastest): coalesced reads of every split, strided writes of the result
     const int64_t total = (int64_t)Cout * Cin * taps;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -438,7 +439,9 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restri
         const int t = (int)(r / Cout);
         float acc = 0.f;
         for (int s = 0; s < splits; ++s) acc += partials[(size_t)s * total + i];
-        grad[((size_t)co * Cin + ci) * taps + t] = acc;
+        const size_t o = ((size_t)co * Cin + ci) * taps + t;
+        grad[o] = acc;
+        if (scores != nullptr) scores[o] += scale * fabsf(acc * w[o]);
     }
 }
 
@@ -558,7 +561,8 @@ NIDT_API int nidt_conv3d_m_tiles(int N, int Do, int Ho, int Wo, int bw, int bh, 
 NIDT_API int64_t nidt_conv3d_wgrad_scratch_floats(int Cout, int Cin, int k, int splits) { return (int64_t)splits * k * k * k * Cout * Cin; }
 
 static int wgrad_impl(const void* dy, const void* x, float* grad, float* scratch, int N, int Di, int Hi, int Wi, int Cin, int Do, int Ho,
-                      int Wo, int Cout, int k, int stride, int pad, int bw, int bh, int bd, int bn, int splits, void* stream) {
+                      int Wo, int Cout, int k, int stride, int pad, int bw, int bh, int bd, int bn, int splits, void* stream,
+                      const float* sal_w = nullptr, float* sal_scores = nullptr, float sal_scale = 0.f) {
     NIDT_REQUIRE(Cin % 64 == 0 && Cout % 8 == 0, "conv3d_wgrad_tc: Cin=%d must be a multiple of 64, Cout=%d of 8", Cin, Cout);
     NIDT_REQUIRE(bw * bh * bd * bn <= 128, "conv3d_wgrad_tc: box exceeds 128 rows");
     NIDT_REQUIRE(splits >= 1 && scratch != nullptr, "conv3d_wgrad_tc: need splits >= 1 and a scratch buffer");
@@ -583,7 +587,7 @@ static int wgrad_impl(const void* dy, const void* x, float* grad, float* scratch
     const int64_t total = (int64_t)Cout * Cin * taps;
     int64_t blocks = (total + 255) / 256;
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    wgrad_reduce_kernel<<<(int)blocks, 256, 0, s>>>(scratch, splits, taps, Cout, Cin, grad);
+    wgrad_reduce_kernel<<<(int)blocks, 256, 0, s>>>(scratch, splits, taps, Cout, Cin, grad, sal_w, sal_scores, sal_scale);
     NIDT_LAUNCH_CHECK();
     return 0;
 }
@@ -593,6 +597,16 @@ static int wgrad_impl(const void* dy, const void* x, float* grad, float* scratch
 NIDT_API int nidt_conv3d_wgrad_tc(const void* dy, const void* x, float* grad, float* scratch, int N, int Di, int Hi, int Wi, int Cin, int Do, int Ho,
                                   int Wo, int Cout, int k, int stride, int pad, int bw, int bh, int bd, int bn, int splits, void* stream) {
     return wgrad_impl(dy, x, grad, scratch, N, Di, Hi, Wi, Cin, Do, Ho, Wo, Cout, k, stride, pad, bw, bh, bd, bn, splits, stream);
+}
+
+// The same weight gradient with the SNIP saliency epilogue: the split-K reduction that writes dW also does
+// scores[co][ci][tap] += scale * |dW * w| (w: the layer's fp32 master weights, same layout) -- the score leaves the wgrad
+// reduction directly instead of a later pass over the gradient slab.  ref: snip.py:60-71 (|weight_mask.grad| = |dL/dw * w|).
+NIDT_API int nidt_conv3d_wgrad_tc_saliency(const void* dy, const void* x, float* grad, float* scratch, int N, int Di, int Hi, int Wi, int Cin, int Do,
+                                           int Ho, int Wo, int Cout, int k, int stride, int pad, int bw, int bh, int bd, int bn, int splits,
+                                           const float* w, float* scores, float scale, void* stream) {
+    NIDT_REQUIRE(w != nullptr && scores != nullptr, "conv3d_wgrad_tc_saliency: w / scores is null");
+    return wgrad_impl(dy, x, grad, scratch, N, Di, Hi, Wi, Cin, Do, Ho, Wo, Cout, k, stride, pad, bw, bh, bd, bn, splits, stream, w, scores, scale);
 }
 
 NIDT_API int nidt_pack_conv_weights(const float* w, int Cout, int Cin, int taps, void* wf, void* wd, void* stream) {

@@ -63,6 +63,9 @@ struct Ctx {
     int launches = 0;
     Box cur_box[8];
     const nidt_dyn_t* dyn = nullptr;      // graph capture: step scalars / result pointers come from device memory
+    const float* sal_w = nullptr;         // SNIP pass: slab base (weights), score slab and scale for the wgrad saliency epilogues
+    float* sal_scores = nullptr;
+    float sal_scale = 0.f;
 };
 
 int pack_weights(Ctx& c, const float* slab) {
@@ -143,7 +146,10 @@ int backward(Ctx& c, const void* x, float* grad) {
         c.launches += 3;
         if (i == 0) {
             float* gb = b.has_bias ? at(grad, b.off_b) : nullptr;
-            if (b.s2d) NIDT_TRY(nidt_conv_in_s2d_wgrad(x, b.dy, at(grad, b.off_w), gb, b.wg_scratch, B, b.in_d, b.in_h, b.in_w, p->input_scale, c.st));
+            if (b.s2d && c.sal_scores != nullptr)
+                NIDT_TRY(nidt_conv_in_s2d_wgrad_saliency(x, b.dy, at(grad, b.off_w), gb, b.wg_scratch, B, b.in_d, b.in_h, b.in_w, p->input_scale,
+                                                         at(c.sal_w, b.off_w), at(c.sal_scores, b.off_w), c.sal_scale, c.st));
+            else if (b.s2d) NIDT_TRY(nidt_conv_in_s2d_wgrad(x, b.dy, at(grad, b.off_w), gb, b.wg_scratch, B, b.in_d, b.in_h, b.in_w, p->input_scale, c.st));
             else NIDT_TRY(nidt_conv_in_wgrad(x, b.dy, at(grad, b.off_w), gb, b.wg_scratch, B, b.in_d, b.in_h, b.in_w, b.k, b.stride, b.pad, p->input_scale, c.st));
             c.launches += 2;
         } else {
@@ -155,8 +161,13 @@ int backward(Ctx& c, const void* x, float* grad) {
                 if (splits > mt) splits = mt;
                 if (splits < 1) splits = 1;
             }
-            NIDT_TRY(nidt_conv3d_wgrad_tc(b.dy, prev.a, at(grad, b.off_w), b.wg_scratch, B, b.in_d, b.in_h, b.in_w, b.cin, b.c_d, b.c_h, b.c_w, b.cout,
-                                          b.k, b.stride, b.pad, bx.bw, bx.bh, bx.bd, bx.bn, splits, c.st));
+            if (c.sal_scores != nullptr)
+                NIDT_TRY(nidt_conv3d_wgrad_tc_saliency(b.dy, prev.a, at(grad, b.off_w), b.wg_scratch, B, b.in_d, b.in_h, b.in_w, b.cin, b.c_d, b.c_h,
+                                                       b.c_w, b.cout, b.k, b.stride, b.pad, bx.bw, bx.bh, bx.bd, bx.bn, splits, at(c.sal_w, b.off_w),
+                                                       at(c.sal_scores, b.off_w), c.sal_scale, c.st));
+            else
+                NIDT_TRY(nidt_conv3d_wgrad_tc(b.dy, prev.a, at(grad, b.off_w), b.wg_scratch, B, b.in_d, b.in_h, b.in_w, b.cin, b.c_d, b.c_h, b.c_w, b.cout,
+                                              b.k, b.stride, b.pad, bx.bw, bx.bh, bx.bd, bx.bn, splits, c.st));
             // dgrad = fprop of dY with the transposed, tap-flipped weights and pad' = k-1-pad
             const Box db = B == p->max_batch ? Box{b.dbox[0], b.dbox[1], b.dbox[2], b.dbox[3]} : choose_box(b.in_w, b.in_h, b.in_d, B);
             NIDT_TRY(nidt_conv3d_fprop_tc(b.dy, b.wd, nullptr, prev.da, nullptr, B, b.c_d, b.c_h, b.c_w, b.cout, b.in_d, b.in_h, b.in_w, b.cin, b.k, 1,
@@ -309,6 +320,27 @@ NIDT_API int nidt_plan_train_step(const nidt_plan_t* plan, const void* x_u8, con
                                       plan->norm_scratch, nullptr, stream));
         c.launches += 2;
         NIDT_TRY(pack_weights(c, slab));
+    }
+    if (launches != nullptr) *launches = c.launches;
+    return 0;
+}
+
+NIDT_API int nidt_plan_saliency_step(const nidt_plan_t* plan, const void* x_u8, const float* y, int batch, float* slab, float* grad, float* scores,
+                                     float scale, int64_t n_params, uint64_t seed, int* launches, void* stream) {
+    NIDT_REQUIRE(plan != nullptr && plan->n_blocks >= 1 && plan->n_blocks <= 8, "nidt_plan: bad plan");
+    NIDT_REQUIRE(batch >= 1 && batch <= plan->max_batch, "nidt_plan_saliency_step: batch %d exceeds the plan's %d", batch, plan->max_batch);
+    NIDT_REQUIRE(scores != nullptr && plan->blocks[0].s2d, "nidt_plan_saliency_step: needs a score slab and the space-to-depth first layer");
+    Ctx c{plan, batch, stream};
+    c.sal_w = slab; c.sal_scores = scores; c.sal_scale = scale;
+    NIDT_TRY(forward(c, x_u8, slab, true));
+    NIDT_TRY(head(c, y, slab, grad, true, nullptr, 1, seed));
+    NIDT_TRY(backward(c, x_u8, grad));
+    // the classifier (everything from fc1.weight to the end of the parameters): one flat pass over that segment
+    const int64_t o = plan->off_fc1_w;
+    NIDT_REQUIRE(o >= 0 && o <= n_params, "nidt_plan_saliency_step: bad classifier offset");
+    if (n_params > o) {
+        NIDT_TRY(nidt_saliency_accumulate(scores + o, grad + o, slab + o, n_params - o, scale, stream));
+        ++c.launches;
     }
     if (launches != nullptr) *launches = c.launches;
     return 0;

@@ -82,15 +82,24 @@ class Client:
         Returns ``(slab, training_flops, num_comm_params)`` like the reference (``client.py:80-104``);
         ``num_comm_params`` is a device scalar (no host sync)."""
         tr = self.model_trainer
+        comm_out = kw.pop("comm_out", None)        # int64 device accumulator: nnz(download) + nnz(upload) are added by the count kernels
         slab = self.ensure_slab(w_global)
         slab.copy_(w_global)
         tr.attach(slab)
         tr.set_id(self.client_idx)
-        num_comm_params = tr.count_communication_params(w_global)
+        if comm_out is not None and slab.flat.is_cuda:
+            from .. import ops
+            ops.count_nonzero(w_global.flat, out=comm_out)
+            num_comm_params = comm_out
+        else:
+            num_comm_params = tr.count_communication_params(w_global)
         tr.train(self.local_training_data, self.device, self.args, round_idx, masks, **kw)
         tr.engine.detach_sync()
         training_flops = self.args.epochs * self.local_sample_number
-        num_comm_params = num_comm_params + tr.count_communication_params(slab)
+        if num_comm_params is comm_out and comm_out is not None:
+            ops.count_nonzero(slab.flat, out=comm_out)
+        else:
+            num_comm_params = num_comm_params + tr.count_communication_params(slab)
         return slab, training_flops, num_comm_params
 
     def local_test(self, w_per: ParamSlab, b_use_test_dataset: bool = True):

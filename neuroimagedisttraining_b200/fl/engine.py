@@ -27,6 +27,18 @@ class StepHParams:
     clip_norm: float = 10.0
 
 
+class LazyMean:
+    """A mean loss that is still on the device: ``sum`` (0-d tensor, the per-step mean losses added up) over ``steps``.  Lets the
+    engines hand out epoch losses without any kernel launch; :meth:`SlabTrainer.flush_losses` reads many of them in one copy."""
+    __slots__ = ("sum", "steps")
+
+    def __init__(self, total: torch.Tensor, steps: int):
+        self.sum, self.steps = total, max(1, int(steps))
+
+    def item(self) -> float:
+        return float(self.sum.item()) / self.steps
+
+
 class EvalCounters:
     """Device-side accumulators (correct, loss_sum, total): no per-batch ``.item()`` syncs
     (the reference does three per batch, ``my_model_trainer.py:270-273``)."""

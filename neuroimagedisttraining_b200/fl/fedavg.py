@@ -4,6 +4,7 @@ from __future__ import annotations
 import time
 
 import numpy as np
+import torch
 
 from .base import FedAPIBase
 
@@ -38,11 +39,15 @@ class FedAvgAPI(FedAPIBase):
                 client = self.client_list[cur_clnt]
                 # stream staging: the next client's first batch is copied while this one finishes
                 nxt = self.client_list[mine[pos + 1]].local_training_data if pos + 1 < len(mine) else None
-                slab, training_flops, num_comm_params = client.train(self.w_global, round_idx, mask, lookahead_data=nxt)
+                if self._comm_params_dev is None and self.device.type == "cuda":
+                    self._comm_params_dev = torch.zeros((), dtype=torch.int64, device=self.device)
+                slab, training_flops, num_comm_params = client.train(self.w_global, round_idx, mask, lookahead_data=nxt,
+                                                                     comm_out=self._comm_params_dev)
                 self._defend(slab)
                 w_locals.append((client.get_sample_number(), slab))
                 self.stat_info["sum_training_flops"] += training_flops
-                self._add_comm_params(num_comm_params)
+                if num_comm_params is not self._comm_params_dev:
+                    self._add_comm_params(num_comm_params)
         # the shared mask rides along in the aggregation kernel (a no-op on already-masked client weights, as in the reference
         # where the multiply at sailentgrads_api.py:109 is commented out; it keeps the global model exactly sparse)
         self._aggregate(w_locals, training_num, mask=mask)

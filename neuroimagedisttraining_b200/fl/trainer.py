@@ -20,7 +20,7 @@ from .. import ops
 from ..runtime.slab import ParamSlab, make_mask_slab
 from ..runtime import xfer
 from ..runtime.staging import BatchStager, make_stager
-from .engine import EvalCounters, StepHParams, TorchEngine
+from .engine import EvalCounters, LazyMean, StepHParams, TorchEngine
 
 
 class ModelTrainer(ABC):
@@ -389,7 +389,9 @@ class SlabTrainer(ModelTrainer):
         """Read the queued per-epoch losses (one host sync) and log them in the reference's format."""
         if not self.pending_losses:
             return []
-        vals = xfer.to_host(torch.stack([l.detach().float().reshape(()) for _, _, l in self.pending_losses])).tolist()
+        sums = torch.stack([(l.sum if isinstance(l, LazyMean) else l).detach().float().reshape(()) for _, _, l in self.pending_losses])
+        vals = xfer.to_host(sums).tolist()
+        vals = [v / l.steps if isinstance(l, LazyMean) else v for v, (_, _, l) in zip(vals, self.pending_losses)]
         out = []
         for (cid, epoch, _), v in zip(self.pending_losses, vals):
             out.append(v)
@@ -432,7 +434,11 @@ class SlabTrainer(ModelTrainer):
         P = self.layout.param_numel
         self.engine.detach_sync()
         saved = self.slab.flat[P:].clone()           # BN running stats must not move (the reference scores a deep copy)
-        self.engine.compute_grads(x, y, train_mode=True)
+        fused = getattr(self.engine, "saliency_step", None)
+        done = bool(fused(x, y, scores.flat, scale)) if fused is not None else False      # |dW*w| from the wgrad reductions themselves
+        if not done:
+            self.engine.compute_grads(x, y, train_mode=True)
         self.slab.flat[P:].copy_(saved)
         self.slab.sync_int_buffers_to(self.model)
-        ops.saliency_accumulate(scores.flat, self.engine.grad.flat, self.slab.params_flat, scale)
+        if not done:
+            ops.saliency_accumulate(scores.flat, self.engine.grad.flat, self.slab.params_flat, scale)

@@ -73,6 +73,8 @@ def _declare(lib) -> None:
     lib.nidt_plan_train_step_graph.restype = i32
     lib.nidt_plan_eval_graph.argtypes = [vp, vp, vp, i32, vp, vp, i32, vp, vp, vp]
     lib.nidt_plan_eval_graph.restype = i32
+    lib.nidt_plan_saliency_step.argtypes = [vp, vp, vp, i32, vp, vp, vp, f32, i64, u64, vp, vp]
+    lib.nidt_plan_saliency_step.restype = i32
     lib.nidt_plan_graph_clear.argtypes = [vp]
     lib.nidt_plan_graph_clear.restype = i32
     lib.nidt_plan_graph_count.argtypes = []
@@ -175,7 +177,10 @@ class B200Engine:
             raise ImportError("native head supports one logit")
         self.grad = ParamSlab(self.layout, device=self.device, params_only=True)
         self.slab: Optional[ParamSlab] = None
-        self.loss_acc = torch.zeros((), dtype=torch.float32, device=self.device)
+        # one slot per (client, epoch) mean loss: popping a loss moves to the next zeroed slot instead of launching a divide + a fill
+        self._loss_ring = torch.zeros(1024, dtype=torch.float32, device=self.device)
+        self._loss_pos = 0
+        self.loss_acc = self._loss_ring[0]
         self.loss_steps = 0
         self._packed_dirty = True
         self.profile = None
@@ -461,6 +466,29 @@ class B200Engine:
         self.step += 1
         return self.loss_acc
 
+    def saliency_step(self, x, y, scores: torch.Tensor, scale: float) -> bool:
+        """One SNIP evaluation with the scores produced by the kernels that produce the gradients: ``scores += scale*|g*w|`` for
+        every conv weight leaves the split-K reduction of its wgrad, the classifier's segment is one flat pass (``snip.py:60-71``).
+        Non-prunable parameters (biases, BatchNorm) are not scored -- the mask is 1 there whatever their score.  Returns False when
+        this engine configuration has no fused path (the caller then scores the gradient slab in a separate pass)."""
+        b0 = self.blocks[0]
+        if not (self._native_ready() and b0.s2d and self.s2d_wgrad):
+            return False
+        lay, h = self.layout, self.head
+        o = lay[h.fc1 + ".weight"].offset
+        if any(lay[s.conv + ".weight"].offset >= o for s in self.plan) or lay[h.fc2 + ".weight"].offset < o:
+            return False
+        x = self._check_x(x)
+        self._x = x
+        y = y.to(self.device, torch.float32).contiguous()
+        native.check(self.lib.nidt_plan_saliency_step(
+            C.byref(self._plan), x.data_ptr(), y.data_ptr(), int(x.shape[0]), self.slab.flat.data_ptr(), self.grad.flat.data_ptr(),
+            native.ptr(scores), float(scale), lay.param_numel, self.seed + 7919 * self.step, C.byref(self._launches), self._stream()),
+            "nidt_plan_saliency_step")
+        native.count_launches(self._launches.value)
+        self.step += 1
+        return True
+
     def _check_x(self, x: torch.Tensor) -> torch.Tensor:
         assert x.dtype == torch.uint8 and x.is_cuda and x.dim() == 4, "B200Engine consumes 8-bit volumes [B,D,H,W]"
         x = x.contiguous()
@@ -507,10 +535,15 @@ class B200Engine:
 
     def pop_mean_loss(self, sync: bool = True):
         """Mean loss since the last call; ``sync=False`` returns a 0-d device tensor (no host synchronisation)."""
-        mean = self.loss_acc / max(1, self.loss_steps)
-        self.loss_acc = torch.zeros_like(self.loss_acc)
+        from ..fl.engine import LazyMean
+        out = LazyMean(self.loss_acc, self.loss_steps)
+        self._loss_pos += 1
+        if self._loss_pos >= self._loss_ring.numel():      # handles keep the old ring alive until they are read
+            self._loss_ring = torch.zeros_like(self._loss_ring)
+            self._loss_pos = 0
+        self.loss_acc = self._loss_ring[self._loss_pos]
         self.loss_steps = 0
-        return float(mean.item()) if sync else mean
+        return out.item() if sync else out
 
     def eval_batch(self, x, y, counters, double_sigmoid: bool = True) -> None:
         y = y.to(self.device, torch.float32).contiguous()

@@ -325,3 +325,32 @@ def test_engine_trains_and_evaluates():
     with torch.no_grad():
         z = ref.model(ref._prep(x)).flatten()
     torch.testing.assert_close(eng.logits(x), z, rtol=5e-2, atol=5e-2)
+
+
+def test_saliency_epilogue_scores_equal_the_separate_pass():
+    """SNIP scores written by the wgrad reductions (conv layers) + the classifier's flat pass == |g*w| computed from the gradient slab
+    afterwards, on every prunable weight (``snip.py:60-71``); the gradients themselves are unchanged by the epilogue."""
+    from neuroimagedisttraining_b200 import ops
+    eng, _ = _engine_pair(4, p_drop=0.0)
+    slab = eng.new_slab()
+    eng.attach(slab)
+    g = torch.Generator().manual_seed(21)
+    x = torch.randint(0, 256, (4, 121, 145, 121), generator=g, dtype=torch.uint8).to(DEV)
+    y = (torch.rand(4, generator=g) > 0.5).float().to(DEV)
+    lay = eng.layout
+    scores = torch.zeros(lay.param_numel, device=DEV)
+    bn_tail = slab.flat[lay.param_numel:].clone()
+    assert eng.saliency_step(x, y, scores, 0.5)
+    g_fused = eng.grad.flat.clone()
+    slab.flat[lay.param_numel:].copy_(bn_tail)
+    eng.step -= 1                                            # same dropout stream (p = 0 here anyway)
+    eng.compute_grads(x, y, True)
+    torch.cuda.synchronize()
+    assert torch.equal(eng.grad.flat, g_fused)
+    ref = torch.zeros_like(scores)
+    ops.saliency_accumulate(ref, eng.grad.flat, slab.params_flat, 0.5)
+    for name in lay.prunable_names:
+        e = lay[name]
+        a, b = scores[e.offset:e.offset + e.numel], ref[e.offset:e.offset + e.numel]
+        assert float(b.abs().sum()) > 0
+        assert torch.equal(a, b), f"{name}: max diff {(a - b).abs().max().item()}"

@@ -32,7 +32,7 @@ def _run(use_graphs: bool):
                 xbuf.copy_(xs[(step + si) % 2]); ybuf.copy_(ys[(step + si) % 2])
                 hp = StepHParams(lr=0.01 * (0.9 ** rnd), momentum=0.9 if si else 0.0, wd=5e-4, clip_norm=10.0)
                 eng.train_step(xbuf[:b], ybuf[:b], hp, mask, mom, step == 0)
-            out.append(eng.pop_mean_loss(sync=False).clone())
+            out.append(eng.pop_mean_loss(sync=False).sum.clone())
             out.append(eng.grad.flat.clone())
         acc = torch.zeros((2, 3), dtype=torch.float64, device=DEV)
         for si, slab in enumerate(slabs):
