@@ -525,7 +525,7 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restri
     for (int q = 0; q < n_cta; ++q) acc += partials[(size_t)q * (3 * 128 * 64) + i];
     const int o = co * 125 + (kd * 5 + kh) * 5 + kw;
     grad[o] = acc;
-    if (scores != nullptr) scores[o] += sal_scale * fabsf(acc * w[o]);      // SNIP |dL/dw * w| straight from the reduction
+    if (scores != nullptr) scores[o] = fmaf(sal_scale, fabsf(acc * w[o]), scores[o]);      // SNIP |dL/dw * w| straight from the reduction
 }
 
 static int make_geom(Geom& g, int N, int Di, int Hi, int Wi, float scale) {

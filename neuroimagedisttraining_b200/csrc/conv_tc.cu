@@ -441,7 +441,7 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restri
         for (int s = 0; s < splits; ++s) acc += partials[(size_t)s * total + i];
         const size_t o = ((size_t)co * Cin + ci) * taps + t;
         grad[o] = acc;
-        if (scores != nullptr) scores[o] += scale * fabsf(acc * w[o]);
+        if (scores != nullptr) scores[o] = fmaf(scale, fabsf(acc * w[o]), scores[o]);      // same arithmetic as saliency_accumulate_kernel
     }
 }
 
