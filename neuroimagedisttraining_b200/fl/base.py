@@ -58,6 +58,7 @@ class FedAPIBase:
         self.init_stat_info()
         self.w_global: ParamSlab = model_trainer.engine.new_slab()
         self.aggregator = Aggregator(self.dist, self.layout, self.device, agg_mode)
+        self.aggregator.adopt_global(self.w_global)
         self.timer = PhaseTimer(self.device)
         self.start_round = 0
         self.mask: Optional[ParamSlab] = None

@@ -5,7 +5,8 @@ kernel, ``ops.weighted_aggregate``); the cross-rank sum + SalientGrads mask mult
 of the new global model into every rank's slab is then either
 
 * ``fused``  one sm_100a kernel per rank over NVLink symmetric memory (``csrc/sym_agg.cu``):
-             reduce-scatter by P2P loads of the peers' partials, mask multiply, all-gather by P2P
+             the sample-count weighting of the rank's own clients, reduce-scatter by P2P loads / bulk-async
+             copies / in-switch multimem reduction of the peers' partials, mask multiply, all-gather by
              stores into every peer's global slab -- no NCCL launch, no extra passes; or
 * ``nccl``   the baseline the fused kernel is measured against: ``all_reduce`` of the partial
              followed by an elementwise mask multiply (what a thin wrapper around the reference's
@@ -13,6 +14,7 @@ of the new global model into every rank's slab is then either
 """
 from __future__ import annotations
 
+import os
 from typing import Optional, Sequence, Tuple
 
 import torch
@@ -65,6 +67,11 @@ class Aggregator:
             return None
         return fused
 
+    def adopt_global(self, slab: ParamSlab) -> None:
+        """Let the global model live where the fused kernel's all-gather writes it (no write-back pass); a no-op on the other paths."""
+        if self._fused is not None and os.environ.get("NIDT_AGG_ADOPT", "1") != "0":
+            self._fused.adopt(slab)
+
     def aggregate(self, out: ParamSlab, local: Sequence[Tuple[float, ParamSlab]], mask: Optional[ParamSlab] = None) -> ParamSlab:
         """``out = mask * sum_{all ranks} sum_{local} weight * slab``; ``local`` holds this rank's
         (already normalised weight n_i/sum n, slab) pairs, in client order."""
@@ -72,16 +79,17 @@ class Aggregator:
         if not self.ctx.is_distributed:
             ops.weighted_aggregate(out.flat, [s.flat for _, s in local], [w for w, _ in local], mflat)
             return out
+        if self._fused is not None:
+            # the sample-count weighting of this rank's clients happens inside the fused kernel, in client order
+            self._fused.aggregate(out.flat, [(w, s.flat) for w, s in local], mflat)
+            return out
         if local:
             ops.weighted_aggregate(self.partial, [s.flat for _, s in local], [w for w, _ in local], None)
         else:
             self.partial.zero_()
-        if self._fused is not None:
-            self._fused.reduce_mask_broadcast(out.flat, mflat)
-        else:
-            dist.all_reduce(self.partial, op=dist.ReduceOp.SUM)
-            if mflat is not None:
-                n = mflat.numel()
-                self.partial[:n].mul_(mflat)
-            out.flat.copy_(self.partial)
+        dist.all_reduce(self.partial, op=dist.ReduceOp.SUM)
+        if mflat is not None:
+            n = mflat.numel()
+            self.partial[:n].mul_(mflat)
+        out.flat.copy_(self.partial)
         return out

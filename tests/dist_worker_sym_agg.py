@@ -67,10 +67,57 @@ def main():
         torch.cuda.synchronize()
         nd = int((mask2 != ref_mask).sum())
         close = torch.equal(sc, ref_sc) if not mm else torch.allclose(sc, ref_sc, rtol=1e-6, atol=0)
-        if nd > (0 if not mm else 4) or abs(fi["kept"] - ri["kept"]) > (0 if not mm else 4) or not close:
+        # the k-th largest score is found exactly; which near-ties of the normalised threshold are kept depends on the last bit of
+        # the norm, which the sharded kernel sums shard by shard in rank order
+        if nd > 4 or abs(fi["kept"] - ri["kept"]) > 4 or not close:
             ok = False
         if ctx.rank == 0:
             print(f"saliency multimem={mm}: mask diff={nd} kept={fi['kept']} (ref {ri['kept']}) thr={fi['threshold']:.6e}")
+    # W1 with the weighting of K local client slabs inside the kernel, every data path, and the in-place (adopted) global slab
+    K = 3
+    locs = [torch.randn(n, generator=torch.Generator().manual_seed(7000 + 10 * ctx.rank + j)).to(dev) for j in range(K)]
+    wts = [0.05 * (j + 1) + 0.01 * ctx.rank for j in range(K)]
+    mine = torch.empty(n, device=dev)
+    ops.weighted_aggregate(mine, locs, wts, None)
+    parts = [torch.empty_like(mine) for _ in range(ctx.world_size)]
+    dist.all_gather(parts, mine)
+    ref = parts[0].clone()
+    for q in parts[1:]:
+        ref += q
+    ref[:nm] *= mask
+    cases = [("p2p", 0.0), ("bulk", 0.0)] + ([("multimem", 0.0), ("bulk", 0.5), ("p2p", 0.25)] if agg.mc_partial else [])
+    for mode, frac in cases:
+        out = torch.full((n,), float("nan"), device=dev)
+        agg.aggregate(out, list(zip(wts, locs)), mask, mode=mode, mm_frac=frac)
+        torch.cuda.synchronize()
+        err = (out - ref).abs().max().item()
+        good = err == 0.0 if (mode != "multimem" and frac == 0.0) else err <= 2e-5
+        ok = ok and good
+        if ctx.rank == 0:
+            print(f"in-kernel weighting mode={mode} mm_frac={frac}: max err {err:.3e} ok={good}")
+    from neuroimagedisttraining_b200.runtime.slab import ParamSlab
+    g_slab = ParamSlab(layout)
+    g_slab.flat = torch.randn(layout.total_numel, device=dev)
+    agg2 = SymmetricAggregator(ctx, layout.total_numel, dev)
+    agg2.adopt(g_slab)
+    assert g_slab.flat.data_ptr() == agg2.local_result.data_ptr()
+    n2 = layout.total_numel
+    locs2 = [l[:n2].contiguous() for l in locs]
+    agg2.aggregate(g_slab.flat, list(zip(wts, locs2)), None, mode="p2p")
+    other = torch.empty(n2, device=dev)
+    agg2.aggregate(other, list(zip(wts, locs2)), None, mode="p2p")          # must not disturb the adopted slab
+    torch.cuda.synchronize()
+    mine2 = torch.empty(n2, device=dev)
+    ops.weighted_aggregate(mine2, locs2, wts, None)
+    parts2 = [torch.empty_like(mine2) for _ in range(ctx.world_size)]
+    dist.all_gather(parts2, mine2)
+    ref2 = parts2[0].clone()
+    for q in parts2[1:]:
+        ref2 += q
+    adopted_ok = torch.equal(g_slab.flat, ref2) and torch.equal(other, ref2)
+    ok = ok and adopted_ok
+    if ctx.rank == 0:
+        print(f"adopted global slab (no write-back) ok={adopted_ok}")
     # a rank that reaches the aggregation long after its peers (uneven client counts, a rank without a sampled client): the launch
     # is preceded by a stream-ordered line-up of the ranks, so the late rank costs time, not a device-side time-out.  12 s is above
     # the 10 s the kernel's own barrier used to allow.
