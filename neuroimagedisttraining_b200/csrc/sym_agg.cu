@@ -166,8 +166,10 @@ __device__ __forceinline__ void rs_ag_p2p(const SymPeers& sp, const float* __res
 template <int U>
 __device__ __forceinline__ void rs_ag_multimem(const SymPeers& sp, const float* __restrict__ mask, int64_t n_mask, int64_t lo, int64_t hi, int cta0,
                                                int nctas, bool broadcast) {
-    const int64_t tid = (int64_t)((int)blockIdx.x - cta0) * blockDim.x + threadIdx.x, nth = (int64_t)nctas * blockDim.x;
-    for (int64_t i = lo + tid; i < hi; i += U * nth) {
+    // a CTA works on contiguous tiles of U * blockDim float4 (32 KiB at U = 4), tiles round-robin over the CTAs: the requests a
+    // CTA has in flight stay within a few pages on every GPU the switch reads from
+    const int64_t tile = (int64_t)U * blockDim.x, nth = blockDim.x;
+    for (int64_t i = lo + (int64_t)((int)blockIdx.x - cta0) * tile + threadIdx.x; i < hi; i += (int64_t)nctas * tile) {
         float4 v[U];
 #pragma unroll
         for (int u = 0; u < U; ++u)
@@ -260,14 +262,14 @@ __device__ __forceinline__ void reduce_mask_broadcast(const SymPeers& sp, const 
     const int64_t per = (n4 + sp.world - 1) / sp.world;
     const int64_t lo = per * sp.rank, hi = min(n4, lo + per);
     const int G = (int)gridDim.x;
-    if (mode == kModeMultimem || mm_frac_q8 >= 256) { rs_ag_multimem<4>(sp, mask, n_mask, lo, hi, 0, G, broadcast); return; }
+    if (mode == kModeMultimem || mm_frac_q8 >= 256) { rs_ag_multimem<8>(sp, mask, n_mask, lo, hi, 0, G, broadcast); return; }
     int g_mm = 0;
     int64_t mid = lo;
     if (mm_frac_q8 > 0 && sp.mc_partial != nullptr && G >= 2 && hi > lo) {
         g_mm = max(1, min(G - 1, (G * mm_frac_q8) >> 8));
         mid = lo + (((hi - lo) * mm_frac_q8) >> 8);
     }
-    if ((int)blockIdx.x < g_mm) { rs_ag_multimem<4>(sp, mask, n_mask, lo, mid, 0, g_mm, broadcast); return; }
+    if ((int)blockIdx.x < g_mm) { rs_ag_multimem<8>(sp, mask, n_mask, lo, mid, 0, g_mm, broadcast); return; }
     if (mode == kModeBulk) rs_ag_bulk(sp, mask, n_mask, mid, hi, g_mm, G - g_mm, broadcast, smem);
     else rs_ag_p2p<kWorld>(sp, mask, n_mask, mid, hi, g_mm, G - g_mm, broadcast);
 }
@@ -414,15 +416,23 @@ __global__ void __launch_bounds__(kSymThreads) sym_saliency_topk_kernel(const Sy
 
     // mask of my shard -> every rank's mask buffer
     unsigned int kept = 0u;
-    for (int64_t i = lo + tid; i < hi; i += nth) {
-        const unsigned char f = flags[i];
-        float m = 0.f;
-        if (f == 1) m = 1.f;
-        else if (f == 2) {
-            m = (__fdiv_rn(scores[i], norm) >= thr_q) ? 1.f : 0.f;
-            kept += (unsigned int)m;
+    for (int64_t i4 = (lo >> 2) + tid; i4 < (hi >> 2); i4 += nth) {             // shard bounds are multiples of 4: 16-byte stores to every peer
+        const uchar4 f4 = *reinterpret_cast<const uchar4*>(flags + 4 * i4);
+        const float4 s4 = ld4(scores + 4 * i4);
+        const unsigned char f[4] = {f4.x, f4.y, f4.z, f4.w};
+        const float sv[4] = {s4.x, s4.y, s4.z, s4.w};
+        float m[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            m[q] = 0.f;
+            if (f[q] == 1) m[q] = 1.f;
+            else if (f[q] == 2) {
+                m[q] = (__fdiv_rn(sv[q], norm) >= thr_q) ? 1.f : 0.f;
+                kept += (unsigned int)m[q];
+            }
         }
-        for (int p = 0; p < P; ++p) aux.mask_out[p][i] = m;
+        const float4 mv = make_float4(m[0], m[1], m[2], m[3]);
+        for (int p = 0; p < P; ++p) st4(aux.mask_out[p] + 4 * i4, mv);
     }
     kept = (unsigned int)warp_sum_u64(kept);
     if ((threadIdx.x & 31) == 0 && kept) atomicAdd(aux.local_hist + 3 * kRadixBins, kept);
@@ -583,11 +593,12 @@ NIDT_API int nidt_sym_saliency_topk_mask(void* const* partial_ptrs, void* const*
     const void* kern = pick_topk_kernel(world);
     NIDT_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kSymThreads, 0));
     NIDT_REQUIRE(per_sm >= 1, "sym_saliency_topk: kernel does not fit on an SM");
-    // a shard is n/world elements: one CTA per 8 K elements, at most one per SM (the passes are latency-, not bandwidth-bound)
-    int64_t want = (n / world + 8191) / 8192;
-    if (want < 1) want = 1;
-    int grid = (int)(want < sms ? want : sms);
-    if (grid > 2 * kNumSMs) grid = 2 * kNumSMs;
+    // a shard is n/world elements and L2-resident: the passes are bound by the grid-wide and cross-rank synchronisations, whose cost
+    // grows with the number of CTAs -- one CTA per 16 K elements, 4 to 48
+    int64_t want = (n / world + 16383) / 16384;
+    if (want < 4) want = 4;
+    int grid = (int)(want < 48 ? want : 48);
+    if (grid > sms) grid = sms;
     int mode = use_multimem ? kModeMultimem : kModeP2P;
     void* args[] = {(void*)&sp, (void*)&aux, (void*)&n, (void*)&flags, (void*)&mask, (void*)&k, (void*)&res, (void*)&scores_out, (void*)&epoch, (void*)&mode};
     NIDT_CUDA_CHECK(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(kSymThreads), args, 0, (cudaStream_t)stream));

@@ -119,15 +119,26 @@ class SymmetricAggregator:
         """True / False forces the path for every size; None returns to the choice by size."""
         self._mm_forced = force
 
-    def pick_mode(self, numel: int) -> str:
+    def pick(self, numel: int) -> Tuple[str, float, int]:
+        """(mode, share of each chunk sent through the in-switch path, CTAs or 0) for a slab of ``numel`` floats -- the fastest
+        variant of the clock-stamped sweeps at 2 and 8 GPUs (profiles/agg_sweep_n*_v3.jsonl): two ranks gain nothing from the
+        switch (P2P moves no more bytes than NVLS there), so they use the shared-memory P2P path; from 3 ranks on, NVLS up to
+        256 MB and above that the shared-memory P2P path with half of every chunk through the switch."""
         env = os.environ.get("NIDT_AGG_MODE")
-        if env in MODES and (env != "multimem" or self.has_multicast):
-            return env
-        if self.use_multimem_for(numel):
-            return "multimem"
-        if 4 * int(numel) >= self.bulk_min_bytes and self.ctx.world_size <= self.lib.nidt_sym_bulk_max_ranks():
-            return "bulk"
-        return "p2p"
+        bulk_ok = self.ctx.world_size <= self.lib.nidt_sym_bulk_max_ranks()
+        if env in MODES and (env != "multimem" or self.has_multicast) and (env != "bulk" or bulk_ok):
+            return env, 0.0, 0
+        p2p = "bulk" if bulk_ok else "p2p"
+        forced = self._mm_forced
+        if not self.has_multicast or forced is False or (forced is None and self.ctx.world_size <= 2):
+            return p2p, 0.0, 0
+        if forced is True or 4 * int(numel) <= self.multimem_max_bytes:
+            return "multimem", 0.0, (148 if 4 * int(numel) >= (64 << 20) else 0)
+        return p2p, 0.5, 0
+
+    def pick_mode(self, numel: int) -> str:
+        mode, frac, _ = self.pick(numel)
+        return mode + (f"+mm{frac:g}" if frac else "")
 
     def align_ranks(self) -> None:
         """Stream-ordered line-up of the ranks before a fused launch: a one-element NCCL all-reduce on the launching stream.
@@ -178,8 +189,14 @@ class SymmetricAggregator:
         if align:
             self.align_ranks()
         self.epoch += 1
-        mode = mode or self.pick_mode(n)
-        frac = float(os.environ.get("NIDT_AGG_MM_FRAC", "0")) if mm_frac is None else float(mm_frac)
+        auto_mode, auto_frac, auto_ctas = self.pick(n)
+        if mode is None:
+            mode, ctas = auto_mode, (ctas or auto_ctas)
+            frac = auto_frac if mm_frac is None else float(mm_frac)
+        else:
+            frac = 0.0 if mm_frac is None else float(mm_frac)
+        if "NIDT_AGG_MM_FRAC" in os.environ and mm_frac is None:
+            frac = float(os.environ["NIDT_AGG_MM_FRAC"])
         if not self.has_multicast:
             frac = 0.0
         n_mask = 0 if mask is None else min(mask.numel(), n) // 4 * 4
@@ -230,7 +247,7 @@ class SymmetricAggregator:
         if align:
             self.align_ranks()
         s["epoch"] += 1
-        mm = bool(s["mc_partial"]) and self.use_multimem_for(n)
+        mm = bool(s["mc_partial"]) and self.pick(n)[0] == "multimem"
         native.check(self.lib.nidt_sym_saliency_topk_mask(
             s["partial"], s["result"], s["flags"], s["mc_partial"], s["mc_result"], s["hist"], s["mask"], self.ctx.rank, self.ctx.world_size, n,
             native.ptr(flags), native.ptr(mask_out), k, native.ptr(s["scratch"]), native.ptr(scores), s["epoch"], int(mm),

@@ -56,11 +56,12 @@ for mb in sizes_mb:
     row = {"kernel": "W1 agg_weighted_reduce_mask_bcast", "size_mb": mb, "n_gpus": P, "local_clients_weighted_in_kernel": K}
     variants = [("p2p", 0.0, 0), ("bulk", 0.0, 0)]
     if agg.has_multicast:
-        variants += [("multimem", 0.0, 0), ("multimem", 0.0, 148), ("bulk", 0.5, 0), ("bulk", 0.67, 0), ("p2p", 0.5, 0)]
+        variants += [("multimem", 0.0, 0), ("multimem", 0.0, 148), ("bulk", 0.33, 0), ("bulk", 0.5, 0)]
     times = {}
     for mode, frac, ctas in variants:
         name = mode + (f"+mm{frac:g}" if frac else "") + (f"@{ctas}" if ctas else "")
         times[name] = timeit(lambda: agg.aggregate(out, locs, mask, align=False, mode=mode, mm_frac=frac, ctas=ctas, use_partial=(K == 0)), reps)
+    times["auto"] = timeit(lambda: agg.aggregate(out, locs, mask, align=False, use_partial=(K == 0)), reps)
     row["fused_ms"] = times
     row["auto_choice"] = agg.pick_mode(n)
 

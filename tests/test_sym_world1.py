@@ -59,6 +59,19 @@ def test_reduce_mask_broadcast_world1_equals_masked_copy(world1):
         agg.reduce_mask_broadcast(out, None)
         torch.cuda.synchronize()
         assert torch.equal(out, part)
+    # every data path, with the weighting of K client slabs inside the kernel, written in place (adopted slab) and to another tensor
+    agg.use_multimem = None
+    locs = [torch.randn(n, generator=g).to(dev) for _ in range(3)]
+    wts = [0.2, 0.3, 0.5]
+    want = torch.empty(n, device=dev)
+    ops.weighted_aggregate(want, locs, wts, None)
+    want[:nm] *= mask
+    cases = [("p2p", 0.0), ("bulk", 0.0)] + ([("multimem", 0.0), ("bulk", 0.5), ("p2p", 0.3)] if agg.has_multicast else [])
+    for mode, frac in cases:
+        for target in (torch.full((n,), float("nan"), device=dev), agg.local_result):
+            agg.aggregate(target, list(zip(wts, locs)), mask, mode=mode, mm_frac=frac)
+            torch.cuda.synchronize()
+            assert torch.equal(target, want), f"mode={mode} mm_frac={frac}: max diff {(target - want).abs().max().item()}"
 
 
 def test_saliency_topk_mask_world1_equals_torch_topk(world1):
