@@ -449,9 +449,9 @@ __global__ void __launch_bounds__(kSymThreads) sym_saliency_topk_kernel(const Sy
     if (blockIdx.x == 0 && threadIdx.x < P) aux.hist[threadIdx.x][((size_t)1 * kMaxRanks + sp.rank) * kRadixBins] = aux.local_hist[3 * kRadixBins];
     cross_rank_barrier(grid, sp, 0, ++bar);
     if (mask != aux.mask_out[sp.rank])
-        for (int64_t i = tid; i < n; i += nth) mask[i] = aux.mask_out[sp.rank][i];
+        for (int64_t i = tid; i < n4; i += nth) st4(mask + 4 * i, ld4(aux.mask_out[sp.rank] + 4 * i));
     if (scores_out != nullptr && scores_out != scores)
-        for (int64_t i = tid; i < n; i += nth) scores_out[i] = scores[i];
+        for (int64_t i = tid; i < n4; i += nth) st4(scores_out + 4 * i, ld4(scores + 4 * i));
     if (tid == 0) {
         unsigned int total = 0u;
         for (int r = 0; r < P; ++r) total += aux.hist[sp.rank][((size_t)1 * kMaxRanks + r) * kRadixBins];
@@ -594,8 +594,8 @@ NIDT_API int nidt_sym_saliency_topk_mask(void* const* partial_ptrs, void* const*
     NIDT_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kSymThreads, 0));
     NIDT_REQUIRE(per_sm >= 1, "sym_saliency_topk: kernel does not fit on an SM");
     // a shard is n/world elements and L2-resident: the passes are bound by the grid-wide and cross-rank synchronisations, whose cost
-    // grows with the number of CTAs -- one CTA per 16 K elements, 4 to 48
-    int64_t want = (n / world + 16383) / 16384;
+    // grows with the number of CTAs -- 4 to 48 CTAs
+    int64_t want = (n + 16383) / 16384;        // the mask / score copy-outs run over the whole slab on every rank
     if (want < 4) want = 4;
     int grid = (int)(want < 48 ? want : 48);
     if (grid > sms) grid = sms;

@@ -121,16 +121,16 @@ class SymmetricAggregator:
 
     def pick(self, numel: int) -> Tuple[str, float, int]:
         """(mode, share of each chunk sent through the in-switch path, CTAs or 0) for a slab of ``numel`` floats -- the fastest
-        variant of the clock-stamped sweeps at 2 and 8 GPUs (profiles/agg_sweep_n*_v3.jsonl): two ranks gain nothing from the
-        switch (P2P moves no more bytes than NVLS there), so they use the shared-memory P2P path; from 3 ranks on, NVLS up to
-        256 MB and above that the shared-memory P2P path with half of every chunk through the switch."""
+        variant of the clock-stamped sweeps at 2, 4 and 8 GPUs (profiles/agg_sweep_n*_v3.jsonl): up to 4 ranks the shared-memory
+        P2P path wins at every size (P2P moves 2(P-1)/P of the slab per direction, little more than the switch path's 1x); from
+        5 ranks on, NVLS up to 256 MB and above that the shared-memory P2P path with half of every chunk through the switch."""
         env = os.environ.get("NIDT_AGG_MODE")
         bulk_ok = self.ctx.world_size <= self.lib.nidt_sym_bulk_max_ranks()
         if env in MODES and (env != "multimem" or self.has_multicast) and (env != "bulk" or bulk_ok):
             return env, 0.0, 0
         p2p = "bulk" if bulk_ok else "p2p"
         forced = self._mm_forced
-        if not self.has_multicast or forced is False or (forced is None and self.ctx.world_size <= 2):
+        if not self.has_multicast or forced is False or (forced is None and self.ctx.world_size <= 4):
             return p2p, 0.0, 0
         if forced is True or 4 * int(numel) <= self.multimem_max_bytes:
             return "multimem", 0.0, (148 if 4 * int(numel) >= (64 << 20) else 0)
