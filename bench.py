@@ -47,6 +47,7 @@ def parse():
     p.add_argument("--agg", default="auto", choices=["auto", "fused", "nccl"])
     p.add_argument("--shape", default="121,145,121")
     p.add_argument("--skip-e2e", action="store_true")
+    p.add_argument("--lanes", type=int, default=int(os.environ.get("NIDT_LANES", "2")), help="concurrent client slots per GPU (engines on their own CUDA streams)")
     p.add_argument("--model", default="alexnet3d", choices=["alexnet3d", "resnet3d"],
                    help="resnet3d = BASELINE.json config 4 (use with --clients 84 --batch 8 --dense-ratio 0.1 --per-site 10; ours arm only)")
     p.add_argument("--algo", default="salientgrads", choices=["salientgrads", "fedavg"], help="fedavg = BASELINE.json config 2 (ours arm only)")
@@ -284,6 +285,9 @@ def run_ours(a):
     if engine is None and a.model == "resnet3d":
         fl_args.amp = True
     trainer = SlabTrainer(model, fl_args, logger, device=device, store=store, engine=engine, staging="client")
+    if engine_name == "b200" and a.model == "alexnet3d":
+        for _ in range(max(0, a.lanes - 1)):
+            trainer.add_lane(make_native_engine(model, device, max_batch=a.batch, input_scale=store.scale))
     from neuroimagedisttraining_b200.fl import FedAvgAPI
     api = (SalientGradsAPI if a.algo == "salientgrads" else FedAvgAPI)(dataset, device, fl_args, trainer, logger, dist=ctx, agg_mode=a.agg)
     api.w_init = api.w_global.clone()
@@ -335,6 +339,7 @@ def run_ours(a):
             "impl": "ours", "engine": engine_name,
             "config": config_dict(a, shape, samples_per_round),
             "parallelism": "client-parallel x%d (one process per GPU)" % ctx.world_size, "aggregation": api.aggregator.mode,
+            "client_lanes_per_gpu": len(trainer.all_lanes()),
             "value_staging": "resident (SlabTrainer.set_staging('resident'): store uploaded once before the timed region)",
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "mask_generation_s": mask_s, "agg_check": check,
             "global_test_acc": float(stat["global_test_acc"][-1]) if stat["global_test_acc"] else None,

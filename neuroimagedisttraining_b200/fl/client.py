@@ -81,7 +81,21 @@ class Client:
         """Local training starting from ``w_global``; the result stays in ``self.slab`` (device).
         Returns ``(slab, training_flops, num_comm_params)`` like the reference (``client.py:80-104``);
         ``num_comm_params`` is a device scalar (no host sync)."""
-        tr = self.model_trainer
+        gen = self.train_steps(w_global, round_idx, masks, **kw)
+        try:
+            while True:
+                next(gen)
+        except StopIteration as stop:
+            return stop.value
+
+    def train_steps(self, w_global: ParamSlab, round_idx: int, masks=None, trainer: Optional[SlabTrainer] = None, **kw):
+        """:meth:`train` as a generator yielding after every enqueued SGD step (see ``SlabTrainer.train_steps``); ``trainer``: the
+        lane to run on (default: the client's own trainer)."""
+        tr = trainer if trainer is not None else self.model_trainer
+        if hasattr(tr.engine, "step"):
+            # the dropout stream of the native engines is a counter: tie it to (round, client) so that the masks do not depend on
+            # how many steps OTHER clients ran on this engine before (sequential and concurrent schedules then agree bit for bit)
+            tr.engine.step = (((int(round_idx) + 2) * 1000003 + int(self.client_idx)) & 0xFFFFFFF) << 12
         comm_out = kw.pop("comm_out", None)        # int64 device accumulator: nnz(download) + nnz(upload) are added by the count kernels
         slab = self.ensure_slab(w_global)
         slab.copy_(w_global)
@@ -93,7 +107,7 @@ class Client:
             num_comm_params = comm_out
         else:
             num_comm_params = tr.count_communication_params(w_global)
-        tr.train(self.local_training_data, self.device, self.args, round_idx, masks, **kw)
+        yield from tr.train_steps(self.local_training_data, self.device, self.args, round_idx, masks, **kw)
         tr.engine.detach_sync()
         training_flops = self.args.epochs * self.local_sample_number
         if num_comm_params is comm_out and comm_out is not None:

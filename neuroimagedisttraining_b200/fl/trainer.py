@@ -108,6 +108,8 @@ class SlabTrainer(ModelTrainer):
         self.double_sigmoid_eval = True
         self.step_counter = 0
         self.pending_losses = []
+        self.lanes: list = []                  # sibling trainers (own engine, stagers, CUDA stream) for concurrent client slots
+        self.stream = None                     # None: whatever stream is current
 
     # ------------------------------------------------------------------ slab plumbing
     @property
@@ -125,8 +127,25 @@ class SlabTrainer(ModelTrainer):
             self._stagers[batch_size] = st
         return st
 
+    def add_lane(self, engine) -> "SlabTrainer":
+        """A second client slot on this GPU: a sibling trainer with its own engine (activation buffers), stagers and CUDA stream.
+        Orchestrators that see lanes train several clients at once, one per lane, interleaving their steps from one host thread
+        (``FedAvgAPI.run_round``): the small layers of one client (grids far below 148 CTAs) run in the shadow of the other's
+        large ones.  The reference trains its clients strictly one after another (``sailentgrads_api.py:126-138``)."""
+        lane = SlabTrainer(self.model, self.args, self.logger, device=self.device, store=self.store, engine=engine, clip_norm=self.clip_norm,
+                           staging=self.staging)
+        lane.double_sigmoid_eval = self.double_sigmoid_eval
+        lane.stream = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" else None
+        self.lanes.append(lane)
+        return lane
+
+    def all_lanes(self) -> list:
+        return [self] + self.lanes
+
     def set_staging(self, mode: str) -> None:
         """Switch the staging mode (``client`` | ``stream`` | ``resident``); existing device buffers are dropped."""
+        for lane in self.lanes:
+            lane.set_staging(mode)
         if mode != self.staging:
             if self.device.type == "cuda":
                 torch.cuda.synchronize(self.device)
@@ -137,7 +156,7 @@ class SlabTrainer(ModelTrainer):
     @property
     def h2d_bytes(self) -> int:
         """Bytes copied host -> device by this trainer's stagers so far."""
-        return sum(st.h2d_bytes for st in self._stagers.values())
+        return sum(st.h2d_bytes for st in self._stagers.values()) + sum(l.h2d_bytes for l in self.lanes)
 
     def _cached(self, data) -> bool:
         return (self.staging != "stream" and self.store is not None and hasattr(data, "indices")
@@ -346,6 +365,18 @@ class SlabTrainer(ModelTrainer):
         """``epochs`` of local SGD on the attached slab.  A fresh optimizer per call (momentum
         buffers reset), ``lr * lr_decay**round``, grad-clip 10, weight decay on every parameter and
         ``w *= mask`` after every step when ``snip_mask`` (``my_model_trainer.py:201-235``)."""
+        gen = self.train_steps(train_data, device, args, round_idx, masks, prox_ref, lamda, epochs, apply_mask, grad_mask, lookahead_data)
+        try:
+            while True:
+                next(gen)
+        except StopIteration as stop:
+            return stop.value
+
+    def train_steps(self, train_data, device=None, args=None, round_idx: int = 0, masks: MaskLike = None,
+                    prox_ref: Optional[ParamSlab] = None, lamda: float = 0.0, epochs: Optional[int] = None,
+                    apply_mask: Optional[bool] = None, grad_mask: bool = False, lookahead_data=None):
+        """:meth:`train` as a generator that yields after every SGD step has been enqueued, so that a caller can interleave the
+        steps of several clients running on several lanes (CUDA streams).  The generator's return value is :meth:`train`'s."""
         args = args if args is not None else self.args
         mslab = self.mask_slab(masks) if masks is not None else self.masks
         use_mask = bool(getattr(args, "snip_mask", True)) if apply_mask is None else apply_mask
@@ -378,6 +409,7 @@ class SlabTrainer(ModelTrainer):
                 ops.prox_pull(self.slab.params_flat, prox_ref.params_flat, hp.lr, lamda)
             first = False
             self.step_counter += 1
+            yield
         if n_epochs > 0:
             end_epoch(cur)
         self.pending_losses.extend(losses)
@@ -387,6 +419,12 @@ class SlabTrainer(ModelTrainer):
 
     def flush_losses(self):
         """Read the queued per-epoch losses (one host sync) and log them in the reference's format."""
+        for lane in self.lanes:              # their losses were enqueued on their own streams
+            if lane.pending_losses:
+                if lane.stream is not None:
+                    torch.cuda.current_stream(self.device).wait_stream(lane.stream)
+                self.pending_losses.extend(lane.pending_losses)
+                lane.pending_losses = []
         if not self.pending_losses:
             return []
         sums = torch.stack([(l.sum if isinstance(l, LazyMean) else l).detach().float().reshape(()) for _, _, l in self.pending_losses])

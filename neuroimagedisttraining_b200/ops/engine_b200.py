@@ -288,7 +288,9 @@ class B200Engine:
         p.off_fc1_w, p.off_fc1_b, p.off_fc2_w, p.off_fc2_b = off(h.fc1 + ".weight"), off(h.fc1 + ".bias"), off(h.fc2 + ".weight"), off(h.fc2 + ".bias")
         p.head_s, p.head_c, p.head_hidden, p.p_drop, p.input_scale = self.head_S, self.head_C, h.hidden, float(h.p_drop), self.input_scale
         p.eval_logits = self.eval_logits.data_ptr()
-        p.norm_scratch = _norm_scratch(self.device).data_ptr()
+        # own grad-norm partials: several engines (client lanes) may run on different streams at once
+        self._norm_scratch_t = torch.zeros(self.lib.nidt_norm_scratch_floats(), dtype=torch.float32, device=self.device)
+        p.norm_scratch = self._norm_scratch_t.data_ptr()
         return p
 
     def _native_ready(self) -> bool:
