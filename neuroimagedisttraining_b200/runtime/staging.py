@@ -35,7 +35,6 @@ class _Slot:
         self.cap = cap
         self.x = torch.empty((cap,) + tuple(shape), dtype=torch.uint8, device=device)
         self.y = torch.empty(cap, dtype=torch.float32, device=device)
-        self.pin_y = torch.empty(cap, dtype=torch.float32).pin_memory()
         self.pin_x = torch.empty((cap,) + tuple(shape), dtype=torch.uint8).pin_memory() if need_pin_x else None
         self.ready = torch.cuda.Event()
         self.consumed = torch.cuda.Event()
@@ -104,6 +103,9 @@ class BatchStager:
             lib.nidt_gather_rows_u8_args.argtypes = [vp, vp, vp, i32, i64, vp, vp, vp]
             lib.nidt_gather_rows_u8_args.restype = i32
             self._native = lib
+            # labels are copied straight out of ONE pinned array of all labels (row copies, like the volumes): no per-slot pinned
+            # bounce buffer that the host could overwrite while an earlier, still queued copy has yet to read it
+            self._pin_labels = torch.from_numpy(np.ascontiguousarray(store.labels, dtype=np.float32)).pin_memory()
             self._gx = [torch.empty((batch_size,) + tuple(store.shape), dtype=torch.uint8, device=self.device) for _ in range(2)]
             self._gy = [torch.empty(batch_size, dtype=torch.float32, device=self.device) for _ in range(2)]
             self._gk = 0
@@ -127,13 +129,25 @@ class BatchStager:
             self.h2d_copies += 1
         self.h2d_bytes += n * self._row_bytes
 
+    def _copy_labels(self, ids: np.ndarray, dst_y: torch.Tensor) -> None:
+        """Enqueue ``dst_y[j] = label ids[j]`` on the copy stream (the caller holds the stream context)."""
+        from ..ops import native
+        n = len(ids)
+        if n == 0:
+            return
+        rows = np.ascontiguousarray(ids, dtype=np.int64)
+        cnt = C.c_int(0)
+        native.check(self._native.nidt_copy_rows_h2d_counted(self._pin_labels.data_ptr(), rows.ctypes.data, n, 4, dst_y.data_ptr(),
+                                                             self.copy_stream.cuda_stream, C.byref(cnt)), "nidt_copy_rows_h2d(labels)")
+        self.h2d_bytes += 4 * n
+        self.h2d_copies += cnt.value
+
     # ------------------------------------------------------------------ stream mode (ring of batch buffers)
     def _ring_init(self) -> None:
         shp = (self.batch_size,) + tuple(self.store.shape)
         d = self.depth
         self.dev_x = [torch.empty(shp, dtype=torch.uint8, device=self.device) for _ in range(d)]
         self.dev_y = [torch.empty(self.batch_size, dtype=torch.float32, device=self.device) for _ in range(d)]
-        self.pin_y = [torch.empty(self.batch_size, dtype=torch.float32).pin_memory() for _ in range(d)]
         self.pin_x = [torch.empty(shp, dtype=torch.uint8).pin_memory() for _ in range(d)] if self._pinned_cache is None else [None] * d
         self.pin_idx = [torch.empty(self.batch_size, dtype=torch.int64).pin_memory() for _ in range(d)]
         self.ready = [torch.cuda.Event() for _ in range(d)]
@@ -151,6 +165,7 @@ class BatchStager:
             self.copy_stream.wait_event(self.consumed[slot])
             if self._pinned_cache is not None and self._kernel_blocks > 0:
                 # a few CTAs read the pinned host rows over PCIe themselves (no copy-engine traffic next to the compute kernels)
+                self.ready[slot].synchronize()             # the pinned index buffer is about to be overwritten by the host
                 self.pin_idx[slot][:b] = torch.from_numpy(np.ascontiguousarray(ids, dtype=np.int64))
                 native.check(self._native.nidt_gather_rows_u8_capped(self._pinned_cache.data_ptr(), self.pin_idx[slot].data_ptr(), self.dev_x[slot].data_ptr(),
                                                                      b, self._row_bytes, self._kernel_blocks, self.copy_stream.cuda_stream),
@@ -161,10 +176,8 @@ class BatchStager:
                 if self.pin_x[slot] is not None:
                     self.ready[slot].synchronize()         # the pinned bounce buffer is about to be overwritten by the host
                 self._copy_rows(ids, self.dev_x[slot], self.pin_x[slot])
-            self.pin_y[slot][:b] = torch.from_numpy(self.store.labels[ids])
-            self.dev_y[slot][:b].copy_(self.pin_y[slot][:b], non_blocking=True)
+            self._copy_labels(ids, self.dev_y[slot])
             self.ready[slot].record(self.copy_stream)
-        self.h2d_bytes += 4 * b
         return b
 
     def iterate(self, loader, lookahead=None) -> Iterator[Tuple[torch.Tensor, torch.Tensor]]:
@@ -291,11 +304,8 @@ class BatchStager:
                 if slot.pin_x is not None:
                     slot.ready.synchronize()
                 self._copy_rows(ent.rows, slot.x, slot.pin_x)
-                slot.pin_y[:n] = torch.from_numpy(self.store.labels[ent.rows])
-                slot.y[:n].copy_(slot.pin_y[:n], non_blocking=True)
+                self._copy_labels(ent.rows, slot.y)
                 slot.ready.record(self.copy_stream)
-            self.h2d_bytes += 4 * n
-            self.h2d_copies += 1
 
     def open(self, loaders, kind: str = "train") -> _Entry:
         """The entry holding ``loaders`` (one loader, or the exact group passed to ``want(group=True)``), uploaded or on its
