@@ -267,19 +267,35 @@ int nidt_plan_eval(const nidt_plan_t* plan, const void* x_u8, const float* y, in
 /* All ranks call these with the same arguments order; the kernels wait for each other through release/acquire flags.
  * partial_ptrs / result_ptrs / flag_ptrs: HOST arrays of `world` peer-mapped device pointers (identical order on every rank);
  * flag pads hold nidt_sym_flag_words() uint32, zero before the first call; `epoch` grows by 1 per call on every rank.
- * mc_*: NVLS multicast addresses of the same buffers (or null); use_multimem selects multimem.ld_reduce / multimem.st. */
+ * mc_*: NVLS multicast addresses of the same buffers (or null). */
 int nidt_sym_max_ranks(void);
 int nidt_sym_flag_words(void);
-/* W1: out = mask * sum_ranks partial.  reduce-scatter (P2P loads in rank order, or in-switch reduction) + SalientGrads mask +
- * all-gather (P2P / multicast stores) + write-back, one launch per rank.  ref: sailentgrads_api.py:212-227 (CPU dict loop). */
+int nidt_sym_max_local(void);          /* client slabs that can be weighted inside one nidt_sym_aggregate call */
+int nidt_sym_bulk_max_ranks(void);     /* ranks the shared-memory (bulk-async) data path supports */
+int nidt_sym_hist_words(void);         /* uint32 words of a W2 histogram-exchange pad */
+int nidt_sym_sal_scratch_bytes(void);  /* bytes of local scratch of W2 */
+/* W1: out = mask * sum_ranks sum_local wt*src.  Sample-count weighting of the rank's k_local client slabs (k_local == 0:
+ * partial_ptrs[rank] already holds the rank's contribution) + reduce-scatter + SalientGrads mask + all-gather (+ write-back when
+ * out_local is neither NULL nor result_ptrs[rank]), one launch per rank.  mode: 0 P2P loads/stores through registers, 1 NVLS
+ * multimem.ld_reduce / multimem.st, 2 P2P through shared memory with bulk-async copies; mm_frac_q8 (0..256): share of every
+ * chunk sent through the in-switch path next to the P2P path; ctas: grid size (0 = auto).
+ * ref: sailentgrads_api.py:212-227 (CPU dict loop). */
+int nidt_sym_aggregate(void* const* partial_ptrs, void* const* result_ptrs, void* const* flag_ptrs, void* mc_partial, void* mc_result,
+                       int rank, int world, const float* const* local_srcs, const float* local_wts, int k_local, const float* mask,
+                       int64_t n_mask, int64_t n, float* out_local, uint32_t epoch, int mode, int mm_frac_q8, int ctas, void* stream);
+/* the first interface of W1: partial already in place, P2P (registers) or multimem */
 int nidt_sym_reduce_mask_broadcast(void* const* partial_ptrs, void* const* result_ptrs, void* const* flag_ptrs, void* mc_partial,
                                    void* mc_result, int rank, int world, const float* mask, int64_t n_mask, int64_t n,
                                    float* out_local, uint32_t epoch, int use_multimem, void* stream);
-/* W2: cross-rank saliency all-reduce fused with the global top-k threshold and the mask emission.  ref: snip.py:80-140. */
+/* W2: cross-rank saliency reduce-scatter fused with the global top-k threshold and the mask emission: every rank histograms only
+ * its shard of the reduced scores, the 2048-bin histograms (3 radix passes) and shard sums are exchanged through hist_ptrs
+ * (peer-mapped pads of nidt_sym_hist_words() uint32), the mask is all-gathered into mask_ptrs (peer-mapped, n floats).  Uses a
+ * flag pad of its own (6 barriers per call).  scratch: nidt_sym_sal_scratch_bytes() bytes.  ref: snip.py:80-140. */
 int nidt_sym_saliency_topk_mask(void* const* partial_ptrs, void* const* result_ptrs, void* const* flag_ptrs, void* mc_partial,
-                                void* mc_result, int rank, int world, int64_t n, const unsigned char* flags, float* mask,
-                                unsigned long long k, void* scratch, float* scores_out, uint32_t epoch, int use_multimem,
-                                void* stream);
+                                void* mc_result, void* const* hist_ptrs, void* const* mask_ptrs, int rank, int world, int64_t n,
+                                const unsigned char* flags, float* mask, unsigned long long k, void* scratch, float* scores_out,
+                                uint32_t epoch, int use_multimem, void* stream);
+int nidt_sym_saliency_read_result(const void* scratch, float* threshold, float* norm, unsigned int* kept, void* stream);
 
 #ifdef __cplusplus
 }

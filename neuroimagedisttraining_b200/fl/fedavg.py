@@ -33,7 +33,7 @@ class FedAvgAPI(FedAPIBase):
             for k, lane in enumerate(tr.all_lanes()[:n_lanes] if n_lanes > 1 else [tr]):      # lane k trains clients mine[k::n_lanes]
                 lane.plan_data([self.client_list[c].local_training_data for c in mine[k::n_lanes]])
             if will_eval:
-                tr.plan_data(self.eval_loaders(), kind="eval", group=True)
+                tr.plan_eval(self.eval_loaders()) if hasattr(tr, "plan_eval") else tr.plan_data(self.eval_loaders(), kind="eval", group=True)
             if round_idx + 1 < int(getattr(args, "comm_round", 0)):
                 nxt_round = self.peek_client_sampling(round_idx + 1)
                 nxt_mine = self.local_clients(nxt_round)

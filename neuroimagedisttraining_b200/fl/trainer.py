@@ -8,6 +8,7 @@ but the state lives in device-resident :class:`ParamSlab` s instead of CPU state
 """
 from __future__ import annotations
 
+import contextlib
 from abc import ABC, abstractmethod
 from collections import OrderedDict
 from typing import Dict, Optional, Union
@@ -229,20 +230,24 @@ class SlabTrainer(ModelTrainer):
         n = len(loaders)
         return [flat[p * n:(p + 1) * n] for p in range(len(slab_sets))]
 
-    def test_jobs(self, jobs, group=None):
-        """Evaluate ``[(loader, slab), ...]`` in order; every distinct loader's volumes are uploaded once (one slot for the whole
-        group) however many jobs use it.  ``group``: the loader list announced with ``plan_data(..., group=True)`` (defaults to the
-        distinct loaders of ``jobs`` in order).  One device->host read returns all counters.  Returns one metrics dict per job."""
-        jobs = list(jobs)
-        if not jobs:
-            return []
-        loaders = list(group) if group is not None else list(dict((id(l), l) for l, _ in jobs).values())
-        if not all(self._cached(l) for l in loaders):
-            return self.test_many([(slab, loader) for loader, slab in jobs])
+    def _eval_split(self, loaders) -> list:
+        """Which lane evaluates which test loader: loader i of the group goes to lane i % L (all jobs of a loader run where its
+        volumes are staged)."""
+        L = len(self.all_lanes()) if len(loaders) > 1 else 1
+        return [loaders[k::L] for k in range(L)]
+
+    def plan_eval(self, loaders) -> None:
+        """Announce the round's evaluation group (see :meth:`plan_data`); with lanes, every lane stages its share."""
+        loaders = list(loaders)
+        for lane, ls in zip(self.all_lanes(), self._eval_split(loaders)):
+            lane.plan_data(ls, kind="eval", group=True)
+
+    def _test_jobs_steps(self, jobs, loaders, acc):
+        """Generator: evaluate ``jobs`` (loader, slab) on this trainer with ``loaders`` staged as one group, counters into ``acc``
+        rows; yields after every enqueued batch."""
         bs = max(l.batch_size for l in loaders)
         st = self._stager(bs)
         ent = st.open(loaders, kind="eval")
-        acc = torch.zeros((len(jobs), 3), dtype=torch.float64, device=self.device)
         try:
             for j, (loader, slab) in enumerate(jobs):
                 self.attach(slab)
@@ -250,10 +255,60 @@ class SlabTrainer(ModelTrainer):
                 for b in loader:
                     x, y = st.batch_from(ent, loader, b[0])
                     self.engine.eval_batch(x, y, c, double_sigmoid=self.double_sigmoid_eval)
+                    yield
         finally:
             st.close(ent)
-        host = xfer.to_host(acc).tolist()                      # ONE device->host read for all jobs' counters
-        return [EvalCounters.as_result(*row) for row in host]
+
+    def test_jobs(self, jobs, group=None):
+        """Evaluate ``[(loader, slab), ...]`` in order; every distinct loader's volumes are uploaded once (one slot for the whole
+        group) however many jobs use it.  ``group``: the loader list announced with ``plan_eval`` (defaults to the distinct loaders
+        of ``jobs`` in order).  With lanes the loaders (and their jobs) are spread over the lanes and run concurrently.  One
+        device->host read returns all counters.  Returns one metrics dict per job."""
+        jobs = list(jobs)
+        if not jobs:
+            return []
+        loaders = list(group) if group is not None else list(dict((id(l), l) for l, _ in jobs).values())
+        if not all(self._cached(l) for l in loaders):
+            return self.test_many([(slab, loader) for loader, slab in jobs])
+        lanes = self.all_lanes()
+        split = self._eval_split(loaders)
+        lane_of = {id(l): k for k, ls in enumerate(split) for l in ls}
+        per_lane = [[] for _ in split]
+        for j, (loader, slab) in enumerate(jobs):
+            per_lane[lane_of[id(loader)]].append((j, loader, slab))
+        main = torch.cuda.current_stream(self.device)
+        accs, gens = [], []
+        for k, items in enumerate(per_lane):
+            lane = lanes[k]
+            acc = torch.zeros((max(1, len(items)), 3), dtype=torch.float64, device=self.device)
+            accs.append(acc)
+            if lane.stream is not None:
+                lane.stream.wait_stream(main)
+            gens.append(lane._test_jobs_steps([(l, s) for _, l, s in items], split[k], acc) if items else None)
+        live = True
+        while live:
+            live = False
+            for k, g in enumerate(gens):
+                if g is None:
+                    continue
+                live = True
+                ctx = torch.cuda.stream(lanes[k].stream) if lanes[k].stream is not None else contextlib.nullcontext()
+                with ctx:
+                    try:
+                        next(g)
+                    except StopIteration:
+                        gens[k] = None
+        for lane in lanes[:len(split)]:
+            if lane.stream is not None:
+                main.wait_stream(lane.stream)
+        host = xfer.to_host(torch.cat(accs)).tolist()          # ONE device->host read for all jobs' counters
+        out = [None] * len(jobs)
+        row = 0
+        for k, items in enumerate(per_lane):
+            for n, (j, _, _) in enumerate(items):
+                out[j] = EvalCounters.as_result(*host[row + n])
+            row += max(1, len(items))
+        return out
 
     def test_many(self, jobs):
         """Evaluate ``[(slab, loader), ...]`` back to back as one staged stream (the copy of the next client's test
