@@ -47,7 +47,7 @@ def parse():
     p.add_argument("--agg", default="auto", choices=["auto", "fused", "nccl"])
     p.add_argument("--shape", default="121,145,121")
     p.add_argument("--skip-e2e", action="store_true")
-    p.add_argument("--lanes", type=int, default=int(os.environ.get("NIDT_LANES", "2")), help="concurrent client slots per GPU (engines on their own CUDA streams)")
+    p.add_argument("--lanes", type=int, default=int(os.environ.get("NIDT_LANES", "3")), help="concurrent client slots per GPU (engines on their own CUDA streams)")
     p.add_argument("--model", default="alexnet3d", choices=["alexnet3d", "resnet3d"],
                    help="resnet3d = BASELINE.json config 4 (use with --clients 84 --batch 8 --dense-ratio 0.1 --per-site 10; ours arm only)")
     p.add_argument("--algo", default="salientgrads", choices=["salientgrads", "fedavg"], help="fedavg = BASELINE.json config 2 (ours arm only)")

@@ -58,6 +58,8 @@ def add_common_args(p: argparse.ArgumentParser, *, model="3DCNN", dataset="ABCD"
     g.add_argument("--staging", default="auto", choices=["auto", "client", "stream", "resident"],
                    help="how volumes reach the GPU: client = each loader's volumes uploaded once per use, batches gathered on the device "
                         "(default on CUDA); stream = batch-by-batch copies; resident = whole store kept on the device")
+    g.add_argument("--client_lanes", type=int, default=3, help="native engines: clients of a rank trained concurrently, each on its own "
+                                                               "engine and CUDA stream (1 = strictly one after another, like the reference)")
     g.add_argument("--placement", default="lpt", choices=["lpt", "roundrobin"], help="client -> rank placement: by training-set size or client_idx %% world")
     g.add_argument("--balance_eval", type=int, default=0, help="1: spread the round's evaluation jobs over ranks by load (personal models are "
                                                                "copied to the evaluating rank)")
@@ -181,6 +183,11 @@ def setup(args, prefix: str, extra_identity: Optional[list] = None, loss_kind: O
             logger.info(f"native engine unavailable for {args.model}: {e}; using the PyTorch engine for forward/backward")
     trainer = SlabTrainer(model, args, logger, device=device, store=store, engine=engine, loss_kind=loss_kind)
     trainer.double_sigmoid_eval = not args.correct_eval_loss
+    if engine is not None and getattr(engine, "native", False) and not spatial:
+        # concurrent client slots: FedAvg / SalientGrads train (and evaluate) this many clients of a rank at once
+        from ..ops.engines import make_native_engine
+        for _ in range(max(0, int(args.client_lanes) - 1)):
+            trainer.add_lane(make_native_engine(model, device, max_batch=args.batch_size, input_scale=store.scale, seed=args.seed))
     args.metrics_path = os.path.join(args.log_dir, args.dataset, args.identity + ".jsonl")
     return ctx, device, logger, dataset, trainer
 
