@@ -65,7 +65,11 @@ class SyntheticABCD(VolumeStore):
     """
 
     def __init__(self, n_subjects: int = 420, shape=ABCD_SHAPE, n_sites: int = 21, seed: int = 0,
-                 pool: int = 8, pin: bool = False, materialize: bool = True, site_sizes: Optional[Sequence[int]] = None):
+                 pool: int = 8, pin: bool = False, materialize: bool = True, site_sizes: Optional[Sequence[int]] = None,
+                 label_noise: float = 0.0, signal_gain: float = 1.0):
+        """``label_noise``: probability that a subject's stored label is the opposite of the one its volume was generated from
+        (an irreducible error: no model can score above ``1 - label_noise`` on held-out subjects); ``signal_gain`` scales the
+        label-dependent regional contrast.  The defaults give the cleanly separable task of the throughput benchmarks."""
         rng = np.random.RandomState(seed)
         self.shape = tuple(shape)
         self.n_sites = n_sites
@@ -78,6 +82,8 @@ class SyntheticABCD(VolumeStore):
         self.sites = np.repeat(np.arange(n_sites), sizes).astype(np.int64)
         n = len(self.sites)
         self.labels = (rng.rand(n) < 0.5).astype(np.float32)
+        self._gen_labels = self.labels.copy()              # what the volumes are generated from
+        self._signal_gain = float(signal_gain)
         self._gain = (0.85 + 0.3 * rng.rand(n)).astype(np.float32)
         self._pool_id = rng.randint(0, pool, size=n)
         d, h, w_ = self.shape
@@ -92,13 +98,16 @@ class SyntheticABCD(VolumeStore):
             self._pool.append((brain * tex).astype(np.float32))
         # label signal: a regional contrast (one hemisphere-ish blob brighter for label 1)
         self._signal = (np.exp(-(((zz - 0.2) ** 2 + (yy + 0.1) ** 2 + (xx - 0.3) ** 2) / 0.08)) * brain).astype(np.float32)
+        if label_noise > 0:
+            flip = np.random.RandomState(seed + 7919).rand(n) < label_noise
+            self.labels = np.where(flip, 1.0 - self.labels, self.labels).astype(np.float32)
         self._cache = None
         self._pin = pin
         if materialize:
             self.materialize()
 
     def _make(self, i: int) -> np.ndarray:
-        v = self._pool[self._pool_id[i]] * self._gain[i] + (0.25 if self.labels[i] > 0.5 else -0.05) * self._signal
+        v = self._pool[self._pool_id[i]] * self._gain[i] + self._signal_gain * (0.25 if self._gen_labels[i] > 0.5 else -0.05) * self._signal
         return np.clip(v * 255.0, 0, 255).astype(np.uint8)
 
     def materialize(self) -> None:
