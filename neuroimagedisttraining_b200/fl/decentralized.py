@@ -86,8 +86,10 @@ class _PerClientModels(LocalAPI):
 
 
 class DPSGDAPI(_PerClientModels):
-    """Several ranks: every rank keeps all clients' models; a client's neighbour average and local training run on its owner, which
-    broadcasts the result at the end of the round (the neighbour draw is re-seeded per round and client, so ranks agree on it)."""
+    """Several ranks: a client's neighbour average and local training run on its owner (the neighbour draw is re-seeded per round
+    and client, so ranks agree on it).  On GPUs the owners keep their clients' models in a peer-mapped arena and the mixing kernel
+    pulls just the neighbours it needs over NVLink (:mod:`..parallel.neighbors`, W11); on CPU / gloo every rank keeps all models and
+    the owners broadcast theirs at the end of the round."""
     NAME = "dpsgd"
     MULTI_RANK = True
 
@@ -95,14 +97,30 @@ class DPSGDAPI(_PerClientModels):
         args = self.args
         models = self._init_models()
         n = args.client_num_in_total
-        last = [m.clone() for m in models]
         mixed = self.w_global.clone()
         topology = self._mixing_matrix(n)
+        # W11: on several GPUs the owners keep their clients' models in a peer-mapped arena and the mixing kernel pulls the
+        # neighbours it needs over NVLink; otherwise (one rank, CPU / gloo) every rank holds all models and owners broadcast
+        from ..parallel.neighbors import make_arena
+        arena = make_arena(self.dist, self.layout.total_numel, n, self.device) if getattr(args, "peer_arena", True) else None
+        self.arena = arena
+        last = [m.clone() for m in models] if arena is None else None
+        if arena is not None:
+            for cid in self.local_clients(range(n)):
+                arena.publish(cid, models[cid].flat, (self.start_round - 1) & 1)
+            arena.align()
+
+        def mix(out, ids, weights, round_idx):
+            if arena is not None:
+                arena.average(out.flat, [int(j) for j in ids], weights, (round_idx - 1) & 1)
+            else:
+                ops.weighted_aggregate(out.flat, [last[int(j)].flat for j in ids], weights)
         for round_idx in range(self.start_round, args.comm_round):
             t0 = time.time()
             self.logger.info("################Communication round : {}".format(round_idx))
-            for i in range(n):
-                last[i].copy_(models[i])
+            if arena is None:
+                for i in range(n):
+                    last[i].copy_(models[i])
             with self.timer.phase("train"):
                 for cid in self.local_clients(range(n)):
                     self.logger.info('@@@@@@@@@@@@@@@@ Training Client CM({}): {}'.format(round_idx, cid))
@@ -110,21 +128,27 @@ class DPSGDAPI(_PerClientModels):
                         row = topology[cid]
                         nei = np.nonzero(row)[0]
                         self.logger.info("client_indexes = " + str(nei))
-                        ops.weighted_aggregate(mixed.flat, [last[int(j)].flat for j in nei], [float(row[j]) for j in nei])
+                        mix(mixed, nei, [float(row[j]) for j in nei], round_idx)
                     else:
                         nei = choose_neighbors(getattr(args, "cs", "ring"), cid, n, args.client_num_per_round, seed=round_idx + cid)
                         if n != args.client_num_per_round:
                             nei = np.append(nei, cid)
                         nei = np.sort(nei)
                         self.logger.info("client_indexes = " + str(nei))
-                        self._mean_of([last[int(j)] for j in nei], mixed)      # neighbour averaging (K: _aggregate_func)
+                        mix(mixed, nei, [1.0 / len(nei)] * len(nei), round_idx)      # neighbour averaging (K: _aggregate_func)
                     _, flops, comm = self.client_list[cid].train(mixed, round_idx, None)
                     self.stat_info["sum_training_flops"] += flops
                     self._add_comm_params(comm)
-            if self.dist.is_distributed:
-                for cid in range(n):
-                    self.dist.broadcast(models[cid].flat, src=self.dist.owner(cid))
-            self._mean_of(models, self.w_global)                               # _avg_aggregate
+                    if arena is not None:
+                        arena.publish(cid, models[cid].flat, round_idx & 1)
+            if arena is not None:
+                arena.align()
+                arena.average(self.w_global.flat, list(range(n)), [1.0 / n] * n, round_idx & 1)      # _avg_aggregate, in client order
+            else:
+                if self.dist.is_distributed:
+                    for cid in range(n):
+                        self.dist.broadcast(models[cid].flat, src=self.dist.owner(cid))
+                self._mean_of(models, self.w_global)                           # _avg_aggregate
             self._test_global_and_personal(round_idx)
             if round_idx % 100 == 99:
                 self._finetune(round_idx)

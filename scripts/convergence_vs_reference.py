@@ -29,13 +29,27 @@ def run(rounds=10, clients=4, per_site=60, batch=16, dense_ratio=0.5, lr=0.01, l
     init = AlexNet3D_Dropout(num_classes=1).state_dict()
     # ---- the reference, verbatim (fp32, TF32 convolutions as torch defaults give it), batches in index order
     torch.backends.cudnn.deterministic = True
-    ref_api, ref_model, _ = ref_harness.build_reference_api("salientgrads", store, train, test, args, dev, shuffle=False,
+    class Grab(logging.Handler):          # the reference only LOGS its test losses ({'global_test_acc': .., 'global_test_loss': ..})
+        def __init__(self):
+            super().__init__()
+            self.rows = []
+
+        def emit(self, record):
+            if isinstance(record.msg, dict):
+                self.rows.append(dict(record.msg))
+    grab = Grab()
+    ref_logger = logging.getLogger("conv_ref")
+    ref_logger.setLevel(logging.INFO)
+    ref_logger.propagate = False
+    ref_logger.handlers = [grab]
+    ref_api, ref_model, _ = ref_harness.build_reference_api("salientgrads", store, train, test, args, dev, logger=ref_logger, shuffle=False,
                                                            model_state={k: v.clone() for k, v in init.items()}, p_drop=0.0)
     masks = []
     orig = ref_api.generate_global_mask_snip
     ref_api.generate_global_mask_snip = lambda: (masks.append(orig()), masks[-1])[1]
     ref_api.train()
-    ref = {"loss": [float(x) for x in ref_api.stat_info["global_test_loss"]], "acc": [float(x) for x in ref_api.stat_info["global_test_acc"]],
+    ref = {"loss": [float(r["global_test_loss"]) for r in grab.rows if "global_test_loss" in r],
+           "acc": [float(x) for x in ref_api.stat_info["global_test_acc"]],
            "person_acc": [float(x) for x in ref_api.stat_info["person_test_acc"]]}
     ref_mask = masks[0]
     # ---- this framework, native engine (bf16 activations, fp32 master weights)
