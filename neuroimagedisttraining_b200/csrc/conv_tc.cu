@@ -286,6 +286,219 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv3d_fprop_tc_kernel(
     }
 }
 
+
+// ------------------------------------------------------------------------------- fprop on CTA pairs (cta_group::2)
+// Two CTAs of a cluster (one TPC) work on two neighbouring M tiles with ONE weight tile between them: every tcgen05.mma is
+// M = 256 (128 positions from each CTA's shared memory) x N = 128, and each CTA stages only 64 of the 128 weight rows per
+// K block -- the tensor cores of both SMs read the halves out of both shared memories.  Per CTA and K block that is 24 KiB
+// instead of 32 KiB of L2 -> SM traffic and half the weight-operand reads per MMA (the operand-read bound of the 1-CTA
+// N = 128 shape, scripts/bench_native/mma_rate.cu).  CTA 0 of the pair issues the MMAs; both run producers and epilogues.
+// All TMA loads are plain loads of this GPU's activations / weights into the loading CTA's own shared memory (no multicast).
+struct Fprop2Cfg {
+    static constexpr int kBlockN = 128;
+    static constexpr int kStages = 6;
+    static constexpr int kBHalfBytes = 64 * 128;                 // 64 weight rows x 64 bf16
+    static constexpr int kStageBytes = kATileBytes + kBHalfBytes;
+    static constexpr int kStagingBytes = 2 * kATileBytes;
+    static constexpr int kTmemCols = 256;
+    static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 + 256 + 128 + 512;
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kConvThreads, 1) conv3d_fprop_tc2_kernel(
+    const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_y,
+    const ConvGeom g, const float* __restrict__ bias, float* __restrict__ stats_partials, int m_tiles, int total_items) {
+    using Cfg = Fprop2Cfg;
+    constexpr int BLOCK_N = Cfg::kBlockN;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    if ((tc::smem_u32(smem) & 1023u) != 0u) __trap();
+    uint8_t* stage_base = smem;
+    uint8_t* staging = smem + Cfg::kStages * Cfg::kStageBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(staging + Cfg::kStagingBytes);
+    uint64_t* full = bars;                       // [kStages]  (used in the pair's CTA 0)
+    uint64_t* empty = bars + Cfg::kStages;       // [kStages]
+    uint64_t* tmem_full = empty + Cfg::kStages;  // [2]
+    uint64_t* tmem_empty = tmem_full + 2;        // [2]        (used in the pair's CTA 0: one arrival per CTA)
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    uint8_t* row_valid = reinterpret_cast<uint8_t*>(tmem_ptr + 2);   // [128]
+
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+    const uint32_t rank = tc::cluster_ctarank();
+    const int pair = (int)(blockIdx.x >> 1), n_pairs = (int)(gridDim.x >> 1);
+    const int taps = g.k * g.k * g.k;
+    const int num_kb = taps * g.cin_blocks;
+
+    if (warp == 0 && lane == 0) {
+        tc::tma_prefetch_desc(&tm_x);
+        tc::tma_prefetch_desc(&tm_w);
+        tc::tma_prefetch_desc(&tm_y);
+        for (int i = 0; i < Cfg::kStages; ++i) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { tc::mbar_init(&tmem_full[i], 1); tc::mbar_init(&tmem_empty[i], 2); }
+        tc::mbar_fence_init();
+    }
+    if (warp == 1) tc::tmem_alloc_pair<Cfg::kTmemCols>(tmem_ptr);
+    tc::tc_fence_before();
+    tc::cluster_sync_all();          // barriers of both CTAs are initialised before anything arrives on them from the other CTA
+    tc::tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    // item = (pair of M tiles, N tile); this CTA's M tile is 2*pm + rank (clamped: an odd tile count leaves the last pair's
+    // second CTA a duplicate that is computed but not stored)
+    auto decode = [&](int item, int& n_tile, int& m_tile, bool& valid, int& w0, int& h0, int& d0, int& n0) {
+        n_tile = item % g.n_tiles;
+        int m = 2 * (item / g.n_tiles) + (int)rank;
+        valid = m < m_tiles;
+        if (!valid) m = m_tiles - 1;
+        m_tile = m;
+        w0 = (m % g.tw) * g.bw; m /= g.tw;
+        h0 = (m % g.th) * g.bh; m /= g.th;
+        d0 = (m % g.td) * g.bd; m /= g.td;
+        n0 = m * g.bn;
+    };
+
+    if (warp == 0) {
+        // ===== TMA producer (both CTAs): own A tile + own half of the weight tile; bytes are counted on CTA 0's full[s] =====
+        const bool leader = tc::elect_one();
+        uint32_t s = 0, ph = 0;
+        for (int item = pair; item < total_items; item += n_pairs) {
+            int n_tile, m_tile, w0, h0, d0, n0;
+            bool valid;
+            decode(item, n_tile, m_tile, valid, w0, h0, d0, n0);
+            const int x0 = w0 * g.stride - g.pad, y0 = h0 * g.stride - g.pad, z0 = d0 * g.stride - g.pad;
+            int kb = 0;
+            for (int kd = 0; kd < g.k; ++kd)
+                for (int kh = 0; kh < g.k; ++kh)
+                    for (int kw = 0; kw < g.k; ++kw)
+                        for (int cb = 0; cb < g.cin_blocks; ++cb, ++kb) {
+                            tc::mbar_wait(&empty[s], ph ^ 1);
+                            if (leader) {
+                                uint8_t* a_dst = stage_base + s * Cfg::kStageBytes;
+                                if (rank == 0) tc::mbar_expect_tx(&full[s], (uint32_t)(2 * (g.box_rows * 128 + Cfg::kBHalfBytes)));
+                                tc::tma_load_5d_pair(&tm_x, &full[s], a_dst, cb * 64, x0 + kw, y0 + kh, z0 + kd, n0);
+                                tc::tma_load_2d_pair(&tm_w, &full[s], a_dst + kATileBytes, kb * 64, n_tile * BLOCK_N + (int)rank * 64);
+                            }
+                            if (++s == (uint32_t)Cfg::kStages) { s = 0; ph ^= 1; }
+                        }
+        }
+    } else if (warp == 1 && rank == 0) {
+        // ===== MMA issuer (CTA 0 of the pair) =====
+        const bool leader = tc::elect_one();
+        constexpr uint32_t idesc = tc::make_idesc_bf16(256, BLOCK_N, 0, 0);
+        constexpr uint32_t kDescHi = tc::desc_hi_sw128(1024);
+        const uint32_t stage_lo = tc::desc_lo_sw128(tc::smem_u32(stage_base));
+        uint32_t s = 0, ph = 0, local = 0;
+        if (pair < total_items) {
+            tc::mbar_wait(&full[0], 0);
+            tc::tc_fence_after();
+        }
+        for (int item = pair; item < total_items; item += n_pairs, ++local) {
+            const int buf = local & 1;
+            tc::mbar_wait(&tmem_empty[buf], ((local >> 1) & 1) ^ 1);
+            tc::tc_fence_after();
+            const uint32_t d_tmem = tmem_base + buf * BLOCK_N;
+            const bool more = item + n_pairs < total_items;
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const uint32_t a_lo = stage_lo + s * (Cfg::kStageBytes >> 4);
+                const uint32_t b_lo = a_lo + (kATileBytes >> 4);
+                uint32_t s1 = s + 1, ph1 = ph;
+                if (s1 == (uint32_t)Cfg::kStages) { s1 = 0; ph1 ^= 1; }
+                if (leader) {
+                    tc::umma_bf16_lohi_pair(d_tmem, a_lo, b_lo, kDescHi, idesc, kb != 0);
+                    tc::umma_bf16_lohi_pair(d_tmem, a_lo + 2, b_lo + 2, kDescHi, idesc, 1);
+                }
+                if (kb + 1 < num_kb || more) {
+                    tc::mbar_wait(&full[s1], ph1);
+                    tc::tc_fence_after();
+                }
+                if (leader) {
+                    tc::umma_bf16_lohi_pair(d_tmem, a_lo + 4, b_lo + 4, kDescHi, idesc, 1);
+                    tc::umma_bf16_lohi_pair(d_tmem, a_lo + 6, b_lo + 6, kDescHi, idesc, 1);
+                    tc::umma_commit_pair(&empty[s]);                 // frees stage s in both CTAs
+                }
+                s = s1; ph = ph1;
+            }
+            if (leader) tc::umma_commit_pair(&tmem_full[buf]);       // both epilogues
+        }
+    } else if (warp >= 2) {
+        // ===== epilogue (both CTAs): this CTA's 128 rows of the pair's accumulator =====
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        const int et = threadIdx.x - 64;     // 0..127
+        const uint32_t tmem_empty0 = tc::map_to_cta(tmem_empty, 0);        // CTA 0's barriers (shared::cluster address)
+        uint32_t local = 0;
+        for (int item = pair; item < total_items; item += n_pairs, ++local) {
+            int n_tile, m_tile, w0, h0, d0, n0;
+            bool valid;
+            decode(item, n_tile, m_tile, valid, w0, h0, d0, n0);
+            const int buf = local & 1;
+            const uint32_t aph = (local >> 1) & 1;
+            if (et == 0) tc::tma_store_wait_read();
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            {
+                int r = row;
+                const int iw = r % g.bw; r /= g.bw;
+                const int ih = r % g.bh; r /= g.bh;
+                const int id = r % g.bd; r /= g.bd;
+                row_valid[row] = (row < g.box_rows && w0 + iw < g.Wo && h0 + ih < g.Ho && d0 + id < g.Do && n0 + r < g.N) ? 1 : 0;
+            }
+            tc::mbar_wait(&tmem_full[buf], aph);
+            tc::tc_fence_after();
+            const int co0 = n_tile * BLOCK_N;
+#pragma unroll 1
+            for (int c = 0; c < BLOCK_N; c += 16) {
+                float v[16];
+                tc::tmem_ld16(tmem_base + buf * BLOCK_N + c + ((uint32_t)(q * 32) << 16), v);
+                if (bias != nullptr) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] += (co0 + c + i < g.Cout) ? __ldg(bias + co0 + c + i) : 0.f;
+                }
+                uint4 o[2];
+                __nv_bfloat162* ob = reinterpret_cast<__nv_bfloat162*>(o);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) ob[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+                uint8_t* blk = staging + (c >> 6) * kATileBytes + row * 128;
+                const int ch0 = (c & 63) >> 3;
+                *reinterpret_cast<uint4*>(blk + (((ch0) ^ (row & 7)) << 4)) = o[0];
+                *reinterpret_cast<uint4*>(blk + (((ch0 + 1) ^ (row & 7)) << 4)) = o[1];
+            }
+            tc::tc_fence_before();
+            tc::fence_proxy_async_smem();
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (et == 0) {
+                tc::mbar_arrive_cluster(tmem_empty0 + (uint32_t)(buf * sizeof(uint64_t)));   // this CTA has drained its half of buffer `buf`
+                if (valid) {
+#pragma unroll
+                    for (int j = 0; j < BLOCK_N / 64; ++j)
+                        if (co0 + j * 64 < g.Cout) tc::tma_store_5d(&tm_y, staging + j * kATileBytes, co0 + j * 64, w0, h0, d0, n0);
+                }
+                tc::tma_store_commit();
+            }
+            if (stats_partials != nullptr && valid) {
+                const int ch = et;      // BLOCK_N == 128 == epilogue threads
+                float s1 = 0.f, s2 = 0.f;
+                if (co0 + ch < g.Cout) {
+                    const uint8_t* blk = staging + (ch >> 6) * kATileBytes;
+                    const int chunk = (ch & 63) >> 3, within = (ch & 7) * 2;
+                    for (int r = 0; r < g.box_rows; ++r) {
+                        if (!row_valid[r]) continue;
+                        const float x = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(blk + r * 128 + ((chunk ^ (r & 7)) << 4) + within));
+                        s1 += x;
+                        s2 = fmaf(x, x, s2);
+                    }
+                    stats_partials[((size_t)m_tile * 2 + 0) * g.Cout + co0 + ch] = s1;
+                    stats_partials[((size_t)m_tile * 2 + 1) * g.Cout + co0 + ch] = s2;
+                }
+            }
+        }
+        if (et == 0) tc::tma_store_wait_read();
+    }
+    tc::tc_fence_before();
+    tc::cluster_sync_all();          // neither CTA leaves (or frees TMEM) while the other may still touch its barriers / operands
+    if (warp == 1) {
+        tc::tc_fence_after();
+        tc::tmem_dealloc_pair<Cfg::kTmemCols>(tmem_base);
+    }
+}
+
 // ------------------------------------------------------------------------------- wgrad
 // Work item = (tap, co tile of 128, ci block of 64, K split).  D[co][ci] (128x64 fp32 in TMEM)
 // accumulates dY^T * X_shift over the positions of the split; both operands are MN-major
@@ -543,6 +756,19 @@ NIDT_API int nidt_conv3d_fprop_tc(const void* x, const void* w, const float* bia
     NIDT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     const int grid = total < sms ? total : sms;
     cudaStream_t s = (cudaStream_t)stream;
+    static const int use_pairs = [] { const char* e = getenv("NIDT_CONV_PAIRS"); return e ? atoi(e) : 1; }();
+    if (block_n == 128 && use_pairs && m_tiles >= 2) {
+        // CTA pairs: two M tiles share one weight tile through tcgen05.mma.cta_group::2 (cluster of 2 CTAs = one TPC)
+        CUtensorMap tw_half;
+        if (make_tmap_mat2d(&tw_half, w, Cout, (int64_t)k * k * k * Cin, 64)) return 1;
+        const int items = ((m_tiles + 1) / 2) * g.n_tiles;
+        int pairs = sms / 2;
+        if (pairs > items) pairs = items;
+        NIDT_CUDA_CHECK(cudaFuncSetAttribute(conv3d_fprop_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Fprop2Cfg::kSmemBytes));
+        conv3d_fprop_tc2_kernel<<<2 * pairs, kConvThreads, Fprop2Cfg::kSmemBytes, s>>>(tx, tw_half, ty, g, bias, stats_partials, m_tiles, items);
+        NIDT_LAUNCH_CHECK();
+        return 0;
+    }
     if (block_n == 128) {
         NIDT_CUDA_CHECK(cudaFuncSetAttribute(conv3d_fprop_tc_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, FpropCfg<128>::kSmemBytes));
         conv3d_fprop_tc_kernel<128><<<grid, kConvThreads, FpropCfg<128>::kSmemBytes, s>>>(tx, tw_, ty, g, bias, stats_partials, total);
