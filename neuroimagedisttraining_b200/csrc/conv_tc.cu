@@ -75,6 +75,70 @@ struct ConvGeom {
 constexpr int kConvThreads = 192;
 constexpr int kATileBytes = 128 * 128;   // 128 rows x 64 bf16
 
+// ---- epilogue helpers shared by the fprop kernels -------------------------------------------------------------------------
+constexpr int kStatsRedBytes = 8 * 128 * 2 * 4;     // per-row-group partial (sum, sum^2) of every channel of a tile
+
+// TMEM accumulator (this thread's row, BLOCK_N fp32 columns) + bias -> bf16 -> the SWIZZLE_128B staging tile of the TMA store
+template <int BLOCK_N>
+__device__ __forceinline__ void drain_tile(uint32_t tmem_addr, const float* __restrict__ bias_s, uint8_t* __restrict__ staging, int row) {
+#pragma unroll 1
+    for (int c = 0; c < BLOCK_N; c += 16) {
+        float v[16];
+        tc::tmem_ld16(tmem_addr + c, v);
+        if (bias_s != nullptr) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] += bias_s[c + i];
+        }
+        uint4 o[2];
+        __nv_bfloat162* ob = reinterpret_cast<__nv_bfloat162*>(o);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) ob[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+        uint8_t* blk = staging + (c >> 6) * kATileBytes + row * 128;
+        const int ch0 = (c & 63) >> 3;
+        *reinterpret_cast<uint4*>(blk + (((ch0) ^ (row & 7)) << 4)) = o[0];
+        *reinterpret_cast<uint4*>(blk + (((ch0 + 1) ^ (row & 7)) << 4)) = o[1];
+    }
+}
+
+// Per-channel (sum, sum^2) over the valid rows of the staged bf16 tile.  Thread `et` of the 128 epilogue threads reads 16-byte
+// chunks (8 channels of one row): chunk column et % (BLOCK_N/8), rows et / (BLOCK_N/8) + RG*j -- 16 vector loads per thread
+// instead of 128 scalar ones -- the row groups are then added up through shared memory (`red`, kStatsRedBytes) in a fixed order.
+// Ends with the result of channel `et` (< BLOCK_N) in (s1, s2).  Uses named barrier 1 (128 threads).
+template <int BLOCK_N>
+__device__ __forceinline__ void tile_stats(const uint8_t* __restrict__ staging, const uint8_t* __restrict__ row_valid, int box_rows,
+                                           float* __restrict__ red, int et, float& s1, float& s2) {
+    constexpr int kChunks = BLOCK_N / 8;          // 16-byte chunks per row
+    constexpr int kRG = 128 / kChunks;            // row groups
+    const int cc = et % kChunks, rg = et / kChunks;
+    float a1[8], a2[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { a1[i] = 0.f; a2[i] = 0.f; }
+    const uint8_t* blk = staging + (cc >> 3) * kATileBytes;
+    const int ch0 = cc & 7;
+    for (int r = rg; r < box_rows; r += kRG) {
+        if (!row_valid[r]) continue;
+        const uint4 u = *reinterpret_cast<const uint4*>(blk + r * 128 + ((ch0 ^ (r & 7)) << 4));
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float2 f = __bfloat1622float2(h[i]);
+            a1[2 * i] += f.x; a2[2 * i] = fmaf(f.x, f.x, a2[2 * i]);
+            a1[2 * i + 1] += f.y; a2[2 * i + 1] = fmaf(f.y, f.y, a2[2 * i + 1]);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        red[(rg * BLOCK_N + cc * 8 + i) * 2 + 0] = a1[i];
+        red[(rg * BLOCK_N + cc * 8 + i) * 2 + 1] = a2[i];
+    }
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    s1 = 0.f; s2 = 0.f;
+    if (et < BLOCK_N) {
+#pragma unroll
+        for (int g = 0; g < kRG; ++g) { s1 += red[(g * BLOCK_N + et) * 2 + 0]; s2 += red[(g * BLOCK_N + et) * 2 + 1]; }
+    }
+}
+
 template <int BLOCK_N>
 struct FpropCfg {
     static constexpr int kStages = BLOCK_N == 128 ? 5 : 6;
@@ -82,7 +146,8 @@ struct FpropCfg {
     static constexpr int kStageBytes = kATileBytes + kBTileBytes;
     static constexpr int kStagingBytes = (BLOCK_N / 64) * kATileBytes;
     static constexpr int kTmemCols = 2 * BLOCK_N;   // double-buffered accumulator (power of two: 128 / 256)
-    static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers, flags*/ + 128 + 512 /*stats halves*/;
+    static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers, flags*/ + 128 + 512 /*bias*/ +
+                                      kStatsRedBytes;
 };
 
 template <int BLOCK_N>
@@ -101,7 +166,8 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv3d_fprop_tc_kernel(
     uint64_t* tmem_empty = tmem_full + 2;        // [2]
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
     uint8_t* row_valid = reinterpret_cast<uint8_t*>(tmem_ptr + 2);   // [128]
-    float* stat_red = reinterpret_cast<float*>(row_valid + 128);      // [2][64]: second half of the rows when BLOCK_N == 64
+    float* bias_s = reinterpret_cast<float*>(row_valid + 128);        // [128]: bias of this tile's channels
+    float* stat_red = bias_s + 128;                                    // kStatsRedBytes
 
     // shuffled warp index = provably warp-uniform: the producer / MMA schedules then live in uniform registers and UTMALDG /
     // UTCHMMA are issued without a per-instruction lane-election loop (the whole warp walks the schedule, one lane issues)
@@ -210,6 +276,8 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv3d_fprop_tc_kernel(
             const uint32_t aph = (local >> 1) & 1;
             // the previous tile's TMA store must have finished reading the staging buffer
             if (et == 0) tc::tma_store_wait_read();
+            const int co0 = n_tile * BLOCK_N;
+            if (bias != nullptr && et < BLOCK_N) bias_s[et] = (co0 + et < g.Cout) ? __ldg(bias + co0 + et) : 0.f;
             asm volatile("bar.sync 1, 128;" ::: "memory");
             {
                 int r = row;
@@ -220,24 +288,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv3d_fprop_tc_kernel(
             }
             tc::mbar_wait(&tmem_full[buf], aph);
             tc::tc_fence_after();
-            const int co0 = n_tile * BLOCK_N;
-#pragma unroll 1
-            for (int c = 0; c < BLOCK_N; c += 16) {
-                float v[16];
-                tc::tmem_ld16(tmem_base + buf * BLOCK_N + c + ((uint32_t)(q * 32) << 16), v);
-                if (bias != nullptr) {
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] += (co0 + c + i < g.Cout) ? __ldg(bias + co0 + c + i) : 0.f;
-                }
-                uint4 o[2];
-                __nv_bfloat162* ob = reinterpret_cast<__nv_bfloat162*>(o);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) ob[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
-                uint8_t* blk = staging + (c >> 6) * kATileBytes + row * 128;
-                const int ch0 = (c & 63) >> 3;
-                *reinterpret_cast<uint4*>(blk + (((ch0) ^ (row & 7)) << 4)) = o[0];
-                *reinterpret_cast<uint4*>(blk + (((ch0 + 1) ^ (row & 7)) << 4)) = o[1];
-            }
+            drain_tile<BLOCK_N>(tmem_base + buf * BLOCK_N + ((uint32_t)(q * 32) << 16), bias != nullptr ? bias_s : nullptr, staging, row);
             tc::tc_fence_before();
             tc::mbar_arrive(&tmem_empty[buf]);
             tc::fence_proxy_async_smem();
@@ -249,30 +300,13 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv3d_fprop_tc_kernel(
                 tc::tma_store_commit();
             }
             if (stats_partials != nullptr) {
-                // per-channel (sum, sum^2) over the valid rows of this tile, from the bf16 values just staged; with 64 channels the
-                // 128 threads split the rows in two halves (this loop sits on the critical path of short K loops)
-                constexpr int kParts = 128 / BLOCK_N;
-                const int ch = et % BLOCK_N, part = et / BLOCK_N;
-                float s1 = 0.f, s2 = 0.f;
-                if (co0 + ch < g.Cout) {
-                    const uint8_t* blk = staging + (ch >> 6) * kATileBytes;
-                    const int chunk = (ch & 63) >> 3, within = (ch & 7) * 2;
-                    for (int r = part; r < g.box_rows; r += kParts) {
-                        if (!row_valid[r]) continue;
-                        const float x = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(blk + r * 128 + ((chunk ^ (r & 7)) << 4) + within));
-                        s1 += x;
-                        s2 = fmaf(x, x, s2);
-                    }
-                }
-                if (kParts == 2) {
-                    if (part == 1) { stat_red[ch] = s1; stat_red[64 + ch] = s2; }
-                    asm volatile("bar.sync 1, 128;" ::: "memory");
-                    if (part == 0) { s1 += stat_red[ch]; s2 += stat_red[64 + ch]; }
-                }
-                if (part == 0 && co0 + ch < g.Cout) {
+                // per-channel (sum, sum^2) over the valid rows of this tile, from the bf16 values just staged
+                float s1, s2;
+                tile_stats<BLOCK_N>(staging, row_valid, g.box_rows, stat_red, et, s1, s2);
+                if (et < BLOCK_N && co0 + et < g.Cout) {
                     const int m_tile = tile / g.n_tiles;
-                    stats_partials[((size_t)m_tile * 2 + 0) * g.Cout + co0 + ch] = s1;
-                    stats_partials[((size_t)m_tile * 2 + 1) * g.Cout + co0 + ch] = s2;
+                    stats_partials[((size_t)m_tile * 2 + 0) * g.Cout + co0 + et] = s1;
+                    stats_partials[((size_t)m_tile * 2 + 1) * g.Cout + co0 + et] = s2;
                 }
             }
         }
@@ -301,7 +335,7 @@ struct Fprop2Cfg {
     static constexpr int kStageBytes = kATileBytes + kBHalfBytes;
     static constexpr int kStagingBytes = 2 * kATileBytes;
     static constexpr int kTmemCols = 256;
-    static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 + 256 + 128 + 512;
+    static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 + 256 + 128 + 512 + kStatsRedBytes;
 };
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kConvThreads, 1) conv3d_fprop_tc2_kernel(
@@ -320,6 +354,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kConvThreads, 1) con
     uint64_t* tmem_empty = tmem_full + 2;        // [2]        (used in the pair's CTA 0: one arrival per CTA)
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
     uint8_t* row_valid = reinterpret_cast<uint8_t*>(tmem_ptr + 2);   // [128]
+    float* bias_s = reinterpret_cast<float*>(row_valid + 128);        // [128]
+    float* stat_red = bias_s + 128;                                    // kStatsRedBytes
 
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const uint32_t rank = tc::cluster_ctarank();
@@ -432,6 +468,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kConvThreads, 1) con
             const int buf = local & 1;
             const uint32_t aph = (local >> 1) & 1;
             if (et == 0) tc::tma_store_wait_read();
+            const int co0 = n_tile * BLOCK_N;
+            if (bias != nullptr) bias_s[et] = (co0 + et < g.Cout) ? __ldg(bias + co0 + et) : 0.f;
             asm volatile("bar.sync 1, 128;" ::: "memory");
             {
                 int r = row;
@@ -442,24 +480,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kConvThreads, 1) con
             }
             tc::mbar_wait(&tmem_full[buf], aph);
             tc::tc_fence_after();
-            const int co0 = n_tile * BLOCK_N;
-#pragma unroll 1
-            for (int c = 0; c < BLOCK_N; c += 16) {
-                float v[16];
-                tc::tmem_ld16(tmem_base + buf * BLOCK_N + c + ((uint32_t)(q * 32) << 16), v);
-                if (bias != nullptr) {
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] += (co0 + c + i < g.Cout) ? __ldg(bias + co0 + c + i) : 0.f;
-                }
-                uint4 o[2];
-                __nv_bfloat162* ob = reinterpret_cast<__nv_bfloat162*>(o);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) ob[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
-                uint8_t* blk = staging + (c >> 6) * kATileBytes + row * 128;
-                const int ch0 = (c & 63) >> 3;
-                *reinterpret_cast<uint4*>(blk + (((ch0) ^ (row & 7)) << 4)) = o[0];
-                *reinterpret_cast<uint4*>(blk + (((ch0 + 1) ^ (row & 7)) << 4)) = o[1];
-            }
+            drain_tile<BLOCK_N>(tmem_base + buf * BLOCK_N + ((uint32_t)(q * 32) << 16), bias != nullptr ? bias_s : nullptr, staging, row);
             tc::tc_fence_before();
             tc::fence_proxy_async_smem();
             asm volatile("bar.sync 1, 128;" ::: "memory");
@@ -472,20 +493,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kConvThreads, 1) con
                 }
                 tc::tma_store_commit();
             }
-            if (stats_partials != nullptr && valid) {
-                const int ch = et;      // BLOCK_N == 128 == epilogue threads
-                float s1 = 0.f, s2 = 0.f;
-                if (co0 + ch < g.Cout) {
-                    const uint8_t* blk = staging + (ch >> 6) * kATileBytes;
-                    const int chunk = (ch & 63) >> 3, within = (ch & 7) * 2;
-                    for (int r = 0; r < g.box_rows; ++r) {
-                        if (!row_valid[r]) continue;
-                        const float x = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(blk + r * 128 + ((chunk ^ (r & 7)) << 4) + within));
-                        s1 += x;
-                        s2 = fmaf(x, x, s2);
-                    }
-                    stats_partials[((size_t)m_tile * 2 + 0) * g.Cout + co0 + ch] = s1;
-                    stats_partials[((size_t)m_tile * 2 + 1) * g.Cout + co0 + ch] = s2;
+            if (stats_partials != nullptr) {        // (uniform over the CTA: the barrier inside is reached by all 128 threads)
+                float s1, s2;
+                tile_stats<BLOCK_N>(staging, row_valid, g.box_rows, stat_red, et, s1, s2);
+                if (valid && co0 + et < g.Cout) {
+                    stats_partials[((size_t)m_tile * 2 + 0) * g.Cout + co0 + et] = s1;
+                    stats_partials[((size_t)m_tile * 2 + 1) * g.Cout + co0 + et] = s2;
                 }
             }
         }
