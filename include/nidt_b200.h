@@ -94,6 +94,13 @@ int nidt_mask_select_read_changed(const void* scratch, unsigned int* changed, vo
 /* ------------------------------------------------- BatchNorm3d + ReLU + MaxPool3d, fused (bn_pool.cu) */
 /* ref: fedml_api/model/cv/salient_models.py:147-168 (cuDNN BN, ATen ReLU/MaxPool3d there). */
 int nidt_bn_bwd_grid(void);
+/* pool 3/3 forward that also records the winning tap of every window (uint8, 255 = gated by ReLU), and the backward reductions
+ * alone (c12, dgamma, dbeta): the two halves the fused first-layer weight gradient (nidt_conv_in_s2d_wgrad_fused) needs */
+int nidt_bn_relu_pool3_fwd_amax(const void* y, void* a, void* ymax, void* amax, int N, int D, int H, int W, int C,
+                                const float* scale, const float* shift, int relu, void* stream);
+int nidt_bn_relu_pool3_bwd_stats(const void* ymax, const void* da, int N, int D, int H, int W, int C, const float* scale,
+                                 const float* shift, const float* mean, const float* invstd, float* partials, float* c12,
+                                 float* dgamma, float* dbeta, int relu, void* stream);
 int nidt_bn_finalize(const float* partials /*[T][2][C]*/, int T, int C, double count, const float* gamma, const float* beta,
                      float* running_mean, float* running_var, float* num_batches, float momentum, float eps, float* scale,
                      float* shift, float* mean, float* invstd, void* stream);
@@ -180,6 +187,14 @@ int nidt_conv_in_s2d_fprop(const void* x, const float* w, const float* bias, voi
 int nidt_conv_in_s2d_wgrad(const void* x, const void* dy, float* grad, float* grad_bias, float* scratch, int N, int Di, int Hi,
                            int Wi, float scale, void* stream);
 
+/* BatchNorm backward (batch statistics) + ReLU gate + MaxPool(3,3) scatter FUSED into the first layer's weight gradient: four extra
+ * warps turn every conv-output tile y into dY in shared memory (dY = cA*y + cB + [position won its window] * da*scale, `amax` from
+ * nidt_bn_relu_pool3_fwd_amax, c12 from nidt_bn_relu_pool3_bwd_stats), so dY (506 MB at batch 16) is neither written nor read
+ * back.  Result identical to nidt_bn_relu_pool_bwd + nidt_conv_in_s2d_wgrad.  ref: autograd of salient_models.py:147-150. */
+int nidt_conv_in_s2d_wgrad_fused(const void* x, const void* y, const void* amax, const void* da, const float* bn_scale,
+                                 const float* bn_mean, const float* bn_invstd, const float* c12, float* grad, float* grad_bias,
+                                 float* scratch, int N, int Di, int Hi, int Wi, float scale, const float* sal_w, float* sal_scores,
+                                 float sal_scale, void* stream);
 int nidt_conv_in_s2d_wgrad_saliency(const void* x, const void* dy, float* grad, float* grad_bias, float* scratch, int N, int Di, int Hi,
                                     int Wi, float scale, const float* w, float* scores, float sal_scale, void* stream);
 
@@ -216,6 +231,7 @@ typedef struct {
     float* wg_scratch;
     int stats_tiles, s2d, block_n, dgrad_block_n, splits;
     int box[4], dbox[4];                                  /* M-tile boxes (bw,bh,bd,bn) of fprop/wgrad and of dgrad at max_batch */
+    void* amax;                                           /* block 0, optional: winning pool taps (uint8) -> fused BN-backward + wgrad */
 } nidt_block_t;
 typedef struct {
     int n_blocks, max_batch;

@@ -329,10 +329,11 @@ __device__ __forceinline__ void ldv(const float* p, float* f) {
 template <int V>
 __global__ void __launch_bounds__(256) bn_relu_pool3_fwd_kernel(
     const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ a, __nv_bfloat16* __restrict__ ymax, BlockGeom g,
-    const float* __restrict__ scale, const float* __restrict__ shift, int relu) {
+    const float* __restrict__ scale, const float* __restrict__ shift, int relu, unsigned char* __restrict__ amax) {
     using VT = typename VecT<V>::T;
     const int CG = g.C / V;
     const int64_t total = (int64_t)g.N * g.Dp * g.Hp * g.Wp * CG;
+    unsigned char ab[V];
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     const int cg = (int)(idx % CG);
@@ -345,7 +346,7 @@ __global__ void __launch_bounds__(256) bn_relu_pool3_fwd_kernel(
     ldv<V>(scale + cg * V, sc);
     ldv<V>(shift + cg * V, sh);
 #pragma unroll
-    for (int i = 0; i < V; ++i) { best[i] = -INFINITY; yb[i] = 0.f; }
+    for (int i = 0; i < V; ++i) { best[i] = -INFINITY; yb[i] = 0.f; ab[i] = 0; }
     const __nv_bfloat16* base = y + ((((int64_t)n * g.D + dp * 3) * g.H + hp * 3) * g.W + wp * 3) * g.C + cg * V;
     const int64_t sH = (int64_t)g.W * g.C, sD = (int64_t)g.H * g.W * g.C;
 #pragma unroll
@@ -360,9 +361,19 @@ __global__ void __launch_bounds__(256) bn_relu_pool3_fwd_kernel(
 #pragma unroll
             for (int i = 0; i < V; ++i) {
                 const float pv = fmaf(f[i], sc[i], sh[i]);
-                if (pv > best[i]) { best[i] = pv; yb[i] = f[i]; }
+                if (pv > best[i]) { best[i] = pv; yb[i] = f[i]; ab[i] = (unsigned char)(kd * 9 + t); }
             }
         }
+    }
+    if (amax != nullptr) {
+        // tap (kd*9 + kh*3 + kw) of the FIRST maximum of every window, 255 when ReLU gates the window (nobody gets a gradient):
+        // lets the backward decide "am I the winner" per element without looking at its neighbours (fused wgrad of block 0)
+#pragma unroll
+        for (int i = 0; i < V; ++i)
+            if (relu && !(best[i] > 0.f)) ab[i] = 255;
+        unsigned char* dst = amax + idx * V;
+#pragma unroll
+        for (int i = 0; i < V; ++i) dst[i] = ab[i];
     }
     if (relu) {
 #pragma unroll
@@ -553,16 +564,30 @@ NIDT_API int nidt_bn_eval_prepare(int C, const float* gamma, const float* beta, 
     return 0;
 }
 
+static int bn_relu_pool_fwd_impl(const void* y, void* a, void* ymax, void* amax, int N, int D, int H, int W, int C, int pk, int ps,
+                                 const float* scale, const float* shift, int relu, void* stream);
 // ymax (bf16, pooled shape) is optional: when given with pool 3/3 the fast path runs and the backward can use it
 NIDT_API int nidt_bn_relu_pool_fwd(const void* y, void* a, void* ymax, int N, int D, int H, int W, int C, int pk, int ps,
                                    const float* scale, const float* shift, int relu, void* stream) {
+    return bn_relu_pool_fwd_impl(y, a, ymax, nullptr, N, D, H, W, C, pk, ps, scale, shift, relu, stream);
+}
+// the pool-3/3 fast path that also records, per pooled element, WHICH of the 27 window positions won (uint8 tap kd*9+kh*3+kw of the
+// first maximum, 255 = gated by ReLU): the input of the fused BatchNorm-backward + weight-gradient kernel of the first layer
+NIDT_API int nidt_bn_relu_pool3_fwd_amax(const void* y, void* a, void* ymax, void* amax, int N, int D, int H, int W, int C,
+                                         const float* scale, const float* shift, int relu, void* stream) {
+    NIDT_REQUIRE(ymax != nullptr && amax != nullptr, "nidt_bn_relu_pool3_fwd_amax: ymax / amax is null");
+    return bn_relu_pool_fwd_impl(y, a, ymax, amax, N, D, H, W, C, 3, 3, scale, shift, relu, stream);
+}
+static int bn_relu_pool_fwd_impl(const void* y, void* a, void* ymax, void* amax, int N, int D, int H, int W, int C, int pk, int ps,
+                                 const float* scale, const float* shift, int relu, void* stream) {
     NIDT_REQUIRE(C % 8 == 0, "nidt_bn_relu_pool_fwd: C=%d must be a multiple of 8", C);
     BlockGeom g = make_geom(N, D, H, W, C, pk, ps);
     const int64_t total = (int64_t)N * g.Dp * g.Hp * g.Wp * (C / 8);
     if (pk == 3 && ps == 3 && ymax != nullptr) {
         // 8 channels per thread measured faster than 4 for the forward (0.094 vs 0.110 ms on block 0 of AlexNet3D)
         bn_relu_pool3_fwd_kernel<8><<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)y, (__nv_bfloat16*)a,
-                                                                                                    (__nv_bfloat16*)ymax, g, scale, shift, relu);
+                                                                                                    (__nv_bfloat16*)ymax, g, scale, shift, relu,
+                                                                                                    (unsigned char*)amax);
         NIDT_LAUNCH_CHECK();
         return 0;
     }
@@ -574,10 +599,26 @@ NIDT_API int nidt_bn_relu_pool_fwd(const void* y, void* a, void* ymax, int N, in
     return 0;
 }
 
+static int bn_relu_pool_bwd_impl(const void* y, const void* ymax, const void* da, void* dy, int N, int D, int H, int W, int C, int pk, int ps,
+                                 const float* scale, const float* shift, const float* mean, const float* invstd,
+                                 float* partials, float* c12, float* dgamma, float* dbeta, int relu, int apply, void* stream);
 // partials: >= nidt_bn_bwd_grid()*2*C floats.  Sequence: reduce -> finalize -> apply.
 NIDT_API int nidt_bn_relu_pool_bwd(const void* y, const void* ymax, const void* da, void* dy, int N, int D, int H, int W, int C, int pk, int ps,
                                    const float* scale, const float* shift, const float* mean, const float* invstd,
                                    float* partials, float* c12, float* dgamma, float* dbeta, int relu, void* stream) {
+    return bn_relu_pool_bwd_impl(y, ymax, da, dy, N, D, H, W, C, pk, ps, scale, shift, mean, invstd, partials, c12, dgamma, dbeta, relu, 1, stream);
+}
+// pool 3/3 with ymax: only the reductions (c12 = the two BatchNorm-backward means, dgamma, dbeta) -- dY itself is then formed on the
+// fly by the consumer (nidt_conv_in_s2d_wgrad_fused) instead of being written to and read back from HBM
+NIDT_API int nidt_bn_relu_pool3_bwd_stats(const void* ymax, const void* da, int N, int D, int H, int W, int C, const float* scale,
+                                          const float* shift, const float* mean, const float* invstd, float* partials, float* c12,
+                                          float* dgamma, float* dbeta, int relu, void* stream) {
+    NIDT_REQUIRE(ymax != nullptr, "nidt_bn_relu_pool3_bwd_stats: ymax is null");
+    return bn_relu_pool_bwd_impl(nullptr, ymax, da, nullptr, N, D, H, W, C, 3, 3, scale, shift, mean, invstd, partials, c12, dgamma, dbeta, relu, 0, stream);
+}
+static int bn_relu_pool_bwd_impl(const void* y, const void* ymax, const void* da, void* dy, int N, int D, int H, int W, int C, int pk, int ps,
+                                 const float* scale, const float* shift, const float* mean, const float* invstd,
+                                 float* partials, float* c12, float* dgamma, float* dbeta, int relu, int apply, void* stream) {
     NIDT_REQUIRE(C % 8 == 0 && C <= 2048, "nidt_bn_relu_pool_bwd: unsupported C=%d", C);
     BlockGeom g = make_geom(N, D, H, W, C, pk, ps);
     const int CG = C / 8;
@@ -597,6 +638,7 @@ NIDT_API int nidt_bn_relu_pool_bwd(const void* y, const void* ymax, const void* 
         NIDT_LAUNCH_CHECK();
         bn_bwd_finalize_kernel<<<(C + 31) / 32, 256, 0, s>>>(partials, rgrid, C, count, c12, dgamma, dbeta);
         NIDT_LAUNCH_CHECK();
+        if (!apply) return 0;
         const int64_t total = (int64_t)N * ((D + 2) / 3) * ((H + 2) / 3) * ((W + 2) / 3) * (C / 4);
         bn_relu_pool3_bwd_apply_kernel<4><<<(unsigned)((total + 255) / 256), 256, 0, s>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)ymax,
                                                                                        (const __nv_bfloat16*)da, (__nv_bfloat16*)dy, g, scale, shift,

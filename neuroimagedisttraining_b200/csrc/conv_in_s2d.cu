@@ -387,8 +387,21 @@ __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __r
 // D_jw[L*8 + c][co] (jw = 0..2, three accumulators of 64 columns) += line_L[pos + jw][c] * dY[pos][co]
 // A = the s2d lines as an MN-major operand: M chunk = one line L = (jd, y' line) (stride 1 KiB), K = positions (16 B apart);
 // line chunk (jd, hl) is the tap (jd, jh = hl) because rows 64..127 of the K range run into the next line, exactly like fprop.
-__global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __restrict__ x, const __grid_constant__ CUtensorMap tm_dy,
-                                                            float* __restrict__ partials /* [grid][3][128][64] */, const Geom g) {
+// kFused: `tm_dy` maps the conv OUTPUT y instead of its gradient, and four more warps turn every y tile into the dY tile in place
+// in shared memory before the MMAs read it:  dY = cA*y + cB + (this position won its pooling window ? da*scale : 0)  -- the
+// BatchNorm backward (batch statistics) + ReLU gate + MaxPool(3,3) scatter of the first block, which otherwise costs a kernel of
+// its own that reads y and writes dY (2 x 506 MB per step at batch 16) for this kernel to read back.
+struct FusedBwd {
+    const unsigned char* amax;       // [N][Dp][Hp][Wp][64] winning tap of every pooling window (255 = gated by ReLU)
+    const __nv_bfloat16* da;         // [N][Dp][Hp][Wp][64] gradient of the block output
+    const float *scale, *mean, *invstd, *c12;      // BatchNorm forward scale = gamma*invstd, batch mean / invstd, backward means (c1 | c2)
+    int Dp, Hp, Wp;
+};
+constexpr int kFusedThreads = kThreads + 4 * 32;     // warps 13-16: y -> dY transform
+
+template <bool kFused>
+__global__ void __launch_bounds__(kFused ? kFusedThreads : kThreads, 1) wgrad_kernel(const uint8_t* __restrict__ x, const __grid_constant__ CUtensorMap tm_dy,
+                                                            float* __restrict__ partials /* [grid][3][128][64] */, const Geom g, const FusedBwd fb) {
     extern __shared__ __align__(1024) uint8_t smem[];
     if ((tc::smem_u32(smem) & 1023u) != 0u) __trap();
     uint8_t* dy_tiles = smem;                              // [kDyRing][128 pos][64 co] swizzled; K row = line*65 + w, the other rows stay zero
@@ -396,16 +409,26 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __res
     uint64_t* bars = reinterpret_cast<uint64_t*>(a_bufs + kARing * kWgABytes);
     uint64_t *a_full = bars, *a_empty = bars + kARing, *t_full = bars + 2 * kARing, *dy_full = t_full + 1, *dy_empty = dy_full + kDyRing;
     uint64_t *raw_full = dy_empty + kDyRing, *raw_empty = raw_full + kRawRing;
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(raw_empty + kRawRing);
-    uint8_t* raws = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(tmem_ptr + 4) + 15) & ~(uintptr_t)15);   // 16-byte vector stores
+    uint64_t* dy_ready = raw_empty + kRawRing;             // [kDyRing] fused: the transform warps have turned the y tile into dY
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(dy_ready + kDyRing);
+    float* bnc = reinterpret_cast<float*>(tmem_ptr + 4);   // [3][64] fused: cA, cB, scale per channel
+    uint8_t* raws = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(bnc + 192) + 15) & ~(uintptr_t)15);   // 16-byte vector stores
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // warp-uniform for the compiler: no per-MMA lane-election loops
 
-    for (int i = threadIdx.x; i < (kDyRing * kT16 + kARing * kWgABytes) / 16; i += kThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = threadIdx.x; i < (kDyRing * kT16 + kARing * kWgABytes) / 16; i += blockDim.x) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+    if (kFused && threadIdx.x < 64) {
+        // dy = scale*dyhat + A*y + B   with  A = -scale*invstd*c2,  B = scale*(mean*invstd*c2 - c1)   (same arithmetic as bn_pool.cu)
+        const int c = threadIdx.x;
+        const float sc = fb.scale[c], is = fb.invstd[c], mu = fb.mean[c], k1 = fb.c12[c], k2 = fb.c12[64 + c];
+        bnc[c] = -sc * is * k2;
+        bnc[64 + c] = sc * (mu * is * k2 - k1);
+        bnc[128 + c] = sc;
+    }
     tc::fence_proxy_async_smem();
     if (threadIdx.x == 0) {
         tc::tma_prefetch_desc(&tm_dy);
         for (int i = 0; i < kARing; ++i) { tc::mbar_init(&a_full[i], 4); tc::mbar_init(&a_empty[i], 1); }
-        for (int i = 0; i < kDyRing; ++i) { tc::mbar_init(&dy_full[i], 1); tc::mbar_init(&dy_empty[i], 1); }
+        for (int i = 0; i < kDyRing; ++i) { tc::mbar_init(&dy_full[i], 1); tc::mbar_init(&dy_empty[i], 1); tc::mbar_init(&dy_ready[i], 4); }
         for (int i = 0; i < kRawRing; ++i) { tc::mbar_init(&raw_full[i], 1); tc::mbar_init(&raw_empty[i], 4); }
         tc::mbar_init(t_full, 1);
         tc::mbar_fence_init();
@@ -430,9 +453,10 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __res
             const uint32_t a_lo_base = tc::desc_lo_sw128(tc::smem_u32(a_bufs), 128);
             const uint32_t b_lo_base = tc::desc_lo_sw128(tc::smem_u32(dy_tiles), kT16);
             const bool any = (int)blockIdx.x < g.total_tiles;
+            uint64_t* dy_go = kFused ? dy_ready : dy_full;     // what the MMAs wait for: the transformed tile, or the TMA load itself
             if (any) {
                 tc::mbar_wait(&a_full[0], 0);
-                tc::mbar_wait(&dy_full[0], 0);
+                tc::mbar_wait(&dy_go[0], 0);
                 tc::tc_fence_after();
             }
             int i = 0;
@@ -454,7 +478,7 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __res
                 if (tile + (int)gridDim.x < g.total_tiles) {   // next tile's operands, checked in the middle of this tile's MMAs
                     const int i1 = i + 1;
                     tc::mbar_wait(&a_full[i1 % kARing], (i1 / kARing) & 1);
-                    tc::mbar_wait(&dy_full[i1 % kDyRing], (i1 / kDyRing) & 1);
+                    tc::mbar_wait(&dy_go[i1 % kDyRing], (i1 / kDyRing) & 1);
                     tc::tc_fence_after();
                 }
                 if (leader) {
@@ -468,6 +492,61 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const uint8_t* __res
                 }
             }
             if (leader) tc::umma_commit(t_full);
+        }
+    } else if (kFused && warp >= 13) {
+        // ===== y -> dY in place (128 threads): thread = one 16-byte chunk column (8 channels) x every 16th row of the tile =====
+        const int tt = threadIdx.x - 13 * 32;
+        const int cc = tt & 7, r0 = tt >> 3;
+        float cA[8], cB[8], sc8[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { cA[i] = bnc[cc * 8 + i]; cB[i] = bnc[64 + cc * 8 + i]; sc8[i] = bnc[128 + cc * 8 + i]; }
+        TileIter t(g, blockIdx.x, gridDim.x);
+        for (int i = 0; t.valid(g); ++i, t.next(g)) {
+            const int slot = i % kDyRing;
+            tc::mbar_wait(&dy_full[slot], (i / kDyRing) & 1);
+            uint8_t* tile = dy_tiles + slot * kT16;
+            const int n = t.n, d = t.d, h0 = t.h0();
+            const int dw = d / 3, tap_d = (d - dw * 3) * 9;
+            const bool d_ok = dw < fb.Dp;
+            for (int j = r0; j < 2 * g.Wo; j += 16) {
+                const int l = j >= g.Wo ? 1 : 0, w = j - l * g.Wo;
+                const int h = h0 + l;
+                if (h >= g.Ho) break;                    // a line past the volume: the load zero-filled it and its dY stays zero
+                const int row = l * kWgPitch + w;
+                uint4* p = reinterpret_cast<uint4*>(tile + row * 128 + ((cc ^ (row & 7)) << 4));
+                const uint4 u = *p;
+                const int hw = h / 3, ww = (w * 43) >> 7;      // w / 3 for w < 64
+                const unsigned tap = (unsigned)(tap_d + (h - hw * 3) * 3 + (w - ww * 3));
+                float dz[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) dz[q] = 0.f;
+                if (d_ok && hw < fb.Hp && ww < fb.Wp) {
+                    const int64_t po = ((((int64_t)n * fb.Dp + dw) * fb.Hp + hw) * fb.Wp + ww) * 64 + cc * 8;
+                    const uint2 am = *reinterpret_cast<const uint2*>(fb.amax + po);
+                    const uint4 dv = *reinterpret_cast<const uint4*>(fb.da + po);
+                    const __nv_bfloat162* dh = reinterpret_cast<const __nv_bfloat162*>(&dv);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const float2 f = __bfloat1622float2(dh[q]);
+                        const unsigned word = q < 2 ? am.x : am.y;
+                        const unsigned b0 = (word >> (16 * (q & 1))) & 255u, b1 = (word >> (16 * (q & 1) + 8)) & 255u;
+                        if (b0 == tap) dz[2 * q] = f.x * sc8[2 * q];
+                        if (b1 == tap) dz[2 * q + 1] = f.y * sc8[2 * q + 1];
+                    }
+                }
+                const __nv_bfloat162* yh = reinterpret_cast<const __nv_bfloat162*>(&u);
+                uint4 o;
+                __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float2 f = __bfloat1622float2(yh[q]);
+                    oh[q] = __floats2bfloat162_rn(fmaf(cA[2 * q], f.x, cB[2 * q]) + dz[2 * q], fmaf(cA[2 * q + 1], f.y, cB[2 * q + 1]) + dz[2 * q + 1]);
+                }
+                *p = o;
+            }
+            tc::fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(&dy_ready[slot]);
         }
     } else {
         if (warp == 9 && lane == 0) {
@@ -540,7 +619,7 @@ static int make_geom(Geom& g, int N, int Di, int Hi, int Wi, float scale) {
     return 0;
 }
 static size_t smem_fprop(const Geom& g) { return 2 * (size_t)kT16 + 36 * 1024 + kARing * (size_t)kABytes + 8 * (2 * kARing + 4 + 2 * kRawRing) + 16 + 256 + 2 * 16 * 2 * 64 * 4 + kRawRing * (size_t)kPlanes * g.raw_pitch + 64; }
-static size_t smem_wgrad(const Geom& g) { return kDyRing * (size_t)kT16 + kARing * (size_t)kWgABytes + 8 * (2 * kARing + 1 + 2 * kDyRing + 2 * kRawRing) + 32 + kRawRing * (size_t)kPlanes * g.raw_pitch + 64; }
+static size_t smem_wgrad(const Geom& g) { return kDyRing * (size_t)kT16 + kARing * (size_t)kWgABytes + 8 * (2 * kARing + 1 + 3 * kDyRing + 2 * kRawRing) + 32 + 768 + kRawRing * (size_t)kPlanes * g.raw_pitch + 64; }
 
 }  // namespace s2d
 }  // namespace nidt
@@ -573,7 +652,24 @@ NIDT_API int nidt_conv_in_s2d_fprop(const void* x, const float* w, const float* 
 
 // scratch: >= nidt_conv_in_s2d_wgrad_scratch_floats() floats
 static int s2d_wgrad_impl(const void* x, const void* dy, float* grad, float* grad_bias, float* scratch, int N, int Di, int Hi, int Wi,
-                          float scale, void* stream, const float* sal_w, float* sal_scores, float sal_scale);
+                          float scale, void* stream, const float* sal_w, float* sal_scores, float sal_scale, const s2d::FusedBwd* fb = nullptr);
+// BatchNorm-backward + ReLU gate + MaxPool(3,3) scatter fused into the weight gradient of the first layer: takes the conv OUTPUT y
+// (bf16 [N][Do][Ho][Wo][64]), the winning taps `amax` and the pooled gradient `da` instead of dY; scale / mean / invstd are the
+// BatchNorm forward's per-channel values, c12 the two backward means (nidt_bn_relu_pool3_bwd_stats).  sal_w / sal_scores may be
+// NULL (else the SNIP epilogue runs in the split reduction).  Same result as nidt_bn_relu_pool_bwd + nidt_conv_in_s2d_wgrad without
+// dY ever touching HBM.  ref: autograd of salient_models.py:147-150.
+NIDT_API int nidt_conv_in_s2d_wgrad_fused(const void* x, const void* y, const void* amax, const void* da, const float* bn_scale,
+                                          const float* bn_mean, const float* bn_invstd, const float* c12, float* grad, float* grad_bias,
+                                          float* scratch, int N, int Di, int Hi, int Wi, float scale, const float* sal_w, float* sal_scores,
+                                          float sal_scale, void* stream) {
+    NIDT_REQUIRE(amax != nullptr && da != nullptr && bn_scale != nullptr && bn_mean != nullptr && bn_invstd != nullptr && c12 != nullptr,
+                 "conv_in_s2d_wgrad_fused: null argument");
+    s2d::FusedBwd fb;
+    fb.amax = (const unsigned char*)amax; fb.da = (const __nv_bfloat16*)da;
+    fb.scale = bn_scale; fb.mean = bn_mean; fb.invstd = bn_invstd; fb.c12 = c12;
+    fb.Dp = (((Di - 5) / 2 + 1) - 3) / 3 + 1; fb.Hp = (((Hi - 5) / 2 + 1) - 3) / 3 + 1; fb.Wp = (((Wi - 5) / 2 + 1) - 3) / 3 + 1;
+    return s2d_wgrad_impl(x, y, grad, grad_bias, scratch, N, Di, Hi, Wi, scale, stream, sal_w, sal_scores, sal_scale, &fb);
+}
 NIDT_API int nidt_conv_in_s2d_wgrad(const void* x, const void* dy, float* grad, float* grad_bias, float* scratch, int N, int Di, int Hi, int Wi,
                                     float scale, void* stream) {
     return s2d_wgrad_impl(x, dy, grad, grad_bias, scratch, N, Di, Hi, Wi, scale, stream, nullptr, nullptr, 0.f);
@@ -585,7 +681,7 @@ NIDT_API int nidt_conv_in_s2d_wgrad_saliency(const void* x, const void* dy, floa
     return s2d_wgrad_impl(x, dy, grad, grad_bias, scratch, N, Di, Hi, Wi, scale, stream, w, scores, sal_scale);
 }
 static int s2d_wgrad_impl(const void* x, const void* dy, float* grad, float* grad_bias, float* scratch, int N, int Di, int Hi, int Wi,
-                          float scale, void* stream, const float* sal_w, float* sal_scores, float sal_scale) {
+                          float scale, void* stream, const float* sal_w, float* sal_scores, float sal_scale, const s2d::FusedBwd* fb) {
     s2d::Geom g;
     if (s2d::make_geom(g, N, Di, Hi, Wi, scale)) return 2;
     CUtensorMap tdy;
@@ -594,8 +690,13 @@ static int s2d_wgrad_impl(const void* x, const void* dy, float* grad, float* gra
     NIDT_REQUIRE(smem <= 227 * 1024, "conv_in_s2d_wgrad: shared memory %zu B", smem);
     const int grid = g.total_tiles < kNumSMs ? g.total_tiles : kNumSMs;
     cudaStream_t s = (cudaStream_t)stream;
-    NIDT_CUDA_CHECK(cudaFuncSetAttribute(s2d::wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    s2d::wgrad_kernel<<<grid, s2d::kThreads, smem, s>>>((const uint8_t*)x, tdy, scratch, g);
+    if (fb != nullptr) {
+        NIDT_CUDA_CHECK(cudaFuncSetAttribute(s2d::wgrad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        s2d::wgrad_kernel<true><<<grid, s2d::kFusedThreads, smem, s>>>((const uint8_t*)x, tdy, scratch, g, *fb);
+    } else {
+        NIDT_CUDA_CHECK(cudaFuncSetAttribute(s2d::wgrad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        s2d::wgrad_kernel<false><<<grid, s2d::kThreads, smem, s>>>((const uint8_t*)x, tdy, scratch, g, s2d::FusedBwd{});
+    }
     NIDT_LAUNCH_CHECK();
     s2d::wgrad_reduce_kernel<<<(3 * 128 * 64 + 255) / 256, 256, 0, s>>>(scratch, grid, grad, grad_bias, sal_w, sal_scores, sal_scale);
     NIDT_LAUNCH_CHECK();

@@ -108,8 +108,11 @@ int forward(Ctx& c, const void* x, float* slab, bool train) {
         else
             NIDT_TRY(nidt_bn_eval_prepare(b.cout, at(slab, b.off_gamma), at(slab, b.off_beta), at(slab, b.off_rm), at(slab, b.off_rv), 1e-5f, b.scale,
                                           b.shift, c.st));
-        NIDT_TRY(nidt_bn_relu_pool_fwd(b.y, b.a, (train && b.ymax != nullptr) ? b.ymax : nullptr, B, b.c_d, b.c_h, b.c_w, b.cout, b.pool_k, b.pool_s,
-                                       b.scale, b.shift, b.relu, c.st));
+        if (train && i == 0 && b.amax != nullptr && b.ymax != nullptr && b.s2d && b.pool_k == 3 && b.pool_s == 3)
+            NIDT_TRY(nidt_bn_relu_pool3_fwd_amax(b.y, b.a, b.ymax, b.amax, B, b.c_d, b.c_h, b.c_w, b.cout, b.scale, b.shift, b.relu, c.st));
+        else
+            NIDT_TRY(nidt_bn_relu_pool_fwd(b.y, b.a, (train && b.ymax != nullptr) ? b.ymax : nullptr, B, b.c_d, b.c_h, b.c_w, b.cout, b.pool_k, b.pool_s,
+                                           b.scale, b.shift, b.relu, c.st));
         c.launches += 3;
         prev = b.a;
     }
@@ -141,6 +144,19 @@ int backward(Ctx& c, const void* x, float* grad) {
     const int B = c.B;
     for (int i = p->n_blocks - 1; i >= 0; --i) {
         const nidt_block_t& b = p->blocks[i];
+        if (i == 0 && b.amax != nullptr && b.ymax != nullptr && b.s2d && b.pool_k == 3 && b.pool_s == 3) {
+            // first block: only the BatchNorm-backward reductions run as kernels of their own; dY is formed inside the weight-gradient
+            // kernel from y, the winning taps and da (never written to HBM)
+            float* gb = b.has_bias ? at(grad, b.off_b) : nullptr;
+            NIDT_TRY(nidt_bn_relu_pool3_bwd_stats(b.ymax, b.da, B, b.c_d, b.c_h, b.c_w, b.cout, b.scale, b.shift, b.mean, b.invstd, b.bwd_partials,
+                                                  b.c12, at(grad, b.off_gamma), at(grad, b.off_beta), b.relu, c.st));
+            const bool sal = c.sal_scores != nullptr;
+            NIDT_TRY(nidt_conv_in_s2d_wgrad_fused(x, b.y, b.amax, b.da, b.scale, b.mean, b.invstd, b.c12, at(grad, b.off_w), gb, b.wg_scratch, B,
+                                                  b.in_d, b.in_h, b.in_w, p->input_scale, sal ? at(c.sal_w, b.off_w) : nullptr,
+                                                  sal ? at(c.sal_scores, b.off_w) : nullptr, c.sal_scale, c.st));
+            c.launches += 4;
+            continue;
+        }
         NIDT_TRY(nidt_bn_relu_pool_bwd(b.y, b.ymax, b.da, b.dy, B, b.c_d, b.c_h, b.c_w, b.cout, b.pool_k, b.pool_s, b.scale, b.shift, b.mean, b.invstd,
                                        b.bwd_partials, b.c12, at(grad, b.off_gamma), at(grad, b.off_beta), b.relu, c.st));
         c.launches += 3;

@@ -73,6 +73,12 @@ def _declare(lib) -> None:
     lib.nidt_plan_train_step_graph.restype = i32
     lib.nidt_plan_eval_graph.argtypes = [vp, vp, vp, i32, vp, vp, i32, vp, vp, vp]
     lib.nidt_plan_eval_graph.restype = i32
+    lib.nidt_bn_relu_pool3_fwd_amax.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, i32, vp]
+    lib.nidt_bn_relu_pool3_fwd_amax.restype = i32
+    lib.nidt_bn_relu_pool3_bwd_stats.argtypes = [vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, vp]
+    lib.nidt_bn_relu_pool3_bwd_stats.restype = i32
+    lib.nidt_conv_in_s2d_wgrad_fused.argtypes = [vp] * 11 + [i32, i32, i32, i32, f32, vp, vp, f32, vp]
+    lib.nidt_conv_in_s2d_wgrad_fused.restype = i32
     lib.nidt_plan_saliency_step.argtypes = [vp, vp, vp, i32, vp, vp, vp, f32, i64, u64, vp, vp]
     lib.nidt_plan_saliency_step.restype = i32
     lib.nidt_plan_graph_clear.argtypes = [vp]
@@ -108,7 +114,7 @@ class _BlockC(C.Structure):
                 + [(n, C.c_void_p) for n in ("y", "dy", "a", "da", "ymax", "scale", "shift", "mean", "invstd", "c12", "bwd_partials", "stats",
                                              "wf", "wd", "wg_scratch")]
                 + [(n, C.c_int) for n in ("stats_tiles", "s2d", "block_n", "dgrad_block_n", "splits")]
-                + [("box", C.c_int * 4), ("dbox", C.c_int * 4)])
+                + [("box", C.c_int * 4), ("dbox", C.c_int * 4), ("amax", C.c_void_p)])
 
 
 class _PlanC(C.Structure):
@@ -232,6 +238,9 @@ class B200Engine:
                 b.stats_tiles = lib.nidt_conv_in_grid()
                 iD, iH, iW = in_dhw
                 b.s2d = bool(lib.nidt_conv_in_s2d_supported(iD, iH, iW, spec.k, spec.stride, spec.pad)) and self.use_s2d
+                # winning pool taps for the fused BatchNorm-backward + weight-gradient kernel (NIDT_FUSED_BWD0=0: separate kernels)
+                b.amax = (torch.empty(b.a.shape, dtype=torch.uint8, device=dev)
+                          if (b.s2d and b.ymax is not None and spec.cout == 64 and os.environ.get("NIDT_FUSED_BWD0", "1") != "0") else None)
                 n_scr = max(lib.nidt_conv_in_grid() * 128 * 64, lib.nidt_conv_in_s2d_wgrad_scratch_floats())
                 b.wg_scratch = torch.zeros(n_scr, dtype=torch.float32, device=dev)
             else:
@@ -279,6 +288,7 @@ class B200Engine:
             c.stats_tiles = int(b.stats_tiles)
             if i == 0:
                 c.s2d = int(b.s2d and self.s2d_wgrad)
+                c.amax = ptr(getattr(b, "amax", None)) if (b.s2d and self.s2d_wgrad) else None
             else:
                 c.wf, c.wd = ptr(b.wf), ptr(b.wd)
                 c.block_n, c.dgrad_block_n, c.splits = b.block_n, b.dgrad_block_n, b.splits
@@ -393,8 +403,12 @@ class B200Engine:
                                                b.mean.data_ptr(), b.invstd.data_ptr(), st), "bn_finalize")
             else:
                 self._chk(lib.nidt_bn_eval_prepare(s.cout, g, be, rm, rv, 1e-5, b.scale.data_ptr(), b.shift.data_ptr(), st), "bn_eval_prepare")
-            self._chk(lib.nidt_bn_relu_pool_fwd(b.y.data_ptr(), b.a.data_ptr(), b.ymax.data_ptr() if (train and b.ymax is not None) else None, B, D, H, W, s.cout, s.pool_k, s.pool_s,
-                                                b.scale.data_ptr(), b.shift.data_ptr(), int(s.relu), st), "bn_relu_pool_fwd")
+            if train and i == 0 and getattr(b, "amax", None) is not None and self.s2d_wgrad:
+                self._chk(lib.nidt_bn_relu_pool3_fwd_amax(b.y.data_ptr(), b.a.data_ptr(), b.ymax.data_ptr(), b.amax.data_ptr(), B, D, H, W, s.cout,
+                                                          b.scale.data_ptr(), b.shift.data_ptr(), int(s.relu), st), "bn_relu_pool_fwd")
+            else:
+                self._chk(lib.nidt_bn_relu_pool_fwd(b.y.data_ptr(), b.a.data_ptr(), b.ymax.data_ptr() if (train and b.ymax is not None) else None, B, D, H, W, s.cout, s.pool_k, s.pool_s,
+                                                    b.scale.data_ptr(), b.shift.data_ptr(), int(s.relu), st), "bn_relu_pool_fwd")
             native.count_launches(2)
             prev = b.a
         return B
@@ -421,6 +435,20 @@ class B200Engine:
             s = b.spec
             self._tag = f"[{i}]"
             D, H, W = b.c_dhw
+            if i == 0 and getattr(b, "amax", None) is not None and b.s2d and self.s2d_wgrad:
+                # BatchNorm-backward reductions, then dY formed inside the weight-gradient kernel (never written to HBM)
+                iD, iH, iW = b.in_dhw
+                self._chk(lib.nidt_bn_relu_pool3_bwd_stats(b.ymax.data_ptr(), b.da.data_ptr(), B, D, H, W, s.cout, b.scale.data_ptr(), b.shift.data_ptr(),
+                                                           b.mean.data_ptr(), b.invstd.data_ptr(), b.bwd_partials.data_ptr(), b.c12.data_ptr(),
+                                                           self._p(self.grad, s.bn + ".weight"), self._p(self.grad, s.bn + ".bias"), int(s.relu), st),
+                          "bn_pool3_bwd_stats")
+                gb = self._p(self.grad, s.conv + ".bias") if s.bias else None
+                self._chk(lib.nidt_conv_in_s2d_wgrad_fused(self._x.data_ptr(), b.y.data_ptr(), b.amax.data_ptr(), b.da.data_ptr(), b.scale.data_ptr(),
+                                                           b.mean.data_ptr(), b.invstd.data_ptr(), b.c12.data_ptr(), self._p(self.grad, s.conv + ".weight"), gb,
+                                                           b.wg_scratch.data_ptr(), B, iD, iH, iW, self.input_scale, None, None, 0.0, st),
+                          "conv_in_s2d_wgrad_fused")
+                native.count_launches(4)
+                continue
             self._chk(lib.nidt_bn_relu_pool_bwd(b.y.data_ptr(), b.ymax.data_ptr() if b.ymax is not None else None, b.da.data_ptr(), b.dy.data_ptr(), B, D, H, W, s.cout, s.pool_k, s.pool_s,
                                                 b.scale.data_ptr(), b.shift.data_ptr(), b.mean.data_ptr(), b.invstd.data_ptr(),
                                                 b.bwd_partials.data_ptr(), b.c12.data_ptr(), self._p(self.grad, s.bn + ".weight"),

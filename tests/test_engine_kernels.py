@@ -354,3 +354,41 @@ def test_saliency_epilogue_scores_equal_the_separate_pass():
         a, b = scores[e.offset:e.offset + e.numel], ref[e.offset:e.offset + e.numel]
         assert float(b.abs().sum()) > 0
         assert torch.equal(a, b), f"{name}: max diff {(a - b).abs().max().item()}"
+
+
+def test_fused_block0_backward_equals_the_separate_kernels_bit_for_bit():
+    """The first block's backward with dY formed inside the weight-gradient kernel (BatchNorm backward + ReLU gate + MaxPool scatter
+    fused, winner known from the argmax taps recorded by the forward) against the separate apply + wgrad kernels: same arithmetic
+    per element, same MMA order, so gradients and updated weights must be identical -- at a full and at a partial batch."""
+    import os
+    from neuroimagedisttraining_b200.fl.engine import StepHParams
+    from neuroimagedisttraining_b200.models import AlexNet3D_Dropout
+    from neuroimagedisttraining_b200.ops.engine_b200 import B200Engine
+    g = torch.Generator().manual_seed(31)
+    x = torch.randint(0, 256, (4, 121, 145, 121), generator=g, dtype=torch.uint8).to(DEV)
+    y = (torch.rand(4, generator=g) > 0.5).float().to(DEV)
+    outs = {}
+    for fused in ("1", "0"):
+        os.environ["NIDT_FUSED_BWD0"] = fused
+        try:
+            torch.manual_seed(5)
+            model = AlexNet3D_Dropout(1, p_drop=0.0)
+            eng = B200Engine(model, DEV, max_batch=4)
+        finally:
+            os.environ.pop("NIDT_FUSED_BWD0", None)
+        assert (eng.blocks[0].amax is not None) == (fused == "1")
+        slab = eng.new_slab()
+        eng.attach(slab)
+        res = []
+        for native_exec in (True, False):                      # graph / native executor, and the Python launch loop
+            eng.native_exec = native_exec
+            eng.use_graphs = native_exec
+            for b in (4, 3):
+                eng.train_step(x[:b], y[:b], StepHParams(lr=0.01, wd=5e-4), None, None, True)
+                res.append(eng.grad.flat.clone())
+        res.append(slab.flat.clone())
+        torch.cuda.synchronize()
+        outs[fused] = res
+    for i, (a, b) in enumerate(zip(outs["1"], outs["0"])):
+        assert torch.isfinite(a).all()
+        assert torch.equal(a, b), f"output {i}: max diff {(a - b).abs().max().item()}"
