@@ -371,9 +371,15 @@ __global__ void __launch_bounds__(256) bn_relu_pool3_fwd_kernel(
 #pragma unroll
         for (int i = 0; i < V; ++i)
             if (relu && !(best[i] > 0.f)) ab[i] = 255;
-        unsigned char* dst = amax + idx * V;
+        // one V-byte store per thread (V = 8: uint2, V = 4: unsigned)
+        unsigned int w0 = 0u, w1 = 0u;
 #pragma unroll
-        for (int i = 0; i < V; ++i) dst[i] = ab[i];
+        for (int i = 0; i < V; ++i) {
+            if (i < 4) w0 |= (unsigned int)ab[i] << (8 * i);
+            else w1 |= (unsigned int)ab[i] << (8 * (i - 4));
+        }
+        if (V == 8) *reinterpret_cast<uint2*>(amax + idx * V) = make_uint2(w0, w1);
+        else *reinterpret_cast<unsigned int*>(amax + idx * V) = w0;
     }
     if (relu) {
 #pragma unroll

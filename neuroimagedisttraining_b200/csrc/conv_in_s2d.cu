@@ -494,55 +494,75 @@ __global__ void __launch_bounds__(kFused ? kFusedThreads : kThreads, 1) wgrad_ke
             if (leader) tc::umma_commit(t_full);
         }
     } else if (kFused && warp >= 13) {
-        // ===== y -> dY in place (128 threads): thread = one 16-byte chunk column (8 channels) x every 16th row of the tile =====
+        // ===== y -> dY in place (128 threads).  A thread owns one 16-byte chunk column (8 channels) and up to three W-triplets of the
+        // tile: the 3 positions of a triplet lie in ONE pooling window, so they share one (amax, da) load -- and those loads depend
+        // only on the tile's coordinates, so they are issued BEFORE waiting for the y tile (their latency hides behind the TMA load)
         const int tt = threadIdx.x - 13 * 32;
-        const int cc = tt & 7, r0 = tt >> 3;
+        const int cc = tt & 7, tg = tt >> 3;
+        const int trips = (g.Wo + 2) / 3;                      // triplets per output line
         float cA[8], cB[8], sc8[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) { cA[i] = bnc[cc * 8 + i]; cB[i] = bnc[64 + cc * 8 + i]; sc8[i] = bnc[128 + cc * 8 + i]; }
         TileIter t(g, blockIdx.x, gridDim.x);
         for (int i = 0; t.valid(g); ++i, t.next(g)) {
             const int slot = i % kDyRing;
-            tc::mbar_wait(&dy_full[slot], (i / kDyRing) & 1);
-            uint8_t* tile = dy_tiles + slot * kT16;
             const int n = t.n, d = t.d, h0 = t.h0();
             const int dw = d / 3, tap_d = (d - dw * 3) * 9;
             const bool d_ok = dw < fb.Dp;
-            for (int j = r0; j < 2 * g.Wo; j += 16) {
-                const int l = j >= g.Wo ? 1 : 0, w = j - l * g.Wo;
-                const int h = h0 + l;
-                if (h >= g.Ho) break;                    // a line past the volume: the load zero-filled it and its dY stays zero
-                const int row = l * kWgPitch + w;
-                uint4* p = reinterpret_cast<uint4*>(tile + row * 128 + ((cc ^ (row & 7)) << 4));
-                const uint4 u = *p;
-                const int hw = h / 3, ww = (w * 43) >> 7;      // w / 3 for w < 64
-                const unsigned tap = (unsigned)(tap_d + (h - hw * 3) * 3 + (w - ww * 3));
-                float dz[8];
+            uint2 am[3];
+            uint4 dv[3];
+            int tap_h[3];
 #pragma unroll
-                for (int q = 0; q < 8; ++q) dz[q] = 0.f;
-                if (d_ok && hw < fb.Hp && ww < fb.Wp) {
+            for (int k = 0; k < 3; ++k) {
+                const int t3 = tg + 16 * k;
+                const int l = t3 >= trips ? 1 : 0, ww = t3 - l * trips;
+                const int h = h0 + l, hw = h / 3;
+                tap_h[k] = tap_d + (h - hw * 3) * 3;
+                am[k] = make_uint2(0xffffffffu, 0xffffffffu);              // 255 everywhere: nobody wins
+                dv[k] = make_uint4(0u, 0u, 0u, 0u);
+                if (t3 < 2 * trips && d_ok && h < g.Ho && hw < fb.Hp && ww < fb.Wp) {
                     const int64_t po = ((((int64_t)n * fb.Dp + dw) * fb.Hp + hw) * fb.Wp + ww) * 64 + cc * 8;
-                    const uint2 am = *reinterpret_cast<const uint2*>(fb.amax + po);
-                    const uint4 dv = *reinterpret_cast<const uint4*>(fb.da + po);
-                    const __nv_bfloat162* dh = reinterpret_cast<const __nv_bfloat162*>(&dv);
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        const float2 f = __bfloat1622float2(dh[q]);
-                        const unsigned word = q < 2 ? am.x : am.y;
-                        const unsigned b0 = (word >> (16 * (q & 1))) & 255u, b1 = (word >> (16 * (q & 1) + 8)) & 255u;
-                        if (b0 == tap) dz[2 * q] = f.x * sc8[2 * q];
-                        if (b1 == tap) dz[2 * q + 1] = f.y * sc8[2 * q + 1];
-                    }
+                    am[k] = *reinterpret_cast<const uint2*>(fb.amax + po);
+                    dv[k] = *reinterpret_cast<const uint4*>(fb.da + po);
                 }
-                const __nv_bfloat162* yh = reinterpret_cast<const __nv_bfloat162*>(&u);
-                uint4 o;
-                __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&o);
+            }
+            tc::mbar_wait(&dy_full[slot], (i / kDyRing) & 1);
+            uint8_t* tile = dy_tiles + slot * kT16;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const int t3 = tg + 16 * k;
+                if (t3 >= 2 * trips) break;
+                const int l = t3 >= trips ? 1 : 0, ww = t3 - l * trips;
+                if (h0 + l >= g.Ho) break;                       // a line past the volume: the load zero-filled it and its dY stays zero
+                float dz[8];
+                const __nv_bfloat162* dh = reinterpret_cast<const __nv_bfloat162*>(&dv[k]);
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    const float2 f = __bfloat1622float2(yh[q]);
-                    oh[q] = __floats2bfloat162_rn(fmaf(cA[2 * q], f.x, cB[2 * q]) + dz[2 * q], fmaf(cA[2 * q + 1], f.y, cB[2 * q + 1]) + dz[2 * q + 1]);
+                    const float2 f = __bfloat1622float2(dh[q]);
+                    dz[2 * q] = f.x * sc8[2 * q];
+                    dz[2 * q + 1] = f.y * sc8[2 * q + 1];
                 }
-                *p = o;
+#pragma unroll
+                for (int e = 0; e < 3; ++e) {
+                    const int w = 3 * ww + e;
+                    if (w >= g.Wo) break;
+                    const unsigned tap = (unsigned)(tap_h[k] + e);
+                    const int row = l * kWgPitch + w;
+                    uint4* p = reinterpret_cast<uint4*>(tile + row * 128 + ((cc ^ (row & 7)) << 4));
+                    const uint4 u = *p;
+                    const __nv_bfloat162* yh = reinterpret_cast<const __nv_bfloat162*>(&u);
+                    uint4 o;
+                    __nv_bfloat162* oh = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const float2 f = __bfloat1622float2(yh[q]);
+                        const unsigned word = q < 2 ? am[k].x : am[k].y;
+                        const unsigned b0 = (word >> (16 * (q & 1))) & 255u, b1 = (word >> (16 * (q & 1) + 8)) & 255u;
+                        oh[q] = __floats2bfloat162_rn(fmaf(cA[2 * q], f.x, cB[2 * q]) + (b0 == tap ? dz[2 * q] : 0.f),
+                                                      fmaf(cA[2 * q + 1], f.y, cB[2 * q + 1]) + (b1 == tap ? dz[2 * q + 1] : 0.f));
+                    }
+                    *p = o;
+                }
             }
             tc::fence_proxy_async_smem();
             __syncwarp();

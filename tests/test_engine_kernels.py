@@ -260,14 +260,17 @@ def test_engine_backward_chain_is_exact_per_block():
         if s.pool_k:
             o = F.max_pool3d(o, s.pool_k, s.pool_s)
         o.backward(_cf(b.da[:B]).float())
-        assert _rel(_cf(b.dy[:B]), yb.grad) < 4e-3, f"dy{i}"
+        fused0 = i == 0 and getattr(b, "amax", None) is not None     # block 0: dY exists only inside the fused weight-gradient kernel
+        if not fused0:
+            assert _rel(_cf(b.dy[:B]), yb.grad) < 4e-3, f"dy{i}"
+        dy_used = yb.grad.bfloat16().float() if fused0 else _cf(b.dy[:B]).float()
         assert _rel(eng.grad.view(s.bn + ".weight"), gam.grad) < 1e-3, f"dgamma{i}"
         assert _rel(eng.grad.view(s.bn + ".bias"), bet.grad) < 1e-3, f"dbeta{i}"
         xin = (x.float() / 255.0).bfloat16().float().unsqueeze(1) if i == 0 else _cf(eng.blocks[i - 1].a[:B]).float()
         xin.requires_grad_(i > 0)
         wq = slab.view(s.conv + ".weight").clone().bfloat16().float().requires_grad_(True)
-        F.conv3d(xin, wq, None, stride=s.stride, padding=s.pad).backward(_cf(b.dy[:B]).float())
-        assert _rel(eng.grad.view(s.conv + ".weight"), wq.grad) < 1e-3, f"dW{i}"
+        F.conv3d(xin, wq, None, stride=s.stride, padding=s.pad).backward(dy_used)
+        assert _rel(eng.grad.view(s.conv + ".weight"), wq.grad) < (3e-3 if fused0 else 1e-3), f"dW{i}"
         if i > 0:
             assert _rel(_cf(eng.blocks[i - 1].da[:B]), xin.grad) < 4e-3, f"da{i - 1}"
 
