@@ -327,7 +327,7 @@ __device__ __forceinline__ void ldv(const float* p, float* f) {
 
 // one thread = one pooled output x V channels (V = 4: twice the threads, half the registers -> more loads in flight)
 template <int V>
-__global__ void __launch_bounds__(256) bn_relu_pool3_fwd_kernel(
+__global__ void __launch_bounds__(256, 3) bn_relu_pool3_fwd_kernel(
     const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ a, __nv_bfloat16* __restrict__ ymax, BlockGeom g,
     const float* __restrict__ scale, const float* __restrict__ shift, int relu, unsigned char* __restrict__ amax) {
     using VT = typename VecT<V>::T;
@@ -591,6 +591,15 @@ static int bn_relu_pool_fwd_impl(const void* y, void* a, void* ymax, void* amax,
     const int64_t total = (int64_t)N * g.Dp * g.Hp * g.Wp * (C / 8);
     if (pk == 3 && ps == 3 && ymax != nullptr) {
         // 8 channels per thread measured faster than 4 for the forward (0.094 vs 0.110 ms on block 0 of AlexNet3D)
+        if (amax != nullptr) {
+            // with the winning taps tracked, 8 channels per thread need 109 registers (2 CTAs per SM): 4 channels keep the loads in flight
+            const int64_t total4 = (int64_t)N * g.Dp * g.Hp * g.Wp * (C / 4);
+            bn_relu_pool3_fwd_kernel<4><<<(unsigned)((total4 + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)y, (__nv_bfloat16*)a,
+                                                                                                         (__nv_bfloat16*)ymax, g, scale, shift, relu,
+                                                                                                         (unsigned char*)amax);
+            NIDT_LAUNCH_CHECK();
+            return 0;
+        }
         bn_relu_pool3_fwd_kernel<8><<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)y, (__nv_bfloat16*)a,
                                                                                                     (__nv_bfloat16*)ymax, g, scale, shift, relu,
                                                                                                     (unsigned char*)amax);

@@ -503,15 +503,11 @@ __global__ void __launch_bounds__(kFused ? kFusedThreads : kThreads, 1) wgrad_ke
         float cA[8], cB[8], sc8[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) { cA[i] = bnc[cc * 8 + i]; cB[i] = bnc[64 + cc * 8 + i]; sc8[i] = bnc[128 + cc * 8 + i]; }
-        TileIter t(g, blockIdx.x, gridDim.x);
-        for (int i = 0; t.valid(g); ++i, t.next(g)) {
-            const int slot = i % kDyRing;
-            const int n = t.n, d = t.d, h0 = t.h0();
+        // (amax, da) of a tile's triplets: issued one tile AHEAD (their L2 / HBM latency is about one tile period)
+        auto fetch = [&](const TileIter& ti, uint2* am, uint4* dv, int* tap_h) {
+            const int n = ti.n, d = ti.d, h0 = ti.h0();
             const int dw = d / 3, tap_d = (d - dw * 3) * 9;
             const bool d_ok = dw < fb.Dp;
-            uint2 am[3];
-            uint4 dv[3];
-            int tap_h[3];
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
                 const int t3 = tg + 16 * k;
@@ -526,6 +522,18 @@ __global__ void __launch_bounds__(kFused ? kFusedThreads : kThreads, 1) wgrad_ke
                     dv[k] = *reinterpret_cast<const uint4*>(fb.da + po);
                 }
             }
+        };
+        TileIter t(g, blockIdx.x, gridDim.x);
+        uint2 am[3], am_n[3];
+        uint4 dv[3], dv_n[3];
+        int tap_h[3], tap_n[3];
+        if (t.valid(g)) fetch(t, am, dv, tap_h);
+        for (int i = 0; t.valid(g); ++i) {
+            const int slot = i % kDyRing;
+            const int h0 = t.h0();
+            TileIter tn = t;
+            tn.next(g);
+            if (tn.valid(g)) fetch(tn, am_n, dv_n, tap_n);
             tc::mbar_wait(&dy_full[slot], (i / kDyRing) & 1);
             uint8_t* tile = dy_tiles + slot * kT16;
 #pragma unroll
@@ -567,6 +575,9 @@ __global__ void __launch_bounds__(kFused ? kFusedThreads : kThreads, 1) wgrad_ke
             tc::fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&dy_ready[slot]);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { am[k] = am_n[k]; dv[k] = dv_n[k]; tap_h[k] = tap_n[k]; }
+            t = tn;
         }
     } else {
         if (warp == 9 && lane == 0) {

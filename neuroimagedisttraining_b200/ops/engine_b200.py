@@ -238,9 +238,12 @@ class B200Engine:
                 b.stats_tiles = lib.nidt_conv_in_grid()
                 iD, iH, iW = in_dhw
                 b.s2d = bool(lib.nidt_conv_in_s2d_supported(iD, iH, iW, spec.k, spec.stride, spec.pad)) and self.use_s2d
-                # winning pool taps for the fused BatchNorm-backward + weight-gradient kernel (NIDT_FUSED_BWD0=0: separate kernels)
+                # NIDT_FUSED_BWD0=1: winning pool taps for the fused BatchNorm-backward + weight-gradient kernel of this block
+                # (nidt_conv_in_s2d_wgrad_fused: dY never written to HBM).  Bit-identical to the separate kernels, but MEASURED SLOWER
+                # at batch 16 (0.62 + 0.03 ms against 0.247 + 0.235 ms, profiles/profile_step_fused_bwd0.txt): the in-place y -> dY
+                # transform competes with the 8 staging warps for the same issue slots, which this kernel is already bound by.  Off.
                 b.amax = (torch.empty(b.a.shape, dtype=torch.uint8, device=dev)
-                          if (b.s2d and b.ymax is not None and spec.cout == 64 and os.environ.get("NIDT_FUSED_BWD0", "1") != "0") else None)
+                          if (b.s2d and b.ymax is not None and spec.cout == 64 and os.environ.get("NIDT_FUSED_BWD0", "0") == "1") else None)
                 n_scr = max(lib.nidt_conv_in_grid() * 128 * 64, lib.nidt_conv_in_s2d_wgrad_scratch_floats())
                 b.wg_scratch = torch.zeros(n_scr, dtype=torch.float32, device=dev)
             else:
