@@ -12,6 +12,7 @@
 //
 // No argmax indices, no normalised activations and no ReLU masks are ever stored.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace nidt {
 
@@ -326,8 +327,8 @@ __device__ __forceinline__ void ldv(const float* p, float* f) {
 }
 
 // one thread = one pooled output x V channels (V = 4: twice the threads, half the registers -> more loads in flight)
-template <int V>
-__global__ void __launch_bounds__(256, 3) bn_relu_pool3_fwd_kernel(
+template <int V, bool kAmax>
+__global__ void __launch_bounds__(256, V == 4 ? 3 : 1) bn_relu_pool3_fwd_kernel(
     const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ a, __nv_bfloat16* __restrict__ ymax, BlockGeom g,
     const float* __restrict__ scale, const float* __restrict__ shift, int relu, unsigned char* __restrict__ amax) {
     using VT = typename VecT<V>::T;
@@ -361,11 +362,14 @@ __global__ void __launch_bounds__(256, 3) bn_relu_pool3_fwd_kernel(
 #pragma unroll
             for (int i = 0; i < V; ++i) {
                 const float pv = fmaf(f[i], sc[i], sh[i]);
-                if (pv > best[i]) { best[i] = pv; yb[i] = f[i]; ab[i] = (unsigned char)(kd * 9 + t); }
+                if (pv > best[i]) {
+                    best[i] = pv; yb[i] = f[i];
+                    if (kAmax) ab[i] = (unsigned char)(kd * 9 + t);
+                }
             }
         }
     }
-    if (amax != nullptr) {
+    if (kAmax) {
         // tap (kd*9 + kh*3 + kw) of the FIRST maximum of every window, 255 when ReLU gates the window (nobody gets a gradient):
         // lets the backward decide "am I the winner" per element without looking at its neighbours (fused wgrad of block 0)
 #pragma unroll
@@ -594,13 +598,20 @@ static int bn_relu_pool_fwd_impl(const void* y, void* a, void* ymax, void* amax,
         if (amax != nullptr) {
             // with the winning taps tracked, 8 channels per thread need 109 registers (2 CTAs per SM): 4 channels keep the loads in flight
             const int64_t total4 = (int64_t)N * g.Dp * g.Hp * g.Wp * (C / 4);
-            bn_relu_pool3_fwd_kernel<4><<<(unsigned)((total4 + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)y, (__nv_bfloat16*)a,
+            bn_relu_pool3_fwd_kernel<4, true><<<(unsigned)((total4 + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)y, (__nv_bfloat16*)a,
                                                                                                          (__nv_bfloat16*)ymax, g, scale, shift, relu,
                                                                                                          (unsigned char*)amax);
             NIDT_LAUNCH_CHECK();
             return 0;
         }
-        bn_relu_pool3_fwd_kernel<8><<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)y, (__nv_bfloat16*)a,
+        static const int pool_v = [] { const char* e = getenv("NIDT_POOL_V"); return e ? atoi(e) : 8; }();
+        if (pool_v == 4) {
+            // 4 channels per thread at 80 registers (3 CTAs per SM) keeps more loads in flight than 8 channels at 106
+            const int64_t total4 = (int64_t)N * g.Dp * g.Hp * g.Wp * (C / 4);
+            bn_relu_pool3_fwd_kernel<4, false><<<(unsigned)((total4 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+                (const __nv_bfloat16*)y, (__nv_bfloat16*)a, (__nv_bfloat16*)ymax, g, scale, shift, relu, nullptr);
+        } else
+            bn_relu_pool3_fwd_kernel<8, false><<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)y, (__nv_bfloat16*)a,
                                                                                                     (__nv_bfloat16*)ymax, g, scale, shift, relu,
                                                                                                     (unsigned char*)amax);
         NIDT_LAUNCH_CHECK();
