@@ -183,7 +183,7 @@ def setup(args, prefix: str, extra_identity: Optional[list] = None, loss_kind: O
             logger.info(f"native engine unavailable for {args.model}: {e}; using the PyTorch engine for forward/backward")
     trainer = SlabTrainer(model, args, logger, device=device, store=store, engine=engine, loss_kind=loss_kind)
     trainer.double_sigmoid_eval = not args.correct_eval_loss
-    if engine is not None and getattr(engine, "native", False) and not spatial:
+    if engine is not None and getattr(engine, "native", False) and not spatial and type(engine).__name__ == "B200Engine":
         # concurrent client slots: FedAvg / SalientGrads train (and evaluate) this many clients of a rank at once
         from ..ops.engines import make_native_engine
         for _ in range(max(0, int(args.client_lanes) - 1)):

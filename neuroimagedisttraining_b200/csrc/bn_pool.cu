@@ -665,6 +665,15 @@ static int bn_relu_pool_bwd_impl(const void* y, const void* ymax, const void* da
         bn_bwd_finalize_kernel<<<(C + 31) / 32, 256, 0, s>>>(partials, rgrid, C, count, c12, dgamma, dbeta);
         NIDT_LAUNCH_CHECK();
         if (!apply) return 0;
+        static const int bwd_v = [] { const char* e = getenv("NIDT_BWD_V"); return e ? atoi(e) : 4; }();
+        if (bwd_v == 8) {
+            const int64_t total8 = (int64_t)N * ((D + 2) / 3) * ((H + 2) / 3) * ((W + 2) / 3) * (C / 8);
+            bn_relu_pool3_bwd_apply_kernel<8><<<(unsigned)((total8 + 255) / 256), 256, 0, s>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)ymax,
+                                                                                            (const __nv_bfloat16*)da, (__nv_bfloat16*)dy, g, scale, shift,
+                                                                                            mean, invstd, c12, relu);
+            NIDT_LAUNCH_CHECK();
+            return 0;
+        }
         const int64_t total = (int64_t)N * ((D + 2) / 3) * ((H + 2) / 3) * ((W + 2) / 3) * (C / 4);
         bn_relu_pool3_bwd_apply_kernel<4><<<(unsigned)((total + 255) / 256), 256, 0, s>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)ymax,
                                                                                        (const __nv_bfloat16*)da, (__nv_bfloat16*)dy, g, scale, shift,
