@@ -1,6 +1,7 @@
 """Built-in HDF5 subset (``data/hdf5_mini.py``): round trips, memory-mapped row access, the volume store and the SalientGrads entry
 point on a file, and clear errors for what lies outside the subset.  (No HDF5 library is available here: reader and writer are
 checked against each other and against byte-level expectations from the format specification.)"""
+import os
 import struct
 
 import numpy as np
@@ -73,15 +74,51 @@ def test_features_outside_the_subset_are_refused_with_a_reason(tmp_path):
     (tmp_path / "v2.h5").write_bytes(bytes(v2))
     with pytest.raises(H.UnsupportedHDF5, match="superblock version 2"):
         H.File(str(tmp_path / "v2.h5"))
-    # flip the layout class of the dataset from contiguous (1) to chunked (2): version 3 layout message = type 8, body starts 03 01
+    # an unknown data layout class (3 = virtual): version 3 layout message = type 8, body starts 03 01
     i = bytes(raw).index(struct.pack("<HH", 8, 24)) + 8
     assert raw[i] == 3 and raw[i + 1] == 1
-    ch = bytearray(raw); ch[i + 1] = 2
-    (tmp_path / "chunked.h5").write_bytes(bytes(ch))
-    with pytest.raises(H.UnsupportedHDF5, match="chunked"):
-        H.File(str(tmp_path / "chunked.h5"))
+    ch = bytearray(raw); ch[i + 1] = 3
+    (tmp_path / "virtual.h5").write_bytes(bytes(ch))
+    with pytest.raises(H.UnsupportedHDF5, match="layout class 3"):
+        H.File(str(tmp_path / "virtual.h5"))
+    # a filter the reader does not implement (szip = 4) is refused when the dataset is opened, not decoded into garbage
+    H.write_file(path, {"X": np.arange(12, dtype=np.int32).reshape(3, 4)}, chunks={"X": (1, 4)}, compression="gzip")
+    z = bytearray(open(path, "rb").read())
+    j = bytes(z).index(struct.pack("<HHHH", H.FILTER_DEFLATE, 0, 0, 1))
+    z[j] = 4
+    (tmp_path / "szip.h5").write_bytes(bytes(z))
+    with pytest.raises(H.UnsupportedHDF5, match="filter 4"):
+        H.File(str(tmp_path / "szip.h5"))
     (tmp_path / "short.h5").write_bytes(bytes(raw[:200]))
     with pytest.raises(H.UnsupportedHDF5, match="truncated"):
         H.File(str(tmp_path / "short.h5"))
     with pytest.raises(H.UnsupportedHDF5, match="subset"):
         H.write_file(path, {"s": np.array(["a", "b"])})
+
+
+@pytest.mark.parametrize("compression,shuffle,chunk", [(None, False, (1, 9, 11, 7)), ("gzip", True, (4, 5, 11, 4)), ("gzip", False, (8, 9, 6, 7))])
+def test_chunked_and_compressed_datasets_round_trip(tmp_path, compression, shuffle, chunk):
+    """Chunked storage with the shuffle + deflate pipeline (what ``h5py.create_dataset(..., chunks=..., compression='gzip', shuffle=True)``
+    writes): full reads, single rows, slices and sorted index lists decode only the chunks they need; a chunk index with more than 64
+    chunks is a two-level B-tree; the volume store serves batches from such a file."""
+    from neuroimagedisttraining_b200.data.volumes import HDF5VolumeStore
+    rng = np.random.RandomState(0)
+    X = (rng.rand(37, 9, 11, 7) * 255).astype(np.uint8)
+    y = (rng.rand(37) > 0.5).astype(np.float32)
+    site = rng.randint(0, 3, 37).astype(np.int64)
+    Z = rng.randn(300, 5)
+    path = str(tmp_path / "c.h5")
+    H.write_file(path, {"X": X, "y": y, "site": site, "Z": Z}, chunks={"X": chunk, "Z": (2, 3)}, compression=compression, shuffle=shuffle)
+    with H.File(path) as f:
+        assert isinstance(f["X"], H.ChunkedDataset) and f["X"].chunks == chunk and f["X"].shape == X.shape
+        assert np.array_equal(f["X"][()], X) and np.array_equal(f["Z"][()], Z) and np.array_equal(f["y"][()], y)
+        assert np.array_equal(f["X"][[1, 5, 6, 30, 36]], X[[1, 5, 6, 30, 36]])
+        assert np.array_equal(f["X"][3], X[3]) and np.array_equal(f["X"][-1], X[-1]) and np.array_equal(f["X"][10:20], X[10:20])
+        assert len(f["Z"]._index) == 300
+        with pytest.raises(TypeError):
+            f["X"][[5, 1]]
+    if compression == "gzip":
+        assert os.path.getsize(path) < X.nbytes + Z.nbytes + 40000
+    store = HDF5VolumeStore(path)
+    xb, yb = store.fetch([2, 7, 11])
+    assert np.array_equal(xb.numpy(), X[[2, 7, 11]]) and np.array_equal(yb.numpy(), y[[2, 7, 11]])
