@@ -246,8 +246,12 @@ def agg_check(api, ctx, device):
     t = torch.stack([d_ord.double(), d_nccl.double()])
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     res.update({"max_abs_diff": float(t[0].item()), "max_abs_diff_vs_nccl_allreduce": float(t[1].item()), "mask_entries_differing_vs_nccl": masks_equal})
-    tol = 0.0 if res["agg_path"] in ("p2p", "bulk") else 1e-5       # in-switch reduction adds in the switch's order
-    res["ok"] = bool(res["max_abs_diff"] <= tol and res["max_abs_diff_vs_nccl_allreduce"] <= 1e-5 and (masks_equal is None or masks_equal <= 8))
+    # the P2P paths add in rank order: exactly the ordered sum.  The in-switch reduction adds in the switch's order: a few ulps of the
+    # largest entries (BatchNorm running statistics are O(10)), and a handful of near-ties of the mask threshold may fall the other way
+    scale = max(1.0, float(ordered.abs().max().item()))
+    res["max_abs_value"] = scale
+    tol = 0.0 if not res["agg_path"].startswith("multimem") and "+mm" not in res["agg_path"] else 4e-6 * scale
+    res["ok"] = bool(res["max_abs_diff"] <= tol and res["max_abs_diff_vs_nccl_allreduce"] <= 4e-6 * scale and (masks_equal is None or masks_equal <= 8))
     return res
 
 
