@@ -226,6 +226,7 @@ def agg_check(api, ctx, device):
         ordered[:api.mask.flat.numel()] *= api.mask.flat
     d_ord = (out_f.flat - ordered).abs().max()
     d_nccl = (out_f.flat - out_n.flat).abs().max()
+    d_rel = ((out_f.flat - ordered).abs() / ordered.abs().clamp_min(1.0)).max()       # in units of max(|value|, 1)
     res = {"agg_path": fused.pick_mode(lay.total_numel)}
     masks_equal = None
     if getattr(api, "scores", None) is not None:
@@ -243,15 +244,17 @@ def agg_check(api, ctx, device):
         diff = (m_f.flat != m_n.flat).sum().double()
         dist.all_reduce(diff, op=dist.ReduceOp.MAX)
         masks_equal = int(diff.item())
-    t = torch.stack([d_ord.double(), d_nccl.double()])
+    d_rel_n = ((out_f.flat - out_n.flat).abs() / out_n.flat.abs().clamp_min(1.0)).max()
+    t = torch.stack([d_ord.double(), d_nccl.double(), d_rel.double(), d_rel_n.double()])
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    res.update({"max_abs_diff": float(t[0].item()), "max_abs_diff_vs_nccl_allreduce": float(t[1].item()), "mask_entries_differing_vs_nccl": masks_equal})
+    res.update({"max_abs_diff": float(t[0].item()), "max_abs_diff_vs_nccl_allreduce": float(t[1].item()), "max_rel_diff": float(t[2].item()),
+                "max_rel_diff_vs_nccl_allreduce": float(t[3].item()), "mask_entries_differing_vs_nccl": masks_equal})
     # the P2P paths add in rank order: exactly the ordered sum.  The in-switch reduction adds in the switch's order: a few ulps of the
     # largest entries (BatchNorm running statistics are O(10)), and a handful of near-ties of the mask threshold may fall the other way
-    scale = max(1.0, float(ordered.abs().max().item()))
-    res["max_abs_value"] = scale
-    tol = 0.0 if not res["agg_path"].startswith("multimem") and "+mm" not in res["agg_path"] else 4e-6 * scale
-    res["ok"] = bool(res["max_abs_diff"] <= tol and res["max_abs_diff_vs_nccl_allreduce"] <= 4e-6 * scale and (masks_equal is None or masks_equal <= 8))
+    # (elementwise, relative to max(|value|, 1): 2e-6 = ~16 ulps)
+    exact = not res["agg_path"].startswith("multimem") and "+mm" not in res["agg_path"]
+    res["ok"] = bool((res["max_abs_diff"] == 0.0 if exact else res["max_rel_diff"] <= 2e-6) and res["max_rel_diff_vs_nccl_allreduce"] <= 2e-6
+                     and (masks_equal is None or masks_equal <= 8))
     return res
 
 
