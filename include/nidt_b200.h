@@ -80,6 +80,12 @@ int nidt_gather_rows_u8_args(const void* src, const int64_t* idx, void* dst, int
  * runs of consecutive row numbers are merged into one copy each.  _counted also reports how many copies were issued. */
 int nidt_copy_rows_h2d(const void* host_base, const int64_t* rows, int n, int64_t row_bytes, void* dst, void* stream);
 int nidt_copy_rows_h2d_counted(const void* host_base, const int64_t* rows, int n, int64_t row_bytes, void* dst, void* stream, int* n_copies);
+/* Dense 8-bit volumes from their zero-run-skipping transfer form (per image row: start, length, offset of the non-zero span; spans
+ * packed back to back): the host sends only the spans and 6 bytes per row, this kernel writes every byte of n_vol <= 32 volumes of
+ * rows x W (W <= 255).  packed_off: HOST array of each volume's byte offset in `packed`.  The reference uploads dense fp32 volumes
+ * (sailentgrads/my_model_trainer.py:185-199). */
+int nidt_expand_sparse_rows_u8(const void* packed, const long long* packed_off, const void* tab, const void* off, void* dst, int n_vol,
+                               int rows, int W, void* stream);
 /* Ditto proximal pull w -= coef*(w - ref).  ref: fedml_api/standalone/ditto/my_model_trainer.py:63-64. */
 int nidt_prox_pull(float* w, const float* ref, int64_t n, float coef, void* stream);
 

@@ -431,6 +431,50 @@ NIDT_API int nidt_gather_rows_u8_args(const void* src, const int64_t* idx, void*
     return 0;
 }
 
+// ---------------------------------------------------------------------------- zero-run-skipping volume transfer
+// Masked grey-matter maps are mostly background: outside the brain every voxel is 0 (Preprocess_ABCD.ipynb applies a group-mean
+// mask), so each image row is [zeros | span | zeros].  The host keeps, per volume, the spans packed back to back plus a 6-byte
+// table entry per row (start, length, offset of the span in the packed volume); only those cross PCIe, and this kernel rebuilds the
+// dense 8-bit volume on the device: one warp per image row, every byte of the row written (span bytes or 0).
+namespace nidt {
+constexpr int kExpandVolumes = 32;
+struct ExpandArgs {
+    long long packed_off[kExpandVolumes];      // byte offset of every volume's packed spans in `packed`
+};
+__global__ void __launch_bounds__(256) expand_sparse_rows_kernel(const uint8_t* __restrict__ packed, const __grid_constant__ ExpandArgs a,
+                                                                 const uint8_t* __restrict__ tab /* [vol][row][2] */, const uint32_t* __restrict__ off /* [vol][row] */,
+                                                                 uint8_t* __restrict__ dst, int n_vol, int rows, int W) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int64_t total = (int64_t)n_vol * rows;
+    for (int64_t r = warp; r < total; r += n_warps) {
+        const int v = (int)(r / rows);
+        const unsigned start = tab[2 * r], len = tab[2 * r + 1];
+        const uint8_t* src = packed + a.packed_off[v] + off[r];
+        uint8_t* out = dst + r * W;
+        for (int c = lane; c < W; c += 32) {
+            const unsigned k = (unsigned)c - start;
+            out[c] = k < len ? src[k] : (uint8_t)0;
+        }
+    }
+}
+}  // namespace nidt
+// packed / tab / off / dst: DEVICE buffers (the packed spans and tables of `n_vol` <= 32 volumes as uploaded); packed_off: HOST array
+NIDT_API int nidt_expand_sparse_rows_u8(const void* packed, const long long* packed_off, const void* tab, const void* off, void* dst, int n_vol,
+                                        int rows, int W, void* stream) {
+    NIDT_REQUIRE(n_vol >= 0 && n_vol <= nidt::kExpandVolumes && rows >= 1 && W >= 1 && W <= 255, "nidt_expand_sparse_rows_u8: n_vol=%d rows=%d W=%d", n_vol, rows, W);
+    if (n_vol == 0) return 0;
+    nidt::ExpandArgs a;
+    for (int i = 0; i < nidt::kExpandVolumes; ++i) a.packed_off[i] = i < n_vol ? packed_off[i] : 0;
+    const int64_t warps = (int64_t)n_vol * rows;
+    int64_t grid = (warps + 7) / 8;
+    if (grid > nidt::kNumSMs * 4) grid = nidt::kNumSMs * 4;       // a few CTAs per SM: it runs next to the training kernels
+    nidt::expand_sparse_rows_kernel<<<(int)grid, 256, 0, (cudaStream_t)stream>>>((const uint8_t*)packed, a, (const uint8_t*)tab, (const uint32_t*)off,
+                                                                                (uint8_t*)dst, n_vol, rows, W);
+    NIDT_LAUNCH_CHECK();
+    return 0;
+}
+
 // dst[j] = host_base[rows[j]] (row_bytes each) as asynchronous copies on `stream`, issued from native code.  Runs of consecutive
 // row numbers (a site's subjects are adjacent in the store) become ONE copy each, so a sorted batch costs a handful of large
 // transfers instead of one per sample.  host_base should be pinned; rows is a HOST array.  *n_copies (optional) = copies issued.

@@ -39,6 +39,52 @@ class _Slot:
         self.ready = torch.cuda.Event()
         self.consumed = torch.cuda.Event()
         self.busy = False
+        self.packed = self.tab = self.off = None      # zero-run-skipping uploads: device copies of the spans / row tables
+
+
+class SparsePack:
+    """Zero-run-skipping transfer form of a pinned 8-bit volume cache ``[N, D, H, W]`` (W <= 255).
+
+    Masked grey-matter maps are zero outside the brain (``Preprocess_ABCD.ipynb`` applies a group-mean mask), so an image row is
+    ``[zeros | span | zeros]``.  Built once per store: the non-zero spans of every volume packed back to back (pinned), and per
+    row a (start, length) byte pair and the span's offset inside its volume (uint32).  An upload then moves the spans and 6 bytes per
+    row; ``nidt_expand_sparse_rows_u8`` rebuilds the dense volume on the device.  Lossless."""
+
+    def __init__(self, cache: torch.Tensor, block: int = 32):
+        n, d, h, w = cache.shape
+        assert w <= 255
+        self.rows, self.w = d * h, w
+        a = cache.numpy().reshape(n, self.rows, w)
+        cols = np.arange(w)
+        tab = np.zeros((n, self.rows, 2), np.uint8)
+        off = np.zeros((n, self.rows), np.uint32)
+        vol_bytes = np.zeros(n, np.int64)
+        chunks = []
+        for i0 in range(0, n, block):
+            blk = a[i0:i0 + block]
+            nz = blk != 0
+            has = nz.any(-1)
+            start = nz.argmax(-1)
+            last = w - 1 - nz[..., ::-1].argmax(-1)
+            ln = np.where(has, last - start + 1, 0)
+            tab[i0:i0 + block, :, 0] = np.where(has, start, 0)
+            tab[i0:i0 + block, :, 1] = ln
+            cs = np.cumsum(ln, axis=1)
+            off[i0:i0 + block] = cs - ln
+            vol_bytes[i0:i0 + block] = cs[:, -1]
+            inside = (cols >= np.where(has, start, 0)[..., None]) & (cols < (np.where(has, start, 0) + ln)[..., None])
+            chunks.append(blk[inside])                     # row-major: volume by volume, row by row
+        self.vol_off = np.concatenate([[0], np.cumsum(vol_bytes)]).astype(np.int64)
+        total = int(self.vol_off[-1])
+        self.dense_bytes = n * self.rows * w
+        self.ratio = (total + tab.nbytes + off.nbytes) / max(1, self.dense_bytes)
+        self.max_vol_bytes = int(vol_bytes.max()) if n else 0
+        pin = torch.cuda.is_available()
+        self.packed = torch.from_numpy(np.concatenate(chunks) if chunks else np.zeros(0, np.uint8))
+        self.tab = torch.from_numpy(tab)
+        self.off = torch.from_numpy(off.view(np.int32))    # bit pattern of the uint32 offsets
+        if pin:
+            self.packed, self.tab, self.off = self.packed.pin_memory(), self.tab.pin_memory(), self.off.pin_memory()
 
 
 class _Entry:
@@ -86,6 +132,7 @@ class BatchStager:
         self._ring_ready = False
         self._native = None
         self._pinned_cache = None
+        self._sparse: Optional[SparsePack] = None
         if self.cuda:
             self.copy_stream = torch.cuda.Stream(device=self.device)
             cache = getattr(store, "_cache", None)
@@ -106,6 +153,16 @@ class BatchStager:
             # labels are copied straight out of ONE pinned array of all labels (row copies, like the volumes): no per-slot pinned
             # bounce buffer that the host could overwrite while an earlier, still queued copy has yet to read it
             self._pin_labels = torch.from_numpy(np.ascontiguousarray(store.labels, dtype=np.float32)).pin_memory()
+            lib.nidt_expand_sparse_rows_u8.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, vp]
+            lib.nidt_expand_sparse_rows_u8.restype = i32
+            # zero-run-skipping uploads for the per-loader device cache when the volumes are sparse enough (NIDT_SPARSE_H2D=0: dense)
+            if (self._pinned_cache is not None and self._pinned_cache.dim() == 4 and self._pinned_cache.shape[-1] <= 255
+                    and os.environ.get("NIDT_SPARSE_H2D", "1") != "0"):
+                pack = getattr(store, "_sparse_pack", None)
+                if pack is None:
+                    pack = SparsePack(self._pinned_cache)
+                    store._sparse_pack = pack                          # shared by every stager of this store
+                self._sparse = pack if pack.ratio < 0.8 else None
             self._gx = [torch.empty((batch_size,) + tuple(store.shape), dtype=torch.uint8, device=self.device) for _ in range(2)]
             self._gy = [torch.empty(batch_size, dtype=torch.float32, device=self.device) for _ in range(2)]
             self._gk = 0
@@ -128,6 +185,43 @@ class BatchStager:
             dst_x[:n].copy_(pin_x[:n], non_blocking=True)
             self.h2d_copies += 1
         self.h2d_bytes += n * self._row_bytes
+
+    def _copy_rows_sparse(self, ids: np.ndarray, slot: _Slot) -> None:
+        """``slot.x[j] = volume ids[j]`` through the zero-run-skipping form: the packed spans and row tables of runs of adjacent
+        volumes are copied (three copies per run), then expanded on the copy stream (the caller holds the stream context)."""
+        from ..ops import native
+        sp = self._sparse
+        n = len(ids)
+        if n == 0:
+            return
+        if getattr(slot, "packed", None) is None or slot.packed.numel() < slot.cap * sp.max_vol_bytes:
+            slot.packed = torch.empty(max(1, slot.cap * sp.max_vol_bytes), dtype=torch.uint8, device=self.device)
+            slot.tab = torch.empty((slot.cap, sp.rows, 2), dtype=torch.uint8, device=self.device)
+            slot.off = torch.empty((slot.cap, sp.rows), dtype=torch.int32, device=self.device)
+        bases = np.zeros(n, np.int64)
+        j, poff = 0, 0
+        while j < n:
+            e = j + 1
+            while e < n and ids[e] == ids[e - 1] + 1:
+                e += 1
+            a, b = int(ids[j]), int(ids[e - 1]) + 1
+            lo, hi = int(sp.vol_off[a]), int(sp.vol_off[b])
+            if hi > lo:
+                slot.packed[poff:poff + hi - lo].copy_(sp.packed[lo:hi], non_blocking=True)
+            slot.tab[j:e].copy_(sp.tab[a:b], non_blocking=True)
+            slot.off[j:e].copy_(sp.off[a:b], non_blocking=True)
+            bases[j:e] = poff + (sp.vol_off[a:b] - lo)
+            self.h2d_bytes += (hi - lo) + (b - a) * sp.rows * 6
+            self.h2d_copies += 3
+            poff += hi - lo
+            j = e
+        st = self.copy_stream.cuda_stream
+        for k in range(0, n, 32):
+            m = min(32, n - k)
+            part = np.ascontiguousarray(bases[k:k + m])
+            native.check(self._native.nidt_expand_sparse_rows_u8(slot.packed.data_ptr(), part.ctypes.data, slot.tab[k:].data_ptr(), slot.off[k:].data_ptr(),
+                                                                 slot.x[k:].data_ptr(), m, sp.rows, sp.w, st), "nidt_expand_sparse_rows_u8")
+            native.count_launches(1)
 
     def _copy_labels(self, ids: np.ndarray, dst_y: torch.Tensor) -> None:
         """Enqueue ``dst_y[j] = label ids[j]`` on the copy stream (the caller holds the stream context)."""
@@ -303,7 +397,10 @@ class BatchStager:
                 self.copy_stream.wait_event(slot.consumed)
                 if slot.pin_x is not None:
                     slot.ready.synchronize()
-                self._copy_rows(ent.rows, slot.x, slot.pin_x)
+                if self._sparse is not None:
+                    self._copy_rows_sparse(ent.rows, slot)
+                else:
+                    self._copy_rows(ent.rows, slot.x, slot.pin_x)
                 self._copy_labels(ent.rows, slot.y)
                 slot.ready.record(self.copy_stream)
 

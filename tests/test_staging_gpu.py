@@ -27,7 +27,10 @@ def _collect(gen):
     return [(x.clone(), y.clone()) for x, y in gen]
 
 
-def test_client_cache_and_resident_batches_equal_the_stream_ring():
+@pytest.mark.parametrize("sparse", ["0", "1"])
+def test_client_cache_and_resident_batches_equal_the_stream_ring(sparse, monkeypatch):
+    """sparse = "1": the per-loader uploads go through the zero-run-skipping form (spans + row tables, expanded on the device)."""
+    monkeypatch.setenv("NIDT_SPARSE_H2D", sparse)
     dev = torch.device("cuda:0")
     store, ds = _setup()
     train, test = ds[5], ds[6]
@@ -48,6 +51,10 @@ def test_client_cache_and_resident_batches_equal_the_stream_ring():
     torch.cuda.synchronize()
     n_train = sum(train[c].num_samples for c in range(4))
     row = int(np.prod(SHAPE))
+    assert (client._sparse is not None) == (sparse == "1")
+    if sparse == "1":
+        assert client.h2d_bytes < 0.85 * n_train * (row + 4)        # the synthetic brains are ~half background
+        return
     assert client.h2d_bytes == n_train * (row + 4)       # one upload per volume (+ its label)
     assert not client._queue                             # everything that was wanted has been consumed
     # two epochs draw from ONE upload; the ring copies every batch again
