@@ -17,6 +17,8 @@ def create_model(model_name: str, class_num: int = 1, in_shape=volumetric.ABCD_S
         return volumetric.AlexNet3D_Dropout_Regression(num_classes=class_num, in_shape=in_shape)
     if name in ("3dresnet", "resnet3d", "resnet_l3", "resnet3d_18"):
         return volumetric.resnet3d_18(num_classes=class_num, in_shape=in_shape)
+    if name in ("3dresnet_bottleneck", "resnet3d_bottleneck", "resnet_l3_bottleneck"):
+        return volumetric.resnet3d_bottleneck(num_classes=class_num, in_shape=in_shape)
     if name in ("tiny3dcnn", "tiny3d"):
         return volumetric.Tiny3DCNN(num_classes=class_num, in_shape=in_shape)
     if name == "resnet18":
@@ -44,5 +46,5 @@ def create_model(model_name: str, class_num: int = 1, in_shape=volumetric.ABCD_S
     raise ValueError(f"unknown model {model_name!r}")
 
 
-MODEL_NAMES = ["3DCNN", "3DCNN_deeper", "3DCNN_regression", "3DResNet", "tiny3DCNN", "resnet18", "resnet18_bn",
+MODEL_NAMES = ["3DCNN", "3DCNN_deeper", "3DCNN_regression", "3DResNet", "3DResNet_bottleneck", "tiny3DCNN", "resnet18", "resnet18_bn",
                "vgg11", "vgg16", "cnn_cifar10", "cnn_cifar100", "lenet5", "lenet5_cifar", "cnn_fedavg", "cnn_dropout"]

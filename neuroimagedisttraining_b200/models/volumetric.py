@@ -288,3 +288,8 @@ ResNet_l3 = ResNet3D_l3
 
 def resnet3d_18(num_classes: int = 1, in_shape=ABCD_SHAPE) -> ResNet3D_l3:
     return ResNet3D_l3(BasicBlock3D, (2, 2, 2), num_classes, in_shape)
+
+
+def resnet3d_bottleneck(num_classes: int = 1, in_shape=ABCD_SHAPE, layers=(2, 2, 2)) -> ResNet3D_l3:
+    """``ResNet_l3(Bottleneck, layers)`` (``salient_models.py:45-81``): 1x1x1 -> 3x3x3 -> 1x1x1 blocks, 4x channel expansion."""
+    return ResNet3D_l3(Bottleneck3D, tuple(layers), num_classes, in_shape)

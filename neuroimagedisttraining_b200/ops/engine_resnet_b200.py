@@ -1,16 +1,19 @@
-"""sm_100a compute engine for the 3-D ResNet (``models.volumetric.ResNet3D_l3`` with ``BasicBlock3D``; BASELINE config 4).
+"""sm_100a compute engine for the 3-D ResNets (``models.volumetric.ResNet3D_l3`` with ``BasicBlock3D`` -- BASELINE config 4 -- or
+``Bottleneck3D`` blocks).
 
 Same contract as :class:`.engine_b200.B200Engine` (no autograd, no cuDNN/cuBLAS, parameters and gradients in flat slabs,
 channels-last bf16 activations), for a residual topology:
 
   stem    conv_in (1->64, k3 s2 p3, tcgen05, im2col in smem from the 8-bit volume) -> BN+ReLU -> MaxPool(3,2,1)
-  block   conv3x3x3 (tcgen05+TMA; stride 2 = element-strided TMA boxes) -> BN+ReLU -> conv3x3x3 -> BN
+  basic   conv3x3x3 (tcgen05+TMA; stride 2 = element-strided TMA boxes) -> BN+ReLU -> conv3x3x3 -> BN
           (+ 1x1x1 stride-2 conv -> BN on the shortcut) -> add + ReLU
+  bottle  conv1x1x1 -> BN+ReLU -> conv3x3x3 (stride) -> BN+ReLU -> conv1x1x1 (x4 channels) -> BN (+ shortcut conv -> BN) -> add + ReLU;
+          the 1x1x1 convolutions are the same tcgen05 implicit-GEMM kernel with one tap (a plain [positions x Cin] x [Cin x Cout] GEMM)
   head    AvgPool3d(3) -> Linear(F,512) -> Linear(512,1) -> BCEWithLogits (+ full backward)
 
 Backward: ReLU gate -> BN backward -> wgrad (split-K tcgen05) and dgrad (the fprop kernel on dY with flipped weights; for
 stride-2 convs on the zero-upsampled dY) -> gradient accumulation at the block input -> ... -> max-pool backward -> stem wgrad.
-Reference model: ``ResNet_l3(BasicBlock, [2,2,2])``, fedml_api/model/cv/salient_models.py:13-139 (its hard-coded
+Reference model: ``ResNet_l3(BasicBlock | Bottleneck, layers)``, fedml_api/model/cv/salient_models.py:13-139 (its hard-coded
 9216-feature FC does not fit the ABCD shape; here the FC is sized from the input, see models/volumetric.py).
 """
 from __future__ import annotations
@@ -21,7 +24,7 @@ from typing import List, Optional
 import torch
 import torch.nn as nn
 
-from ..models.volumetric import BasicBlock3D, ResNet3D_l3
+from ..models.volumetric import BasicBlock3D, Bottleneck3D, ResNet3D_l3
 from ..runtime.slab import ParamSlab, SlabLayout
 from . import flat as flat_ops
 from . import native
@@ -49,8 +52,8 @@ class ResNet3DEngine:
             raise ImportError("model is not a ResNet3D_l3")
         for layer in (model.layer1, model.layer2, model.layer3):
             for blk in layer:
-                if not isinstance(blk, BasicBlock3D):
-                    raise ImportError("native ResNet path supports BasicBlock3D only")
+                if not isinstance(blk, (BasicBlock3D, Bottleneck3D)):
+                    raise ImportError("native ResNet path supports BasicBlock3D / Bottleneck3D blocks")
         if model.num_classes != 1:
             raise ImportError("native head supports one logit")
         self.lib = native.load()
@@ -130,22 +133,33 @@ class ResNet3DEngine:
                 b = _Conv()
                 b.name = pre
                 planes, stride = blk.conv1.out_channels, blk.stride
-                b.c1 = self._new_conv(pre + ".conv1", pre + ".bn1", ch, planes, 3, stride, 1, dhw)
-                b.c2 = self._new_conv(pre + ".conv2", pre + ".bn2", planes, planes, 3, 1, 1, b.c1.out_dhw)
+                if isinstance(blk, Bottleneck3D):
+                    specs = [(planes, 1, 1, 0), (planes, 3, stride, 1), (planes * 4, 1, 1, 0)]
+                else:
+                    specs = [(planes, 3, stride, 1), (planes, 3, 1, 1)]
+                b.main, cin, cdhw = [], ch, dhw                # the main branch: conv -> BN (-> ReLU except after the last one)
+                for j, (co, k, s_, p_) in enumerate(specs):
+                    c = self._new_conv(f"{pre}.conv{j + 1}", f"{pre}.bn{j + 1}", cin, co, k, s_, p_, cdhw)
+                    b.main.append(c)
+                    cin, cdhw = co, c.out_dhw
+                out_ch = cin
                 b.ds = None
                 if blk.downsample is not None:
-                    b.ds = self._new_conv(pre + ".downsample.0", pre + ".downsample.1", ch, planes, 1, stride, 0, dhw)
-                    assert b.ds.out_dhw == b.c2.out_dhw
-                    b.zd = self._act(b.ds.out_dhw, planes)
-                b.a1 = self._act(b.c1.out_dhw, planes)
-                b.da1 = torch.empty_like(b.a1)
-                b.z2 = self._act(b.c2.out_dhw, planes)
-                b.out = self._act(b.c2.out_dhw, planes)
+                    b.ds = self._new_conv(pre + ".downsample.0", pre + ".downsample.1", ch, out_ch, 1, stride, 0, dhw)
+                    assert b.ds.out_dhw == cdhw
+                    b.zd = self._act(b.ds.out_dhw, out_ch)
+                else:
+                    assert ch == out_ch and dhw == cdhw, "identity shortcut needs equal shapes"
+                b.acts = [self._act(c.out_dhw, c.cout) for c in b.main[:-1]]      # relu(bn(conv_j)) for all but the last conv
+                b.dacts = [torch.empty_like(a) for a in b.acts]
+                b.z = self._act(cdhw, out_ch)                  # bn(last conv)
+                b.out = self._act(cdhw, out_ch)
                 b.dout = torch.empty_like(b.out)          # gradient w.r.t. the block output (written by the next block / head)
                 b.dz = torch.empty_like(b.out)            # gated gradient shared by the main branch and the shortcut
                 b.dtmp = self._act(dhw, ch) if b.ds is not None else None
+                b.c1, b.c2, b.a1, b.da1, b.z2 = b.main[0], b.main[1], b.acts[0], b.dacts[0], b.z      # names the basic-block tests use
                 self.blocks.append(b)
-                dhw, ch = b.c2.out_dhw, planes
+                dhw, ch = cdhw, out_ch
         self.last_dhw, self.last_ch = dhw, ch
         self.avg_k = 3
         S = 1
@@ -159,7 +173,7 @@ class ResNet3DEngine:
         self.feat, self.dfeat = torch.zeros((B, self.F), **f32), torch.zeros((B, self.F), **f32)
         self.hidden, self.dhidden = torch.zeros(B * self.Hd, **f32), torch.zeros(B * self.Hd, **f32)
         self.eval_logits = torch.zeros(B, **f32)
-        self.convs = [self.stem] + [c for b in self.blocks for c in ((b.c1, b.c2) + ((b.ds,) if b.ds is not None else ()))]
+        self.convs = [self.stem] + [c for b in self.blocks for c in (tuple(b.main) + ((b.ds,) if b.ds is not None else ()))]
 
     # ------------------------------------------------------------------------- slab plumbing
     def new_slab(self) -> ParamSlab:
@@ -298,17 +312,19 @@ class ResNet3DEngine:
                   "maxpool3d_fwd")
         cur = s.p
         for b in self.blocks:
-            self._conv_bn(b.c1, cur, B, train)
-            self._bn_apply(b.c1, b.a1, B, True)
-            self._conv_bn(b.c2, b.a1, B, train)
-            self._bn_apply(b.c2, b.z2, B, False)
+            h = cur
+            for j, c in enumerate(b.main):
+                self._conv_bn(c, h, B, train)
+                last = j == len(b.main) - 1
+                h = b.z if last else b.acts[j]
+                self._bn_apply(c, h, B, not last)
             idt = cur
             if b.ds is not None:
                 self._conv_bn(b.ds, cur, B, train)
                 self._bn_apply(b.ds, b.zd, B, False)
                 idt = b.zd
             self._tag = f"[{b.name}]"
-            self._ew(b.z2, idt, b.out, B, 0, "add_relu_fwd")
+            self._ew(b.z, idt, b.out, B, 0, "add_relu_fwd")
             b.x_in = cur
             cur = b.out
         D, H, W = self.last_dhw
@@ -337,10 +353,11 @@ class ResNet3DEngine:
             dx = self.blocks[i - 1].dout if i > 0 else self.stem.dp        # gradient w.r.t. this block's input
             self._tag = f"[{b.name}]"
             self._ew(b.dout, b.out, b.dz, B, 1, "relu_gate_bwd")
-            self._bn_bwd(b.c2, b.dz, B, False)
-            self._conv_bwd(b.c2, b.a1, b.da1, B)
-            self._bn_bwd(b.c1, b.da1, B, True)
-            self._conv_bwd(b.c1, b.x_in, dx, B)
+            for j in range(len(b.main) - 1, -1, -1):
+                c = b.main[j]
+                last = j == len(b.main) - 1
+                self._bn_bwd(c, b.dz if last else b.dacts[j], B, not last)
+                self._conv_bwd(c, b.acts[j - 1] if j > 0 else b.x_in, b.dacts[j - 1] if j > 0 else dx, B)
             self._tag = f"[{b.name}]"
             if b.ds is not None:
                 self._bn_bwd(b.ds, b.dz, B, False)

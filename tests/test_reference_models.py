@@ -57,6 +57,9 @@ def test_3d_models_are_drop_in():
     ours = V.resnet3d_18(1, in_shape=(193, 160, 160))
     ref = R.ResNet_l3(R.BasicBlock, [2, 2, 2], num_classes=1)
     _same(ours, ref, x9216, atol=1e-4, pick=first)
+    # bottleneck blocks (salient_models.py:45-81): the reference's FC is 9216 * expansion, the same input shape fits
+    _same(V.resnet3d_bottleneck(1, in_shape=(193, 160, 160), layers=(1, 1, 1)), R.ResNet_l3(R.Bottleneck, [1, 1, 1], num_classes=1), x9216,
+          atol=1e-4, pick=first)
 
 
 def test_group_norm_layers_match_reference():

@@ -20,12 +20,15 @@ def _rel(a, b):
     return (a - b).norm().item() / (b.norm().item() + 1e-30)
 
 
-def _pair(B, shape=SHAPE):
+KINDS = ["basic", "bottleneck"]
+
+
+def _pair(B, shape=SHAPE, kind="basic"):
     from neuroimagedisttraining_b200.fl.engine import TorchEngine
-    from neuroimagedisttraining_b200.models.volumetric import resnet3d_18
+    from neuroimagedisttraining_b200.models.volumetric import resnet3d_18, resnet3d_bottleneck
     from neuroimagedisttraining_b200.ops.engines import make_native_engine
     torch.manual_seed(11)
-    model = resnet3d_18(1, shape)
+    model = resnet3d_18(1, shape) if kind == "basic" else resnet3d_bottleneck(1, shape, layers=(2, 1, 1))
     # non-trivial BN affine parameters so the test sees them
     for m in model.modules():
         if isinstance(m, torch.nn.BatchNorm3d):
@@ -44,11 +47,12 @@ def _batch(B, shape=SHAPE, seed=0):
     return x, y
 
 
-def test_resnet_backward_chain_is_exact_per_op():
+@pytest.mark.parametrize("kind", KINDS)
+def test_resnet_backward_chain_is_exact_per_op(kind):
     """Each backward kernel on the engine's own saved bf16 tensors against fp32 autograd of the same op."""
     torch.backends.cudnn.allow_tf32 = False
     B = 4
-    eng, _ = _pair(B)
+    eng, _ = _pair(B, kind=kind)
     slab = eng.new_slab()
     eng.attach(slab)
     x, y = _batch(B)
@@ -78,9 +82,13 @@ def test_resnet_backward_chain_is_exact_per_op():
         # gate
         ref_dz = torch.where(b.out[:B] > 0, b.dout[:B], torch.zeros_like(b.dout[:B]))
         assert torch.equal(ref_dz, b.dz[:B]), f"gate {b.name}"
-        g_a1 = check_conv_bn(b.c2, _cf(b.a1[:B]).float(), b.dz, False, True, b.name + ".c2")
-        assert _rel(_cf(b.da1[:B]), g_a1) < 5e-3, f"da1 {b.name}"
-        g_x = check_conv_bn(b.c1, xin, b.da1, True, True, b.name + ".c1")
+        n_main = len(b.main)
+        assert n_main == (2 if kind == "basic" else 3)
+        for j in range(n_main - 1, 0, -1):
+            g_a = check_conv_bn(b.main[j], _cf(b.acts[j - 1][:B]).float(), b.dz if j == n_main - 1 else b.dacts[j], j < n_main - 1, True,
+                                f"{b.name}.c{j + 1}")
+            assert _rel(_cf(b.dacts[j - 1][:B]), g_a) < 5e-3, f"da{j} {b.name}"
+        g_x = check_conv_bn(b.main[0], xin, b.dacts[0], True, True, b.name + ".c1")
         if b.ds is not None:
             g_x = g_x + check_conv_bn(b.ds, xin, b.dz, False, True, b.name + ".ds")
         else:
@@ -99,9 +107,10 @@ def test_resnet_backward_chain_is_exact_per_op():
     torch.testing.assert_close(eng.feat[:B], feat, rtol=1e-5, atol=1e-5)
 
 
-def test_resnet_end_to_end_vs_fp32_autograd():
+@pytest.mark.parametrize("kind", KINDS)
+def test_resnet_end_to_end_vs_fp32_autograd(kind):
     B = 4
-    eng, ref = _pair(B)
+    eng, ref = _pair(B, kind=kind)
     slab = eng.new_slab()
     slab2 = slab.clone()
     eng.attach(slab)
@@ -129,10 +138,11 @@ def test_resnet_end_to_end_vs_fp32_autograd():
     torch.testing.assert_close(eng.logits(x), z, rtol=5e-2, atol=5e-2)
 
 
-def test_resnet_trains_evaluates_and_handles_partial_batches():
+@pytest.mark.parametrize("kind", KINDS)
+def test_resnet_trains_evaluates_and_handles_partial_batches(kind):
     from neuroimagedisttraining_b200.fl.engine import EvalCounters, StepHParams
     B = 4
-    eng, _ = _pair(B)
+    eng, _ = _pair(B, kind=kind)
     slab = eng.new_slab()
     eng.attach(slab)
     x, y = _batch(B, seed=1)
@@ -153,12 +163,13 @@ def test_resnet_trains_evaluates_and_handles_partial_batches():
     assert torch.isfinite(slab.flat).all()
 
 
-def test_resnet_abcd_shape_step_runs():
-    """One step at the ABCD shape (the FC is sized from the input: 3072 features)."""
+@pytest.mark.parametrize("kind", KINDS)
+def test_resnet_abcd_shape_step_runs(kind):
+    """One step at the ABCD shape (the FC is sized from the input: 3072 features, 4x that with bottleneck blocks)."""
     from neuroimagedisttraining_b200.fl.engine import StepHParams
     B = 2
-    eng, _ = _pair(B, (121, 145, 121))
-    assert eng.F == 3072
+    eng, _ = _pair(B, (121, 145, 121), kind=kind)
+    assert eng.F == (3072 if kind == "basic" else 4 * 3072)
     slab = eng.new_slab()
     eng.attach(slab)
     x, y = _batch(B, (121, 145, 121))
