@@ -107,6 +107,15 @@ int nidt_bn_relu_pool3_fwd_amax(const void* y, void* a, void* ymax, void* amax, 
 int nidt_bn_relu_pool3_bwd_stats(const void* ymax, const void* da, int N, int D, int H, int W, int C, const float* scale,
                                  const float* shift, const float* mean, const float* invstd, float* partials, float* c12,
                                  float* dgamma, float* dbeta, int relu, void* stream);
+/* the three launches of nidt_bn_relu_pool_bwd one at a time (phases: 1 = reduce -> *rows_out rows of [2][C] partial sums in `partials`,
+ * 4 = apply with the c12 given), with nidt_bn_bwd_finalize between them: data-parallel training of one client all-reduces the partial
+ * sums over its ranks before the finalisation (ref: the SyncBN of fedml_api/model/cv/batchnorm_utils.py:150-237) */
+int nidt_bn_relu_pool_bwd_phases(const void* y, const void* ymax, const void* da, void* dy, int N, int D, int H, int W, int C, int pk,
+                                 int ps, const float* scale, const float* shift, const float* mean, const float* invstd,
+                                 float* partials, float* c12, float* dgamma, float* dbeta, int relu, int phases, int* rows_out,
+                                 void* stream);
+int nidt_bn_bwd_finalize(const float* partials /*[rows][2][C]*/, int rows, int C, double count, float* c12, float* dgamma /*opt*/,
+                         float* dbeta /*opt*/, void* stream);
 int nidt_bn_finalize(const float* partials /*[T][2][C]*/, int T, int C, double count, const float* gamma, const float* beta,
                      float* running_mean, float* running_var, float* num_batches, float momentum, float eps, float* scale,
                      float* shift, float* mean, float* invstd, void* stream);

@@ -84,6 +84,9 @@ def add_common_args(p: argparse.ArgumentParser, *, model="3DCNN", dataset="ABCD"
     g.add_argument("--spatial_parallel", action="store_true",
                    help="under torchrun: all ranks train every client together, each holding a depth slab of the activations "
                         "(for volumes / batches that do not fit one device); PyTorch engine")
+    g.add_argument("--data_parallel", action="store_true",
+                   help="under torchrun: all ranks train every client together on the sm_100a engine, each taking 1/world of every "
+                        "mini-batch (BatchNorm statistics and gradients summed over the ranks); for few, large clients")
     g.add_argument("--rescale", action="store_true", help="ABCD: cut the site-ordered data into client_num_in_total equal shards")
     g.add_argument("--correct_eval_loss", action="store_true", help="evaluate BCEWithLogits(logit) instead of the reference's BCEWithLogits(sigmoid(logit))")
     return p
@@ -139,7 +142,14 @@ def setup(args, prefix: str, extra_identity: Optional[list] = None, loss_kind: O
     args.identity = build_identity(args, prefix, extra_identity)
     ctx = init_distributed(device=args.device)
     spatial = bool(getattr(args, "spatial_parallel", False)) and ctx.is_distributed
-    if spatial:
+    data_par = bool(getattr(args, "data_parallel", False)) and ctx.is_distributed
+    if spatial and data_par:
+        raise SystemExit("--spatial_parallel and --data_parallel are alternatives")
+    dp_group = None
+    if data_par:
+        from ..ops.engine_dp import DistGroup
+        dp_group = DistGroup(ctx.group)
+    if spatial or data_par:
         from ..parallel import ReplicatedContext
         ctx = ReplicatedContext.of(ctx)
     device = ctx.device
@@ -173,6 +183,11 @@ def setup(args, prefix: str, extra_identity: Optional[list] = None, loss_kind: O
     if spatial:
         from ..fl.engine import SpatialTorchEngine
         engine = SpatialTorchEngine(model, device, loss_kind=loss_kind, volumetric=store is not None, input_scale=getattr(store, "scale", 1.0))
+    elif data_par:
+        if store is None or device.type != "cuda":
+            raise SystemExit("--data_parallel runs the sm_100a engine: needs CUDA devices and a volumetric dataset (ABCD)")
+        from ..ops.engine_dp import DataParallelB200Engine
+        engine = DataParallelB200Engine(model, device, dp_group, max_batch=args.batch_size, input_scale=store.scale, seed=args.seed)
     elif device.type == "cuda" and args.engine in ("auto", "b200") and store is not None:
         try:
             from ..ops.engines import make_native_engine

@@ -627,12 +627,30 @@ static int bn_relu_pool_fwd_impl(const void* y, void* a, void* ymax, void* amax,
 
 static int bn_relu_pool_bwd_impl(const void* y, const void* ymax, const void* da, void* dy, int N, int D, int H, int W, int C, int pk, int ps,
                                  const float* scale, const float* shift, const float* mean, const float* invstd,
-                                 float* partials, float* c12, float* dgamma, float* dbeta, int relu, int apply, void* stream);
+                                 float* partials, float* c12, float* dgamma, float* dbeta, int relu, int phases, int* rows_out, void* stream);
+constexpr int kBwdReduce = 1, kBwdFinalize = 2, kBwdApply = 4;
 // partials: >= nidt_bn_bwd_grid()*2*C floats.  Sequence: reduce -> finalize -> apply.
 NIDT_API int nidt_bn_relu_pool_bwd(const void* y, const void* ymax, const void* da, void* dy, int N, int D, int H, int W, int C, int pk, int ps,
                                    const float* scale, const float* shift, const float* mean, const float* invstd,
                                    float* partials, float* c12, float* dgamma, float* dbeta, int relu, void* stream) {
-    return bn_relu_pool_bwd_impl(y, ymax, da, dy, N, D, H, W, C, pk, ps, scale, shift, mean, invstd, partials, c12, dgamma, dbeta, relu, 1, stream);
+    return bn_relu_pool_bwd_impl(y, ymax, da, dy, N, D, H, W, C, pk, ps, scale, shift, mean, invstd, partials, c12, dgamma, dbeta, relu, kBwdReduce | kBwdFinalize | kBwdApply, nullptr, stream);
+}
+// The same three launches one at a time, for callers that put a cross-device sum between them (data-parallel training of one client:
+// the per-channel partial sums are all-reduced over the ranks before the finalisation, ops/engine_dp.py).  phases: 1 = reduce (writes
+// *rows_out rows of 2*C partial sums), 2 = finalise `rows` rows with `count` elements per channel, 4 = apply.
+NIDT_API int nidt_bn_relu_pool_bwd_phases(const void* y, const void* ymax, const void* da, void* dy, int N, int D, int H, int W, int C, int pk,
+                                          int ps, const float* scale, const float* shift, const float* mean, const float* invstd,
+                                          float* partials, float* c12, float* dgamma, float* dbeta, int relu, int phases, int* rows_out,
+                                          void* stream) {
+    NIDT_REQUIRE(phases == kBwdReduce || phases == kBwdApply, "nidt_bn_relu_pool_bwd_phases: phases=%d (1 = reduce, 4 = apply)", phases);
+    return bn_relu_pool_bwd_impl(y, ymax, da, dy, N, D, H, W, C, pk, ps, scale, shift, mean, invstd, partials, c12, dgamma, dbeta, relu, phases,
+                                 rows_out, stream);
+}
+NIDT_API int nidt_bn_bwd_finalize(const float* partials, int rows, int C, double count, float* c12, float* dgamma, float* dbeta, void* stream) {
+    NIDT_REQUIRE(rows >= 1 && C >= 1 && count > 0 && c12 != nullptr, "nidt_bn_bwd_finalize: rows=%d C=%d", rows, C);
+    bn_bwd_finalize_kernel<<<(C + 31) / 32, 256, 0, (cudaStream_t)stream>>>(partials, rows, C, count, c12, dgamma, dbeta);
+    NIDT_LAUNCH_CHECK();
+    return 0;
 }
 // pool 3/3 with ymax: only the reductions (c12 = the two BatchNorm-backward means, dgamma, dbeta) -- dY itself is then formed on the
 // fly by the consumer (nidt_conv_in_s2d_wgrad_fused) instead of being written to and read back from HBM
@@ -640,11 +658,11 @@ NIDT_API int nidt_bn_relu_pool3_bwd_stats(const void* ymax, const void* da, int 
                                           const float* shift, const float* mean, const float* invstd, float* partials, float* c12,
                                           float* dgamma, float* dbeta, int relu, void* stream) {
     NIDT_REQUIRE(ymax != nullptr, "nidt_bn_relu_pool3_bwd_stats: ymax is null");
-    return bn_relu_pool_bwd_impl(nullptr, ymax, da, nullptr, N, D, H, W, C, 3, 3, scale, shift, mean, invstd, partials, c12, dgamma, dbeta, relu, 0, stream);
+    return bn_relu_pool_bwd_impl(nullptr, ymax, da, nullptr, N, D, H, W, C, 3, 3, scale, shift, mean, invstd, partials, c12, dgamma, dbeta, relu, kBwdReduce | kBwdFinalize, nullptr, stream);
 }
 static int bn_relu_pool_bwd_impl(const void* y, const void* ymax, const void* da, void* dy, int N, int D, int H, int W, int C, int pk, int ps,
                                  const float* scale, const float* shift, const float* mean, const float* invstd,
-                                 float* partials, float* c12, float* dgamma, float* dbeta, int relu, int apply, void* stream) {
+                                 float* partials, float* c12, float* dgamma, float* dbeta, int relu, int phases, int* rows_out, void* stream) {
     NIDT_REQUIRE(C % 8 == 0 && C <= 2048, "nidt_bn_relu_pool_bwd: unsupported C=%d", C);
     BlockGeom g = make_geom(N, D, H, W, C, pk, ps);
     const int CG = C / 8;
@@ -659,12 +677,17 @@ static int bn_relu_pool_bwd_impl(const void* y, const void* ymax, const void* da
         const int64_t npos = (int64_t)N * g.Dp * g.Hp * g.Wp;
         int rgrid = (int)((npos + PB - 1) / PB);
         if (rgrid > grid) rgrid = grid;
-        bn_pool3_bwd_reduce_kernel<<<rgrid, threads, smem, s>>>((const __nv_bfloat16*)ymax, (const __nv_bfloat16*)da, npos, C, scale, shift, mean,
-                                                               invstd, partials, relu);
-        NIDT_LAUNCH_CHECK();
-        bn_bwd_finalize_kernel<<<(C + 31) / 32, 256, 0, s>>>(partials, rgrid, C, count, c12, dgamma, dbeta);
-        NIDT_LAUNCH_CHECK();
-        if (!apply) return 0;
+        if (phases & kBwdReduce) {
+            bn_pool3_bwd_reduce_kernel<<<rgrid, threads, smem, s>>>((const __nv_bfloat16*)ymax, (const __nv_bfloat16*)da, npos, C, scale, shift, mean,
+                                                                   invstd, partials, relu);
+            NIDT_LAUNCH_CHECK();
+            if (rows_out) *rows_out = rgrid;
+        }
+        if (phases & kBwdFinalize) {
+            bn_bwd_finalize_kernel<<<(C + 31) / 32, 256, 0, s>>>(partials, rgrid, C, count, c12, dgamma, dbeta);
+            NIDT_LAUNCH_CHECK();
+        }
+        if (!(phases & kBwdApply)) return 0;
         static const int bwd_v = [] { const char* e = getenv("NIDT_BWD_V"); return e ? atoi(e) : 4; }();
         if (bwd_v == 8) {
             const int64_t total8 = (int64_t)N * ((D + 2) / 3) * ((H + 2) / 3) * ((W + 2) / 3) * (C / 8);
@@ -681,11 +704,17 @@ static int bn_relu_pool_bwd_impl(const void* y, const void* ymax, const void* da
         NIDT_LAUNCH_CHECK();
         return 0;
     }
-    bn_relu_pool_bwd_kernel<false><<<grid, threads, smem, s>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)da, nullptr, g, scale, shift,
-                                                               mean, invstd, nullptr, partials, relu);
-    NIDT_LAUNCH_CHECK();
-    bn_bwd_finalize_kernel<<<(C + 31) / 32, 256, 0, s>>>(partials, grid, C, count, c12, dgamma, dbeta);
-    NIDT_LAUNCH_CHECK();
+    if (phases & kBwdReduce) {
+        bn_relu_pool_bwd_kernel<false><<<grid, threads, smem, s>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)da, nullptr, g, scale, shift,
+                                                                   mean, invstd, nullptr, partials, relu);
+        NIDT_LAUNCH_CHECK();
+        if (rows_out) *rows_out = grid;
+    }
+    if (phases & kBwdFinalize) {
+        bn_bwd_finalize_kernel<<<(C + 31) / 32, 256, 0, s>>>(partials, grid, C, count, c12, dgamma, dbeta);
+        NIDT_LAUNCH_CHECK();
+    }
+    if (!(phases & kBwdApply)) return 0;
     bn_relu_pool_bwd_kernel<true><<<grid, threads, 0, s>>>((const __nv_bfloat16*)y, (const __nv_bfloat16*)da, (__nv_bfloat16*)dy, g, scale, shift,
                                                            mean, invstd, c12, nullptr, relu);
     NIDT_LAUNCH_CHECK();

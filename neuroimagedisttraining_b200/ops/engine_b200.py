@@ -38,6 +38,8 @@ def _declare(lib) -> None:
         "nidt_bn_eval_prepare": [i32, vp, vp, vp, vp, f32, vp, vp, vp],
         "nidt_bn_relu_pool_fwd": [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp, i32, vp],
         "nidt_bn_relu_pool_bwd": [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, vp],
+        "nidt_bn_relu_pool_bwd_phases": [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, vp, vp],
+        "nidt_bn_bwd_finalize": [vp, i32, i32, f64, vp, vp, vp, vp],
         "nidt_head_fwd_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, u64, i32, i32, vp],
         "nidt_conv3d_fprop_tc": [vp, vp, vp, vp, vp] + [i32] * 17 + [vp],
         "nidt_conv3d_m_tiles": [i32] * 8,
@@ -193,6 +195,7 @@ class B200Engine:
         self._tag = ""
         self.use_s2d = use_s2d
         self.s2d_wgrad = True
+        self._seed_extra = 0
         self._alloc(wgrad_ctas)
         # native step executor (csrc/executor.cu): one C call per step instead of one per kernel; NIDT_PY_EXEC=1 keeps the
         # Python launch loop (it is also what start_profile() switches to, for per-kernel timings)
@@ -401,7 +404,8 @@ class B200Engine:
             rm, rv = self._p(slab, s.bn + ".running_mean"), self._p(slab, s.bn + ".running_var")
             if train:
                 tiles = b.stats_tiles if (i == 0 or B == self.max_batch) else lib.nidt_conv3d_m_tiles(B, D, H, W, *b.cur_box)
-                self._chk(lib.nidt_bn_finalize(b.stats.data_ptr(), tiles, s.cout, float(B * D * H * W), g, be, rm, rv,
+                stats_ptr, tiles, count = self._bn_batch_sums(b, tiles, float(B * D * H * W))
+                self._chk(lib.nidt_bn_finalize(stats_ptr, tiles, s.cout, count, g, be, rm, rv,
                                                self._p(slab, s.bn + ".num_batches_tracked"), 0.1, 1e-5, b.scale.data_ptr(), b.shift.data_ptr(),
                                                b.mean.data_ptr(), b.invstd.data_ptr(), st), "bn_finalize")
             else:
@@ -427,7 +431,8 @@ class B200Engine:
             gp(h.fc1 + ".weight"), gp(h.fc1 + ".bias"), gp(h.fc2 + ".weight"), gp(h.fc2 + ".bias"),
             last.da.data_ptr() if train else None, self.loss_acc.data_ptr() if train else None,
             counters.buf.data_ptr() if counters is not None else None, self.eval_logits.data_ptr(),
-            B, self.head_S, self.head_C, h.hidden, float(h.p_drop), self.seed + 7919 * self.step, int(train), int(double_sigmoid), st),
+            B, self.head_S, self.head_C, h.hidden, float(h.p_drop), self.seed + 7919 * self.step + self._seed_extra, int(train),
+            int(double_sigmoid), st),
             "head_fwd_bwd")
         native.count_launches(1)
 
@@ -452,11 +457,7 @@ class B200Engine:
                           "conv_in_s2d_wgrad_fused")
                 native.count_launches(4)
                 continue
-            self._chk(lib.nidt_bn_relu_pool_bwd(b.y.data_ptr(), b.ymax.data_ptr() if b.ymax is not None else None, b.da.data_ptr(), b.dy.data_ptr(), B, D, H, W, s.cout, s.pool_k, s.pool_s,
-                                                b.scale.data_ptr(), b.shift.data_ptr(), b.mean.data_ptr(), b.invstd.data_ptr(),
-                                                b.bwd_partials.data_ptr(), b.c12.data_ptr(), self._p(self.grad, s.bn + ".weight"),
-                                                self._p(self.grad, s.bn + ".bias"), int(s.relu), st), "bn_relu_pool_bwd")
-            native.count_launches(3)
+            self._bn_backward(b, B)
             iD, iH, iW = b.in_dhw
             if i == 0:
                 gb = self._p(self.grad, s.conv + ".bias") if s.bias else None
@@ -482,6 +483,22 @@ class B200Engine:
             # Conv bias gradients: block 0 gets sum(dY) for free from the bias column of its wgrad GEMM.  For the
             # other blocks it is identically zero in exact arithmetic (BatchNorm subtracts the batch mean right
             # after the conv): the grad slab keeps 0 there, weight decay still applies in the update.
+
+    def _bn_batch_sums(self, b: _Block, tiles: int, count: float):
+        """(pointer, rows, elements per channel) of the [rows][2][C] partial sums the BatchNorm finalisation reads: the conv epilogue's
+        per-tile sums of this device's batch (the data-parallel engine replaces them with the sums over all ranks)."""
+        return b.stats.data_ptr(), tiles, count
+
+    def _bn_backward(self, b: _Block, B: int) -> None:
+        """dY of a block from d(pooled activation): BatchNorm + ReLU + MaxPool backward, BN weight / bias gradients into the slab."""
+        s = b.spec
+        D, H, W = b.c_dhw
+        self._chk(self.lib.nidt_bn_relu_pool_bwd(b.y.data_ptr(), b.ymax.data_ptr() if b.ymax is not None else None, b.da.data_ptr(), b.dy.data_ptr(),
+                                                 B, D, H, W, s.cout, s.pool_k, s.pool_s, b.scale.data_ptr(), b.shift.data_ptr(), b.mean.data_ptr(),
+                                                 b.invstd.data_ptr(), b.bwd_partials.data_ptr(), b.c12.data_ptr(),
+                                                 self._p(self.grad, s.bn + ".weight"), self._p(self.grad, s.bn + ".bias"), int(s.relu),
+                                                 self._stream()), "bn_relu_pool_bwd")
+        native.count_launches(3)
 
     # ---------------------------------------------------------------------------- public API
     def compute_grads(self, x, y, train_mode: bool = True) -> torch.Tensor:

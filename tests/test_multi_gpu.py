@@ -82,6 +82,16 @@ def test_dpsgd_neighbour_averaging_over_the_peer_arena_matches_broadcasts():
     assert "RESULT ok=True" in r.stdout, r.stdout[-2000:]
 
 
+@pytest.mark.gpu
+def test_native_data_parallel_engine_over_nccl_matches_whole_batches():
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    r = _torchrun("dist_worker_dp_gpu.py", min(n, 3), timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "RESULT ok=True" in r.stdout, r.stdout[-2000:]
+
+
 def test_spatial_parallel_cli_run_equals_the_single_process_run(tmp_path):
     """``--spatial_parallel`` under torchrun (2 gloo ranks): both ranks train every client together on depth slabs; the checkpointed
     global model and the accuracy series equal the plain one-process run; only the real rank 0 writes files."""
