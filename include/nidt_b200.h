@@ -231,6 +231,24 @@ int nidt_linear_head_fwd_bwd(const float* feat, const float* y, const float* W1,
                              float* loss_acc, double* eval_counters, float* logits_out, int B, int F, int Hd, int train,
                              int double_sigmoid, void* stream);
 
+/* ------------------------------------------- first-layer weight gradient from pooled tensors + cached input Gram matrices (conv_in_alg.cu) */
+/* dW of Conv3d(1,64,5,stride 2) -> BN -> ReLU -> MaxPool(3,3) without reading y or writing dY: the dense part of the gradient is a
+ * product with the Gram matrix of the INPUT patches (128 x 128 fp32 per sample, tap 125 = constant 1), which depends on the volume
+ * only and is computed once per sample; per step only one patch per pooling window and channel is touched.  rows / slots are HOST
+ * int arrays (<= nidt_conv_in_gram_max_samples()).  ref: autograd through salient_models.py:147-150. */
+int nidt_conv_in_gram_floats(void);
+int nidt_conv_in_gram_max_samples(void);
+int nidt_conv_in_alg_grid(void);
+int64_t nidt_conv_in_gram_scratch_floats(int n, int Di);
+int64_t nidt_conv_in_alg_scratch_floats(void);
+int nidt_conv_in_gram_samples(const void* x_u8, const int* rows, const int* slots, int n, float* cache, float* scratch, int Di, int Hi, int Wi,
+                              float scale, void* stream);
+int nidt_conv_in_gram_sum(const float* cache, const int* slots, int n, double* gb, void* stream);
+int nidt_conv_in_alg_wgrad(const void* x_u8, const void* amax, const void* da, const float* W, const float* bias, const float* bn_scale,
+                           const float* mean, const float* invstd, const float* c12, const double* gb, float* grad_w, float* grad_b,
+                           float* scratch, int N, int Di, int Hi, int Wi, float scale, const float* sal_w, float* sal_scores,
+                           float sal_scale, void* stream);
+
 /* ------------------------------------------------------- native step executor (executor.cu) */
 /* One call runs a whole forward / training step / evaluation batch of a conv-BN-ReLU-pool stack + the classifier head: the
  * ~45 kernel launches of a step are issued from native code instead of one Python -> C transition each (host time per step
@@ -246,7 +264,11 @@ typedef struct {
     float* wg_scratch;
     int stats_tiles, s2d, block_n, dgrad_block_n, splits;
     int box[4], dbox[4];                                  /* M-tile boxes (bw,bh,bd,bn) of fprop/wgrad and of dgrad at max_batch */
-    void* amax;                                           /* block 0, optional: winning pool taps (uint8) -> fused BN-backward + wgrad */
+    void* amax;                                           /* block 0, optional: winning pool taps (uint8), written by the forward when bwd0_mode != 0 */
+    double* gram;                                         /* block 0, bwd0_mode 2: the batch's patch Gram matrix (nidt_conv_in_gram_sum) */
+    float* alg_scratch;                                   /* block 0, bwd0_mode 2: nidt_conv_in_alg_scratch_floats() floats */
+    int bwd0_mode;                                        /* block 0 backward: 0 = dY written, then wgrad; 1 = dY formed inside the wgrad kernel
+                                                             (nidt_conv_in_s2d_wgrad_fused); 2 = no pass over y / dY at all (nidt_conv_in_alg_wgrad) */
 } nidt_block_t;
 typedef struct {
     int n_blocks, max_batch;

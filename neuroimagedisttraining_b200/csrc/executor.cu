@@ -66,6 +66,7 @@ struct Ctx {
     const float* sal_w = nullptr;         // SNIP pass: slab base (weights), score slab and scale for the wgrad saliency epilogues
     float* sal_scores = nullptr;
     float sal_scale = 0.f;
+    const float* w_slab = nullptr;        // the slab the forward ran with (the algebraic first-layer gradient reads W and b again)
 };
 
 int pack_weights(Ctx& c, const float* slab) {
@@ -86,6 +87,7 @@ int pack_weights(Ctx& c, const float* slab) {
 int forward(Ctx& c, const void* x, float* slab, bool train) {
     const nidt_plan_t* p = c.p;
     const int B = c.B;
+    c.w_slab = slab;
     const void* prev = nullptr;
     for (int i = 0; i < p->n_blocks; ++i) {
         const nidt_block_t& b = p->blocks[i];
@@ -108,7 +110,7 @@ int forward(Ctx& c, const void* x, float* slab, bool train) {
         else
             NIDT_TRY(nidt_bn_eval_prepare(b.cout, at(slab, b.off_gamma), at(slab, b.off_beta), at(slab, b.off_rm), at(slab, b.off_rv), 1e-5f, b.scale,
                                           b.shift, c.st));
-        if (train && i == 0 && b.amax != nullptr && b.ymax != nullptr && b.s2d && b.pool_k == 3 && b.pool_s == 3)
+        if (train && i == 0 && b.bwd0_mode != 0 && b.amax != nullptr && b.ymax != nullptr && b.s2d && b.pool_k == 3 && b.pool_s == 3)
             NIDT_TRY(nidt_bn_relu_pool3_fwd_amax(b.y, b.a, b.ymax, b.amax, B, b.c_d, b.c_h, b.c_w, b.cout, b.scale, b.shift, b.relu, c.st));
         else
             NIDT_TRY(nidt_bn_relu_pool_fwd(b.y, b.a, (train && b.ymax != nullptr) ? b.ymax : nullptr, B, b.c_d, b.c_h, b.c_w, b.cout, b.pool_k, b.pool_s,
@@ -144,7 +146,21 @@ int backward(Ctx& c, const void* x, float* grad) {
     const int B = c.B;
     for (int i = p->n_blocks - 1; i >= 0; --i) {
         const nidt_block_t& b = p->blocks[i];
-        if (i == 0 && b.amax != nullptr && b.ymax != nullptr && b.s2d && b.pool_k == 3 && b.pool_s == 3) {
+        if (i == 0 && b.bwd0_mode == 2 && b.amax != nullptr && b.ymax != nullptr && b.gram != nullptr && b.alg_scratch != nullptr && b.s2d &&
+            b.pool_k == 3 && b.pool_s == 3 && b.cout == 64) {
+            // first block, algebraic form: BatchNorm-backward reductions over the pooled tensors, then the weight gradient from one
+            // input patch per pooling window + the cached Gram matrix of the batch's input patches; y and dY are not touched
+            NIDT_TRY(nidt_bn_relu_pool3_bwd_stats(b.ymax, b.da, B, b.c_d, b.c_h, b.c_w, b.cout, b.scale, b.shift, b.mean, b.invstd, b.bwd_partials,
+                                                  b.c12, at(grad, b.off_gamma), at(grad, b.off_beta), b.relu, c.st));
+            const bool sal = c.sal_scores != nullptr;
+            NIDT_TRY(nidt_conv_in_alg_wgrad(x, b.amax, b.da, at(c.w_slab, b.off_w), b.has_bias ? at(c.w_slab, b.off_b) : nullptr, b.scale, b.mean,
+                                            b.invstd, b.c12, b.gram, at(grad, b.off_w), b.has_bias ? at(grad, b.off_b) : nullptr, b.alg_scratch, B,
+                                            b.in_d, b.in_h, b.in_w, p->input_scale, sal ? at(c.sal_w, b.off_w) : nullptr,
+                                            sal ? at(c.sal_scores, b.off_w) : nullptr, c.sal_scale, c.st));
+            c.launches += 4;
+            continue;
+        }
+        if (i == 0 && b.bwd0_mode == 1 && b.amax != nullptr && b.ymax != nullptr && b.s2d && b.pool_k == 3 && b.pool_s == 3) {
             // first block: only the BatchNorm-backward reductions run as kernels of their own; dY is formed inside the weight-gradient
             // kernel from y, the winning taps and da (never written to HBM)
             float* gb = b.has_bias ? at(grad, b.off_b) : nullptr;
@@ -267,7 +283,8 @@ NIDT_API int nidt_plan_train_step_graph(const nidt_plan_t* plan, const void* x_u
     int device = 0;
     NIDT_CUDA_CHECK(cudaGetDevice(&device));
     float* mom_used = (do_update && momentum != 0.f) ? mom : nullptr;
-    const GraphKey key{plan, x_u8, y, slab, grad, mom_used, do_update ? mask : nullptr, dyn, n_params, batch, 0, do_update, device};
+    const GraphKey key{plan, x_u8, y, slab, grad, mom_used, do_update ? mask : nullptr, dyn, n_params, batch, 0,
+                       do_update | (plan->blocks[0].bwd0_mode << 1), device};
     nidt_dyn_t v{lr, momentum, wd, clip_norm, first_step, 0, seed, loss_acc, nullptr};
     const nidt_plan_t snap = *plan;       // the launch sequence bakes the plan's buffers in by value
     return replay(key, v, dyn, launches, stream, [&](void* st, int* n) -> int {

@@ -195,6 +195,13 @@ class SlabTrainer(ModelTrainer):
                     yield b
         return index_stream(), tags
 
+    def _announce_ids(self, data) -> None:
+        """Tell the engine which samples (ids in the volume store) the batch it is about to train on holds, in row order: engines
+        that cache per-sample quantities (``B200Engine``: Gram matrices of the first layer's input patches) key them on these."""
+        if hasattr(self.engine, "batch_ids") and self.store is not None and hasattr(data, "indices"):
+            st = self._stagers.get(data.batch_size) if hasattr(self, "_stagers") else None
+            self.engine.batch_ids = getattr(st, "last_ids", None) if st is not None else None
+
     def _batches_epochs(self, data, epochs: int, lookahead_data=None):
         """``(epoch, x, y)`` over ``epochs`` passes of ``data``.  Client staging: the loader's volumes are uploaded once (ahead of
         time when :meth:`plan_data` announced them) and every epoch's batches are gathered on the device.  Stream staging: ONE
@@ -456,6 +463,7 @@ class SlabTrainer(ModelTrainer):
             if epoch != cur:
                 end_epoch(cur)
                 cur = epoch
+            self._announce_ids(train_data)
             if grad_mask:
                 self.engine.train_step(x, y, hp, None, mom, first, grad_mask=mslab.flat if mslab is not None else None)
             else:

@@ -87,6 +87,19 @@ def _declare(lib) -> None:
     lib.nidt_plan_graph_clear.restype = i32
     lib.nidt_plan_graph_count.argtypes = []
     lib.nidt_plan_graph_count.restype = i32
+    for name in ("nidt_conv_in_gram_floats", "nidt_conv_in_gram_max_samples", "nidt_conv_in_alg_grid"):
+        getattr(lib, name).argtypes = []
+        getattr(lib, name).restype = i32
+    lib.nidt_conv_in_gram_scratch_floats.argtypes = [i32, i32]
+    lib.nidt_conv_in_gram_scratch_floats.restype = i64
+    lib.nidt_conv_in_alg_scratch_floats.argtypes = []
+    lib.nidt_conv_in_alg_scratch_floats.restype = i64
+    lib.nidt_conv_in_gram_samples.argtypes = [vp, vp, vp, i32, vp, vp, i32, i32, i32, f32, vp]
+    lib.nidt_conv_in_gram_samples.restype = i32
+    lib.nidt_conv_in_gram_sum.argtypes = [vp, vp, i32, vp, vp]
+    lib.nidt_conv_in_gram_sum.restype = i32
+    lib.nidt_conv_in_alg_wgrad.argtypes = [vp] * 13 + [i32, i32, i32, i32, f32, vp, vp, f32, vp]
+    lib.nidt_conv_in_alg_wgrad.restype = i32
     for name, argtypes in {
         "nidt_ew_bf16": [vp, vp, vp, i64, i32, vp],
         "nidt_maxpool3d_fwd": [vp, vp, vp] + [i32] * 8 + [vp],
@@ -116,7 +129,8 @@ class _BlockC(C.Structure):
                 + [(n, C.c_void_p) for n in ("y", "dy", "a", "da", "ymax", "scale", "shift", "mean", "invstd", "c12", "bwd_partials", "stats",
                                              "wf", "wd", "wg_scratch")]
                 + [(n, C.c_int) for n in ("stats_tiles", "s2d", "block_n", "dgrad_block_n", "splits")]
-                + [("box", C.c_int * 4), ("dbox", C.c_int * 4), ("amax", C.c_void_p)])
+                + [("box", C.c_int * 4), ("dbox", C.c_int * 4), ("amax", C.c_void_p), ("gram", C.c_void_p), ("alg_scratch", C.c_void_p),
+                   ("bwd0_mode", C.c_int)])
 
 
 class _PlanC(C.Structure):
@@ -148,6 +162,70 @@ def choose_box(W: int, H: int, D: int, N: int, max_rows: int = 128) -> Tuple[int
                 if key > best_key:
                     best, best_key = (bw, bh, bd, bn), key
     return best
+
+
+class GramCache:
+    """Per-sample Gram matrices of the first layer's input patches (``csrc/conv_in_alg.cu``), on the device, keyed by the sample's
+    id in the volume store.  They depend on the volume only, so a sample pays for its matrix (~0.2 ms) the first time it is trained
+    on and never again; 64 KiB per sample.  ``NIDT_GRAM_CACHE_MB`` bounds the buffer (default 8192; when full it starts over)."""
+
+    def __init__(self, lib, device, in_shape, scale: float, max_batch: int):
+        self.lib, self.device, self.in_shape, self.scale = lib, device, tuple(in_shape), float(scale)
+        self.floats = lib.nidt_conv_in_gram_floats()
+        self.max_list = lib.nidt_conv_in_gram_max_samples()
+        self.limit = max(64, (int(os.environ.get("NIDT_GRAM_CACHE_MB", "8192")) << 20) // (4 * self.floats))
+        self.slots: dict = {}
+        self.cap = 0
+        self.buf: Optional[torch.Tensor] = None
+        self.scratch: Optional[torch.Tensor] = None
+        self.scratch_n = 0
+        self.built = 0                                     # matrices computed so far (cold misses)
+        self.batch = torch.zeros(self.floats, dtype=torch.float64, device=device)       # the current batch's sum: a stable address
+
+    def _grow(self, need: int) -> None:
+        cap = min(self.limit, max(256, 2 * self.cap, need))
+        if need > cap:                                     # over the limit: start over (the matrices are recomputed when next seen)
+            self.slots.clear()
+            cap = min(self.limit, max(256, need))
+            self.buf, self.cap = None, 0
+        new = torch.empty((cap, self.floats), dtype=torch.float32, device=self.device)
+        if self.buf is not None and self.slots:
+            new[:self.cap] = self.buf
+        self.buf, self.cap = new, cap
+
+    def sum_for(self, ids, x: torch.Tensor, stream: int) -> bool:
+        """``self.batch`` <- sum of the Gram matrices of the samples ``ids`` (row i of the u8 batch ``x`` is sample ids[i]); computes
+        the ones not seen before.  False when the batch cannot be served (too many samples for one launch)."""
+        n = len(ids)
+        if n == 0 or n > self.max_list or n != x.shape[0]:
+            return False
+        ids = [int(i) for i in ids]
+        miss = [k for k, i in enumerate(ids) if i not in self.slots]
+        if miss:
+            if len(self.slots) + len(miss) > self.cap:
+                self._grow(len(self.slots) + len(miss))
+                miss = [k for k, i in enumerate(ids) if i not in self.slots]
+            first = {}
+            for k in miss:                                 # a sample may occur twice in a batch
+                first.setdefault(ids[k], k)
+            rows = list(first.values())
+            base = len(self.slots)
+            for j, k in enumerate(rows):
+                self.slots[ids[k]] = base + j
+            if self.scratch_n < len(rows):
+                self.scratch_n = max(len(rows), min(self.max_list, x.shape[0]))
+                self.scratch = torch.empty(self.lib.nidt_conv_in_gram_scratch_floats(self.scratch_n, self.in_shape[0]), dtype=torch.float32,
+                                           device=self.device)
+            r = (C.c_int * len(rows))(*rows)
+            s = (C.c_int * len(rows))(*[self.slots[ids[k]] for k in rows])
+            native.check(self.lib.nidt_conv_in_gram_samples(x.data_ptr(), r, s, len(rows), self.buf.data_ptr(), self.scratch.data_ptr(),
+                                                            *self.in_shape, self.scale, stream), "nidt_conv_in_gram_samples")
+            native.count_launches(2)
+            self.built += len(rows)
+        s = (C.c_int * n)(*[self.slots[i] for i in ids])
+        native.check(self.lib.nidt_conv_in_gram_sum(self.buf.data_ptr(), s, n, self.batch.data_ptr(), stream), "nidt_conv_in_gram_sum")
+        native.count_launches(1)
+        return True
 
 
 class _Block:
@@ -196,6 +274,8 @@ class B200Engine:
         self.use_s2d = use_s2d
         self.s2d_wgrad = True
         self._seed_extra = 0
+        self._mode = 0                    # block-0 backward variant of the step being issued by the Python launch loop (see _bwd0_mode)
+        self.batch_ids = None             # store ids of the samples of the NEXT training batch (set by the trainer, consumed by the step)
         self._alloc(wgrad_ctas)
         # native step executor (csrc/executor.cu): one C call per step instead of one per kernel; NIDT_PY_EXEC=1 keeps the
         # Python launch loop (it is also what start_profile() switches to, for per-kernel timings)
@@ -245,8 +325,15 @@ class B200Engine:
                 # (nidt_conv_in_s2d_wgrad_fused: dY never written to HBM).  Bit-identical to the separate kernels, but MEASURED SLOWER
                 # at batch 16 (0.62 + 0.03 ms against 0.247 + 0.235 ms, profiles/profile_step_fused_bwd0.txt): the in-place y -> dY
                 # transform competes with the 8 staging warps for the same issue slots, which this kernel is already bound by.  Off.
-                b.amax = (torch.empty(b.a.shape, dtype=torch.uint8, device=dev)
-                          if (b.s2d and b.ymax is not None and spec.cout == 64 and os.environ.get("NIDT_FUSED_BWD0", "0") == "1") else None)
+                # NIDT_ALG_BWD0 (default on): the backward of this block without any pass over y / dY -- weight gradient from one input
+                # patch per pooling window + the batch's cached patch Gram matrix (csrc/conv_in_alg.cu); used for the steps whose
+                # sample ids the caller supplies (``batch_ids``), the dY-based kernels otherwise.
+                self.fused_bwd0 = os.environ.get("NIDT_FUSED_BWD0", "0") == "1"
+                self.alg_bwd0 = os.environ.get("NIDT_ALG_BWD0", "1") != "0" and b.s2d and b.ymax is not None and spec.cout == 64 and spec.k == 5
+                want_amax = b.s2d and b.ymax is not None and spec.cout == 64 and (self.fused_bwd0 or self.alg_bwd0)
+                b.amax = torch.empty(b.a.shape, dtype=torch.uint8, device=dev) if want_amax else None
+                self.gram = GramCache(lib, dev, in_dhw, self.input_scale, B) if self.alg_bwd0 else None
+                b.alg_scratch = (torch.empty(lib.nidt_conv_in_alg_scratch_floats(), dtype=torch.float32, device=dev) if self.alg_bwd0 else None)
                 n_scr = max(lib.nidt_conv_in_grid() * 128 * 64, lib.nidt_conv_in_s2d_wgrad_scratch_floats())
                 b.wg_scratch = torch.zeros(n_scr, dtype=torch.float32, device=dev)
             else:
@@ -295,6 +382,9 @@ class B200Engine:
             if i == 0:
                 c.s2d = int(b.s2d and self.s2d_wgrad)
                 c.amax = ptr(getattr(b, "amax", None)) if (b.s2d and self.s2d_wgrad) else None
+                if self.alg_bwd0 and c.amax:
+                    c.gram, c.alg_scratch = self.gram.batch.data_ptr(), b.alg_scratch.data_ptr()
+                c.bwd0_mode = 1 if (self.fused_bwd0 and c.amax) else 0
             else:
                 c.wf, c.wd = ptr(b.wf), ptr(b.wd)
                 c.block_n, c.dgrad_block_n, c.splits = b.block_n, b.dgrad_block_n, b.splits
@@ -410,7 +500,7 @@ class B200Engine:
                                                b.mean.data_ptr(), b.invstd.data_ptr(), st), "bn_finalize")
             else:
                 self._chk(lib.nidt_bn_eval_prepare(s.cout, g, be, rm, rv, 1e-5, b.scale.data_ptr(), b.shift.data_ptr(), st), "bn_eval_prepare")
-            if train and i == 0 and getattr(b, "amax", None) is not None and self.s2d_wgrad:
+            if train and i == 0 and self._mode != 0 and getattr(b, "amax", None) is not None and self.s2d_wgrad:
                 self._chk(lib.nidt_bn_relu_pool3_fwd_amax(b.y.data_ptr(), b.a.data_ptr(), b.ymax.data_ptr(), b.amax.data_ptr(), B, D, H, W, s.cout,
                                                           b.scale.data_ptr(), b.shift.data_ptr(), int(s.relu), st), "bn_relu_pool_fwd")
             else:
@@ -443,7 +533,23 @@ class B200Engine:
             s = b.spec
             self._tag = f"[{i}]"
             D, H, W = b.c_dhw
-            if i == 0 and getattr(b, "amax", None) is not None and b.s2d and self.s2d_wgrad:
+            if i == 0 and self._mode == 2:
+                # BatchNorm-backward reductions over the pooled tensors, then the weight gradient from one input patch per pooling
+                # window and the batch's cached patch Gram matrix: no pass over y or dY (csrc/conv_in_alg.cu)
+                iD, iH, iW = b.in_dhw
+                self._chk(lib.nidt_bn_relu_pool3_bwd_stats(b.ymax.data_ptr(), b.da.data_ptr(), B, D, H, W, s.cout, b.scale.data_ptr(), b.shift.data_ptr(),
+                                                           b.mean.data_ptr(), b.invstd.data_ptr(), b.bwd_partials.data_ptr(), b.c12.data_ptr(),
+                                                           self._p(self.grad, s.bn + ".weight"), self._p(self.grad, s.bn + ".bias"), int(s.relu), st),
+                          "bn_pool3_bwd_stats")
+                self._chk(lib.nidt_conv_in_alg_wgrad(self._x.data_ptr(), b.amax.data_ptr(), b.da.data_ptr(), self._p(slab, s.conv + ".weight"),
+                                                     self._p(slab, s.conv + ".bias") if s.bias else None, b.scale.data_ptr(), b.mean.data_ptr(),
+                                                     b.invstd.data_ptr(), b.c12.data_ptr(), self.gram.batch.data_ptr(),
+                                                     self._p(self.grad, s.conv + ".weight"), self._p(self.grad, s.conv + ".bias") if s.bias else None,
+                                                     b.alg_scratch.data_ptr(), B, iD, iH, iW, self.input_scale, None, None, 0.0, st),
+                          "conv_in_alg_wgrad")
+                native.count_launches(4)
+                continue
+            if i == 0 and self._mode == 1 and getattr(b, "amax", None) is not None and b.s2d and self.s2d_wgrad:
                 # BatchNorm-backward reductions, then dY formed inside the weight-gradient kernel (never written to HBM)
                 iD, iH, iW = b.in_dhw
                 self._chk(lib.nidt_bn_relu_pool3_bwd_stats(b.ymax.data_ptr(), b.da.data_ptr(), B, D, H, W, s.cout, b.scale.data_ptr(), b.shift.data_ptr(),
@@ -510,6 +616,7 @@ class B200Engine:
         if self._native_ready():
             self._native_step(x, y, None, None, None, False, do_update=False)
             return self.loss_acc
+        self._mode = self._bwd0_mode(self._check_x(x))
         B = self._forward(x, train=True)
         self._head(B, y, train=True)
         self._backward(B)
@@ -530,6 +637,7 @@ class B200Engine:
             return False
         x = self._check_x(x)
         self._x = x
+        self._plan.blocks[0].bwd0_mode = self._bwd0_mode(x)
         y = y.to(self.device, torch.float32).contiguous()
         native.check(self.lib.nidt_plan_saliency_step(
             C.byref(self._plan), x.data_ptr(), y.data_ptr(), int(x.shape[0]), self.slab.flat.data_ptr(), self.grad.flat.data_ptr(),
@@ -545,9 +653,19 @@ class B200Engine:
         assert x.shape[0] <= self.max_batch and tuple(x.shape[1:]) == self.in_shape
         return x
 
+    def _bwd0_mode(self, x: torch.Tensor) -> int:
+        """Backward variant of block 0 for this batch: 2 (no pass over y / dY) when the sample ids are known, so that the cached Gram
+        matrices can be summed; else 1 (NIDT_FUSED_BWD0) or 0."""
+        ids, self.batch_ids = self.batch_ids, None
+        base = 1 if (self.fused_bwd0 and self._plan.blocks[0].amax) else 0
+        if ids is None or not self.alg_bwd0 or not self.s2d_wgrad or not self._plan.blocks[0].amax:
+            return base
+        return 2 if self.gram.sum_for(ids, x, self._stream()) else base
+
     def _native_step(self, x, y, hp, mask, mom, first_step: bool, do_update: bool) -> None:
         x = self._check_x(x)
         self._x = x
+        self._plan.blocks[0].bwd0_mode = self._bwd0_mode(x)
         n = self.layout.param_numel
         if self.use_graphs:
             native.check(self.lib.nidt_plan_train_step_graph(

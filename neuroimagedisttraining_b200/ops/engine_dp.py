@@ -85,9 +85,8 @@ class DataParallelB200Engine(B200Engine):
 
     def __init__(self, model, device, dp, max_batch: int = 16, **kw):
         super().__init__(model, device, max_batch=max_batch, **kw)
-        if any(getattr(b, "amax", None) is not None for b in self.blocks):
-            raise RuntimeError("data-parallel engine: the fused first-block backward (NIDT_FUSED_BWD0) is not supported")
         self.dp = dp
+        self.alg_bwd0 = self.fused_bwd0 = False      # block 0 backward through dY (the variants without it are single-device paths)
         self.use_graphs = False          # the step is issued launch by launch (cross-rank sums sit between the launches)
         self._dp_f = 1.0                 # this rank's share of the current batch, B_r / B
         self._dp_B = 0                   # whole-batch size of the current step (0 = not inside a split step)

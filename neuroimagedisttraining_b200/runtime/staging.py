@@ -123,6 +123,8 @@ class BatchStager:
         self.h2d_bytes = 0
         self.h2d_copies = 0
         self.gather_launches = 0
+        self.last_ids = None              # store ids of the rows of the batch handed out last, in row order (engines key per-sample caches on them)
+        self._slot_ids = {}
         self.fixed_output = False         # True: every batch is gathered into ONE buffer (stable addresses for CUDA-graph replays)
         self._row_bytes = int(np.prod(store.shape))
         self.max_cache_rows = max(1, max_cache_bytes // self._row_bytes)
@@ -255,6 +257,7 @@ class BatchStager:
         if self.sort_indices:
             ids = np.sort(ids)
         b = len(ids)
+        self._slot_ids[slot] = ids
         with torch.cuda.stream(self.copy_stream):
             self.copy_stream.wait_event(self.consumed[slot])
             if self._pinned_cache is not None and self._kernel_blocks > 0:
@@ -287,6 +290,7 @@ class BatchStager:
                 if self.sort_indices:
                     ids = np.sort(ids)
                 x, y = self.store.fetch(ids)
+                self.last_ids = ids
                 yield x, y
             return
         if not self._ring_ready:
@@ -324,6 +328,7 @@ class BatchStager:
                             pass
             s, n = pending.pop(0)
             cur.wait_event(self.ready[s])
+            self.last_ids = self._slot_ids.get(s)
             yield self.dev_x[s][:n], self.dev_y[s][:n]
             self.consumed[s].record(cur)
 
@@ -438,6 +443,7 @@ class BatchStager:
         pos = self._positions(ent, loader, ids)
         n = len(pos)
         slot = ent.slot
+        self.last_ids = ids
         if not self.fixed_output and n > 0 and int(pos[-1]) - int(pos[0]) == n - 1 and (n == 1 or bool(np.all(np.diff(pos) == 1))):
             p0 = int(pos[0])
             return slot.x[p0:p0 + n], slot.y[p0:p0 + n]

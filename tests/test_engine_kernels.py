@@ -260,7 +260,7 @@ def test_engine_backward_chain_is_exact_per_block():
         if s.pool_k:
             o = F.max_pool3d(o, s.pool_k, s.pool_s)
         o.backward(_cf(b.da[:B]).float())
-        fused0 = i == 0 and getattr(b, "amax", None) is not None     # block 0: dY exists only inside the fused weight-gradient kernel
+        fused0 = i == 0 and getattr(eng, "fused_bwd0", False)       # block 0: dY exists only inside the fused weight-gradient kernel
         if not fused0:
             assert _rel(_cf(b.dy[:B]), yb.grad) < 4e-3, f"dy{i}"
         dy_used = yb.grad.bfloat16().float() if fused0 else _cf(b.dy[:B]).float()
@@ -379,7 +379,7 @@ def test_fused_block0_backward_equals_the_separate_kernels_bit_for_bit():
             eng = B200Engine(model, DEV, max_batch=4)
         finally:
             os.environ.pop("NIDT_FUSED_BWD0", None)
-        assert (eng.blocks[0].amax is not None) == (fused == "1")
+        assert eng.fused_bwd0 == (fused == "1")
         slab = eng.new_slab()
         eng.attach(slab)
         res = []
