@@ -22,6 +22,8 @@
 // Reference op: autograd through Conv3d + BatchNorm3d + ReLU + MaxPool3d, fedml_api/model/cv/salient_models.py:147-150 (cuDNN).
 #include "common.cuh"
 #include "../../include/nidt_b200.h"
+#include <stdlib.h>
+#include <type_traits>
 
 namespace nidt {
 namespace alg {
@@ -32,6 +34,17 @@ constexpr int kCout = 64;
 constexpr int kMaxList = 64;
 
 struct IntList { int n; int v[kMaxList]; };
+
+// acc += x * g with x, g bf16 halves of 32-bit registers: sm_100's mixed-precision FMA (fma.rn.f32.bf16 -> FHFMA.BF16 with .H0 / .H1
+// operand selectors) -- the product of two bf16 is exact in fp32, so this equals fmaf(float(x), float(g), acc) without the unpacking
+// instructions.  `gw`: the gradient in the HIGH half.
+__device__ __forceinline__ void fma_pair(float& acc_lo, float& acc_hi, uint32_t pair, uint32_t gw) {
+    asm("{\n .reg .b16 xl, xh, gl, gh;\n mov.b32 {xl, xh}, %2;\n mov.b32 {gl, gh}, %3;\n fma.rn.f32.bf16 %0, xl, gh, %0;\n fma.rn.f32.bf16 %1, xh, gh, %1;\n}\n"
+        : "+f"(acc_lo), "+f"(acc_hi) : "r"(pair), "r"(gw));
+}
+__device__ __forceinline__ void fma_lo(float& acc_lo, uint32_t pair, uint32_t gw) {
+    asm("{\n .reg .b16 xl, xh, gl, gh;\n mov.b32 {xl, xh}, %1;\n mov.b32 {gl, gh}, %2;\n fma.rn.f32.bf16 %0, xl, gh, %0;\n}\n" : "+f"(acc_lo) : "r"(pair), "r"(gw));
+}
 
 __device__ __forceinline__ float xt(unsigned char b, float scale) { return __bfloat162float(__float2bfloat16((float)b * scale)); }
 
@@ -107,72 +120,203 @@ __global__ void __launch_bounds__(256) gram_sum_kernel(const float* __restrict__
 }
 
 // ------------------------------------------------------------------------------------------------ sparse term
-// One CTA walks pooling windows (n, dp, hp, wp).  Per window: the 9 x 9 x 9 input neighbourhood it covers goes to shared memory
-// as x~ (double-buffered), then thread (c = tid % 64, tg = tid / 64) adds da[w][c] * x~[winner patch of (w,c)][t] for its 32 taps
-// t = 32*tg ..  into registers.  partials[cta][c][128].
-constexpr int kNbPitch = 9;
-constexpr int kNbPlane = 9 * kNbPitch;
-constexpr int kNbSize = 9 * kNbPlane;       // 729
+// Unit of work: one row of up to kG pooling windows along W, (n, dp, hp, chunk).  The 9 planes x 9 rows x (6g+3) input columns
+// the row covers are contiguous byte runs in global memory (coalesced loads) and go to shared memory as x~ in bf16 PAIRS (x~ is
+// bf16-exact; one 32-bit load feeds two taps), double-buffered, together with every (window, channel)'s pooled gradient and the
+// word offset of its winning patch.  Thread (c = tid % 64, tg = tid / 64) then adds  da[w][c] * x~[winner patch of (w,c)][t]  for
+// its 6-7 of the 25 (td,th) tap rows (5 taps each) into registers.
+// The loop is bound by shared-memory loads (75 per patch), so the layout is made conflict-free: a winner (ad,ah,aw) moves the patch
+// by 2*ad planes, 2*ah rows, 2*aw columns; planes and rows are stored EVEN ONES FIRST (slot = i/2 + 5*(i%2)), which turns those
+// into +ad plane slots, +ah row slots, +aw words, and with row pitch = 3, plane pitch = 9 (mod 32 words) the 27 possible winners
+// of a warp's 32 channels read 27 different banks.
+constexpr int kG = 19;                      // windows per unit
+constexpr int kRowW = 67;                   // words per strip row  (>= ceil((6*kG + 3) / 2) = 59;  = 3 mod 32)
+constexpr int kPlaneW = 617;                // words per plane      (>= 9 * kRowW;                  = 9 mod 32)
+constexpr int kStripW = 9 * kPlaneW;        // 5553 words
+__host__ __device__ constexpr int slot9(int i) { return (i >> 1) + 5 * (i & 1); }
+struct __align__(16) StripBuf {
+    uint32_t nb[kStripW + 3];
+    uint32_t pw[kG * kCout];                // per (window, channel): low half = word offset of the winning patch inside the strip (without
+                                            // 3*wi; 0xFFFF = gated by ReLU), high half = the pooled gradient's bf16 bits
+};
+constexpr int kSparseSmem = 2 * (int)sizeof(StripBuf);
+constexpr int kSparseRows = 7;              // tap rows per thread: 7, 6, 6, 6
 
-__global__ void __launch_bounds__(256) alg_sparse_kernel(const unsigned char* __restrict__ x, const unsigned char* __restrict__ amax,
-                                                        const __nv_bfloat16* __restrict__ da, int N, int Di, int Hi, int Wi, int Dp, int Hp, int Wp,
-                                                        float scale, float* __restrict__ partials) {
-    __shared__ float nb[2][kNbSize + 3];
+__global__ void __launch_bounds__(256, 2) alg_sparse_kernel(const unsigned char* __restrict__ x, const unsigned char* __restrict__ amax,
+                                                           const __nv_bfloat16* __restrict__ da, int N, int Di, int Hi, int Wi, int Dp, int Hp, int Wp,
+                                                           float scale, float* __restrict__ partials) {
+    extern __shared__ __align__(16) unsigned char sp_smem[];
+    StripBuf* bufs = reinterpret_cast<StripBuf*>(sp_smem);
     const int tid = threadIdx.x, c = tid & 63, tg = tid >> 6;
-    int toff[32];
+    const int r0 = tg == 0 ? 0 : 1 + 6 * tg, nr = tg == 0 ? 7 : 6;
+    int roff[kSparseRows];
 #pragma unroll
-    for (int k = 0; k < 32; ++k) {
-        const int t = tg * 32 + k;
-        toff[k] = t < kTaps ? (t / 25) * kNbPlane + ((t / 5) % 5) * kNbPitch + t % 5 : -1;
+    for (int i = 0; i < kSparseRows; ++i) {
+        const int r = r0 + (i < nr ? i : 0);
+        roff[i] = slot9(r / 5) * kPlaneW + slot9(r % 5) * kRowW;
     }
-    float acc[32];
+    float acc[kSparseRows][5];
 #pragma unroll
-    for (int k = 0; k < 32; ++k) acc[k] = 0.f;
-    const int total = N * Dp * Hp * Wp;
-    auto load = [&](int w, int buf) {
-        const int wp = w % Wp, hp = (w / Wp) % Hp, dp = (w / (Wp * Hp)) % Dp, n = w / (Wp * Hp * Dp);
-        const unsigned char* base = x + (((size_t)n * Di + 6 * dp) * Hi + 6 * hp) * Wi + 6 * wp;
-        for (int i = tid; i < kNbSize; i += 256) {
-            const int z = i / kNbPlane, r = (i / kNbPitch) % 9, col = i % kNbPitch;
-            nb[buf][i] = xt(base[((size_t)z * Hi + r) * Wi + col], scale);
+    for (int i = 0; i < kSparseRows; ++i)
+#pragma unroll
+        for (int j = 0; j < 5; ++j) acc[i][j] = 0.f;
+    const int chunks = (Wp + kG - 1) / kG;
+    const int units = N * Dp * Hp * chunks;
+    // The next unit's bytes are loaded into REGISTERS before the current unit is processed and converted / stored after it, so
+    // the global-memory latency hides behind the compute loop.  Thread (q = tid / 64, j = tid % 64) fetches word j of the rows
+    // 4k + q; q is uniform per warp pair and dispatched to code specialised on it, so every row's (plane, row) is a constant.
+    constexpr int kLd = 21;                                 // ceil(81 / 4)
+    constexpr int kWd = (kG * kCout + 255) / 256;           // 5
+    uint32_t vv[kLd];                                       // two bytes per register
+    uint32_t pw[kWd];                                       // winner offset (low half) | pooled gradient bf16 bits (high half)
+    const int lq = tid >> 6, lj = tid & 63;
+    const int HiWi = Hi * Wi;
+    // unit walker without per-unit integer divisions: units advance by gridDim.x, so (ch, hp, dp, n) advance by fixed deltas with carries
+    int u_ch, u_hp, u_dp, u_n, s_ch, s_hp, s_dp, s_n;
+    {
+        const int u0 = blockIdx.x, st = gridDim.x;
+        u_ch = u0 % chunks; u_hp = (u0 / chunks) % Hp; u_dp = (u0 / (chunks * Hp)) % Dp; u_n = u0 / (chunks * Hp * Dp);
+        s_ch = st % chunks; s_hp = (st / chunks) % Hp; s_dp = (st / (chunks * Hp)) % Dp; s_n = st / (chunks * Hp * Dp);
+    }
+    auto advance = [&]() {
+        u_ch += s_ch;
+        int cy = 0;
+        if (u_ch >= chunks) { u_ch -= chunks; cy = 1; }
+        u_hp += s_hp + cy; cy = 0;
+        if (u_hp >= Hp) { u_hp -= Hp; cy = 1; }
+        u_dp += s_dp + cy; cy = 0;
+        if (u_dp >= Dp) { u_dp -= Dp; cy = 1; }
+        u_n += s_n + cy;
+    };
+    auto issue_q = [&](auto qc) {           // loads of the unit (u_ch, u_hp, u_dp, u_n)
+        constexpr int Q = decltype(qc)::value;
+        const int ch = u_ch, hp = u_hp, dp = u_dp, n = u_n;
+        const int w0 = ch * kG, g = min(kG, Wp - w0);
+        const int ncols = 6 * g + 3;
+        const unsigned char* src = x + (((size_t)n * Di + 6 * dp) * Hi + 6 * hp) * Wi + 6 * w0 + 2 * lj;
+        const bool in0 = 2 * lj < ncols, in1 = 2 * lj + 1 < ncols;
+#pragma unroll
+        for (int k = 0; k < kLd; ++k) {
+            constexpr int dummy = 0; (void)dummy;
+            const int row = 4 * k + Q;
+            if (row < 81) {
+                const unsigned char* s2 = src + (row / 9) * HiWi + (row % 9) * Wi;
+                const uint32_t b0 = in0 ? s2[0] : 0u, b1 = in1 ? s2[1] : 0u;
+                vv[k] = b0 | (b1 << 8);
+            }
+        }
+        const size_t wbase = ((((size_t)n * Dp + dp) * Hp + hp) * Wp + w0) * kCout;
+#pragma unroll
+        for (int k = 0; k < kWd; ++k) {
+            const int i = tid + 256 * k;
+            const bool ok = i < g * kCout;
+            const unsigned int am = ok ? amax[wbase + i] : 255u;          // (used in commit: no wait for the load here)
+            const __nv_bfloat16 dv = ok ? da[wbase + i] : __float2bfloat16(0.f);
+            pw[k] = am | ((uint32_t)__bfloat16_as_ushort(dv) << 16);
         }
     };
-    int w = blockIdx.x, it = 0;
-    if (w < total) load(w, 0);
-    for (; w < total; w += gridDim.x, ++it) {
-        __syncthreads();                                   // nb[it & 1] is complete; everybody is done with nb[(it + 1) & 1]
-        const int wn = w + gridDim.x;
-        if (wn < total) load(wn, (it + 1) & 1);
-        const unsigned int am = amax[(size_t)w * kCout + c];
-        if (am != 255u) {
-            const float g = __bfloat162float(da[(size_t)w * kCout + c]);
-            const float* p = nb[it & 1] + (2 * (am / 9)) * kNbPlane + (2 * ((am / 3) % 3)) * kNbPitch + 2 * (am % 3);
+    auto commit_q = [&](auto qc, StripBuf& sb) {
+        constexpr int Q = decltype(qc)::value;
 #pragma unroll
-            for (int k = 0; k < 32; ++k)
-                if (toff[k] >= 0) acc[k] = fmaf(g, p[toff[k]], acc[k]);
+        for (int k = 0; k < kLd; ++k) {
+            const int row = 4 * k + Q;
+            if (row < 81) {
+                __nv_bfloat162 v = __floats2bfloat162_rn((float)(vv[k] & 255u) * scale, (float)(vv[k] >> 8) * scale);
+                sb.nb[slot9(row / 9) * kPlaneW + slot9(row % 9) * kRowW + lj] = *reinterpret_cast<uint32_t*>(&v);
+            }
         }
-    }
-    float* out = partials + ((size_t)blockIdx.x * kCout + c) * kTP + tg * 32;
 #pragma unroll
-    for (int k = 0; k < 32; k += 4) *reinterpret_cast<float4*>(out + k) = make_float4(acc[k], acc[k + 1], acc[k + 2], acc[k + 3]);
+        for (int k = 0; k < kWd; ++k) {
+            const int i = tid + 256 * k;
+            const uint32_t am = pw[k] & 0xFFFFu;
+            const uint32_t po = am == 255u ? 0xFFFFu : (am / 9) * kPlaneW + ((am / 3) % 3) * kRowW + am % 3;
+            if (i < kG * kCout) sb.pw[i] = (pw[k] & 0xFFFF0000u) | po;
+        }
+    };
+    auto issue = [&]() {
+        switch (lq) {
+            case 0: issue_q(std::integral_constant<int, 0>{}); break;
+            case 1: issue_q(std::integral_constant<int, 1>{}); break;
+            case 2: issue_q(std::integral_constant<int, 2>{}); break;
+            default: issue_q(std::integral_constant<int, 3>{}); break;
+        }
+    };
+    auto commit = [&](StripBuf& sb) {
+        switch (lq) {
+            case 0: commit_q(std::integral_constant<int, 0>{}, sb); break;
+            case 1: commit_q(std::integral_constant<int, 1>{}, sb); break;
+            case 2: commit_q(std::integral_constant<int, 2>{}, sb); break;
+            default: commit_q(std::integral_constant<int, 3>{}, sb); break;
+        }
+    };
+    int u = blockIdx.x, it = 0;
+    if (u < units) { issue(); commit(bufs[0]); }
+    for (; u < units; u += gridDim.x, ++it) {
+        __syncthreads();                                   // bufs[it & 1] is complete; everybody is done with bufs[(it + 1) & 1]
+        const int g = min(kG, Wp - u_ch * kG);             // windows of the unit being processed
+        const int un = u + gridDim.x;
+        advance();
+        if (un < units) issue();
+        const StripBuf& sb = bufs[it & 1];
+        for (int wi = 0; wi < g; ++wi) {
+            const uint32_t w = sb.pw[wi * kCout + c];
+            if ((w & 0xFFFFu) == 0xFFFFu) continue;
+            const uint32_t* p = sb.nb + (w & 0xFFFFu) + 3 * wi;
+#pragma unroll
+            for (int i = 0; i < kSparseRows; ++i) {
+                if (i < nr) {
+                    const uint32_t a0 = p[roff[i]], a1 = p[roff[i] + 1], a2 = p[roff[i] + 2];
+                    fma_pair(acc[i][0], acc[i][1], a0, w);
+                    fma_pair(acc[i][2], acc[i][3], a1, w);
+                    fma_lo(acc[i][4], a2, w);
+                }
+            }
+        }
+        if (un < units) commit(bufs[(it + 1) & 1]);
+    }
+    float* out = partials + ((size_t)blockIdx.x * kCout + c) * kTP;
+#pragma unroll
+    for (int i = 0; i < kSparseRows; ++i)
+        if (i < nr) {
+#pragma unroll
+            for (int j = 0; j < 5; ++j) out[(r0 + i) * 5 + j] = acc[i][j];
+        }
 }
 
 // ------------------------------------------------------------------------------------------------ combine
-// grid 64 (channel), 128 threads (tap).  dW as in the file header; fp64 throughout (the bracket is a difference of sums over 4 M
-// positions).  Optional SNIP epilogue: scores += sal_scale * |dW * w|.
-__global__ void __launch_bounds__(128) alg_combine_kernel(const float* __restrict__ partials, int n_part, const double* __restrict__ gb,
+// grid 64 (channel), 512 threads = 4 groups x 128 taps: every group adds a quarter of the sparse partials and of the W~ G product
+// (fp64: the bracket is a difference of sums over 4 M positions), then the groups are added.  dW as in the file header.
+// Optional SNIP epilogue: scores += sal_scale * |dW * w|.
+__global__ void __launch_bounds__(512) alg_combine_kernel(const float* __restrict__ partials, int n_part, const double* __restrict__ gb,
                                                          const float* __restrict__ W, const float* __restrict__ bias, const float* __restrict__ bn_scale,
                                                          const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ c12,
                                                          float* __restrict__ grad_w, float* __restrict__ grad_b, const float* __restrict__ sal_w,
                                                          float* __restrict__ sal_scores, float sal_scale) {
     __shared__ double wq[kTP];
-    const int c = blockIdx.x, t = threadIdx.x;
-    wq[t] = t < kTaps ? (double)__bfloat162float(__float2bfloat16(W[c * kTaps + t])) : 0.0;
+    __shared__ double red[2][4][kTP];
+    const int c = blockIdx.x, t = threadIdx.x & 127, grp = threadIdx.x >> 7;
+    if (grp == 0) wq[t] = t < kTaps ? (double)__bfloat162float(__float2bfloat16(W[c * kTaps + t])) : 0.0;
     __syncthreads();
-    double S = 0.0;
-    for (int b = 0; b < n_part; ++b) S += (double)partials[((size_t)b * kCout + c) * kTP + t];
-    double wg = 0.0;
-    for (int u = 0; u < kTaps; ++u) wg = fma(wq[u], gb[u * kTP + t], wg);
+    double s0 = 0.0, s1 = 0.0;
+    int b = grp;
+    for (; b + 4 < n_part; b += 8) {
+        s0 += (double)partials[((size_t)b * kCout + c) * kTP + t];
+        s1 += (double)partials[((size_t)(b + 4) * kCout + c) * kTP + t];
+    }
+    if (b < n_part) s0 += (double)partials[((size_t)b * kCout + c) * kTP + t];
+    double w0 = 0.0, w1 = 0.0;
+    int u = grp;
+    for (; u + 4 < kTaps; u += 8) {
+        w0 = fma(wq[u], gb[u * kTP + t], w0);
+        w1 = fma(wq[u + 4], gb[(u + 4) * kTP + t], w1);
+    }
+    if (u < kTaps) w0 = fma(wq[u], gb[u * kTP + t], w0);
+    red[0][grp][t] = s0 + s1;
+    red[1][grp][t] = w0 + w1;
+    __syncthreads();
+    if (grp != 0) return;
+    const double S = red[0][0][t] + red[0][1][t] + red[0][2][t] + red[0][3][t];
+    const double wg = red[1][0][t] + red[1][1][t] + red[1][2][t] + red[1][3][t];
     const double sx = gb[kTaps * kTP + t];
     const double is = (double)invstd[c], mu = (double)mean[c], k1 = (double)c12[c], k2 = (double)c12[kCout + c];
     const double bc = bias != nullptr ? (double)bias[c] : 0.0;
@@ -193,7 +337,7 @@ static bool alg_shape_ok(int Di, int Hi, int Wi) { return Di >= 5 && Hi >= 5 && 
 
 NIDT_API int nidt_conv_in_gram_floats(void) { return alg::kTP * alg::kTP; }
 NIDT_API int nidt_conv_in_gram_max_samples(void) { return alg::kMaxList; }
-NIDT_API int nidt_conv_in_alg_grid(void) { return 4 * kNumSMs; }
+NIDT_API int nidt_conv_in_alg_grid(void) { return 2 * kNumSMs; }
 // floats of scratch for nidt_conv_in_gram_samples over n samples of depth Di
 NIDT_API int64_t nidt_conv_in_gram_scratch_floats(int n, int Di) { return (int64_t)n * ((Di - 5) / 2 + 1) * alg::kTP * alg::kTP; }
 // floats of scratch for nidt_conv_in_alg_wgrad
@@ -243,15 +387,24 @@ NIDT_API int nidt_conv_in_alg_wgrad(const void* x, const void* amax, const void*
     const int Do = (Di - 5) / 2 + 1, Ho = (Hi - 5) / 2 + 1, Wo = (Wi - 5) / 2 + 1;
     const int Dp = (Do - 3) / 3 + 1, Hp = (Ho - 3) / 3 + 1, Wp = (Wo - 3) / 3 + 1;
     NIDT_REQUIRE(Do >= 3 && Ho >= 3 && Wo >= 3, "nidt_conv_in_alg_wgrad: conv output %dx%dx%d smaller than the pooling window", Do, Ho, Wo);
-    const int total = N * Dp * Hp * Wp;
+    const int units = N * Dp * Hp * ((Wp + alg::kG - 1) / alg::kG);
     int grid = nidt_conv_in_alg_grid();
-    if (grid > total) grid = total;
+    if (grid > units) grid = units;
     cudaStream_t st = (cudaStream_t)stream;
-    alg::alg_sparse_kernel<<<grid, 256, 0, st>>>((const unsigned char*)x, (const unsigned char*)amax, (const __nv_bfloat16*)da, N, Di, Hi, Wi, Dp,
-                                                 Hp, Wp, scale, scratch);
-    NIDT_LAUNCH_CHECK();
-    alg::alg_combine_kernel<<<alg::kCout, 128, 0, st>>>(scratch, grid, gb, W, bias, bn_scale, mean, invstd, c12, grad_w, grad_b, sal_w, sal_scores,
-                                                       sal_scale);
+    static const int dbg = [] { const char* e = getenv("NIDT_ALG_DEBUG"); return e ? atoi(e) : 0; }();      // timing aid: 1 = no sparse pass, 2 = no combine
+    static bool attr_set = false;
+    if (!attr_set) {
+        NIDT_CUDA_CHECK(cudaFuncSetAttribute(alg::alg_sparse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, alg::kSparseSmem));
+        attr_set = true;
+    }
+    if (!(dbg & 1)) {
+        alg::alg_sparse_kernel<<<grid, 256, alg::kSparseSmem, st>>>((const unsigned char*)x, (const unsigned char*)amax, (const __nv_bfloat16*)da, N, Di,
+                                                                    Hi, Wi, Dp, Hp, Wp, scale, scratch);
+        NIDT_LAUNCH_CHECK();
+    }
+    if (!(dbg & 2))
+        alg::alg_combine_kernel<<<alg::kCout, 512, 0, st>>>(scratch, grid, gb, W, bias, bn_scale, mean, invstd, c12, grad_w, grad_b, sal_w, sal_scores,
+                                                           sal_scale);
     NIDT_LAUNCH_CHECK();
     return 0;
 }
