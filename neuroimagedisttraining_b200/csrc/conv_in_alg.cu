@@ -142,7 +142,8 @@ struct __align__(16) StripBuf {
 constexpr int kSparseSmem = 2 * (int)sizeof(StripBuf);
 constexpr int kSparseRows = 7;              // tap rows per thread: 7, 6, 6, 6
 
-__global__ void __launch_bounds__(256, 2) alg_sparse_kernel(const unsigned char* __restrict__ x, const unsigned char* __restrict__ amax,
+template <int kCtasPerSM>
+__global__ void __launch_bounds__(256, kCtasPerSM) alg_sparse_kernel(const unsigned char* __restrict__ x, const unsigned char* __restrict__ amax,
                                                            const __nv_bfloat16* __restrict__ da, int N, int Di, int Hi, int Wi, int Dp, int Hp, int Wp,
                                                            float scale, float* __restrict__ partials) {
     extern __shared__ __align__(16) unsigned char sp_smem[];
@@ -163,14 +164,15 @@ __global__ void __launch_bounds__(256, 2) alg_sparse_kernel(const unsigned char*
     const int chunks = (Wp + kG - 1) / kG;
     const int units = N * Dp * Hp * chunks;
     // The next unit's bytes are loaded into REGISTERS before the current unit is processed and converted / stored after it, so
-    // the global-memory latency hides behind the compute loop.  Thread (q = tid / 64, j = tid % 64) fetches word j of the rows
-    // 4k + q; q is uniform per warp pair and dispatched to code specialised on it, so every row's (plane, row) is a constant.
-    constexpr int kLd = 21;                                 // ceil(81 / 4)
+    // the global-memory latency hides behind the compute loop.  Thread (q = tid / 64, j = tid % 64) fetches word j (two bytes) of
+    // rows q and q + 4 of every plane, q = 0 also of row 8: four bytes per register, all offsets compile-time multiples of Wi, Hi*Wi.
     constexpr int kWd = (kG * kCout + 255) / 256;           // 5
-    uint32_t vv[kLd];                                       // two bytes per register
-    uint32_t pw[kWd];                                       // winner offset (low half) | pooled gradient bf16 bits (high half)
+    uint32_t va[9];                                         // plane z: bytes of row q (low half) and row q + 4 (high half)
+    uint32_t vb[5];                                         // q == 0: bytes of row 8 of planes 2m (low half) and 2m + 1 (high half)
+    uint32_t pw[kWd];                                       // winning tap (low half) | pooled gradient bf16 bits (high half)
     const int lq = tid >> 6, lj = tid & 63;
     const int HiWi = Hi * Wi;
+    const int dst_q = slot9(lq) * kRowW + lj;               // row q -> its slot; row q + 4 is two slots further, row 8 is slot 4
     // unit walker without per-unit integer divisions: units advance by gridDim.x, so (ch, hp, dp, n) advance by fixed deltas with carries
     int u_ch, u_hp, u_dp, u_n, s_ch, s_hp, s_dp, s_n;
     {
@@ -188,24 +190,25 @@ __global__ void __launch_bounds__(256, 2) alg_sparse_kernel(const unsigned char*
         if (u_dp >= Dp) { u_dp -= Dp; cy = 1; }
         u_n += s_n + cy;
     };
-    auto issue_q = [&](auto qc) {           // loads of the unit (u_ch, u_hp, u_dp, u_n)
-        constexpr int Q = decltype(qc)::value;
-        const int ch = u_ch, hp = u_hp, dp = u_dp, n = u_n;
-        const int w0 = ch * kG, g = min(kG, Wp - w0);
+    auto issue = [&]() {                    // loads of the unit (u_ch, u_hp, u_dp, u_n)
+        const int w0 = u_ch * kG, g = min(kG, Wp - w0);
         const int ncols = 6 * g + 3;
-        const unsigned char* src = x + (((size_t)n * Di + 6 * dp) * Hi + 6 * hp) * Wi + 6 * w0 + 2 * lj;
+        const unsigned char* src = x + (((size_t)u_n * Di + 6 * u_dp) * Hi + 6 * u_hp) * Wi + 6 * w0 + 2 * lj + lq * Wi;
         const bool in0 = 2 * lj < ncols, in1 = 2 * lj + 1 < ncols;
+        auto two = [&](const unsigned char* s2) -> uint32_t {
+            const uint32_t b0 = in0 ? s2[0] : 0u, b1 = in1 ? s2[1] : 0u;
+            return b0 | (b1 << 8);
+        };
 #pragma unroll
-        for (int k = 0; k < kLd; ++k) {
-            constexpr int dummy = 0; (void)dummy;
-            const int row = 4 * k + Q;
-            if (row < 81) {
-                const unsigned char* s2 = src + (row / 9) * HiWi + (row % 9) * Wi;
-                const uint32_t b0 = in0 ? s2[0] : 0u, b1 = in1 ? s2[1] : 0u;
-                vv[k] = b0 | (b1 << 8);
+        for (int z = 0; z < 9; ++z) va[z] = two(src + z * HiWi) | (two(src + z * HiWi + 4 * Wi) << 16);
+        if (lq == 0) {
+#pragma unroll
+            for (int m = 0; m < 5; ++m) {
+                vb[m] = two(src + (2 * m) * HiWi + 8 * Wi);
+                if (2 * m + 1 < 9) vb[m] |= two(src + (2 * m + 1) * HiWi + 8 * Wi) << 16;
             }
         }
-        const size_t wbase = ((((size_t)n * Dp + dp) * Hp + hp) * Wp + w0) * kCout;
+        const size_t wbase = ((((size_t)u_n * Dp + u_dp) * Hp + u_hp) * Wp + w0) * kCout;
 #pragma unroll
         for (int k = 0; k < kWd; ++k) {
             const int i = tid + 256 * k;
@@ -215,14 +218,21 @@ __global__ void __launch_bounds__(256, 2) alg_sparse_kernel(const unsigned char*
             pw[k] = am | ((uint32_t)__bfloat16_as_ushort(dv) << 16);
         }
     };
-    auto commit_q = [&](auto qc, StripBuf& sb) {
-        constexpr int Q = decltype(qc)::value;
+    auto commit = [&](StripBuf& sb) {
+        auto put = [&](int word, uint32_t two_bytes) {
+            __nv_bfloat162 v = __floats2bfloat162_rn((float)(two_bytes & 255u) * scale, (float)((two_bytes >> 8) & 255u) * scale);
+            sb.nb[word] = *reinterpret_cast<uint32_t*>(&v);
+        };
 #pragma unroll
-        for (int k = 0; k < kLd; ++k) {
-            const int row = 4 * k + Q;
-            if (row < 81) {
-                __nv_bfloat162 v = __floats2bfloat162_rn((float)(vv[k] & 255u) * scale, (float)(vv[k] >> 8) * scale);
-                sb.nb[slot9(row / 9) * kPlaneW + slot9(row % 9) * kRowW + lj] = *reinterpret_cast<uint32_t*>(&v);
+        for (int z = 0; z < 9; ++z) {
+            put(slot9(z) * kPlaneW + dst_q, va[z]);
+            put(slot9(z) * kPlaneW + dst_q + 2 * kRowW, va[z] >> 16);
+        }
+        if (lq == 0) {
+#pragma unroll
+            for (int m = 0; m < 5; ++m) {
+                put(slot9(2 * m) * kPlaneW + 4 * kRowW + lj, vb[m]);
+                if (2 * m + 1 < 9) put(slot9(2 * m + 1) * kPlaneW + 4 * kRowW + lj, vb[m] >> 16);
             }
         }
 #pragma unroll
@@ -231,22 +241,6 @@ __global__ void __launch_bounds__(256, 2) alg_sparse_kernel(const unsigned char*
             const uint32_t am = pw[k] & 0xFFFFu;
             const uint32_t po = am == 255u ? 0xFFFFu : (am / 9) * kPlaneW + ((am / 3) % 3) * kRowW + am % 3;
             if (i < kG * kCout) sb.pw[i] = (pw[k] & 0xFFFF0000u) | po;
-        }
-    };
-    auto issue = [&]() {
-        switch (lq) {
-            case 0: issue_q(std::integral_constant<int, 0>{}); break;
-            case 1: issue_q(std::integral_constant<int, 1>{}); break;
-            case 2: issue_q(std::integral_constant<int, 2>{}); break;
-            default: issue_q(std::integral_constant<int, 3>{}); break;
-        }
-    };
-    auto commit = [&](StripBuf& sb) {
-        switch (lq) {
-            case 0: commit_q(std::integral_constant<int, 0>{}, sb); break;
-            case 1: commit_q(std::integral_constant<int, 1>{}, sb); break;
-            case 2: commit_q(std::integral_constant<int, 2>{}, sb); break;
-            default: commit_q(std::integral_constant<int, 3>{}, sb); break;
         }
     };
     int u = blockIdx.x, it = 0;
@@ -337,7 +331,11 @@ static bool alg_shape_ok(int Di, int Hi, int Wi) { return Di >= 5 && Hi >= 5 && 
 
 NIDT_API int nidt_conv_in_gram_floats(void) { return alg::kTP * alg::kTP; }
 NIDT_API int nidt_conv_in_gram_max_samples(void) { return alg::kMaxList; }
-NIDT_API int nidt_conv_in_alg_grid(void) { return 2 * kNumSMs; }
+static int alg_ctas_per_sm() {
+    static const int v = [] { const char* e = getenv("NIDT_ALG_CTAS"); const int n = e ? atoi(e) : 2; return n == 3 ? 3 : 2; }();
+    return v;
+}
+NIDT_API int nidt_conv_in_alg_grid(void) { return 3 * kNumSMs; }      // upper bound (scratch sizing); the launch uses alg_ctas_per_sm() * SMs
 // floats of scratch for nidt_conv_in_gram_samples over n samples of depth Di
 NIDT_API int64_t nidt_conv_in_gram_scratch_floats(int n, int Di) { return (int64_t)n * ((Di - 5) / 2 + 1) * alg::kTP * alg::kTP; }
 // floats of scratch for nidt_conv_in_alg_wgrad
@@ -388,18 +386,24 @@ NIDT_API int nidt_conv_in_alg_wgrad(const void* x, const void* amax, const void*
     const int Dp = (Do - 3) / 3 + 1, Hp = (Ho - 3) / 3 + 1, Wp = (Wo - 3) / 3 + 1;
     NIDT_REQUIRE(Do >= 3 && Ho >= 3 && Wo >= 3, "nidt_conv_in_alg_wgrad: conv output %dx%dx%d smaller than the pooling window", Do, Ho, Wo);
     const int units = N * Dp * Hp * ((Wp + alg::kG - 1) / alg::kG);
-    int grid = nidt_conv_in_alg_grid();
+    const int per_sm = alg_ctas_per_sm();
+    int grid = per_sm * kNumSMs;
     if (grid > units) grid = units;
     cudaStream_t st = (cudaStream_t)stream;
     static const int dbg = [] { const char* e = getenv("NIDT_ALG_DEBUG"); return e ? atoi(e) : 0; }();      // timing aid: 1 = no sparse pass, 2 = no combine
     static bool attr_set = false;
     if (!attr_set) {
-        NIDT_CUDA_CHECK(cudaFuncSetAttribute(alg::alg_sparse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, alg::kSparseSmem));
+        NIDT_CUDA_CHECK(cudaFuncSetAttribute(alg::alg_sparse_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, alg::kSparseSmem));
+        NIDT_CUDA_CHECK(cudaFuncSetAttribute(alg::alg_sparse_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, alg::kSparseSmem));
         attr_set = true;
     }
     if (!(dbg & 1)) {
-        alg::alg_sparse_kernel<<<grid, 256, alg::kSparseSmem, st>>>((const unsigned char*)x, (const unsigned char*)amax, (const __nv_bfloat16*)da, N, Di,
-                                                                    Hi, Wi, Dp, Hp, Wp, scale, scratch);
+        if (per_sm == 2)
+            alg::alg_sparse_kernel<2><<<grid, 256, alg::kSparseSmem, st>>>((const unsigned char*)x, (const unsigned char*)amax, (const __nv_bfloat16*)da,
+                                                                           N, Di, Hi, Wi, Dp, Hp, Wp, scale, scratch);
+        else
+            alg::alg_sparse_kernel<3><<<grid, 256, alg::kSparseSmem, st>>>((const unsigned char*)x, (const unsigned char*)amax, (const __nv_bfloat16*)da,
+                                                                           N, Di, Hi, Wi, Dp, Hp, Wp, scale, scratch);
         NIDT_LAUNCH_CHECK();
     }
     if (!(dbg & 2))
