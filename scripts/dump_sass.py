@@ -22,7 +22,7 @@ PAT = collections.OrderedDict([
     ("UTCBAR (tcgen05.commit)", r"\bUTCBAR"), ("SYNCS (mbarrier)", r"\bSYNCS"),
     ("multimem ld_reduce (LDGMC/..RED)", r"\bLDGMC|\bLDG\S*\.MC"), ("multimem st / red (STG.MC / REDG.MC)", r"\bSTGMC|\bSTG\S*\.MC|\bREDG\S*\.MC|\bREDGMC"),
     ("ld.acquire.sys (LDG..STRONG.SYS)", r"\bLDG\S*STRONG\.SYS"), ("st.release.sys (STG..STRONG.SYS)", r"\bSTG\S*STRONG\.SYS"),
-    ("HMMA (legacy mma.sync)", r"\bHMMA"),
+    ("HMMA (legacy mma.sync)", r"\bHMMA"), ("FHFMA.BF16 (fma.rn.f32.bf16, mixed precision)", r"\bFHFMA"),
 ])
 
 
