@@ -524,22 +524,32 @@ __global__ void __launch_bounds__(256) bn_relu_pool3_bwd_apply_kernel(
 }
 
 // partials [T][2][C] -> c12 [2][C] (c1 = sum(dyhat)/M, c2 = sum(dyhat*xhat)/M), dgamma, dbeta
-__global__ void __launch_bounds__(256) bn_bwd_finalize_kernel(const float* __restrict__ partials, int T, int C, double count,
-                                                              float* __restrict__ c12, float* __restrict__ dgamma, float* __restrict__ dbeta) {
-    __shared__ double s1[8][32], s2[8][32];
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const int c = blockIdx.x * 32 + tx;
+// 16 channels x 64 row slices per CTA (as bn_finalize_kernel): with up to 592 partial rows a thread adds ~9 of them instead of 74,
+// which is what this latency-bound kernel's 8 us were made of (420 launches per federated round)
+__global__ void __launch_bounds__(kFinCh * kFinSlices) bn_bwd_finalize_kernel(const float* __restrict__ partials, int T, int C, double count,
+                                                                              float* __restrict__ c12, float* __restrict__ dgamma,
+                                                                              float* __restrict__ dbeta) {
+    __shared__ double s1[kFinSlices][kFinCh], s2[kFinSlices][kFinCh];
+    const int tx = threadIdx.x % kFinCh, ty = threadIdx.x / kFinCh;
+    const int c = blockIdx.x * kFinCh + tx;
     double a = 0.0, b = 0.0;
-    if (c < C)
-        for (int t = ty; t < T; t += 8) {
+    if (c < C) {
+        int t = ty;
+        for (; t + kFinSlices < T; t += 2 * kFinSlices) {          // 4 independent loads in flight
+            const float v0 = partials[((size_t)t * 2 + 0) * C + c], v1 = partials[((size_t)t * 2 + 1) * C + c];
+            const float v2 = partials[((size_t)(t + kFinSlices) * 2 + 0) * C + c], v3 = partials[((size_t)(t + kFinSlices) * 2 + 1) * C + c];
+            a += (double)v0; b += (double)v1; a += (double)v2; b += (double)v3;
+        }
+        for (; t < T; t += kFinSlices) {
             a += (double)partials[((size_t)t * 2 + 0) * C + c];
             b += (double)partials[((size_t)t * 2 + 1) * C + c];
         }
+    }
     s1[ty][tx] = a;
     s2[ty][tx] = b;
     __syncthreads();
     if (ty == 0 && c < C) {
-        for (int i = 1; i < 8; ++i) { a += s1[i][tx]; b += s2[i][tx]; }
+        for (int i = 1; i < kFinSlices; ++i) { a += s1[i][tx]; b += s2[i][tx]; }
         c12[c] = (float)(a / count);
         c12[C + c] = (float)(b / count);
         if (dgamma) dgamma[c] = (float)b;
@@ -648,7 +658,7 @@ NIDT_API int nidt_bn_relu_pool_bwd_phases(const void* y, const void* ymax, const
 }
 NIDT_API int nidt_bn_bwd_finalize(const float* partials, int rows, int C, double count, float* c12, float* dgamma, float* dbeta, void* stream) {
     NIDT_REQUIRE(rows >= 1 && C >= 1 && count > 0 && c12 != nullptr, "nidt_bn_bwd_finalize: rows=%d C=%d", rows, C);
-    bn_bwd_finalize_kernel<<<(C + 31) / 32, 256, 0, (cudaStream_t)stream>>>(partials, rows, C, count, c12, dgamma, dbeta);
+    bn_bwd_finalize_kernel<<<(C + kFinCh - 1) / kFinCh, kFinCh * kFinSlices, 0, (cudaStream_t)stream>>>(partials, rows, C, count, c12, dgamma, dbeta);
     NIDT_LAUNCH_CHECK();
     return 0;
 }
@@ -684,7 +694,7 @@ static int bn_relu_pool_bwd_impl(const void* y, const void* ymax, const void* da
             if (rows_out) *rows_out = rgrid;
         }
         if (phases & kBwdFinalize) {
-            bn_bwd_finalize_kernel<<<(C + 31) / 32, 256, 0, s>>>(partials, rgrid, C, count, c12, dgamma, dbeta);
+            bn_bwd_finalize_kernel<<<(C + kFinCh - 1) / kFinCh, kFinCh * kFinSlices, 0, s>>>(partials, rgrid, C, count, c12, dgamma, dbeta);
             NIDT_LAUNCH_CHECK();
         }
         if (!(phases & kBwdApply)) return 0;
@@ -711,7 +721,7 @@ static int bn_relu_pool_bwd_impl(const void* y, const void* ymax, const void* da
         if (rows_out) *rows_out = grid;
     }
     if (phases & kBwdFinalize) {
-        bn_bwd_finalize_kernel<<<(C + 31) / 32, 256, 0, s>>>(partials, grid, C, count, c12, dgamma, dbeta);
+        bn_bwd_finalize_kernel<<<(C + kFinCh - 1) / kFinCh, kFinCh * kFinSlices, 0, s>>>(partials, grid, C, count, c12, dgamma, dbeta);
         NIDT_LAUNCH_CHECK();
     }
     if (!(phases & kBwdApply)) return 0;
