@@ -1,5 +1,11 @@
+"""Timing of the first-layer backward without y / dY passes (csrc/conv_in_alg.cu) against the dY-based kernels: whole SGD step in
+both modes (CUDA-graph replays), the per-sample Gram matrices cold, the per-batch sum, and the block-0 kernels through the Python
+launch loop.  NIDT_ALG_DEBUG=1 / 2 drops the sparse pass / the combine kernel (isolates the other one); NIDT_ALG_CTAS=2|3.
+
+    python scripts/time_alg_bwd0.py
+"""
 import os, sys
-ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch
 from neuroimagedisttraining_b200.fl.engine import StepHParams
