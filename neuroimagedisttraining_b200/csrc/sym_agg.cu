@@ -20,6 +20,9 @@
 // it histograms the shard's fp32 bit patterns (3 radix passes of 11/11/10 bits), the 2048-bin histograms (and the shard sums)
 // are exchanged through symmetric memory and added in rank order, so all ranks agree on the k-th largest score without anyone
 // holding all scores; each rank emits the mask of its shard into every rank's mask buffer (all-gather by P2P stores).
+// `replicate`: for slabs that fit in L2 the three dependent histogram exchanges (one cross-rank barrier each, ~10 us at 8 GPUs) cost more
+// than the passes themselves; the kernel then all-gathers the reduced scores (as W1 does) and every rank selects over the whole slab on
+// its own -- 2 cross-rank barriers per call instead of 6, same kernel, same buffers.
 // Reference: snip.py:80-140 (mean over clients, cat, /sum, topk, >= threshold).
 #include "common.cuh"
 #include "tc_common.cuh"
@@ -308,7 +311,7 @@ __device__ __forceinline__ int radix_bits(int pass) { return pass == 2 ? kRadixB
 template <int kWorld>
 __global__ void __launch_bounds__(kSymThreads) sym_saliency_topk_kernel(const SymPeers sp, const SalAux aux, int64_t n, const unsigned char* __restrict__ flags,
                                                                         float* __restrict__ mask, unsigned long long k, SalResult* __restrict__ res,
-                                                                        float* __restrict__ scores_out, uint32_t epoch, int mode) {
+                                                                        float* __restrict__ scores_out, uint32_t epoch, int mode, int replicate) {
     extern __shared__ __align__(128) unsigned char sym_smem[];
     __shared__ unsigned int sh_hist[kRadixBins];
     __shared__ unsigned long long sh_scan[kSymThreads / 32];
@@ -319,16 +322,22 @@ __global__ void __launch_bounds__(kSymThreads) sym_saliency_topk_kernel(const Sy
     const int P = sp.world;
     const int64_t n4 = n >> 2;
     const int64_t per4 = (n4 + P - 1) / P;
-    const int64_t lo = min(n, 4 * per4 * sp.rank), hi = min(n, lo + 4 * per4);       // this rank's shard, in elements
+    // the range this rank selects over: its shard, or everything (replicate)
+    const int64_t lo = replicate ? 0 : min(n, 4 * per4 * sp.rank), hi = replicate ? n : min(n, lo + 4 * per4);
+    const int Ps = replicate ? 1 : P;                                                 // histograms added per pass
     const int64_t tid = (int64_t)blockIdx.x * kSymThreads + threadIdx.x, nth = (int64_t)gridDim.x * kSymThreads;
 
     // clear this call's scratch, then reduce-scatter: the reduced shard stays HERE (result[rank][lo:hi))
     for (int64_t i = tid; i < 3 * kRadixBins + 1; i += nth) aux.local_hist[i] = 0u;
     uint32_t bar = 6 * epoch;
     cross_rank_barrier(grid, sp, 0, ++bar, false);                            // every rank's partial is complete
-    reduce_mask_broadcast<kWorld>(sp, nullptr, 0, n, mode, 0, false, sym_smem);
-    __threadfence();
-    grid.sync();
+    reduce_mask_broadcast<kWorld>(sp, nullptr, 0, n, mode, 0, replicate != 0, sym_smem);
+    if (replicate) {
+        cross_rank_barrier(grid, sp, 0, ++bar);                               // every chunk of reduced scores has landed here
+    } else {
+        __threadfence();
+        grid.sync();
+    }
     const float* scores = sp.result[sp.rank];
 
     // shard sum of the prunable scores (fixed-order block partials)
@@ -358,6 +367,13 @@ __global__ void __launch_bounds__(kSymThreads) sym_saliency_topk_kernel(const Sy
         __threadfence();
         grid.sync();
         // publish the shard histogram (and, with pass 0, the shard sum) into every rank's exchange pad
+        if (replicate) {
+            if (pass == 0) {                                                   // everybody adds the block sums in the same order
+                float p = 0.f;
+                for (int i = threadIdx.x; i < (int)gridDim.x; i += kSymThreads) p += aux.block_sums[i];
+                norm = block_sum<kSymThreads>(p, red);
+            }
+        } else {
         if (pass == 0 && blockIdx.x == 0) {
             float p = 0.f;
             for (int i = threadIdx.x; i < (int)gridDim.x; i += kSymThreads) p += aux.block_sums[i];
@@ -369,15 +385,16 @@ __global__ void __launch_bounds__(kSymThreads) sym_saliency_topk_kernel(const Sy
             aux.hist[dst][((size_t)pass * kMaxRanks + sp.rank) * kRadixBins + b] = lh[b];
         }
         cross_rank_barrier(grid, sp, 0, ++bar);
-        // every block finds the digit itself from the P published histograms (no extra grid-wide step)
-        const uint32_t* hp = aux.hist[sp.rank] + (size_t)pass * kMaxRanks * kRadixBins;
+        }
+        // every block finds the digit itself from the published histograms (no extra grid-wide step)
+        const uint32_t* hp = replicate ? lh : aux.hist[sp.rank] + (size_t)pass * kMaxRanks * kRadixBins;
         constexpr int kPer = kRadixBins / kSymThreads;                         // 4 consecutive bins per thread
         unsigned int c[kPer];
         unsigned long long mine = 0ull;
 #pragma unroll
         for (int q = 0; q < kPer; ++q) {
             unsigned int s = 0u;
-            for (int r = 0; r < P; ++r) s += hp[(size_t)r * kRadixBins + threadIdx.x * kPer + q];
+            for (int r = 0; r < Ps; ++r) s += hp[(size_t)r * kRadixBins + threadIdx.x * kPer + q];
             c[q] = s;
             mine += s;
         }
@@ -406,7 +423,7 @@ __global__ void __launch_bounds__(kSymThreads) sym_saliency_topk_kernel(const Sy
         __syncthreads();
         prefix = sh_prefix;
         krem = sh_k;
-        if (pass == 0) {                                                       // shard sums arrived with the first exchange; add in rank order
+        if (pass == 0 && !replicate) {                                         // shard sums arrived with the first exchange; add in rank order
             const uint32_t* sums = aux.hist[sp.rank] + 3 * kMaxRanks * kRadixBins;
             for (int r = 0; r < P; ++r) norm += __uint_as_float(sums[r]);
         }
@@ -432,11 +449,12 @@ __global__ void __launch_bounds__(kSymThreads) sym_saliency_topk_kernel(const Sy
             }
         }
         const float4 mv = make_float4(m[0], m[1], m[2], m[3]);
-        for (int p = 0; p < P; ++p) st4(aux.mask_out[p] + 4 * i4, mv);
+        if (replicate) st4(aux.mask_out[sp.rank] + 4 * i4, mv);
+        else for (int p = 0; p < P; ++p) st4(aux.mask_out[p] + 4 * i4, mv);
     }
     kept = (unsigned int)warp_sum_u64(kept);
     if ((threadIdx.x & 31) == 0 && kept) atomicAdd(aux.local_hist + 3 * kRadixBins, kept);
-    if (scores_out != nullptr) {            // all-gather of the reduced scores through the result buffers (api.scores / diagnostics)
+    if (scores_out != nullptr && !replicate) {            // all-gather of the reduced scores through the result buffers (api.scores / diagnostics)
         for (int64_t i = (lo >> 2) + tid; i < (hi >> 2); i += nth) {
             const float4 v = ld4(scores + 4 * i);
             for (int p = 0; p < P; ++p)
@@ -446,19 +464,24 @@ __global__ void __launch_bounds__(kSymThreads) sym_saliency_topk_kernel(const Sy
     // the kept counts travel through the (now free) pass-1 rows of the exchange pads
     __threadfence();
     grid.sync();
-    if (blockIdx.x == 0 && threadIdx.x < P) aux.hist[threadIdx.x][((size_t)1 * kMaxRanks + sp.rank) * kRadixBins] = aux.local_hist[3 * kRadixBins];
-    cross_rank_barrier(grid, sp, 0, ++bar);
+    if (!replicate) {
+        if (blockIdx.x == 0 && threadIdx.x < P) aux.hist[threadIdx.x][((size_t)1 * kMaxRanks + sp.rank) * kRadixBins] = aux.local_hist[3 * kRadixBins];
+        cross_rank_barrier(grid, sp, 0, ++bar);
+    }
     if (mask != aux.mask_out[sp.rank])
         for (int64_t i = tid; i < n4; i += nth) st4(mask + 4 * i, ld4(aux.mask_out[sp.rank] + 4 * i));
     if (scores_out != nullptr && scores_out != scores)
         for (int64_t i = tid; i < n4; i += nth) st4(scores_out + 4 * i, ld4(scores + 4 * i));
     if (tid == 0) {
         unsigned int total = 0u;
-        for (int r = 0; r < P; ++r) total += aux.hist[sp.rank][((size_t)1 * kMaxRanks + r) * kRadixBins];
+        if (replicate) total = aux.local_hist[3 * kRadixBins];
+        else for (int r = 0; r < P; ++r) total += aux.hist[sp.rank][((size_t)1 * kMaxRanks + r) * kRadixBins];
         res->threshold = thr_q; res->norm = norm; res->kept = total;
     }
-    // one more line-up so that nobody starts the next call's pad writes while a slower rank still reads this call's
-    cross_rank_barrier(grid, sp, 0, ++bar);
+    // one more line-up so that nobody starts the next call's pad writes while a slower rank still reads this call's.  (replicate: nothing
+    // of this rank is written by a peer after the all-gather barrier, and the next call's writes into it come after ITS first barrier,
+    // which needs this rank to have left this call.)
+    if (!replicate) cross_rank_barrier(grid, sp, 0, ++bar);
 }
 
 // NIDT_SYM_TIMEOUT_S (default 300 s) at the nominal 1.965 GHz SM clock.
@@ -597,10 +620,16 @@ NIDT_API int nidt_sym_saliency_topk_mask(void* const* partial_ptrs, void* const*
     // grows with the number of CTAs -- 4 to 48 CTAs
     int64_t want = (n + 16383) / 16384;        // the mask / score copy-outs run over the whole slab on every rank
     if (want < 4) want = 4;
-    int grid = (int)(want < 48 ? want : 48);
-    if (grid > sms) grid = sms;
+    // NIDT_SAL_REPLICATE=0|1 (default: on for slabs up to 64 MB): select on every rank over the all-gathered scores instead of
+    // exchanging three shard histograms -- 2 cross-rank barriers instead of 6; the passes then cover the whole slab, on a wider grid
+    int replicate = world >= 2 && n <= ((int64_t)16 << 20);
+    if (const char* e = getenv("NIDT_SAL_REPLICATE")) replicate = atoi(e) != 0;
+    const int cap = replicate ? sms : 48;
+    int grid = (int)(want < cap ? want : cap);
+    if (grid > sms * per_sm) grid = sms * per_sm;
     int mode = use_multimem ? kModeMultimem : kModeP2P;
-    void* args[] = {(void*)&sp, (void*)&aux, (void*)&n, (void*)&flags, (void*)&mask, (void*)&k, (void*)&res, (void*)&scores_out, (void*)&epoch, (void*)&mode};
+    void* args[] = {(void*)&sp, (void*)&aux, (void*)&n, (void*)&flags, (void*)&mask, (void*)&k, (void*)&res, (void*)&scores_out, (void*)&epoch, (void*)&mode,
+                    (void*)&replicate};
     NIDT_CUDA_CHECK(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(kSymThreads), args, 0, (cudaStream_t)stream));
     return 0;
 }

@@ -96,9 +96,13 @@ sc = (torch.rand(Pn, device=dev) ** 3) * 1e-3
 mask_out = torch.empty(Pn, device=dev)
 work = sc.clone()
 t_w2 = {}
-for mm in ([False, True] if agg.has_multicast else [False]):
-    agg.use_multimem = mm
-    t_w2["multimem" if mm else "p2p"] = timeit(lambda: agg.saliency_topk_mask(work, layout, 0.5, mask_out, flags, read=False, align=False), 30)
+for rep in ("0", "1"):              # sharded histogram exchange (6 cross-rank barriers) / select on every rank after an in-kernel all-gather (2)
+    os.environ["NIDT_SAL_REPLICATE"] = rep
+    for mm in ([False, True] if agg.has_multicast else [False]):
+        agg.use_multimem = mm
+        t_w2[("multimem" if mm else "p2p") + ("+replicated_select" if rep == "1" else "")] = timeit(
+            lambda: agg.saliency_topk_mask(work, layout, 0.5, mask_out, flags, read=False, align=False), 30)
+os.environ.pop("NIDT_SAL_REPLICATE", None)
 
 
 def nccl_w2():
@@ -112,6 +116,6 @@ if ctx.is_main:
     print(json.dumps({"kernel": "W2 saliency_reduce_topk_mask", "scores": Pn, "bytes_scores": 4 * Pn, "n_gpus": P, "fused_ms": t_w2,
                       "nccl_allreduce_plus_topk_ms": t_nccl, "nvlink_roofline_ms": round(roof, 4),
                       "fraction_of_roofline": round(roof / min(t_w2.values()), 3), "speedup_vs_nccl": round(t_nccl / min(t_w2.values()), 2),
-                      "note": "6 cross-rank barriers + 3 radix passes per call: latency-bound at 10 MB"}))
+                      "note": "sharded: 6 cross-rank barriers + 3 radix passes over n/P scores; replicated_select: 2 barriers, passes over all n scores"}))
     print(json.dumps({"clocks": clocks, "applies_to": "every line of this run (sampled over the whole sweep)"}))
 shutdown()

@@ -52,8 +52,9 @@ def main():
     layout = SlabLayout.from_module(AlexNet3D_Dropout(1))
     flags = ops.prunable_flags(layout, dev)
     P = layout.param_numel
-    for mm in ([False, True] if agg.mc_partial else [False]):
+    for mm, rep in [(m, r) for m in ([False, True] if agg.mc_partial else [False]) for r in ("0", "1")]:
         agg.use_multimem = mm
+        os.environ["NIDT_SAL_REPLICATE"] = rep          # sharded histogram exchange / select on every rank over the all-gathered scores
         sc = (torch.rand(P, generator=torch.Generator().manual_seed(5 + ctx.rank)) ** 3).to(dev) * 1e-3
         scs = [torch.empty_like(sc) for _ in range(ctx.world_size)]
         dist.all_gather(scs, sc)
@@ -72,7 +73,8 @@ def main():
         if nd > 4 or abs(fi["kept"] - ri["kept"]) > 4 or not close:
             ok = False
         if ctx.rank == 0:
-            print(f"saliency multimem={mm}: mask diff={nd} kept={fi['kept']} (ref {ri['kept']}) thr={fi['threshold']:.6e}")
+            print(f"saliency multimem={mm} replicate={rep}: mask diff={nd} kept={fi['kept']} (ref {ri['kept']}) thr={fi['threshold']:.6e}")
+    os.environ.pop("NIDT_SAL_REPLICATE", None)
     # W1 with the weighting of K local client slabs inside the kernel, every data path, and the in-place (adopted) global slab
     K = 3
     locs = [torch.randn(n, generator=torch.Generator().manual_seed(7000 + 10 * ctx.rank + j)).to(dev) for j in range(K)]

@@ -74,8 +74,12 @@ def test_reduce_mask_broadcast_world1_equals_masked_copy(world1):
             assert torch.equal(target, want), f"mode={mode} mm_frac={frac}: max diff {(target - want).abs().max().item()}"
 
 
-def test_saliency_topk_mask_world1_equals_torch_topk(world1):
+@pytest.mark.parametrize("replicate", ["0", "1"])
+def test_saliency_topk_mask_world1_equals_torch_topk(world1, replicate, monkeypatch):
+    """replicate = 1: the variant that all-gathers the reduced scores and selects over the whole slab on every rank (what runs from
+    4 ranks on for L2-sized slabs); 0: sharded histograms exchanged per radix pass."""
     from neuroimagedisttraining_b200.parallel.symmetric import SymmetricAggregator
+    monkeypatch.setenv("NIDT_SAL_REPLICATE", replicate)
     dev = world1.device
     layout = SlabLayout.from_module(AlexNet3D_Dropout(1))
     P = layout.param_numel
