@@ -183,3 +183,45 @@ def bce_eval_counters(logits: torch.Tensor, target: torch.Tensor, double_sigmoid
     loss = torch.nn.functional.binary_cross_entropy_with_logits(z, t, reduction="sum")
     correct = ((p >= 0.5).float() == t).float().sum()
     return correct, loss
+
+
+def conv1_wgrad_from_pooled(x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor], gamma: torch.Tensor, beta: torch.Tensor,
+                            da: torch.Tensor, eps: float = 1e-5) -> Tuple[torch.Tensor, torch.Tensor]:
+    """PyTorch statement of ``csrc/conv_in_alg.cu``: the weight gradient of ``Conv3d(1, C, 5, stride 2) -> BatchNorm3d (batch
+    statistics) -> ReLU -> MaxPool3d(3, 3)`` from the POOLED gradient ``da`` [N, C, Dp, Hp, Wp] without ever forming dY:
+
+        dW[c, t] = s_c * ( S[c, t] - c1_c * sx[t] - c2_c * invstd_c * ((W G)[c, t] + (b_c - mu_c) * sx[t]) )
+
+    ``G = P^T P`` and ``sx = P^T 1`` over the patch matrix ``P`` [positions, 125] of the input (they depend on ``x`` only -- the kernels
+    cache them per sample), ``S`` sums the winning position's patch of every pooling window times its ``da``, ``c1 = mean(dz)``,
+    ``c2 = mean(dz * yhat)`` are the two BatchNorm-backward means over ALL positions, ``s = gamma * invstd``.  Returns ``(dW, dgamma)``;
+    the conv bias gradient is identically zero.  The forward is recomputed here (this is an oracle, not a fast path).
+    ref: autograd through salient_models.py:147-150."""
+    N, _, D, H, W_ = x.shape
+    C = w.shape[0]
+    patches = x[:, 0].unfold(1, 5, 2).unfold(2, 5, 2).unfold(3, 5, 2)                 # [N, Do, Ho, Wo, 5, 5, 5]
+    Do, Ho, Wo = patches.shape[1:4]
+    P = patches.reshape(N * Do * Ho * Wo, 125)
+    y = P @ w.reshape(C, 125).t()
+    if b is not None:
+        y = y + b
+    mu, var = y.mean(0), y.var(0, unbiased=False)
+    invstd = (var + eps).rsqrt()
+    yhat = (y - mu) * invstd
+    z = torch.relu(yhat * gamma + beta).reshape(N, Do, Ho, Wo, C).permute(0, 4, 1, 2, 3)
+    pooled, idx = torch.nn.functional.max_pool3d(z, 3, 3, return_indices=True)       # idx: flat position inside (Do, Ho, Wo)
+    gate = (pooled > 0).to(da.dtype)
+    n_i = torch.arange(N, device=x.device).view(N, 1, 1, 1, 1).expand_as(idx)
+    pos = (n_i * (Do * Ho * Wo) + idx).reshape(-1)                                     # row of P / y of every window's winner
+    ch = torch.arange(C, device=x.device).view(1, C, 1, 1, 1).expand_as(idx).reshape(-1)
+    g = (da * gate).reshape(-1)
+    count = float(P.shape[0])
+    S = torch.zeros(C, 125, dtype=x.dtype, device=x.device)
+    S.index_add_(0, ch, g.unsqueeze(1) * P[pos])                                       # one patch per (window, channel)
+    c1 = torch.zeros(C, dtype=x.dtype, device=x.device).index_add_(0, ch, g) / count
+    c2 = torch.zeros(C, dtype=x.dtype, device=x.device).index_add_(0, ch, g * yhat[pos, ch]) / count
+    G, sx = P.t() @ P, P.sum(0)
+    bb = b if b is not None else torch.zeros(C, dtype=x.dtype, device=x.device)
+    inner = w.reshape(C, 125) @ G + (bb - mu).unsqueeze(1) * sx.unsqueeze(0)
+    dW = (gamma * invstd).unsqueeze(1) * (S - c1.unsqueeze(1) * sx.unsqueeze(0) - (c2 * invstd).unsqueeze(1) * inner)
+    return dW.reshape(C, 1, 5, 5, 5), c2 * count
