@@ -360,7 +360,6 @@ class B200Engine:
         self.eval_logits = torch.zeros(B, dtype=torch.float32, device=dev)
 
     def _build_plan(self) -> _PlanC:
-        from .flat import _norm_scratch
         lay = self.layout
         off = lambda name: int(lay[name].offset) if name in lay else -1
         ptr = lambda t: (t.data_ptr() if t is not None else None)
