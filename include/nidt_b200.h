@@ -86,6 +86,14 @@ int nidt_copy_rows_h2d_counted(const void* host_base, const int64_t* rows, int n
  * (sailentgrads/my_model_trainer.py:185-199). */
 int nidt_expand_sparse_rows_u8(const void* packed, const long long* packed_off, const void* tab, const void* off, void* dst, int n_vol,
                                int rows, int W, void* stream);
+/* host side of the same transfer form: span table of a volume cache ([n_vol][rows][W] bytes, W <= 255) on `threads` host threads --
+ * per row (first non-zero byte, length up to the last one) into tab, the row's offset among its volume's spans into off, the packed
+ * size of every volume into vol_bytes; then the spans copied back to back (vol_off = exclusive prefix of vol_bytes).
+ * The reference has no counterpart (it copies dense fp32 batches, my_model_trainer.py:185-199). */
+int nidt_sparse_scan_rows(const unsigned char* cache, int64_t n_vol, int rows, int W, unsigned char* tab, unsigned int* off,
+                          int64_t* vol_bytes, int threads);
+int nidt_sparse_copy_rows(const unsigned char* cache, int64_t n_vol, int rows, int W, const unsigned char* tab, const unsigned int* off,
+                          const int64_t* vol_off, unsigned char* packed, int threads);
 /* Ditto proximal pull w -= coef*(w - ref).  ref: fedml_api/standalone/ditto/my_model_trainer.py:63-64. */
 int nidt_prox_pull(float* w, const float* ref, int64_t n, float coef, void* stream);
 

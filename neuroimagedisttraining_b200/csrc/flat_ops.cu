@@ -498,3 +498,68 @@ NIDT_API int nidt_copy_rows_h2d(const void* host_base, const int64_t* rows, int 
 NIDT_API int nidt_copy_rows_h2d_counted(const void* host_base, const int64_t* rows, int n, int64_t row_bytes, void* dst, void* stream, int* n_copies) {
     return copy_rows_h2d(host_base, rows, n, row_bytes, dst, stream, n_copies);
 }
+
+// ------------------------------------------------------------------------------------------------ host side of the zero-run-skipping uploads
+// The span table of a volume cache (runtime/staging.py::SparsePack): for every image row of W bytes the first non-zero byte and the
+// length up to the last one, and the row's offset among its volume's packed spans.  Plain host code on a few threads: the numpy
+// statement of the same scan takes seconds per GB, which every rank pays at start-up.
+#include <thread>
+#include <vector>
+namespace {
+template <class F>
+void parallel_volumes(int64_t n_vol, int threads, F f) {
+    if (threads < 1) threads = 1;
+    if (threads > 64) threads = 64;
+    if ((int64_t)threads > n_vol) threads = (int)(n_vol > 0 ? n_vol : 1);
+    std::vector<std::thread> pool;
+    for (int t = 0; t < threads; ++t)
+        pool.emplace_back([=] { for (int64_t v = t; v < n_vol; v += threads) f(v); });
+    for (auto& th : pool) th.join();
+}
+}  // namespace
+
+// tab: [n_vol][rows][2] bytes (start, length); off: [n_vol][rows] uint32; vol_bytes: [n_vol] int64 (packed bytes of each volume)
+NIDT_API int nidt_sparse_scan_rows(const unsigned char* cache, int64_t n_vol, int rows, int W, unsigned char* tab, unsigned int* off,
+                                   int64_t* vol_bytes, int threads) {
+    NIDT_REQUIRE(cache != nullptr && tab != nullptr && off != nullptr && vol_bytes != nullptr, "nidt_sparse_scan_rows: null argument");
+    NIDT_REQUIRE(n_vol >= 0 && rows >= 1 && W >= 1 && W <= 255, "nidt_sparse_scan_rows: n_vol=%lld rows=%d W=%d (W <= 255)", (long long)n_vol, rows, W);
+    parallel_volumes(n_vol, threads, [=](int64_t v) {
+        const unsigned char* p = cache + (size_t)v * rows * W;
+        unsigned char* tb = tab + (size_t)v * rows * 2;
+        unsigned int* of = off + (size_t)v * rows;
+        unsigned int acc = 0;
+        for (int r = 0; r < rows; ++r, p += W) {
+            int a = 0, b = W - 1;
+            while (a < W && p[a] == 0) ++a;
+            int len = 0;
+            if (a < W) {
+                while (p[b] == 0) --b;
+                len = b - a + 1;
+            } else {
+                a = 0;
+            }
+            tb[2 * r] = (unsigned char)a;
+            tb[2 * r + 1] = (unsigned char)len;
+            of[r] = acc;
+            acc += (unsigned int)len;
+        }
+        vol_bytes[v] = (int64_t)acc;
+    });
+    return 0;
+}
+
+// packed[vol_off[v] + off[v][r] ...] = the span of row r of volume v
+NIDT_API int nidt_sparse_copy_rows(const unsigned char* cache, int64_t n_vol, int rows, int W, const unsigned char* tab, const unsigned int* off,
+                                   const int64_t* vol_off, unsigned char* packed, int threads) {
+    NIDT_REQUIRE(cache != nullptr && tab != nullptr && off != nullptr && vol_off != nullptr && (packed != nullptr || n_vol == 0),
+                 "nidt_sparse_copy_rows: null argument");
+    parallel_volumes(n_vol, threads, [=](int64_t v) {
+        const unsigned char* p = cache + (size_t)v * rows * W;
+        const unsigned char* tb = tab + (size_t)v * rows * 2;
+        const unsigned int* of = off + (size_t)v * rows;
+        unsigned char* dst = packed + vol_off[v];
+        for (int r = 0; r < rows; ++r, p += W)
+            if (tb[2 * r + 1]) memcpy(dst + of[r], p + tb[2 * r], tb[2 * r + 1]);
+    });
+    return 0;
+}

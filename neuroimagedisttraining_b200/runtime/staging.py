@@ -50,10 +50,54 @@ class SparsePack:
     row a (start, length) byte pair and the span's offset inside its volume (uint32).  An upload then moves the spans and 6 bytes per
     row; ``nidt_expand_sparse_rows_u8`` rebuilds the dense volume on the device.  Lossless."""
 
-    def __init__(self, cache: torch.Tensor, block: int = 32):
+    def __init__(self, cache: torch.Tensor, block: int = 32, native: Optional[bool] = None):
         n, d, h, w = cache.shape
         assert w <= 255
         self.rows, self.w = d * h, w
+        self.dense_bytes = n * self.rows * w
+        pin = torch.cuda.is_available()
+        lib = self._native_lib() if native in (None, True) else None
+        if native is True and lib is None:
+            raise RuntimeError("SparsePack: the native scan is not available")
+        if lib is not None and cache.is_contiguous() and cache.dtype == torch.uint8:
+            self._build_native(lib, cache, n, pin)
+        else:
+            self._build_numpy(cache, n, block, pin)
+        self.ratio = (int(self.vol_off[-1]) + self.tab.numel() + 4 * self.off.numel()) / max(1, self.dense_bytes)
+
+    @staticmethod
+    def _native_lib():
+        try:
+            from ..ops import native as _n
+            lib = _n.load()
+            i32, i64, vp = C.c_int, C.c_int64, C.c_void_p
+            lib.nidt_sparse_scan_rows.argtypes = [vp, i64, i32, i32, vp, vp, vp, i32]
+            lib.nidt_sparse_scan_rows.restype = i32
+            lib.nidt_sparse_copy_rows.argtypes = [vp, i64, i32, i32, vp, vp, vp, vp, i32]
+            lib.nidt_sparse_copy_rows.restype = i32
+            return lib
+        except Exception:
+            return None
+
+    def _build_native(self, lib, cache: torch.Tensor, n: int, pin: bool) -> None:
+        """Span table + packed spans by the library's host code (a few threads; seconds -> tenths of a second per GB)."""
+        from ..ops import native as _n
+        threads = max(1, min(16, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)))
+        self.tab = torch.empty((n, self.rows, 2), dtype=torch.uint8)
+        self.off = torch.empty((n, self.rows), dtype=torch.int32)                 # bit pattern of the uint32 offsets
+        vol_bytes = np.zeros(n, np.int64)
+        _n.check(lib.nidt_sparse_scan_rows(cache.data_ptr(), n, self.rows, self.w, self.tab.data_ptr(), self.off.data_ptr(), vol_bytes.ctypes.data,
+                                           threads), "nidt_sparse_scan_rows")
+        self.vol_off = np.concatenate([[0], np.cumsum(vol_bytes)]).astype(np.int64)
+        self.max_vol_bytes = int(vol_bytes.max()) if n else 0
+        self.packed = torch.empty(int(self.vol_off[-1]), dtype=torch.uint8)
+        if pin:
+            self.packed, self.tab, self.off = self.packed.pin_memory(), self.tab.pin_memory(), self.off.pin_memory()
+        _n.check(lib.nidt_sparse_copy_rows(cache.data_ptr(), n, self.rows, self.w, self.tab.data_ptr(), self.off.data_ptr(), self.vol_off.ctypes.data,
+                                           self.packed.data_ptr(), threads), "nidt_sparse_copy_rows")
+
+    def _build_numpy(self, cache: torch.Tensor, n: int, block: int, pin: bool) -> None:
+        w = self.w
         a = cache.numpy().reshape(n, self.rows, w)
         cols = np.arange(w)
         tab = np.zeros((n, self.rows, 2), np.uint8)
@@ -75,11 +119,7 @@ class SparsePack:
             inside = (cols >= np.where(has, start, 0)[..., None]) & (cols < (np.where(has, start, 0) + ln)[..., None])
             chunks.append(blk[inside])                     # row-major: volume by volume, row by row
         self.vol_off = np.concatenate([[0], np.cumsum(vol_bytes)]).astype(np.int64)
-        total = int(self.vol_off[-1])
-        self.dense_bytes = n * self.rows * w
-        self.ratio = (total + tab.nbytes + off.nbytes) / max(1, self.dense_bytes)
         self.max_vol_bytes = int(vol_bytes.max()) if n else 0
-        pin = torch.cuda.is_available()
         self.packed = torch.from_numpy(np.concatenate(chunks) if chunks else np.zeros(0, np.uint8))
         self.tab = torch.from_numpy(tab)
         self.off = torch.from_numpy(off.view(np.int32))    # bit pattern of the uint32 offsets
