@@ -201,6 +201,7 @@ class SlabTrainer(ModelTrainer):
         if hasattr(self.engine, "batch_ids") and self.store is not None and hasattr(data, "indices"):
             st = self._stagers.get(data.batch_size) if hasattr(self, "_stagers") else None
             self.engine.batch_ids = getattr(st, "last_ids", None) if st is not None else None
+            self.engine.batch_ids_key = id(self.store)
 
     def _batches_epochs(self, data, epochs: int, lookahead_data=None):
         """``(epoch, x, y)`` over ``epochs`` passes of ``data``.  Client staging: the loader's volumes are uploaded once (ahead of

@@ -180,6 +180,7 @@ class GramCache:
         self.scratch: Optional[torch.Tensor] = None
         self.scratch_n = 0
         self.built = 0                                     # matrices computed so far (cold misses)
+        self.key = None                                    # which volume store the ids refer to (a new store empties the cache)
         self.batch = torch.zeros(self.floats, dtype=torch.float64, device=device)       # the current batch's sum: a stable address
 
     def _grow(self, need: int) -> None:
@@ -192,6 +193,12 @@ class GramCache:
         if self.buf is not None and self.slots:
             new[:self.cap] = self.buf
         self.buf, self.cap = new, cap
+
+    def use_store(self, key) -> None:
+        """The ids that follow index the store identified by ``key``; matrices cached for another store are dropped."""
+        if key != self.key:
+            self.slots.clear()
+            self.key = key
 
     def sum_for(self, ids, x: torch.Tensor, stream: int) -> bool:
         """``self.batch`` <- sum of the Gram matrices of the samples ``ids`` (row i of the u8 batch ``x`` is sample ids[i]); computes
@@ -276,6 +283,7 @@ class B200Engine:
         self._seed_extra = 0
         self._mode = 0                    # block-0 backward variant of the step being issued by the Python launch loop (see _bwd0_mode)
         self.batch_ids = None             # store ids of the samples of the NEXT training batch (set by the trainer, consumed by the step)
+        self.batch_ids_key = None         # identity of the store those ids index (per-sample caches are per store)
         self._alloc(wgrad_ctas)
         # native step executor (csrc/executor.cu): one C call per step instead of one per kernel; NIDT_PY_EXEC=1 keeps the
         # Python launch loop (it is also what start_profile() switches to, for per-kernel timings)
@@ -659,6 +667,7 @@ class B200Engine:
         base = 1 if (self.fused_bwd0 and self._plan.blocks[0].amax) else 0
         if ids is None or not self.alg_bwd0 or not self.s2d_wgrad or not self._plan.blocks[0].amax:
             return base
+        self.gram.use_store(self.batch_ids_key)
         return 2 if self.gram.sum_for(ids, x, self._stream()) else base
 
     def _native_step(self, x, y, hp, mask, mom, first_step: bool, do_update: bool) -> None:

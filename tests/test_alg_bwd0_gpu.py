@@ -144,3 +144,7 @@ def test_training_with_cached_gram_matrices_and_partial_batches():
     xx = torch.stack([x[0], x[0], x[3], x[1]])
     eng.train_step(xx, y, hp, None, mom, False)
     assert eng.gram.built == 5
+    # ids are per volume store: the same ids under another store key are new samples
+    eng.batch_ids, eng.batch_ids_key = [11, 12, 13, 14], "another store"
+    eng.train_step(x, y, hp, None, mom, False)
+    assert eng.gram.built == 9 and eng._plan.blocks[0].bwd0_mode == 2
