@@ -207,6 +207,14 @@ int nidt_conv_in_s2d_supported(int Di, int Hi, int Wi, int k, int stride, int pa
 int64_t nidt_conv_in_s2d_wgrad_scratch_floats(void);
 int nidt_conv_in_s2d_fprop(const void* x, const float* w, const float* bias, void* y, float* stats_partials, int N, int Di, int Hi,
                            int Wi, float scale, void* stream);
+/* the same convolution with every 3 consecutive output columns reduced in the epilogue to the one BatchNorm + ReLU + MaxPool3d(3,3) would
+ * pick (max of y where gamma >= 0, min where gamma < 0): yw bf16 [N][Do][Ho][Wp][64], aw uint16 [N][Do][Ho][Wp][8] (2 bits per channel: the
+ * column), Wp = (Wo - 3) / 3 + 1; the full-resolution output is not written.  nidt_bn_relu_pool3w_fwd finishes the pooling from these
+ * (a, and -- both or neither -- ymax / amax as nidt_bn_relu_pool3_fwd_amax would produce them from the full tensor). */
+int nidt_conv_in_s2d_fprop_poolw(const void* x, const float* w, const float* bias, const float* gamma, void* yw, void* aw,
+                                 float* stats_partials, int N, int Di, int Hi, int Wi, float scale, void* stream);
+int nidt_bn_relu_pool3w_fwd(const void* yw, const void* aw, void* a, void* ymax, void* amax, int N, int D, int H, int W, int C,
+                            const float* scale, const float* shift, int relu, void* stream);
 int nidt_conv_in_s2d_wgrad(const void* x, const void* dy, float* grad, float* grad_bias, float* scratch, int N, int Di, int Hi,
                            int Wi, float scale, void* stream);
 
@@ -275,6 +283,8 @@ typedef struct {
     void* amax;                                           /* block 0, optional: winning pool taps (uint8), written by the forward when bwd0_mode != 0 */
     double* gram;                                         /* block 0, bwd0_mode 2: the batch's patch Gram matrix (nidt_conv_in_gram_sum) */
     float* alg_scratch;                                   /* block 0, bwd0_mode 2: nidt_conv_in_alg_scratch_floats() floats */
+    void *yw, *aw;                                        /* block 0, optional: conv output reduced along W in the conv epilogue (nidt_conv_in_s2d_fprop_poolw)
+                                                             -- used by evaluation batches and by training steps with bwd0_mode 2, which never read y */
     int bwd0_mode;                                        /* block 0 backward: 0 = dY written, then wgrad; 1 = dY formed inside the wgrad kernel
                                                              (nidt_conv_in_s2d_wgrad_fused); 2 = no pass over y / dY at all (nidt_conv_in_alg_wgrad) */
 } nidt_block_t;

@@ -393,6 +393,70 @@ __global__ void __launch_bounds__(256, V == 4 ? 3 : 1) bn_relu_pool3_fwd_kernel(
     *reinterpret_cast<VT*>(ymax + idx * V) = packv<V>(yb);
 }
 
+// The same pooling from a conv output that was already reduced along W in the conv epilogue (nidt_conv_in_s2d_fprop_poolw): per window
+// 9 candidates (kd, kh) -- each the winner of its 3 columns, with the column in 2 bits -- instead of 27.  One thread = one pooled output
+// x 8 channels.  Candidates are visited in (kd, kh) order with a strict comparison, and the column winner was the first maximum of its
+// three, so the tap recorded is the first maximum in (kd, kh, kw) order: exactly what bn_relu_pool3_fwd_kernel finds on the full tensor.
+template <bool kTrain>
+__global__ void __launch_bounds__(256) bn_relu_pool3w_fwd_kernel(const __nv_bfloat16* __restrict__ yw, const unsigned short* __restrict__ aw,
+                                                                 __nv_bfloat16* __restrict__ a, __nv_bfloat16* __restrict__ ymax,
+                                                                 unsigned char* __restrict__ amax, int N, int D, int H, int Dp, int Hp, int Wp,
+                                                                 const float* __restrict__ scale, const float* __restrict__ shift, int relu) {
+    constexpr int C = 64, CG = 8;
+    const int64_t total = (int64_t)N * Dp * Hp * Wp * CG;
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const int cg = (int)(idx % CG);
+    int64_t p = idx / CG;
+    const int wp = (int)(p % Wp); p /= Wp;
+    const int hp = (int)(p % Hp); p /= Hp;
+    const int dp = (int)(p % Dp);
+    const int n = (int)(p / Dp);
+    float sc[8], sh[8], best[8], yb[8];
+    unsigned int tap[8];
+    ldv<8>(scale + cg * 8, sc);
+    ldv<8>(shift + cg * 8, sh);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { best[i] = -INFINITY; yb[i] = 0.f; tap[i] = 0u; }
+    uint4 v[9];
+    unsigned short cw[9];
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+        const int64_t pos = (((int64_t)n * D + dp * 3 + t / 3) * H + hp * 3 + t % 3) * Wp + wp;
+        v[t] = *reinterpret_cast<const uint4*>(yw + pos * C + cg * 8);
+        cw[t] = aw[pos * CG + cg];
+    }
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+        float f[8];
+        unpack8(v[t], f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float pv = fmaf(f[i], sc[i], sh[i]);
+            if (pv > best[i]) {
+                best[i] = pv; yb[i] = f[i];
+                tap[i] = (unsigned int)((t / 3) * 9 + (t % 3) * 3) + (((unsigned int)cw[t] >> (2 * i)) & 3u);
+            }
+        }
+    }
+    if (kTrain) {
+        unsigned int w0 = 0u, w1 = 0u;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const unsigned int tb = (relu && !(best[i] > 0.f)) ? 255u : tap[i];
+            if (i < 4) w0 |= tb << (8 * i);
+            else w1 |= tb << (8 * (i - 4));
+        }
+        *reinterpret_cast<uint2*>(amax + idx * 8) = make_uint2(w0, w1);
+        *reinterpret_cast<uint4*>(ymax + idx * 8) = packv<8>(yb);
+    }
+    if (relu) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) best[i] = fmaxf(best[i], 0.f);
+    }
+    *reinterpret_cast<uint4*>(a + idx * 8) = packv<8>(best);
+}
+
 // reduce over the pooled tensor: partials[block][2][C]
 __global__ void __launch_bounds__(256) bn_pool3_bwd_reduce_kernel(
     const __nv_bfloat16* __restrict__ ymax, const __nv_bfloat16* __restrict__ da, int64_t npos, int C,
@@ -631,6 +695,28 @@ static int bn_relu_pool_fwd_impl(const void* y, void* a, void* ymax, void* amax,
     if (blocks > (int64_t)kNumSMs * 16) blocks = kNumSMs * 16;
     if (blocks < 1) blocks = 1;
     bn_relu_pool_fwd_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)y, (__nv_bfloat16*)a, g, scale, shift, relu);
+    NIDT_LAUNCH_CHECK();
+    return 0;
+}
+
+// BatchNorm + ReLU + MaxPool3d(3,3) of a 64-channel conv output [N][D][H][W] that arrives reduced along W: yw bf16 [N][D][H][Wp][64]
+// and aw uint16 [N][D][H][Wp][8] as nidt_conv_in_s2d_fprop_poolw writes them (Wp = (W - 3) / 3 + 1).  a: pooled activation
+// [N][Dp][Hp][Wp][64]; ymax / amax (both or neither): raw conv output and tap (kd*9 + kh*3 + kw, 255 = gated by ReLU) of every
+// window's winner -- the same three tensors nidt_bn_relu_pool3_fwd_amax produces from the full-resolution output.
+NIDT_API int nidt_bn_relu_pool3w_fwd(const void* yw, const void* aw, void* a, void* ymax, void* amax, int N, int D, int H, int W, int C,
+                                     const float* scale, const float* shift, int relu, void* stream) {
+    NIDT_REQUIRE(C == 64 && D >= 3 && H >= 3 && W >= 3, "nidt_bn_relu_pool3w_fwd: C=%d (64) D=%d H=%d W=%d (>= 3)", C, D, H, W);
+    NIDT_REQUIRE(yw != nullptr && aw != nullptr && a != nullptr && (ymax == nullptr) == (amax == nullptr), "nidt_bn_relu_pool3w_fwd: bad pointers");
+    const int Dp = (D - 3) / 3 + 1, Hp = (H - 3) / 3 + 1, Wp = (W - 3) / 3 + 1;
+    const int64_t total = (int64_t)N * Dp * Hp * Wp * 8;
+    const unsigned grid = (unsigned)((total + 255) / 256);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (ymax != nullptr)
+        bn_relu_pool3w_fwd_kernel<true><<<grid, 256, 0, s>>>((const __nv_bfloat16*)yw, (const unsigned short*)aw, (__nv_bfloat16*)a, (__nv_bfloat16*)ymax,
+                                                             (unsigned char*)amax, N, D, H, Dp, Hp, Wp, scale, shift, relu);
+    else
+        bn_relu_pool3w_fwd_kernel<false><<<grid, 256, 0, s>>>((const __nv_bfloat16*)yw, (const unsigned short*)aw, (__nv_bfloat16*)a, nullptr, nullptr, N,
+                                                              D, H, Dp, Hp, Wp, scale, shift, relu);
     NIDT_LAUNCH_CHECK();
     return 0;
 }

@@ -208,8 +208,22 @@ __device__ __forceinline__ void staging_loop(const uint8_t* __restrict__ x, cons
 }
 
 // ======================================================================================= fprop
+// Optional epilogue for consumers that only need the layer's output max-pooled 3x3x3 (the engine's forward when the backward does not
+// read y): instead of storing the tile, the epilogue reduces every 3 consecutive output columns of a line to the one BatchNorm + ReLU
+// + MaxPool would pick -- the maximum of y where gamma >= 0, the minimum where gamma < 0 (the affine map is monotone per channel;
+// first one on ties) -- and stores that value (raw y, bf16) plus its column 0..2.  A third of the bytes written, and the pooling
+// kernel that follows (nidt_bn_relu_pool3w_fwd) reads 9 candidates per window instead of 27.  BatchNorm statistics are unaffected
+// (they are summed from the staged tile either way).
+struct PoolW {
+    __nv_bfloat16* yw;          // [N][Do][Ho][Wp][64]; nullptr = store the full tile through tm_y
+    unsigned short* aw;         // [N][Do][Ho][Wp][8]: 2 bits per channel (column of the winner) for the 8 channels of a 16-byte chunk
+    const float* gamma;         // BatchNorm weight: its sign decides max / min
+    int Wp;                     // (Wo - 3) / 3 + 1
+};
+
 __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
-                                                              const __grid_constant__ CUtensorMap tm_y, float* __restrict__ stats_partials, const Geom g) {
+                                                              const __grid_constant__ CUtensorMap tm_y, float* __restrict__ stats_partials, const Geom g,
+                                                              const PoolW pw) {
     extern __shared__ __align__(1024) uint8_t smem[];
     if ((tc::smem_u32(smem) & 1023u) != 0u) __trap();
     uint8_t* staging = smem;                              // [2][128 rows][128 B] swizzled (TMA store source), one per epilogue group
@@ -236,7 +250,7 @@ __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __r
     if (threadIdx.x < 64) sbias[threadIdx.x] = bias != nullptr ? bias[threadIdx.x] : 0.f;
     tc::fence_proxy_async_smem();
     if (threadIdx.x == 0) {
-        tc::tma_prefetch_desc(&tm_y);
+        if (pw.yw == nullptr) tc::tma_prefetch_desc(&tm_y);
         for (int i = 0; i < kARing; ++i) { tc::mbar_init(&a_full[i], 4); tc::mbar_init(&a_empty[i], 1); }
         for (int i = 0; i < 2; ++i) { tc::mbar_init(&t_full[i], 1); tc::mbar_init(&t_empty[i], 4); }
         for (int i = 0; i < kRawRing; ++i) { tc::mbar_init(&raw_full[i], 1); tc::mbar_init(&raw_empty[i], 4); }
@@ -311,6 +325,12 @@ __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __r
         float s1[8], s2[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) s1[j] = s2[j] = 0.f;
+        uint32_t sgn[4] = {0u, 0u, 0u, 0u};             // pooled epilogue: sign-bit flips of this thread's 8 channels (gamma < 0: minimum wins)
+        if (pw.yw != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (pw.gamma[c8 * 8 + j] < 0.f) sgn[j >> 1] |= (j & 1) ? 0x80000000u : 0x00008000u;
+        }
         TileIter t(g, blockIdx.x + e * gridDim.x, 2 * gridDim.x);
         for (int i = e; t.valid(g); i += 2, t.next(g)) {
             const uint32_t u = i >> 1;
@@ -340,10 +360,44 @@ __global__ void __launch_bounds__(kFpThreads, 1) fprop_kernel(const uint8_t* __r
             }
             tc::fence_proxy_async_smem();
             named_bar(3 + e, 128);
-            if (et == 0) {
-                tc::tma_store_5d(&tm_y, stg, 0, 0, h0, d, n);
-                if (lines == 2) tc::tma_store_5d(&tm_y, stg + 64 * 128, 0, 0, h0 + 1, d, n);
-                tc::tma_store_commit();
+            if (pw.yw == nullptr) {
+                if (et == 0) {
+                    tc::tma_store_5d(&tm_y, stg, 0, 0, h0, d, n);
+                    if (lines == 2) tc::tma_store_5d(&tm_y, stg + 64 * 128, 0, 0, h0 + 1, d, n);
+                    tc::tma_store_commit();
+                }
+            } else {
+                // item = (line, window along W, 16-byte channel chunk); 128 threads step by 128 items, so a thread keeps its chunk c8
+                const int items = lines * pw.Wp * 8;
+                for (int item = et; item < items; item += 128) {
+                    const int q = item >> 3;
+                    const int ln = q / pw.Wp, wq = q - ln * pw.Wp;
+                    const int r0 = ln * 64 + 3 * wq;
+                    uint4 v[3];
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) v[k] = *reinterpret_cast<const uint4*>(stg + (r0 + k) * 128 + ((c8 ^ ((r0 + k) & 7)) << 4));
+                    const uint32_t* v0 = reinterpret_cast<const uint32_t*>(&v[0]);
+                    const uint32_t* v1 = reinterpret_cast<const uint32_t*>(&v[1]);
+                    const uint32_t* v2 = reinterpret_cast<const uint32_t*>(&v[2]);
+                    uint4 o;
+                    uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
+                    uint32_t code = 0u;
+#pragma unroll
+                    for (int wd = 0; wd < 4; ++wd) {
+                        const uint32_t x0 = v0[wd] ^ sgn[wd], x1 = v1[wd] ^ sgn[wd], x2 = v2[wd] ^ sgn[wd];
+                        const __nv_bfloat162 b0 = *reinterpret_cast<const __nv_bfloat162*>(&x0), b1 = *reinterpret_cast<const __nv_bfloat162*>(&x1),
+                                             b2 = *reinterpret_cast<const __nv_bfloat162*>(&x2);
+                        const uint32_t g1 = __hgt2_mask(b1, b0);                       // strictly greater: the first one wins ties
+                        const uint32_t g2 = __hgt2_mask(b2, __hmax2(b0, b1));
+                        const uint32_t w01 = (v1[wd] & g1) | (v0[wd] & ~g1);
+                        ow[wd] = (v2[wd] & g2) | (w01 & ~g2);
+                        const uint32_t cc = (g1 & ~g2 & 0x00010001u) | (g2 & 0x00020002u);   // 2-bit column per half
+                        code |= ((cc & 3u) | ((cc >> 14) & 0xCu)) << (4 * wd);
+                    }
+                    const size_t pos = (((size_t)n * g.Do + d) * g.Ho + (h0 + ln)) * pw.Wp + wq;
+                    *reinterpret_cast<uint4*>(pw.yw + pos * 64 + c8 * 8) = o;
+                    pw.aw[pos * 8 + c8] = (unsigned short)code;
+                }
             }
             if (stats_partials != nullptr) {
                 // 16-byte shared loads: thread (c8, part) sums 8 channels over rows w = part, part+16, ... of each line
@@ -662,19 +716,38 @@ NIDT_API int nidt_conv_in_s2d_supported(int Di, int Hi, int Wi, int k, int strid
 }
 NIDT_API int64_t nidt_conv_in_s2d_wgrad_scratch_floats() { return (int64_t)kNumSMs * 3 * 128 * 64; }
 
+static int s2d_fprop_impl(const void* x, const float* w, const float* bias, void* y, float* stats_partials, int N, int Di, int Hi, int Wi,
+                          float scale, void* stream, const s2d::PoolW& pw);
 // same contract as nidt_conv_in_fprop, for k = 5, stride = 2, pad = 0
 NIDT_API int nidt_conv_in_s2d_fprop(const void* x, const float* w, const float* bias, void* y, float* stats_partials, int N, int Di, int Hi, int Wi,
                                     float scale, void* stream) {
+    NIDT_REQUIRE(y != nullptr, "nidt_conv_in_s2d_fprop: y is null");
+    return s2d_fprop_impl(x, w, bias, y, stats_partials, N, Di, Hi, Wi, scale, stream, s2d::PoolW{nullptr, nullptr, nullptr, 0});
+}
+// The same convolution with its output reduced over every 3 consecutive output columns in the epilogue (see s2d::PoolW): yw is bf16
+// [N][Do][Ho][Wp][64] with Wp = (Wo - 3) / 3 + 1, aw uint16 [N][Do][Ho][Wp][8] (2 bits per channel: which of the 3 columns), gamma the
+// BatchNorm weight that follows (its sign selects maximum / minimum).  The full-resolution output is not written.
+NIDT_API int nidt_conv_in_s2d_fprop_poolw(const void* x, const float* w, const float* bias, const float* gamma, void* yw, void* aw,
+                                          float* stats_partials, int N, int Di, int Hi, int Wi, float scale, void* stream) {
+    NIDT_REQUIRE(yw != nullptr && aw != nullptr && gamma != nullptr, "nidt_conv_in_s2d_fprop_poolw: null argument");
+    const int Wo = (Wi - 5) / 2 + 1;
+    NIDT_REQUIRE(Wo >= 3, "nidt_conv_in_s2d_fprop_poolw: output width %d < 3", Wo);
+    return s2d_fprop_impl(x, w, bias, nullptr, stats_partials, N, Di, Hi, Wi, scale, stream,
+                          s2d::PoolW{(__nv_bfloat16*)yw, (unsigned short*)aw, gamma, (Wo - 3) / 3 + 1});
+}
+static int s2d_fprop_impl(const void* x, const float* w, const float* bias, void* y, float* stats_partials, int N, int Di, int Hi, int Wi,
+                          float scale, void* stream, const s2d::PoolW& pw) {
     s2d::Geom g;
     if (s2d::make_geom(g, N, Di, Hi, Wi, scale)) return 2;
     CUtensorMap ty;
-    if (make_tmap_act5d(&ty, y, N, g.Do, g.Ho, g.Wo, 64, g.Wo, 1, 1, 1, 1)) return 1;
+    memset(&ty, 0, sizeof(ty));
+    if (y != nullptr && make_tmap_act5d(&ty, y, N, g.Do, g.Ho, g.Wo, 64, g.Wo, 1, 1, 1, 1)) return 1;
     const size_t smem = s2d::smem_fprop(g);
     NIDT_REQUIRE(smem <= 227 * 1024, "conv_in_s2d_fprop: shared memory %zu B", smem);
     const int grid = g.total_tiles < kNumSMs ? g.total_tiles : kNumSMs;
     cudaStream_t s = (cudaStream_t)stream;
     NIDT_CUDA_CHECK(cudaFuncSetAttribute(s2d::fprop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    s2d::fprop_kernel<<<grid, s2d::kFpThreads, smem, s>>>((const uint8_t*)x, w, bias, ty, stats_partials, g);
+    s2d::fprop_kernel<<<grid, s2d::kFpThreads, smem, s>>>((const uint8_t*)x, w, bias, ty, stats_partials, g, pw);
     NIDT_LAUNCH_CHECK();
     if (stats_partials != nullptr && grid < kNumSMs)
         NIDT_CUDA_CHECK(cudaMemsetAsync(stats_partials + (size_t)grid * 128, 0, (size_t)(kNumSMs - grid) * 128 * sizeof(float), s));

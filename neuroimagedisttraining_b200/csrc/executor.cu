@@ -94,8 +94,14 @@ int forward(Ctx& c, const void* x, float* slab, bool train) {
         float* stats = train ? b.stats : nullptr;
         const float* bias = b.has_bias ? at((const float*)slab, b.off_b) : nullptr;
         int tiles = b.stats_tiles;
+        // block 0 with nobody reading the full-resolution y afterwards (evaluation; training whose backward works from the pooled tensors):
+        // the conv epilogue reduces along W and the pooling kernel finishes from a third of the data
+        const bool poolw = i == 0 && b.s2d && b.yw != nullptr && b.aw != nullptr && b.pool_k == 3 && b.pool_s == 3 && b.cout == 64 && b.c_w >= 3 &&
+                           (!train || (b.bwd0_mode == 2 && b.amax != nullptr && b.ymax != nullptr));
         if (i == 0) {
-            if (b.s2d) NIDT_TRY(nidt_conv_in_s2d_fprop(x, at(slab, b.off_w), bias, b.y, stats, B, b.in_d, b.in_h, b.in_w, p->input_scale, c.st));
+            if (poolw) NIDT_TRY(nidt_conv_in_s2d_fprop_poolw(x, at(slab, b.off_w), bias, at(slab, b.off_gamma), b.yw, b.aw, stats, B, b.in_d, b.in_h,
+                                                             b.in_w, p->input_scale, c.st));
+            else if (b.s2d) NIDT_TRY(nidt_conv_in_s2d_fprop(x, at(slab, b.off_w), bias, b.y, stats, B, b.in_d, b.in_h, b.in_w, p->input_scale, c.st));
             else NIDT_TRY(nidt_conv_in_fprop(x, at(slab, b.off_w), bias, b.y, stats, B, b.in_d, b.in_h, b.in_w, b.k, b.stride, b.pad, p->input_scale, c.st));
         } else {
             const Box bx = B == p->max_batch ? Box{b.box[0], b.box[1], b.box[2], b.box[3]} : choose_box(b.c_w, b.c_h, b.c_d, B);
@@ -110,7 +116,10 @@ int forward(Ctx& c, const void* x, float* slab, bool train) {
         else
             NIDT_TRY(nidt_bn_eval_prepare(b.cout, at(slab, b.off_gamma), at(slab, b.off_beta), at(slab, b.off_rm), at(slab, b.off_rv), 1e-5f, b.scale,
                                           b.shift, c.st));
-        if (train && i == 0 && b.bwd0_mode != 0 && b.amax != nullptr && b.ymax != nullptr && b.s2d && b.pool_k == 3 && b.pool_s == 3)
+        if (poolw)
+            NIDT_TRY(nidt_bn_relu_pool3w_fwd(b.yw, b.aw, b.a, train ? b.ymax : nullptr, train ? b.amax : nullptr, B, b.c_d, b.c_h, b.c_w, b.cout, b.scale,
+                                             b.shift, b.relu, c.st));
+        else if (train && i == 0 && b.bwd0_mode != 0 && b.amax != nullptr && b.ymax != nullptr && b.s2d && b.pool_k == 3 && b.pool_s == 3)
             NIDT_TRY(nidt_bn_relu_pool3_fwd_amax(b.y, b.a, b.ymax, b.amax, B, b.c_d, b.c_h, b.c_w, b.cout, b.scale, b.shift, b.relu, c.st));
         else
             NIDT_TRY(nidt_bn_relu_pool_fwd(b.y, b.a, (train && b.ymax != nullptr) ? b.ymax : nullptr, B, b.c_d, b.c_h, b.c_w, b.cout, b.pool_k, b.pool_s,

@@ -100,6 +100,10 @@ def _declare(lib) -> None:
     lib.nidt_conv_in_gram_sum.restype = i32
     lib.nidt_conv_in_alg_wgrad.argtypes = [vp] * 13 + [i32, i32, i32, i32, f32, vp, vp, f32, vp]
     lib.nidt_conv_in_alg_wgrad.restype = i32
+    lib.nidt_conv_in_s2d_fprop_poolw.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, vp]
+    lib.nidt_conv_in_s2d_fprop_poolw.restype = i32
+    lib.nidt_bn_relu_pool3w_fwd.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, i32, vp]
+    lib.nidt_bn_relu_pool3w_fwd.restype = i32
     for name, argtypes in {
         "nidt_ew_bf16": [vp, vp, vp, i64, i32, vp],
         "nidt_maxpool3d_fwd": [vp, vp, vp] + [i32] * 8 + [vp],
@@ -130,7 +134,7 @@ class _BlockC(C.Structure):
                                              "wf", "wd", "wg_scratch")]
                 + [(n, C.c_int) for n in ("stats_tiles", "s2d", "block_n", "dgrad_block_n", "splits")]
                 + [("box", C.c_int * 4), ("dbox", C.c_int * 4), ("amax", C.c_void_p), ("gram", C.c_void_p), ("alg_scratch", C.c_void_p),
-                   ("bwd0_mode", C.c_int)])
+                   ("yw", C.c_void_p), ("aw", C.c_void_p), ("bwd0_mode", C.c_int)])
 
 
 class _PlanC(C.Structure):
@@ -342,6 +346,17 @@ class B200Engine:
                 b.amax = torch.empty(b.a.shape, dtype=torch.uint8, device=dev) if want_amax else None
                 self.gram = GramCache(lib, dev, in_dhw, self.input_scale, B) if self.alg_bwd0 else None
                 b.alg_scratch = (torch.empty(lib.nidt_conv_in_alg_scratch_floats(), dtype=torch.float32, device=dev) if self.alg_bwd0 else None)
+                # NIDT_POOLW: when nobody reads the full-resolution conv output afterwards (evaluation; training steps whose backward
+                # works from the pooled tensors), the conv epilogue reduces every 3 output columns to the pooling winner and the pooling
+                # kernel finishes from a third of the data (nidt_conv_in_s2d_fprop_poolw + nidt_bn_relu_pool3w_fwd)
+                self.poolw = (os.environ.get("NIDT_POOLW", "0") == "1" and b.s2d and b.ymax is not None and spec.cout == 64 and spec.k == 5
+                              and W >= 3)
+                if self.poolw:
+                    Wp = (W - 3) // 3 + 1
+                    b.yw = torch.empty((B, D, H, Wp, 64), dtype=bf, device=dev)
+                    b.aw = torch.empty((B, D, H, Wp, 8), dtype=torch.int16, device=dev)
+                else:
+                    b.yw = b.aw = None
                 n_scr = max(lib.nidt_conv_in_grid() * 128 * 64, lib.nidt_conv_in_s2d_wgrad_scratch_floats())
                 b.wg_scratch = torch.zeros(n_scr, dtype=torch.float32, device=dev)
             else:
@@ -391,6 +406,8 @@ class B200Engine:
                 c.amax = ptr(getattr(b, "amax", None)) if (b.s2d and self.s2d_wgrad) else None
                 if self.alg_bwd0 and c.amax:
                     c.gram, c.alg_scratch = self.gram.batch.data_ptr(), b.alg_scratch.data_ptr()
+                if self.poolw and c.s2d:
+                    c.yw, c.aw = b.yw.data_ptr(), b.aw.data_ptr()
                 c.bwd0_mode = 1 if (self.fused_bwd0 and c.amax) else 0
             else:
                 c.wf, c.wd = ptr(b.wf), ptr(b.wd)
@@ -482,9 +499,15 @@ class B200Engine:
             D, H, W = b.c_dhw
             stats = b.stats.data_ptr() if train else None
             bias = self._p(slab, s.conv + ".bias") if s.bias else None
+            poolw = (i == 0 and getattr(self, "poolw", False) and b.s2d and self.s2d_wgrad
+                     and (not train or (self._mode == 2 and getattr(b, "amax", None) is not None)))
             if i == 0:
                 iD, iH, iW = b.in_dhw
-                if b.s2d:     # 5^3 / stride 2: space-to-depth lines feed tcgen05 directly, no im2col
+                if poolw:     # nobody reads the full-resolution y afterwards: reduced along W in the conv epilogue
+                    self._chk(lib.nidt_conv_in_s2d_fprop_poolw(x.data_ptr(), self._p(slab, s.conv + ".weight"), bias, self._p(slab, s.bn + ".weight"),
+                                                               b.yw.data_ptr(), b.aw.data_ptr(), stats, B, iD, iH, iW, self.input_scale, st),
+                              "conv_in_s2d_fprop_poolw")
+                elif b.s2d:   # 5^3 / stride 2: space-to-depth lines feed tcgen05 directly, no im2col
                     self._chk(lib.nidt_conv_in_s2d_fprop(x.data_ptr(), self._p(slab, s.conv + ".weight"), bias, b.y.data_ptr(), stats,
                                                          B, iD, iH, iW, self.input_scale, st), "conv_in_s2d_fprop")
                 else:
@@ -507,7 +530,11 @@ class B200Engine:
                                                b.mean.data_ptr(), b.invstd.data_ptr(), st), "bn_finalize")
             else:
                 self._chk(lib.nidt_bn_eval_prepare(s.cout, g, be, rm, rv, 1e-5, b.scale.data_ptr(), b.shift.data_ptr(), st), "bn_eval_prepare")
-            if train and i == 0 and self._mode != 0 and getattr(b, "amax", None) is not None and self.s2d_wgrad:
+            if poolw:
+                self._chk(lib.nidt_bn_relu_pool3w_fwd(b.yw.data_ptr(), b.aw.data_ptr(), b.a.data_ptr(), b.ymax.data_ptr() if train else None,
+                                                      b.amax.data_ptr() if train else None, B, D, H, W, s.cout, b.scale.data_ptr(), b.shift.data_ptr(),
+                                                      int(s.relu), st), "bn_relu_pool3w_fwd")
+            elif train and i == 0 and self._mode != 0 and getattr(b, "amax", None) is not None and self.s2d_wgrad:
                 self._chk(lib.nidt_bn_relu_pool3_fwd_amax(b.y.data_ptr(), b.a.data_ptr(), b.ymax.data_ptr(), b.amax.data_ptr(), B, D, H, W, s.cout,
                                                           b.scale.data_ptr(), b.shift.data_ptr(), int(s.relu), st), "bn_relu_pool_fwd")
             else:

@@ -148,3 +148,36 @@ def test_training_with_cached_gram_matrices_and_partial_batches():
     eng.batch_ids, eng.batch_ids_key = [11, 12, 13, 14], "another store"
     eng.train_step(x, y, hp, None, mom, False)
     assert eng.gram.built == 9 and eng._plan.blocks[0].bwd0_mode == 2
+
+
+def test_forward_with_the_conv_epilogue_pooling_along_w_is_bit_identical(monkeypatch):
+    """NIDT_POOLW=1: when nobody reads the full-resolution conv output (evaluation; training with the backward from pooled tensors),
+    the conv epilogue keeps the pooling winner of every 3 output columns and the pooling kernel finishes from those.  Same winners, same
+    values: pooled activation, winner values / taps, every gradient, evaluation counters and logits must not change by a bit --
+    including the channel with a negative BatchNorm weight (its winner is the window's MINIMUM of y)."""
+    from neuroimagedisttraining_b200.fl.engine import EvalCounters
+    B = 4
+    monkeypatch.setenv("NIDT_POOLW", "1")
+    eng_p, _ = _engine(B)
+    monkeypatch.setenv("NIDT_POOLW", "0")
+    eng_s, _ = _engine(B)
+    assert eng_p.poolw and not eng_s.poolw
+    x, y = _batch(B, seed=7)
+    ids = [3, 1, 4, 2]
+    for native_exec in (True, False):                      # executor / graph replay, and the Python launch loop
+        res = []
+        for eng in (eng_p, eng_s):
+            eng.native_exec = eng.use_graphs = native_exec
+            for b in (B, B - 1):                           # a partial batch too
+                eng.batch_ids = ids[:b]
+                eng.compute_grads(x[:b], y[:b], True)
+                torch.cuda.synchronize()
+                b0 = eng.blocks[0]
+                res.append((eng.grad.flat.clone(), b0.a[:b].clone(), b0.ymax[:b].clone(), b0.amax[:b].clone()))
+            c = EvalCounters(DEV)
+            eng.eval_batch(x, y, c)
+            res.append((c.buf.clone(), eng.logits(x)))
+        n = len(res) // 2
+        for i in range(n):
+            for j, (p, s) in enumerate(zip(res[i], res[n + i])):
+                assert torch.equal(p, s), f"native_exec={native_exec} item {i}.{j}: {(p.double() - s.double()).abs().max().item()}"
