@@ -287,6 +287,7 @@ typedef struct {
                                                              -- used by evaluation batches and by training steps with bwd0_mode 2, which never read y */
     int bwd0_mode;                                        /* block 0 backward: 0 = dY written, then wgrad; 1 = dY formed inside the wgrad kernel
                                                              (nidt_conv_in_s2d_wgrad_fused); 2 = no pass over y / dY at all (nidt_conv_in_alg_wgrad) */
+    int poolw_train;                                      /* block 0: use yw / aw in training steps too (bwd0_mode 2 only); evaluation always does */
 } nidt_block_t;
 typedef struct {
     int n_blocks, max_batch;

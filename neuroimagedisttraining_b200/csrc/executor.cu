@@ -97,7 +97,7 @@ int forward(Ctx& c, const void* x, float* slab, bool train) {
         // block 0 with nobody reading the full-resolution y afterwards (evaluation; training whose backward works from the pooled tensors):
         // the conv epilogue reduces along W and the pooling kernel finishes from a third of the data
         const bool poolw = i == 0 && b.s2d && b.yw != nullptr && b.aw != nullptr && b.pool_k == 3 && b.pool_s == 3 && b.cout == 64 && b.c_w >= 3 &&
-                           (!train || (b.bwd0_mode == 2 && b.amax != nullptr && b.ymax != nullptr));
+                           (!train || (b.poolw_train && b.bwd0_mode == 2 && b.amax != nullptr && b.ymax != nullptr));
         if (i == 0) {
             if (poolw) NIDT_TRY(nidt_conv_in_s2d_fprop_poolw(x, at(slab, b.off_w), bias, at(slab, b.off_gamma), b.yw, b.aw, stats, B, b.in_d, b.in_h,
                                                              b.in_w, p->input_scale, c.st));

@@ -134,7 +134,7 @@ class _BlockC(C.Structure):
                                              "wf", "wd", "wg_scratch")]
                 + [(n, C.c_int) for n in ("stats_tiles", "s2d", "block_n", "dgrad_block_n", "splits")]
                 + [("box", C.c_int * 4), ("dbox", C.c_int * 4), ("amax", C.c_void_p), ("gram", C.c_void_p), ("alg_scratch", C.c_void_p),
-                   ("yw", C.c_void_p), ("aw", C.c_void_p), ("bwd0_mode", C.c_int)])
+                   ("yw", C.c_void_p), ("aw", C.c_void_p), ("bwd0_mode", C.c_int), ("poolw_train", C.c_int)])
 
 
 class _PlanC(C.Structure):
@@ -346,11 +346,15 @@ class B200Engine:
                 b.amax = torch.empty(b.a.shape, dtype=torch.uint8, device=dev) if want_amax else None
                 self.gram = GramCache(lib, dev, in_dhw, self.input_scale, B) if self.alg_bwd0 else None
                 b.alg_scratch = (torch.empty(lib.nidt_conv_in_alg_scratch_floats(), dtype=torch.float32, device=dev) if self.alg_bwd0 else None)
-                # NIDT_POOLW: when nobody reads the full-resolution conv output afterwards (evaluation; training steps whose backward
-                # works from the pooled tensors), the conv epilogue reduces every 3 output columns to the pooling winner and the pooling
-                # kernel finishes from a third of the data (nidt_conv_in_s2d_fprop_poolw + nidt_bn_relu_pool3w_fwd)
-                self.poolw = (os.environ.get("NIDT_POOLW", "0") == "1" and b.s2d and b.ymax is not None and spec.cout == 64 and spec.k == 5
-                              and W >= 3)
+                # NIDT_POOLW: when nobody reads the full-resolution conv output afterwards, the conv epilogue reduces every 3 output
+                # columns to the pooling winner and the pooling kernel finishes from a third of the data (nidt_conv_in_s2d_fprop_poolw +
+                # nidt_bn_relu_pool3w_fwd); bit-identical results.  "eval" (default): evaluation batches only -- MEASURED at batch 16:
+                # evaluation 0.501 -> 0.456 ms, but a training step 1.10 -> 1.14 ms (with the BatchNorm statistics loop in the same
+                # epilogue warps the extra work costs the conv more than the smaller pooling pass saves); "1": training steps with the
+                # backward from pooled tensors too; "0": off.
+                pw_env = os.environ.get("NIDT_POOLW", "eval")
+                self.poolw = pw_env in ("1", "eval") and b.s2d and b.ymax is not None and spec.cout == 64 and spec.k == 5 and W >= 3
+                self.poolw_train = self.poolw and pw_env == "1"
                 if self.poolw:
                     Wp = (W - 3) // 3 + 1
                     b.yw = torch.empty((B, D, H, Wp, 64), dtype=bf, device=dev)
@@ -407,7 +411,7 @@ class B200Engine:
                 if self.alg_bwd0 and c.amax:
                     c.gram, c.alg_scratch = self.gram.batch.data_ptr(), b.alg_scratch.data_ptr()
                 if self.poolw and c.s2d:
-                    c.yw, c.aw = b.yw.data_ptr(), b.aw.data_ptr()
+                    c.yw, c.aw, c.poolw_train = b.yw.data_ptr(), b.aw.data_ptr(), int(self.poolw_train)
                 c.bwd0_mode = 1 if (self.fused_bwd0 and c.amax) else 0
             else:
                 c.wf, c.wd = ptr(b.wf), ptr(b.wd)
@@ -500,7 +504,7 @@ class B200Engine:
             stats = b.stats.data_ptr() if train else None
             bias = self._p(slab, s.conv + ".bias") if s.bias else None
             poolw = (i == 0 and getattr(self, "poolw", False) and b.s2d and self.s2d_wgrad
-                     and (not train or (self._mode == 2 and getattr(b, "amax", None) is not None)))
+                     and (not train or (self.poolw_train and self._mode == 2 and getattr(b, "amax", None) is not None)))
             if i == 0:
                 iD, iH, iW = b.in_dhw
                 if poolw:     # nobody reads the full-resolution y afterwards: reduced along W in the conv epilogue

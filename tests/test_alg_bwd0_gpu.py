@@ -151,7 +151,7 @@ def test_training_with_cached_gram_matrices_and_partial_batches():
 
 
 def test_forward_with_the_conv_epilogue_pooling_along_w_is_bit_identical(monkeypatch):
-    """NIDT_POOLW=1: when nobody reads the full-resolution conv output (evaluation; training with the backward from pooled tensors),
+    """NIDT_POOLW=1 (training steps too; the default "eval" uses it for evaluation batches only): when nobody reads the full-resolution conv output (evaluation; training with the backward from pooled tensors),
     the conv epilogue keeps the pooling winner of every 3 output columns and the pooling kernel finishes from those.  Same winners, same
     values: pooled activation, winner values / taps, every gradient, evaluation counters and logits must not change by a bit --
     including the channel with a negative BatchNorm weight (its winner is the window's MINIMUM of y)."""
@@ -161,7 +161,7 @@ def test_forward_with_the_conv_epilogue_pooling_along_w_is_bit_identical(monkeyp
     eng_p, _ = _engine(B)
     monkeypatch.setenv("NIDT_POOLW", "0")
     eng_s, _ = _engine(B)
-    assert eng_p.poolw and not eng_s.poolw
+    assert eng_p.poolw and eng_p.poolw_train and not eng_s.poolw
     x, y = _batch(B, seed=7)
     ids = [3, 1, 4, 2]
     for native_exec in (True, False):                      # executor / graph replay, and the Python launch loop
