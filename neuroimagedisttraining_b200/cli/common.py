@@ -84,6 +84,9 @@ def add_common_args(p: argparse.ArgumentParser, *, model="3DCNN", dataset="ABCD"
     g.add_argument("--spatial_parallel", action="store_true",
                    help="under torchrun: all ranks train every client together, each holding a depth slab of the activations "
                         "(for volumes / batches that do not fit one device); PyTorch engine")
+    g.add_argument("--preload", action="store_true",
+                   help="ABCD from --data_dir: read the whole HDF5 file into (pinned) host memory once and serve batches from there "
+                        "(row copies, zero-run-skipping uploads, device caches) instead of re-reading the file per batch")
     g.add_argument("--data_parallel", action="store_true",
                    help="under torchrun: all ranks train every client together on the sm_100a engine, each taking 1/world of every "
                         "mini-batch (BatchNorm statistics and gradients summed over the ranks); for few, large clients")
@@ -163,7 +166,7 @@ def setup(args, prefix: str, extra_identity: Optional[list] = None, loss_kind: O
     store = None
     if args.dataset == "ABCD":
         if args.data_dir:
-            store = HDF5VolumeStore(args.data_dir, args.labels_file)
+            store = HDF5VolumeStore(args.data_dir, args.labels_file, preload=bool(getattr(args, "preload", False)))
         else:
             n = args.synthetic_subjects or 20 * args.client_num_in_total
             n_sites = args.client_num_in_total if not args.rescale else min(21, args.client_num_in_total)

@@ -15,8 +15,10 @@ writer below, which follows the published file-format specification (HDF5 File F
 """
 from __future__ import annotations
 
+import os
 import struct
 import zlib
+from concurrent.futures import ThreadPoolExecutor
 from typing import Dict, Iterator, List, Optional, Tuple
 
 import numpy as np
@@ -113,6 +115,9 @@ def _parse_filters(body: bytes) -> List[Tuple[int, Tuple[int, ...]]]:
     return out
 
 
+READ_THREADS = max(1, min(8, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)))
+
+
 class ChunkedDataset:
     """Read-only view of a chunked (optionally shuffled / deflated / checksummed) dataset with the same face as :class:`Dataset`.
     The chunk index (a version-1 B-tree) is walked once; ``ds[i]``, ``ds[a:b]`` and ``ds[sorted_indices]`` decode only the chunks that
@@ -155,6 +160,12 @@ class ChunkedDataset:
     def _chunk(self, origin: Tuple[int, ...]) -> np.ndarray:
         if self._cache[0] == origin:
             return self._cache[1]
+        arr = self._decode(origin)
+        self._cache = (origin, arr)
+        return arr
+
+    def _decode(self, origin: Tuple[int, ...]) -> np.ndarray:
+        """One chunk, read and run back through the filter pipeline (no shared state: callable from several threads)."""
         n = int(np.prod(self.chunks))
         ent = self._index.get(origin)
         if ent is None:                                   # never written: fill value (0)
@@ -174,7 +185,6 @@ class ChunkedDataset:
                     isz = self.dtype.itemsize
                     buf = np.frombuffer(buf, np.uint8).reshape(isz, -1).T.tobytes() if isz > 1 else buf
             arr = np.frombuffer(buf, self.dtype, count=n).reshape(self.chunks)
-        self._cache = (origin, arr)
         return arr
 
     def _rows(self, rows: np.ndarray) -> np.ndarray:
@@ -183,17 +193,29 @@ class ChunkedDataset:
             return out
         c0 = self.chunks[0]
         grids = [range(0, s, c) for s, c in zip(self.shape[1:], self.chunks[1:])]
+        blocks: Dict[int, List[Tuple[int, int]]] = {}                 # first row of a chunk row-block -> [(position in out, row)]
         for j, r in enumerate(rows):
             r = int(r)
             if not 0 <= r < self.shape[0]:
                 raise IndexError(f"row {r} out of range")
-            base0 = r // c0 * c0
+            blocks.setdefault(r // c0 * c0, []).append((j, r))
+
+        def fill(base0: int, cached: bool) -> None:
             for rest in np.ndindex(*[len(g) for g in grids]) if grids else [()]:
                 origin = (base0,) + tuple(g[i] for g, i in zip(grids, rest))
-                ch = self._chunk(origin)
+                ch = self._chunk(origin) if cached else self._decode(origin)
                 sl_out = tuple(slice(o, min(o + c, s)) for o, c, s in zip(origin[1:], self.chunks[1:], self.shape[1:]))
                 sl_in = tuple(slice(0, s.stop - s.start) for s in sl_out)
-                out[(j,) + sl_out] = ch[(r - base0,) + sl_in]
+                for j, r in blocks[base0]:
+                    out[(j,) + sl_out] = ch[(r - base0,) + sl_in]
+
+        threads = min(READ_THREADS, len(blocks))
+        if threads > 1 and self._filters:             # inflating is the cost, and zlib releases the GIL: decode row-blocks side by side
+            with ThreadPoolExecutor(threads) as pool:
+                list(pool.map(lambda b: fill(b, False), blocks))
+        else:
+            for b in blocks:
+                fill(b, True)
         return out
 
     def __getitem__(self, key):
@@ -230,8 +252,7 @@ class File:
 
     # -- low-level helpers
     def _read(self, off: int, n: int) -> bytes:
-        self._f.seek(off)
-        b = self._f.read(n)
+        b = os.pread(self._f.fileno(), n, off)             # positional: safe from several decode threads at once
         if len(b) != n:
             raise UnsupportedHDF5(f"truncated file: wanted {n} bytes at offset {off}")
         return b

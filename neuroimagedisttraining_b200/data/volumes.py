@@ -153,10 +153,17 @@ def hdf5_backend():
 class HDF5VolumeStore(VolumeStore):
     """Reader for the reference's files: ``X`` volumes in one HDF5 (``alldatain8bitsnormalized.h5``),
     ``y``/``site`` in another (``dataset_all_labels_site.h5``; ``ABCD/data_loader.py:105-141``).
-    The file is opened once, not per batch.  Uses ``h5py`` when installed, else the built-in reader for plain contiguous files
-    (:mod:`.hdf5_mini`)."""
+    The file is opened once, not per batch.  Uses ``h5py`` when installed, else the built-in reader (:mod:`.hdf5_mini`: contiguous
+    and chunked / gzip / shuffle / fletcher32 layouts, chunk row-blocks inflated on several threads).
 
-    def __init__(self, volumes_path: str, labels_path: Optional[str] = None, scale: Optional[float] = None):
+    ``preload=True`` reads every volume once into host memory as 8 bits (pinned when CUDA is there) and serves batches from it: the
+    stagers then treat the store like the synthetic one -- row copies straight out of the pinned cache, zero-run-skipping uploads,
+    per-loader device caches -- instead of going back to the file (and, for compressed files, inflating again) for every batch.
+    The reference re-reads every batch through h5py (``ABCD/data_loader.py:105-141``).  Every rank holds the whole cache: meant for
+    datasets that fit in host memory ``world_size`` times (``--preload``)."""
+
+    def __init__(self, volumes_path: str, labels_path: Optional[str] = None, scale: Optional[float] = None, preload: bool = False,
+                 pin: bool = True, block_rows: int = 64):
         h5py = hdf5_backend()
         self._f = h5py.File(volumes_path, "r")
         self._X = self._f["X"]
@@ -169,10 +176,31 @@ class HDF5VolumeStore(VolumeStore):
             self.scale = scale
         elif not self._is_u8:
             self.scale = 1.0 / 255.0
+        self._cache = None
+        if preload:
+            n = len(self.labels)
+            buf = torch.empty((n,) + self.shape, dtype=torch.uint8)
+            if pin and torch.cuda.is_available():
+                buf = buf.pin_memory()
+            for a in range(0, n, block_rows):
+                b = min(n, a + block_rows)
+                xb = np.asarray(self._X[a:b])
+                if not self._is_u8:
+                    xb = np.clip(np.rint(xb * 255.0), 0, 255).astype(np.uint8)
+                buf[a:b] = torch.from_numpy(xb)
+            self._cache = buf
 
     def fetch(self, indices, out=None):
         """Rows in the order requested.  HDF5 fancy indexing wants increasing, unique indices: read sorted, then un-permute."""
         idx = np.asarray(indices).astype(np.int64)
+        if self._cache is not None:
+            ti = torch.from_numpy(idx)
+            y = torch.from_numpy(self.labels[idx])
+            if out is None:
+                return self._cache.index_select(0, ti), y
+            x = out[:len(idx)]
+            torch.index_select(self._cache, 0, ti, out=x)
+            return x, y
         uniq, inverse = np.unique(idx, return_inverse=True)
         xb = np.asarray(self._X[uniq])[inverse]
         if not self._is_u8:

@@ -122,3 +122,42 @@ def test_chunked_and_compressed_datasets_round_trip(tmp_path, compression, shuff
     store = HDF5VolumeStore(path)
     xb, yb = store.fetch([2, 7, 11])
     assert np.array_equal(xb.numpy(), X[[2, 7, 11]]) and np.array_equal(yb.numpy(), y[[2, 7, 11]])
+
+
+def test_preloaded_store_serves_the_same_volumes_and_parallel_decode_matches(tmp_path):
+    """``HDF5VolumeStore(preload=True)`` (the whole file read once into host memory, chunk row-blocks inflated on several threads)
+    hands out exactly what the per-batch reader does, in any index order; the threaded decode equals the one-thread decode."""
+    import time
+    from neuroimagedisttraining_b200.data import hdf5_mini
+    from neuroimagedisttraining_b200.data.volumes import HDF5VolumeStore
+    g = np.random.default_rng(3)
+    n, shape = 24, (20, 24, 22)
+    X = g.integers(0, 256, size=(n,) + shape, dtype=np.uint8)
+    X[:, :, :, :6] = 0
+    y = (g.random(n) > 0.5).astype(np.float32)
+    site = np.repeat(np.arange(4), 6).astype(np.int64)
+    p = str(tmp_path / "vol.h5")
+    hdf5_mini.write_file(p, {"X": X, "y": y, "site": site}, chunks={"X": (2,) + shape}, compression="gzip", shuffle=True)
+    lazy = HDF5VolumeStore(p)
+    t0 = time.time()
+    pre = HDF5VolumeStore(p, preload=True, block_rows=8)
+    t_pre = time.time() - t0
+    assert pre._cache is not None and tuple(pre._cache.shape) == (n,) + shape and t_pre < 60
+    for idx in ([5, 1, 1, 23, 0], list(range(n)), [7]):
+        a, ya = lazy.fetch(idx)
+        b, yb = pre.fetch(idx)
+        assert torch.equal(a, b) and torch.equal(ya, yb)
+        assert np.array_equal(b.numpy(), X[np.asarray(idx)])
+    out = torch.empty((8,) + shape, dtype=torch.uint8)
+    b, _ = pre.fetch([3, 2], out=out)
+    assert np.array_equal(b.numpy(), X[[3, 2]]) and b.data_ptr() == out.data_ptr()
+    # threaded == single-threaded decode
+    ds = hdf5_mini.File(p)["X"]
+    rows = np.arange(0, n, 3)
+    many = ds[rows]
+    old, hdf5_mini.READ_THREADS = hdf5_mini.READ_THREADS, 1
+    try:
+        one = hdf5_mini.File(p)["X"][rows]
+    finally:
+        hdf5_mini.READ_THREADS = old
+    assert np.array_equal(many, one) and np.array_equal(many, X[rows])
