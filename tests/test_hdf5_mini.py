@@ -61,6 +61,11 @@ def test_volume_store_and_cli_on_a_file(tmp_path):
                                    str(tmp_path / "lab.h5"), "--client_num_in_total", "3", "--batch_size", "4", "--epochs", "1", "--comm_round", "1",
                                    "--device", "cpu", "--log_dir", str(tmp_path / "LOG")])
     assert len(stat["global_test_acc"]) == 2
+    # --preload: the same job served from the in-memory copy of the file gives the same result
+    stat2 = main_sailentgrads.main(["--model", "tiny3DCNN", "--in_shape", "32,32,32", "--data_dir", str(tmp_path / "vol.h5"), "--labels_file",
+                                    str(tmp_path / "lab.h5"), "--client_num_in_total", "3", "--batch_size", "4", "--epochs", "1", "--comm_round", "1",
+                                    "--device", "cpu", "--log_dir", str(tmp_path / "LOG2"), "--preload"])
+    assert [float(a) for a in stat2["global_test_acc"]] == [float(a) for a in stat["global_test_acc"]]
 
 
 def test_features_outside_the_subset_are_refused_with_a_reason(tmp_path):
