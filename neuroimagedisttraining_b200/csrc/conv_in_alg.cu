@@ -12,7 +12,7 @@
 //   sx[t]    = sum over all p of x~[p (+) t]                                    (row 125 of the padded 128 x 128 G: a constant-1 tap)
 //
 // G and sx depend on the INPUT VOLUME only -- not on the weights, not on the step.  They are computed once per sample
-// (gram_plane_kernel + gram_reduce_kernel, ~0.2 ms) and kept on the device keyed by the sample's id (ops/engine_b200.py: GramCache);
+// (gram_plane_kernel + gram_reduce_kernel, 0.33 ms measured) and kept on the device keyed by the sample's id (ops/engine_b200.py: GramCache);
 // a step adds up the matrices of its 16 samples (gram_sum_kernel).  What is left per step is S (alg_sparse_kernel: 8.5 M patch
 // reads instead of 4 M positions x 64 channels x 216 taps on the tensor cores and two 506 MB passes) and a 64 x 125 x 125 fp64
 // product (alg_combine_kernel).  The bias gradient is exactly zero (BatchNorm subtracts the batch mean right after the conv).

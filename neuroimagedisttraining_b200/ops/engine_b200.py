@@ -170,7 +170,7 @@ def choose_box(W: int, H: int, D: int, N: int, max_rows: int = 128) -> Tuple[int
 
 class GramCache:
     """Per-sample Gram matrices of the first layer's input patches (``csrc/conv_in_alg.cu``), on the device, keyed by the sample's
-    id in the volume store.  They depend on the volume only, so a sample pays for its matrix (~0.2 ms) the first time it is trained
+    id in the volume store.  They depend on the volume only, so a sample pays for its matrix (0.33 ms) the first time it is trained
     on and never again; 64 KiB per sample.  ``NIDT_GRAM_CACHE_MB`` bounds the buffer (default 8192; when full it starts over)."""
 
     def __init__(self, lib, device, in_shape, scale: float, max_batch: int):
