@@ -313,8 +313,13 @@ def run_ours(a):
         api.run_round(rnd[0], mask=api.mask)
         rnd[0] += 1
 
+    def gram_built():
+        """Per-sample Gram matrices (first-layer backward, csrc/conv_in_alg.cu) computed so far on this rank, all client lanes."""
+        return sum(int(getattr(getattr(l.engine, "gram", None), "built", 0) or 0) for l in trainer.all_lanes())
+
     for _ in range(a.warmup):
         one_round(0)
+    g_warm = gram_built()
     # ---- e2e: the public API as a user runs it (staging="client"): every volume a round touches is copied host -> device from
     # pinned memory inside the round (once per client-round, not once per epoch / per evaluated model), metrics are read back
     e2e = None
@@ -325,6 +330,7 @@ def run_ours(a):
                "d2h_bytes_per_step": (xfer.D2H_BYTES - d0) / a.steps, "d2h_copies_per_step": (xfer.D2H_COPIES - c0) / a.steps,
                "ms_per_step": 1e3 * t_e2e / a.steps, "staging": "client (per-client-round device cache, uploads queued ahead on a copy stream)",
                "bytes_scope": "rank 0" if ctx.world_size > 1 else "all"}
+    g_e2e = gram_built()
     # ---- device-timed: the same API with staging="resident" (whole store uploaded once, outside the timed region)
     trainer.set_staging("resident")
     one_round(0)
@@ -332,8 +338,10 @@ def run_ours(a):
     if ctx.is_main:
         clk.start()
     n0 = native.LAUNCH_COUNT
+    g_dev0 = gram_built()
     t_dev = timed_rounds(one_round, a.steps, ctx, device)
     launches = native.LAUNCH_COUNT - n0
+    g_dev1 = gram_built()
     clocks = clk.stop() if ctx.is_main else None
     stat = api.finalize_stats()
     check = agg_check(api, ctx, device) if ctx.world_size > 1 else None
@@ -348,6 +356,14 @@ def run_ours(a):
             "parallelism": "client-parallel x%d (one process per GPU)" % ctx.world_size, "aggregation": api.aggregator.mode,
             "client_lanes_per_gpu": len(trainer.all_lanes()),
             "value_staging": "resident (SlabTrainer.set_staging('resident'): store uploaded once before the timed region)",
+            # disclosure: the first layer's weight gradient is computed from the pooled tensors plus the Gram matrix of the batch's input
+            # patches, and those matrices are an input-only quantity cached per sample (0.33 ms each, paid the first time a sample is
+            # trained on -- in the warm-up rounds here).  The gradient is exact (tests/test_alg_bwd0_gpu.py, tests/test_alg_reference.py);
+            # NIDT_ALG_BWD0=0 runs the dY-based kernels instead (106.4 ms/round at 1 GPU on the same box).
+            "first_layer_backward": ({"form": "pooled tensors + cached per-sample Gram matrices of the input patches (exact gradient)",
+                                      "gram_matrices_built_rank0": {"before_timed_rounds": g_warm, "in_e2e_rounds": g_e2e - g_warm,
+                                                                    "in_device_timed_rounds": g_dev1 - g_dev0},
+                                      "off_switch": "NIDT_ALG_BWD0=0"} if g_dev1 > 0 else {"form": "dY-based kernels"}),
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "mask_generation_s": mask_s, "agg_check": check,
             "global_test_acc": float(stat["global_test_acc"][-1]) if stat["global_test_acc"] else None,
             "phase_time_s": {k: round(v["total_s"], 4) for k, v in stat["phase_time_s"].items()},
