@@ -88,8 +88,9 @@ def add_common_args(p: argparse.ArgumentParser, *, model="3DCNN", dataset="ABCD"
                    help="ABCD from --data_dir: read the whole HDF5 file into (pinned) host memory once and serve batches from there "
                         "(row copies, zero-run-skipping uploads, device caches) instead of re-reading the file per batch")
     g.add_argument("--data_parallel", action="store_true",
-                   help="under torchrun: all ranks train every client together on the sm_100a engine, each taking 1/world of every "
-                        "mini-batch (BatchNorm statistics and gradients summed over the ranks); for few, large clients")
+                   help="under torchrun: all ranks train every client together, each taking 1/world of every mini-batch (BatchNorm "
+                        "statistics and gradients summed over the ranks): the sm_100a engine on GPUs, PyTorch ops with --device cpu / "
+                        "--engine torch; for few, large clients")
     g.add_argument("--rescale", action="store_true", help="ABCD: cut the site-ordered data into client_num_in_total equal shards")
     g.add_argument("--correct_eval_loss", action="store_true", help="evaluate BCEWithLogits(logit) instead of the reference's BCEWithLogits(sigmoid(logit))")
     return p
@@ -149,7 +150,8 @@ def setup(args, prefix: str, extra_identity: Optional[list] = None, loss_kind: O
     if spatial and data_par:
         raise SystemExit("--spatial_parallel and --data_parallel are alternatives")
     dp_group = None
-    if data_par:
+    dp_native = data_par and ctx.device.type == "cuda" and getattr(args, "engine", "auto") in ("auto", "b200") and args.dataset == "ABCD"
+    if dp_native:
         from ..ops.engine_dp import DistGroup
         dp_group = DistGroup(ctx.group)
     if spatial or data_par:
@@ -186,11 +188,13 @@ def setup(args, prefix: str, extra_identity: Optional[list] = None, loss_kind: O
     if spatial:
         from ..fl.engine import SpatialTorchEngine
         engine = SpatialTorchEngine(model, device, loss_kind=loss_kind, volumetric=store is not None, input_scale=getattr(store, "scale", 1.0))
-    elif data_par:
-        if store is None or device.type != "cuda":
-            raise SystemExit("--data_parallel runs the sm_100a engine: needs CUDA devices and a volumetric dataset (ABCD)")
+    elif dp_native:
         from ..ops.engine_dp import DataParallelB200Engine
         engine = DataParallelB200Engine(model, device, dp_group, max_batch=args.batch_size, input_scale=store.scale, seed=args.seed)
+    elif data_par:      # CPUs / --engine torch / image datasets: the same split on PyTorch ops (SyncBN + gradient all-reduce)
+        from ..fl.engine import DataParallelTorchEngine
+        engine = DataParallelTorchEngine(model, device, ctx.group, loss_kind=loss_kind, volumetric=store is not None,
+                                         input_scale=getattr(store, "scale", 1.0))
     elif device.type == "cuda" and args.engine in ("auto", "b200") and store is not None:
         try:
             from ..ops.engines import make_native_engine

@@ -1,6 +1,6 @@
 from .trainer import ModelTrainer, SlabTrainer  # noqa: F401
 from .client import Client  # noqa: F401
-from .engine import TorchEngine, SpatialTorchEngine, StepHParams, EvalCounters  # noqa: F401
+from .engine import TorchEngine, SpatialTorchEngine, DataParallelTorchEngine, StepHParams, EvalCounters  # noqa: F401
 from .fedavg import FedAvgAPI  # noqa: F401
 from .salientgrads import SalientGradsAPI, SailentGradsAPI  # noqa: F401
 from .local import LocalAPI  # noqa: F401

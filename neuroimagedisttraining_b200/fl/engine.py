@@ -192,3 +192,44 @@ class SpatialTorchEngine(TorchEngine):
             loss = F.cross_entropy(logits, y.long(), reduction="sum")
             correct = (logits.argmax(1) == y.long()).float().sum()
         counters.buf += torch.stack([correct.double(), loss.double(), torch.tensor(float(y.shape[0]), dtype=torch.float64, device=self.device)])
+
+
+class DataParallelTorchEngine(TorchEngine):
+    """:class:`TorchEngine` whose training step covers ``1 / world`` of every mini-batch: every rank executes the same FL programme
+    on the same clients (``ReplicatedContext``), takes its contiguous share of each batch, BatchNorm layers use the statistics of
+    the WHOLE batch (:mod:`..parallel.syncbn`: one small all-reduce per layer forward and backward -- the reference's
+    SynchronizedBatchNorm, ``batchnorm_utils.py:150-237``, as one process per device), and the gradients are summed over the ranks,
+    so the replicas of the model never diverge.  The loss is the sum over a rank's samples divided by the WHOLE batch size, which puts
+    every rank's backward pass in the same scale whatever the shares are (ragged and empty shares included).  The PyTorch-op
+    counterpart of :class:`~..ops.engine_dp.DataParallelB200Engine`; with gloo it runs on CPUs (``--data_parallel --device cpu``)."""
+
+    def __init__(self, model: nn.Module, device, group=None, **kw):
+        import torch.distributed as dist
+        from ..parallel.syncbn import convert_sync_batchnorm
+        super().__init__(convert_sync_batchnorm(model, group), device, **kw)
+        self._dist, self.group = dist, group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+
+    def compute_grads(self, x, y, train_mode: bool = True) -> torch.Tensor:
+        from ..ops.engine_dp import share
+        B = int(x.shape[0])
+        lo, hi = share(B, self.world, self.rank)
+        self.model.train(train_mode)
+        self.grad.flat.zero_()
+        for name, p in self.model.named_parameters():
+            if p.grad is None or p.grad.data_ptr() != self.grad.view(name).data_ptr():
+                p.grad = self.grad.view(name)
+        out = self.model(self._prep(x[lo:hi]))
+        if isinstance(out, (list, tuple)):
+            out = out[0]
+        yl = y[lo:hi].to(self.device)
+        if self.loss_kind == "bce":
+            loss = F.binary_cross_entropy_with_logits(out.float().flatten(), yl.float().flatten(), reduction="sum") / B
+        else:
+            loss = F.cross_entropy(out.float(), yl.long(), reduction="sum") / B
+        loss.backward()
+        self._dist.all_reduce(self.grad.flat, group=self.group)
+        total = loss.detach().clone()
+        self._dist.all_reduce(total, group=self.group)
+        return total
+

@@ -119,3 +119,36 @@ def test_spatial_parallel_cli_run_equals_the_single_process_run(tmp_path):
         torch.testing.assert_close(ck2["state_dict"][k].float(), v.float(), rtol=1e-4, atol=1e-5, msg=lambda m: f"{k}: {m}")
     assert all(torch.equal(ck1["mask"][k], ck2["mask"][k]) for k in ck1["mask"])
     assert s1["global_test_acc"] == s2["global_test_acc"] and s1["person_test_acc"] == s2["person_test_acc"]
+
+
+def test_data_parallel_cli_run_equals_the_single_process_run(tmp_path):
+    """``--data_parallel`` under torchrun (2 and 3 gloo ranks, PyTorch-op engine): every rank takes its share of each mini-batch
+    (batch 4 on 3 ranks = 2 + 1 + 1, the last batches of a client are smaller still), BatchNorm statistics and gradients are summed
+    over the ranks; global model, mask and accuracies equal the plain one-process run; only the real rank 0 writes files."""
+    import json
+    common = ["--model", "tiny3DCNN", "--in_shape", "32,32,32", "--client_num_in_total", "3", "--synthetic_subjects", "30", "--batch_size", "4",
+              "--epochs", "1", "--comm_round", "2", "--device", "cpu", "--frac", "1.0", "--lr", "0.02", "--checkpoint_every", "1"]
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
+    outs = {}
+    for tag, n in (("one", 1), ("two", 2), ("three", 3)):
+        launcher = [sys.executable, "-m"] if n == 1 else [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+                                                          "--master-addr", "127.0.0.1", "--master-port", str(29900 + os.getpid() % 90 + n), "-m"]
+        d = tmp_path / tag
+        cmd = launcher + ["neuroimagedisttraining_b200.cli.main_sailentgrads"] + common + ["--log_dir", str(d / "LOG"), "--checkpoint_path", str(d / "ck.pt")]
+        if n > 1:
+            cmd.append("--data_parallel")
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=400, env=env, cwd=ROOT)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+        files = os.listdir(d / "LOG" / "ABCD")
+        assert sum(f.endswith(".jsonl") for f in files) == 1
+        summary = [json.loads(l) for l in open(d / "LOG" / "ABCD" / next(f for f in files if f.endswith(".jsonl")))][-1]
+        outs[tag] = (torch.load(d / "ck.pt", weights_only=False), summary)
+    ck1, s1 = outs["one"]
+    for tag in ("two", "three"):
+        ck2, s2 = outs[tag]
+        assert ck1["round"] == ck2["round"] == 1
+        for k, v in ck1["state_dict"].items():
+            torch.testing.assert_close(ck2["state_dict"][k].float(), v.float(), rtol=2e-4, atol=2e-5, msg=lambda m: f"{tag} {k}: {m}")
+        assert all(torch.equal(ck1["mask"][k], ck2["mask"][k]) for k in ck1["mask"])
+        assert s1["global_test_acc"] == s2["global_test_acc"] and s1["person_test_acc"] == s2["person_test_acc"]
+
