@@ -8,7 +8,8 @@ Per kernel: FLOPs of the GEMM-shaped work (2*M*N*K), the bytes that MUST cross H
 every output written once; bf16 activations, 8-bit input volume, fp32 weight gradients), the time each would take at the measured
 bf16 rate / copy bandwidth, and the achieved fraction of the binding one.  Compulsory traffic is a lower bound of what the kernel
 really moves, so a fraction is an upper bound of how close the kernel is to ITS roofline only when re-reads are absent -- the ncu
-DRAM counters in ``profiles/ncu_all_kernels_v2.md`` give the real bytes.
+DRAM counters in ``profiles/ncu_all_kernels_v2.md`` give the real bytes.  ``conv_in_alg_wgrad`` (first-layer weight gradient from pooled
+tensors) is CUDA-core work bound by shared-memory loads: its row compares against fp32 FMA issue and HBM only for orientation.
 """
 from __future__ import annotations
 
@@ -57,6 +58,12 @@ def kernel_model(name: str, idx, L):
         return 0.0, r["conv_elems"] * 2 + out
     if name.startswith("bn_relu_pool_bwd"):
         return 0.0, r["conv_elems"] * 2 * 2 + r["pool_elems"] * 2 * 2  # read y, write dy (conv resolution); read pooled dy + max
+    if name.startswith("bn_pool3_bwd_stats"):
+        return 0.0, r["pool_elems"] * 2 * 2                           # the reductions read the pooled winner values and gradients only
+    if name.startswith("conv_in_alg_wgrad"):
+        # one 125-tap patch per pooling window and channel; the input volume (8 bit), winner taps (8 bit) and pooled gradients
+        # (bf16) are read once.  The kernel's real bound is its shared-memory loads (75 per patch), see ncu_conv_in_alg_sparse.txt.
+        return 2.0 * r["pool_elems"] * r["K"], r["in_elems"] + r["pool_elems"] * 3
     return None
 
 
@@ -91,6 +98,13 @@ def main(argv=None):
         t_math, t_mem = flops / tf * 1e3, nbytes / bw * 1e3
         roof = max(t_math, t_mem)
         modelled += tmin
+        if name.startswith("conv_in_alg_wgrad"):
+            # CUDA-core kernel: 75 32-bit shared-memory loads per (window, channel) patch, one 32-lane wavefront per clock and SM
+            sm_clk = float(peaks.get("sm_max_mhz", 1965.0)) * 1e6
+            t_smem = L[idx]["pool_elems"] * 75 / 32 / 148 / sm_clk * 1e3
+            lines.append(f"| `{label}` | {tmin:.4f} | {flops / 1e9:.1f} (fp32 FMA) | {nbytes / 1e6:.1f} | - | {t_mem:.4f} (HBM), {t_smem:.4f} (shared-memory loads) | "
+                         f"shared memory | {t_smem / tmin:.2f} |")
+            continue
         lines.append(f"| `{label}` | {tmin:.4f} | {flops / 1e9:.1f} | {nbytes / 1e6:.1f} | {t_math:.4f} | {t_mem:.4f} | "
                      f"{'math' if t_math >= t_mem else 'memory'} | {roof / tmin:.2f} |")
     lines += ["", f"Sum of kernel minima {total:.3f} ms, of which {modelled:.3f} ms in kernels with a bandwidth / math roofline; the rest is "
