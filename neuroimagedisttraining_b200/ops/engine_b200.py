@@ -341,7 +341,10 @@ class B200Engine:
                 # patch per pooling window + the batch's cached patch Gram matrix (csrc/conv_in_alg.cu); used for the steps whose
                 # sample ids the caller supplies (``batch_ids``), the dY-based kernels otherwise.
                 self.fused_bwd0 = os.environ.get("NIDT_FUSED_BWD0", "0") == "1"
-                self.alg_bwd0 = os.environ.get("NIDT_ALG_BWD0", "1") != "0" and b.s2d and b.ymax is not None and spec.cout == 64 and spec.k == 5
+                # (pooled width <= 19: the sparse pass walks one strip of up to 19 windows per unit; wider rows are split into two strips,
+                # a path no measured configuration has exercised, so such shapes keep the dY-based kernels)
+                self.alg_bwd0 = (os.environ.get("NIDT_ALG_BWD0", "1") != "0" and b.s2d and b.ymax is not None and spec.cout == 64 and spec.k == 5
+                                 and W >= 3 and (W - 3) // 3 + 1 <= 19)
                 want_amax = b.s2d and b.ymax is not None and spec.cout == 64 and (self.fused_bwd0 or self.alg_bwd0)
                 b.amax = torch.empty(b.a.shape, dtype=torch.uint8, device=dev) if want_amax else None
                 self.gram = GramCache(lib, dev, in_dhw, self.input_scale, B) if self.alg_bwd0 else None
